@@ -1,0 +1,164 @@
+#!/usr/bin/env python3
+"""Build the UNMODIFIED reference (w3ntao/pbrt-minus) for sm_100 into oracle/_ref/.
+
+TEST INFRASTRUCTURE ONLY. Nothing under oracle/ is on the product path.
+
+The reference is a CUDA-only program (no CPU render path), so "the reference itself" can only be
+run on the GPU box.  This recipe compiles its sources where they lie under /root/reference (never
+copied into the repo) with two headless shims first on the include path:
+
+  shims/pbrt/gui/gl_helper.h   - no GLFW/OpenGL (no graphics stack on either machine)
+  shims/ext/tinyexr/tinyexr.h  - the tinyexr submodule is missing from the archive
+
+Outputs (all git-ignored, all travel to the GPU box with the gpurun snapshot):
+
+  oracle/_ref/pbrt-minus-ref   the reference CLI; its Film::write_to_png additionally dumps the
+                               linear float RGB film next to the PNG (<name>.f32, W*H*3 floats);
+                               the dump is injected into a generated copy of base/film.cu at build
+                               time (oracle/_ref/gen/film.cu), nothing else is touched.
+  oracle/_ref/ref_trace        our ID-recording harness (ref_trace.cu) linked against the
+                               reference's own objects: builds the reference HLBVH over a raw
+                               triangle soup and traces ray files with the reference's traversal
+                               order and the reference's Primitive::intersect, recording the
+                               winning primitive index (the reference API returns none).
+  oracle/_ref/ref_probe        host-only probe (ref_probe.cu): calls the reference's
+                               __host__ __device__ functions on the CPU to emit golden vectors.
+
+Usage: python oracle/ref_build/build_ref.py [-j N] [--only probe|trace|cli]
+"""
+import argparse
+import concurrent.futures as cf
+import os
+import re
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(os.path.dirname(HERE))
+REF = os.environ.get("PBRT_MINUS_REF", "/root/reference")
+OUT = os.path.join(REPO, "oracle", "_ref")
+OBJ = os.path.join(OUT, "obj")
+GEN = os.path.join(OUT, "gen")
+
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+COMMON = ["-std=c++20", "--expt-relaxed-constexpr", "-arch=sm_100", "-O3", "-w",
+          "-I" + os.path.join(HERE, "shims"), "-I" + os.path.join(REF, "src")]
+
+
+def run(cmd):
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(" ".join(cmd) + "\n" + r.stdout + "\n")
+        raise SystemExit(1)
+    return r.stdout
+
+
+def newer(src, dst):
+    return (not os.path.exists(dst)) or os.path.getmtime(src) > os.path.getmtime(dst)
+
+
+def reference_sources():
+    cm = open(os.path.join(REF, "CMakeLists.txt")).read()
+    return re.findall(r"^\s*(src/pbrt/\S+\.cu)\s*$", cm, flags=re.M)
+
+
+def gen_film_dump():
+    """Generated copy of base/film.cu whose write_to_png also dumps the float film."""
+    src = open(os.path.join(REF, "src/pbrt/base/film.cu")).read()
+    marker = "    // Encode the image"
+    assert src.count(marker) == 1, "reference film.cu changed; update the dump injection"
+    dump = r'''
+    {   // [oracle/ref_build] float dump of the linear output RGB (Film::get_pixel_rgb)
+        std::vector<float> raw(size_t(width) * height * 3);
+        for (int y = 0; y < height; y++) {
+            for (int x = 0; x < width; x++) {
+                const auto c = get_pixel_rgb(Point2i(x, y), splat_scale);
+                raw[3 * (size_t(y) * width + x) + 0] = c.r;
+                raw[3 * (size_t(y) * width + x) + 1] = c.g;
+                raw[3 * (size_t(y) * width + x) + 2] = c.b;
+            }
+        }
+        if (FILE *fp = fopen((filename + ".f32").c_str(), "wb")) {
+            fwrite(raw.data(), sizeof(float), raw.size(), fp);
+            fclose(fp);
+        }
+    }
+'''
+    os.makedirs(GEN, exist_ok=True)
+    path = os.path.join(GEN, "film.cu")
+    new = src.replace(marker, dump + marker)
+    if not os.path.exists(path) or open(path).read() != new:
+        open(path, "w").write(new)
+    return path
+
+
+def build_probe():
+    """Host-only probe of the reference's integer paths -> tests/golden/ref_probe.json."""
+    os.makedirs(OUT, exist_ok=True)
+    exe = os.path.join(OUT, "ref_probe")
+    run([NVCC, "-std=c++20", "--expt-relaxed-constexpr", "-O2", "-w", "-Wno-deprecated-gpu-targets",
+         "-I" + os.path.join(HERE, "shims"), "-I" + os.path.join(REF, "src"),
+         os.path.join(HERE, "ref_probe.cu"), "-o", exe])
+    out = run([exe])
+    gold = os.path.join(REPO, "tests", "golden", "ref_probe.json")
+    open(gold, "w").write(out)
+    print("wrote", gold)
+    return 0
+
+
+def compile_one(job):
+    src, obj, extra = job
+    if newer(src, obj):
+        run([NVCC] + COMMON + extra + ["-dc", src, "-o", obj])
+    return obj
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("-j", type=int, default=os.cpu_count() or 4)
+    ap.add_argument("--only", default="")
+    args = ap.parse_args()
+    if not os.path.isdir(REF):
+        print("reference tree not present at %s; keeping prebuilt oracle/_ref as is" % REF)
+        return 0
+    os.makedirs(OBJ, exist_ok=True)
+
+    jobs = []
+    for rel in reference_sources():
+        src = os.path.join(REF, rel)
+        if rel == "src/pbrt/base/film.cu":
+            src = gen_film_dump()
+        obj = os.path.join(OBJ, rel.replace("/", "_")[:-3] + ".o")
+        jobs.append((src, obj, []))
+    ext = [("src/ext/lodepng/lodepng.cpp", "ext_lodepng.o"), ("src/ext/rply/rply.cpp", "ext_rply.o")]
+    for rel, o in ext:
+        jobs.append((os.path.join(REF, rel), os.path.join(OBJ, o), ["-x", "cu"] if False else []))
+    if args.only == "probe":
+        return build_probe()
+    for name in ("ref_trace",):
+        p = os.path.join(HERE, name + ".cu")
+        if os.path.exists(p):
+            jobs.append((p, os.path.join(OBJ, "harness_" + name + ".o"), []))
+
+    with cf.ThreadPoolExecutor(args.j) as ex:
+        objs = list(ex.map(compile_one, jobs))
+
+    main_o = [o for o in objs if o.endswith("src_pbrt_main.o")]
+    harness = [o for o in objs if os.path.basename(o).startswith("harness_")]
+    lib = [o for o in objs if o not in main_o and o not in harness]
+    link = [NVCC, "-arch=sm_100"]
+    tail = ["-lz", "-lpthread"]
+    if args.only == "":
+        build_probe()
+    if args.only in ("", "cli"):
+        run(link + main_o + lib + tail + ["-o", os.path.join(OUT, "pbrt-minus-ref")])
+    for h in harness:
+        name = os.path.basename(h)[len("harness_"):-2]
+        if args.only in ("", name.replace("ref_", "")):
+            run(link + [h] + lib + tail + ["-o", os.path.join(OUT, name)])
+    print("oracle/_ref built:", sorted(f for f in os.listdir(OUT) if not os.path.isdir(os.path.join(OUT, f))))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
