@@ -1,0 +1,241 @@
+/*
+ * b200pt.h -- C-ABI of libb200pt.so, the B200-native (sm_100a) wavefront path-tracing core that
+ * replaces the reference's HLBVH accelerator and WavefrontPathIntegrator.
+ *
+ * The reference (w3ntao/pbrt-minus) has no FFI: its host front-end reaches the hot path at two
+ * C++ call sites, and this header is what a binding at those sites calls instead:
+ *
+ *   scene/scene_builder.cu:912        allocator.create<HLBVH>(gpu_primitives, "for ROOT", ...)
+ *                                       -> b200pt_scene_create + b200pt_bvh_build
+ *   scene/scene_builder.cu:1036-1043  wavefront_path_integrator->render(film, preview);
+ *                                     film->write_to_png(output_filename)
+ *                                       -> b200pt_film_create + b200pt_render + b200pt_film_read
+ *   accelerator/hlbvh.h:96-100        HLBVH::intersect / fast_intersect (per ray, device side)
+ *                                       -> b200pt_trace / b200pt_trace_device (batched, ids out)
+ *
+ * Conventions: plain pointers and sizes only; host arrays in (copied, caller keeps ownership),
+ * opaque handles out; one b200pt_scene per GPU, driven by one host thread; every call returns 0
+ * or a negative b200pt_status and never exits, throws or falls back to the CPU (the reference
+ * prints and exit(1)s, gpu/macro.h:23-48).  b200pt_last_error() gives the thread-local message.
+ * Pointers whose name ends in _dev are DEVICE pointers on the scene's GPU.
+ */
+#ifndef B200PT_H
+#define B200PT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200PT_ABI_VERSION 1
+
+typedef enum {
+    B200PT_OK = 0,
+    B200PT_ERR_INVALID = -1,   /* bad argument / inconsistent description */
+    B200PT_ERR_CUDA = -2,      /* a CUDA runtime call failed; message has the CUDA error string */
+    B200PT_ERR_NO_DEVICE = -3, /* no usable sm_100 device: there is NO CPU fallback */
+    B200PT_ERR_STATE = -4,     /* call order violated (e.g. trace before bvh_build) */
+    B200PT_ERR_NCCL = -5,
+    B200PT_ERR_UNSUPPORTED = -6
+} b200pt_status;
+
+typedef struct b200pt_scene b200pt_scene; /* owns all device memory of one GPU's scene replica */
+typedef struct b200pt_film b200pt_film;   /* W*H*{sum_x,sum_y,sum_z,sum_w} fp32 on device     */
+
+/* ---- spectra (base/spectrum.cu:122-201) ------------------------------------------------- */
+enum {
+    B200PT_SPEC_CONSTANT = 0,       /* c[0]                                  spectra/constant_spectrum.h */
+    B200PT_SPEC_RGB_ALBEDO = 1,     /* sigmoid(c0 l^2 + c1 l + c2)           spectra/rgb_albedo_spectrum.h */
+    B200PT_SPEC_RGB_UNBOUNDED = 2,  /* c[3] * sigmoid(...)                   spectra/rgb_unbounded_spectrum.h */
+    B200PT_SPEC_RGB_ILLUMINANT = 3, /* c[3] * sigmoid(...) * illuminant(l)   spectra/rgb_illuminant_spectrum.cu */
+    B200PT_SPEC_PIECEWISE = 4,      /* n (lambda,value) knots, lerp          spectra/piecewise_linear_spectrum.cu:82-103 */
+    B200PT_SPEC_DENSE = 5           /* n = 471 values at 360..830 nm, 1 nm   spectra/densely_sampled_spectrum.h */
+};
+typedef struct {
+    int32_t type;
+    float c[4];           /* constant value, or sigmoid c0,c1,c2 and scale */
+    int32_t n;            /* knots (PIECEWISE) or samples (DENSE) */
+    const float *lambda;  /* [n] PIECEWISE only */
+    const float *value;   /* [n] */
+} b200pt_spectrum;
+
+/* ---- materials (base/material.cu:97-131) ------------------------------------------------ */
+enum { B200PT_MAT_DIFFUSE = 0, B200PT_MAT_CONDUCTOR = 1, B200PT_MAT_DIELECTRIC = 2 };
+typedef struct {
+    int32_t type;
+    int32_t reflectance; /* spectrum id: diffuse reflectance, or conductor "reflectance" (-1: use eta/k) */
+    int32_t eta;         /* spectrum id: conductor eta / dielectric eta */
+    int32_t k;           /* spectrum id: conductor k */
+    float u_roughness, v_roughness;
+    int32_t remap_roughness; /* materials/conductor_material.cu:52-75: alpha = sqrt(roughness) */
+} b200pt_material;
+
+/* ---- lights: one DiffuseAreaLight per emissive triangle (base/light.cu:56-75) ------------ */
+typedef struct {
+    int32_t triangle;  /* index into the triangle array */
+    int32_t spectrum;  /* Lemit spectrum id */
+    float scale;       /* already divided by the photometric integral (lights/diffuse_area_light.cu:17-26) */
+    int32_t two_sided;
+} b200pt_light;
+
+/* ---- spheres (shapes/sphere.h:71-125); intersected in object space ----------------------- */
+typedef struct {
+    float render_from_object[16]; /* row-major 4x4 */
+    float object_from_render[16];
+    float radius, z_min, z_max, phi_max; /* phi_max in radians; theta range derived from z */
+    int32_t reverse_orientation, transform_swaps_handedness;
+    int32_t material; /* material id */
+    int32_t light;    /* -1: spheres as emitters are not supported */
+} b200pt_sphere;
+
+/* ---- camera (cameras/perspective.cu:7-86) ------------------------------------------------ */
+typedef struct {
+    float camera_from_raster[16]; /* row-major 4x4 */
+    float render_from_camera[16];
+    float lens_radius, focal_distance;
+} b200pt_camera;
+
+/* ---- pixel filter, tabulated for importance sampling (filters/filter_sampler.{h,cu}) ----- */
+typedef struct {
+    float radius_x, radius_y;
+    int32_t nx, ny;     /* table resolution: 32*radius per axis */
+    const float *f;     /* [ny*nx] filter values at the cell centres (signed) */
+} b200pt_filter;
+
+/* ---- film / sensor (film/rgb_film.cu:27-47, film/pixel_sensor.h:19-26) ------------------- */
+typedef struct {
+    int32_t width, height;
+    const float *cie_x, *cie_y, *cie_z; /* 471 samples, 360..830 nm (sensor = CIE 1931 XYZ) */
+    float imaging_ratio;
+    float output_rgb_from_sensor_rgb[9]; /* row-major 3x3 */
+    const float *illuminant;             /* 471 samples: colour-space illuminant (D65), normalised */
+} b200pt_film_desc;
+
+typedef struct {
+    int64_t n_vertices;
+    const float *P;            /* [n_vertices*3] render-space positions */
+    const float *N;            /* optional [n_vertices*3] shading normals */
+    const float *uv;           /* optional [n_vertices*2] */
+    int64_t n_triangles;
+    const int32_t *indices;    /* [n_triangles*3] */
+    const int32_t *tri_material; /* optional [n_triangles]; default 0 */
+    const int32_t *tri_light;    /* optional [n_triangles]; -1 = not emissive */
+    const uint8_t *tri_flip;     /* optional [n_triangles]; reverse_orientation ^ swaps_handedness */
+    int32_t n_spheres;
+    const b200pt_sphere *spheres;
+    int32_t n_spectra;
+    const b200pt_spectrum *spectra;
+    int32_t n_materials;
+    const b200pt_material *materials;
+    int32_t n_lights;
+    const b200pt_light *lights;
+    const b200pt_camera *camera; /* may be NULL for traversal-only scenes */
+    const b200pt_filter *filter;
+    const b200pt_film_desc *film;
+} b200pt_scene_desc;
+
+typedef struct {
+    int64_t n_triangles;
+    int64_t n_bvh2_nodes;
+    int64_t n_bvh8_nodes;
+    int32_t key_bits;      /* 30 (N <= 16Mi) or 63 */
+    int32_t sort_passes;
+    float ms_bounds_morton, ms_sort, ms_emit, ms_refit, ms_collapse, ms_total; /* device events */
+    int64_t device_bytes;  /* resident accelerator + geometry bytes after the build */
+} b200pt_build_stats;
+
+typedef struct {
+    int32_t spp_total;      /* sampler is configured for the TOTAL spp (strata stay global) */
+    int32_t sample_begin;   /* this GPU renders sample_idx in [sample_begin, sample_end) */
+    int32_t sample_end;
+    int32_t max_depth;      /* Integrator "integer maxdepth" (5), integrators/wavefront_path.cu:589 */
+    int32_t regularize;     /* "bool regularize" (false) */
+    int32_t sampler;        /* 0 = stratified, 1 = independent (scene/scene_builder.cu:392-407) */
+    int32_t pool_size;      /* path-pool slots; 0 = default */
+    int32_t reserved;
+} b200pt_render_opts;
+
+typedef struct {
+    int64_t paths;          /* camera paths generated = W*H*(sample_end-sample_begin) */
+    int64_t rays_closest;   /* closest-hit rays traced */
+    int64_t rays_shadow;    /* any-hit (NEE visibility) rays traced */
+    int64_t passes;         /* wavefront iterations */
+    int64_t kernel_launches;
+    float ms_total;         /* device events around the whole render */
+    float ms_trace, ms_shade, ms_generate, ms_logic; /* per-stage sums (0 when not profiled) */
+} b200pt_render_stats;
+
+/* Library / device */
+int b200pt_abi_version(void);
+const char *b200pt_last_error(void);
+int b200pt_device_count(void);
+
+/* Scene + accelerator: replaces HLBVH::HLBVH (accelerator/hlbvh.cu:172-404) */
+int b200pt_scene_create(const b200pt_scene_desc *desc, int device, b200pt_scene **out);
+void b200pt_scene_destroy(b200pt_scene *scene);
+int b200pt_bvh_build(b200pt_scene *scene, b200pt_build_stats *stats_out);
+/* Morton codes of the build (reference-compatible 30-bit codes, accelerator/hlbvh.cu:128-142):
+ * sorted primitive order and keys, for parity tests of the build stages. */
+int b200pt_bvh_debug_sorted(b200pt_scene *scene, int32_t *prim_order_out, uint64_t *keys_out);
+/* Host walk statistics of the built BVH8 (node / triangle visit counts for a ray set are
+ * accumulated on the device by b200pt_trace when counters_out is non-NULL). */
+
+/* Traversal: replaces HLBVH::intersect / fast_intersect (accelerator/hlbvh.cu:407-516).
+ * Host-pointer form (copies in/out inside the call) and device-pointer form.
+ * rays: o_xyz[n*3], d_xyz[n*3], tmax[n].  Outputs (any may be NULL): prim_out[n] = primitive
+ * index (triangle index, or n_triangles + sphere index; -1 = miss; any_hit: 1/0),
+ * t_out[n] (inf on miss), b1b2_out[n*2] barycentrics b1,b2 of the hit. */
+int b200pt_trace(b200pt_scene *scene, const float *o_xyz, const float *d_xyz, const float *tmax,
+                 int64_t n, int any_hit, int32_t *prim_out, float *t_out, float *b1b2_out);
+/* Device form: rays_dev = n x {ox,oy,oz,tmax, dx,dy,dz,0} (32 B), hits_dev = n x
+ * {prim (int bits), t, b1, b2} (16 B).  Asynchronous on the scene's stream unless sync != 0. */
+int b200pt_trace_device(b200pt_scene *scene, const void *rays_dev, int64_t n, int any_hit,
+                        void *hits_dev, int sync);
+/* Per-launch traversal counters of the most recent trace with counting enabled:
+ * out[0] = BVH8 nodes fetched, out[1] = triangles tested, out[2] = rays. */
+int b200pt_trace_set_counting(b200pt_scene *scene, int enable);
+int b200pt_trace_counters(b200pt_scene *scene, int64_t out[3]);
+void *b200pt_scene_stream(b200pt_scene *scene); /* cudaStream_t the scene launches on */
+int b200pt_scene_sync(b200pt_scene *scene);
+
+/* Device buffers for callers without their own CUDA allocator (tests, bench, host front-end) */
+int b200pt_device_alloc(b200pt_scene *scene, size_t bytes, void **out_dev);
+int b200pt_device_free(b200pt_scene *scene, void *ptr_dev);
+int b200pt_copy_to_device(b200pt_scene *scene, void *dst_dev, const void *src, size_t bytes);
+int b200pt_copy_to_host(b200pt_scene *scene, void *dst, const void *src_dev, size_t bytes);
+
+/* Wavefront path integrator: replaces WavefrontPathIntegrator::render
+ * (integrators/wavefront_path.cu:594-735) and RGBFilm (film/rgb_film.cu:63-122). */
+int b200pt_film_create(b200pt_scene *scene, b200pt_film **out);
+void b200pt_film_destroy(b200pt_film *film);
+int b200pt_film_clear(b200pt_film *film);
+int b200pt_render(b200pt_scene *scene, b200pt_film *film, const b200pt_render_opts *opts,
+                  b200pt_render_stats *stats_out);
+/* Sum of the per-GPU films onto root: ncclReduce(sum, fp32) of 4*W*H floats.  nccl_comm is an
+ * ncclComm_t, stream a cudaStream_t (NULL = the film's scene stream). */
+int b200pt_film_reduce(b200pt_film *film, void *nccl_comm, int root, void *stream);
+void *b200pt_film_device_ptr(b200pt_film *film); /* float4[W*H] accumulators (for torch.distributed) */
+int b200pt_film_dims(b200pt_film *film, int32_t *width, int32_t *height);
+/* rgb_out[W*H*3] = output_rgb_from_sensor_rgb * (xyz_sum / weight_sum) (film/rgb_film.cu:107-122) */
+int b200pt_film_read(b200pt_film *film, float *rgb_out);
+/* raw accumulators: xyzw_out[W*H*4] */
+int b200pt_film_read_raw(b200pt_film *film, float *xyzw_out);
+
+/* Stage probes for parity tests (each runs the production device functions on small batches).
+ * Sampler (samplers/stratified.h, samplers/independent.h): same contract as the oracle's
+ * oracle_sampler_stream: for each (pixel, sample) emit draws following pattern[] (1 = get_1d,
+ * 2 = get_2d). */
+int b200pt_probe_sampler(b200pt_scene *scene, int kind, int spp, const int32_t *pixel,
+                         const int32_t *sample, int npairs, const int32_t *pattern, int ndraw,
+                         float *out);
+/* Triangle test (shapes/triangle.cu:213-323) on explicit (ray, triangle) pairs:
+ * o,d [n*3], tmax[n], tri[n*9]; hit_out[n] (0/1), bt_out[n*4] = b0,b1,b2,t */
+int b200pt_probe_triangle(b200pt_scene *scene, const float *o, const float *d, const float *tmax,
+                          const float *tri, int64_t n, int32_t *hit_out, float *bt_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PT_H */

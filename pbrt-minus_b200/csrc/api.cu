@@ -1,0 +1,367 @@
+// api.cu -- the C-ABI of libb200pt.so (include/b200pt.h): scene upload, accelerator build,
+// batched traversal, device buffer helpers.  Errors come back as status codes with a
+// thread-local message; nothing here exits, throws across the boundary or runs on the CPU.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+#include "triangle.cuh"
+
+namespace b200pt {
+
+static thread_local char g_error[1024] = "";
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
+    set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    return (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? B200PT_ERR_NO_DEVICE : B200PT_ERR_CUDA;
+}
+
+template <typename T>
+static int upload(T **dst, const T *src, size_t count, cudaStream_t st, int64_t *bytes) {
+    *dst = nullptr;
+    if (!src || count == 0) return B200PT_OK;
+    CU_TRY(cudaMalloc((void **)dst, count * sizeof(T)));
+    CU_TRY(cudaMemcpyAsync(*dst, src, count * sizeof(T), cudaMemcpyHostToDevice, st));
+    *bytes += int64_t(count * sizeof(T));
+    return B200PT_OK;
+}
+
+// host rays (o[n*3], d[n*3], tmax[n]) -> packed 2 x float4
+__global__ void k_pack_rays(const float *__restrict__ o, const float *__restrict__ d, const float *__restrict__ tmax,
+                            long long n, float4 *__restrict__ rays) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    rays[2 * i] = make_float4(o[3 * i], o[3 * i + 1], o[3 * i + 2], tmax[i]);
+    rays[2 * i + 1] = make_float4(d[3 * i], d[3 * i + 1], d[3 * i + 2], 0.f);
+}
+
+__global__ void k_unpack_hits(const float4 *__restrict__ hits, long long n, int32_t *__restrict__ prim,
+                              float *__restrict__ t, float *__restrict__ b12) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 h = hits[i];
+    if (prim) prim[i] = __float_as_int(h.x);
+    if (t) t[i] = h.y;
+    if (b12) {
+        b12[2 * i] = h.z;
+        b12[2 * i + 1] = h.w;
+    }
+}
+
+__global__ void k_probe_triangle(const float *__restrict__ o, const float *__restrict__ d, const float *__restrict__ tmax,
+                                 const float *__restrict__ tri, long long n, int32_t *__restrict__ hit,
+                                 float *__restrict__ bt) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *v = tri + 9 * i;
+    TriHit th = {0.f, 0.f, 0.f, 0.f};
+    const bool h = intersect_triangle(o[3 * i], o[3 * i + 1], o[3 * i + 2], d[3 * i], d[3 * i + 1], d[3 * i + 2], tmax[i], v[0],
+                                      v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8], th);
+    hit[i] = h ? 1 : 0;
+    bt[4 * i] = h ? th.b0 : 0.f;
+    bt[4 * i + 1] = h ? th.b1 : 0.f;
+    bt[4 * i + 2] = h ? th.b2 : 0.f;
+    bt[4 * i + 3] = h ? th.t : 0.f;
+}
+
+struct TempDev {
+    std::vector<void *> ptrs;
+    ~TempDev() {
+        for (void *p : ptrs) cudaFree(p);
+    }
+    template <typename T>
+    cudaError_t alloc(T **out, size_t count) {
+        void *p = nullptr;
+        const cudaError_t e = cudaMalloc(&p, (count ? count : 1) * sizeof(T));
+        if (e == cudaSuccess) ptrs.push_back(p);
+        *out = (T *)p;
+        return e;
+    }
+};
+
+static int select_device(int device) {
+    int count = 0;
+    const cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        set_error("no CUDA device available (%s); libb200pt has no CPU fallback",
+                  e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        return B200PT_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= count) {
+        set_error("device %d out of range (0..%d)", device, count - 1);
+        return B200PT_ERR_INVALID;
+    }
+    CU_TRY(cudaSetDevice(device));
+    return B200PT_OK;
+}
+
+} // namespace b200pt
+
+using namespace b200pt;
+
+B200PT_API int b200pt_abi_version(void) { return B200PT_ABI_VERSION; }
+B200PT_API const char *b200pt_last_error(void) { return g_error; }
+B200PT_API int b200pt_device_count(void) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) return 0;
+    return count;
+}
+
+int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc); // render.cu
+
+B200PT_API int b200pt_scene_create(const b200pt_scene_desc *desc, int device, b200pt_scene **out) {
+    if (!desc || !out) {
+        set_error("b200pt_scene_create: null argument");
+        return B200PT_ERR_INVALID;
+    }
+    *out = nullptr;
+    if (desc->n_triangles < 0 || desc->n_vertices < 0 || (desc->n_triangles > 0 && (!desc->P || !desc->indices))) {
+        set_error("b200pt_scene_create: inconsistent geometry description");
+        return B200PT_ERR_INVALID;
+    }
+    int rc = select_device(device);
+    if (rc) return rc;
+    b200pt_scene *s = new b200pt_scene();
+    s->device = device;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) s->sm_count = prop.multiProcessorCount;
+    auto fail = [&](int code) {
+        b200pt_scene_destroy(s);
+        return code;
+    };
+    if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        set_error("b200pt_scene_create: cannot create a stream");
+        return fail(B200PT_ERR_CUDA);
+    }
+    s->n_vertices = desc->n_vertices;
+    s->n_triangles = desc->n_triangles;
+    // index sanity (a bad index would fault on the device)
+    for (int64_t i = 0; i < desc->n_triangles * 3; i++) {
+        const int32_t v = desc->indices[i];
+        if (v < 0 || v >= desc->n_vertices) {
+            set_error("b200pt_scene_create: vertex index %d out of range at position %lld", v, (long long)i);
+            return fail(B200PT_ERR_INVALID);
+        }
+    }
+    if ((rc = upload(&s->d_P, desc->P, size_t(desc->n_vertices) * 3, s->stream, &s->device_bytes))) return fail(rc);
+    if ((rc = upload(&s->d_N, desc->N, size_t(desc->n_vertices) * 3, s->stream, &s->device_bytes))) return fail(rc);
+    if ((rc = upload(&s->d_uv, desc->uv, size_t(desc->n_vertices) * 2, s->stream, &s->device_bytes))) return fail(rc);
+    if ((rc = upload(&s->d_idx, desc->indices, size_t(desc->n_triangles) * 3, s->stream, &s->device_bytes))) return fail(rc);
+    if ((rc = upload(&s->d_tri_material, desc->tri_material, size_t(desc->n_triangles), s->stream, &s->device_bytes))) return fail(rc);
+    if ((rc = upload(&s->d_tri_light, desc->tri_light, size_t(desc->n_triangles), s->stream, &s->device_bytes))) return fail(rc);
+    if ((rc = upload(&s->d_tri_flip, desc->tri_flip, size_t(desc->n_triangles), s->stream, &s->device_bytes))) return fail(rc);
+    if (cudaMalloc((void **)&s->d_trace_counters, 4 * sizeof(unsigned long long)) != cudaSuccess) {
+        set_error("b200pt_scene_create: out of device memory");
+        return fail(B200PT_ERR_CUDA);
+    }
+    if ((rc = b200pt_upload_render_data(s, desc))) return fail(rc);
+    if (cudaStreamSynchronize(s->stream) != cudaSuccess) {
+        set_error("b200pt_scene_create: upload failed");
+        return fail(B200PT_ERR_CUDA);
+    }
+    *out = s;
+    return B200PT_OK;
+}
+
+B200PT_API void b200pt_scene_destroy(b200pt_scene *s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    free_render(s);
+    void *ptrs[] = {s->d_P, s->d_N, s->d_uv, s->d_idx, s->d_tri_material, s->d_tri_light, s->d_tri_flip, s->d_spheres,
+                    s->d_nodes, s->d_tris, s->d_sorted_keys, s->d_sorted_prim, s->d_trace_counters};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    for (void *p : s->user_allocs) cudaFree(p);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+B200PT_API int b200pt_bvh_build(b200pt_scene *s, b200pt_build_stats *stats_out) {
+    if (!s) {
+        set_error("b200pt_bvh_build: null scene");
+        return B200PT_ERR_INVALID;
+    }
+    CU_TRY(cudaSetDevice(s->device));
+    return build_bvh(s, stats_out);
+}
+
+B200PT_API int b200pt_bvh_debug_sorted(b200pt_scene *s, int32_t *prim_order_out, uint64_t *keys_out) {
+    if (!s || !s->built) {
+        set_error("b200pt_bvh_debug_sorted: build first");
+        return B200PT_ERR_STATE;
+    }
+    CU_TRY(cudaSetDevice(s->device));
+    if (s->n_triangles == 0) return B200PT_OK;
+    if (prim_order_out)
+        CU_TRY(cudaMemcpyAsync(prim_order_out, s->d_sorted_prim, s->n_triangles * 4, cudaMemcpyDeviceToHost, s->stream));
+    if (keys_out) CU_TRY(cudaMemcpyAsync(keys_out, s->d_sorted_keys, s->n_triangles * 8, cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    return B200PT_OK;
+}
+
+static int check_trace_status(b200pt_scene *s) {
+    unsigned long long c[4];
+    CU_TRY(cudaMemcpyAsync(c, s->d_trace_counters, sizeof(c), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    s->last_counts[0] = (int64_t)c[1];
+    s->last_counts[1] = (int64_t)c[2];
+    if (c[3]) {
+        set_error("b200pt_trace: traversal stack overflow (tree deeper than %d groups)", 96);
+        return B200PT_ERR_STATE;
+    }
+    return B200PT_OK;
+}
+
+B200PT_API int b200pt_trace_device(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev, int sync) {
+    if (!s || (n > 0 && (!rays_dev || !hits_dev))) {
+        set_error("b200pt_trace_device: null argument");
+        return B200PT_ERR_INVALID;
+    }
+    CU_TRY(cudaSetDevice(s->device));
+    const int rc = launch_trace(s, rays_dev, n, any_hit, hits_dev);
+    if (rc) return rc;
+    s->last_counts[2] = n;
+    if (sync) return check_trace_status(s);
+    return B200PT_OK;
+}
+
+B200PT_API int b200pt_trace(b200pt_scene *s, const float *o_xyz, const float *d_xyz, const float *tmax, int64_t n,
+                            int any_hit, int32_t *prim_out, float *t_out, float *b1b2_out) {
+    if (!s || n < 0 || (n > 0 && (!o_xyz || !d_xyz || !tmax))) {
+        set_error("b200pt_trace: null argument");
+        return B200PT_ERR_INVALID;
+    }
+    if (!s->built) {
+        set_error("b200pt_trace: call b200pt_bvh_build first");
+        return B200PT_ERR_STATE;
+    }
+    if (n == 0) return B200PT_OK;
+    CU_TRY(cudaSetDevice(s->device));
+    TempDev tmp;
+    float *d_o, *d_d, *d_tmax, *d_t, *d_b;
+    int32_t *d_prim;
+    float4 *d_rays, *d_hits;
+    CU_TRY(tmp.alloc(&d_o, n * 3));
+    CU_TRY(tmp.alloc(&d_d, n * 3));
+    CU_TRY(tmp.alloc(&d_tmax, n));
+    CU_TRY(tmp.alloc(&d_rays, n * 2));
+    CU_TRY(tmp.alloc(&d_hits, n));
+    CU_TRY(tmp.alloc(&d_prim, n));
+    CU_TRY(tmp.alloc(&d_t, n));
+    CU_TRY(tmp.alloc(&d_b, n * 2));
+    CU_TRY(cudaMemcpyAsync(d_o, o_xyz, n * 12, cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaMemcpyAsync(d_d, d_xyz, n * 12, cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaMemcpyAsync(d_tmax, tmax, n * 4, cudaMemcpyHostToDevice, s->stream));
+    const int tb = 256;
+    const unsigned grid = unsigned((n + tb - 1) / tb);
+    k_pack_rays<<<grid, tb, 0, s->stream>>>(d_o, d_d, d_tmax, n, d_rays);
+    int rc = launch_trace(s, d_rays, n, any_hit, d_hits);
+    if (rc) return rc;
+    s->last_counts[2] = n;
+    k_unpack_hits<<<grid, tb, 0, s->stream>>>(d_hits, n, d_prim, d_t, d_b);
+    if (prim_out) CU_TRY(cudaMemcpyAsync(prim_out, d_prim, n * 4, cudaMemcpyDeviceToHost, s->stream));
+    if (t_out) CU_TRY(cudaMemcpyAsync(t_out, d_t, n * 4, cudaMemcpyDeviceToHost, s->stream));
+    if (b1b2_out) CU_TRY(cudaMemcpyAsync(b1b2_out, d_b, n * 8, cudaMemcpyDeviceToHost, s->stream));
+    return check_trace_status(s);
+}
+
+B200PT_API int b200pt_trace_set_counting(b200pt_scene *s, int enable) {
+    if (!s) return B200PT_ERR_INVALID;
+    s->counting = enable != 0;
+    return B200PT_OK;
+}
+
+B200PT_API int b200pt_trace_counters(b200pt_scene *s, int64_t out[3]) {
+    if (!s || !out) return B200PT_ERR_INVALID;
+    CU_TRY(cudaSetDevice(s->device));
+    const int rc = check_trace_status(s);
+    out[0] = s->last_counts[0];
+    out[1] = s->last_counts[1];
+    out[2] = s->last_counts[2];
+    return rc;
+}
+
+B200PT_API void *b200pt_scene_stream(b200pt_scene *s) { return s ? (void *)s->stream : nullptr; }
+
+B200PT_API int b200pt_scene_sync(b200pt_scene *s) {
+    if (!s) return B200PT_ERR_INVALID;
+    CU_TRY(cudaSetDevice(s->device));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    return B200PT_OK;
+}
+
+B200PT_API int b200pt_device_alloc(b200pt_scene *s, size_t bytes, void **out_dev) {
+    if (!s || !out_dev) return B200PT_ERR_INVALID;
+    CU_TRY(cudaSetDevice(s->device));
+    void *p = nullptr;
+    CU_TRY(cudaMalloc(&p, bytes ? bytes : 1));
+    s->user_allocs.push_back(p);
+    *out_dev = p;
+    return B200PT_OK;
+}
+
+B200PT_API int b200pt_device_free(b200pt_scene *s, void *ptr_dev) {
+    if (!s) return B200PT_ERR_INVALID;
+    CU_TRY(cudaSetDevice(s->device));
+    for (size_t i = 0; i < s->user_allocs.size(); i++)
+        if (s->user_allocs[i] == ptr_dev) {
+            s->user_allocs.erase(s->user_allocs.begin() + i);
+            CU_TRY(cudaFree(ptr_dev));
+            return B200PT_OK;
+        }
+    set_error("b200pt_device_free: pointer not owned by this scene");
+    return B200PT_ERR_INVALID;
+}
+
+B200PT_API int b200pt_copy_to_device(b200pt_scene *s, void *dst_dev, const void *src, size_t bytes) {
+    if (!s) return B200PT_ERR_INVALID;
+    CU_TRY(cudaSetDevice(s->device));
+    CU_TRY(cudaMemcpyAsync(dst_dev, src, bytes, cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    return B200PT_OK;
+}
+
+B200PT_API int b200pt_copy_to_host(b200pt_scene *s, void *dst, const void *src_dev, size_t bytes) {
+    if (!s) return B200PT_ERR_INVALID;
+    CU_TRY(cudaSetDevice(s->device));
+    CU_TRY(cudaMemcpyAsync(dst, src_dev, bytes, cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    return B200PT_OK;
+}
+
+B200PT_API int b200pt_probe_triangle(b200pt_scene *s, const float *o, const float *d, const float *tmax, const float *tri,
+                                     int64_t n, int32_t *hit_out, float *bt_out) {
+    if (!s || n < 0 || (n > 0 && (!o || !d || !tmax || !tri || !hit_out || !bt_out))) {
+        set_error("b200pt_probe_triangle: null argument");
+        return B200PT_ERR_INVALID;
+    }
+    if (n == 0) return B200PT_OK;
+    CU_TRY(cudaSetDevice(s->device));
+    TempDev tmp;
+    float *d_o, *d_d, *d_tmax, *d_tri, *d_bt;
+    int32_t *d_hit;
+    CU_TRY(tmp.alloc(&d_o, n * 3));
+    CU_TRY(tmp.alloc(&d_d, n * 3));
+    CU_TRY(tmp.alloc(&d_tmax, n));
+    CU_TRY(tmp.alloc(&d_tri, n * 9));
+    CU_TRY(tmp.alloc(&d_bt, n * 4));
+    CU_TRY(tmp.alloc(&d_hit, n));
+    CU_TRY(cudaMemcpyAsync(d_o, o, n * 12, cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaMemcpyAsync(d_d, d, n * 12, cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaMemcpyAsync(d_tmax, tmax, n * 4, cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaMemcpyAsync(d_tri, tri, n * 36, cudaMemcpyHostToDevice, s->stream));
+    k_probe_triangle<<<unsigned((n + 255) / 256), 256, 0, s->stream>>>(d_o, d_d, d_tmax, d_tri, n, d_hit, d_bt);
+    CU_TRY(cudaMemcpyAsync(hit_out, d_hit, n * 4, cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaMemcpyAsync(bt_out, d_bt, n * 16, cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    return B200PT_OK;
+}

@@ -1,0 +1,651 @@
+// bvh_build.cu -- HLBVH build for B200, entirely on the device.
+//
+// Replaces HLBVH::HLBVH (accelerator/hlbvh.cu:172-404): the reference interleaves 12+ kernels
+// with host loops over managed memory, a CPU SAH over treelets and one-thread-per-node serial
+// partitions.  Here:
+//   k_centroid_bounds   triangle bounds + centroid box reduction         (ref :102-115, :206-209)
+//   k_cubify            widen the minor axes to the major extent         (ref :210-225)
+//   k_morton            30-bit reference-compatible codes (N <= 16 Mi) or 63-bit codes
+//                                                                        (ref :128-142, util/math.h:183-208)
+//   radix_sort_u64      LSD radix sort, 8-bit digits (sort.cuh)          (ref :56-82, :256-281)
+//   k_emit_hierarchy    binary radix tree over the sorted Morton prefixes, one thread per
+//                       interior node (replaces the CPU SAH :611-813 and the per-level
+//                       midpoint splits :518-609, :815-844)
+//   k_refit             bottom-up AABBs with arrival counters
+//   k_collapse_level    work-queue emission of 8-wide treelets: each queue item turns one BVH2
+//                       subtree root into one quantised 80-byte BVH8 node, allocates its child
+//                       nodes / triangle slots with atomic counters, re-lays the triangles out
+//                       in node order and pushes the interior children on the next queue.
+#include <algorithm>
+#include <cmath>
+
+#include "common.cuh"
+#include "sort.cuh"
+
+namespace b200pt {
+
+// ------------------------------------------------------------------ orderable float <-> uint
+__device__ __forceinline__ uint32_t f2ord(float f) {
+    const uint32_t u = __float_as_uint(f);
+    return u ^ ((u >> 31) ? 0xffffffffu : 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(uint32_t u) {
+    return __uint_as_float(u ^ ((u >> 31) ? 0x80000000u : 0xffffffffu));
+}
+
+struct TriVerts {
+    float3 a, b, c;
+};
+__device__ __forceinline__ TriVerts load_tri(const float *__restrict__ P, const int32_t *__restrict__ idx, int64_t t) {
+    const int64_t i0 = idx[3 * t], i1 = idx[3 * t + 1], i2 = idx[3 * t + 2];
+    TriVerts v;
+    v.a = make_float3(P[3 * i0], P[3 * i0 + 1], P[3 * i0 + 2]);
+    v.b = make_float3(P[3 * i1], P[3 * i1 + 1], P[3 * i1 + 2]);
+    v.c = make_float3(P[3 * i2], P[3 * i2 + 1], P[3 * i2 + 2]);
+    return v;
+}
+__device__ __forceinline__ void tri_bounds(const TriVerts &v, float3 &lo, float3 &hi) {
+    lo = make_float3(fminf(v.a.x, fminf(v.b.x, v.c.x)), fminf(v.a.y, fminf(v.b.y, v.c.y)), fminf(v.a.z, fminf(v.b.z, v.c.z)));
+    hi = make_float3(fmaxf(v.a.x, fmaxf(v.b.x, v.c.x)), fmaxf(v.a.y, fmaxf(v.b.y, v.c.y)), fmaxf(v.a.z, fmaxf(v.b.z, v.c.z)));
+}
+// euclidean_space/bounds3.h:102-104  centroid = 0.5 * (p_min + p_max)
+__device__ __forceinline__ float3 centroid_of(const float3 &lo, const float3 &hi) {
+    return make_float3(__fmul_rn(0.5f, __fadd_rn(lo.x, hi.x)), __fmul_rn(0.5f, __fadd_rn(lo.y, hi.y)),
+                       __fmul_rn(0.5f, __fadd_rn(lo.z, hi.z)));
+}
+
+// red[0..5] = centroid box (min xyz, max xyz), red[6..11] = scene box; all as orderable uints
+__global__ void __launch_bounds__(256) k_centroid_bounds(const float *__restrict__ P, const int32_t *__restrict__ idx, int64_t n,
+                                                         uint32_t *__restrict__ red) {
+    float v[12] = {kInf, kInf, kInf, -kInf, -kInf, -kInf, kInf, kInf, kInf, -kInf, -kInf, -kInf};
+    for (int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; t < n; t += int64_t(gridDim.x) * blockDim.x) {
+        const TriVerts tv = load_tri(P, idx, t);
+        float3 lo, hi;
+        tri_bounds(tv, lo, hi);
+        const float3 c = centroid_of(lo, hi);
+        v[0] = fminf(v[0], c.x); v[1] = fminf(v[1], c.y); v[2] = fminf(v[2], c.z);
+        v[3] = fmaxf(v[3], c.x); v[4] = fmaxf(v[4], c.y); v[5] = fmaxf(v[5], c.z);
+        v[6] = fminf(v[6], lo.x); v[7] = fminf(v[7], lo.y); v[8] = fminf(v[8], lo.z);
+        v[9] = fmaxf(v[9], hi.x); v[10] = fmaxf(v[10], hi.y); v[11] = fmaxf(v[11], hi.z);
+    }
+#pragma unroll
+    for (int k = 0; k < 12; k++) {
+        const bool is_min = (k % 6) < 3;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float other = __shfl_xor_sync(0xffffffffu, v[k], o);
+            v[k] = is_min ? fminf(v[k], other) : fmaxf(v[k], other);
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < 12; k++) {
+            if ((k % 6) < 3) atomicMin(&red[k], f2ord(v[k]));
+            else atomicMax(&red[k], f2ord(v[k]));
+        }
+    }
+}
+
+__global__ void k_init_reduction(uint32_t *red) {
+    const int k = threadIdx.x;
+    if (k < 12) red[k] = ((k % 6) < 3) ? 0xffffffffu : 0u;
+}
+
+// accelerator/hlbvh.cu:210-225: the centroid box is widened on its two minor axes to the major
+// extent, so all Morton cells are cubes.  boxes[0..5] = cubified centroid box, [6..11] scene box.
+__global__ void k_cubify(const uint32_t *__restrict__ red, float *__restrict__ boxes) {
+    float lo[3], hi[3];
+    for (int a = 0; a < 3; a++) {
+        lo[a] = ord2f(red[a]);
+        hi[a] = ord2f(red[3 + a]);
+    }
+    const float dx = __fsub_rn(hi[0], lo[0]), dy = __fsub_rn(hi[1], lo[1]), dz = __fsub_rn(hi[2], lo[2]);
+    const int md = (dx > dy && dx > dz) ? 0 : ((dy > dz) ? 1 : 2); // bounds3.h:124-133
+    const float radius = __fdiv_rn(__fsub_rn(hi[md], lo[md]), 2.0f);
+    for (int a = 0; a < 3; a++) {
+        if (a == md) {
+            boxes[a] = lo[a];
+            boxes[3 + a] = hi[a];
+        } else {
+            const float center = __fmul_rn(0.5f, __fadd_rn(lo[a], hi[a]));
+            boxes[a] = __fsub_rn(center, radius);
+            boxes[3 + a] = __fadd_rn(center, radius);
+        }
+    }
+    for (int a = 0; a < 6; a++) boxes[6 + a] = ord2f(red[6 + a]);
+}
+
+// util/math.h:183-208 (10 bits per axis, x lowest; the value 1024 is clamped to 1023)
+__device__ __forceinline__ uint32_t left_shift3(uint32_t x) {
+    if (x == (1u << 10)) --x;
+    x = (x | (x << 16)) & 0x030000FFu;
+    x = (x | (x << 8)) & 0x0300F00Fu;
+    x = (x | (x << 4)) & 0x030C30C3u;
+    x = (x | (x << 2)) & 0x09249249u;
+    return x;
+}
+__device__ __forceinline__ uint64_t spread21(uint64_t x) {
+    x &= 0x1fffffull;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+// KEY30: key = morton30 << 32 | prim (sorted key-only on bits 32..63).
+// otherwise: key = morton63, vals = prim.
+template <bool KEY30>
+__global__ void __launch_bounds__(256) k_morton(const float *__restrict__ P, const int32_t *__restrict__ idx, int64_t n,
+                                                const float *__restrict__ boxes, uint64_t *__restrict__ keys,
+                                                uint32_t *__restrict__ vals) {
+    const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (t >= n) return;
+    const TriVerts tv = load_tri(P, idx, t);
+    float3 lo, hi;
+    tri_bounds(tv, lo, hi);
+    const float3 c = centroid_of(lo, hi);
+    const float cc[3] = {c.x, c.y, c.z};
+    float off[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) { // bounds3.h:106-122 offset()
+        float o = __fsub_rn(cc[a], boxes[a]);
+        if (boxes[3 + a] > boxes[a]) o = __fdiv_rn(o, __fsub_rn(boxes[3 + a], boxes[a]));
+        off[a] = o;
+    }
+    if (KEY30) {
+        const uint32_t qx = uint32_t(__fmul_rn(off[0], 1024.0f));
+        const uint32_t qy = uint32_t(__fmul_rn(off[1], 1024.0f));
+        const uint32_t qz = uint32_t(__fmul_rn(off[2], 1024.0f));
+        const uint32_t m = (left_shift3(qz) << 2) | (left_shift3(qy) << 1) | left_shift3(qx);
+        keys[t] = (uint64_t(m) << 32) | uint64_t(uint32_t(t));
+    } else {
+        uint64_t q[3];
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            const float s = off[a] * 2097152.0f;
+            q[a] = s <= 0.0f ? 0ull : (s >= 2097151.0f ? 2097151ull : uint64_t(s));
+        }
+        keys[t] = (spread21(q[2]) << 2) | (spread21(q[1]) << 1) | spread21(q[0]);
+        vals[t] = uint32_t(t);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_unpack_prims(const uint64_t *__restrict__ keys, int64_t n, uint32_t *__restrict__ prims) {
+    const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (t < n) prims[t] = uint32_t(keys[t]);
+}
+
+// ------------------------------------------------------------------------ BVH2 (build only)
+// Node ids: interior i in [0, n-1), leaf k -> (n-1) + k (k = position in sorted order).
+struct Bvh2 {
+    float4 *lo;    // xyz = box min, w = left child id (int bits)
+    float4 *hi;    // xyz = box max, w = right child id
+    int2 *range;   // interior: [first, last] sorted positions covered
+    int32_t *parent;
+    uint32_t *arrive;
+    int32_t n; // leaves
+};
+
+__device__ __forceinline__ int delta_fn(const uint64_t *__restrict__ keys, int n, int i, uint64_t ki, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint64_t kj = keys[j];
+    if (ki == kj) return 64 + __clz(i ^ j);
+    return __clzll((long long)(ki ^ kj));
+}
+
+// Binary radix tree over sorted keys, one thread per interior node (every split is the highest
+// differing Morton bit of its range -- the same splits the reference's midpoint recursion makes
+// on a power-of-two grid, found without recursion or partitioning).
+__global__ void __launch_bounds__(256) k_emit_hierarchy(const uint64_t *__restrict__ keys, Bvh2 t) {
+    const int n = t.n;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const uint64_t ki = keys[i];
+    const int d = (delta_fn(keys, n, i, ki, i + 1) - delta_fn(keys, n, i, ki, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta_fn(keys, n, i, ki, i - d);
+    int lmax = 2;
+    while (delta_fn(keys, n, i, ki, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int s = lmax >> 1; s >= 1; s >>= 1)
+        if (delta_fn(keys, n, i, ki, i + (l + s) * d) > dmin) l += s;
+    const int j = i + l * d;
+    const int dnode = delta_fn(keys, n, i, ki, j);
+    int s = 0;
+    int step = l;
+    do {
+        step = (step + 1) >> 1;
+        if (delta_fn(keys, n, i, ki, i + (s + step) * d) > dnode) s += step;
+    } while (step > 1);
+    const int gamma = i + s * d + min(d, 0);
+    const int first = min(i, j), last = max(i, j);
+    const int left = (first == gamma) ? (n - 1 + gamma) : gamma;
+    const int right = (last == gamma + 1) ? (n - 1 + gamma + 1) : (gamma + 1);
+    t.lo[i].w = __int_as_float(left);
+    t.hi[i].w = __int_as_float(right);
+    t.range[i] = make_int2(first, last);
+    t.parent[left] = i;
+    t.parent[right] = i;
+    if (i == 0) t.parent[0] = -1;
+}
+
+__global__ void __launch_bounds__(256) k_refit(const float *__restrict__ P, const int32_t *__restrict__ idx,
+                                               const uint32_t *__restrict__ sorted_prim, Bvh2 t) {
+    const int n = t.n;
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const TriVerts tv = load_tri(P, idx, sorted_prim[k]);
+    float3 lo, hi;
+    tri_bounds(tv, lo, hi);
+    const int leaf = n - 1 + k;
+    t.lo[leaf] = make_float4(lo.x, lo.y, lo.z, __int_as_float(-1));
+    t.hi[leaf] = make_float4(hi.x, hi.y, hi.z, __int_as_float(-1));
+    int cur = (n > 1) ? t.parent[leaf] : -1;
+    while (cur >= 0) {
+        __threadfence();
+        if (atomicAdd(&t.arrive[cur], 1u) == 0u) return; // first arrival: the sibling finishes the job
+        __threadfence();
+        const int l = __float_as_int(__ldcg(&t.lo[cur].w)), r = __float_as_int(__ldcg(&t.hi[cur].w));
+        const float4 llo = __ldcg(&t.lo[l]), lhi = __ldcg(&t.hi[l]);
+        const float4 rlo = __ldcg(&t.lo[r]), rhi = __ldcg(&t.hi[r]);
+        float4 *plo = &t.lo[cur], *phi = &t.hi[cur];
+        plo->x = fminf(llo.x, rlo.x); plo->y = fminf(llo.y, rlo.y); plo->z = fminf(llo.z, rlo.z);
+        phi->x = fmaxf(lhi.x, rhi.x); phi->y = fmaxf(lhi.y, rhi.y); phi->z = fmaxf(lhi.z, rhi.z);
+        cur = t.parent[cur];
+    }
+}
+
+// ------------------------------------------------------------------- BVH8 work-queue collapse
+struct CollapseArgs {
+    Bvh2 t;
+    const float *P;
+    const int32_t *idx;
+    const uint32_t *sorted_prim;
+    float4 *nodes; // BVH8 out
+    float4 *tris;  // re-laid-out triangles out
+    const int2 *q_in; // (bvh2 node, bvh8 node index)
+    int2 *q_out;
+    int q_in_count;
+    unsigned int *counters; // [0] bvh8 nodes allocated, [1] tris allocated, [2] next-queue count, [3] overflow flag
+    unsigned int node_capacity;
+};
+
+__device__ __forceinline__ float half_area(const float4 &lo, const float4 &hi) {
+    const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void __launch_bounds__(128) k_collapse_level(CollapseArgs a) {
+    const int item = blockIdx.x * blockDim.x + threadIdx.x;
+    if (item >= a.q_in_count) return;
+    const int n = a.t.n;
+    const int2 work = a.q_in[item];
+    const int root2 = work.x;
+
+    int c[8];
+    float area[8];
+    int cnt;
+    if (root2 >= n - 1) { // single-leaf tree (n == 1)
+        c[0] = root2;
+        area[0] = 0.f;
+        cnt = 1;
+    } else {
+        c[0] = __float_as_int(a.t.lo[root2].w);
+        c[1] = __float_as_int(a.t.hi[root2].w);
+        area[0] = (c[0] >= n - 1) ? -1.f : half_area(a.t.lo[c[0]], a.t.hi[c[0]]);
+        area[1] = (c[1] >= n - 1) ? -1.f : half_area(a.t.lo[c[1]], a.t.hi[c[1]]);
+        cnt = 2;
+    }
+    // open the interior child with the largest surface area until the treelet has 8 leaves
+    while (cnt < 8) {
+        int best = -1;
+        float best_a = -1.f;
+        for (int i = 0; i < cnt; i++)
+            if (area[i] > best_a) {
+                best_a = area[i];
+                best = i;
+            }
+        if (best < 0) break;
+        const int l = __float_as_int(a.t.lo[c[best]].w), r = __float_as_int(a.t.hi[c[best]].w);
+        c[best] = l;
+        area[best] = (l >= n - 1) ? -1.f : half_area(a.t.lo[l], a.t.hi[l]);
+        c[cnt] = r;
+        area[cnt] = (r >= n - 1) ? -1.f : half_area(a.t.lo[r], a.t.hi[r]);
+        cnt++;
+    }
+
+    // child boxes, triangle counts, node box
+    float clo[8][3], chi[8][3];
+    int tcount[8], tfirst[8];
+    float nlo[3] = {kInf, kInf, kInf}, nhi[3] = {-kInf, -kInf, -kInf};
+    for (int i = 0; i < cnt; i++) {
+        const float4 lo = a.t.lo[c[i]], hi = a.t.hi[c[i]];
+        clo[i][0] = lo.x; clo[i][1] = lo.y; clo[i][2] = lo.z;
+        chi[i][0] = hi.x; chi[i][1] = hi.y; chi[i][2] = hi.z;
+        for (int k = 0; k < 3; k++) {
+            nlo[k] = fminf(nlo[k], clo[i][k]);
+            nhi[k] = fmaxf(nhi[k], chi[i][k]);
+        }
+        if (c[i] >= n - 1) {
+            tfirst[i] = c[i] - (n - 1);
+            tcount[i] = 1;
+        } else {
+            const int2 rg = a.t.range[c[i]];
+            tfirst[i] = rg.x;
+            tcount[i] = rg.y - rg.x + 1;
+        }
+    }
+
+    // octant-ordered slots: slot s prefers the child farthest along (+-x, +-y, +-z) by the bits
+    // of s (4 = +x, 2 = +y, 1 = +z); traversal visits slots in (slot ^ octant) order, so near
+    // children of any ray octant come first.  Greedy assignment on the 8x8 cost table.
+    int slot_of[8];
+    {
+        const float pcx = 0.5f * (nlo[0] + nhi[0]), pcy = 0.5f * (nlo[1] + nhi[1]), pcz = 0.5f * (nlo[2] + nhi[2]);
+        float ccx[8], ccy[8], ccz[8];
+        for (int i = 0; i < cnt; i++) {
+            ccx[i] = 0.5f * (clo[i][0] + chi[i][0]) - pcx;
+            ccy[i] = 0.5f * (clo[i][1] + chi[i][1]) - pcy;
+            ccz[i] = 0.5f * (clo[i][2] + chi[i][2]) - pcz;
+            slot_of[i] = -1;
+        }
+        unsigned used_slots = 0;
+        for (int round = 0; round < cnt; round++) {
+            float best = -kInf;
+            int bi = -1, bs = -1;
+            for (int i = 0; i < cnt; i++) {
+                if (slot_of[i] >= 0) continue;
+                for (int s = 0; s < 8; s++) {
+                    if (used_slots & (1u << s)) continue;
+                    const float cost = ((s & 4) ? ccx[i] : -ccx[i]) + ((s & 2) ? ccy[i] : -ccy[i]) + ((s & 1) ? ccz[i] : -ccz[i]);
+                    if (cost > best) {
+                        best = cost;
+                        bi = i;
+                        bs = s;
+                    }
+                }
+            }
+            if (bi < 0) { // non-finite centroids: first free child / slot
+                for (int i = cnt - 1; i >= 0; i--)
+                    if (slot_of[i] < 0) bi = i;
+                for (int s2 = 7; s2 >= 0; s2--)
+                    if (!(used_slots & (1u << s2))) bs = s2;
+            }
+            slot_of[bi] = bs;
+            used_slots |= 1u << bs;
+        }
+    }
+    int child_in_slot[8];
+    for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
+    for (int i = 0; i < cnt; i++) child_in_slot[slot_of[i]] = i;
+
+    // allocate child nodes, triangle slots and queue entries
+    unsigned imask = 0;
+    int n_inner = 0, n_tris = 0;
+    for (int s = 0; s < 8; s++) {
+        const int i = child_in_slot[s];
+        if (i < 0) continue;
+        if (tcount[i] > 3) {
+            imask |= 1u << s;
+            n_inner++;
+        } else {
+            n_tris += tcount[i];
+        }
+    }
+    unsigned child_base = 0, tri_base = 0, q_base = 0;
+    if (n_inner) {
+        child_base = atomicAdd(&a.counters[0], (unsigned)n_inner);
+        q_base = atomicAdd(&a.counters[2], (unsigned)n_inner);
+        if (child_base + n_inner > a.node_capacity) {
+            a.counters[3] = 1;
+            return;
+        }
+    }
+    if (n_tris) tri_base = atomicAdd(&a.counters[1], (unsigned)n_tris);
+
+    // quantisation grid: p = node min, 2^e >= extent / 255 per axis
+    int e[3];
+    double scale[3], inv_scale[3];
+    for (int k = 0; k < 3; k++) {
+        const double ext = (double)nhi[k] - (double)nlo[k];
+        int ek = -100;
+        if (ext > 0) {
+            ek = (int)ceil(log2(ext / 255.0));
+            while (ldexp(255.0, ek) < ext) ek++;
+            ek = max(-100, min(127, ek));
+        }
+        e[k] = ek;
+        scale[k] = ldexp(1.0, ek);
+        inv_scale[k] = ldexp(1.0, -ek);
+    }
+
+    unsigned char meta[8], qlo[3][8], qhi[3][8];
+    int tri_off = 0, inner_rank = 0;
+    for (int s = 0; s < 8; s++) {
+        const int i = child_in_slot[s];
+        if (i < 0) { // empty slot: inverted box never hit
+            meta[s] = 0;
+            for (int k = 0; k < 3; k++) {
+                qlo[k][s] = 255;
+                qhi[k][s] = 0;
+            }
+            continue;
+        }
+        for (int k = 0; k < 3; k++) {
+            const double l = ((double)clo[i][k] - (double)nlo[k]) * inv_scale[k];
+            const double h = ((double)chi[i][k] - (double)nlo[k]) * inv_scale[k];
+            int ql = (int)floor(l), qh = (int)ceil(h);
+            ql = max(0, min(255, ql));
+            qh = max(0, min(255, qh));
+            // exactness guard (all terms are exact in double): p + ql*2^e <= lo, p + qh*2^e >= hi
+            while (ql > 0 && (double)nlo[k] + ql * scale[k] > (double)clo[i][k]) ql--;
+            while (qh < 255 && (double)nlo[k] + qh * scale[k] < (double)chi[i][k]) qh++;
+            qlo[k][s] = (unsigned char)ql;
+            qhi[k][s] = (unsigned char)qh;
+        }
+        if (imask & (1u << s)) {
+            meta[s] = (unsigned char)((1u << 5) | (24u + s));
+            a.q_out[q_base + inner_rank] = make_int2(c[i], (int)(child_base + inner_rank));
+            inner_rank++;
+        } else {
+            const unsigned unary = (1u << tcount[i]) - 1u; // 1, 3, 7
+            meta[s] = (unsigned char)((unary << 5) | (unsigned)tri_off);
+            for (int k = 0; k < tcount[i]; k++) {
+                const uint32_t prim = a.sorted_prim[tfirst[i] + k];
+                const TriVerts tv = load_tri(a.P, a.idx, prim);
+                float4 *dst = a.tris + 3 * (size_t)(tri_base + tri_off + k);
+                dst[0] = make_float4(tv.a.x, tv.a.y, tv.a.z, __int_as_float((int)prim));
+                dst[1] = make_float4(tv.b.x, tv.b.y, tv.b.z, 0.f);
+                dst[2] = make_float4(tv.c.x, tv.c.y, tv.c.z, 0.f);
+            }
+            tri_off += tcount[i];
+        }
+    }
+
+    auto pack4 = [](const unsigned char *b) -> float {
+        return __uint_as_float((unsigned)b[0] | ((unsigned)b[1] << 8) | ((unsigned)b[2] << 16) | ((unsigned)b[3] << 24));
+    };
+    const unsigned ebits = (unsigned)(e[0] + 127) | ((unsigned)(e[1] + 127) << 8) | ((unsigned)(e[2] + 127) << 16) | (imask << 24);
+    float4 *dst = a.nodes + 5 * (size_t)work.y;
+    dst[0] = make_float4(nlo[0], nlo[1], nlo[2], __uint_as_float(ebits));
+    dst[1] = make_float4(__uint_as_float(child_base), __uint_as_float(tri_base), pack4(meta), pack4(meta + 4));
+    dst[2] = make_float4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
+    dst[3] = make_float4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
+    dst[4] = make_float4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
+}
+
+__global__ void k_seed_queue(int2 *q, unsigned int *counters, int root2) {
+    q[0] = make_int2(root2, 0);
+    counters[0] = 1; // node 0 = root
+    counters[1] = 0;
+    counters[2] = 0;
+    counters[3] = 0;
+}
+
+// ------------------------------------------------------------------------------ host driver
+namespace {
+struct DevFree {
+    std::vector<void *> ptrs;
+    ~DevFree() {
+        for (void *p : ptrs) cudaFree(p);
+    }
+    template <typename T>
+    cudaError_t alloc(T **out, size_t count) {
+        void *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
+        if (e == cudaSuccess) ptrs.push_back(p);
+        *out = (T *)p;
+        return e;
+    }
+};
+} // namespace
+
+int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
+    const int64_t n = s->n_triangles;
+    cudaStream_t st = s->stream;
+    b200pt_build_stats bs = {};
+    bs.n_triangles = n;
+    if (s->d_nodes) { cudaFree(s->d_nodes); s->d_nodes = nullptr; }
+    if (s->d_tris) { cudaFree(s->d_tris); s->d_tris = nullptr; }
+    if (s->d_sorted_keys) { cudaFree(s->d_sorted_keys); s->d_sorted_keys = nullptr; }
+    if (s->d_sorted_prim) { cudaFree(s->d_sorted_prim); s->d_sorted_prim = nullptr; }
+    s->bvh = BVH8();
+    s->built = false;
+    if (n == 0) {
+        s->built = true;
+        if (stats) *stats = bs;
+        return B200PT_OK;
+    }
+    if (n > (int64_t(1) << 30)) {
+        set_error("b200pt_bvh_build: %lld triangles exceed the 2^30 limit", (long long)n);
+        return B200PT_ERR_UNSUPPORTED;
+    }
+    const bool key30 = n <= (int64_t(1) << 24);
+    bs.key_bits = key30 ? 30 : 63;
+
+    cudaEvent_t ev[7];
+    for (auto &e : ev) CU_TRY(cudaEventCreate(&e));
+    struct EvFree {
+        cudaEvent_t *e;
+        ~EvFree() { for (int i = 0; i < 7; i++) cudaEventDestroy(e[i]); }
+    } evfree{ev};
+
+    DevFree tmp;
+    uint32_t *d_red;
+    float *d_boxes;
+    CU_TRY(tmp.alloc(&d_red, 12));
+    CU_TRY(tmp.alloc(&d_boxes, 12));
+    SortBuffers sb;
+    CU_TRY(tmp.alloc(&sb.keys[0], n));
+    CU_TRY(tmp.alloc(&sb.keys[1], n));
+    if (!key30) {
+        CU_TRY(tmp.alloc(&sb.vals[0], n));
+        CU_TRY(tmp.alloc(&sb.vals[1], n));
+    }
+    CU_TRY(tmp.alloc(&sb.tile_hist, 256 * sort_tiles(n)));
+    CU_TRY(tmp.alloc(&sb.scan_tmp, sort_scan_tmp_words(n)));
+
+    const int tb = 256;
+    const int grid_n = int((n + tb - 1) / tb);
+    CU_TRY(cudaEventRecord(ev[0], st));
+    // 1. centroid box + Morton keys
+    k_init_reduction<<<1, 32, 0, st>>>(d_red);
+    k_centroid_bounds<<<std::min<int64_t>(grid_n, s->sm_count * 16), tb, 0, st>>>(s->d_P, s->d_idx, n, d_red);
+    k_cubify<<<1, 1, 0, st>>>(d_red, d_boxes);
+    if (key30) k_morton<true><<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, n, d_boxes, sb.keys[0], nullptr);
+    else k_morton<false><<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, n, d_boxes, sb.keys[0], sb.vals[0]);
+    CU_TRY(cudaEventRecord(ev[1], st));
+    // 2. LSD radix sort
+    const int res = key30 ? radix_sort_u64(sb, n, 32, 64, st, &bs.sort_passes) : radix_sort_u64(sb, n, 0, 64, st, &bs.sort_passes);
+    CU_TRY(cudaMalloc(&s->d_sorted_keys, n * sizeof(uint64_t)));
+    CU_TRY(cudaMalloc(&s->d_sorted_prim, n * sizeof(uint32_t)));
+    CU_TRY(cudaMemcpyAsync(s->d_sorted_keys, sb.keys[res], n * sizeof(uint64_t), cudaMemcpyDeviceToDevice, st));
+    if (key30) k_unpack_prims<<<grid_n, tb, 0, st>>>(sb.keys[res], n, s->d_sorted_prim);
+    else CU_TRY(cudaMemcpyAsync(s->d_sorted_prim, sb.vals[res], n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+    CU_TRY(cudaEventRecord(ev[2], st));
+    // 3. hierarchy emission
+    Bvh2 t;
+    t.n = int32_t(n);
+    CU_TRY(tmp.alloc(&t.lo, 2 * n));
+    CU_TRY(tmp.alloc(&t.hi, 2 * n));
+    CU_TRY(tmp.alloc(&t.range, n));
+    CU_TRY(tmp.alloc(&t.parent, 2 * n));
+    CU_TRY(tmp.alloc(&t.arrive, n));
+    CU_TRY(cudaMemsetAsync(t.arrive, 0, n * sizeof(uint32_t), st));
+    if (n > 1) k_emit_hierarchy<<<int((n - 1 + tb - 1) / tb), tb, 0, st>>>(s->d_sorted_keys, t);
+    CU_TRY(cudaEventRecord(ev[3], st));
+    // 4. refit
+    k_refit<<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, s->d_sorted_prim, t);
+    CU_TRY(cudaEventRecord(ev[4], st));
+    // 5. work-queue collapse to BVH8
+    const unsigned node_capacity = unsigned(n / 2 + 64);
+    CU_TRY(cudaMalloc(&s->d_nodes, size_t(node_capacity) * 5 * sizeof(float4)));
+    CU_TRY(cudaMalloc(&s->d_tris, size_t(n) * 3 * sizeof(float4)));
+    int2 *q[2];
+    unsigned int *d_counters;
+    CU_TRY(tmp.alloc(&q[0], n));
+    CU_TRY(tmp.alloc(&q[1], n));
+    CU_TRY(tmp.alloc(&d_counters, 4));
+    k_seed_queue<<<1, 1, 0, st>>>(q[0], d_counters, n > 1 ? 0 : 0 /* leaf id n-1+0 == 0 when n == 1 */);
+    unsigned int h_counters[4] = {1, 0, 0, 0};
+    int q_count = 1, cur = 0, levels = 0;
+    while (q_count > 0) {
+        CollapseArgs a;
+        a.t = t;
+        a.P = s->d_P;
+        a.idx = s->d_idx;
+        a.sorted_prim = s->d_sorted_prim;
+        a.nodes = s->d_nodes;
+        a.tris = s->d_tris;
+        a.q_in = q[cur];
+        a.q_out = q[cur ^ 1];
+        a.q_in_count = q_count;
+        a.counters = d_counters;
+        a.node_capacity = node_capacity;
+        k_collapse_level<<<(q_count + 127) / 128, 128, 0, st>>>(a);
+        CU_TRY(cudaMemcpyAsync(h_counters, d_counters, sizeof(h_counters), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaStreamSynchronize(st));
+        if (h_counters[3]) {
+            set_error("b200pt_bvh_build: BVH8 node pool overflow (capacity %u)", node_capacity);
+            return B200PT_ERR_STATE;
+        }
+        q_count = int(h_counters[2]);
+        CU_TRY(cudaMemsetAsync(d_counters + 2, 0, sizeof(unsigned int), st));
+        cur ^= 1;
+        if (++levels > 4096) {
+            set_error("b200pt_bvh_build: collapse did not terminate");
+            return B200PT_ERR_STATE;
+        }
+    }
+    CU_TRY(cudaEventRecord(ev[5], st));
+    float boxes[12];
+    CU_TRY(cudaMemcpyAsync(boxes, d_boxes, sizeof(boxes), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    for (int k = 0; k < 6; k++) s->scene_bounds[k] = boxes[6 + k];
+
+    bs.n_bvh2_nodes = 2 * n - 1;
+    bs.n_bvh8_nodes = h_counters[0];
+    if (int64_t(h_counters[1]) != n) {
+        set_error("b200pt_bvh_build: %u of %lld triangles placed", h_counters[1], (long long)n);
+        return B200PT_ERR_STATE;
+    }
+    CU_TRY(cudaEventElapsedTime(&bs.ms_bounds_morton, ev[0], ev[1]));
+    CU_TRY(cudaEventElapsedTime(&bs.ms_sort, ev[1], ev[2]));
+    CU_TRY(cudaEventElapsedTime(&bs.ms_emit, ev[2], ev[3]));
+    CU_TRY(cudaEventElapsedTime(&bs.ms_refit, ev[3], ev[4]));
+    CU_TRY(cudaEventElapsedTime(&bs.ms_collapse, ev[4], ev[5]));
+    CU_TRY(cudaEventElapsedTime(&bs.ms_total, ev[0], ev[5]));
+
+    s->bvh.nodes = s->d_nodes;
+    s->bvh.tris = s->d_tris;
+    s->bvh.n_nodes = bs.n_bvh8_nodes;
+    s->bvh.n_tris = n;
+    s->key_bits = bs.key_bits;
+    s->built = true;
+    bs.device_bytes = int64_t(node_capacity) * 80 + n * 48 + n * 12;
+    if (stats) *stats = bs;
+    return B200PT_OK;
+}
+
+} // namespace b200pt

@@ -1,0 +1,104 @@
+// common.cuh -- shared declarations of libb200pt.so (hand-written CUDA for sm_100a).
+// No CPU fallback anywhere: every entry point needs a CUDA device and fails with a status code
+// when there is none (the reference prints and exit(1)s instead, gpu/macro.h:23-48).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/b200pt.h"
+
+#define B200PT_API extern "C" __attribute__((visibility("default")))
+
+namespace b200pt {
+
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
+
+#define CU_TRY(expr)                                                        \
+    do {                                                                    \
+        cudaError_t _e = (expr);                                            \
+        if (_e != cudaSuccess) return ::b200pt::cuda_fail(_e, #expr, __FILE__, __LINE__); \
+    } while (0)
+
+constexpr float kInf = __builtin_huge_valf();
+
+// ---- BVH8 node: 80 B = 5 x 128-bit loads ---------------------------------------------------
+//  n0 = { p.x, p.y, p.z, bytes(ex, ey, ez, imask) }   origin + per-axis pow-2 scale + inner mask
+//  n1 = { child_base, tri_base, meta[0..3], meta[4..7] }
+//  n2 = { qlo_x[0..3], qlo_x[4..7], qlo_y[0..3], qlo_y[4..7] }
+//  n3 = { qlo_z[0..3], qlo_z[4..7], qhi_x[0..3], qhi_x[4..7] }
+//  n4 = { qhi_y[0..3], qhi_y[4..7], qhi_z[0..3], qhi_z[4..7] }
+// meta (per child slot): 0 = empty; inner child: 0b001'11sss (low 5 bits = 24 + slot);
+// leaf child: high 3 bits = unary triangle count (001, 011, 111), low 5 bits = offset of its
+// first triangle from tri_base (0..23).  Child boxes are quantised conservatively (mins rounded
+// down, maxes up) on the node's grid  p + q * 2^e.
+struct BVH8 {
+    const float4 *nodes = nullptr; // 5 float4 per node
+    const float4 *tris = nullptr;  // 3 float4 per triangle, BVH8 leaf order; v0.w = primitive id
+    int64_t n_nodes = 0;
+    int64_t n_tris = 0;
+};
+
+// Device-side sphere record for the (few) quadrics of a scene: tested linearly beside the BVH.
+struct SphereRec {
+    float rfo[12]; // render_from_object, rows 0..2
+    float ofr[12]; // object_from_render
+    float radius, z_min, z_max, phi_max;
+    float theta_z_min, theta_z_max;
+    int flip; // reverse_orientation ^ transform_swaps_handedness
+    int material;
+};
+
+struct RenderData; // render.cu
+
+} // namespace b200pt
+
+struct b200pt_scene {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+
+    // geometry as uploaded (render space)
+    int64_t n_vertices = 0, n_triangles = 0;
+    float *d_P = nullptr;        // [nv*3]
+    float *d_N = nullptr;        // [nv*3] or null
+    float *d_uv = nullptr;       // [nv*2] or null
+    int32_t *d_idx = nullptr;    // [nt*3]
+    int32_t *d_tri_material = nullptr;
+    int32_t *d_tri_light = nullptr;
+    uint8_t *d_tri_flip = nullptr;
+    int32_t n_spheres = 0;
+    b200pt::SphereRec *d_spheres = nullptr;
+
+    // accelerator
+    bool built = false;
+    b200pt::BVH8 bvh;
+    float4 *d_nodes = nullptr;
+    float4 *d_tris = nullptr;
+    // debug copies of the sorted build order (kept for parity tests of the build stages)
+    uint64_t *d_sorted_keys = nullptr;
+    uint32_t *d_sorted_prim = nullptr;
+    int key_bits = 0;
+    float scene_bounds[6] = {0, 0, 0, 0, 0, 0};
+
+    // traversal
+    unsigned long long *d_trace_counters = nullptr; // [0] ray ticket, [1] nodes, [2] tris, [3] err
+    bool counting = false;
+    int64_t last_counts[3] = {0, 0, 0};
+    int64_t device_bytes = 0;
+
+    b200pt::RenderData *render = nullptr;
+    std::vector<void *> user_allocs;
+};
+
+namespace b200pt {
+
+int build_bvh(b200pt_scene *s, b200pt_build_stats *stats);
+int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev);
+void free_render(b200pt_scene *s);
+
+} // namespace b200pt

@@ -1,0 +1,149 @@
+// traverse.cuh -- per-ray BVH8 traversal (device function shared by the trace kernels and the
+// wavefront stages).  Replaces HLBVH::intersect / fast_intersect (accelerator/hlbvh.cu:407-516):
+// instead of a 128-entry local-memory stack of BVH2 nodes with a 7-deep pointer chase per leaf,
+// a ray walks 80-byte quantised 8-wide nodes (5 x 128-bit loads), keeps a short stack of
+// (node-group, hit-mask) pairs in shared memory, and tests 48-byte triangle records with the
+// reference's exact watertight arithmetic (triangle.cuh), which is what defines the hit id.
+#pragma once
+
+#include "common.cuh"
+#include "triangle.cuh"
+
+namespace b200pt {
+
+constexpr int TRACE_BLOCK = 128;
+constexpr int SM_STACK = 10;    // entries per thread in shared memory
+constexpr int LOCAL_STACK = 86; // overflow entries in local memory (rarely touched)
+
+struct RayHit {
+    int prim; // -1 = miss
+    float t, b1, b2;
+};
+
+struct TraceCounters {
+    unsigned nodes = 0, tris = 0;
+};
+
+__device__ __forceinline__ float safe_rcp_dir(float d) {
+    // 1/d with |d| clamped away from zero so slab distances stay finite (no 0*inf NaNs)
+    const float c = fabsf(d) > 1e-18f ? d : copysignf(1e-18f, d);
+    return __fdiv_rn(1.0f, c);
+}
+
+__device__ __forceinline__ float byte_to_float(uint32_t word, int byte) {
+    return (float)((word >> (8 * byte)) & 0xffu);
+}
+
+// sm_stack: this thread's column of the CTA's shared stack, addressed as sm_stack[depth * stride]
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool traverse_bvh8(const BVH8 &bvh, float ox, float oy, float oz, float dx, float dy, float dz,
+                                              float t_max, uint2 *sm_stack, int stride, RayHit &hit, TraceCounters &ctr,
+                                              unsigned *overflow_flag) {
+    hit.prim = -1;
+    hit.t = t_max;
+    hit.b1 = 0.f;
+    hit.b2 = 0.f;
+    if (bvh.n_nodes == 0) return false;
+
+    const float idx = safe_rcp_dir(dx), idy = safe_rcp_dir(dy), idz = safe_rcp_dir(dz);
+    const bool negx = idx < 0.f, negy = idy < 0.f, negz = idz < 0.f; // sign of the clamped reciprocal (covers -0)
+    const uint32_t octinv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
+    const uint32_t octinv4 = octinv * 0x01010101u;
+    constexpr float kSlack = 0x1p-20f; // relative guard for the decode arithmetic
+
+    uint2 lstack[LOCAL_STACK];
+    int sp = 0;
+    uint2 ng = make_uint2(0u, 0x80000000u); // node group: x = child base index, y = hit bits | imask
+    uint2 tg = make_uint2(0u, 0u);          // triangle group: x = tri base, y = hit bits
+
+    while (true) {
+        if (ng.y > 0x00ffffffu) {
+            const uint32_t hits = ng.y;
+            const int child_bit = 31 - __clz(hits);
+            ng.y &= ~(1u << child_bit);
+            if (ng.y > 0x00ffffffu) { // siblings left: keep the group for later
+                if (sp < SM_STACK) sm_stack[sp * stride] = ng;
+                else if (sp < SM_STACK + LOCAL_STACK) lstack[sp - SM_STACK] = ng;
+                else *overflow_flag = 1u;
+                sp++;
+            }
+            const uint32_t slot = (uint32_t(child_bit) - 24u) ^ octinv;
+            const uint32_t rel = __popc(hits & 0xffu & ((1u << slot) - 1u));
+            const float4 *np = bvh.nodes + 5 * size_t(ng.x + rel);
+            const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+            if (COUNT) ctr.nodes++;
+
+            const uint32_t ebits = __float_as_uint(n0.w);
+            const float sx = __uint_as_float((ebits & 0xffu) << 23);
+            const float sy = __uint_as_float(((ebits >> 8) & 0xffu) << 23);
+            const float sz = __uint_as_float(((ebits >> 16) & 0xffu) << 23);
+            const float ax = sx * idx, ay = sy * idy, az = sz * idz;
+            const float bx = (n0.x - ox) * idx, by = (n0.y - oy) * idy, bz = (n0.z - oz) * idz;
+            // decode error bound per axis: k*eps*(|origin term| + 256*|scale term|)
+            const float ex = kSlack * (fabsf(bx) + 256.f * fabsf(ax));
+            const float ey = kSlack * (fabsf(by) + 256.f * fabsf(ay));
+            const float ez = kSlack * (fabsf(bz) + 256.f * fabsf(az));
+            const float bxl = bx - ex, bxh = bx + ex, byl = by - ey, byh = by + ey, bzl = bz - ez, bzh = bz + ez;
+
+            ng.x = __float_as_uint(n1.x);
+            tg.x = __float_as_uint(n1.y);
+            uint32_t hitmask = 0;
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const uint32_t meta4 = __float_as_uint(h ? n1.w : n1.z);
+                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+                const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+                const uint32_t qlox = __float_as_uint(h ? n2.y : n2.x), qloy = __float_as_uint(h ? n2.w : n2.z);
+                const uint32_t qloz = __float_as_uint(h ? n3.y : n3.x), qhix = __float_as_uint(h ? n3.w : n3.z);
+                const uint32_t qhiy = __float_as_uint(h ? n4.y : n4.x), qhiz = __float_as_uint(h ? n4.w : n4.z);
+                const uint32_t nx = negx ? qhix : qlox, fx = negx ? qlox : qhix;
+                const uint32_t ny = negy ? qhiy : qloy, fy = negy ? qloy : qhiy;
+                const uint32_t nz = negz ? qhiz : qloz, fz = negz ? qloz : qhiz;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const float tnx = fmaf(byte_to_float(nx, j), ax, bxl), tfx = fmaf(byte_to_float(fx, j), ax, bxh);
+                    const float tny = fmaf(byte_to_float(ny, j), ay, byl), tfy = fmaf(byte_to_float(fy, j), ay, byh);
+                    const float tnz = fmaf(byte_to_float(nz, j), az, bzl), tfz = fmaf(byte_to_float(fz, j), az, bzh);
+                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
+                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, hit.t));
+                    if (tn <= tf) {
+                        const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu;
+                        const uint32_t bi = (bit_index4 >> (8 * j)) & 0xffu;
+                        hitmask |= cb << bi;
+                    }
+                }
+            }
+            ng.y = (hitmask & 0xff000000u) | (ebits >> 24);
+            tg.y = hitmask & 0x00ffffffu;
+        }
+
+        while (tg.y != 0u) {
+            const int ti = __ffs(tg.y) - 1;
+            tg.y &= tg.y - 1u;
+            const float4 *tp = bvh.tris + 3 * size_t(tg.x + ti);
+            const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+            if (COUNT) ctr.tris++;
+            TriHit th;
+            if (intersect_triangle(ox, oy, oz, dx, dy, dz, hit.t, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, th)) {
+                hit.t = th.t;
+                hit.b1 = th.b1;
+                hit.b2 = th.b2;
+                hit.prim = __float_as_int(v0.w);
+                if (ANY) return true;
+            }
+        }
+
+        if (ng.y <= 0x00ffffffu) {
+            if (sp == 0) break;
+            sp--;
+            if (sp < SM_STACK) ng = sm_stack[sp * stride];
+            else if (sp < SM_STACK + LOCAL_STACK) ng = lstack[sp - SM_STACK];
+            else ng = make_uint2(0u, 0u);
+        }
+    }
+    return hit.prim >= 0;
+}
+
+} // namespace b200pt

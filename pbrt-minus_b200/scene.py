@@ -1,0 +1,159 @@
+"""Host-side mirror of the reference's interface for the hot path, over the C-ABI.
+
+Names follow the reference: `HLBVH(primitives)` builds the accelerator (accelerator/hlbvh.h:76-78),
+`intersect` / `fast_intersect` are its closest-hit / any-hit queries (hlbvh.h:96-100) -- batched
+here, and returning primitive ids (the reference returns an interaction; the id is what parity is
+defined on).  `WavefrontPathIntegrator.render(film)` mirrors integrators/wavefront_path.h:136-140.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import api
+from .api import _check, _f32, _fp, _i32, _ip
+
+
+class DeviceBuffer:
+    """A raw device allocation owned by a scene (plain pointer + size; no torch types)."""
+
+    def __init__(self, scene, nbytes):
+        self.scene = scene
+        self.nbytes = int(nbytes)
+        p = C.c_void_p()
+        _check(scene.lib.b200pt_device_alloc(scene.handle, self.nbytes, C.byref(p)))
+        self.ptr = p.value
+
+    def upload(self, array):
+        a = np.ascontiguousarray(array)
+        assert a.nbytes <= self.nbytes
+        _check(self.scene.lib.b200pt_copy_to_device(self.scene.handle, self.ptr, a.ctypes.data, a.nbytes))
+
+    def download(self, dtype, count):
+        out = np.empty(count, dtype=dtype)
+        assert out.nbytes <= self.nbytes
+        _check(self.scene.lib.b200pt_copy_to_host(self.scene.handle, out.ctypes.data, self.ptr, out.nbytes))
+        return out
+
+    def free(self):
+        if self.ptr:
+            self.scene.lib.b200pt_device_free(self.scene.handle, self.ptr)
+            self.ptr = None
+
+
+class HLBVH:
+    """Scene replica on one GPU + its accelerator.  `desc_extra` carries the render-side arrays."""
+
+    def __init__(self, P, indices, device=0, build=True, desc=None, keep=None):
+        self.lib = api.load_library()
+        self._keep = [keep]
+        if desc is None:
+            P = _f32(P).reshape(-1, 3)
+            indices = _i32(indices).reshape(-1, 3)
+            desc = api.SceneDesc()
+            desc.n_vertices = P.shape[0]
+            desc.P = _fp(P)
+            desc.n_triangles = indices.shape[0]
+            desc.indices = _ip(indices)
+            self._keep += [P, indices]
+        self.n_triangles = int(desc.n_triangles)
+        h = C.c_void_p()
+        _check(self.lib.b200pt_scene_create(C.byref(desc), int(device), C.byref(h)))
+        self.handle = h
+        self.build_stats = None
+        if build:
+            self.build()
+
+    def build(self):
+        st = api.BuildStats()
+        _check(self.lib.b200pt_bvh_build(self.handle, C.byref(st)))
+        self.build_stats = st.as_dict()
+        return self.build_stats
+
+    def sorted_order(self):
+        prim = np.empty(self.n_triangles, dtype=np.int32)
+        keys = np.empty(self.n_triangles, dtype=np.uint64)
+        _check(self.lib.b200pt_bvh_debug_sorted(self.handle, _ip(prim), keys.ctypes.data_as(C.POINTER(C.c_uint64))))
+        return prim, keys
+
+    def _trace(self, o, d, tmax, any_hit):
+        o = _f32(o).reshape(-1, 3)
+        d = _f32(d).reshape(-1, 3)
+        n = o.shape[0]
+        tmax = _f32(np.broadcast_to(np.asarray(tmax, dtype=np.float32), (n,)))
+        prim = np.empty(n, dtype=np.int32)
+        t = np.empty(n, dtype=np.float32)
+        b = np.empty((n, 2), dtype=np.float32)
+        _check(self.lib.b200pt_trace(self.handle, _fp(o), _fp(d), _fp(tmax), n, int(any_hit), _ip(prim), _fp(t), _fp(b)))
+        return prim, t, b
+
+    def intersect(self, o, d, tmax=np.inf):
+        """closest hit: (prim ids [-1 = miss], t, (b1, b2))"""
+        return self._trace(o, d, tmax, 0)
+
+    def fast_intersect(self, o, d, tmax=np.inf):
+        """any hit within tmax: bool array"""
+        return self._trace(o, d, tmax, 1)[0].astype(bool)
+
+    # ---- device-resident form (bench `value`: inputs already in HBM)
+    def alloc(self, nbytes):
+        return DeviceBuffer(self, nbytes)
+
+    def pack_rays(self, o, d, tmax):
+        o = _f32(o).reshape(-1, 3)
+        d = _f32(d).reshape(-1, 3)
+        n = o.shape[0]
+        r = np.zeros((n, 8), dtype=np.float32)
+        r[:, 0:3] = o
+        r[:, 3] = np.broadcast_to(np.asarray(tmax, dtype=np.float32), (n,))
+        r[:, 4:7] = d
+        return r
+
+    def trace_device(self, rays_buf, n, hits_buf, any_hit=False, sync=False):
+        _check(self.lib.b200pt_trace_device(self.handle, rays_buf.ptr, int(n), int(any_hit), hits_buf.ptr, int(sync)))
+
+    def set_counting(self, enable):
+        _check(self.lib.b200pt_trace_set_counting(self.handle, int(enable)))
+
+    def counters(self):
+        out = (C.c_int64 * 3)()
+        _check(self.lib.b200pt_trace_counters(self.handle, out))
+        return {"nodes": out[0], "tris": out[1], "rays": out[2]}
+
+    def sync(self):
+        _check(self.lib.b200pt_scene_sync(self.handle))
+
+    @property
+    def stream(self):
+        return self.lib.b200pt_scene_stream(self.handle)
+
+    def probe_triangle(self, o, d, tmax, tri):
+        o = _f32(o).reshape(-1, 3)
+        d = _f32(d).reshape(-1, 3)
+        tri = _f32(tri).reshape(-1, 9)
+        n = o.shape[0]
+        tmax = _f32(np.broadcast_to(np.asarray(tmax, dtype=np.float32), (n,)))
+        hit = np.empty(n, dtype=np.int32)
+        bt = np.empty((n, 4), dtype=np.float32)
+        _check(self.lib.b200pt_probe_triangle(self.handle, _fp(o), _fp(d), _fp(tmax), _fp(tri), n, _ip(hit), _fp(bt)))
+        return hit, bt
+
+    def probe_sampler(self, kind, spp, pixel, sample, pattern):
+        pixel = _i32(pixel)
+        sample = _i32(sample)
+        pattern = _i32(pattern)
+        per = int(sum(1 if p == 1 else 2 for p in pattern))
+        out = np.empty((len(pixel), per), dtype=np.float32)
+        _check(self.lib.b200pt_probe_sampler(self.handle, int(kind), int(spp), _ip(pixel), _ip(sample), len(pixel),
+                                             _ip(pattern), len(pattern), _fp(out)))
+        return out
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.b200pt_scene_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,294 @@
+"""GPU parity tests of the accelerator + traversal slice, through the C-ABI.
+
+Bar (BASELINE.json): hit primitive ids bit-exact.  The checker is the CPU oracle (brute force with
+the reference's triangle arithmetic, oracle/oracle.c) and, when the prebuilt harness is present,
+the reference's own HLBVH traversal (oracle/_ref/ref_trace).  Rays whose two nearest candidates
+are within a few ulp ("near ties") resolve by visitation order, which differs between any two
+trees (and is non-deterministic inside the reference's own treelets, hlbvh.cu:67); they are
+counted separately and must be rare, all other rays must match exactly.
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def ulp_diff(a, b):
+    a = np.asarray(a, np.float32).view(np.int32).astype(np.int64)
+    b = np.asarray(b, np.float32).view(np.int32).astype(np.int64)
+    return np.abs(a - b)
+
+
+def random_rays(n, seed, lo=-0.2, hi=1.2):
+    rng = np.random.default_rng(seed)
+    o = rng.uniform(lo, hi, (n, 3)).astype(np.float32)
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    return o, d.astype(np.float32)
+
+
+def check_closest(oracle, P, idx, o, d, tmax, prim, t, b, max_tie_frac=2e-3):
+    oprim, ot, ob, t2 = oracle.closest_hit(P, idx, o, d, tmax, want_t2=True)
+    same = prim == oprim
+    # near tie: runner-up within 4 ulp of the winner (SURVEY.md hard part 2)
+    tie = np.isfinite(t2) & (ulp_diff(ot, t2) <= 4)
+    bad = ~same & ~tie
+    assert not bad.any(), "hit ids differ on %d non-tie rays (first %s: ours %s oracle %s)" % (
+        bad.sum(), np.flatnonzero(bad)[:5], prim[bad][:5], oprim[bad][:5])
+    assert (~same).sum() <= max(2, max_tie_frac * len(prim))
+    ok = same & (oprim >= 0)
+    assert np.array_equal(t[ok].view(np.uint32), ot[ok].view(np.uint32))
+    assert np.array_equal(b[ok].view(np.uint32), ob[ok].view(np.uint32))
+    assert np.all(np.isinf(t[same & (oprim < 0)]))
+    return int((~same).sum())
+
+
+def test_triangle_predicate_bit_exact(b200pt, oracle):
+    """shapes/triangle.cu:213-323 on explicit pairs, incl. edge/vertex grazing and degenerate cases"""
+    rng = np.random.default_rng(1)
+    n = 200000
+    tri = rng.uniform(-1, 1, (n, 9)).astype(np.float32)
+    # aim most rays at a point of the triangle; a third exactly at an edge or vertex combination
+    w = rng.dirichlet([1, 1, 1], n).astype(np.float32)
+    w[: n // 6] = np.array([0.5, 0.5, 0.0], np.float32)
+    w[n // 6: n // 3] = np.array([1.0, 0.0, 0.0], np.float32)
+    target = (w[:, :, None] * tri.reshape(n, 3, 3)).sum(1)
+    o = rng.uniform(-3, 3, (n, 3)).astype(np.float32)
+    d = (target - o).astype(np.float32)
+    d[n // 2:] /= np.linalg.norm(d[n // 2:], axis=1, keepdims=True)
+    tri[-100:, 3:6] = tri[-100:, 0:3]  # degenerate
+    d[-200:-100, 0] = 0.0              # axis-aligned components
+    tmax = np.full(n, np.inf, np.float32)
+    tmax[::7] = 1.0                    # the un-normalised half: t == 1 at the target
+    s = b200pt.HLBVH(np.zeros((3, 3), np.float32), np.array([[0, 1, 2]], np.int32), build=False)
+    hit, bt = s.probe_triangle(o, d, tmax, tri)
+    P = tri.reshape(-1, 3)
+    idx = np.arange(3 * n, dtype=np.int32).reshape(-1, 3)
+    ok, obt = oracle.intersect_pairs(P, idx, np.arange(n, dtype=np.int32), o, d, tmax)
+    assert np.array_equal(hit.astype(bool), ok)
+    assert np.array_equal(bt[ok].view(np.uint32), obt[ok].view(np.uint32))
+    assert 0.2 < ok.mean() < 0.99
+
+
+def test_sampler_bit_exact(b200pt, oracle):
+    """samplers/stratified.h + independent.h, PCG32, MurmurHash64A, permutation_element"""
+    import json
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_probe.json")))
+    s = b200pt.HLBVH(np.zeros((3, 3), np.float32), np.array([[0, 1, 2]], np.int32), build=False)
+    pattern = gold["pattern"]
+    rng = np.random.default_rng(3)
+    for kind in (0, 1):
+        for spp in (1, 16, 1024, 4096):
+            pixel = rng.integers(0, 1920 * 1080, 512).astype(np.int32)
+            sample = rng.integers(0, spp, 512).astype(np.int32)
+            got = s.probe_sampler(kind, spp, pixel, sample, pattern)
+            want = oracle.sampler_stream(kind, spp, pixel, sample, pattern)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    # and directly against the reference-produced golden (stratified entries; host order caveat for
+    # the independent 2-D pairs is documented in test_oracle_golden.py)
+    for g in gold["sampler"]:
+        if g["kind"] != 0:
+            continue
+        got = s.probe_sampler(0, g["spp"], [g["pixel"]], [g["sample"]], pattern)[0]
+        assert got.view(np.uint32).tolist() == g["draws"]
+
+
+def test_morton_sort_matches_reference_formula(b200pt, oracle):
+    """accelerator/hlbvh.cu:206-233 (cubified centroid box, 30-bit codes), stable LSD sort"""
+    import ctypes as C
+    P, idx = b200pt.workloads.triangle_soup(50000, seed=5)
+    s = b200pt.HLBVH(P, idx)
+    prim, keys = s.sorted_order()
+    assert s.build_stats["key_bits"] == 30
+    assert np.array_equal(np.sort(prim), np.arange(len(idx)))
+    assert np.all(keys[1:] > keys[:-1])  # (morton, prim) keys strictly increasing: sorted and stable
+    assert np.array_equal((keys & 0xFFFFFFFF).astype(np.int64), prim.astype(np.int64))
+    tri = P[idx]
+    lo, hi = tri.min(1), tri.max(1)
+    cen = (np.float32(0.5) * (lo + hi)).astype(np.float32)
+    blo, bhi = cen.min(0), cen.max(0)
+    dgn = bhi - blo
+    md = 0 if (dgn[0] > dgn[1] and dgn[0] > dgn[2]) else (1 if dgn[1] > dgn[2] else 2)
+    radius = np.float32((bhi[md] - blo[md]) / np.float32(2))
+    for a in range(3):
+        if a != md:
+            c = np.float32(0.5) * (blo[a] + bhi[a])
+            blo[a], bhi[a] = c - radius, c + radius
+    L = oracle.lib()
+    fp = C.POINTER(C.c_float)
+    blo, bhi = blo.astype(np.float32), bhi.astype(np.float32)
+    for k in np.random.default_rng(0).integers(0, len(idx), 2000):
+        c = np.ascontiguousarray(cen[prim[k]])
+        code = L.oracle_morton_of_centroid(c.ctypes.data_as(fp), blo.ctypes.data_as(fp), bhi.ctypes.data_as(fp))
+        assert code == int(keys[k] >> np.uint64(32))
+
+
+@pytest.mark.parametrize("n_tris,seed", [(1, 0), (2, 1), (3, 2), (4, 3), (9, 4), (100, 5), (1000, 6), (20000, 7)])
+def test_closest_hit_ids_vs_oracle(b200pt, oracle, n_tris, seed):
+    P, idx = b200pt.workloads.triangle_soup(n_tris, seed=seed)
+    if n_tris < 100:
+        P = (P - P.mean(0)) * np.float32(0.3) + np.float32(0.5)
+    s = b200pt.HLBVH(P, idx)
+    o, d = random_rays(16384, seed + 100)
+    prim, t, b = s.intersect(o, d)
+    check_closest(oracle, P, idx, o, d, np.inf, prim, t, b)
+    if n_tris >= 100:
+        assert (prim >= 0).mean() > 0.3
+
+
+def test_any_hit_vs_oracle(b200pt, oracle):
+    P, idx = b200pt.workloads.triangle_soup(5000, seed=11)
+    s = b200pt.HLBVH(P, idx)
+    o, d = random_rays(32768, 12)
+    rng = np.random.default_rng(13)
+    tmax = rng.uniform(0.01, 0.5, len(o)).astype(np.float32)
+    occ = s.fast_intersect(o, d, tmax)
+    want = oracle.any_hit(P, idx, o, d, tmax)
+    assert np.array_equal(occ, want)
+    assert 0.05 < occ.mean() < 0.95
+
+
+def test_edge_cases(b200pt, oracle):
+    # empty scene
+    s = b200pt.HLBVH(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.int32))
+    prim, t, _ = s.intersect([[0, 0, 0]], [[0, 0, 1]])
+    assert prim[0] == -1 and np.isinf(t[0])
+    assert s.intersect(np.zeros((0, 3)), np.zeros((0, 3)))[0].shape == (0,)
+    # duplicated triangles (coincident centroids: the reference keeps multi-primitive leaves,
+    # hlbvh.cu:580-589), degenerate triangles, axis-aligned rays, zero direction components
+    rng = np.random.default_rng(21)
+    base, bidx = b200pt.workloads.triangle_soup(300, seed=22)
+    P = np.concatenate([base, base, base[:30]], 0)
+    idx = np.arange(len(P), dtype=np.int32).reshape(-1, 3)
+    P[-9:-6] = P[-6:-3]  # degenerate: repeated vertex
+    s = b200pt.HLBVH(P, idx)
+    o, d = random_rays(20000, 23)
+    d[:5000] = np.eye(3, dtype=np.float32)[rng.integers(0, 3, 5000)] * rng.choice([-1, 1], (5000, 1)).astype(np.float32)
+    d[5000:8000, rng.integers(0, 3)] = 0.0
+    prim, t, b = s.intersect(o, d)
+    oprim, ot, ob, t2 = oracle.closest_hit(P, idx, o, d, np.inf, want_t2=True)
+    # every duplicate is an exact tie: ids may differ between the copies, t must not
+    assert np.array_equal(prim >= 0, oprim >= 0)
+    hitm = oprim >= 0
+    assert np.array_equal(t[hitm].view(np.uint32), ot[hitm].view(np.uint32))
+    assert np.array_equal(P[idx[prim[hitm]]], P[idx[oprim[hitm]]])
+    # finite t_max: closest hit beyond t_max is a miss; t == t_max is accepted
+    prim2, t2_, _ = s.intersect(o[hitm], d[hitm], ot[hitm])
+    assert np.all(prim2 >= 0) and np.array_equal(t2_.view(np.uint32), ot[hitm].view(np.uint32))
+    prim3, _, _ = s.intersect(o[hitm], d[hitm], ot[hitm] * np.float32(0.999))
+    oprim3, _, _ = oracle.closest_hit(P, idx, o[hitm], d[hitm], ot[hitm] * np.float32(0.999))
+    assert np.array_equal(prim3 >= 0, oprim3 >= 0)
+
+
+def test_shared_vertex_mesh_watertight(b200pt, oracle):
+    """indexed grid mesh: rays through shared edges/vertices must hit (watertightness)"""
+    m = 64
+    xs = np.linspace(0, 1, m + 1, dtype=np.float32)
+    X, Y = np.meshgrid(xs, xs)
+    P = np.stack([X.ravel(), Y.ravel(), (0.1 * np.sin(7 * X) * np.cos(5 * Y)).ravel().astype(np.float32) + 1], 1).astype(np.float32)
+    i, j = np.meshgrid(np.arange(m), np.arange(m))
+    a = (j * (m + 1) + i).ravel()
+    idx = np.concatenate([np.stack([a, a + 1, a + m + 1], 1), np.stack([a + 1, a + m + 2, a + m + 1], 1)]).astype(np.int32)
+    s = b200pt.HLBVH(P, idx)
+    # rays aimed exactly at vertices and edge midpoints from a common origin
+    tgt = np.concatenate([P[(m + 1) + 1: -(m + 2)], 0.5 * (P[idx[:, 0]] + P[idx[:, 1]])])
+    tgt = tgt[(tgt[:, 0] > 0.02) & (tgt[:, 0] < 0.98) & (tgt[:, 1] > 0.02) & (tgt[:, 1] < 0.98)]
+    o = np.broadcast_to(np.array([0.5, 0.5, -2], np.float32), tgt.shape).copy()
+    d = (tgt - o).astype(np.float32)
+    prim, t, b = s.intersect(o, d)
+    oprim, ot, _, _ = oracle.closest_hit(P, idx, o, d, np.inf, want_t2=True)
+    assert np.array_equal(prim >= 0, oprim >= 0)
+    assert (prim >= 0).all()
+    assert np.array_equal(t.view(np.uint32), ot.view(np.uint32))
+
+
+def test_device_resident_form_matches_host_form(b200pt):
+    P, idx = b200pt.workloads.triangle_soup(30000, seed=31)
+    s = b200pt.HLBVH(P, idx)
+    o, d = random_rays(50000, 32)
+    prim, t, b = s.intersect(o, d)
+    rays = s.pack_rays(o, d, np.inf)
+    rb, hb = s.alloc(rays.nbytes), s.alloc(len(o) * 16)
+    rb.upload(rays)
+    s.set_counting(True)
+    s.trace_device(rb, len(o), hb, sync=True)
+    h = hb.download(np.float32, len(o) * 4).reshape(-1, 4)
+    assert np.array_equal(h[:, 0].view(np.int32), prim)
+    assert np.array_equal(h[:, 1].view(np.uint32), t.view(np.uint32))
+    c = s.counters()
+    assert c["rays"] == len(o) and c["nodes"] > len(o) and c["tris"] > 0
+    s.set_counting(False)
+
+
+def test_full_size_properties(b200pt, oracle):
+    """C2 shape at reduced ray count but FULL triangle count is in bench.py; here 2M triangles:
+    every returned (prim, t, b1, b2) must be reproduced bit-exactly by the oracle's triangle test on
+    that pair, any-hit(t_max = t) must be true, and any-hit(t_max just below the nearest t) false
+    wherever no other candidate is near."""
+    P, idx = b200pt.workloads.triangle_soup(2_000_000, seed=41)
+    s = b200pt.HLBVH(P, idx)
+    st = s.build_stats
+    assert st["n_bvh8_nodes"] > 0 and st["n_triangles"] == 2_000_000
+    o, d, tmax = b200pt.workloads.primary_rays(640, 360)
+    prim, t, b = s.intersect(o, d, tmax)
+    hitm = prim >= 0
+    assert hitm.mean() > 0.5
+    ok, bt = oracle.intersect_pairs(P, idx, prim, o, d, tmax)
+    assert np.array_equal(ok, hitm)
+    assert np.array_equal(bt[hitm, 3].view(np.uint32), t[hitm].view(np.uint32))
+    assert np.array_equal(bt[hitm, 1:3].view(np.uint32), b[hitm].view(np.uint32))
+    occ = s.fast_intersect(o[hitm], d[hitm], t[hitm])
+    assert occ.all()
+    occ2 = s.fast_intersect(o[hitm], d[hitm], t[hitm] * np.float32(1 - 1e-3))
+    assert occ2.mean() < 0.02
+    # sub-sample against brute force (oracle finishes in seconds at 256 rays x 2M triangles)
+    pick = np.random.default_rng(42).choice(len(o), 256, replace=False)
+    check_closest(oracle, P, idx, o[pick], d[pick], np.inf, prim[pick], t[pick], b[pick])
+
+
+def test_hit_ids_vs_reference_hlbvh(b200pt, oracle, tmp_path):
+    """ids bit-exact against the REFERENCE's own HLBVH traversal (oracle/_ref/ref_trace, the
+    unmodified reference objects + our id-recording loop).  Also dumps a small golden."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_trace")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/ref_trace not prebuilt")
+    wl = b200pt.workloads
+    P, idx = wl.triangle_soup(200_000, seed=51)
+    s = b200pt.HLBVH(P, idx)
+    o, d, tmax = wl.primary_rays(480, 270)
+    prim, t, b = s.intersect(o, d, tmax)
+    bo, bd, bt = wl.bounce_rays(P, idx, o, d, prim, t)
+    so, sd, stm = wl.shadow_rays(P, idx, o, d, prim, t)
+    wl.write_soup(tmp_path / "soup.bin", P, idx)
+    jobs = []
+    for name, (ro, rd, rt), mode in (("primary", (o, d, tmax), "closest"), ("bounce", (bo, bd, bt), "closest"),
+                                     ("shadow", (so, sd, stm), "any")):
+        wl.write_rays(tmp_path / (name + ".rays"), ro, rd, rt)
+        jobs.append("%s:%s:%s" % (mode, tmp_path / (name + ".rays"), tmp_path / (name + ".out")))
+    r = subprocess.run([exe, str(tmp_path / "soup.bin")] + jobs, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout + r.stderr
+    mism = {}
+    for name, (ro, rd, rt), any_hit in (("primary", (o, d, tmax), 0), ("bounce", (bo, bd, bt), 0), ("shadow", (so, sd, stm), 1)):
+        rprim, rtt = wl.read_hits(tmp_path / (name + ".out"), len(ro))
+        if any_hit:
+            ours = s.fast_intersect(ro, rd, rt)
+            mism[name] = int((ours != rprim.astype(bool)).sum())
+            assert mism[name] == 0
+        else:
+            p2, t2, _ = s.intersect(ro, rd, rt)
+            diff = p2 != rprim
+            mism[name] = int(diff.sum())
+            if diff.any():  # only near ties may differ: verify with the brute-force oracle's runner-up distance
+                _, ot, _, ot2 = oracle.closest_hit(P, idx, ro[diff], rd[diff], rt[diff], want_t2=True)
+                assert np.all(ulp_diff(ot, ot2) <= 4), "non-tie mismatch vs reference HLBVH"
+            same = ~diff & (rprim >= 0)
+            assert np.array_equal(t2[same].view(np.uint32), rtt[same].view(np.uint32))
+            assert diff.mean() < 1e-3
+    out = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    with open(os.path.join(out, "ref_hlbvh_parity.txt"), "w") as f:
+        f.write("200k-triangle soup, 480x270 primary/bounce/shadow vs reference HLBVH: mismatching ids %s\n%s\n" % (mism, r.stdout))
