@@ -87,6 +87,20 @@ struct TempDev {
     }
 };
 
+int ensure_scratch(b200pt_scene *s, size_t bytes) {
+    if (bytes <= s->scratch_bytes) return B200PT_OK;
+    if (s->d_scratch) {
+        CU_TRY(cudaStreamSynchronize(s->stream));
+        CU_TRY(cudaFree(s->d_scratch));
+        s->d_scratch = nullptr;
+        s->scratch_bytes = 0;
+    }
+    const size_t want = bytes + bytes / 4;
+    CU_TRY(cudaMalloc(&s->d_scratch, want));
+    s->scratch_bytes = want;
+    return B200PT_OK;
+}
+
 static int select_device(int device) {
     int count = 0;
     const cudaError_t e = cudaGetDeviceCount(&count);
@@ -176,7 +190,7 @@ B200PT_API void b200pt_scene_destroy(b200pt_scene *s) {
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     free_render(s);
-    void *ptrs[] = {s->d_P, s->d_N, s->d_uv, s->d_idx, s->d_tri_material, s->d_tri_light, s->d_tri_flip, s->d_spheres,
+    void *ptrs[] = {s->d_scratch, s->d_P, s->d_N, s->d_uv, s->d_idx, s->d_tri_material, s->d_tri_light, s->d_tri_flip, s->d_spheres,
                     s->d_nodes, s->d_tris, s->d_sorted_keys, s->d_sorted_prim, s->d_trace_counters};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -246,18 +260,19 @@ B200PT_API int b200pt_trace(b200pt_scene *s, const float *o_xyz, const float *d_
     }
     if (n == 0) return B200PT_OK;
     CU_TRY(cudaSetDevice(s->device));
-    TempDev tmp;
-    float *d_o, *d_d, *d_tmax, *d_t, *d_b;
-    int32_t *d_prim;
-    float4 *d_rays, *d_hits;
-    CU_TRY(tmp.alloc(&d_o, n * 3));
-    CU_TRY(tmp.alloc(&d_d, n * 3));
-    CU_TRY(tmp.alloc(&d_tmax, n));
-    CU_TRY(tmp.alloc(&d_rays, n * 2));
-    CU_TRY(tmp.alloc(&d_hits, n));
-    CU_TRY(tmp.alloc(&d_prim, n));
-    CU_TRY(tmp.alloc(&d_t, n));
-    CU_TRY(tmp.alloc(&d_b, n * 2));
+    // scratch layout (all 16-byte aligned): rays | hits | o | d | tmax | prim | t | b
+    const size_t n16 = (size_t(n) + 3) & ~size_t(3);
+    int rc0 = ensure_scratch(s, n16 * (32 + 16 + 12 + 12 + 4 + 4 + 4 + 8));
+    if (rc0) return rc0;
+    char *base = (char *)s->d_scratch;
+    float4 *d_rays = (float4 *)base;
+    float4 *d_hits = (float4 *)(base + n16 * 32);
+    float *d_o = (float *)(base + n16 * 48);
+    float *d_d = (float *)(base + n16 * 60);
+    float *d_tmax = (float *)(base + n16 * 72);
+    int32_t *d_prim = (int32_t *)(base + n16 * 76);
+    float *d_t = (float *)(base + n16 * 80);
+    float *d_b = (float *)(base + n16 * 84);
     CU_TRY(cudaMemcpyAsync(d_o, o_xyz, n * 12, cudaMemcpyHostToDevice, s->stream));
     CU_TRY(cudaMemcpyAsync(d_d, d_xyz, n * 12, cudaMemcpyHostToDevice, s->stream));
     CU_TRY(cudaMemcpyAsync(d_tmax, tmax, n * 4, cudaMemcpyHostToDevice, s->stream));

@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(128) k_collapse_level(CollapseArgs a) {
     int cnt;
     if (root2 >= n - 1) { // single-leaf tree (n == 1)
         c[0] = root2;
-        area[0] = 0.f;
+        area[0] = -1.f;
         cnt = 1;
     } else {
         c[0] = __float_as_int(a.t.lo[root2].w);

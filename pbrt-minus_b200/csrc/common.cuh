@@ -93,6 +93,9 @@ struct b200pt_scene {
 
     b200pt::RenderData *render = nullptr;
     std::vector<void *> user_allocs;
+    // grow-only scratch for the host-pointer entry points (no cudaMalloc on the steady-state path)
+    void *d_scratch = nullptr;
+    size_t scratch_bytes = 0;
 };
 
 namespace b200pt {
@@ -100,5 +103,6 @@ namespace b200pt {
 int build_bvh(b200pt_scene *s, b200pt_build_stats *stats);
 int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev);
 void free_render(b200pt_scene *s);
+int ensure_scratch(b200pt_scene *s, size_t bytes);
 
 } // namespace b200pt

@@ -18,12 +18,14 @@ def triangle_soup(n, seed=20251104):
     return P, idx
 
 
-def primary_rays(width, height, fov_deg=40.0, eye=(0.5, 0.5, -1.5)):
-    """one ray per pixel centre, camera at `eye` looking +z"""
+def primary_rays(width, height, fov_deg=40.0, eye=(0.5, 0.5, -1.5), jitter_index=0):
+    """one ray per pixel, camera at `eye` looking +z.  jitter_index 0 = pixel centre; r > 0 = the centre
+    of stratum r of a 4x4 sub-pixel grid (sample-index sharding across GPUs)."""
     aspect = width / height
     t = np.tan(np.radians(fov_deg) / 2.0)
-    xs = ((np.arange(width) + 0.5) / width * 2.0 - 1.0) * t * aspect
-    ys = (1.0 - (np.arange(height) + 0.5) / height * 2.0) * t
+    jx, jy = (0.5, 0.5) if jitter_index == 0 else (((jitter_index % 4) + 0.5) / 4.0, (((jitter_index // 4) % 4) + 0.5) / 4.0)
+    xs = ((np.arange(width) + jx) / width * 2.0 - 1.0) * t * aspect
+    ys = (1.0 - (np.arange(height) + jy) / height * 2.0) * t
     X, Y = np.meshgrid(xs, ys)
     d = np.stack([X, Y, np.ones_like(X)], axis=-1).reshape(-1, 3)
     d /= np.linalg.norm(d, axis=1, keepdims=True)
