@@ -2,11 +2,21 @@
 //
 // Replaces ray_cast (integrators/wavefront_path.cu:348-366 -> HLBVH::intersect,
 // accelerator/hlbvh.cu:459-516) and the inline HLBVH::fast_intersect calls of the shading
-// kernels (accelerator/hlbvh.cu:407-456).  The grid is sized to the machine (SMs x resident
-// CTAs); each warp claims 32 rays at a time with ONE atomicAdd on the ray ticket
-// (warp-aggregated fetch), and the traversal keeps its short stack in shared memory.
+// kernels (accelerator/hlbvh.cu:407-456).
+//
+// Shape of the kernel (the reference launches one thread per ray with a local-memory stack):
+//  * persistent grid sized to the machine (SMs x resident CTAs);
+//  * warp-aggregated ray fetch: whenever REFILL or more lanes of a warp are idle, ONE atomicAdd
+//    on the ray ticket claims a ray for each idle lane (ballot + popc), so finished lanes are
+//    replaced instead of idling until the slowest ray of the warp is done;
+//  * "while-while" traversal: all lanes first walk interior nodes until they hold triangle work,
+//    re-converge, then test triangles together -- the two long code paths (node decode, watertight
+//    triangle test) each run with as many active lanes as possible;
+//  * short stack of (node-group, hit-mask) pairs in shared memory, overflow in local memory.
 // Rays: n x {ox,oy,oz,tmax, dx,dy,dz,-} (2 x 128-bit loads); hits: n x {prim,t,b1,b2} (one
 // 128-bit store).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "traverse.cuh"
 
@@ -18,35 +28,132 @@ struct TraceParams {
     float4 *hits;
     long long n;
     unsigned long long *counters; // [0] ticket, [1] nodes, [2] tris, [3] overflow flag
+    uint32_t prmt_bias;           // 0x47000000 (32768.0f), passed as a parameter so PRMT keeps an immediate selector
 };
 
-template <bool ANY, bool COUNT>
+template <bool ANY, bool COUNT, int REFILL>
 __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
-    __shared__ uint2 sm_stack[SM_STACK * TRACE_BLOCK];
+    __shared__ uint2 sm_stack_all[SM_STACK * TRACE_BLOCK];
+    uint2 *const sm_stack = sm_stack_all + threadIdx.x;
+    uint2 lstack[LOCAL_STACK];
     const int lane = threadIdx.x & 31;
-    TraceCounters ctr;
-    unsigned overflow = 0;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const bool have_tree = p.bvh.n_nodes > 0;
+
+    long long ray = -1; // this lane's ray index, -1 = idle
+    bool exhausted = false;
+    float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 0, idx = 0, idy = 0, idz = 0;
+    uint32_t octinv4 = 0;
+    uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
+    int sp = 0;
+    float ht = 0, hb1 = 0, hb2 = 0;
+    int hprim = -1;
+    unsigned n_nodes = 0, n_tris = 0, overflow = 0;
+
     while (true) {
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(p.counters, 32ull);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if ((long long)base >= p.n) break;
-        const long long r = (long long)base + lane;
-        if (r < p.n) {
-            const float4 ro = __ldg(p.rays + 2 * r), rd = __ldg(p.rays + 2 * r + 1);
-            RayHit hit;
-            traverse_bvh8<ANY, COUNT>(p.bvh, ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, ro.w, sm_stack + threadIdx.x, TRACE_BLOCK, hit,
-                                      ctr, &overflow);
-            if (ANY) p.hits[r] = make_float4(__int_as_float(hit.prim >= 0 ? 1 : 0), 0.f, 0.f, 0.f);
-            else p.hits[r] = make_float4(__int_as_float(hit.prim), hit.prim >= 0 ? hit.t : kInf, hit.b1, hit.b2);
+        // ---- warp-aggregated fetch of new rays into idle lanes
+        const unsigned idle = __ballot_sync(0xffffffffu, ray < 0);
+        if (!exhausted && (__popc(idle) >= REFILL || idle == 0xffffffffu)) {
+            const int n_idle = __popc(idle);
+            const int leader = __ffs(idle) - 1;
+            unsigned long long base = 0;
+            if (lane == leader) base = atomicAdd(p.counters, (unsigned long long)n_idle);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if ((long long)base + n_idle >= p.n) exhausted = true;
+            if (ray < 0) {
+                const long long r = (long long)base + __popc(idle & lt_mask);
+                if (r < p.n) {
+                    ray = r;
+                    const float4 ro = __ldg(p.rays + 2 * r), rd = __ldg(p.rays + 2 * r + 1);
+                    ox = ro.x; oy = ro.y; oz = ro.z;
+                    dx = rd.x; dy = rd.y; dz = rd.z;
+                    idx = safe_rcp_dir(dx); idy = safe_rcp_dir(dy); idz = safe_rcp_dir(dz);
+                    octinv4 = ((idx < 0.f ? 0u : 4u) | (idy < 0.f ? 0u : 2u) | (idz < 0.f ? 0u : 1u)) * 0x01010101u;
+                    ng = make_uint2(0u, have_tree ? 0x80000000u : 0u);
+                    tg = make_uint2(0u, 0u);
+                    sp = 0;
+                    ht = ro.w;
+                    hb1 = 0.f; hb2 = 0.f;
+                    hprim = -1;
+                }
+            }
         }
-        __syncwarp();
+        if (__ballot_sync(0xffffffffu, ray >= 0) == 0u) break;
+
+        // ---- phase vote: lanes holding triangle work vs lanes needing node work; the larger
+        //      group runs ONE step (one triangle test / one node decode), the other group waits,
+        //      so each of the two long code paths always runs with at least half the live lanes.
+        const bool act = ray >= 0;
+        const bool want_tri = act && tg.y != 0u;
+        const unsigned m_tri = __ballot_sync(0xffffffffu, want_tri);
+        const unsigned m_node = __ballot_sync(0xffffffffu, act && !want_tri);
+        if (__popc(m_tri) >= __popc(m_node)) {
+            if (want_tri) {
+                const int ti = __ffs(tg.y) - 1;
+                tg.y &= tg.y - 1u;
+                const float4 *tp = p.bvh.tris + 3 * size_t(tg.x + ti);
+                const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                if (COUNT) n_tris++;
+                TriHit th;
+                if (intersect_triangle(ox, oy, oz, dx, dy, dz, ht, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, th)) {
+                    ht = th.t;
+                    hb1 = th.b1;
+                    hb2 = th.b2;
+                    hprim = __float_as_int(v0.w);
+                    if (ANY) { // first accepted candidate ends the ray
+                        tg.y = 0u;
+                        ng.y = 0u;
+                        sp = 0;
+                    }
+                }
+            }
+        } else if (act && !want_tri) {
+            if (ng.y <= 0x00ffffffu && sp > 0) {
+                sp--;
+                if (sp < SM_STACK) ng = sm_stack[sp * TRACE_BLOCK];
+                else if (sp < SM_STACK + LOCAL_STACK) ng = lstack[sp - SM_STACK];
+                else ng = make_uint2(0u, 0u);
+            }
+            if (ng.y > 0x00ffffffu) {
+                const uint32_t hits = ng.y;
+                const int child_bit = 31 - __clz(hits);
+                ng.y &= ~(1u << child_bit);
+                if (ng.y > 0x00ffffffu) {
+                    if (sp < SM_STACK) sm_stack[sp * TRACE_BLOCK] = ng;
+                    else if (sp < SM_STACK + LOCAL_STACK) lstack[sp - SM_STACK] = ng;
+                    else overflow = 1u;
+                    sp++;
+                }
+                const uint32_t slot = (uint32_t(child_bit) - 24u) ^ (octinv4 & 0xffu);
+                const uint32_t rel = __popc(hits & 0xffu & ((1u << slot) - 1u));
+                const float4 *np = p.bvh.nodes + 5 * size_t(ng.x + rel);
+                const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+                if (COUNT) n_nodes++;
+                const uint32_t hitmask = intersect_node8(n0, n1, n2, n3, n4, ox, oy, oz, idx, idy, idz, octinv4, ht, p.prmt_bias);
+                ng.x = __float_as_uint(n1.x);
+                tg.x = __float_as_uint(n1.y);
+                ng.y = (hitmask & 0xff000000u) | (__float_as_uint(n0.w) >> 24);
+                tg.y = hitmask & 0x00ffffffu;
+            } else { // nothing left: retire the ray
+                if (ANY) p.hits[ray] = make_float4(__int_as_float(hprim >= 0 ? 1 : 0), 0.f, 0.f, 0.f);
+                else p.hits[ray] = make_float4(__int_as_float(hprim), hprim >= 0 ? ht : kInf, hb1, hb2);
+                ray = -1;
+            }
+        }
     }
     if (COUNT) {
-        atomicAdd(p.counters + 1, (unsigned long long)ctr.nodes);
-        atomicAdd(p.counters + 2, (unsigned long long)ctr.tris);
+        atomicAdd(p.counters + 1, (unsigned long long)n_nodes);
+        atomicAdd(p.counters + 2, (unsigned long long)n_tris);
     }
     if (overflow) p.counters[3] = 1ull;
+}
+
+typedef void (*TraceKernel)(TraceParams);
+
+template <int REFILL>
+static TraceKernel pick_kernel(bool any_hit, bool counting) {
+    return any_hit ? (counting ? k_trace<true, true, REFILL> : k_trace<true, false, REFILL>)
+                   : (counting ? k_trace<false, true, REFILL> : k_trace<false, false, REFILL>);
 }
 
 int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev) {
@@ -61,13 +168,21 @@ int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, 
     p.hits = (float4 *)hits_dev;
     p.n = n;
     p.counters = s->d_trace_counters;
+    p.prmt_bias = 0x47000000u;
     CU_TRY(cudaMemsetAsync(s->d_trace_counters, 0, 4 * sizeof(unsigned long long), s->stream));
 
-    void (*kern)(TraceParams) = any_hit ? (s->counting ? k_trace<true, true> : k_trace<true, false>)
-                                        : (s->counting ? k_trace<false, true> : k_trace<false, false>);
+    // tuning knobs (defaults are the measured best)
+    static const int refill = getenv("B200PT_REFILL") ? atoi(getenv("B200PT_REFILL")) : 4;
+    static const int cta_per_sm_cap = getenv("B200PT_TRACE_CTAS") ? atoi(getenv("B200PT_TRACE_CTAS")) : 0;
+    TraceKernel kern = refill <= 1 ? pick_kernel<1>(any_hit, s->counting)
+                     : refill <= 4 ? pick_kernel<4>(any_hit, s->counting)
+                     : refill <= 8 ? pick_kernel<8>(any_hit, s->counting)
+                     : refill <= 16 ? pick_kernel<16>(any_hit, s->counting)
+                                    : pick_kernel<32>(any_hit, s->counting);
     int per_sm = 0;
     CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TRACE_BLOCK, 0));
     if (per_sm < 1) per_sm = 1;
+    if (cta_per_sm_cap > 0 && per_sm > cta_per_sm_cap) per_sm = cta_per_sm_cap;
     long long blocks = (long long)s->sm_count * per_sm;
     const long long needed = (n + TRACE_BLOCK - 1) / TRACE_BLOCK;
     if (blocks > needed) blocks = needed;

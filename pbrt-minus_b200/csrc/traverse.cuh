@@ -30,8 +30,73 @@ __device__ __forceinline__ float safe_rcp_dir(float d) {
     return __fdiv_rn(1.0f, c);
 }
 
-__device__ __forceinline__ float byte_to_float(uint32_t word, int byte) {
-    return (float)((word >> (8 * byte)) & 0xffu);
+// Quantised byte -> float without the quarter-rate I2F: PRMT drops byte `byte` of `word` into
+// mantissa bits 8..15 of 32768.0f, giving exactly 32768 + q on the ALU pipe; the constant is folded
+// into the per-node origin term (b - 32768*a), whose rounding (<= a/256) the slack term covers.
+// `bias` = 0x47000000 arrives through a kernel parameter (constant bank) so the compiler keeps the
+// selector as the instruction's immediate instead of materialising 48 selector registers.
+__device__ __forceinline__ float byte_to_float_biased(uint32_t word, int byte, uint32_t bias) {
+    return __uint_as_float(__byte_perm(word, bias, 0x7604u | (uint32_t(byte) << 4)));
+}
+constexpr float kByteBias = 32768.f;
+
+struct NodeAxis {
+    float a, lo, hi; // t_near = q_near*a + lo, t_far = q_far*a + hi (with the byte bias folded in)
+};
+
+// per-axis decode terms of one node: scale a = 2^e/d, origin b = (p - o)/d, widened by the decode
+// error bound k*eps*(|b| + 256|a|) + |a|/128 (conservative: never culls a box the exact arithmetic hits)
+__device__ __forceinline__ NodeAxis node_axis(float p, float o, float inv_d, uint32_t e_byte) {
+    constexpr float kSlack = 0x1p-20f;
+    NodeAxis r;
+    r.a = __uint_as_float(e_byte << 23) * inv_d;
+    const float b = (p - o) * inv_d;
+    const float err = fmaf(kSlack, fabsf(b), 0x1p-6f * fabsf(r.a));
+    const float shift = b - kByteBias * r.a;
+    r.lo = shift - err;
+    r.hi = shift + err;
+    return r;
+}
+
+// One BVH8 node against one ray: returns the hit mask (bits 24..31 = interior children in
+// octant-sorted order, bits 0..23 = triangles relative to the node's triangle base).
+__device__ __forceinline__ uint32_t intersect_node8(const float4 &n0, const float4 &n1, const float4 &n2, const float4 &n3,
+                                                    const float4 &n4, float ox, float oy, float oz, float idx, float idy,
+                                                    float idz, uint32_t octinv4, float t_far_limit, uint32_t bias) {
+    const uint32_t ebits = __float_as_uint(n0.w);
+    const NodeAxis X = node_axis(n0.x, ox, idx, ebits & 0xffu);
+    const NodeAxis Y = node_axis(n0.y, oy, idy, (ebits >> 8) & 0xffu);
+    const NodeAxis Z = node_axis(n0.z, oz, idz, (ebits >> 16) & 0xffu);
+    const bool negx = idx < 0.f, negy = idy < 0.f, negz = idz < 0.f;
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const uint32_t meta4 = __float_as_uint(h ? n1.w : n1.z);
+        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+        const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+        const uint32_t qlox = __float_as_uint(h ? n2.y : n2.x), qloy = __float_as_uint(h ? n2.w : n2.z);
+        const uint32_t qloz = __float_as_uint(h ? n3.y : n3.x), qhix = __float_as_uint(h ? n3.w : n3.z);
+        const uint32_t qhiy = __float_as_uint(h ? n4.y : n4.x), qhiz = __float_as_uint(h ? n4.w : n4.z);
+        const uint32_t nx = negx ? qhix : qlox, fx = negx ? qlox : qhix;
+        const uint32_t ny = negy ? qhiy : qloy, fy = negy ? qloy : qhiy;
+        const uint32_t nz = negz ? qhiz : qloz, fz = negz ? qloz : qhiz;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const float tnx = fmaf(byte_to_float_biased(nx, j, bias), X.a, X.lo), tfx = fmaf(byte_to_float_biased(fx, j, bias), X.a, X.hi);
+            const float tny = fmaf(byte_to_float_biased(ny, j, bias), Y.a, Y.lo), tfy = fmaf(byte_to_float_biased(fy, j, bias), Y.a, Y.hi);
+            const float tnz = fmaf(byte_to_float_biased(nz, j, bias), Z.a, Z.lo), tfz = fmaf(byte_to_float_biased(fz, j, bias), Z.a, Z.hi);
+            const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
+            const float tf = fminf(fminf(tfx, tfy), fminf(tfz, t_far_limit));
+            if (tn <= tf) {
+                const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu;
+                const uint32_t bi = (bit_index4 >> (8 * j)) & 0xffu;
+                hitmask |= cb << bi;
+            }
+        }
+    }
+    return hitmask;
 }
 
 // sm_stack: this thread's column of the CTA's shared stack, addressed as sm_stack[depth * stride]
@@ -49,7 +114,6 @@ __device__ __forceinline__ bool traverse_bvh8(const BVH8 &bvh, float ox, float o
     const bool negx = idx < 0.f, negy = idy < 0.f, negz = idz < 0.f; // sign of the clamped reciprocal (covers -0)
     const uint32_t octinv = (negx ? 0u : 4u) | (negy ? 0u : 2u) | (negz ? 0u : 1u);
     const uint32_t octinv4 = octinv * 0x01010101u;
-    constexpr float kSlack = 0x1p-20f; // relative guard for the decode arithmetic
 
     uint2 lstack[LOCAL_STACK];
     int sp = 0;
@@ -74,47 +138,9 @@ __device__ __forceinline__ bool traverse_bvh8(const BVH8 &bvh, float ox, float o
             if (COUNT) ctr.nodes++;
 
             const uint32_t ebits = __float_as_uint(n0.w);
-            const float sx = __uint_as_float((ebits & 0xffu) << 23);
-            const float sy = __uint_as_float(((ebits >> 8) & 0xffu) << 23);
-            const float sz = __uint_as_float(((ebits >> 16) & 0xffu) << 23);
-            const float ax = sx * idx, ay = sy * idy, az = sz * idz;
-            const float bx = (n0.x - ox) * idx, by = (n0.y - oy) * idy, bz = (n0.z - oz) * idz;
-            // decode error bound per axis: k*eps*(|origin term| + 256*|scale term|)
-            const float ex = kSlack * (fabsf(bx) + 256.f * fabsf(ax));
-            const float ey = kSlack * (fabsf(by) + 256.f * fabsf(ay));
-            const float ez = kSlack * (fabsf(bz) + 256.f * fabsf(az));
-            const float bxl = bx - ex, bxh = bx + ex, byl = by - ey, byh = by + ey, bzl = bz - ez, bzh = bz + ez;
-
             ng.x = __float_as_uint(n1.x);
             tg.x = __float_as_uint(n1.y);
-            uint32_t hitmask = 0;
-#pragma unroll
-            for (int h = 0; h < 2; h++) {
-                const uint32_t meta4 = __float_as_uint(h ? n1.w : n1.z);
-                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-                const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
-                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-                const uint32_t qlox = __float_as_uint(h ? n2.y : n2.x), qloy = __float_as_uint(h ? n2.w : n2.z);
-                const uint32_t qloz = __float_as_uint(h ? n3.y : n3.x), qhix = __float_as_uint(h ? n3.w : n3.z);
-                const uint32_t qhiy = __float_as_uint(h ? n4.y : n4.x), qhiz = __float_as_uint(h ? n4.w : n4.z);
-                const uint32_t nx = negx ? qhix : qlox, fx = negx ? qlox : qhix;
-                const uint32_t ny = negy ? qhiy : qloy, fy = negy ? qloy : qhiy;
-                const uint32_t nz = negz ? qhiz : qloz, fz = negz ? qloz : qhiz;
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const float tnx = fmaf(byte_to_float(nx, j), ax, bxl), tfx = fmaf(byte_to_float(fx, j), ax, bxh);
-                    const float tny = fmaf(byte_to_float(ny, j), ay, byl), tfy = fmaf(byte_to_float(fy, j), ay, byh);
-                    const float tnz = fmaf(byte_to_float(nz, j), az, bzl), tfz = fmaf(byte_to_float(fz, j), az, bzh);
-                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
-                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, hit.t));
-                    if (tn <= tf) {
-                        const uint32_t cb = (child_bits4 >> (8 * j)) & 0xffu;
-                        const uint32_t bi = (bit_index4 >> (8 * j)) & 0xffu;
-                        hitmask |= cb << bi;
-                    }
-                }
-            }
+            const uint32_t hitmask = intersect_node8(n0, n1, n2, n3, n4, ox, oy, oz, idx, idy, idz, octinv4, hit.t, 0x47000000u);
             ng.y = (hitmask & 0xff000000u) | (ebits >> 24);
             tg.y = hitmask & 0x00ffffffu;
         }
