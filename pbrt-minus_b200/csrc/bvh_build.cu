@@ -262,6 +262,9 @@ struct CollapseArgs {
     const float *P;
     const int32_t *idx;
     const uint32_t *sorted_prim;
+    const int32_t *tri_material; // optional per-triangle ids, carried in the w lanes of the leaf record
+    const int32_t *tri_light;
+    const uint8_t *tri_flip;
     float4 *nodes; // BVH8 out
     float4 *tris;  // re-laid-out triangles out
     const int2 *q_in; // (bvh2 node, bvh8 node index)
@@ -456,8 +459,12 @@ __global__ void __launch_bounds__(128) k_collapse_level(CollapseArgs a) {
                 const TriVerts tv = load_tri(a.P, a.idx, prim);
                 float4 *dst = a.tris + 3 * (size_t)(tri_base + tri_off + k);
                 dst[0] = make_float4(tv.a.x, tv.a.y, tv.a.z, __int_as_float((int)prim));
-                dst[1] = make_float4(tv.b.x, tv.b.y, tv.b.z, 0.f);
-                dst[2] = make_float4(tv.c.x, tv.c.y, tv.c.z, 0.f);
+                // v1.w = material id | flip << 31 (reverse_orientation ^ swaps_handedness), v2.w = light id (-1: none)
+                const uint32_t mat = (a.tri_material ? (uint32_t)a.tri_material[prim] : 0u) |
+                                     ((a.tri_flip && a.tri_flip[prim]) ? 0x80000000u : 0u);
+                const int light = a.tri_light ? a.tri_light[prim] : -1;
+                dst[1] = make_float4(tv.b.x, tv.b.y, tv.b.z, __uint_as_float(mat));
+                dst[2] = make_float4(tv.c.x, tv.c.y, tv.c.z, __int_as_float(light));
             }
             tri_off += tcount[i];
         }
@@ -596,6 +603,9 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
         a.P = s->d_P;
         a.idx = s->d_idx;
         a.sorted_prim = s->d_sorted_prim;
+        a.tri_material = s->d_tri_material;
+        a.tri_light = s->d_tri_light;
+        a.tri_flip = s->d_tri_flip;
         a.nodes = s->d_nodes;
         a.tris = s->d_tris;
         a.q_in = q[cur];

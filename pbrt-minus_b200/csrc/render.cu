@@ -1,22 +1,1107 @@
-// render.cu -- wavefront path integrator entry points (film, render, stage probes).
+// render.cu -- the wavefront path integrator: scene-side tables, SoA path pool, stage kernels,
+// film, and the host loop that drives a pass as a fixed kernel sequence without host syncs.
+//
+// Replaces WavefrontPathIntegrator::render (integrators/wavefront_path.cu:594-735) and its kernels:
+//   gpu_generate_new_path :245-287  -> k_generate     (sampler start, filter sample, wavelengths, camera ray)
+//   ray_cast              :348-366  -> k_trace_wf<false> (trace.cu)
+//   control_logic         :68-214   -> k_logic        (termination, RR, Le + MIS, film add, material routing)
+//   gpu_evaluate_material :322-346 + sample_bsdf :438-475 + sample_Ld_volume (megakernel_path.cu:185-264)
+//                                   -> k_shade<MAT>   (one kernel per material, BSDF in registers,
+//                                                      NEE emitted as a shadow-queue entry)
+//   inline fast_intersect / compute_transmittance (base/integrator_base.cu:12-71)
+//                                   -> k_trace_wf<true> (any-hit on the shadow queue + resolve)
+//   write_frame_buffer :216-234 + CPU std::sort :689-694 + RGBFilm::add_sample (film/rgb_film.cu:63-80)
+//                                   -> fp32 vector atomics on the film inside k_logic
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cmath>
+#include <numeric>
+#include <set>
+
+#include "bxdf.cuh"
 #include "common.cuh"
 #include "sampler.cuh"
+#include "sphere.cuh"
+#include "wavefront.cuh"
 
 struct b200pt_film {
     b200pt_scene *scene = nullptr;
     int32_t width = 0, height = 0;
-    float4 *d_accum = nullptr; // {sum_x, sum_y, sum_z, sum_w}
+    float4 *d_accum = nullptr; // {sum_x, sum_y, sum_z, sum_w} (sensor XYZ * filter weight, filter weight)
 };
 
 namespace b200pt {
 
 struct RenderData {
-    int dummy = 0;
+    bool have_render = false;
+    std::vector<void *> allocs;
+    // scene tables
+    SpecRec *d_spec = nullptr;
+    float *d_spec_pool = nullptr;
+    float *d_illuminant = nullptr;
+    MatRec *d_materials = nullptr;
+    LightRec *d_lights = nullptr;
+    AliasBin *d_alias = nullptr;
+    int n_lights = 0, n_materials = 0, n_spectra = 0;
+    FilterTab filter = {};
+    CameraRec camera = {};
+    float *d_cie[3] = {nullptr, nullptr, nullptr};
+    int width = 0, height = 0;
+    float imaging_ratio = 1.f;
+    float out_rgb[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    std::vector<b200pt_light> h_lights;
+    // path pool (allocated on first render / when the pool size changes)
+    int pool_size = 0;
+    PathPool pool = {};
+    WFQueues q = {};
+    WFCounters *d_counters = nullptr;
+    WFCounters *h_counters = nullptr; // pinned
+    std::vector<void *> pool_allocs;
 };
 
+template <typename T>
+static int dev_upload(RenderData *r, T **dst, const T *src, size_t count, cudaStream_t st) {
+    *dst = nullptr;
+    void *p = nullptr;
+    CU_TRY(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+    r->allocs.push_back(p);
+    if (count) CU_TRY(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, st));
+    *dst = (T *)p;
+    return B200PT_OK;
+}
+
 void free_render(b200pt_scene *s) {
+    if (!s->render) return;
+    for (void *p : s->render->allocs) cudaFree(p);
+    for (void *p : s->render->pool_allocs) cudaFree(p);
+    if (s->render->d_counters) cudaFree(s->render->d_counters);
+    if (s->render->h_counters) cudaFreeHost(s->render->h_counters);
     delete s->render;
     s->render = nullptr;
+}
+
+// PiecewiseConstant1D ctor (distribution/piecewise_constant_1d.h:14-41), in fp32 like the reference
+static float build_pc1d(const float *f, int n, float mn, float mx, float *func, float *cdf) {
+    for (int i = 0; i < n; i++) func[i] = std::fabs(f[i]);
+    cdf[0] = 0.f;
+    for (int i = 1; i < n + 1; i++) cdf[i] = cdf[i - 1] + func[i - 1] * (mx - mn) / n;
+    const float func_int = cdf[n];
+    if (func_int == 0.f) {
+        for (int i = 1; i < n + 1; i++) cdf[i] = float(i) / float(n);
+    } else {
+        for (int i = 1; i < n + 1; i++) cdf[i] /= func_int;
+    }
+    return func_int;
+}
+
+__global__ void k_light_power(SpectrumTable tab, const LightRec *lights, int n, float *out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    // light_samplers/power_light_sampler.cu:15-21: phi at the wavelengths of sample_visible(0.5)
+    S4 lambda, pdf;
+    sample_visible(0.5f, &lambda, &pdf);
+    const LightRec L = lights[i];
+    const S4 Le = spectrum_sample(tab, L.spectrum, lambda) * L.scale;
+    const S4 phi = Le * (kPi * ((L.flags & 1) ? 2.f : 1.f) * L.area);
+    out[i] = average(safe_div(phi, pdf));
+}
+
+} // namespace b200pt
+
+using namespace b200pt;
+
+// AliasTable ctor (distribution/alias_table.cu:9-68): repeatedly take the smallest bin, top it up
+// from the largest.  The reference re-sorts the whole vector per step (O(n^2 log n)); an ordered
+// set gives the same extraction order (up to ties) in O(n log n), which config C4 (100 k lights) needs.
+static void build_alias(const std::vector<float> &values, std::vector<AliasBin> &bins, std::vector<float> &pdfs) {
+    const int n = (int)values.size();
+    bins.assign(n, AliasBin{1.f, 0, -1});
+    pdfs.assign(n, 0.f);
+    double sum = 0.0;
+    for (float v : values) sum += v;
+    if (sum == 0.0) {
+        for (int i = 0; i < n; i++) {
+            bins[i] = AliasBin{1.f, i, -1};
+            pdfs[i] = float(i) / n;
+        }
+        return;
+    }
+    struct B {
+        float p;
+        int first, second, seq;
+    };
+    auto cmp = [](const B &a, const B &b) { return a.p < b.p || (a.p == b.p && a.seq < b.seq); };
+    std::vector<B> all(n);
+    for (int i = 0; i < n; i++) {
+        all[i] = B{float(values[i] * n / sum), i, -1, i};
+        pdfs[i] = float(values[i] / sum);
+    }
+    std::multiset<B, decltype(cmp)> todo(all.begin(), all.end(), cmp);
+    const float tol = 0.001f;
+    int out = 0;
+    while (!todo.empty()) {
+        if (todo.size() == 1) {
+            const B b = *todo.begin();
+            bins[out++] = AliasBin{b.p, b.first, b.second};
+            break;
+        }
+        B lo = *todo.begin();
+        todo.erase(todo.begin());
+        if (lo.p < 1.f - tol) {
+            const float under = 1.f - lo.p;
+            auto it = std::prev(todo.end());
+            B hi = *it;
+            todo.erase(it);
+            lo.second = hi.first;
+            hi.p -= under;
+            todo.insert(hi);
+        }
+        bins[out++] = AliasBin{lo.p, lo.first, lo.second};
+    }
+}
+
+int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
+    RenderData *r = new RenderData();
+    s->render = r;
+    cudaStream_t st = s->stream;
+    // ---- spheres
+    s->n_spheres = desc->n_spheres;
+    if (desc->n_spheres > 0) {
+        if (!desc->spheres) {
+            set_error("b200pt_scene_create: n_spheres > 0 but spheres == NULL");
+            return B200PT_ERR_INVALID;
+        }
+        std::vector<SphereRec> recs(desc->n_spheres);
+        for (int i = 0; i < desc->n_spheres; i++) {
+            const b200pt_sphere &sp = desc->spheres[i];
+            SphereRec &o = recs[i];
+            for (int k = 0; k < 12; k++) {
+                o.rfo[k] = sp.render_from_object[k];
+                o.ofr[k] = sp.object_from_render[k];
+            }
+            // shapes/sphere.h ctor: z range clamped to the radius, theta range from z
+            o.radius = sp.radius;
+            o.z_min = std::min(std::max(std::min(sp.z_min, sp.z_max), -sp.radius), sp.radius);
+            o.z_max = std::min(std::max(std::max(sp.z_min, sp.z_max), -sp.radius), sp.radius);
+            o.theta_z_min = std::acos(std::min(std::max(std::min(sp.z_min, sp.z_max) / sp.radius, -1.f), 1.f));
+            o.theta_z_max = std::acos(std::min(std::max(std::max(sp.z_min, sp.z_max) / sp.radius, -1.f), 1.f));
+            o.phi_max = sp.phi_max;
+            o.flip = (sp.reverse_orientation != 0) ^ (sp.transform_swaps_handedness != 0);
+            o.material = sp.material;
+            if (sp.light >= 0) {
+                set_error("b200pt_scene_create: emissive spheres are not supported");
+                return B200PT_ERR_UNSUPPORTED;
+            }
+        }
+        CU_TRY(cudaMalloc((void **)&s->d_spheres, recs.size() * sizeof(SphereRec)));
+        CU_TRY(cudaMemcpyAsync(s->d_spheres, recs.data(), recs.size() * sizeof(SphereRec), cudaMemcpyHostToDevice, st));
+        CU_TRY(cudaStreamSynchronize(st));
+    }
+    if (!desc->film || !desc->camera || !desc->filter) return B200PT_OK; // traversal-only scene
+    const b200pt_film_desc &fd = *desc->film;
+    if (fd.width <= 0 || fd.height <= 0 || !fd.cie_x || !fd.cie_y || !fd.cie_z || !fd.illuminant) {
+        set_error("b200pt_scene_create: incomplete film description");
+        return B200PT_ERR_INVALID;
+    }
+    // ---- spectra
+    std::vector<SpecRec> spec(desc->n_spectra);
+    std::vector<float> pool;
+    for (int i = 0; i < desc->n_spectra; i++) {
+        const b200pt_spectrum &sp = desc->spectra[i];
+        SpecRec &o = spec[i];
+        o.type = sp.type;
+        o.n = sp.n;
+        o.offset = (int)pool.size();
+        o.pad = 0;
+        for (int k = 0; k < 4; k++) o.c[k] = sp.c[k];
+        if (sp.type == B200PT_SPEC_PIECEWISE) {
+            if (sp.n < 2 || !sp.lambda || !sp.value) {
+                set_error("b200pt_scene_create: spectrum %d: piecewise spectrum needs >= 2 knots", i);
+                return B200PT_ERR_INVALID;
+            }
+            pool.insert(pool.end(), sp.lambda, sp.lambda + sp.n);
+            pool.insert(pool.end(), sp.value, sp.value + sp.n);
+        } else if (sp.type == B200PT_SPEC_DENSE) {
+            if (sp.n != 471 || !sp.value) {
+                set_error("b200pt_scene_create: spectrum %d: dense spectrum needs 471 samples", i);
+                return B200PT_ERR_INVALID;
+            }
+            pool.insert(pool.end(), sp.value, sp.value + sp.n);
+        } else if (sp.type < 0 || sp.type > B200PT_SPEC_DENSE) {
+            set_error("b200pt_scene_create: spectrum %d: unknown type %d", i, sp.type);
+            return B200PT_ERR_INVALID;
+        }
+    }
+    r->n_spectra = desc->n_spectra;
+    int rc;
+    if ((rc = dev_upload(r, &r->d_spec, spec.data(), spec.size(), st))) return rc;
+    if ((rc = dev_upload(r, &r->d_spec_pool, pool.data(), pool.size(), st))) return rc;
+    if ((rc = dev_upload(r, &r->d_illuminant, fd.illuminant, 471, st))) return rc;
+    if ((rc = dev_upload(r, &r->d_cie[0], fd.cie_x, 471, st))) return rc;
+    if ((rc = dev_upload(r, &r->d_cie[1], fd.cie_y, 471, st))) return rc;
+    if ((rc = dev_upload(r, &r->d_cie[2], fd.cie_z, 471, st))) return rc;
+    // ---- materials
+    std::vector<MatRec> mats(desc->n_materials);
+    auto spec_ok = [&](int id) { return id >= 0 && id < desc->n_spectra; };
+    for (int i = 0; i < desc->n_materials; i++) {
+        const b200pt_material &m = desc->materials[i];
+        mats[i] = MatRec{m.type, m.reflectance, m.eta, m.k, m.u_roughness, m.v_roughness, m.remap_roughness, 0};
+        bool ok = true;
+        if (m.type == B200PT_MAT_DIFFUSE) ok = spec_ok(m.reflectance);
+        else if (m.type == B200PT_MAT_CONDUCTOR) ok = (spec_ok(m.eta) && spec_ok(m.k)) || (m.eta < 0 && spec_ok(m.reflectance));
+        else if (m.type == B200PT_MAT_DIELECTRIC) ok = spec_ok(m.eta);
+        else ok = false;
+        if (!ok) {
+            set_error("b200pt_scene_create: material %d is inconsistent (type %d)", i, m.type);
+            return B200PT_ERR_INVALID;
+        }
+    }
+    r->n_materials = desc->n_materials;
+    if ((rc = dev_upload(r, &r->d_materials, mats.data(), mats.size(), st))) return rc;
+    if (desc->tri_material)
+        for (int64_t i = 0; i < desc->n_triangles; i++)
+            if (desc->tri_material[i] < 0 || desc->tri_material[i] >= desc->n_materials) {
+                set_error("b200pt_scene_create: triangle %lld has material id %d", (long long)i, desc->tri_material[i]);
+                return B200PT_ERR_INVALID;
+            }
+    if (desc->n_materials == 0) {
+        set_error("b200pt_scene_create: a render scene needs at least one material");
+        return B200PT_ERR_INVALID;
+    }
+    // ---- lights
+    r->n_lights = desc->n_lights;
+    std::vector<LightRec> lights(desc->n_lights);
+    for (int i = 0; i < desc->n_lights; i++) {
+        const b200pt_light &l = desc->lights[i];
+        if (l.triangle < 0 || l.triangle >= desc->n_triangles || !spec_ok(l.spectrum)) {
+            set_error("b200pt_scene_create: light %d is inconsistent", i);
+            return B200PT_ERR_INVALID;
+        }
+        if (!desc->tri_light || desc->tri_light[l.triangle] != i) {
+            set_error("b200pt_scene_create: tri_light[%d] must be %d", l.triangle, i);
+            return B200PT_ERR_INVALID;
+        }
+        LightRec &o = lights[i];
+        const int32_t *v = desc->indices + 3 * (size_t)l.triangle;
+        for (int k = 0; k < 3; k++) {
+            o.p0[k] = desc->P[3 * (size_t)v[0] + k];
+            o.p1[k] = desc->P[3 * (size_t)v[1] + k];
+            o.p2[k] = desc->P[3 * (size_t)v[2] + k];
+        }
+        o.scale = l.scale;
+        o.spectrum = l.spectrum;
+        o.flags = (l.two_sided ? 1 : 0) | ((desc->tri_flip && desc->tri_flip[l.triangle]) ? 2 : 0);
+        o.pmf = 0.f;
+        const float e1[3] = {o.p1[0] - o.p0[0], o.p1[1] - o.p0[1], o.p1[2] - o.p0[2]};
+        const float e2[3] = {o.p2[0] - o.p0[0], o.p2[1] - o.p0[1], o.p2[2] - o.p0[2]};
+        const float cx = e1[1] * e2[2] - e1[2] * e2[1], cy = e1[2] * e2[0] - e1[0] * e2[2], cz = e1[0] * e2[1] - e1[1] * e2[0];
+        o.area = 0.5f * std::sqrt(cx * cx + cy * cy + cz * cz);
+        o.pad[0] = o.pad[1] = 0;
+    }
+    if ((rc = dev_upload(r, &r->d_lights, lights.data(), lights.size(), st))) return rc;
+    if (desc->n_lights > 0) {
+        // power weights on the device (needs the spectra), alias table on the host
+        float *d_w = nullptr;
+        std::vector<float> w(desc->n_lights);
+        if ((rc = dev_upload(r, &d_w, w.data(), w.size(), st))) return rc;
+        SpectrumTable tab{r->d_spec, r->d_spec_pool, r->d_illuminant};
+        k_light_power<<<(desc->n_lights + 127) / 128, 128, 0, st>>>(tab, r->d_lights, desc->n_lights, d_w);
+        CU_TRY(cudaMemcpyAsync(w.data(), d_w, w.size() * 4, cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaStreamSynchronize(st));
+        std::vector<AliasBin> bins;
+        std::vector<float> pdfs;
+        build_alias(w, bins, pdfs);
+        for (int i = 0; i < desc->n_lights; i++) lights[i].pmf = pdfs[i];
+        CU_TRY(cudaMemcpyAsync(r->d_lights, lights.data(), lights.size() * sizeof(LightRec), cudaMemcpyHostToDevice, st));
+        if ((rc = dev_upload(r, &r->d_alias, bins.data(), bins.size(), st))) return rc;
+        CU_TRY(cudaStreamSynchronize(st));
+    }
+    // ---- pixel filter: FilterSampler + PiecewiseConstant2D (filters/filter_sampler.cu:4-20,
+    //      distribution/piecewise_constant_2d.h:11-32)
+    const b200pt_filter &fl = *desc->filter;
+    if (fl.nx <= 0 || fl.ny <= 0 || !fl.f) {
+        set_error("b200pt_scene_create: filter table missing");
+        return B200PT_ERR_INVALID;
+    }
+    {
+        const int nx = fl.nx, ny = fl.ny;
+        std::vector<float> cfunc(nx * ny), ccdf(ny * (nx + 1)), cint(ny), mfunc(ny), mcdf(ny + 1);
+        for (int v = 0; v < ny; v++) cint[v] = build_pc1d(fl.f + v * nx, nx, -fl.radius_x, fl.radius_x, &cfunc[v * nx], &ccdf[v * (nx + 1)]);
+        const float mint = build_pc1d(cint.data(), ny, -fl.radius_y, fl.radius_y, mfunc.data(), mcdf.data());
+        FilterTab &t = r->filter;
+        t.nx = nx;
+        t.ny = ny;
+        t.min_x = -fl.radius_x;
+        t.max_x = fl.radius_x;
+        t.min_y = -fl.radius_y;
+        t.max_y = fl.radius_y;
+        t.marg_int = mint;
+        float *p;
+        if ((rc = dev_upload(r, &p, fl.f, (size_t)nx * ny, st))) return rc;
+        t.f = p;
+        if ((rc = dev_upload(r, &p, cfunc.data(), cfunc.size(), st))) return rc;
+        t.cond_func = p;
+        if ((rc = dev_upload(r, &p, ccdf.data(), ccdf.size(), st))) return rc;
+        t.cond_cdf = p;
+        if ((rc = dev_upload(r, &p, cint.data(), cint.size(), st))) return rc;
+        t.cond_int = p;
+        if ((rc = dev_upload(r, &p, mfunc.data(), mfunc.size(), st))) return rc;
+        t.marg_func = p;
+        if ((rc = dev_upload(r, &p, mcdf.data(), mcdf.size(), st))) return rc;
+        t.marg_cdf = p;
+        CU_TRY(cudaStreamSynchronize(st));
+    }
+    for (int k = 0; k < 16; k++) {
+        r->camera.cfr[k] = desc->camera->camera_from_raster[k];
+        r->camera.rfc[k] = desc->camera->render_from_camera[k];
+    }
+    r->camera.lens_radius = desc->camera->lens_radius;
+    r->camera.focal_distance = desc->camera->focal_distance;
+    r->width = fd.width;
+    r->height = fd.height;
+    r->imaging_ratio = fd.imaging_ratio;
+    for (int k = 0; k < 9; k++) r->out_rgb[k] = fd.output_rgb_from_sensor_rgb[k];
+    r->have_render = true;
+    return B200PT_OK;
+}
+
+namespace b200pt {
+
+constexpr int WF_BLOCK = 256;
+
+// PiecewiseConstant1D::sample (distribution/piecewise_constant_1d.h:46-63)
+__device__ __forceinline__ float pc1d_sample(const float *func, const float *cdf, float func_int, int size, float mn, float mx,
+                                             float u, float *pdf, int *offset) {
+    // find_interval(size + 1, cdf[i] <= u)
+    int sz = size + 1 - 2, first = 1;
+    while (sz > 0) {
+        const int half = sz >> 1, middle = first + half;
+        const bool pred = __ldg(cdf + middle) <= u;
+        first = pred ? middle + 1 : first;
+        sz = pred ? sz - (half + 1) : half;
+    }
+    int o = first - 1;
+    o = o < 0 ? 0 : (o > size - 1 ? size - 1 : o);
+    *offset = o;
+    const float c0 = __ldg(cdf + o), c1 = __ldg(cdf + o + 1);
+    float du = u - c0;
+    if (c1 - c0 > 0.f) du /= c1 - c0;
+    *pdf = func_int > 0.f ? __ldg(func + o) / func_int : 0.f;
+    return lerpf((o + du) / size, mn, mx);
+}
+
+// FilterSampler::sample (filters/filter_sampler.h:23-30)
+__device__ __forceinline__ void filter_sample(const FilterTab &t, float2 u, float2 *p, float *weight) {
+    float pdf0, pdf1;
+    int ox, oy;
+    const float d1 = pc1d_sample(t.marg_func, t.marg_cdf, t.marg_int, t.ny, t.min_y, t.max_y, u.y, &pdf1, &oy);
+    const float d0 = pc1d_sample(t.cond_func + oy * t.nx, t.cond_cdf + oy * (t.nx + 1), __ldg(t.cond_int + oy), t.nx, t.min_x,
+                                 t.max_x, u.x, &pdf0, &ox);
+    *p = make_float2(d0, d1);
+    *weight = __ldg(t.f + oy * t.nx + ox) / (pdf0 * pdf1);
+}
+
+__device__ __forceinline__ Sampler load_sampler(const WF &wf, int slot, const int4 &ids) {
+    Sampler s;
+    s.kind = wf.sampler_kind;
+    s.spp = wf.spp;
+    s.sqrt_spp = wf.sqrt_spp;
+    s.pixel_idx = ids.x;
+    s.sample_idx = ids.y;
+    s.dimension = ids.z;
+    s.state = wf.pool.rng[slot];
+    s.inc = (hash_i32(ids.x) << 1u) | 1u;
+    return s;
+}
+
+__global__ void k_pass_begin(WF wf, int cur) {
+    WFCounters *c = wf.c;
+    c->rays_closest += c->n_rays[cur];
+    c->n_rays[cur ^ 1] = 0;
+    c->n_mat[0] = c->n_mat[1] = c->n_mat[2] = 0;
+    c->n_shadow = 0;
+    c->ticket_closest = 0;
+    c->ticket_shadow = 0;
+}
+// runs between the stages that fill the free list (k_logic) and the one that drains it (k_generate)
+__global__ void k_after_generate(WF wf) { wf.c->n_free = 0; }
+__global__ void k_pass_end(WF wf) { wf.c->rays_shadow += wf.c->n_shadow; }
+
+__global__ void k_init_pool(WF wf) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < wf.pool_size) wf.q.free_slots[i] = i;
+    if (i == 0) {
+        WFCounters z = {};
+        z.n_free = (unsigned)wf.pool_size;
+        *wf.c = z;
+    }
+}
+
+// ---- gpu_generate_new_path (integrators/wavefront_path.cu:245-287)
+__global__ void __launch_bounds__(WF_BLOCK) k_generate(WF wf, int cur) {
+    const unsigned n = wf.c->n_free;
+    const unsigned stride = gridDim.x * blockDim.x;
+    const unsigned n_round = (n + 31u) & ~31u;
+    const int lane = threadIdx.x & 31;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        const bool have_slot = i < n;
+        // one 64-bit atomic per warp claims consecutive path ids (the reference: one per path)
+        const unsigned m = __ballot_sync(0xffffffffu, have_slot);
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&wf.c->next_path, (unsigned long long)__popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        const long long id = (long long)base + __popc(m & ((1u << lane) - 1u));
+        const bool live = have_slot && id < wf.total_paths;
+        int slot = -1;
+        if (live) {
+            slot = wf.q.free_slots[i];
+            const int pixel = int(id % wf.n_pixels);
+            const int sample = wf.sample_begin + int(id / wf.n_pixels);
+            const int px = pixel % wf.film.width, py = pixel / wf.film.width;
+            Sampler s;
+            s.start(wf.sampler_kind, wf.spp, wf.sqrt_spp, pixel, sample, 0);
+            // Sampler::get_camera_sample (base/sampler.cu:167-171)
+            float2 fp;
+            float fw;
+            filter_sample(wf.filter, s.get_2d(), &fp, &fw);
+            const float fx = float(px) + fp.x + 0.5f, fy = float(py) + fp.y + 0.5f;
+            S4 lambda, lpdf;
+            sample_visible(s.get_1d(), &lambda, &lpdf);
+            // PerspectiveCamera::generate_ray (cameras/perspective.cu:65-86)
+            const float *M = wf.camera.cfr;
+            V3 pc = v3(M[0] * fx + M[1] * fy + M[3], M[4] * fx + M[5] * fy + M[7], M[8] * fx + M[9] * fy + M[11]);
+            const float wp = M[12] * fx + M[13] * fy + M[15];
+            if (wp != 1.f) pc = pc / wp;
+            V3 o = v3(0.f, 0.f, 0.f), d = normalize(pc);
+            if (wf.camera.lens_radius > 0.f) {
+                const float2 pl = sample_disk_concentric(s.get_2d());
+                const float ft = wf.camera.focal_distance / d.z;
+                const V3 pfocus = ft * d;
+                o = v3(wf.camera.lens_radius * pl.x, wf.camera.lens_radius * pl.y, 0.f);
+                d = normalize(pfocus - o);
+            }
+            // Transform::operator()(Ray) (euclidean_space/transform.cu:19-33): origin pushed to the
+            // edge of its transform error bound
+            const float *R = wf.camera.rfc;
+            const V3 ow = xf_point(R, o);
+            const V3 oerr = xf_point_error(R, o, v3(0.f, 0.f, 0.f), true);
+            const V3 dw = xf_vector(R, d);
+            V3 orig = ow;
+            const float l2 = len2(dw);
+            if (l2 > 0.f) {
+                const float dt = dot(vabs(dw), oerr) / l2;
+                orig = ow + dt * dw;
+            }
+            wf.pool.ray_o[slot] = make_float4(orig.x, orig.y, orig.z, kInf);
+            wf.pool.ray_d[slot] = make_float4(dw.x, dw.y, dw.z, 0.f);
+            wf.pool.beta[slot] = s4(1.f);
+            wf.pool.L[slot] = s4(0.f);
+            wf.pool.lambda[slot] = lambda;
+            wf.pool.lpdf[slot] = lpdf;
+            wf.pool.misc[slot] = make_float4(fw, 0.f, 0.f, 0.f);
+            wf.pool.rng[slot] = s.state;
+            // depth 0, next_time_russian_roulette = 8 (util/russian_roulette.h:5)
+            wf.pool.ids[slot] = make_int4(pixel, sample, s.dimension, 8 << 16);
+        }
+        queue_push(&wf.c->n_rays[cur ^ 1], wf.q.rays[cur ^ 1], slot, live);
+    }
+}
+
+// RGBFilm::add_sample + PixelSensor::to_sensor_rgb (film/rgb_film.cu:63-80, film/pixel_sensor.h:19-26)
+__device__ __forceinline__ void film_add(const WF &wf, int pixel, S4 L, S4 lambda, S4 lpdf, float weight) {
+    if (weight == 0.f) return;
+    const S4 sp = safe_div(L, lpdf);
+    const S4 xb = make_float4(dense_lookup(wf.film.cie_x, lambda.x), dense_lookup(wf.film.cie_x, lambda.y),
+                              dense_lookup(wf.film.cie_x, lambda.z), dense_lookup(wf.film.cie_x, lambda.w));
+    const S4 yb = make_float4(dense_lookup(wf.film.cie_y, lambda.x), dense_lookup(wf.film.cie_y, lambda.y),
+                              dense_lookup(wf.film.cie_y, lambda.z), dense_lookup(wf.film.cie_y, lambda.w));
+    const S4 zb = make_float4(dense_lookup(wf.film.cie_z, lambda.x), dense_lookup(wf.film.cie_z, lambda.y),
+                              dense_lookup(wf.film.cie_z, lambda.z), dense_lookup(wf.film.cie_z, lambda.w));
+    const float X = wf.film.imaging_ratio * average(xb * sp), Y = wf.film.imaging_ratio * average(yb * sp),
+                Z = wf.film.imaging_ratio * average(zb * sp);
+    // one 128-bit vector reduction per finished path (sm_90+), instead of the reference's
+    // sort-by-pixel on the CPU + serial per-pixel adds
+    atomicAdd(wf.film.accum + pixel, make_float4(weight * X, weight * Y, weight * Z, weight));
+}
+
+// geometric normal of a leaf-record triangle as Triangle::interaction_from_intersection sets it
+// (shapes/triangle.cu:388-394): normalize(dp02 x dp12), flipped by reverse_orientation ^ swaps_handedness
+__device__ __forceinline__ V3 tri_normal(V3 p0, V3 p1, V3 p2, bool flip) {
+    const V3 n = normalize(cross(p0 - p2, p1 - p2));
+    return flip ? -n : n;
+}
+
+// ---- control_logic (integrators/wavefront_path.cu:68-214)
+__global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf, int cur) {
+    const unsigned n = wf.c->n_rays[cur];
+    const unsigned stride = gridDim.x * blockDim.x;
+    const unsigned n_round = (n + 31u) & ~31u;
+    unsigned n_finished = 0;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        const bool act = i < n;
+        int slot = -1, route = -1; // route: material type, or -1
+        bool terminate = false;
+        if (act) {
+            slot = wf.q.rays[cur][i];
+            int4 ids = wf.pool.ids[slot];
+            int depth = (ids.w >> 8) & 0xff, next_rr = (ids.w >> 16) & 0xff;
+            S4 beta = wf.pool.beta[slot];
+            S4 L = wf.pool.L[slot];
+            const float4 hit = wf.pool.hit[slot];
+            const int prim = __float_as_int(hit.x);
+            terminate = depth >= wf.max_depth || !is_positive(beta);
+            bool dirty_L = false;
+            if (!terminate && depth >= next_rr) {
+                // russian_roulette (util/russian_roulette.h:12-29)
+                next_rr += 1;
+                Sampler s = load_sampler(wf, slot, ids);
+                const float q = fminf(max_component(beta), 0.95f);
+                if (s.get_1d() > q) {
+                    beta = s4(0.f);
+                    terminate = true;
+                } else {
+                    beta = beta / q;
+                }
+                wf.pool.beta[slot] = beta;
+                wf.pool.rng[slot] = s.state;
+                ids.z = s.dimension;
+            }
+            if (!terminate && prim < 0) terminate = true; // escaped; no infinite lights on this path
+            if (!terminate) {
+                int mat;
+                if (prim >= (int)wf.bvh.n_tris) {
+                    mat = wf.spheres[prim - (int)wf.bvh.n_tris].material;
+                } else {
+                    const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
+                    const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                    const uint32_t mw = __float_as_uint(v1.w);
+                    mat = int(mw & 0x7fffffffu);
+                    const int light = __float_as_int(v2.w);
+                    if (light >= 0) {
+                        // SurfaceInteraction::le -> DiffuseAreaLight::l, then MIS against NEE (:155-171)
+                        const LightRec Lr = wf.lights[light];
+                        const V3 n = tri_normal(v3(v0), v3(v1), v3(v2), (mw >> 31) != 0u);
+                        const V3 rd = v3(wf.pool.ray_d[slot]);
+                        if (light_emits_towards(Lr, n, -rd)) {
+                            const S4 lambda = wf.pool.lambda[slot];
+                            const S4 Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * Lr.scale;
+                            if (is_positive(Le)) {
+                                if (depth == 0 || (ids.w & PF_SPECULAR)) {
+                                    L = L + beta * Le;
+                                } else {
+                                    const float4 c0 = wf.pool.ctx0[slot], c1 = wf.pool.ctx1[slot], c2 = wf.pool.ctx2[slot];
+                                    const LightCtx ctx{v3(c0), v3(c0.w, c1.w, c2.w), v3(c1), v3(c2)};
+                                    const float pdf_light = Lr.pmf * light_pdf(Lr, ctx, rd);
+                                    const float dir_pdf = wf.pool.misc[slot].y;
+                                    L = L + beta * Le * power_heuristic(dir_pdf, pdf_light);
+                                }
+                                dirty_L = true;
+                            }
+                        }
+                    }
+                }
+                depth += 1;
+                route = wf.materials[mat].type;
+            }
+            if (terminate) {
+                const float fw = wf.pool.misc[slot].x;
+                film_add(wf, ids.x, L, wf.pool.lambda[slot], wf.pool.lpdf[slot], fw);
+                n_finished++;
+            } else {
+                if (dirty_L) wf.pool.L[slot] = L;
+                ids.w = (ids.w & 0xff) | (depth << 8) | (next_rr << 16);
+                wf.pool.ids[slot] = ids;
+            }
+        }
+        queue_push(&wf.c->n_free, wf.q.free_slots, slot, act && terminate);
+        queue_push(&wf.c->n_mat[0], wf.q.mat[0], slot, route == B200PT_MAT_DIFFUSE);
+        queue_push(&wf.c->n_mat[1], wf.q.mat[1], slot, route == B200PT_MAT_CONDUCTOR);
+        queue_push(&wf.c->n_mat[2], wf.q.mat[2], slot, route == B200PT_MAT_DIELECTRIC);
+    }
+    // finished-path count: warp reduce, one atomic per warp
+    for (int o = 16; o > 0; o >>= 1) n_finished += __shfl_xor_sync(0xffffffffu, n_finished, o);
+    if ((threadIdx.x & 31) == 0 && n_finished) atomicAdd(&wf.c->finished, (unsigned long long)n_finished);
+}
+
+// what the shade stage needs of SurfaceInteraction (base/interaction.h:96-164)
+struct Isect {
+    V3 p, err;  // pi = p +- err
+    V3 n, ns;   // geometric / shading normal
+    V3 dpdu;    // shading.dpdu
+    V3 wo;
+};
+
+// Triangle::interaction_from_intersection (shapes/triangle.cu:325-465) for a mesh without per-vertex
+// normals / uvs (default uv (0,0),(1,0),(1,1)), from the 48-byte leaf record
+__device__ __forceinline__ void triangle_interaction(V3 p0, V3 p1, V3 p2, float b1, float b2, bool flip, V3 wo, Isect &si) {
+    const float b0 = 1.f - b1 - b2;
+    const V3 dp02 = p0 - p2, dp12 = p1 - p2;
+    // duv02 = (-1,-1), duv12 = (0,-1): determinant 1
+    V3 dpdu = v3(diff_of_products(-1.f, dp02.x, -1.f, dp12.x), diff_of_products(-1.f, dp02.y, -1.f, dp12.y),
+                 diff_of_products(-1.f, dp02.z, -1.f, dp12.z));
+    V3 dpdv = v3(diff_of_products(-1.f, dp12.x, 0.f, dp02.x), diff_of_products(-1.f, dp12.y, 0.f, dp02.y),
+                 diff_of_products(-1.f, dp12.z, 0.f, dp02.z));
+    if (len2(cross(dpdu, dpdv)) == 0.f) {
+        const V3 ng = cross(p2 - p0, p1 - p0);
+        coordinate_system(normalize(ng), &dpdu, &dpdv);
+    }
+    si.p = b0 * p0 + b1 * p1 + b2 * p2;
+    si.err = gamma_n(7) * (vabs(b0 * p0) + vabs(b1 * p1) + vabs(b2 * p2));
+    V3 n = normalize(cross(dp02, dp12));
+    if (flip) n = -n;
+    si.n = n;
+    si.ns = n;
+    si.dpdu = dpdu;
+    si.wo = normalize(wo);
+}
+
+// Sphere::interaction_from_intersection (shapes/sphere.h:71-125) + Transform::operator()(SurfaceInteraction)
+// (euclidean_space/transform.cu:57-97)
+__device__ __forceinline__ void sphere_interaction(const SphereRec &s, V3 ro, V3 rd, float t, V3 wo, Isect &si) {
+    // recompute the refined object-space hit point exactly as basic_intersect does
+    const V3 o = xf_point(s.ofr, ro), d = xf_vector(s.ofr, rd);
+    V3 pHit = o + t * d;
+    pHit = pHit * (s.radius / len(pHit));
+    if (pHit.x == 0.f && pHit.y == 0.f) pHit.x = 1e-5f * s.radius;
+    const float cosTheta = pHit.z / s.radius;
+    const float zRadius = sqrtf(sqr(pHit.x) + sqr(pHit.y));
+    const float cosPhi = pHit.x / zRadius, sinPhi = pHit.y / zRadius;
+    const V3 dpdu = v3(-s.phi_max * pHit.y, s.phi_max * pHit.x, 0.f);
+    const float sinTheta = safe_sqrt(1.f - sqr(cosTheta));
+    const V3 dpdv = (s.theta_z_max - s.theta_z_min) * v3(pHit.z * cosPhi, pHit.z * sinPhi, -s.radius * sinTheta);
+    const V3 perr = gamma_n(5) * vabs(pHit);
+    V3 n = normalize(cross(dpdu, dpdv));
+    if (s.flip) n = -n;
+    // to render space
+    si.p = xf_point(s.rfo, pHit);
+    si.err = xf_point_error(s.rfo, pHit, perr, false);
+    V3 nr = normalize(xf_normal(s.ofr, n));
+    V3 nsr = nr;
+    nr = face_forward(nr, nsr);
+    si.n = nr;
+    si.ns = nsr;
+    si.dpdu = xf_vector(s.rfo, dpdu);
+    si.wo = normalize(wo);
+}
+
+template <int MAT>
+__device__ __forceinline__ void make_bsdf(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf, bool &lpdf_dirty,
+                                          BSDF<MAT> &b);
+
+template <>
+__device__ __forceinline__ void make_bsdf<B200PT_MAT_DIFFUSE>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf,
+                                                              bool &lpdf_dirty, BSDF<B200PT_MAT_DIFFUSE> &b) {
+    // materials/diffuse_material.cu:17-22
+    b.r = clamp_s4(spectrum_sample(wf.spectra, m.reflectance, lambda), 0.f, 1.f);
+}
+template <>
+__device__ __forceinline__ void make_bsdf<B200PT_MAT_CONDUCTOR>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf,
+                                                                bool &lpdf_dirty, BSDF<B200PT_MAT_CONDUCTOR> &b) {
+    // materials/conductor_material.cu:52-75
+    float ur = m.u_rough, vr = m.v_rough;
+    if (m.remap) {
+        ur = sqrtf(ur);
+        vr = sqrtf(vr);
+    }
+    if (m.eta >= 0) {
+        b.eta = spectrum_sample(wf.spectra, m.eta, lambda);
+        b.k = spectrum_sample(wf.spectra, m.k, lambda);
+    } else {
+        const S4 r = clamp_s4(spectrum_sample(wf.spectra, m.reflectance, lambda), 0.f, 0.9999f);
+        b.eta = s4(1.f);
+        b.k = 2.f * sqrt_s4(r) / sqrt_s4(clamp_s4(s4(1.f) + r * -1.f, 0.f, kInf));
+    }
+    b.d = make_trdist(ur, vr);
+}
+template <>
+__device__ __forceinline__ void make_bsdf<B200PT_MAT_DIELECTRIC>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf,
+                                                                 bool &lpdf_dirty, BSDF<B200PT_MAT_DIELECTRIC> &b) {
+    // materials/dielectric_material.cu:39-66
+    float eta = spectrum_at(wf.spectra, m.eta, lambda.x);
+    if (!spectrum_is_constant(wf.spectra, m.eta)) {
+        // SampledWavelengths::terminate_secondary (spectrum_util/sampled_wavelengths.h:120-131)
+        if (!(lpdf.y == 0.f && lpdf.z == 0.f && lpdf.w == 0.f)) {
+            lpdf = make_float4(lpdf.x / 4.f, 0.f, 0.f, 0.f);
+            lpdf_dirty = true;
+        }
+    }
+    if (eta == 0.f) eta = 1.f;
+    float ur = m.u_rough, vr = m.v_rough;
+    if (m.remap) {
+        ur = sqrtf(ur);
+        vr = sqrtf(vr);
+    }
+    b.eta = eta;
+    b.d = make_trdist(ur, vr);
+}
+
+// ---- gpu_evaluate_material + sample_bsdf + sample_Ld_volume, specialised per material
+template <int MAT>
+__global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf, int cur) {
+    const unsigned n = wf.c->n_mat[MAT];
+    const unsigned stride = gridDim.x * blockDim.x;
+    const unsigned n_round = (n + 31u) & ~31u;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        const bool act = i < n;
+        int slot = -1;
+        bool shadow = false;
+        float4 sh_o = make_float4(0, 0, 0, 0), sh_d = sh_o, sh_c = sh_o;
+        if (act) {
+            slot = wf.q.mat[MAT][i];
+            const float4 ro4 = wf.pool.ray_o[slot], rd4 = wf.pool.ray_d[slot];
+            const V3 ro = v3(ro4), rd = v3(rd4);
+            const float4 hit = wf.pool.hit[slot];
+            const int prim = __float_as_int(hit.x);
+            Isect si;
+            int mat;
+            if (prim >= (int)wf.bvh.n_tris) {
+                const SphereRec &sp = wf.spheres[prim - (int)wf.bvh.n_tris];
+                sphere_interaction(sp, ro, rd, hit.y, -rd, si);
+                mat = sp.material;
+            } else {
+                const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
+                const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                const uint32_t mw = __float_as_uint(v1.w);
+                mat = int(mw & 0x7fffffffu);
+                triangle_interaction(v3(v0), v3(v1), v3(v2), hit.z, hit.w, (mw >> 31) != 0u, -rd, si);
+            }
+            const MatRec m = wf.materials[mat];
+            const S4 lambda = wf.pool.lambda[slot];
+            S4 lpdf = wf.pool.lpdf[slot];
+            bool lpdf_dirty = false;
+            int4 ids = wf.pool.ids[slot];
+            BSDF<MAT> bsdf;
+            // BSDF(ns, dpdus) (base/bsdf.h:16-17): Frame::from_xz(normalize(dpdus), ns)
+            bsdf.frame = frame_from_xz(normalize(si.dpdu), si.ns);
+            make_bsdf<MAT>(wf, m, si, lambda, lpdf, lpdf_dirty, bsdf);
+            if (lpdf_dirty) wf.pool.lpdf[slot] = lpdf;
+            if (wf.regularize && (ids.w & PF_ANY_NON_SPECULAR)) bsdf.regularize();
+            const uint32_t flags = bsdf.flags();
+            S4 beta = wf.pool.beta[slot];
+            Sampler s = load_sampler(wf, slot, ids);
+            const V3 wo = si.wo;
+            const V3 wo_l = bsdf.frame.to_local(wo);
+
+            // ---- next-event estimation (MegakernelPathIntegrator::sample_Ld_volume, megakernel_path.cu:185-264)
+            if (flags_non_specular(flags)) {
+                LightCtx ctx{si.p, si.err, si.n, si.ns};
+                if ((flags & BXDF_REFLECTION) && !(flags & BXDF_TRANSMISSION)) {
+                    ctx.p = offset_ray_origin(si.p, si.err, si.n, wo);
+                    ctx.err = v3(0.f, 0.f, 0.f);
+                } else if ((flags & BXDF_TRANSMISSION) && !(flags & BXDF_REFLECTION)) {
+                    ctx.p = offset_ray_origin(si.p, si.err, si.n, -wo);
+                    ctx.err = v3(0.f, 0.f, 0.f);
+                }
+                const float ul = s.get_1d();
+                const float2 up = s.get_2d(); // both drawn before any early-out, as the reference does
+                if (wf.n_lights > 0) {
+                    const int li = alias_sample(wf.alias, wf.n_lights, ul);
+                    const LightRec Lr = wf.lights[li];
+                    LightSample ls;
+                    if (light_sample(Lr, ctx, up, ls) && light_emits_towards(Lr, ls.n, -ls.wi)) {
+                        const S4 Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * Lr.scale;
+                        if (is_positive(Le) && wo_l.z != 0.f) {
+                            const V3 wi_l = bsdf.frame.to_local(ls.wi);
+                            const S4 f = bsdf.f(wo_l, wi_l) * absdot(ls.wi, si.ns);
+                            if (is_positive(f)) {
+                                const float pdf_light = Lr.pmf * ls.pdf;
+                                const float pdf_bsdf = bsdf.pdf(wo_l, wi_l);
+                                const float w = power_heuristic(pdf_light, pdf_bsdf);
+                                const S4 Ld = f * (Le / pdf_light) * w;
+                                // visibility: Ray::spawn_ray_to (base/ray.h:51-58) from the surface point to the
+                                // light point, both ends offset; the segment (0, 1] of the un-normalised ray covers
+                                // the union of the reference's three visibility rays (integrator_base.cu:12-14,24-33)
+                                const V3 pf = offset_ray_origin(si.p, si.err, si.n, ls.p - si.p);
+                                const V3 pt = offset_ray_origin(ls.p, ls.err, ls.n, pf - ls.p);
+                                const V3 sd = pt - pf;
+                                shadow = true;
+                                sh_o = make_float4(pf.x, pf.y, pf.z, 1.f);
+                                sh_d = make_float4(sd.x, sd.y, sd.z, 0.f);
+                                sh_c = beta * Ld;
+                            }
+                        }
+                    }
+                }
+            }
+
+            // ---- BSDF sampling (WavefrontPathIntegrator::sample_bsdf, wavefront_path.cu:456-474)
+            const float uc = s.get_1d();
+            const float2 u2 = s.get_2d();
+            BSDFSample bs;
+            bool ok = wo_l.z != 0.f && flags != 0u && bsdf.sample(wo_l, uc, u2, bs);
+            if (ok) ok = is_positive(bs.f) && bs.pdf != 0.f && bs.wi.z != 0.f;
+            if (!ok) {
+                wf.pool.beta[slot] = s4(0.f);
+                wf.pool.ray_o[slot] = make_float4(ro.x, ro.y, ro.z, -1.f); // dead: the next logic stage retires it
+            } else {
+                const V3 wi = bsdf.frame.from_local(bs.wi);
+                beta = beta * bs.f * (absdot(wi, si.ns) / bs.pdf);
+                wf.pool.beta[slot] = beta;
+                const bool spec = (bs.flags & BXDF_SPECULAR) != 0u;
+                ids.w = (ids.w & ~PF_SPECULAR) | (spec ? PF_SPECULAR : PF_ANY_NON_SPECULAR);
+                float4 misc = wf.pool.misc[slot];
+                misc.y = bs.pdf;
+                wf.pool.misc[slot] = misc;
+                wf.pool.ctx0[slot] = make_float4(si.p.x, si.p.y, si.p.z, si.err.x);
+                wf.pool.ctx1[slot] = make_float4(si.n.x, si.n.y, si.n.z, si.err.y);
+                wf.pool.ctx2[slot] = make_float4(si.ns.x, si.ns.y, si.ns.z, si.err.z);
+                // Interaction::spawn_ray (base/interaction.h:73-76)
+                const V3 o = offset_ray_origin(si.p, si.err, si.n, wi);
+                wf.pool.ray_o[slot] = make_float4(o.x, o.y, o.z, kInf);
+                wf.pool.ray_d[slot] = make_float4(wi.x, wi.y, wi.z, 0.f);
+            }
+            ids.z = s.dimension;
+            wf.pool.ids[slot] = ids;
+            wf.pool.rng[slot] = s.state;
+        }
+        const int spos = queue_claim(&wf.c->n_shadow, shadow);
+        if (spos >= 0) {
+            wf.q.sh_o[spos] = sh_o;
+            wf.q.sh_d[spos] = sh_d;
+            wf.q.sh_contrib[spos] = sh_c;
+            wf.q.sh_slot[spos] = slot;
+        }
+        queue_push(&wf.c->n_rays[cur ^ 1], wf.q.rays[cur ^ 1], slot, act);
+    }
+}
+
+} // namespace b200pt
+
+namespace b200pt {
+
+template <typename T>
+static int pool_alloc(RenderData *r, T **out, size_t count) {
+    void *p = nullptr;
+    CU_TRY(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+    r->pool_allocs.push_back(p);
+    *out = (T *)p;
+    return B200PT_OK;
+}
+
+static int ensure_pool(b200pt_scene *s, int pool_size) {
+    RenderData *r = s->render;
+    if (r->pool_size == pool_size) return B200PT_OK;
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    for (void *p : r->pool_allocs) cudaFree(p);
+    r->pool_allocs.clear();
+    r->pool_size = 0;
+    const size_t n = (size_t)pool_size;
+    int rc = 0;
+    PathPool &P = r->pool;
+    float4 **lanes[] = {&P.ray_o, &P.ray_d, &P.hit, &P.beta, &P.L, &P.lambda, &P.lpdf, &P.ctx0, &P.ctx1, &P.ctx2, &P.misc};
+    for (float4 **l : lanes)
+        if ((rc = pool_alloc(r, l, n))) return rc;
+    if ((rc = pool_alloc(r, &P.rng, n))) return rc;
+    if ((rc = pool_alloc(r, &P.ids, n))) return rc;
+    WFQueues &Q = r->q;
+    int32_t **qs[] = {&Q.rays[0], &Q.rays[1], &Q.mat[0], &Q.mat[1], &Q.mat[2], &Q.free_slots, &Q.sh_slot};
+    for (int32_t **q : qs)
+        if ((rc = pool_alloc(r, q, n))) return rc;
+    if ((rc = pool_alloc(r, &Q.sh_o, n))) return rc;
+    if ((rc = pool_alloc(r, &Q.sh_d, n))) return rc;
+    if ((rc = pool_alloc(r, &Q.sh_contrib, n))) return rc;
+    if (!r->d_counters) CU_TRY(cudaMalloc((void **)&r->d_counters, sizeof(WFCounters)));
+    if (!r->h_counters) CU_TRY(cudaMallocHost((void **)&r->h_counters, sizeof(WFCounters)));
+    r->pool_size = pool_size;
+    return B200PT_OK;
+}
+
+} // namespace b200pt
+
+B200PT_API int b200pt_probe_sampler(b200pt_scene *s, int kind, int spp, const int32_t *pixel, const int32_t *sample,
+                                    int npairs, const int32_t *pattern, int ndraw, float *out);
+
+B200PT_API int b200pt_film_create(b200pt_scene *s, b200pt_film **out) {
+    if (!s || !out) {
+        set_error("b200pt_film_create: null argument");
+        return B200PT_ERR_INVALID;
+    }
+    *out = nullptr;
+    if (!s->render || !s->render->have_render) {
+        set_error("b200pt_film_create: scene has no film / camera / filter description");
+        return B200PT_ERR_STATE;
+    }
+    CU_TRY(cudaSetDevice(s->device));
+    b200pt_film *f = new b200pt_film();
+    f->scene = s;
+    f->width = s->render->width;
+    f->height = s->render->height;
+    const size_t bytes = (size_t)f->width * f->height * sizeof(float4);
+    if (cudaMalloc((void **)&f->d_accum, bytes) != cudaSuccess) {
+        delete f;
+        set_error("b200pt_film_create: out of device memory");
+        return B200PT_ERR_CUDA;
+    }
+    cudaMemsetAsync(f->d_accum, 0, bytes, s->stream);
+    cudaStreamSynchronize(s->stream);
+    *out = f;
+    return B200PT_OK;
+}
+
+B200PT_API void b200pt_film_destroy(b200pt_film *film) {
+    if (!film) return;
+    if (film->scene) cudaSetDevice(film->scene->device);
+    if (film->d_accum) cudaFree(film->d_accum);
+    delete film;
+}
+
+B200PT_API int b200pt_film_clear(b200pt_film *film) {
+    if (!film) return B200PT_ERR_INVALID;
+    CU_TRY(cudaSetDevice(film->scene->device));
+    CU_TRY(cudaMemsetAsync(film->d_accum, 0, (size_t)film->width * film->height * sizeof(float4), film->scene->stream));
+    CU_TRY(cudaStreamSynchronize(film->scene->stream));
+    return B200PT_OK;
+}
+
+B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_render_opts *opts, b200pt_render_stats *st_out) {
+    if (!s || !film || !opts) {
+        set_error("b200pt_render: null argument");
+        return B200PT_ERR_INVALID;
+    }
+    if (!s->render || !s->render->have_render || film->scene != s) {
+        set_error("b200pt_render: scene has no render description, or the film belongs to another scene");
+        return B200PT_ERR_STATE;
+    }
+    if (!s->built) {
+        set_error("b200pt_render: call b200pt_bvh_build first");
+        return B200PT_ERR_STATE;
+    }
+    RenderData *r = s->render;
+    const int spp = opts->spp_total;
+    const int sqrt_spp = (int)std::lround(std::sqrt((double)spp));
+    if (spp <= 0 || opts->sample_begin < 0 || opts->sample_end > spp || opts->sample_begin > opts->sample_end) {
+        set_error("b200pt_render: bad sample range [%d, %d) of %d", opts->sample_begin, opts->sample_end, spp);
+        return B200PT_ERR_INVALID;
+    }
+    if (opts->sampler == 0 && sqrt_spp * sqrt_spp != spp) {
+        // samplers/stratified.h:11-16: fatal in the reference
+        set_error("b200pt_render: the stratified sampler needs a perfect-square spp (got %d)", spp);
+        return B200PT_ERR_INVALID;
+    }
+    if (opts->max_depth < 0 || opts->max_depth > 255) {
+        set_error("b200pt_render: max_depth must be in [0, 255]");
+        return B200PT_ERR_INVALID;
+    }
+    CU_TRY(cudaSetDevice(s->device));
+    const long long n_pixels = (long long)r->width * r->height;
+    const long long total = n_pixels * (opts->sample_end - opts->sample_begin);
+    int pool_size = opts->pool_size > 0 ? opts->pool_size : (1 << 21);
+    pool_size = (int)std::min<long long>(pool_size, std::max<long long>(total, 1024));
+    pool_size = (pool_size + 31) & ~31;
+    int rc = ensure_pool(s, pool_size);
+    if (rc) return rc;
+
+    WF wf = {};
+    wf.pool = r->pool;
+    wf.q = r->q;
+    wf.c = r->d_counters;
+    wf.pool_size = pool_size;
+    wf.bvh = s->bvh;
+    wf.spheres = s->d_spheres;
+    wf.n_spheres = s->n_spheres;
+    wf.spectra = SpectrumTable{r->d_spec, r->d_spec_pool, r->d_illuminant};
+    wf.materials = r->d_materials;
+    wf.lights = r->d_lights;
+    wf.alias = r->d_alias;
+    wf.n_lights = r->n_lights;
+    wf.filter = r->filter;
+    wf.camera = r->camera;
+    wf.film = FilmRec{r->width, r->height, r->d_cie[0], r->d_cie[1], r->d_cie[2], r->imaging_ratio, film->d_accum};
+    wf.sampler_kind = opts->sampler;
+    wf.spp = spp;
+    wf.sqrt_spp = sqrt_spp;
+    wf.max_depth = opts->max_depth;
+    wf.regularize = opts->regularize;
+    wf.sample_begin = opts->sample_begin;
+    wf.total_paths = total;
+    wf.n_pixels = n_pixels;
+
+    cudaStream_t st = s->stream;
+    cudaEvent_t ev0, ev1, ev_poll;
+    CU_TRY(cudaEventCreate(&ev0));
+    CU_TRY(cudaEventCreate(&ev1));
+    CU_TRY(cudaEventCreateWithFlags(&ev_poll, cudaEventDisableTiming));
+    struct EvGuard {
+        cudaEvent_t a, b, c;
+        ~EvGuard() {
+            cudaEventDestroy(a);
+            cudaEventDestroy(b);
+            cudaEventDestroy(c);
+        }
+    } guard{ev0, ev1, ev_poll};
+
+    const int grid = s->sm_count * 8; // stage kernels: grid-stride over device-side queue counts
+    CU_TRY(cudaEventRecord(ev0, st));
+    k_init_pool<<<(pool_size + 255) / 256, 256, 0, st>>>(wf);
+    long long passes = 0, launches = 1;
+    int cur = 0;
+    bool done = total == 0;
+    const int batch = 8; // passes enqueued between two looks at the finished-path counter
+    while (!done) {
+        for (int b = 0; b < batch; b++) {
+            k_pass_begin<<<1, 1, 0, st>>>(wf, cur);
+            if ((rc = launch_trace_wf(s, wf, cur, false))) return rc;
+            k_logic<<<grid, WF_BLOCK, 0, st>>>(wf, cur);
+            k_generate<<<grid, WF_BLOCK, 0, st>>>(wf, cur);
+            k_after_generate<<<1, 1, 0, st>>>(wf);
+            k_shade<B200PT_MAT_DIFFUSE><<<grid, WF_BLOCK, 0, st>>>(wf, cur);
+            k_shade<B200PT_MAT_CONDUCTOR><<<grid, WF_BLOCK, 0, st>>>(wf, cur);
+            k_shade<B200PT_MAT_DIELECTRIC><<<grid, WF_BLOCK, 0, st>>>(wf, cur);
+            if ((rc = launch_trace_wf(s, wf, cur, true))) return rc;
+            k_pass_end<<<1, 1, 0, st>>>(wf);
+            cur ^= 1;
+            passes++;
+            launches += 10;
+        }
+        CU_TRY(cudaGetLastError());
+        // the only host<->device traffic of the render loop: one 64-byte counter block per batch
+        CU_TRY(cudaMemcpyAsync(r->h_counters, r->d_counters, sizeof(WFCounters), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaEventRecord(ev_poll, st));
+        CU_TRY(cudaEventSynchronize(ev_poll));
+        if (r->h_counters->stack_overflow) {
+            set_error("b200pt_render: traversal stack overflow");
+            return B200PT_ERR_STATE;
+        }
+        done = (long long)r->h_counters->finished >= total;
+        if (passes > 100000000ll) {
+            set_error("b200pt_render: did not terminate");
+            return B200PT_ERR_STATE;
+        }
+    }
+    CU_TRY(cudaEventRecord(ev1, st));
+    CU_TRY(cudaEventSynchronize(ev1));
+    if (st_out) {
+        b200pt_render_stats o = {};
+        o.paths = total;
+        if (total > 0) {
+            o.rays_closest = (int64_t)r->h_counters->rays_closest;
+            o.rays_shadow = (int64_t)r->h_counters->rays_shadow;
+        }
+        o.passes = passes;
+        o.kernel_launches = launches;
+        CU_TRY(cudaEventElapsedTime(&o.ms_total, ev0, ev1));
+        *st_out = o;
+    }
+    return B200PT_OK;
+}
+
+// ---- film read-out and reduce -------------------------------------------------------------------
+namespace b200pt {
+// RGBFilm::get_pixel_rgb (film/rgb_film.cu:107-122): rgb_sum / weight_sum, then output_rgb_from_sensor_rgb
+__global__ void k_film_resolve(const float4 *accum, long long n, const float *M, float *rgb) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = accum[i];
+    float x = a.x, y = a.y, z = a.z;
+    if (a.w != 0.f) {
+        x /= a.w;
+        y /= a.w;
+        z /= a.w;
+    }
+    rgb[3 * i + 0] = M[0] * x + M[1] * y + M[2] * z;
+    rgb[3 * i + 1] = M[3] * x + M[4] * y + M[5] * z;
+    rgb[3 * i + 2] = M[6] * x + M[7] * y + M[8] * z;
 }
 
 __global__ void k_probe_sampler(int kind, int spp, int sqrt_spp, const int32_t *__restrict__ pixel,
@@ -37,14 +1122,73 @@ __global__ void k_probe_sampler(int kind, int spp, int sqrt_spp, const int32_t *
         }
     }
 }
-
 } // namespace b200pt
 
-using namespace b200pt;
+B200PT_API int b200pt_film_read_raw(b200pt_film *film, float *xyzw_out) {
+    if (!film || !xyzw_out) return B200PT_ERR_INVALID;
+    b200pt_scene *s = film->scene;
+    CU_TRY(cudaSetDevice(s->device));
+    CU_TRY(cudaMemcpyAsync(xyzw_out, film->d_accum, (size_t)film->width * film->height * sizeof(float4), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    return B200PT_OK;
+}
 
-int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
-    (void)s;
-    (void)desc;
+B200PT_API int b200pt_film_read(b200pt_film *film, float *rgb_out) {
+    if (!film || !rgb_out) return B200PT_ERR_INVALID;
+    b200pt_scene *s = film->scene;
+    CU_TRY(cudaSetDevice(s->device));
+    const long long n = (long long)film->width * film->height;
+    int rc = ensure_scratch(s, (size_t)n * 12 + 64);
+    if (rc) return rc;
+    float *d_M = (float *)s->d_scratch;
+    float *d_rgb = d_M + 16;
+    CU_TRY(cudaMemcpyAsync(d_M, s->render->out_rgb, 9 * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    k_film_resolve<<<unsigned((n + 255) / 256), 256, 0, s->stream>>>(film->d_accum, n, d_M, d_rgb);
+    CU_TRY(cudaMemcpyAsync(rgb_out, d_rgb, (size_t)n * 12, cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    return B200PT_OK;
+}
+
+// ncclReduce(sum, fp32, root) of the 4*W*H accumulators.  NCCL is resolved at run
+// time from the hosting process (torch.distributed has it loaded) or libnccl.so.2: libb200pt.so
+// itself has no link-time dependency on it.
+B200PT_API int b200pt_film_reduce(b200pt_film *film, void *comm, int root, void *stream) {
+    if (!film || !comm) {
+        set_error("b200pt_film_reduce: null argument");
+        return B200PT_ERR_INVALID;
+    }
+    typedef int (*nccl_reduce_t)(const void *, void *, size_t, int, int, int, void *, cudaStream_t);
+    static nccl_reduce_t fn = nullptr;
+    if (!fn) {
+        fn = (nccl_reduce_t)dlsym(RTLD_DEFAULT, "ncclReduce");
+        if (!fn) {
+            void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+            if (h) fn = (nccl_reduce_t)dlsym(h, "ncclReduce");
+        }
+        if (!fn) {
+            set_error("b200pt_film_reduce: ncclReduce not found (load NCCL in the hosting process)");
+            return B200PT_ERR_NCCL;
+        }
+    }
+    b200pt_scene *s = film->scene;
+    CU_TRY(cudaSetDevice(s->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+    const size_t count = (size_t)film->width * film->height * 4;
+    // ncclFloat32 = 7, ncclSum = 0
+    const int rc = fn(film->d_accum, film->d_accum, count, 7, 0, root, comm, st);
+    if (rc != 0) {
+        set_error("b200pt_film_reduce: ncclReduce failed with %d", rc);
+        return B200PT_ERR_NCCL;
+    }
+    CU_TRY(cudaStreamSynchronize(st));
+    return B200PT_OK;
+}
+
+B200PT_API void *b200pt_film_device_ptr(b200pt_film *film) { return film ? (void *)film->d_accum : nullptr; }
+B200PT_API int b200pt_film_dims(b200pt_film *film, int32_t *w, int32_t *h) {
+    if (!film) return B200PT_ERR_INVALID;
+    if (w) *w = film->width;
+    if (h) *h = film->height;
     return B200PT_OK;
 }
 
@@ -74,7 +1218,7 @@ B200PT_API int b200pt_probe_sampler(b200pt_scene *s, int kind, int spp, const in
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_sample, sample, npairs * 4, cudaMemcpyHostToDevice, s->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_pattern, pattern, ndraw * 4, cudaMemcpyHostToDevice, s->stream);
     if (e == cudaSuccess) {
-        const int sqrt_spp = (int)sqrt((double)spp);
+        const int sqrt_spp = (int)std::lround(std::sqrt((double)spp));
         k_probe_sampler<<<(npairs + 127) / 128, 128, 0, s->stream>>>(kind, spp, sqrt_spp, d_pixel, d_sample, npairs, d_pattern,
                                                                     ndraw, per, d_out);
         e = cudaMemcpyAsync(out, d_out, (size_t)npairs * per * 4, cudaMemcpyDeviceToHost, s->stream);
@@ -84,34 +1228,3 @@ B200PT_API int b200pt_probe_sampler(b200pt_scene *s, int kind, int spp, const in
     if (e != cudaSuccess) return cuda_fail(e, "b200pt_probe_sampler", __FILE__, __LINE__);
     return B200PT_OK;
 }
-
-B200PT_API int b200pt_film_create(b200pt_scene *s, b200pt_film **out) {
-    (void)s;
-    (void)out;
-    set_error("b200pt_film_create: scene has no film description");
-    return B200PT_ERR_UNSUPPORTED;
-}
-B200PT_API void b200pt_film_destroy(b200pt_film *film) {
-    if (!film) return;
-    if (film->d_accum) cudaFree(film->d_accum);
-    delete film;
-}
-B200PT_API int b200pt_film_clear(b200pt_film *film) { (void)film; return B200PT_ERR_UNSUPPORTED; }
-B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_render_opts *opts, b200pt_render_stats *st) {
-    (void)s; (void)film; (void)opts; (void)st;
-    set_error("b200pt_render: not built in this revision");
-    return B200PT_ERR_UNSUPPORTED;
-}
-B200PT_API int b200pt_film_reduce(b200pt_film *film, void *comm, int root, void *stream) {
-    (void)film; (void)comm; (void)root; (void)stream;
-    return B200PT_ERR_UNSUPPORTED;
-}
-B200PT_API void *b200pt_film_device_ptr(b200pt_film *film) { return film ? (void *)film->d_accum : nullptr; }
-B200PT_API int b200pt_film_dims(b200pt_film *film, int32_t *w, int32_t *h) {
-    if (!film) return B200PT_ERR_INVALID;
-    if (w) *w = film->width;
-    if (h) *h = film->height;
-    return B200PT_OK;
-}
-B200PT_API int b200pt_film_read(b200pt_film *film, float *rgb_out) { (void)film; (void)rgb_out; return B200PT_ERR_UNSUPPORTED; }
-B200PT_API int b200pt_film_read_raw(b200pt_film *film, float *xyzw_out) { (void)film; (void)xyzw_out; return B200PT_ERR_UNSUPPORTED; }

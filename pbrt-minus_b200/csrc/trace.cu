@@ -18,7 +18,9 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "sphere.cuh"
 #include "traverse.cuh"
+#include "wavefront.cuh"
 
 namespace b200pt {
 
@@ -146,6 +148,173 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
         atomicAdd(p.counters + 2, (unsigned long long)n_tris);
     }
     if (overflow) p.counters[3] = 1ull;
+}
+
+// ---- queue-driven form used by the wavefront integrator (render.cu) ---------------------------
+// Same traversal loop; what differs from k_trace: the ray count and the ray list come from DEVICE
+// memory (queue + counter written by the previous stage, no host round trip), rays are gathered from
+// the SoA path pool by slot, spheres are tested beside the BVH, and
+//   SHADOW = false: closest hit, writes {leaf-order triangle slot | n_tris + sphere, t, b1, b2} to
+//                   pool.hit[slot] (the shade stage reads vertices / material / light ids from the
+//                   48-byte leaf record directly: no prim -> index -> vertex pointer chase);
+//   SHADOW = true:  any hit on the compact shadow queue; an UNOCCLUDED ray adds its pre-weighted
+//                   NEE contribution to pool.L[slot] on retirement (one shadow ray per slot per pass,
+//                   so the add needs no atomic) -- the reference runs these traversals inline in the
+//                   shading threads (integrators/megakernel_path.cu:217-233, base/integrator_base.cu:12-71).
+template <bool SHADOW>
+__global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf, int cur) {
+    __shared__ uint2 sm_stack_all[SM_STACK * TRACE_BLOCK];
+    uint2 *const sm_stack = sm_stack_all + threadIdx.x;
+    uint2 lstack[LOCAL_STACK];
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const bool have_tree = wf.bvh.n_nodes > 0;
+    const long long n = SHADOW ? wf.c->n_shadow : wf.c->n_rays[cur];
+    unsigned *const ticket = SHADOW ? &wf.c->ticket_shadow : &wf.c->ticket_closest;
+    const int32_t *const queue = wf.q.rays[cur];
+    constexpr int REFILL = 4;
+    const uint32_t prmt_bias = 0x47000000u;
+
+    long long ray = -1;
+    int slot = -1;
+    bool exhausted = false;
+    float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 0, idx = 0, idy = 0, idz = 0;
+    uint32_t octinv4 = 0;
+    uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
+    int sp = 0;
+    float ht = 0, hb1 = 0, hb2 = 0;
+    int hprim = -1;
+    unsigned overflow = 0;
+
+    while (true) {
+        const unsigned idle = __ballot_sync(0xffffffffu, ray < 0);
+        if (!exhausted && (__popc(idle) >= REFILL || idle == 0xffffffffu)) {
+            const int n_idle = __popc(idle);
+            const int leader = __ffs(idle) - 1;
+            unsigned base = 0;
+            if (lane == leader) base = atomicAdd(ticket, (unsigned)n_idle);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if ((long long)base + n_idle >= n) exhausted = true;
+            if (ray < 0) {
+                const long long r = (long long)base + __popc(idle & lt_mask);
+                if (r < n) {
+                    ray = r;
+                    float4 ro, rd;
+                    if (SHADOW) {
+                        ro = __ldg(wf.q.sh_o + r);
+                        rd = __ldg(wf.q.sh_d + r);
+                    } else {
+                        slot = __ldg(queue + r);
+                        ro = wf.pool.ray_o[slot];
+                        rd = wf.pool.ray_d[slot];
+                    }
+                    ox = ro.x; oy = ro.y; oz = ro.z;
+                    dx = rd.x; dy = rd.y; dz = rd.z;
+                    idx = safe_rcp_dir(dx); idy = safe_rcp_dir(dy); idz = safe_rcp_dir(dz);
+                    octinv4 = ((idx < 0.f ? 0u : 4u) | (idy < 0.f ? 0u : 2u) | (idz < 0.f ? 0u : 1u)) * 0x01010101u;
+                    const bool live = ro.w >= 0.f; // tmax < 0 marks a dead path: report a miss
+                    ng = make_uint2(0u, (have_tree && live) ? 0x80000000u : 0u);
+                    tg = make_uint2(0u, 0u);
+                    sp = 0;
+                    ht = ro.w;
+                    hb1 = 0.f; hb2 = 0.f;
+                    hprim = -1;
+                    if (live) {
+                        for (int k = 0; k < wf.n_spheres; k++) {
+                            SphereHit sh;
+                            if (sphere_intersect(wf.spheres[k], v3(ox, oy, oz), v3(dx, dy, dz), ht, sh)) {
+                                ht = sh.t;
+                                hprim = int(wf.bvh.n_tris) + k;
+                                if (SHADOW) ng.y = 0u;
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        if (__ballot_sync(0xffffffffu, ray >= 0) == 0u) break;
+
+        const bool act = ray >= 0;
+        const bool want_tri = act && tg.y != 0u;
+        const unsigned m_tri = __ballot_sync(0xffffffffu, want_tri);
+        const unsigned m_node = __ballot_sync(0xffffffffu, act && !want_tri);
+        if (__popc(m_tri) >= __popc(m_node)) {
+            if (want_tri) {
+                const int ti = __ffs(tg.y) - 1;
+                tg.y &= tg.y - 1u;
+                const float4 *tp = wf.bvh.tris + 3 * size_t(tg.x + ti);
+                const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                TriHit th;
+                if (intersect_triangle(ox, oy, oz, dx, dy, dz, ht, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, th)) {
+                    ht = th.t;
+                    hb1 = th.b1;
+                    hb2 = th.b2;
+                    hprim = int(tg.x + ti);
+                    if (SHADOW) {
+                        tg.y = 0u;
+                        ng.y = 0u;
+                        sp = 0;
+                    }
+                }
+            }
+        } else if (act && !want_tri) {
+            if (ng.y <= 0x00ffffffu && sp > 0) {
+                sp--;
+                if (sp < SM_STACK) ng = sm_stack[sp * TRACE_BLOCK];
+                else if (sp < SM_STACK + LOCAL_STACK) ng = lstack[sp - SM_STACK];
+                else ng = make_uint2(0u, 0u);
+            }
+            if (ng.y > 0x00ffffffu) {
+                const uint32_t hits = ng.y;
+                const int child_bit = 31 - __clz(hits);
+                ng.y &= ~(1u << child_bit);
+                if (ng.y > 0x00ffffffu) {
+                    if (sp < SM_STACK) sm_stack[sp * TRACE_BLOCK] = ng;
+                    else if (sp < SM_STACK + LOCAL_STACK) lstack[sp - SM_STACK] = ng;
+                    else overflow = 1u;
+                    sp++;
+                }
+                const uint32_t cslot = (uint32_t(child_bit) - 24u) ^ (octinv4 & 0xffu);
+                const uint32_t rel = __popc(hits & 0xffu & ((1u << cslot) - 1u));
+                const float4 *np = wf.bvh.nodes + 5 * size_t(ng.x + rel);
+                const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+                const uint32_t hitmask = intersect_node8(n0, n1, n2, n3, n4, ox, oy, oz, idx, idy, idz, octinv4, ht, prmt_bias);
+                ng.x = __float_as_uint(n1.x);
+                tg.x = __float_as_uint(n1.y);
+                ng.y = (hitmask & 0xff000000u) | (__float_as_uint(n0.w) >> 24);
+                tg.y = hitmask & 0x00ffffffu;
+            } else {
+                if (SHADOW) {
+                    if (hprim < 0) {
+                        const int s2 = __ldg(wf.q.sh_slot + ray);
+                        const float4 c = __ldg(wf.q.sh_contrib + ray);
+                        float4 L = wf.pool.L[s2];
+                        L.x += c.x; L.y += c.y; L.z += c.z; L.w += c.w;
+                        wf.pool.L[s2] = L;
+                    }
+                } else {
+                    wf.pool.hit[slot] = make_float4(__int_as_float(hprim), hprim >= 0 ? ht : kInf, hb1, hb2);
+                }
+                ray = -1;
+            }
+        }
+    }
+    if (overflow) wf.c->stack_overflow = 1u;
+}
+
+int launch_trace_wf(b200pt_scene *s, const WF &wf, int cur, bool shadow) {
+    static int per_sm[2] = {0, 0};
+    if (per_sm[shadow] == 0) {
+        int v = 0;
+        if (shadow) CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k_trace_wf<true>, TRACE_BLOCK, 0));
+        else CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k_trace_wf<false>, TRACE_BLOCK, 0));
+        per_sm[shadow] = v < 1 ? 1 : v;
+    }
+    const unsigned blocks = unsigned(s->sm_count * per_sm[shadow]);
+    if (shadow) k_trace_wf<true><<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf, cur);
+    else k_trace_wf<false><<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf, cur);
+    CU_TRY(cudaGetLastError());
+    return B200PT_OK;
 }
 
 typedef void (*TraceKernel)(TraceParams);

@@ -1,0 +1,135 @@
+// wavefront.cuh -- device-resident state of the wavefront path integrator (shared by render.cu and
+// the queue-driven trace kernels in trace.cu).
+//
+// Replaces WavefrontPathIntegrator::PathState / Queues (integrators/wavefront_path.h:28-134): the
+// reference keeps 15 AoS arrays (~858 B/slot, a 256-B optional<ShapeIntersection>, a 124-B BSDF and
+// a 264-B MISParameter per slot) in managed memory, pushes with one atomicAdd per thread and lets
+// the HOST zero and read the queue counters between kernels.  Here the pool is SoA float4 lanes
+// (208 B/slot), every queue push is warp-aggregated, and all counters live on the device: a pass
+// is a fixed kernel sequence with no host synchronisation.
+#pragma once
+
+#include "common.cuh"
+#include "light.cuh"
+#include "spectrum.cuh"
+
+namespace b200pt {
+
+struct MatRec {
+    int32_t type, reflectance, eta, k;
+    float u_rough, v_rough;
+    int32_t remap, pad;
+};
+
+struct FilterTab {
+    int32_t nx, ny;
+    float min_x, max_x, min_y, max_y;
+    const float *f;         // [ny*nx] signed filter values
+    const float *cond_func; // [ny*nx] |f|
+    const float *cond_cdf;  // [ny*(nx+1)]
+    const float *cond_int;  // [ny]
+    const float *marg_func; // [ny]
+    const float *marg_cdf;  // [ny+1]
+    float marg_int;
+};
+
+struct CameraRec {
+    float cfr[16]; // camera_from_raster (projective)
+    float rfc[16]; // render_from_camera
+    float lens_radius, focal_distance;
+};
+
+struct FilmRec {
+    int32_t width, height;
+    const float *cie_x, *cie_y, *cie_z; // dense 471
+    float imaging_ratio;
+    float4 *accum;
+};
+
+// flags word of a path (ids.w): bit 0 specular_bounce, bit 1 any_non_specular_bounces,
+// bits 8..15 depth, bits 16..23 next_time_russian_roulette
+constexpr int PF_SPECULAR = 1, PF_ANY_NON_SPECULAR = 2;
+
+struct PathPool {
+    float4 *ray_o;  // o.xyz, tmax (< 0: dead path, skipped by the trace kernel)
+    float4 *ray_d;  // d.xyz, -
+    float4 *hit;    // {leaf-order triangle slot | n_tris + sphere (int bits), t, b1, b2}
+    float4 *beta, *L, *lambda, *lpdf;
+    float4 *ctx0;   // previous vertex for MIS: p.xyz, err.x
+    float4 *ctx1;   //                          n.xyz, err.y
+    float4 *ctx2;   //                          ns.xyz, err.z
+    float4 *misc;   // filter_weight, prev_direction_pdf, -, -
+    uint64_t *rng;  // PCG32 state (inc is re-derived from the pixel index)
+    int4 *ids;      // pixel, sample, sampler dimension, flags
+};
+
+struct WFCounters {
+    unsigned n_rays[2];
+    unsigned n_mat[3];
+    unsigned n_free;
+    unsigned n_shadow;
+    unsigned ticket_closest;
+    unsigned long long next_path, finished, rays_closest, rays_shadow;
+    unsigned stack_overflow, ticket_shadow;
+};
+
+struct WFQueues {
+    int32_t *rays[2];
+    int32_t *mat[3];
+    int32_t *free_slots;
+    // shadow rays: compact SoA by queue position
+    float4 *sh_o, *sh_d, *sh_contrib;
+    int32_t *sh_slot;
+};
+
+struct WF {
+    PathPool pool;
+    WFQueues q;
+    WFCounters *c;
+    int32_t pool_size;
+    // scene
+    BVH8 bvh;
+    const SphereRec *spheres;
+    int32_t n_spheres;
+    SpectrumTable spectra;
+    const MatRec *materials;
+    const LightRec *lights;
+    const AliasBin *alias;
+    int32_t n_lights;
+    FilterTab filter;
+    CameraRec camera;
+    FilmRec film;
+    // render options
+    int32_t sampler_kind, spp, sqrt_spp, max_depth, regularize;
+    int32_t sample_begin;
+    long long total_paths; // W*H*(sample_end - sample_begin)
+    long long n_pixels;
+};
+
+// warp-aggregated queue push: one atomicAdd per warp (the reference: one per thread,
+// integrators/wavefront_path.h:80-83).  Must be called by all 32 lanes of a converged warp.
+__device__ __forceinline__ void queue_push(unsigned *counter, int32_t *queue, int32_t value, bool pred) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0u) return;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(m) - 1;
+    unsigned base = 0;
+    if (lane == leader) base = atomicAdd(counter, (unsigned)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (pred) queue[base + __popc(m & ((1u << lane) - 1u))] = value;
+}
+// same, returning the claimed position (or -1)
+__device__ __forceinline__ int queue_claim(unsigned *counter, bool pred) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0u) return -1;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(m) - 1;
+    unsigned base = 0;
+    if (lane == leader) base = atomicAdd(counter, (unsigned)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return pred ? int(base + __popc(m & ((1u << lane) - 1u))) : -1;
+}
+
+int launch_trace_wf(b200pt_scene *s, const WF &wf, int cur, bool shadow);
+
+} // namespace b200pt

@@ -1,0 +1,650 @@
+"""The `.pbrt` scene front-end: same directives and string keys as the reference's host front-end
+(scene/lexer.h, scene/tokenizer.h, scene/parameter_dictionary.{h,cu}, scene/scene_builder.cu:287-469,
+741-893), emitting the flat arrays the C-ABI takes (include/b200pt.h: b200pt_scene_desc) instead of a
+graph of managed-memory objects.  Host code only: nothing here runs a kernel.
+
+Supported (what the hot-path configs use; everything else raises SceneError like the reference's
+REPORT_FATAL_ERROR): LookAt / Translate / Scale / Rotate / Transform / ConcatTransform / Identity /
+CoordSysTransform / ReverseOrientation / AttributeBegin|End, Camera "perspective", Film "rgb",
+PixelFilter box|gaussian|mitchell|triangle, Sampler stratified|independent, Integrator path|volpath,
+Material / MakeNamedMaterial / NamedMaterial diffuse|conductor|dielectric, AreaLightSource "diffuse",
+Shape trianglemesh|sphere|plymesh (binary little-endian or ascii PLY, triangles and quads), Include.
+"""
+import math
+import os
+import re
+
+import numpy as np
+
+from . import api, spectral
+
+F32 = np.float32
+
+
+class SceneError(ValueError):
+    pass
+
+
+# ------------------------------------------------------------------------------------- lexing
+_TYPES = ("bool", "blackbody", "float", "integer", "normal", "rgb", "point2", "point3", "string", "spectrum",
+          "texture", "vector3", "vector2", "normal3", "point")
+_TOKEN = re.compile(r'#[^\n]*|"([^"]*)"|\[|\]|([A-Za-z_]+)|([-+.0-9eE]+)')
+
+
+def lex(text):
+    """Directive stream: [(keyword, [args...])]; an arg is a str, a float, a list, or ('param', type, name)."""
+    out, cur, lst = [], None, None
+    for m in _TOKEN.finditer(text):
+        tok = m.group(0)
+        if tok.startswith("#"):
+            continue
+        if tok == "[":
+            lst = []
+            continue
+        if tok == "]":
+            cur[1].append(lst)
+            lst = None
+            continue
+        if m.group(1) is not None:
+            s = m.group(1)
+            if lst is not None:
+                lst.append(s)
+            elif " " in s.strip() and s.split()[0] in _TYPES:
+                t, n = s.split()[:2]
+                cur[1].append(("param", t, n))
+            else:
+                cur[1].append(s)
+            continue
+        if m.group(2) is not None:
+            w = m.group(2)
+            if lst is not None:
+                lst.append(w)            # bare true / false inside brackets
+            elif w in ("true", "false"):
+                cur[1].append(w)
+            else:
+                cur = (w, [])
+                out.append(cur)
+            continue
+        v = float(tok)
+        if lst is not None:
+            lst.append(v)
+        else:
+            cur[1].append(v)
+    return out
+
+
+def params_of(args):
+    """ParameterDictionary: {name: (type, values)} from the args after the type string."""
+    d, i = {}, 0
+    while i < len(args):
+        a = args[i]
+        if isinstance(a, tuple) and a[0] == "param":
+            v = args[i + 1] if i + 1 < len(args) else []
+            if not isinstance(v, list):
+                v = [v]
+            d[a[2]] = (a[1], v)
+            i += 2
+        else:
+            i += 1
+    return d
+
+
+def p_float(p, name, default):
+    return float(p[name][1][0]) if name in p else default
+
+
+def p_int(p, name, default):
+    return int(p[name][1][0]) if name in p else default
+
+
+def p_bool(p, name, default):
+    if name not in p:
+        return default
+    v = p[name][1][0]
+    return v is True or str(v).lower() == "true"
+
+
+def p_str(p, name, default):
+    return str(p[name][1][0]) if name in p else default
+
+
+# ---------------------------------------------------------------------------------- transforms
+def _m(rows):
+    return np.array(rows, dtype=F32)
+
+
+def translate(x, y, z):
+    return _m([[1, 0, 0, x], [0, 1, 0, y], [0, 0, 1, z], [0, 0, 0, 1]])
+
+
+def scale(x, y, z):
+    return _m([[x, 0, 0, 0], [0, y, 0, 0], [0, 0, z, 0], [0, 0, 0, 1]])
+
+
+def rotate(theta_deg, ax):
+    a = np.asarray(ax, dtype=np.float64)
+    a = a / np.linalg.norm(a)
+    s, c = math.sin(math.radians(theta_deg)), math.cos(math.radians(theta_deg))
+    x, y, z = a
+    return _m([[x * x + (1 - x * x) * c, x * y * (1 - c) - z * s, x * z * (1 - c) + y * s, 0],
+               [x * y * (1 - c) + z * s, y * y + (1 - y * y) * c, y * z * (1 - c) - x * s, 0],
+               [x * z * (1 - c) - y * s, y * z * (1 - c) + x * s, z * z + (1 - z * z) * c, 0], [0, 0, 0, 1]])
+
+
+def lookat(pos, look, up):
+    """euclidean_space/transform.h lookat: camera_from_world (inverse of the world_from_camera frame)."""
+    pos, look, up = (np.asarray(v, dtype=F32) for v in (pos, look, up))
+    d = look - pos
+    d = d / F32(np.linalg.norm(d))
+    upn = up / F32(np.linalg.norm(up))
+    right = np.cross(upn, d)
+    if np.linalg.norm(right) == 0:
+        raise SceneError("LookAt: up vector and viewing direction are parallel")
+    right = (right / np.linalg.norm(right)).astype(F32)
+    new_up = np.cross(d, right).astype(F32)
+    wfc = np.eye(4, dtype=F32)
+    wfc[:3, 0], wfc[:3, 1], wfc[:3, 2], wfc[:3, 3] = right, new_up, d, pos
+    return inv(wfc)
+
+
+def inv(m):
+    return np.linalg.inv(m.astype(np.float64)).astype(F32)
+
+
+def perspective(fov, n, f):
+    persp = _m([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, f / (f - n), -f * n / (f - n)], [0, 0, 1, 0]])
+    it = 1.0 / math.tan(math.radians(fov) / 2.0)
+    return scale(it, it, 1.0) @ persp
+
+
+def xf_points(m, P):
+    """Transform::operator()(Point3f): m00 x + m01 y + m02 z + m03 in fp32, left to right."""
+    P = np.asarray(P, dtype=F32).reshape(-1, 3)
+    x, y, z = P[:, 0], P[:, 1], P[:, 2]
+    out = np.empty_like(P)
+    for r in range(3):
+        out[:, r] = ((m[r, 0] * x + m[r, 1] * y) + m[r, 2] * z) + m[r, 3]
+    w = ((m[3, 0] * x + m[3, 1] * y) + m[3, 2] * z) + m[3, 3]
+    if not np.all(w == 1):
+        out = out / w[:, None]
+    return out.astype(F32)
+
+
+def swaps_handedness(m):
+    return float(np.linalg.det(m[:3, :3].astype(np.float64))) < 0
+
+
+# ---------------------------------------------------------------------------------------- PLY
+def read_ply(path):
+    """Triangles (quads split 0-1-2, 0-2-3) of an ascii / binary_little_endian PLY (shapes/tri_quad_mesh.cu)."""
+    with open(path, "rb") as f:
+        data = f.read()
+    end = data.index(b"end_header") + len(b"end_header")
+    end = data.index(b"\n", end) + 1
+    header = data[:end].decode("ascii", "replace").split("\n")
+    fmt, elems, cur = None, [], None
+    for line in header:
+        t = line.split()
+        if not t:
+            continue
+        if t[0] == "format":
+            fmt = t[1]
+        elif t[0] == "element":
+            cur = {"name": t[1], "count": int(t[2]), "props": []}
+            elems.append(cur)
+        elif t[0] == "property":
+            cur["props"].append(t[1:])
+    np_t = {"char": "i1", "uchar": "u1", "int8": "i1", "uint8": "u1", "short": "i2", "ushort": "u2", "int16": "i2",
+            "uint16": "u2", "int": "i4", "uint": "u4", "int32": "i4", "uint32": "u4", "float": "f4", "float32": "f4",
+            "double": "f8", "float64": "f8"}
+    body, off = data[end:], 0
+    verts = faces = None
+    if fmt == "ascii":
+        toks = body.split()
+        pos = 0
+    for e in elems:
+        if e["name"] == "vertex":
+            names = [p[-1] for p in e["props"]]
+            if fmt == "ascii":
+                k = len(names)
+                arr = np.array(toks[pos:pos + k * e["count"]], dtype=np.float64).reshape(e["count"], k)
+                pos += k * e["count"]
+                verts = {n: arr[:, i] for i, n in enumerate(names)}
+            else:
+                dt = np.dtype([(p[-1], "<" + np_t[p[0]]) for p in e["props"]])
+                arr = np.frombuffer(body, dtype=dt, count=e["count"], offset=off)
+                off += dt.itemsize * e["count"]
+                verts = {n: arr[n] for n in names}
+        elif e["name"] == "face":
+            tris = []
+            if fmt == "ascii":
+                for _ in range(e["count"]):
+                    k = int(toks[pos])
+                    idx = [int(v) for v in toks[pos + 1:pos + 1 + k]]
+                    pos += 1 + k
+                    tris.append(idx[:3])
+                    if k == 4:
+                        tris.append([idx[0], idx[2], idx[3]])
+                faces = np.array(tris, dtype=np.int32)
+            else:
+                lp = [p for p in e["props"] if p[0] == "list"][0]
+                ct, it = "<" + np_t[lp[1]], "<" + np_t[lp[2]]
+                cs, isz = np.dtype(ct).itemsize, np.dtype(it).itemsize
+                first = int(np.frombuffer(body, dtype=ct, count=1, offset=off)[0])
+                rec = np.dtype([("n", ct), ("v", it, (first,))])
+                arr = np.frombuffer(body, dtype=rec, count=e["count"], offset=off)
+                if len(e["props"]) != 1 or not np.all(arr["n"] == first):
+                    raise SceneError("PLY: mixed polygon sizes are not supported")
+                off += rec.itemsize * e["count"]
+                v = arr["v"].astype(np.int32)
+                faces = v if first == 3 else np.concatenate([v[:, [0, 1, 2]], v[:, [0, 2, 3]]]) if first == 4 else None
+                if faces is None:
+                    raise SceneError("PLY: only triangles and quads")
+                del cs, isz
+    P = np.stack([verts["x"], verts["y"], verts["z"]], axis=1).astype(F32)
+    N = np.stack([verts["nx"], verts["ny"], verts["nz"]], axis=1).astype(F32) if "nx" in verts else None
+    return P, faces, N
+
+
+# ------------------------------------------------------------------------------ pixel filters
+def filter_table(kind, p):
+    """FilterSampler's table (filters/filter_sampler.cu:4-20): f at the cell centres of a 32*radius grid."""
+    defaults = {"box": 0.5, "gaussian": 1.5, "mitchell": 2.0, "triangle": 2.0}
+    if kind not in defaults:
+        raise SceneError("PixelFilter '%s' not implemented" % kind)
+    rx, ry = F32(p_float(p, "xradius", defaults[kind])), F32(p_float(p, "yradius", defaults[kind]))
+    nx, ny = int(F32(32) * rx), int(F32(32) * ry)
+    xs = (F32(-rx) * (F32(1) - (np.arange(nx, dtype=F32) + F32(0.5)) / F32(nx)) + (np.arange(nx, dtype=F32) + F32(0.5)) / F32(nx) * rx).astype(F32)
+    ys = (F32(-ry) * (F32(1) - (np.arange(ny, dtype=F32) + F32(0.5)) / F32(ny)) + (np.arange(ny, dtype=F32) + F32(0.5)) / F32(ny) * ry).astype(F32)
+    if kind == "mitchell":
+        b, c = F32(p_float(p, "B", 1.0 / 3.0)), F32(p_float(p, "C", 1.0 / 3.0))
+
+        def m1d(x):   # filters/mitchell.cu:25-39
+            x = np.abs(x).astype(F32)
+            a = ((12 - 9 * b - 6 * c) * x * x * x + (-18 + 12 * b + 6 * c) * x * x + (6 - 2 * b)) * F32(1.0 / 6.0)
+            bb = ((-b - 6 * c) * x * x * x + (6 * b + 30 * c) * x * x + (-12 * b - 48 * c) * x + (8 * b + 24 * c)) * F32(1.0 / 6.0)
+            return np.where(x <= 1, a, np.where(x <= 2, bb, 0)).astype(F32)
+
+        f = np.outer(m1d(F32(2) * ys / ry), m1d(F32(2) * xs / rx))
+    elif kind == "box":
+        f = np.ones((ny, nx))
+    elif kind == "triangle":
+        f = np.outer(np.maximum(0, ry - np.abs(ys)), np.maximum(0, rx - np.abs(xs)))
+    else:  # gaussian
+        sigma = F32(p_float(p, "sigma", 0.5))
+
+        def g(x, r):
+            gs = lambda v: np.exp(-v * v / (2 * sigma * sigma)) / np.sqrt(2 * np.pi * sigma * sigma)
+            return np.maximum(0, gs(x) - gs(r))
+
+        f = np.outer(g(ys, ry), g(xs, rx))
+    return float(rx), float(ry), nx, ny, np.ascontiguousarray(f, dtype=F32)
+
+
+# ------------------------------------------------------------------------------ scene assembly
+class Scene:
+    """Flat scene arrays + options, ready for b200pt_scene_create."""
+
+    def __init__(self):
+        self.P, self.idx, self.tri_material, self.tri_light, self.tri_flip = [], [], [], [], []
+        self.n_verts = 0
+        self.spheres, self.spectra, self.materials, self.lights = [], [], [], []
+        self.camera = self.filter = self.film = None
+        self.spp, self.max_depth, self.regularize, self.sampler = None, 5, False, "stratified"
+        self.integrator = "path"
+        self.filename = "pbrt.png"
+        self._spec_cache = {}
+        self._keep = []
+
+    # ---- spectra
+    def add_spectrum(self, key, rec):
+        if key in self._spec_cache:
+            return self._spec_cache[key]
+        self.spectra.append(rec)
+        self._spec_cache[key] = len(self.spectra) - 1
+        return len(self.spectra) - 1
+
+    def spec_constant(self, v):
+        return self.add_spectrum(("c", float(v)), {"type": 0, "c": [float(v), 0, 0, 0]})
+
+    def spec_rgb(self, rgb, kind):
+        rgb = tuple(float(v) for v in rgb)
+        if kind == "albedo":
+            if max(rgb) > 1:
+                raise SceneError("rgb albedo components must be <= 1 (base/spectrum.cu:67-69)")
+            c = spectral.rgb_to_sigmoid(rgb)
+            return self.add_spectrum(("a",) + rgb, {"type": 1, "c": [c[0], c[1], c[2], 1.0]})
+        if kind == "unbounded":
+            m = max(rgb)
+            sc = 2.0 * m
+            c = spectral.rgb_to_sigmoid([v / sc for v in rgb] if sc > 0 else (0, 0, 0))
+            return self.add_spectrum(("u",) + rgb, {"type": 2, "c": [c[0], c[1], c[2], sc]})
+        sc = 2.0 * max(rgb)
+        c = spectral.rgb_to_sigmoid([v / sc for v in rgb] if sc > 0 else (0, 0, 0))
+        return self.add_spectrum(("i",) + rgb, {"type": 3, "c": [c[0], c[1], c[2], sc]})
+
+    def spec_piecewise(self, key, lam, val):
+        lam, val = np.ascontiguousarray(lam, dtype=F32), np.ascontiguousarray(val, dtype=F32)
+        return self.add_spectrum(("p", key), {"type": 4, "c": [0, 0, 0, 0], "lambda": lam, "value": val})
+
+    def spec_param(self, p, name, kind, scene_dir):
+        """ParameterDictionary::get_spectrum (scene/parameter_dictionary.cu:127-176,198-221)."""
+        if name not in p:
+            return None
+        t, v = p[name]
+        if t == "rgb":
+            return self.spec_rgb(v[:3], kind)
+        if t == "spectrum":
+            if isinstance(v[0], str):
+                path = os.path.join(scene_dir, v[0])
+                if os.path.exists(path):
+                    nums = [float(x) for x in open(path).read().split() if not x.startswith("#")]
+                    lam, val = spectral.interleaved_to_knots(nums)
+                    return self.spec_piecewise(("file", path), lam, val)
+                lam, val = spectral.named_spectrum(v[0])
+                return self.spec_piecewise(("named", v[0]), lam, val)
+            lam, val = spectral.interleaved_to_knots(v)
+            return self.spec_piecewise(("inline", tuple(v)), lam, val)
+        if t == "float":
+            return self.spec_constant(v[0])
+        raise SceneError("spectrum parameter '%s' of type '%s' not supported" % (name, t))
+
+    # ---- materials
+    def add_material(self, kind, p, scene_dir):
+        if kind == "diffuse":
+            r = self.spec_param(p, "reflectance", "albedo", scene_dir)
+            if r is None:
+                r = self.spec_constant(0.5)
+            self.materials.append({"type": 0, "reflectance": r, "eta": -1, "k": -1, "ur": 0.0, "vr": 0.0, "remap": 1})
+        elif kind == "conductor":
+            refl = self.spec_param(p, "reflectance", "albedo", scene_dir)
+            eta = self.spec_param(p, "eta", "unbounded", scene_dir)
+            k = self.spec_param(p, "k", "unbounded", scene_dir)
+            if refl is not None and (eta is not None or k is not None):
+                raise SceneError("conductor: both reflectance and (eta, k) given")
+            if refl is None:
+                if eta is None:
+                    eta = self.spec_piecewise(("named", "metal-Cu-eta"), *spectral.named_spectrum("metal-Cu-eta"))
+                if k is None:
+                    k = self.spec_piecewise(("named", "metal-Cu-k"), *spectral.named_spectrum("metal-Cu-k"))
+            ro = p_float(p, "roughness", 0.0)
+            self.materials.append({"type": 1, "reflectance": -1 if refl is None else refl, "eta": -1 if eta is None else eta,
+                                   "k": -1 if k is None else k, "ur": p_float(p, "uroughness", ro), "vr": p_float(p, "vroughness", ro),
+                                   "remap": int(p_bool(p, "remaproughness", True))})
+        elif kind == "dielectric":
+            if "eta" in p and p["eta"][0] == "float":
+                eta = self.spec_constant(p["eta"][1][0])
+            else:
+                eta = self.spec_param(p, "eta", "unbounded", scene_dir)
+            if eta is None:
+                eta = self.spec_constant(1.5)
+            ro = p_float(p, "roughness", 0.0)
+            self.materials.append({"type": 2, "reflectance": -1, "eta": eta, "k": -1, "ur": p_float(p, "uroughness", ro),
+                                   "vr": p_float(p, "vroughness", ro), "remap": int(p_bool(p, "remaproughness", True))})
+        else:
+            raise SceneError("Material '%s' is outside the hot path (SURVEY.md 8f)" % kind)
+        return len(self.materials) - 1
+
+    # ---- geometry
+    def add_mesh(self, P, idx, material, flip, light_params, scene_dir):
+        P = np.asarray(P, dtype=F32).reshape(-1, 3)
+        idx = np.asarray(idx, dtype=np.int32).reshape(-1, 3)
+        nt = len(idx)
+        first_tri = sum(len(i) for i in self.idx)
+        self.P.append(P)
+        self.idx.append(idx + self.n_verts)
+        self.n_verts += len(P)
+        self.tri_material.append(np.full(nt, material, dtype=np.int32))
+        self.tri_flip.append(np.full(nt, 1 if flip else 0, dtype=np.uint8))
+        tl = np.full(nt, -1, dtype=np.int32)
+        if light_params is not None:
+            # one DiffuseAreaLight per triangle (base/light.cu:56-75, lights/diffuse_area_light.cu:9-31)
+            L = self.spec_param(light_params, "L", "illuminant", scene_dir)
+            if L is None:
+                lam, val, _ = spectral.illuminant_d65()
+                L = self.spec_piecewise(("illuminant",), lam, val)
+            sc = F32(p_float(light_params, "scale", 1.0))
+            sc = F32(sc / self.photometric(L))
+            two = p_bool(light_params, "twosided", False)
+            for k in range(nt):
+                tl[k] = len(self.lights)
+                self.lights.append({"triangle": first_tri + k, "spectrum": L, "scale": float(sc), "two_sided": int(two)})
+        self.tri_light.append(tl)
+
+    def photometric(self, spec_id):
+        """Spectrum::to_photometric (base/spectrum.cu:115-120): RGB illuminants use the illuminant's integral."""
+        rec = self.spectra[spec_id]
+        y = spectral.cie_xyz()[1]
+        grid = np.arange(360, 831)
+        if rec["type"] == 3:
+            return F32(spectral.inner_product_dense(spectral.illuminant_d65()[2], y))
+        if rec["type"] == 4:
+            return F32(spectral.inner_product_dense(spectral.piecewise_eval(rec["lambda"], rec["value"], grid), y))
+        if rec["type"] == 0:
+            return F32(rec["c"][0] * float(np.sum(y.astype(np.float64))))
+        raise SceneError("to_photometric: unsupported spectrum type")
+
+    # ---- to the C-ABI
+    def to_desc(self):
+        keep = self._keep = []
+        d = api.SceneDesc()
+        P = np.ascontiguousarray(np.concatenate(self.P) if self.P else np.zeros((0, 3), F32), dtype=F32)
+        idx = np.ascontiguousarray(np.concatenate(self.idx) if self.idx else np.zeros((0, 3), np.int32), dtype=np.int32)
+        tm = np.ascontiguousarray(np.concatenate(self.tri_material) if self.idx else np.zeros(0, np.int32))
+        tl = np.ascontiguousarray(np.concatenate(self.tri_light) if self.idx else np.zeros(0, np.int32))
+        tf = np.ascontiguousarray(np.concatenate(self.tri_flip) if self.idx else np.zeros(0, np.uint8))
+        keep += [P, idx, tm, tl, tf]
+        d.n_vertices, d.P = len(P), api._fp(P)
+        d.n_triangles, d.indices = len(idx), api._ip(idx)
+        d.tri_material, d.tri_light = api._ip(tm), api._ip(tl)
+        d.tri_flip = tf.ctypes.data_as(api.C.POINTER(api.C.c_uint8))
+        C = api.C
+        sph = (api.Sphere * max(1, len(self.spheres)))()
+        for i, s in enumerate(self.spheres):
+            sph[i].render_from_object[:] = [float(v) for v in s["rfo"].reshape(-1)]
+            sph[i].object_from_render[:] = [float(v) for v in s["ofr"].reshape(-1)]
+            sph[i].radius, sph[i].z_min, sph[i].z_max, sph[i].phi_max = s["radius"], s["zmin"], s["zmax"], s["phimax"]
+            sph[i].reverse_orientation, sph[i].transform_swaps_handedness = int(s["ro"]), int(s["swaps"])
+            sph[i].material, sph[i].light = s["material"], -1
+        d.n_spheres, d.spheres = len(self.spheres), sph
+        spec = (api.Spectrum * max(1, len(self.spectra)))()
+        for i, s in enumerate(self.spectra):
+            spec[i].type = s["type"]
+            spec[i].c[:] = [float(v) for v in s["c"]]
+            if "value" in s:
+                spec[i].n = len(s["value"])
+                spec[i].value = api._fp(s["value"])
+                keep.append(s["value"])
+                if "lambda" in s:
+                    spec[i].lambda_ = api._fp(s["lambda"])
+                    keep.append(s["lambda"])
+        d.n_spectra, d.spectra = len(self.spectra), spec
+        mats = (api.Material * max(1, len(self.materials)))()
+        for i, m in enumerate(self.materials):
+            mats[i].type, mats[i].reflectance, mats[i].eta, mats[i].k = m["type"], m["reflectance"], m["eta"], m["k"]
+            mats[i].u_roughness, mats[i].v_roughness, mats[i].remap_roughness = m["ur"], m["vr"], m["remap"]
+        d.n_materials, d.materials = len(self.materials), mats
+        lights = (api.Light * max(1, len(self.lights)))()
+        for i, l in enumerate(self.lights):
+            lights[i].triangle, lights[i].spectrum, lights[i].scale, lights[i].two_sided = l["triangle"], l["spectrum"], l["scale"], l["two_sided"]
+        d.n_lights, d.lights = len(self.lights), lights
+        keep += [sph, spec, mats, lights]
+        if self.camera is not None:
+            cam = api.Camera()
+            cam.camera_from_raster[:] = [float(v) for v in self.camera["cfr"].reshape(-1)]
+            cam.render_from_camera[:] = [float(v) for v in self.camera["rfc"].reshape(-1)]
+            cam.lens_radius, cam.focal_distance = self.camera["lens_radius"], self.camera["focal_distance"]
+            flt = api.Filter()
+            flt.radius_x, flt.radius_y, flt.nx, flt.ny, ftab = self.filter
+            flt.f = api._fp(ftab)
+            film = api.FilmDesc()
+            film.width, film.height = self.film["width"], self.film["height"]
+            cx, cy, cz = spectral.cie_xyz()
+            ill = spectral.illuminant_d65()[2]
+            film.cie_x, film.cie_y, film.cie_z, film.illuminant = api._fp(cx), api._fp(cy), api._fp(cz), api._fp(ill)
+            film.imaging_ratio = 1.0
+            M = spectral.srgb_color_space()["rgb_from_xyz"]
+            film.output_rgb_from_sensor_rgb[:] = [float(v) for v in M.reshape(-1)]
+            d.camera, d.filter, d.film = C.pointer(cam), C.pointer(flt), C.pointer(film)
+            keep += [cam, flt, film, ftab, cx, cy, cz, ill]
+        return d
+
+
+# ------------------------------------------------------------------------------------ parsing
+class _GState:
+    def __init__(self):
+        self.ctm = np.eye(4, dtype=F32)
+        self.reverse_orientation = False
+        self.material = 0
+        self.area_light = None
+
+    def copy(self):
+        g = _GState()
+        g.ctm, g.reverse_orientation, g.material, g.area_light = self.ctm.copy(), self.reverse_orientation, self.material, self.area_light
+        return g
+
+
+def load(path=None, text=None, spp=None, integrator=None):
+    """SceneBuilder::parse_file + preprocess (scene/scene_builder.cu:741-966) -> Scene."""
+    if text is None:
+        text = open(path).read()
+    scene_dir = os.path.dirname(os.path.abspath(path)) if path else os.getcwd()
+    sc = Scene()
+    g, stack = _GState(), []
+    named_cs, named_mat = {}, {}
+    pre = {"Camera": None, "Film": None, "PixelFilter": None, "Sampler": None, "Integrator": None}
+    cam_ctm = None
+    render_from_world = np.eye(4, dtype=F32)
+    sc.add_material("diffuse", {}, scene_dir)   # default material = diffuse 0.5 (scene_builder.cu:140-141)
+
+    def directives(txt, base):
+        for kw, args in lex(txt):
+            if kw == "Include":
+                inc = os.path.join(base, args[0])
+                yield from directives(open(inc).read(), os.path.dirname(inc))
+            else:
+                yield kw, args
+
+    def world_begin():
+        nonlocal render_from_world
+        # build_filter, build_film, build_camera (scene_builder.cu:778-781)
+        fa = pre["PixelFilter"]
+        sc.filter = filter_table(fa[0] if fa else "mitchell", params_of(fa[1:]) if fa else {})
+        fp = params_of(pre["Film"][1:]) if pre["Film"] else {}
+        sc.film = {"width": p_int(fp, "xresolution", 1280), "height": p_int(fp, "yresolution", 720)}
+        sc.filename = os.path.splitext(p_str(fp, "filename", "pbrt.png"))[0] + ".png"
+        if pre["Camera"] is None or pre["Camera"][0] != "perspective":
+            raise SceneError("Camera 'perspective' is required")
+        cp = params_of(pre["Camera"][1:])
+        world_from_camera = inv(cam_ctm)
+        named_cs["camera"] = world_from_camera
+        pos = xf_points(world_from_camera, [[0, 0, 0]])[0]
+        world_from_render = translate(*pos)            # CameraWorldCoordSystem (cameras/camera_base.h:34-39)
+        render_from_world = inv(world_from_render)
+        rfc = (render_from_world @ world_from_camera).astype(F32)
+        W, H = sc.film["width"], sc.film["height"]
+        aspect = F32(W) / F32(H)
+        if aspect > 1:
+            smin, smax = (-aspect, -1.0), (aspect, 1.0)
+        else:
+            smin, smax = (-1.0, -1.0 / aspect), (1.0, 1.0 / aspect)
+        ndc_from_screen = scale(1.0 / (smax[0] - smin[0]), 1.0 / (smax[1] - smin[1]), 1.0) @ translate(-smin[0], -smax[1], 0.0)
+        raster_from_ndc = scale(W, -H, 1.0)
+        raster_from_screen = (raster_from_ndc @ ndc_from_screen).astype(F32)
+        screen_from_camera = perspective(p_float(cp, "fov", 90.0), 1e-2, 1000.0)
+        cfr = (inv(screen_from_camera) @ inv(raster_from_screen)).astype(F32)
+        sc.camera = {"cfr": cfr, "rfc": rfc, "lens_radius": p_float(cp, "lensradius", 0.0),
+                     "focal_distance": p_float(cp, "focaldistance", 1e6)}
+        sp = pre["Sampler"]
+        if sp:
+            sc.sampler = sp[0] if sp[0] in ("independent", "stratified") else "stratified"
+            sc.spp = p_int(params_of(sp[1:]), "pixelsamples", None)
+        ip = pre["Integrator"]
+        if ip:
+            sc.integrator = ip[0]
+            ipp = params_of(ip[1:])
+            sc.max_depth = p_int(ipp, "maxdepth", 5)
+            sc.regularize = p_bool(ipp, "regularize", False)
+
+    for kw, args in directives(text, scene_dir):
+        if kw in pre:
+            if kw == "Camera":
+                cam_ctm = g.ctm.copy()
+            pre[kw] = args
+        elif kw == "WorldBegin":
+            world_begin()
+            g.ctm = np.eye(4, dtype=F32)
+            named_cs["world"] = g.ctm.copy()
+        elif kw == "AttributeBegin":
+            stack.append(g.copy())
+        elif kw == "AttributeEnd":
+            g = stack.pop()
+        elif kw == "Identity":
+            g.ctm = np.eye(4, dtype=F32)
+        elif kw == "Translate":
+            g.ctm = (g.ctm @ translate(*args[:3])).astype(F32)
+        elif kw == "Scale":
+            g.ctm = (g.ctm @ scale(*args[:3])).astype(F32)
+        elif kw == "Rotate":
+            g.ctm = (g.ctm @ rotate(args[0], args[1:4])).astype(F32)
+        elif kw == "LookAt":
+            g.ctm = (g.ctm @ lookat(args[0:3], args[3:6], args[6:9])).astype(F32)
+        elif kw == "Transform":
+            g.ctm = np.array(args[0], dtype=F32).reshape(4, 4).T.copy()
+        elif kw == "ConcatTransform":
+            g.ctm = (g.ctm @ np.array(args[0], dtype=F32).reshape(4, 4).T).astype(F32)
+        elif kw == "CoordSysTransform":
+            if args[0] in named_cs:
+                g.ctm = named_cs[args[0]].copy()
+        elif kw == "ReverseOrientation":
+            g.reverse_orientation = not g.reverse_orientation
+        elif kw == "Material":
+            g.material = sc.add_material(args[0], params_of(args[1:]), scene_dir)
+        elif kw == "MakeNamedMaterial":
+            p = params_of(args[1:])
+            named_mat[args[0]] = sc.add_material(p_str(p, "type", "diffuse"), p, scene_dir)
+        elif kw == "NamedMaterial":
+            if args[0] not in named_mat:
+                raise SceneError("NamedMaterial '%s' not defined" % args[0])
+            g.material = named_mat[args[0]]
+        elif kw == "AreaLightSource":
+            if args[0] != "diffuse":
+                raise SceneError("AreaLightSource: only 'diffuse' (scene_builder.cu:604-616)")
+            g.area_light = params_of(args[1:])
+        elif kw == "Shape":
+            p = params_of(args[1:])
+            rfo = (render_from_world @ g.ctm).astype(F32)
+            flip = g.reverse_orientation ^ swaps_handedness(rfo)
+            if args[0] in ("trianglemesh", "plymesh"):
+                if args[0] == "plymesh":
+                    P, idx, _N = read_ply(os.path.join(scene_dir, p_str(p, "filename", "")))
+                else:
+                    P = np.array(p["P"][1], dtype=F32).reshape(-1, 3)
+                    idx = np.array(p["indices"][1], dtype=np.int32).reshape(-1, 3) if "indices" in p else np.array([[0, 1, 2]], np.int32)
+                is_identity = np.array_equal(rfo, np.eye(4, dtype=F32))
+                Pr = P if is_identity else xf_points(rfo, P)   # shapes/triangle_mesh.cu:49-78
+                sc.add_mesh(Pr, idx, g.material, flip, g.area_light, scene_dir)
+            elif args[0] == "sphere":
+                if g.area_light is not None:
+                    raise SceneError("emissive spheres are outside the hot path")
+                r = p_float(p, "radius", 1.0)
+                sc.spheres.append({"rfo": rfo, "ofr": inv(rfo), "radius": r, "zmin": p_float(p, "zmin", -r), "zmax": p_float(p, "zmax", r),
+                                   "phimax": math.radians(min(max(p_float(p, "phimax", 360.0), 0.0), 360.0)),
+                                   "ro": g.reverse_orientation, "swaps": swaps_handedness(rfo), "material": g.material})
+            else:
+                raise SceneError("Shape '%s' is outside the hot path (SURVEY.md 8f)" % args[0])
+        elif kw in ("ObjectBegin", "ObjectEnd", "ObjectInstance", "LightSource", "MakeNamedMedium", "MediumInterface", "Texture"):
+            raise SceneError("directive '%s' is outside the hot path (SURVEY.md 8f)" % kw)
+        elif kw in ("ColorSpace", "Option", "Attribute"):
+            continue
+        else:
+            raise SceneError("unknown directive '%s'" % kw)   # scene_builder.cu:467-468
+    if sc.camera is None:
+        raise SceneError("no WorldBegin")
+    # spp: CLI --spp > Sampler "integer pixelsamples" > 4 (scene_builder.cu:249-251,402-404)
+    sc.spp = spp if spp is not None else (sc.spp if sc.spp is not None else 4)
+    if integrator is not None:
+        sc.integrator = integrator
+    if sc.integrator == "volpath":
+        sc.integrator = "path"
+    return sc

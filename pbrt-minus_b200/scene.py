@@ -157,3 +157,93 @@ class HLBVH:
             self.close()
         except Exception:
             pass
+
+
+class Film:
+    """RGBFilm (film/rgb_film.h:16-75) as a device accumulator: {sum X*w, sum Y*w, sum Z*w, sum w} per pixel."""
+
+    def __init__(self, accel):
+        self.accel = accel
+        self.lib = accel.lib
+        h = C.c_void_p()
+        _check(self.lib.b200pt_film_create(accel.handle, C.byref(h)))
+        self.handle = h
+        w, hh = C.c_int32(), C.c_int32()
+        _check(self.lib.b200pt_film_dims(self.handle, C.byref(w), C.byref(hh)))
+        self.width, self.height = w.value, hh.value
+
+    def clear(self):
+        _check(self.lib.b200pt_film_clear(self.handle))
+
+    def get_pixel_rgb(self):
+        """[H, W, 3] linear output RGB (RGBFilm::get_pixel_rgb, film/rgb_film.cu:107-122)."""
+        out = np.empty((self.height, self.width, 3), dtype=np.float32)
+        _check(self.lib.b200pt_film_read(self.handle, _fp(out)))
+        return out
+
+    def raw(self):
+        out = np.empty((self.height, self.width, 4), dtype=np.float32)
+        _check(self.lib.b200pt_film_read_raw(self.handle, _fp(out)))
+        return out
+
+    @property
+    def device_ptr(self):
+        return self.lib.b200pt_film_device_ptr(self.handle)
+
+    def reduce(self, nccl_comm, root=0, stream=None):
+        _check(self.lib.b200pt_film_reduce(self.handle, nccl_comm, int(root), stream))
+
+    def write_to_png(self, path):
+        """Film::write_to_png (base/film.cu:57-99): sRGB-encode, clamp, 8 bit."""
+        from . import png
+        png.write_png(path, srgb8(self.get_pixel_rgb()))
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.b200pt_film_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def srgb8(rgb):
+    """spectrum_util/color_encoding.h: linear -> sRGB 8 bit."""
+    v = np.clip(rgb, 0.0, 1.0)
+    e = np.where(v <= 0.0031308, 12.92 * v, 1.055 * np.power(v, 1.0 / 2.4) - 0.055)
+    return np.clip(np.round(255.0 * e), 0, 255).astype(np.uint8)
+
+
+class WavefrontPathIntegrator:
+    """integrators/wavefront_path.h:136-140: WavefrontPathIntegrator(spp, sampler, params, base) + render(film).
+    `scene` is a pbrt_scene.Scene; the accelerator is built here (scene_builder.cu:912)."""
+
+    def __init__(self, scene, device=0, spp=None):
+        self.scene = scene
+        desc = scene.to_desc()
+        self.accel = HLBVH(None, None, device=device, desc=desc, keep=scene)
+        self.spp = spp if spp is not None else scene.spp
+        self.last_stats = None
+
+    def create_film(self):
+        return Film(self.accel)
+
+    def render(self, film, sample_begin=0, sample_end=None, pool_size=0):
+        o = api.RenderOpts()
+        o.spp_total = int(self.spp)
+        o.sample_begin = int(sample_begin)
+        o.sample_end = int(self.spp if sample_end is None else sample_end)
+        o.max_depth = int(self.scene.max_depth)
+        o.regularize = int(self.scene.regularize)
+        o.sampler = 1 if self.scene.sampler == "independent" else 0
+        o.pool_size = int(pool_size)
+        st = api.RenderStats()
+        _check(self.accel.lib.b200pt_render(self.accel.handle, film.handle, C.byref(o), C.byref(st)))
+        self.last_stats = st.as_dict()
+        return self.last_stats
+
+    def close(self):
+        self.accel.close()
