@@ -92,6 +92,32 @@ def gen_film_dump():
     return path
 
 
+def gen_light_debug():
+    """Generated copy of light_samplers/power_light_sampler.cu that prints the light weights and the alias
+    table (debug binary pbrt-minus-ref-debug only; the timed / golden binary stays unmodified)."""
+    src = open(os.path.join(REF, "src/pbrt/light_samplers/power_light_sampler.cu")).read()
+    marker = "    lights_power_distribution = allocator.create<Distribution1D>(lights_pmf, allocator);\n"
+    assert src.count(marker) == 1, "reference power_light_sampler.cu changed"
+    dump = r'''
+    {   // [oracle/ref_build] debug dump
+        cudaDeviceSynchronize();
+        const AliasTable *t = lights_power_distribution->alias_table;
+        for (int i = 0; i < light_num && i < 64; ++i) {
+            printf("[lightdbg] %d weight %.9g pdf %.9g bin p %.9g first %d second %d\\n", i, (double)lights_pmf[i],
+                   (double)t->pdfs[i], (double)t->bins[i].p, t->bins[i].first_idx, t->bins[i].second_idx);
+        }
+    }
+'''
+    os.makedirs(GEN, exist_ok=True)
+    path = os.path.join(GEN, "power_light_sampler_debug.cu")
+    new = src.replace(marker, marker + dump).replace("#include <pbrt/light_samplers/power_light_sampler.h>",
+                                                     "#include <pbrt/light_samplers/power_light_sampler.h>\n#include <pbrt/distribution/alias_table.h>\n#include <cstdio>")
+    new = "#define private public  // [oracle/ref_build] debug copy only: Distribution1D::alias_table is private\n" + new
+    if not os.path.exists(path) or open(path).read() != new:
+        open(path, "w").write(new)
+    return path
+
+
 def build_probe():
     """Host-only probe of the reference's integer paths -> tests/golden/ref_probe.json."""
     os.makedirs(OUT, exist_ok=True)
@@ -152,6 +178,10 @@ def main():
         build_probe()
     if args.only in ("", "cli"):
         run(link + main_o + lib + tail + ["-o", os.path.join(OUT, "pbrt-minus-ref")])
+    if args.only in ("", "cli", "debug"):
+        dbg_o = compile_one((gen_light_debug(), os.path.join(OBJ, "gen_power_light_sampler_debug.o"), []))
+        lib_dbg = [o for o in lib if not o.endswith("src_pbrt_light_samplers_power_light_sampler.o")] + [dbg_o]
+        run(link + main_o + lib_dbg + tail + ["-o", os.path.join(OUT, "pbrt-minus-ref-debug")])
     for h in harness:
         name = os.path.basename(h)[len("harness_"):-2]
         if args.only in ("", name.replace("ref_", "")):

@@ -25,7 +25,8 @@ struct LightRec { // 64 B
     int32_t flags;    // bit 0: two_sided, bit 1: flip normal (reverse_orientation ^ swaps_handedness)
     float pmf;        // power_light_sampler pdfs[idx]
     float area;
-    int32_t pad[2];
+    int32_t prim;     // primitive (triangle) index of this light: its own shadow rays skip it
+    int32_t pad;
 };
 
 struct AliasBin {

@@ -16,6 +16,8 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <numeric>
 #include <set>
 
@@ -95,12 +97,12 @@ static float build_pc1d(const float *f, int n, float mn, float mx, float *func, 
     return func_int;
 }
 
-__global__ void k_light_power(SpectrumTable tab, const LightRec *lights, int n, float *out) {
+__global__ void k_light_power(SpectrumTable tab, const LightRec *lights, int n, S4 lambda, S4 pdf, float *out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    // light_samplers/power_light_sampler.cu:15-21: phi at the wavelengths of sample_visible(0.5)
-    S4 lambda, pdf;
-    sample_visible(0.5f, &lambda, &pdf);
+    // light_samplers/power_light_sampler.cu:15-21: phi at the wavelengths of sample_visible(0.5), which the
+    // reference evaluates on the HOST; the 4th wavelength sits within an ulp of the 830 nm cut-off of
+    // visible_wavelengths_pdf, so lambda / pdf come from the host's libm (see b200pt_upload_render_data)
     const LightRec L = lights[i];
     const S4 Le = spectrum_sample(tab, L.spectrum, lambda) * L.scale;
     const S4 phi = Le * (kPi * ((L.flags & 1) ? 2.f : 1.f) * L.area);
@@ -293,11 +295,21 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
         o.spectrum = l.spectrum;
         o.flags = (l.two_sided ? 1 : 0) | ((desc->tri_flip && desc->tri_flip[l.triangle]) ? 2 : 0);
         o.pmf = 0.f;
+        // Triangle::area (shapes/triangle.h:41-44) with the reference's compensated cross product
+        // (euclidean_space/vector3.h:151-155, util/math.h:167-173): the alias-table layout depends on the
+        // ORDER of nearly equal light powers, so the area must round the way the reference's does
+        auto dop = [](float a, float b, float c, float d) {
+            const float cd = c * d;
+            const float diff = std::fma(a, b, -cd);
+            const float err = std::fma(-c, d, cd);
+            return diff + err;
+        };
         const float e1[3] = {o.p1[0] - o.p0[0], o.p1[1] - o.p0[1], o.p1[2] - o.p0[2]};
         const float e2[3] = {o.p2[0] - o.p0[0], o.p2[1] - o.p0[1], o.p2[2] - o.p0[2]};
-        const float cx = e1[1] * e2[2] - e1[2] * e2[1], cy = e1[2] * e2[0] - e1[0] * e2[2], cz = e1[0] * e2[1] - e1[1] * e2[0];
-        o.area = 0.5f * std::sqrt(cx * cx + cy * cy + cz * cz);
-        o.pad[0] = o.pad[1] = 0;
+        const float cx = dop(e1[1], e2[2], e1[2], e2[1]), cy = dop(e1[2], e2[0], e1[0], e2[2]), cz = dop(e1[0], e2[1], e1[1], e2[0]);
+        o.area = std::sqrt(cx * cx + cy * cy + cz * cz) * 0.5f;
+        o.prim = l.triangle;
+        o.pad = 0;
     }
     if ((rc = dev_upload(r, &r->d_lights, lights.data(), lights.size(), st))) return rc;
     if (desc->n_lights > 0) {
@@ -306,13 +318,28 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
         std::vector<float> w(desc->n_lights);
         if ((rc = dev_upload(r, &d_w, w.data(), w.size(), st))) return rc;
         SpectrumTable tab{r->d_spec, r->d_spec_pool, r->d_illuminant};
-        k_light_power<<<(desc->n_lights + 127) / 128, 128, 0, st>>>(tab, r->d_lights, desc->n_lights, d_w);
+        // SampledWavelengths::sample_visible(0.5f) with the host's atanhf / coshf, as the reference's host
+        // constructor computes it (spectrum_util/sampled_wavelengths.h:62-78, util/sampling.h:296-307)
+        float hl[4], hp[4];
+        for (int i = 0; i < 4; i++) {
+            float up = 0.5f + float(i) / 4;
+            if (up > 1) up -= 1;
+            hl[i] = 538 - 138.888889f * std::atanh(0.85691062f - 1.82750197f * up);
+            const float c = std::cosh(0.0072f * (hl[i] - 538));
+            hp[i] = (hl[i] < 360 || hl[i] > 830) ? 0.f : 0.0039398042f / (c * c);
+        }
+        k_light_power<<<(desc->n_lights + 127) / 128, 128, 0, st>>>(tab, r->d_lights, desc->n_lights, make_float4(hl[0], hl[1], hl[2], hl[3]),
+                                                                  make_float4(hp[0], hp[1], hp[2], hp[3]), d_w);
         CU_TRY(cudaMemcpyAsync(w.data(), d_w, w.size() * 4, cudaMemcpyDeviceToHost, st));
         CU_TRY(cudaStreamSynchronize(st));
         std::vector<AliasBin> bins;
         std::vector<float> pdfs;
         build_alias(w, bins, pdfs);
         for (int i = 0; i < desc->n_lights; i++) lights[i].pmf = pdfs[i];
+        if (getenv("B200PT_DEBUG_LIGHTS"))
+            for (int i = 0; i < desc->n_lights && i < 64; i++)
+                fprintf(stderr, "[lightdbg] %d weight %.9g pdf %.9g bin p %.9g first %d second %d\n", i, (double)w[i], (double)pdfs[i],
+                        (double)bins[i].p, bins[i].first, bins[i].second);
         CU_TRY(cudaMemcpyAsync(r->d_lights, lights.data(), lights.size() * sizeof(LightRec), cudaMemcpyHostToDevice, st));
         if ((rc = dev_upload(r, &r->d_alias, bins.data(), bins.size(), st))) return rc;
         CU_TRY(cudaStreamSynchronize(st));
@@ -817,7 +844,7 @@ __global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf, int cur) {
                                 const V3 sd = pt - pf;
                                 shadow = true;
                                 sh_o = make_float4(pf.x, pf.y, pf.z, 1.f);
-                                sh_d = make_float4(sd.x, sd.y, sd.z, 0.f);
+                                sh_d = make_float4(sd.x, sd.y, sd.z, __int_as_float(Lr.prim)); // .w: primitive to skip
                                 sh_c = beta * Ld;
                             }
                         }

@@ -184,6 +184,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf, int cur) {
     int sp = 0;
     float ht = 0, hb1 = 0, hb2 = 0;
     int hprim = -1;
+    int skip_prim = -1; // SHADOW: the sampled light's own triangle (the reference's three visibility rays cannot reach it)
     unsigned overflow = 0;
 
     while (true) {
@@ -203,6 +204,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf, int cur) {
                     if (SHADOW) {
                         ro = __ldg(wf.q.sh_o + r);
                         rd = __ldg(wf.q.sh_d + r);
+                        skip_prim = __float_as_int(rd.w);
                     } else {
                         slot = __ldg(queue + r);
                         ro = wf.pool.ray_o[slot];
@@ -245,7 +247,8 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf, int cur) {
                 const float4 *tp = wf.bvh.tris + 3 * size_t(tg.x + ti);
                 const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                 TriHit th;
-                if (intersect_triangle(ox, oy, oz, dx, dy, dz, ht, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, th)) {
+                if ((!SHADOW || __float_as_int(v0.w) != skip_prim) &&
+                    intersect_triangle(ox, oy, oz, dx, dy, dz, ht, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, th)) {
                     ht = th.t;
                     hb1 = th.b1;
                     hb2 = th.b2;

@@ -109,64 +109,120 @@ def p_str(p, name, default):
 
 
 # ---------------------------------------------------------------------------------- transforms
+# The reference's Transform carries (m, inv_m) and multiplies both (euclidean_space/transform.h:245-252)
+# with an fp32 FMA chain per element (euclidean_space/squared_matrix.h:98-109).  The same is done here,
+# operation for operation: vertex bits decide the order of nearly equal light areas (alias-table layout).
+def _mm(a, b):
+    r = np.zeros((4, 4), dtype=F32)
+    for k in range(4):
+        r = (a[:, k:k + 1].astype(np.float64) * b[k:k + 1, :].astype(np.float64) + r.astype(np.float64)).astype(F32)
+    return r
+
+
+class Xf:
+    def __init__(self, m, inv_m=None):
+        self.m = np.asarray(m, dtype=F32).reshape(4, 4).copy()
+        self.inv = (np.linalg.inv(self.m.astype(np.float64)).astype(F32) if inv_m is None else np.asarray(inv_m, dtype=F32).reshape(4, 4).copy())
+
+    def __mul__(self, o):
+        return Xf(_mm(self.m, o.m), _mm(o.inv, self.inv))
+
+    def inverse(self):
+        return Xf(self.inv, self.m)
+
+    def copy(self):
+        return Xf(self.m, self.inv)
+
+    def is_identity(self):
+        return np.array_equal(self.m, np.eye(4, dtype=F32)) and np.array_equal(self.inv, self.m)
+
+
+def identity():
+    return Xf(np.eye(4, dtype=F32), np.eye(4, dtype=F32))
+
+
 def _m(rows):
     return np.array(rows, dtype=F32)
 
 
 def translate(x, y, z):
-    return _m([[1, 0, 0, x], [0, 1, 0, y], [0, 0, 1, z], [0, 0, 0, 1]])
+    x, y, z = F32(x), F32(y), F32(z)
+    return Xf(_m([[1, 0, 0, x], [0, 1, 0, y], [0, 0, 1, z], [0, 0, 0, 1]]), _m([[1, 0, 0, -x], [0, 1, 0, -y], [0, 0, 1, -z], [0, 0, 0, 1]]))
 
 
 def scale(x, y, z):
-    return _m([[x, 0, 0, 0], [0, y, 0, 0], [0, 0, z, 0], [0, 0, 0, 1]])
+    x, y, z = F32(x), F32(y), F32(z)
+    return Xf(_m([[x, 0, 0, 0], [0, y, 0, 0], [0, 0, z, 0], [0, 0, 0, 1]]),
+              _m([[F32(1) / x, 0, 0, 0], [0, F32(1) / y, 0, 0], [0, 0, F32(1) / z, 0], [0, 0, 0, 1]]))
 
 
 def rotate(theta_deg, ax):
-    a = np.asarray(ax, dtype=np.float64)
-    a = a / np.linalg.norm(a)
-    s, c = math.sin(math.radians(theta_deg)), math.cos(math.radians(theta_deg))
+    """Transform::rotate (euclidean_space/transform.h:62-89): fp32 sin/cos of an fp32 angle, elements
+    evaluated in double (the 1.0 literals promote) and stored as fp32; inverse = transpose."""
+    theta = F32(np.float64(F32(np.pi)) / 180.0 * np.float64(F32(theta_deg)))
+    s, c = np.float64(F32(np.sin(np.float64(theta)))), np.float64(F32(np.cos(np.float64(theta))))
+    a = np.asarray(ax, dtype=F32)
+    ln = F32(np.sqrt(F32(F32(a[0] * a[0]) + F32(a[1] * a[1])) + F32(a[2] * a[2])))
+    a = (a / ln).astype(F32)
     x, y, z = a
-    return _m([[x * x + (1 - x * x) * c, x * y * (1 - c) - z * s, x * z * (1 - c) + y * s, 0],
-               [x * y * (1 - c) + z * s, y * y + (1 - y * y) * c, y * z * (1 - c) - x * s, 0],
-               [x * z * (1 - c) - y * s, y * z * (1 - c) + x * s, z * z + (1 - z * z) * c, 0], [0, 0, 0, 1]])
+    xx, yy, zz = np.float64(F32(x * x)), np.float64(F32(y * y)), np.float64(F32(z * z))
+    xy, xz, yz = np.float64(F32(x * y)), np.float64(F32(x * z)), np.float64(F32(y * z))
+    x64, y64, z64 = np.float64(x), np.float64(y), np.float64(z)
+    m = _m([[xx + (1.0 - xx) * c, xy * (1.0 - c) - z64 * s, xz * (1.0 - c) + y64 * s, 0],
+            [xy * (1.0 - c) + z64 * s, yy + (1.0 - yy) * c, yz * (1.0 - c) - x64 * s, 0],
+            [xz * (1.0 - c) - y64 * s, yz * (1.0 - c) + x64 * s, zz + (1.0 - zz) * c, 0], [0, 0, 0, 1]])
+    return Xf(m, m.T)
 
 
 def lookat(pos, look, up):
-    """euclidean_space/transform.h lookat: camera_from_world (inverse of the world_from_camera frame)."""
+    """Transform::lookat (euclidean_space/transform.h:172-207): Transform(inverse(world_from_camera), world_from_camera)."""
     pos, look, up = (np.asarray(v, dtype=F32) for v in (pos, look, up))
-    d = look - pos
-    d = d / F32(np.linalg.norm(d))
-    upn = up / F32(np.linalg.norm(up))
-    right = np.cross(upn, d)
+
+    def norm(v):
+        return (v / F32(np.sqrt(F32(F32(v[0] * v[0]) + F32(v[1] * v[1])) + F32(v[2] * v[2])))).astype(F32)
+
+    d = norm((look - pos).astype(F32))
+    right = np.cross(norm(up).astype(np.float64), d.astype(np.float64)).astype(F32)
     if np.linalg.norm(right) == 0:
         raise SceneError("LookAt: up vector and viewing direction are parallel")
-    right = (right / np.linalg.norm(right)).astype(F32)
-    new_up = np.cross(d, right).astype(F32)
+    right = norm(right)
+    new_up = np.cross(d.astype(np.float64), right.astype(np.float64)).astype(F32)
     wfc = np.eye(4, dtype=F32)
     wfc[:3, 0], wfc[:3, 1], wfc[:3, 2], wfc[:3, 3] = right, new_up, d, pos
-    return inv(wfc)
-
-
-def inv(m):
-    return np.linalg.inv(m.astype(np.float64)).astype(F32)
+    return Xf(np.linalg.inv(wfc.astype(np.float64)).astype(F32), wfc)
 
 
 def perspective(fov, n, f):
-    persp = _m([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, f / (f - n), -f * n / (f - n)], [0, 0, 1, 0]])
-    it = 1.0 / math.tan(math.radians(fov) / 2.0)
-    return scale(it, it, 1.0) @ persp
+    n, f = F32(n), F32(f)
+    persp = Xf(_m([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, f / (f - n), -f * n / (f - n)], [0, 0, 1, 0]]))
+    it = 1.0 / math.tan(float(F32(np.float64(F32(np.pi)) / 180.0 * fov)) / 2.0)
+    return scale(it, it, 1.0) * persp
+
+
+def _fma32(a, b, c):
+    """fp32 fused multiply-add emulated in fp64 (the 48-bit product is exact; one rounding to 53 bits
+    before the final rounding to 24 is the only difference from a hardware FMA, and it is vanishingly rare)."""
+    return (np.asarray(a, np.float64) * np.asarray(b, np.float64) + np.asarray(c, np.float64)).astype(F32)
 
 
 def xf_points(m, P):
-    """Transform::operator()(Point3f): m00 x + m01 y + m02 z + m03 in fp32, left to right."""
+    """Transform::operator()(Point3f) as the reference's gpu_transform<Point3f> kernel evaluates it on the
+    device (shapes/triangle_mesh.cu:7-18; sm_100 SASS: FMUL m1*y, FFMA m0*x, FFMA m2*z, FADD m3), so mesh
+    vertices get the same bits -- the alias-table layout depends on the order of nearly equal light areas."""
     P = np.asarray(P, dtype=F32).reshape(-1, 3)
+    m = np.asarray(m, dtype=F32)
     x, y, z = P[:, 0], P[:, 1], P[:, 2]
-    out = np.empty_like(P)
-    for r in range(3):
-        out[:, r] = ((m[r, 0] * x + m[r, 1] * y) + m[r, 2] * z) + m[r, 3]
-    w = ((m[3, 0] * x + m[3, 1] * y) + m[3, 2] * z) + m[3, 3]
+
+    def row(r):
+        t = (m[r, 1] * y).astype(F32)
+        t = _fma32(m[r, 0], x, t)
+        t = _fma32(m[r, 2], z, t)
+        return (t + m[r, 3]).astype(F32)
+
+    out = np.stack([row(0), row(1), row(2)], axis=1)
+    w = row(3)
     if not np.all(w == 1):
-        out = out / w[:, None]
+        out = (out / w[:, None]).astype(F32)
     return out.astype(F32)
 
 
@@ -493,7 +549,7 @@ class Scene:
 # ------------------------------------------------------------------------------------ parsing
 class _GState:
     def __init__(self):
-        self.ctm = np.eye(4, dtype=F32)
+        self.ctm = identity()
         self.reverse_orientation = False
         self.material = 0
         self.area_light = None
@@ -514,7 +570,7 @@ def load(path=None, text=None, spp=None, integrator=None):
     named_cs, named_mat = {}, {}
     pre = {"Camera": None, "Film": None, "PixelFilter": None, "Sampler": None, "Integrator": None}
     cam_ctm = None
-    render_from_world = np.eye(4, dtype=F32)
+    render_from_world = identity()
     sc.add_material("diffuse", {}, scene_dir)   # default material = diffuse 0.5 (scene_builder.cu:140-141)
 
     def directives(txt, base):
@@ -536,23 +592,25 @@ def load(path=None, text=None, spp=None, integrator=None):
         if pre["Camera"] is None or pre["Camera"][0] != "perspective":
             raise SceneError("Camera 'perspective' is required")
         cp = params_of(pre["Camera"][1:])
-        world_from_camera = inv(cam_ctm)
+        world_from_camera = cam_ctm.inverse()
         named_cs["camera"] = world_from_camera
-        pos = xf_points(world_from_camera, [[0, 0, 0]])[0]
+        pos = xf_points(world_from_camera.m, [[0, 0, 0]])[0]
         world_from_render = translate(*pos)            # CameraWorldCoordSystem (cameras/camera_base.h:34-39)
-        render_from_world = inv(world_from_render)
-        rfc = (render_from_world @ world_from_camera).astype(F32)
+        render_from_world = world_from_render.inverse()
+        rfc = (render_from_world * world_from_camera).m
         W, H = sc.film["width"], sc.film["height"]
         aspect = F32(W) / F32(H)
         if aspect > 1:
             smin, smax = (-aspect, -1.0), (aspect, 1.0)
         else:
             smin, smax = (-1.0, -1.0 / aspect), (1.0, 1.0 / aspect)
-        ndc_from_screen = scale(1.0 / (smax[0] - smin[0]), 1.0 / (smax[1] - smin[1]), 1.0) @ translate(-smin[0], -smax[1], 0.0)
+        ndc_from_screen = scale(1.0 / (smax[0] - smin[0]), 1.0 / (smax[1] - smin[1]), 1.0) * translate(-smin[0], -smax[1], 0.0)
         raster_from_ndc = scale(W, -H, 1.0)
-        raster_from_screen = (raster_from_ndc @ ndc_from_screen).astype(F32)
+        raster_from_screen = raster_from_ndc * ndc_from_screen
         screen_from_camera = perspective(p_float(cp, "fov", 90.0), 1e-2, 1000.0)
-        cfr = (inv(screen_from_camera) @ inv(raster_from_screen)).astype(F32)
+        # Transform::inverse() of a product swaps (m, inv_m); raster_from_screen.inverse() is numeric in the
+        # reference too (SquareMatrix::inverse); cameras/perspective.cu:34-40
+        cfr = (screen_from_camera.inverse() * Xf(raster_from_screen.m).inverse()).m
         sc.camera = {"cfr": cfr, "rfc": rfc, "lens_radius": p_float(cp, "lensradius", 0.0),
                      "focal_distance": p_float(cp, "focaldistance", 1e6)}
         sp = pre["Sampler"]
@@ -573,26 +631,26 @@ def load(path=None, text=None, spp=None, integrator=None):
             pre[kw] = args
         elif kw == "WorldBegin":
             world_begin()
-            g.ctm = np.eye(4, dtype=F32)
+            g.ctm = identity()
             named_cs["world"] = g.ctm.copy()
         elif kw == "AttributeBegin":
             stack.append(g.copy())
         elif kw == "AttributeEnd":
             g = stack.pop()
         elif kw == "Identity":
-            g.ctm = np.eye(4, dtype=F32)
+            g.ctm = identity()
         elif kw == "Translate":
-            g.ctm = (g.ctm @ translate(*args[:3])).astype(F32)
+            g.ctm = g.ctm * translate(*args[:3])
         elif kw == "Scale":
-            g.ctm = (g.ctm @ scale(*args[:3])).astype(F32)
+            g.ctm = g.ctm * scale(*args[:3])
         elif kw == "Rotate":
-            g.ctm = (g.ctm @ rotate(args[0], args[1:4])).astype(F32)
+            g.ctm = g.ctm * rotate(args[0], args[1:4])
         elif kw == "LookAt":
-            g.ctm = (g.ctm @ lookat(args[0:3], args[3:6], args[6:9])).astype(F32)
+            g.ctm = g.ctm * lookat(args[0:3], args[3:6], args[6:9])
         elif kw == "Transform":
-            g.ctm = np.array(args[0], dtype=F32).reshape(4, 4).T.copy()
+            g.ctm = Xf(np.array(args[0], dtype=F32).reshape(4, 4).T)
         elif kw == "ConcatTransform":
-            g.ctm = (g.ctm @ np.array(args[0], dtype=F32).reshape(4, 4).T).astype(F32)
+            g.ctm = g.ctm * Xf(np.array(args[0], dtype=F32).reshape(4, 4).T)
         elif kw == "CoordSysTransform":
             if args[0] in named_cs:
                 g.ctm = named_cs[args[0]].copy()
@@ -613,7 +671,8 @@ def load(path=None, text=None, spp=None, integrator=None):
             g.area_light = params_of(args[1:])
         elif kw == "Shape":
             p = params_of(args[1:])
-            rfo = (render_from_world @ g.ctm).astype(F32)
+            rfo_x = render_from_world * g.ctm
+            rfo = rfo_x.m
             flip = g.reverse_orientation ^ swaps_handedness(rfo)
             if args[0] in ("trianglemesh", "plymesh"):
                 if args[0] == "plymesh":
@@ -621,14 +680,14 @@ def load(path=None, text=None, spp=None, integrator=None):
                 else:
                     P = np.array(p["P"][1], dtype=F32).reshape(-1, 3)
                     idx = np.array(p["indices"][1], dtype=np.int32).reshape(-1, 3) if "indices" in p else np.array([[0, 1, 2]], np.int32)
-                is_identity = np.array_equal(rfo, np.eye(4, dtype=F32))
+                is_identity = rfo_x.is_identity()
                 Pr = P if is_identity else xf_points(rfo, P)   # shapes/triangle_mesh.cu:49-78
                 sc.add_mesh(Pr, idx, g.material, flip, g.area_light, scene_dir)
             elif args[0] == "sphere":
                 if g.area_light is not None:
                     raise SceneError("emissive spheres are outside the hot path")
                 r = p_float(p, "radius", 1.0)
-                sc.spheres.append({"rfo": rfo, "ofr": inv(rfo), "radius": r, "zmin": p_float(p, "zmin", -r), "zmax": p_float(p, "zmax", r),
+                sc.spheres.append({"rfo": rfo, "ofr": rfo_x.inv, "radius": r, "zmin": p_float(p, "zmin", -r), "zmax": p_float(p, "zmax", r),
                                    "phimax": math.radians(min(max(p_float(p, "phimax", 360.0), 0.0), 360.0)),
                                    "ro": g.reverse_orientation, "swaps": swaps_handedness(rfo), "material": g.material})
             else:

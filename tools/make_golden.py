@@ -1,0 +1,60 @@
+#!/usr/bin/env python3
+"""Generate golden films with the REFERENCE's own CUDA build (oracle/_ref/pbrt-minus-ref, float film
+dump) on the GPU box: python tools/make_golden.py  -> gpurun_out/golden/*.f32 + manifest.json.
+The outputs are then committed under tests/golden/ (this script is how they were made)."""
+import json
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+from render_compare import with_resolution  # noqa: E402
+
+CASES = [
+    # name, scene, (W, H) or None, spp, integrator, sampler override
+    ("cornell_64_16spp", "cornell-box-specular.pbrt", (64, 64), 16, None, None),
+    ("cornell_48_4096spp", "cornell-box-specular.pbrt", (48, 48), 4096, None, None),
+    ("cornell_48_4096spp_megakernel", "cornell-box-specular.pbrt", (48, 48), 4096, "megakernelpath", None),
+    ("cornell_64_9spp_independent", "cornell-box-specular.pbrt", (64, 64), 9, None, "independent"),
+    ("materials_96x64_64spp", "materials.pbrt", None, 64, None, None),
+    ("materials_96x64_1024spp", "materials.pbrt", None, 1024, None, None),
+]
+
+
+def main():
+    out = os.path.join(ROOT, "gpurun_out", "golden")
+    os.makedirs(out, exist_ok=True)
+    exe = os.path.join(ROOT, "oracle", "_ref", "pbrt-minus-ref")
+    manifest = {}
+    for name, scene, res, spp, integ, sampler in CASES:
+        text = open(os.path.join(ROOT, "tests", "scenes", scene)).read()
+        if res:
+            text = with_resolution(text, *res)
+        if sampler:
+            text = text.replace("WorldBegin", 'Sampler "%s"\nWorldBegin' % sampler, 1)
+        sp = os.path.join(out, name + ".pbrt")
+        open(sp, "w").write(text)
+        png = os.path.join(out, name + ".png")
+        cmd = [exe, sp, "--spp", str(spp), "--outfile", png] + (["--integrator", integ] if integ else [])
+        r = subprocess.run(cmd, capture_output=True, text=True, cwd=out, timeout=3000)
+        if r.returncode != 0 or not os.path.exists(png + ".f32"):
+            print(name, "FAILED", (r.stdout + r.stderr)[-400:])
+            continue
+        m = re.search(r'xresolution"\s*\[\s*(\d+)', text)
+        n = re.search(r'yresolution"\s*\[\s*(\d+)', text)
+        W, H = int(m.group(1)), int(n.group(1))
+        film = np.fromfile(png + ".f32", dtype=np.float32).reshape(H, W, 3)
+        os.replace(png + ".f32", os.path.join(out, name + ".f32"))
+        took = re.search(r"rendering took\s+([0-9.]+)", r.stdout)
+        manifest[name] = {"scene": scene, "width": W, "height": H, "spp": spp, "integrator": integ or "path", "sampler": sampler or "stratified",
+                          "mean": float(film.mean()), "reference_render_s": float(took.group(1)) if took else None}
+        print(name, manifest[name])
+    json.dump(manifest, open(os.path.join(out, "manifest.json"), "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
