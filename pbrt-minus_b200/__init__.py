@@ -6,6 +6,6 @@ fallback: importing works anywhere, but every compute call needs the built libra
 """
 from . import api  # noqa: F401
 from .api import B200ptError, load_library  # noqa: F401
-from .scene import HLBVH, DeviceBuffer, Film, WavefrontPathIntegrator  # noqa: F401
+from .scene import HLBVH, DeviceBuffer, Film, WavefrontPathIntegrator, sample_range  # noqa: F401
 from . import pbrt_scene, spectral  # noqa: F401
 from . import workloads  # noqa: F401

@@ -247,3 +247,11 @@ class WavefrontPathIntegrator:
 
     def close(self):
         self.accel.close()
+
+
+def sample_range(spp, rank, world):
+    """Sample-index sharding: rank r of G renders sample_idx in [r*spp/G, (r+1)*spp/G) of every
+    pixel, with the sampler configured for the TOTAL spp so strata stay global.  Ranges tile [0, spp)."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("bad rank %d of %d" % (rank, world))
+    return (rank * spp) // world, ((rank + 1) * spp) // world
