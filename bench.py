@@ -40,6 +40,7 @@ def parse_args():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-render", action="store_true", help="skip the extra config-C1 render line item")
     ap.add_argument("--cpu-rays", type=int, default=96, help="rays of the bounded CPU-oracle sample")
     return ap.parse_args()
 
@@ -103,6 +104,52 @@ def scene_P(scene):
 
 def scene_idx(scene):
     return scene._keep[2]
+
+
+CORNELL = os.path.join(ROOT, "tests", "scenes", "cornell-box-specular.pbrt")
+
+
+def render_c1_ours(pkg, local, rank, world, spp=16):
+    """config C1 (cornell-box-specular, 1080x1080, 16 spp per GPU) through WavefrontPathIntegrator.render:
+    an extra line item beside the C2 headline.  N > 1: sample-index sharding, spp_total = 16 * N when that is a
+    perfect square (stratified sampler), else the ranks render the same 16-sample image independently."""
+    total = spp * world
+    r = int(round(total ** 0.5))
+    sharded = r * r == total
+    sc = pkg.pbrt_scene.load(CORNELL, spp=total if sharded else spp)
+    integ = pkg.WavefrontPathIntegrator(sc, device=local)
+    film = integ.create_film()
+    b, e = pkg.sample_range(total, rank, world) if sharded else (0, spp)
+    integ.render(film, sample_begin=b, sample_end=e)      # warm-up
+    film.clear()
+    st = integ.render(film, sample_begin=b, sample_end=e)
+    img = film.get_pixel_rgb()
+    out = {"scene": "cornell-box-specular.pbrt 1080x1080", "spp_per_gpu": e - b, "ms": round(st["ms_total"], 3),
+           "Msamples_s_per_gpu": round(st["paths"] / st["ms_total"] / 1e3, 2),
+           "Mrays_s_per_gpu": round((st["rays_closest"] + st["rays_shadow"]) / st["ms_total"] / 1e3, 1),
+           "passes": st["passes"], "kernel_launches": st["kernel_launches"], "mean_rgb": [round(float(v), 6) for v in img.reshape(-1, 3).mean(0)]}
+    film.close()
+    integ.close()
+    return out
+
+
+def render_c1_reference(td, spp=16):
+    """the reference's own CLI (oracle/_ref/pbrt-minus-ref, unmodified hot path) on the same scene"""
+    import re
+    exe = os.path.join(ROOT, "oracle", "_ref", "pbrt-minus-ref")
+    if not os.path.exists(exe):
+        return {"unavailable": "oracle/_ref/pbrt-minus-ref not prebuilt"}
+    t0 = time.time()
+    r = subprocess.run([exe, CORNELL, "--spp", str(spp), "--outfile", os.path.join(td, "ref.png")], capture_output=True, text=True,
+                       timeout=3000, cwd=td)
+    wall = time.time() - t0
+    if r.returncode != 0:
+        return {"unavailable": (r.stdout + r.stderr)[-200:].replace("\n", " ")}
+    m = re.search(r"rendering took\s+([0-9.]+)", r.stdout)
+    bvh = re.search(r"BVH building:[^\n]*", r.stdout)
+    sec = float(m.group(1)) if m else None
+    return {"scene": "cornell-box-specular.pbrt 1080x1080", "spp": spp, "render_s": sec, "wall_s": round(wall, 2),
+            "Msamples_s": round(1080 * 1080 * spp / sec / 1e6, 2) if sec else None, "bvh_line": bvh.group(0) if bvh else None}
 
 
 def run_ours(args):
@@ -270,6 +317,14 @@ def run_ours(args):
         "bvh_build": {k2: (round(v, 3) if isinstance(v, float) else v) for k2, v in build.items()},
         "setup_s": {"generate": round(t_gen, 2), "upload": round(t_upload, 2)},
     }
+    if not args.no_render:
+        rc1 = render_c1_ours(pkg, local, rank, world)
+        if world > 1:
+            tt = torch.tensor([rc1["ms"]], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            rc1["ms_max_over_ranks"] = round(float(tt.item()), 3)
+            rc1["Msamples_s_job"] = round(1080 * 1080 * rc1["spp_per_gpu"] * world / float(tt.item()) / 1e3, 2)
+        out["render_c1"] = rc1
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(args, P, idx, sets)
     if rank == 0:
@@ -337,6 +392,7 @@ def run_reference(args):
                             "closest:%s:-" % os.path.join(td, "primary.rays"), "closest:%s:-" % os.path.join(td, "bounce.rays"),
                             "any:%s:-" % os.path.join(td, "shadow.rays")], capture_output=True, text=True, timeout=3000)
         wall = time.time() - t0
+        ref_render = None if args.no_render else render_c1_reference(td)
     if r.returncode != 0:
         base["unavailable"] = "ref_trace failed: " + (r.stdout + r.stderr)[-300:].replace("\n", " ")
         print(json.dumps(base))
@@ -359,6 +415,7 @@ def run_reference(args):
         "per_set_ms": {n: round(s["ms"], 3) for n, s in zip(("primary", "bounce", "shadow"), info["sets"])},
         "reference_bvh_build_s": info["bvh_build_s"], "reference_load_s": info["load_s"],
         "reference_build_line": build_line[-1] if build_line else None, "wall_s": round(wall, 1),
+        "render_c1": ref_render,
     })
     print(json.dumps(base))
 

@@ -442,10 +442,8 @@ __device__ __forceinline__ Sampler load_sampler(const WF &wf, int slot, const in
     return s;
 }
 
-__global__ void k_pass_begin(WF wf, int cur) {
+__global__ void k_pass_begin(WF wf) {
     WFCounters *c = wf.c;
-    c->rays_closest += c->n_rays[cur];
-    c->n_rays[cur ^ 1] = 0;
     c->n_mat[0] = c->n_mat[1] = c->n_mat[2] = 0;
     c->n_shadow = 0;
     c->ticket_closest = 0;
@@ -457,7 +455,10 @@ __global__ void k_pass_end(WF wf) { wf.c->rays_shadow += wf.c->n_shadow; }
 
 __global__ void k_init_pool(WF wf) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < wf.pool_size) wf.q.free_slots[i] = i;
+    if (i < wf.pool_size) {
+        wf.q.free_slots[i] = i;
+        wf.pool.state[i] = ST_IDLE;
+    }
     if (i == 0) {
         WFCounters z = {};
         z.n_free = (unsigned)wf.pool_size;
@@ -466,7 +467,7 @@ __global__ void k_init_pool(WF wf) {
 }
 
 // ---- gpu_generate_new_path (integrators/wavefront_path.cu:245-287)
-__global__ void __launch_bounds__(WF_BLOCK) k_generate(WF wf, int cur) {
+__global__ void __launch_bounds__(WF_BLOCK) k_generate(WF wf) {
     const unsigned n = wf.c->n_free;
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned n_round = (n + 31u) & ~31u;
@@ -480,9 +481,9 @@ __global__ void __launch_bounds__(WF_BLOCK) k_generate(WF wf, int cur) {
         base = __shfl_sync(0xffffffffu, base, 0);
         const long long id = (long long)base + __popc(m & ((1u << lane) - 1u));
         const bool live = have_slot && id < wf.total_paths;
-        int slot = -1;
+        if (have_slot && !live) wf.pool.state[wf.q.free_slots[i]] = ST_IDLE; // no paths left: the slot retires
         if (live) {
-            slot = wf.q.free_slots[i];
+            const int slot = wf.q.free_slots[i];
             const int pixel = int(id % wf.n_pixels);
             const int sample = wf.sample_begin + int(id / wf.n_pixels);
             const int px = pixel % wf.film.width, py = pixel / wf.film.width;
@@ -530,8 +531,8 @@ __global__ void __launch_bounds__(WF_BLOCK) k_generate(WF wf, int cur) {
             wf.pool.rng[slot] = s.state;
             // depth 0, next_time_russian_roulette = 8 (util/russian_roulette.h:5)
             wf.pool.ids[slot] = make_int4(pixel, sample, s.dimension, 8 << 16);
+            wf.pool.state[slot] = ST_RAY;
         }
-        queue_push(&wf.c->n_rays[cur ^ 1], wf.q.rays[cur ^ 1], slot, live);
     }
 }
 
@@ -560,17 +561,20 @@ __device__ __forceinline__ V3 tri_normal(V3 p0, V3 p1, V3 p2, bool flip) {
 }
 
 // ---- control_logic (integrators/wavefront_path.cu:68-214)
-__global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf, int cur) {
-    const unsigned n = wf.c->n_rays[cur];
+__global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf) {
+    // one thread per pool slot, in slot order: every lane access below is a coalesced 16-byte gather
+    const unsigned n = (unsigned)wf.pool_size;
     const unsigned stride = gridDim.x * blockDim.x;
-    const unsigned n_round = (n + 31u) & ~31u;
+    const unsigned n_round = (n + WF_BLOCK - 1u) / WF_BLOCK * WF_BLOCK;
     unsigned n_finished = 0;
+    unsigned *const counters[4] = {&wf.c->n_mat[0], &wf.c->n_mat[1], &wf.c->n_mat[2], &wf.c->n_free};
+    int32_t *const queues[4] = {wf.q.mat[0], wf.q.mat[1], wf.q.mat[2], wf.q.free_slots};
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
-        const bool act = i < n;
-        int slot = -1, route = -1; // route: material type, or -1
+        const bool act = i < n && wf.pool.state[i] == ST_RAY;
+        const int slot = (int)i;
+        int route = -1; // route: material type, or -1
         bool terminate = false;
         if (act) {
-            slot = wf.q.rays[cur][i];
             int4 ids = wf.pool.ids[slot];
             int depth = (ids.w >> 8) & 0xff, next_rr = (ids.w >> 16) & 0xff;
             S4 beta = wf.pool.beta[slot];
@@ -641,10 +645,9 @@ __global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf, int cur) {
                 wf.pool.ids[slot] = ids;
             }
         }
-        queue_push(&wf.c->n_free, wf.q.free_slots, slot, act && terminate);
-        queue_push(&wf.c->n_mat[0], wf.q.mat[0], slot, route == B200PT_MAT_DIFFUSE);
-        queue_push(&wf.c->n_mat[1], wf.q.mat[1], slot, route == B200PT_MAT_CONDUCTOR);
-        queue_push(&wf.c->n_mat[2], wf.q.mat[2], slot, route == B200PT_MAT_DIELECTRIC);
+        const int cat = (act && terminate) ? 3 : route; // 0..2 material queue, 3 free list, -1 nothing
+        if (act) wf.pool.state[slot] = terminate ? ST_FREE : uint8_t(ST_MAT0 + route);
+        block_push<4>(cat, slot, counters, queues);
     }
     // finished-path count: warp reduce, one atomic per warp
     for (int o = 16; o > 0; o >>= 1) n_finished += __shfl_xor_sync(0xffffffffu, n_finished, o);
@@ -765,7 +768,7 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_DIELECTRIC>(const WF &wf, c
 
 // ---- gpu_evaluate_material + sample_bsdf + sample_Ld_volume, specialised per material
 template <int MAT>
-__global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf, int cur) {
+__global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf) {
     const unsigned n = wf.c->n_mat[MAT];
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned n_round = (n + 31u) & ~31u;
@@ -881,6 +884,7 @@ __global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf, int cur) {
             ids.z = s.dimension;
             wf.pool.ids[slot] = ids;
             wf.pool.rng[slot] = s.state;
+            wf.pool.state[slot] = ST_RAY; // traced and judged by the next pass (dead paths: tmax < 0)
         }
         const int spos = queue_claim(&wf.c->n_shadow, shadow);
         if (spos >= 0) {
@@ -889,7 +893,6 @@ __global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf, int cur) {
             wf.q.sh_contrib[spos] = sh_c;
             wf.q.sh_slot[spos] = slot;
         }
-        queue_push(&wf.c->n_rays[cur ^ 1], wf.q.rays[cur ^ 1], slot, act);
     }
 }
 
@@ -921,15 +924,16 @@ static int ensure_pool(b200pt_scene *s, int pool_size) {
         if ((rc = pool_alloc(r, l, n))) return rc;
     if ((rc = pool_alloc(r, &P.rng, n))) return rc;
     if ((rc = pool_alloc(r, &P.ids, n))) return rc;
+    if ((rc = pool_alloc(r, &P.state, n))) return rc;
     WFQueues &Q = r->q;
-    int32_t **qs[] = {&Q.rays[0], &Q.rays[1], &Q.mat[0], &Q.mat[1], &Q.mat[2], &Q.free_slots, &Q.sh_slot};
+    int32_t **qs[] = {&Q.mat[0], &Q.mat[1], &Q.mat[2], &Q.free_slots, &Q.sh_slot};
     for (int32_t **q : qs)
         if ((rc = pool_alloc(r, q, n))) return rc;
     if ((rc = pool_alloc(r, &Q.sh_o, n))) return rc;
     if ((rc = pool_alloc(r, &Q.sh_d, n))) return rc;
     if ((rc = pool_alloc(r, &Q.sh_contrib, n))) return rc;
     if (!r->d_counters) CU_TRY(cudaMalloc((void **)&r->d_counters, sizeof(WFCounters)));
-    if (!r->h_counters) CU_TRY(cudaMallocHost((void **)&r->h_counters, sizeof(WFCounters)));
+    if (!r->h_counters) CU_TRY(cudaMallocHost((void **)&r->h_counters, 2 * sizeof(WFCounters)));
     r->pool_size = pool_size;
     return B200PT_OK;
 }
@@ -1045,54 +1049,69 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     wf.n_pixels = n_pixels;
 
     cudaStream_t st = s->stream;
-    cudaEvent_t ev0, ev1, ev_poll;
+    cudaEvent_t ev0, ev1, ev_poll[2];
     CU_TRY(cudaEventCreate(&ev0));
     CU_TRY(cudaEventCreate(&ev1));
-    CU_TRY(cudaEventCreateWithFlags(&ev_poll, cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&ev_poll[0], cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&ev_poll[1], cudaEventDisableTiming));
     struct EvGuard {
-        cudaEvent_t a, b, c;
+        cudaEvent_t a, b, c, d;
         ~EvGuard() {
             cudaEventDestroy(a);
             cudaEventDestroy(b);
             cudaEventDestroy(c);
+            cudaEventDestroy(d);
         }
-    } guard{ev0, ev1, ev_poll};
+    } guard{ev0, ev1, ev_poll[0], ev_poll[1]};
 
-    const int grid = s->sm_count * 8; // stage kernels: grid-stride over device-side queue counts
+    const int grid = s->sm_count * 8; // stage kernels: grid-stride over the pool / device-side queue counts
     CU_TRY(cudaEventRecord(ev0, st));
     k_init_pool<<<(pool_size + 255) / 256, 256, 0, st>>>(wf);
     long long passes = 0, launches = 1;
-    int cur = 0;
+    const int batch = 4; // passes enqueued between two looks at the finished-path counter
+    // The only host<->device traffic of the render loop is one 64-byte counter block per batch, read ONE
+    // BATCH LATE: batch k+1 is already enqueued when the host waits for the counters of batch k, so the
+    // GPU never idles on the poll.
+    WFCounters *hc = r->h_counters; // [2], pinned
+    int last = -1;
     bool done = total == 0;
-    const int batch = 8; // passes enqueued between two looks at the finished-path counter
-    while (!done) {
+    for (long long k = 0; !done; k++) {
         for (int b = 0; b < batch; b++) {
-            k_pass_begin<<<1, 1, 0, st>>>(wf, cur);
-            if ((rc = launch_trace_wf(s, wf, cur, false))) return rc;
-            k_logic<<<grid, WF_BLOCK, 0, st>>>(wf, cur);
-            k_generate<<<grid, WF_BLOCK, 0, st>>>(wf, cur);
+            k_pass_begin<<<1, 1, 0, st>>>(wf);
+            if ((rc = launch_trace_wf(s, wf, false))) return rc;
+            k_logic<<<grid, WF_BLOCK, 0, st>>>(wf);
+            k_generate<<<grid, WF_BLOCK, 0, st>>>(wf);
             k_after_generate<<<1, 1, 0, st>>>(wf);
-            k_shade<B200PT_MAT_DIFFUSE><<<grid, WF_BLOCK, 0, st>>>(wf, cur);
-            k_shade<B200PT_MAT_CONDUCTOR><<<grid, WF_BLOCK, 0, st>>>(wf, cur);
-            k_shade<B200PT_MAT_DIELECTRIC><<<grid, WF_BLOCK, 0, st>>>(wf, cur);
-            if ((rc = launch_trace_wf(s, wf, cur, true))) return rc;
+            k_shade<B200PT_MAT_DIFFUSE><<<grid, WF_BLOCK, 0, st>>>(wf);
+            k_shade<B200PT_MAT_CONDUCTOR><<<grid, WF_BLOCK, 0, st>>>(wf);
+            k_shade<B200PT_MAT_DIELECTRIC><<<grid, WF_BLOCK, 0, st>>>(wf);
+            if ((rc = launch_trace_wf(s, wf, true))) return rc;
             k_pass_end<<<1, 1, 0, st>>>(wf);
-            cur ^= 1;
             passes++;
             launches += 10;
         }
         CU_TRY(cudaGetLastError());
-        // the only host<->device traffic of the render loop: one 64-byte counter block per batch
-        CU_TRY(cudaMemcpyAsync(r->h_counters, r->d_counters, sizeof(WFCounters), cudaMemcpyDeviceToHost, st));
-        CU_TRY(cudaEventRecord(ev_poll, st));
-        CU_TRY(cudaEventSynchronize(ev_poll));
-        if (r->h_counters->stack_overflow) {
-            set_error("b200pt_render: traversal stack overflow");
-            return B200PT_ERR_STATE;
+        const int cur = int(k & 1);
+        CU_TRY(cudaMemcpyAsync(&hc[cur], r->d_counters, sizeof(WFCounters), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaEventRecord(ev_poll[cur], st));
+        if (k >= 1) {
+            CU_TRY(cudaEventSynchronize(ev_poll[cur ^ 1]));
+            if (hc[cur ^ 1].stack_overflow) {
+                set_error("b200pt_render: traversal stack overflow");
+                return B200PT_ERR_STATE;
+            }
+            done = (long long)hc[cur ^ 1].finished >= total;
         }
-        done = (long long)r->h_counters->finished >= total;
+        last = cur;
         if (passes > 100000000ll) {
             set_error("b200pt_render: did not terminate");
+            return B200PT_ERR_STATE;
+        }
+    }
+    if (last >= 0) {
+        CU_TRY(cudaEventSynchronize(ev_poll[last]));
+        if ((long long)hc[last].finished < total) { // the look-ahead batch was needed after all
+            set_error("b200pt_render: internal error: %lld of %lld paths finished", (long long)hc[last].finished, total);
             return B200PT_ERR_STATE;
         }
     }
@@ -1102,8 +1121,8 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
         b200pt_render_stats o = {};
         o.paths = total;
         if (total > 0) {
-            o.rays_closest = (int64_t)r->h_counters->rays_closest;
-            o.rays_shadow = (int64_t)r->h_counters->rays_shadow;
+            o.rays_closest = (int64_t)hc[last].rays_closest;
+            o.rays_shadow = (int64_t)hc[last].rays_shadow;
         }
         o.passes = passes;
         o.kernel_launches = launches;

@@ -162,16 +162,18 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
 //                   so the add needs no atomic) -- the reference runs these traversals inline in the
 //                   shading threads (integrators/megakernel_path.cu:217-233, base/integrator_base.cu:12-71).
 template <bool SHADOW>
-__global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf, int cur) {
+__global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
     __shared__ uint2 sm_stack_all[SM_STACK * TRACE_BLOCK];
     uint2 *const sm_stack = sm_stack_all + threadIdx.x;
     uint2 lstack[LOCAL_STACK];
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
     const bool have_tree = wf.bvh.n_nodes > 0;
-    const long long n = SHADOW ? wf.c->n_shadow : wf.c->n_rays[cur];
+    // closest hit: every pool slot in slot order (coalesced gathers), live ones have state ST_RAY;
+    // shadow: the compact shadow queue
+    const long long n = SHADOW ? (long long)wf.c->n_shadow : (long long)wf.pool_size;
     unsigned *const ticket = SHADOW ? &wf.c->ticket_shadow : &wf.c->ticket_closest;
-    const int32_t *const queue = wf.q.rays[cur];
+    unsigned n_live = 0;
     constexpr int REFILL = 4;
     const uint32_t prmt_bias = 0x47000000u;
 
@@ -198,7 +200,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf, int cur) {
             if ((long long)base + n_idle >= n) exhausted = true;
             if (ray < 0) {
                 const long long r = (long long)base + __popc(idle & lt_mask);
-                if (r < n) {
+                if (r < n && (SHADOW || wf.pool.state[r] == ST_RAY)) {
                     ray = r;
                     float4 ro, rd;
                     if (SHADOW) {
@@ -206,9 +208,10 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf, int cur) {
                         rd = __ldg(wf.q.sh_d + r);
                         skip_prim = __float_as_int(rd.w);
                     } else {
-                        slot = __ldg(queue + r);
+                        slot = int(r);
                         ro = wf.pool.ray_o[slot];
                         rd = wf.pool.ray_d[slot];
+                        n_live++;
                     }
                     ox = ro.x; oy = ro.y; oz = ro.z;
                     dx = rd.x; dy = rd.y; dz = rd.z;
@@ -234,7 +237,10 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf, int cur) {
                 }
             }
         }
-        if (__ballot_sync(0xffffffffu, ray >= 0) == 0u) break;
+        if (__ballot_sync(0xffffffffu, ray >= 0) == 0u) {
+            if (exhausted) break;
+            continue; // every fetched slot was inactive: fetch again
+        }
 
         const bool act = ray >= 0;
         const bool want_tri = act && tg.y != 0u;
@@ -303,9 +309,13 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf, int cur) {
         }
     }
     if (overflow) wf.c->stack_overflow = 1u;
+    if (!SHADOW) {
+        for (int o = 16; o > 0; o >>= 1) n_live += __shfl_xor_sync(0xffffffffu, n_live, o);
+        if (lane == 0 && n_live) atomicAdd(&wf.c->rays_closest, (unsigned long long)n_live);
+    }
 }
 
-int launch_trace_wf(b200pt_scene *s, const WF &wf, int cur, bool shadow) {
+int launch_trace_wf(b200pt_scene *s, const WF &wf, bool shadow) {
     static int per_sm[2] = {0, 0};
     if (per_sm[shadow] == 0) {
         int v = 0;
@@ -314,8 +324,8 @@ int launch_trace_wf(b200pt_scene *s, const WF &wf, int cur, bool shadow) {
         per_sm[shadow] = v < 1 ? 1 : v;
     }
     const unsigned blocks = unsigned(s->sm_count * per_sm[shadow]);
-    if (shadow) k_trace_wf<true><<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf, cur);
-    else k_trace_wf<false><<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf, cur);
+    if (shadow) k_trace_wf<true><<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf);
+    else k_trace_wf<false><<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf);
     CU_TRY(cudaGetLastError());
     return B200PT_OK;
 }

@@ -50,6 +50,9 @@ struct FilmRec {
 // bits 8..15 depth, bits 16..23 next_time_russian_roulette
 constexpr int PF_SPECULAR = 1, PF_ANY_NON_SPECULAR = 2;
 
+// per-slot state byte: what the next stage has to do with the slot
+enum : uint8_t { ST_IDLE = 0, ST_RAY = 1, ST_MAT0 = 2 /* + material type */, ST_FREE = 5 };
+
 struct PathPool {
     float4 *ray_o;  // o.xyz, tmax (< 0: dead path, skipped by the trace kernel)
     float4 *ray_d;  // d.xyz, -
@@ -61,10 +64,10 @@ struct PathPool {
     float4 *misc;   // filter_weight, prev_direction_pdf, -, -
     uint64_t *rng;  // PCG32 state (inc is re-derived from the pixel index)
     int4 *ids;      // pixel, sample, sampler dimension, flags
+    uint8_t *state; // ST_*
 };
 
 struct WFCounters {
-    unsigned n_rays[2];
     unsigned n_mat[3];
     unsigned n_free;
     unsigned n_shadow;
@@ -74,7 +77,6 @@ struct WFCounters {
 };
 
 struct WFQueues {
-    int32_t *rays[2];
     int32_t *mat[3];
     int32_t *free_slots;
     // shadow rays: compact SoA by queue position
@@ -130,6 +132,36 @@ __device__ __forceinline__ int queue_claim(unsigned *counter, bool pred) {
     return pred ? int(base + __popc(m & ((1u << lane) - 1u))) : -1;
 }
 
-int launch_trace_wf(b200pt_scene *s, const WF &wf, int cur, bool shadow);
+// block-ordered push into up to NCAT queues: the entries of one 256-slot block land contiguously and in
+// thread (= slot) order, with ONE atomicAdd per block and queue.  cat < 0: nothing to push.  Must be
+// called by every thread of the block (it synchronises); blockDim.x <= 1024.
+template <int NCAT>
+__device__ __forceinline__ void block_push(int cat, int32_t value, unsigned *const *counters, int32_t *const *queues) {
+    __shared__ unsigned s_warp[NCAT][32];
+    __shared__ unsigned s_base[NCAT];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = (blockDim.x + 31) >> 5;
+    unsigned my_ballot = 0;
+#pragma unroll
+    for (int c = 0; c < NCAT; c++) {
+        const unsigned m = __ballot_sync(0xffffffffu, cat == c);
+        if (lane == 0) s_warp[c][warp] = __popc(m);
+        if (cat == c) my_ballot = m;
+    }
+    __syncthreads();
+    if (threadIdx.x < NCAT) {
+        unsigned total = 0;
+        for (int w = 0; w < n_warps; w++) {
+            const unsigned v = s_warp[threadIdx.x][w];
+            s_warp[threadIdx.x][w] = total;
+            total += v;
+        }
+        s_base[threadIdx.x] = total ? atomicAdd(counters[threadIdx.x], total) : 0u;
+    }
+    __syncthreads();
+    if (cat >= 0) queues[cat][s_base[cat] + s_warp[cat][warp] + __popc(my_ballot & ((1u << lane) - 1u))] = value;
+    __syncthreads(); // the shared arrays are reused by the next call
+}
+
+int launch_trace_wf(b200pt_scene *s, const WF &wf, bool shadow);
 
 } // namespace b200pt

@@ -255,3 +255,55 @@ def sample_range(spp, rank, world):
     if world <= 0 or not (0 <= rank < world):
         raise ValueError("bad rank %d of %d" % (rank, world))
     return (rank * spp) // world, ((rank + 1) * spp) // world
+
+
+class NcclComm:
+    """A raw ncclComm_t for b200pt_film_reduce, created next to a torch.distributed process group: rank 0
+    makes the unique id, the group broadcasts its 128 bytes, every rank calls ncclCommInitRank.  NCCL is the
+    copy torch loaded (libnccl.so.2), opened RTLD_GLOBAL so libb200pt.so resolves ncclReduce from it."""
+
+    def __init__(self, rank, world, device):
+        import glob
+        import os
+        import sys
+
+        import torch
+        import torch.distributed as dist
+        cands = []
+        for p in sys.path:
+            cands += glob.glob(os.path.join(p, "nvidia", "nccl", "lib", "libnccl.so*"))
+        cands += ["libnccl.so.2"]
+        self.lib = None
+        for c in cands:
+            try:
+                self.lib = C.CDLL(c, mode=C.RTLD_GLOBAL)
+                break
+            except OSError:
+                continue
+        if self.lib is None:
+            raise api.B200ptError(-5, "libnccl.so.2 not found")
+        uid = (C.c_char * 128)()
+        if rank == 0:
+            rc = self.lib.ncclGetUniqueId(C.byref(uid))
+            if rc != 0:
+                raise api.B200ptError(-5, "ncclGetUniqueId failed: %d" % rc)
+        t = torch.tensor(list(bytes(uid)), dtype=torch.uint8, device="cuda:%d" % device)
+        dist.broadcast(t, src=0)
+        uid = (C.c_char * 128).from_buffer_copy(bytes(t.cpu().tolist()))
+        torch.cuda.set_device(device)
+        self.comm = C.c_void_p()
+
+        class _Uid(C.Structure):
+            _fields_ = [("internal", C.c_char * 128)]
+        u = _Uid()
+        C.memmove(C.byref(u), uid, 128)
+        self.lib.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, _Uid, C.c_int]
+        rc = self.lib.ncclCommInitRank(C.byref(self.comm), int(world), u, int(rank))
+        if rc != 0:
+            raise api.B200ptError(-5, "ncclCommInitRank failed: %d" % rc)
+
+    def close(self):
+        if getattr(self, "comm", None) and self.comm.value:
+            self.lib.ncclCommDestroy.argtypes = [C.c_void_p]
+            self.lib.ncclCommDestroy(self.comm)
+            self.comm = C.c_void_p()
