@@ -96,3 +96,151 @@ def read_hits(path, n):
     raw = np.fromfile(path, dtype=np.int32, count=n)
     t = np.fromfile(path, dtype=np.float32, count=n, offset=4 * n)
     return raw, t
+
+
+# ------------------------------------------------------------------------------------------------
+# C4 "procedural scene": displaced parametric meshes (spheres / tori / terrain patches), mixed
+# diffuse / conductor / dielectric materials, a ceiling grid of small emissive quads for the power
+# light sampler.  Written as one .pbrt + binary little-endian PLY files so that the reference's CLI
+# and this package's front-end read identical bits.
+def _value_noise(u, v, rng, lattice=8, octaves=4):
+    """periodic 2-D value noise on [0,1)^2: seeded lattice values, smoothstep interpolation, `octaves`
+    octaves of halving amplitude; result in about [-1, 1]"""
+    out = np.zeros_like(u, dtype=np.float64)
+    amp, tot = 1.0, 0.0
+    L = lattice
+    for _ in range(octaves):
+        g = rng.random((L, L)) * 2.0 - 1.0
+        x, y = u * L, v * L
+        x0, y0 = np.floor(x).astype(np.int64), np.floor(y).astype(np.int64)
+        fx, fy = x - x0, y - y0
+        fx, fy = fx * fx * (3 - 2 * fx), fy * fy * (3 - 2 * fy)
+        x0, y0 = x0 % L, y0 % L
+        x1, y1 = (x0 + 1) % L, (y0 + 1) % L
+        out += amp * ((g[y0, x0] * (1 - fx) + g[y0, x1] * fx) * (1 - fy) + (g[y1, x0] * (1 - fx) + g[y1, x1] * fx) * fy)
+        tot += amp
+        amp *= 0.5
+        L *= 2
+    return out / tot
+
+
+def _grid_indices(m):
+    """two triangles per cell of an (m+1) x (m+1) vertex grid -> int32 (2*m*m, 3)"""
+    i, j = np.meshgrid(np.arange(m, dtype=np.int64), np.arange(m, dtype=np.int64), indexing="ij")
+    a = (i * (m + 1) + j).reshape(-1)
+    b, c, d = a + 1, a + (m + 1), a + (m + 2)
+    return np.stack([np.stack([a, c, b], 1), np.stack([b, c, d], 1)], 1).reshape(-1, 3).astype(np.int32)
+
+
+def _displaced_mesh(kind, m, centre, size, rng):
+    """(m+1)^2 vertices, 2 m^2 triangles.  kind 0: terrain patch (size x size, height-displaced),
+    1: sphere of radius size/2, 2: torus (major 0.35*size, minor 0.14*size); value-noise displacement
+    along the surface normal"""
+    t = np.linspace(0.0, 1.0, m + 1)
+    u, v = np.meshgrid(t, t, indexing="ij")
+    nz = _value_noise(u % 1.0, v % 1.0, rng)
+    if kind == 0:
+        P = np.stack([(u - 0.5) * size, 0.12 * size * nz, (v - 0.5) * size], -1)
+    elif kind == 1:
+        th, ph = np.pi * v, 2 * np.pi * u
+        r = 0.5 * size * (1.0 + 0.12 * nz * np.sin(th))       # no displacement at the poles (noise is not periodic there)
+        P = np.stack([r * np.sin(th) * np.cos(ph), r * np.cos(th), r * np.sin(th) * np.sin(ph)], -1)
+    else:
+        ph, th = 2 * np.pi * u, 2 * np.pi * v
+        R, r = 0.35 * size, 0.14 * size * (1.0 + 0.25 * nz)
+        P = np.stack([(R + r * np.cos(th)) * np.cos(ph), r * np.sin(th), (R + r * np.cos(th)) * np.sin(ph)], -1)
+    P = P.reshape(-1, 3) + np.asarray(centre, dtype=np.float64)
+    return P.astype(np.float32), _grid_indices(m)
+
+
+def write_ply(path, P, idx):
+    """binary little-endian PLY, float x y z + uchar/int face lists (read by rply in the reference,
+    shapes/tri_quad_mesh.cu, and by pbrt_scene.load_ply here)"""
+    hdr = ("ply\nformat binary_little_endian 1.0\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n"
+           "element face %d\nproperty list uchar int vertex_indices\nend_header\n" % (len(P), len(idx)))
+    rec = np.empty(len(idx), dtype=np.dtype([("n", "u1"), ("v", "<i4", (3,))]))
+    rec["n"] = 3
+    rec["v"] = idx
+    with open(path, "wb") as f:
+        f.write(hdr.encode("ascii"))
+        np.ascontiguousarray(P, dtype="<f4").tofile(f)
+        rec.tofile(f)
+
+
+def procedural_scene(out_dir, n_meshes=48, grid=721, n_light_quads=50000, width=1920, height=1080, seed=7,
+                     light_levels=64, name="c4"):
+    """Writes <out_dir>/<name>.pbrt + mesh PLYs; returns (scene path, dict of counts).
+    Full size (defaults): 48 meshes x 2*721^2 = 49.90 M triangles + 100,000 emissive triangles = 50.0 M,
+    inside a 10 x 4 x 10 box (y up).  Materials round-robin per mesh: diffuse (seeded rgb) / conductor
+    (Au, Cu, Ag; roughness 0, 0.05, 0.3) / dielectric (eta 1.5; roughness 0, 0.1).  The emissive quads sit on a
+    regular ceiling grid at y = 4 facing down, radiance L ~ U[1, 20] quantised to `light_levels` values
+    (one AreaLightSource block per level keeps both parsers fast)."""
+    import os
+    os.makedirs(out_dir, exist_ok=True)
+    rng = np.random.Generator(np.random.PCG64(seed))
+    lines = ["LookAt 5 2.6 -7.5  5 1.2 5  0 1 0", 'Camera "perspective" "float fov" [42]',
+             'Film "rgb" "string filename" ["%s.png"] "integer xresolution" [%d] "integer yresolution" [%d]' % (name, width, height),
+             'Integrator "path" "integer maxdepth" [5]', "WorldBegin",
+             'Material "diffuse" "rgb reflectance" [0.2 0.2 0.2]']
+    metals = ("Au", "Cu", "Ag")
+    n_tris = n_obj = 0
+    cols = int(np.ceil(np.sqrt(n_meshes / 3.0)))          # terrain tiles per side; objects share the same grid
+    cell = 10.0 / cols
+    kinds = [k % 3 for k in range(n_meshes)]
+    slot = {0: 0, 1: 0, 2: 0}
+    for k in range(n_meshes):
+        kind = kinds[k]
+        s = slot[kind]
+        slot[kind] += 1
+        cx, cz = (s % cols + 0.5) * cell, ((s // cols) % cols + 0.5) * cell
+        if kind == 0:
+            centre, size = (cx, 0.0, cz), cell * 1.02
+        elif kind == 1:
+            centre, size = (cx - 0.18 * cell, 0.28 * cell + 0.3, cz + 0.15 * cell), 0.5 * cell
+        else:
+            centre, size = (cx + 0.2 * cell, 0.75 * cell + 0.5, cz - 0.15 * cell), 0.6 * cell
+        P, idx = _displaced_mesh(kind, grid, centre, size, rng)
+        ply = "%s_mesh_%02d.ply" % (name, k)
+        write_ply(os.path.join(out_dir, ply), P, idx)
+        n_tris += len(idx)
+        if kind == 0:                                      # terrain stays diffuse so the floor carries the NEE load
+            j = 0
+        else:
+            j = n_obj
+            n_obj += 1
+        if j % 3 == 1:
+            metal = metals[(j // 3) % 3]
+            mat = 'Material "conductor" "spectrum eta" ["metal-%s-eta"] "spectrum k" ["metal-%s-k"] "float roughness" [%g]' % (
+                metal, metal, (0.0, 0.05, 0.3)[(j // 9) % 3])
+        elif j % 3 == 2:
+            mat = 'Material "dielectric" "float eta" [1.5] "float roughness" [%g]' % ((0.0, 0.1)[(j // 3) % 2])
+        else:
+            c = 0.15 + 0.7 * rng.random(3)
+            mat = 'Material "diffuse" "rgb reflectance" [%.4f %.4f %.4f]' % tuple(c)
+        lines += ["AttributeBegin", "  " + mat, '  Shape "plymesh" "string filename" ["%s"]' % ply, "AttributeEnd"]
+    # ceiling grid of emissive quads (two triangles each), facing -y
+    gx = int(np.ceil(np.sqrt(n_light_quads)))
+    gz = (n_light_quads + gx - 1) // gx
+    q = np.arange(n_light_quads)
+    qx, qz = (q % gx + 0.5) * (10.0 / gx), (q // gx + 0.5) * (10.0 / gz)
+    h = 0.25 * min(10.0 / gx, 10.0 / gz)
+    level = rng.integers(0, light_levels, n_light_quads)
+    for lv in range(light_levels):
+        sel = np.nonzero(level == lv)[0]
+        if len(sel) == 0:
+            continue
+        Lv = 1.0 + 19.0 * (lv + 0.5) / light_levels
+        x, z = qx[sel], qz[sel]
+        y = np.full_like(x, 4.0)
+        Pq = np.stack([np.stack([x - h, y, z - h], 1), np.stack([x + h, y, z - h], 1),
+                       np.stack([x + h, y, z + h], 1), np.stack([x - h, y, z + h], 1)], 1).reshape(-1, 3).astype(np.float32)
+        base = 4 * np.arange(len(sel), dtype=np.int32)[:, None]
+        iq = np.concatenate([base + np.array([[0, 1, 2]], np.int32), base + np.array([[2, 3, 0]], np.int32)], 1).reshape(-1, 3)
+        n_tris += len(iq)
+        lines += ["AttributeBegin", '  AreaLightSource "diffuse" "rgb L" [%.5f %.5f %.5f]' % (Lv, Lv, Lv),
+                  '  Shape "trianglemesh" "integer indices" [%s] "point3 P" [%s]' % (
+                      " ".join(map(str, iq.reshape(-1))), " ".join("%.9g" % v for v in Pq.reshape(-1))), "AttributeEnd"]
+    path = os.path.join(out_dir, name + ".pbrt")
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return path, {"triangles": n_tris, "meshes": n_meshes, "emissive_triangles": 2 * n_light_quads, "width": width, "height": height}
