@@ -140,10 +140,12 @@ typedef struct {
     int64_t n_triangles;
     int64_t n_bvh2_nodes;
     int64_t n_bvh8_nodes;
-    int32_t key_bits;      /* 30 (N <= 16Mi) or 63 */
+    int32_t key_bits;      /* Morton bits: 30 (N <= 16Mi, the reference's code) else 3*floor((64-ceil(log2 N))/3) */
     int32_t sort_passes;
     float ms_bounds_morton, ms_sort, ms_emit, ms_refit, ms_collapse, ms_total; /* device events */
     int64_t device_bytes;  /* resident accelerator + geometry bytes after the build */
+    float ms_wall;         /* host wall clock of the whole call, allocations included */
+    int32_t collapse_levels;
 } b200pt_build_stats;
 
 typedef struct {

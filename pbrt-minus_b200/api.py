@@ -73,7 +73,7 @@ class BuildStats(C.Structure):
                 ("key_bits", C.c_int32), ("sort_passes", C.c_int32),
                 ("ms_bounds_morton", C.c_float), ("ms_sort", C.c_float), ("ms_emit", C.c_float),
                 ("ms_refit", C.c_float), ("ms_collapse", C.c_float), ("ms_total", C.c_float),
-                ("device_bytes", C.c_int64)]
+                ("device_bytes", C.c_int64), ("ms_wall", C.c_float), ("collapse_levels", C.c_int32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -17,6 +17,7 @@
 //                       nodes / triangle slots with atomic counters, re-lays the triangles out
 //                       in node order and pushes the interior children on the next queue.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 
 #include "common.cuh"
@@ -134,12 +135,13 @@ __device__ __forceinline__ uint64_t spread21(uint64_t x) {
     return x;
 }
 
-// KEY30: key = morton30 << 32 | prim (sorted key-only on bits 32..63).
-// otherwise: key = morton63, vals = prim.
+// KEY30: key = morton30 << 32 | prim (sorted key-only on bits 32..63; the reference's code, util/math.h:183-208).
+// otherwise (N > 16 Mi): key = morton(3 * axis_bits) << prim_bits | prim, axis_bits = (64 - prim_bits) / 3 <= 21 --
+// still one 8-byte key-only sort, over 3 * axis_bits bits instead of 63 bits + a 4-byte payload.
 template <bool KEY30>
 __global__ void __launch_bounds__(256) k_morton(const float *__restrict__ P, const int32_t *__restrict__ idx, int64_t n,
-                                                const float *__restrict__ boxes, uint64_t *__restrict__ keys,
-                                                uint32_t *__restrict__ vals) {
+                                                const float *__restrict__ boxes, uint64_t *__restrict__ keys, int axis_bits,
+                                                int prim_bits) {
     const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (t >= n) return;
     const TriVerts tv = load_tri(P, idx, t);
@@ -161,20 +163,22 @@ __global__ void __launch_bounds__(256) k_morton(const float *__restrict__ P, con
         const uint32_t m = (left_shift3(qz) << 2) | (left_shift3(qy) << 1) | left_shift3(qx);
         keys[t] = (uint64_t(m) << 32) | uint64_t(uint32_t(t));
     } else {
+        const float cells = float(1u << axis_bits);
         uint64_t q[3];
 #pragma unroll
         for (int a = 0; a < 3; a++) {
-            const float s = off[a] * 2097152.0f;
-            q[a] = s <= 0.0f ? 0ull : (s >= 2097151.0f ? 2097151ull : uint64_t(s));
+            const float s = off[a] * cells;
+            q[a] = s <= 0.0f ? 0ull : (s >= cells - 1.0f ? uint64_t(cells - 1.0f) : uint64_t(s));
         }
-        keys[t] = (spread21(q[2]) << 2) | (spread21(q[1]) << 1) | spread21(q[0]);
-        vals[t] = uint32_t(t);
+        const uint64_t m = (spread21(q[2]) << 2) | (spread21(q[1]) << 1) | spread21(q[0]);
+        keys[t] = (m << prim_bits) | uint64_t(t);
     }
 }
 
-__global__ void __launch_bounds__(256) k_unpack_prims(const uint64_t *__restrict__ keys, int64_t n, uint32_t *__restrict__ prims) {
+__global__ void __launch_bounds__(256) k_unpack_prims(const uint64_t *__restrict__ keys, int64_t n, uint32_t mask,
+                                                      uint32_t *__restrict__ prims) {
     const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (t < n) prims[t] = uint32_t(keys[t]);
+    if (t < n) prims[t] = uint32_t(keys[t]) & mask;
 }
 
 // ------------------------------------------------------------------------ BVH2 (build only)
@@ -269,8 +273,11 @@ struct CollapseArgs {
     float4 *tris;  // re-laid-out triangles out
     const int2 *q_in; // (bvh2 node, bvh8 node index)
     int2 *q_out;
-    int q_in_count;
-    unsigned int *counters; // [0] bvh8 nodes allocated, [1] tris allocated, [2] next-queue count, [3] overflow flag
+    // [0] bvh8 nodes allocated, [1] tris allocated, [2] overflow flag, [3] levels run,
+    // [4 + parity] items in q_in, [4 + (parity ^ 1)] items pushed to q_out -- all on the device: the host
+    // enqueues a batch of levels without looking and reads the block back once per batch
+    unsigned int *counters;
+    int parity;
     unsigned int node_capacity;
 };
 
@@ -279,9 +286,7 @@ __device__ __forceinline__ float half_area(const float4 &lo, const float4 &hi) {
     return dx * dy + dy * dz + dz * dx;
 }
 
-__global__ void __launch_bounds__(128) k_collapse_level(CollapseArgs a) {
-    const int item = blockIdx.x * blockDim.x + threadIdx.x;
-    if (item >= a.q_in_count) return;
+__device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
     const int n = a.t.n;
     const int2 work = a.q_in[item];
     const int root2 = work.x;
@@ -399,9 +404,9 @@ __global__ void __launch_bounds__(128) k_collapse_level(CollapseArgs a) {
     unsigned child_base = 0, tri_base = 0, q_base = 0;
     if (n_inner) {
         child_base = atomicAdd(&a.counters[0], (unsigned)n_inner);
-        q_base = atomicAdd(&a.counters[2], (unsigned)n_inner);
+        q_base = atomicAdd(&a.counters[4 + (a.parity ^ 1)], (unsigned)n_inner);
         if (child_base + n_inner > a.node_capacity) {
-            a.counters[3] = 1;
+            a.counters[2] = 1;
             return;
         }
     }
@@ -482,28 +487,42 @@ __global__ void __launch_bounds__(128) k_collapse_level(CollapseArgs a) {
     dst[4] = make_float4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
 }
 
+__global__ void __launch_bounds__(128) k_collapse_level(CollapseArgs a) {
+    const int count = (int)a.counters[4 + a.parity];
+    for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < count; item += gridDim.x * blockDim.x) collapse_item(a, item);
+}
+
+// between two levels: the consumed queue's counter becomes the empty out-counter of the level after next
+__global__ void k_collapse_advance(unsigned int *counters, int parity) {
+    if (counters[4 + parity]) counters[3] += 1;
+    counters[4 + parity] = 0;
+}
+
 __global__ void k_seed_queue(int2 *q, unsigned int *counters, int root2) {
     q[0] = make_int2(root2, 0);
     counters[0] = 1; // node 0 = root
     counters[1] = 0;
     counters[2] = 0;
     counters[3] = 0;
+    counters[4] = 1; // one item in queue 0
+    counters[5] = 0;
 }
 
 // ------------------------------------------------------------------------------ host driver
 namespace {
-struct DevFree {
-    std::vector<void *> ptrs;
-    ~DevFree() {
-        for (void *p : ptrs) cudaFree(p);
+// one cudaMalloc for all build scratch, carved into 256-byte aligned pieces (every cudaMalloc costs
+// 0.2-0.4 ms of host time with the stream idle -- more than the whole Morton + sort phase at 1 M triangles)
+struct Arena {
+    char *base = nullptr;
+    size_t size = 0, used = 0;
+    ~Arena() {
+        if (base) cudaFree(base);
     }
+    static size_t pad(size_t b) { return (b + 255) & ~size_t(255); }
     template <typename T>
-    cudaError_t alloc(T **out, size_t count) {
-        void *p = nullptr;
-        cudaError_t e = cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
-        if (e == cudaSuccess) ptrs.push_back(p);
-        *out = (T *)p;
-        return e;
+    void take(T **out, size_t count) {
+        *out = reinterpret_cast<T *>(base + used);
+        used += pad(std::max<size_t>(count, 1) * sizeof(T));
     }
 };
 } // namespace
@@ -528,8 +547,19 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
         set_error("b200pt_bvh_build: %lld triangles exceed the 2^30 limit", (long long)n);
         return B200PT_ERR_UNSUPPORTED;
     }
+    const auto wall0 = std::chrono::steady_clock::now();
+    // key layout: the reference's 30-bit code above a 32-bit primitive id (N <= 16 Mi), else the widest Morton
+    // code that fits above ceil(log2 N) primitive-id bits; both sort as 8-byte keys with no payload
     const bool key30 = n <= (int64_t(1) << 24);
-    bs.key_bits = key30 ? 30 : 63;
+    int prim_bits = 32, axis_bits = 10;
+    if (!key30) {
+        prim_bits = 1;
+        while ((int64_t(1) << prim_bits) < n) prim_bits++;
+        axis_bits = std::min(21, (64 - prim_bits) / 3);
+    }
+    const int sort_lo = prim_bits, sort_hi = prim_bits + ((3 * axis_bits + 7) / 8) * 8;
+    const int n_passes = (sort_hi - sort_lo) / 8;
+    bs.key_bits = 3 * axis_bits;
 
     cudaEvent_t ev[7];
     for (auto &e : ev) CU_TRY(cudaEventCreate(&e));
@@ -538,20 +568,48 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
         ~EvFree() { for (int i = 0; i < 7; i++) cudaEventDestroy(e[i]); }
     } evfree{ev};
 
-    DevFree tmp;
+    // ---- all memory up front: outputs (kept) and one scratch arena (freed on return)
+    const unsigned node_capacity = unsigned(n / 2 + 64);
+    CU_TRY(cudaMalloc(&s->d_sorted_keys, n * sizeof(uint64_t)));
+    CU_TRY(cudaMalloc(&s->d_sorted_prim, n * sizeof(uint32_t)));
+    CU_TRY(cudaMalloc(&s->d_nodes, size_t(node_capacity) * 5 * sizeof(float4)));
+    CU_TRY(cudaMalloc(&s->d_tris, size_t(n) * 3 * sizeof(float4)));
+    Arena tmp;
+    {
+        const size_t sz = Arena::pad(12 * 4) * 2 + Arena::pad(n * 8) + Arena::pad(256 * sort_tiles(n) * 4) +
+                          Arena::pad(sort_scan_tmp_words(n) * 4) + 2 * Arena::pad(2 * n * sizeof(float4)) + Arena::pad(n * sizeof(int2)) +
+                          Arena::pad(2 * n * 4) + Arena::pad(n * 4) + 2 * Arena::pad(n * sizeof(int2)) + Arena::pad(8 * 4);
+        CU_TRY(cudaMalloc(&tmp.base, sz));
+        tmp.size = sz;
+    }
     uint32_t *d_red;
     float *d_boxes;
-    CU_TRY(tmp.alloc(&d_red, 12));
-    CU_TRY(tmp.alloc(&d_boxes, 12));
+    tmp.take(&d_red, 12);
+    tmp.take(&d_boxes, 12);
     SortBuffers sb;
-    CU_TRY(tmp.alloc(&sb.keys[0], n));
-    CU_TRY(tmp.alloc(&sb.keys[1], n));
-    if (!key30) {
-        CU_TRY(tmp.alloc(&sb.vals[0], n));
-        CU_TRY(tmp.alloc(&sb.vals[1], n));
+    uint64_t *d_keys_tmp;
+    tmp.take(&d_keys_tmp, n);
+    // the sort ping-pongs between two buffers; the one the last pass writes is the kept output
+    sb.keys[n_passes & 1] = s->d_sorted_keys;
+    sb.keys[(n_passes & 1) ^ 1] = d_keys_tmp;
+    tmp.take(&sb.tile_hist, 256 * sort_tiles(n));
+    tmp.take(&sb.scan_tmp, sort_scan_tmp_words(n));
+    Bvh2 t;
+    t.n = int32_t(n);
+    tmp.take(&t.lo, 2 * n);
+    tmp.take(&t.hi, 2 * n);
+    tmp.take(&t.range, n);
+    tmp.take(&t.parent, 2 * n);
+    tmp.take(&t.arrive, n);
+    int2 *q[2];
+    unsigned int *d_counters;
+    tmp.take(&q[0], n);
+    tmp.take(&q[1], n);
+    tmp.take(&d_counters, 8);
+    if (tmp.used > tmp.size) {
+        set_error("b200pt_bvh_build: scratch arena overrun");
+        return B200PT_ERR_STATE;
     }
-    CU_TRY(tmp.alloc(&sb.tile_hist, 256 * sort_tiles(n)));
-    CU_TRY(tmp.alloc(&sb.scan_tmp, sort_scan_tmp_words(n)));
 
     const int tb = 256;
     const int grid_n = int((n + tb - 1) / tb);
@@ -560,70 +618,60 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
     k_init_reduction<<<1, 32, 0, st>>>(d_red);
     k_centroid_bounds<<<std::min<int64_t>(grid_n, s->sm_count * 16), tb, 0, st>>>(s->d_P, s->d_idx, n, d_red);
     k_cubify<<<1, 1, 0, st>>>(d_red, d_boxes);
-    if (key30) k_morton<true><<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, n, d_boxes, sb.keys[0], nullptr);
-    else k_morton<false><<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, n, d_boxes, sb.keys[0], sb.vals[0]);
+    if (key30) k_morton<true><<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
+    else k_morton<false><<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
     CU_TRY(cudaEventRecord(ev[1], st));
-    // 2. LSD radix sort
-    const int res = key30 ? radix_sort_u64(sb, n, 32, 64, st, &bs.sort_passes) : radix_sort_u64(sb, n, 0, 64, st, &bs.sort_passes);
-    CU_TRY(cudaMalloc(&s->d_sorted_keys, n * sizeof(uint64_t)));
-    CU_TRY(cudaMalloc(&s->d_sorted_prim, n * sizeof(uint32_t)));
-    CU_TRY(cudaMemcpyAsync(s->d_sorted_keys, sb.keys[res], n * sizeof(uint64_t), cudaMemcpyDeviceToDevice, st));
-    if (key30) k_unpack_prims<<<grid_n, tb, 0, st>>>(sb.keys[res], n, s->d_sorted_prim);
-    else CU_TRY(cudaMemcpyAsync(s->d_sorted_prim, sb.vals[res], n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+    // 2. LSD radix sort (key-only)
+    const int res = radix_sort_u64(sb, n, sort_lo, sort_hi, st, &bs.sort_passes);
+    if (sb.keys[res] != s->d_sorted_keys) {
+        set_error("b200pt_bvh_build: sort ended in the wrong buffer");
+        return B200PT_ERR_STATE;
+    }
+    k_unpack_prims<<<grid_n, tb, 0, st>>>(s->d_sorted_keys, n, key30 ? 0xffffffffu : uint32_t((uint64_t(1) << prim_bits) - 1), s->d_sorted_prim);
     CU_TRY(cudaEventRecord(ev[2], st));
     // 3. hierarchy emission
-    Bvh2 t;
-    t.n = int32_t(n);
-    CU_TRY(tmp.alloc(&t.lo, 2 * n));
-    CU_TRY(tmp.alloc(&t.hi, 2 * n));
-    CU_TRY(tmp.alloc(&t.range, n));
-    CU_TRY(tmp.alloc(&t.parent, 2 * n));
-    CU_TRY(tmp.alloc(&t.arrive, n));
     CU_TRY(cudaMemsetAsync(t.arrive, 0, n * sizeof(uint32_t), st));
     if (n > 1) k_emit_hierarchy<<<int((n - 1 + tb - 1) / tb), tb, 0, st>>>(s->d_sorted_keys, t);
     CU_TRY(cudaEventRecord(ev[3], st));
     // 4. refit
     k_refit<<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, s->d_sorted_prim, t);
     CU_TRY(cudaEventRecord(ev[4], st));
-    // 5. work-queue collapse to BVH8
-    const unsigned node_capacity = unsigned(n / 2 + 64);
-    CU_TRY(cudaMalloc(&s->d_nodes, size_t(node_capacity) * 5 * sizeof(float4)));
-    CU_TRY(cudaMalloc(&s->d_tris, size_t(n) * 3 * sizeof(float4)));
-    int2 *q[2];
-    unsigned int *d_counters;
-    CU_TRY(tmp.alloc(&q[0], n));
-    CU_TRY(tmp.alloc(&q[1], n));
-    CU_TRY(tmp.alloc(&d_counters, 4));
-    k_seed_queue<<<1, 1, 0, st>>>(q[0], d_counters, n > 1 ? 0 : 0 /* leaf id n-1+0 == 0 when n == 1 */);
-    unsigned int h_counters[4] = {1, 0, 0, 0};
-    int q_count = 1, cur = 0, levels = 0;
-    while (q_count > 0) {
-        CollapseArgs a;
-        a.t = t;
-        a.P = s->d_P;
-        a.idx = s->d_idx;
-        a.sorted_prim = s->d_sorted_prim;
-        a.tri_material = s->d_tri_material;
-        a.tri_light = s->d_tri_light;
-        a.tri_flip = s->d_tri_flip;
-        a.nodes = s->d_nodes;
-        a.tris = s->d_tris;
-        a.q_in = q[cur];
-        a.q_out = q[cur ^ 1];
-        a.q_in_count = q_count;
-        a.counters = d_counters;
-        a.node_capacity = node_capacity;
-        k_collapse_level<<<(q_count + 127) / 128, 128, 0, st>>>(a);
+    // 5. work-queue collapse to BVH8: levels are enqueued in batches, queue sizes stay on the device
+    k_seed_queue<<<1, 1, 0, st>>>(q[0], d_counters, 0 /* leaf id n-1+0 == 0 when n == 1 */);
+    unsigned int h_counters[8] = {1, 0, 0, 0, 1, 0, 0, 0};
+    int parity = 0, levels = 0;
+    const int collapse_grid = s->sm_count * 16;
+    while (true) {
+        const int batch = levels == 0 ? 12 : 6;
+        for (int b = 0; b < batch; b++) {
+            CollapseArgs a;
+            a.t = t;
+            a.P = s->d_P;
+            a.idx = s->d_idx;
+            a.sorted_prim = s->d_sorted_prim;
+            a.tri_material = s->d_tri_material;
+            a.tri_light = s->d_tri_light;
+            a.tri_flip = s->d_tri_flip;
+            a.nodes = s->d_nodes;
+            a.tris = s->d_tris;
+            a.q_in = q[parity];
+            a.q_out = q[parity ^ 1];
+            a.counters = d_counters;
+            a.parity = parity;
+            a.node_capacity = node_capacity;
+            k_collapse_level<<<collapse_grid, 128, 0, st>>>(a);
+            k_collapse_advance<<<1, 1, 0, st>>>(d_counters, parity);
+            parity ^= 1;
+            levels++;
+        }
         CU_TRY(cudaMemcpyAsync(h_counters, d_counters, sizeof(h_counters), cudaMemcpyDeviceToHost, st));
         CU_TRY(cudaStreamSynchronize(st));
-        if (h_counters[3]) {
+        if (h_counters[2]) {
             set_error("b200pt_bvh_build: BVH8 node pool overflow (capacity %u)", node_capacity);
             return B200PT_ERR_STATE;
         }
-        q_count = int(h_counters[2]);
-        CU_TRY(cudaMemsetAsync(d_counters + 2, 0, sizeof(unsigned int), st));
-        cur ^= 1;
-        if (++levels > 4096) {
+        if (h_counters[4 + parity] == 0) break;
+        if (levels > 4096) {
             set_error("b200pt_bvh_build: collapse did not terminate");
             return B200PT_ERR_STATE;
         }
@@ -636,6 +684,7 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
 
     bs.n_bvh2_nodes = 2 * n - 1;
     bs.n_bvh8_nodes = h_counters[0];
+    bs.collapse_levels = int32_t(h_counters[3]);
     if (int64_t(h_counters[1]) != n) {
         set_error("b200pt_bvh_build: %u of %lld triangles placed", h_counters[1], (long long)n);
         return B200PT_ERR_STATE;
@@ -646,6 +695,7 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
     CU_TRY(cudaEventElapsedTime(&bs.ms_refit, ev[3], ev[4]));
     CU_TRY(cudaEventElapsedTime(&bs.ms_collapse, ev[4], ev[5]));
     CU_TRY(cudaEventElapsedTime(&bs.ms_total, ev[0], ev[5]));
+    bs.ms_wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - wall0).count();
 
     s->bvh.nodes = s->d_nodes;
     s->bvh.tris = s->d_tris;

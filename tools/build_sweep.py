@@ -3,7 +3,7 @@
 
 For every N: soup as C2 (seed = N, s = 2*N^(-1/3)); timed = b200pt_bvh_build, all phases, device events
 (first build = with allocation of the build scratch, then --repeat rebuilds, median reported);
-algorithmic bytes = 428 B/triangle (30-bit keys, N <= 16 Mi) or 568 B/triangle (63-bit keys).
+algorithmic bytes = 428 B/triangle (30-bit keys, N <= 16 Mi) or 372 + 16 * sort passes (packed keys, N > 16 Mi).
 --reference additionally times the reference's own HLBVH constructor on the same soup file
 (oracle/_ref/ref_trace with no ray jobs; its "BVH building" line, host cores + managed memory), for N <= --ref-max.
 Validation per N (--check): a sample of primary rays traced through the fresh tree must hit the same
@@ -56,9 +56,11 @@ def main():
         reps = [scene.build() for _ in range(args.repeat)]
         keys = ("ms_bounds_morton", "ms_sort", "ms_emit", "ms_refit", "ms_collapse", "ms_total")
         med = {k: float(np.median([r[k] for r in reps])) for k in keys}
-        bpt = 428 if first["key_bits"] == 30 else 568
+        # bounds+key 56, sort 4|8 + 16 P, emit+refit 116|120, collapse 92, re-layout 96
+        bpt = 428 if first["key_bits"] == 30 else 372 + 16 * first["sort_passes"]
         row = {"n_triangles": n, "key_bits": first["key_bits"], "sort_passes": first["sort_passes"],
-               "n_bvh8_nodes": first["n_bvh8_nodes"], "first_build_ms": round(first["ms_total"], 3),
+               "n_bvh8_nodes": first["n_bvh8_nodes"], "first_build_ms": round(first["ms_total"], 3), "first_build_wall_ms": round(first["ms_wall"], 3),
+               "median_wall_ms": round(float(np.median([r["ms_wall"] for r in reps])), 3), "collapse_levels": first["collapse_levels"],
                "median_ms": {k: round(v, 3) for k, v in med.items()},
                "Mtris_s": round(n / med["ms_total"] / 1e3, 1), "algorithmic_bytes_per_tri": bpt,
                "achieved_GBs": round(n * bpt / med["ms_total"] / 1e6, 1),
