@@ -62,7 +62,8 @@ typedef struct {
 } b200pt_spectrum;
 
 /* ---- materials (base/material.cu:97-131) ------------------------------------------------ */
-enum { B200PT_MAT_DIFFUSE = 0, B200PT_MAT_CONDUCTOR = 1, B200PT_MAT_DIELECTRIC = 2 };
+enum { B200PT_MAT_DIFFUSE = 0, B200PT_MAT_CONDUCTOR = 1, B200PT_MAT_DIELECTRIC = 2, B200PT_MAT_DIFFUSE_TRANSMISSION = 3,
+       B200PT_MAT_COUNT = 4 };
 typedef struct {
     int32_t type;
     int32_t reflectance; /* spectrum id: diffuse reflectance, or conductor "reflectance" (-1: use eta/k) */
@@ -70,14 +71,23 @@ typedef struct {
     int32_t k;           /* spectrum id: conductor k */
     float u_roughness, v_roughness;
     int32_t remap_roughness; /* materials/conductor_material.cu:52-75: alpha = sqrt(roughness) */
+    int32_t transmittance;   /* spectrum id: diffuse-transmission "transmittance" (materials/diffuse_transmission_material.cu:8-31) */
+    float scale;             /* diffuse-transmission "scale" */
 } b200pt_material;
 
-/* ---- lights: one DiffuseAreaLight per emissive triangle (base/light.cu:56-75) ------------ */
+/* ---- lights (base/light.cu:22-75), in the order the scene file creates them (= light-sampler index):
+ *      one DiffuseAreaLight per emissive triangle; DistantLight (lights/distant_light.cu), UniformInfiniteLight
+ *      (lights/uniform_infinite_light.cu) and SpotLight (lights/spot_light.cu) from "LightSource" */
+enum { B200PT_LIGHT_AREA = 0, B200PT_LIGHT_DISTANT = 1, B200PT_LIGHT_UNIFORM_INFINITE = 2, B200PT_LIGHT_SPOT = 3 };
 typedef struct {
-    int32_t triangle;  /* index into the triangle array */
-    int32_t spectrum;  /* Lemit spectrum id */
-    float scale;       /* already divided by the photometric integral (lights/diffuse_area_light.cu:17-26) */
+    int32_t triangle;  /* AREA: index into the triangle array; other types: -1 */
+    int32_t spectrum;  /* Lemit / I spectrum id */
+    float scale;       /* already divided by the photometric integral (and times illuminance / power factors) */
     int32_t two_sided;
+    int32_t type;      /* B200PT_LIGHT_* */
+    float v[3];        /* DISTANT: render_from_light(0,0,1) (not normalised); SPOT: render_from_light(0,0,0) */
+    float light_from_render[9]; /* SPOT: upper 3x3 of the inverse transform, row-major (Transform::apply_inverse) */
+    float cos_falloff_start, cos_falloff_end; /* SPOT */
 } b200pt_light;
 
 /* ---- spheres (shapes/sphere.h:71-125); intersected in object space ----------------------- */

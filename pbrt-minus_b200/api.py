@@ -25,11 +25,14 @@ class Spectrum(C.Structure):
 
 class Material(C.Structure):
     _fields_ = [("type", C.c_int32), ("reflectance", C.c_int32), ("eta", C.c_int32), ("k", C.c_int32),
-                ("u_roughness", C.c_float), ("v_roughness", C.c_float), ("remap_roughness", C.c_int32)]
+                ("u_roughness", C.c_float), ("v_roughness", C.c_float), ("remap_roughness", C.c_int32),
+                ("transmittance", C.c_int32), ("scale", C.c_float)]
 
 
 class Light(C.Structure):
-    _fields_ = [("triangle", C.c_int32), ("spectrum", C.c_int32), ("scale", C.c_float), ("two_sided", C.c_int32)]
+    _fields_ = [("triangle", C.c_int32), ("spectrum", C.c_int32), ("scale", C.c_float), ("two_sided", C.c_int32),
+                ("type", C.c_int32), ("v", C.c_float * 3), ("light_from_render", C.c_float * 9),
+                ("cos_falloff_start", C.c_float), ("cos_falloff_end", C.c_float)]
 
 
 class Sphere(C.Structure):

@@ -209,6 +209,41 @@ struct BSDF<B200PT_MAT_DIFFUSE> {
     }
 };
 
+// DiffuseTransmissionBxDF (bxdfs/diffuse_transmission_bxdf.h:8-103)
+template <>
+struct BSDF<B200PT_MAT_DIFFUSE_TRANSMISSION> {
+    Frame frame;
+    S4 r, t;
+    __device__ __forceinline__ uint32_t flags() const {
+        return (is_positive(r) ? (BXDF_DIFFUSE | BXDF_REFLECTION) : 0u) | (is_positive(t) ? (BXDF_DIFFUSE | BXDF_TRANSMISSION) : 0u);
+    }
+    __device__ __forceinline__ void regularize() {}
+    __device__ __forceinline__ S4 f(V3 wo, V3 wi) const { return (same_hemisphere(wo, wi) ? r : t) * kInvPi; }
+    __device__ __forceinline__ float pdf(V3 wo, V3 wi) const {
+        const float pr = max_component(r), pt = max_component(t);
+        if (pr == 0.f && pt == 0.f) return 0.f;
+        return (same_hemisphere(wo, wi) ? pr : pt) / (pr + pt) * (fabsf(wi.z) / kPi);
+    }
+    __device__ __forceinline__ bool sample(V3 wo, float uc, float2 u, BSDFSample &bs) const {
+        const float pr = max_component(r), pt = max_component(t);
+        if (pr == 0.f && pt == 0.f) return false;
+        V3 wi = sample_cosine_hemisphere(u);
+        if (uc < pr / (pr + pt)) {
+            if (wo.z < 0.f) wi.z *= -1.f;
+            bs.pdf = fabsf(wi.z) / kPi * pr / (pr + pt);
+            bs.flags = BXDF_DIFFUSE | BXDF_REFLECTION;
+        } else {
+            if (wo.z > 0.f) wi.z *= -1.f;
+            bs.pdf = fabsf(wi.z) / kPi * pt / (pr + pt);
+            bs.flags = BXDF_DIFFUSE | BXDF_TRANSMISSION;
+        }
+        bs.f = f(wo, wi);
+        bs.wi = wi;
+        bs.eta = 1.f;
+        return true;
+    }
+};
+
 template <>
 struct BSDF<B200PT_MAT_CONDUCTOR> {
     Frame frame;

@@ -19,14 +19,20 @@
 namespace b200pt {
 
 struct LightRec { // 64 B
-    float p0[3], p1[3], p2[3];
+    float p0[3], p1[3], p2[3]; // AREA: vertices.  DISTANT: p0 = render_from_light(0,0,1).  SPOT: p0 = position
     float scale;      // already divided by the photometric integral
     int32_t spectrum; // Lemit
-    int32_t flags;    // bit 0: two_sided, bit 1: flip normal (reverse_orientation ^ swaps_handedness)
+    int32_t flags;    // bit 0: two_sided, bit 1: flip normal (reverse_orientation ^ swaps_handedness), bits 4..5: B200PT_LIGHT_*
     float pmf;        // power_light_sampler pdfs[idx]
     float area;
-    int32_t prim;     // primitive (triangle) index of this light: its own shadow rays skip it
-    int32_t pad;
+    int32_t prim;     // primitive (triangle) index of this light: its own shadow rays skip it (-1: none)
+    int32_t ext;      // SPOT: index into the LightExt array
+};
+__device__ __host__ __forceinline__ int light_type(const LightRec &L) { return (L.flags >> 4) & 3; }
+
+struct LightExt { // 48 B, spot lights only (lights/spot_light.h)
+    float m[9];   // upper 3x3 of light_from_render
+    float cos_start, cos_end, pad;
 };
 
 struct AliasBin {
@@ -221,6 +227,64 @@ __device__ __forceinline__ bool light_sample(const LightRec &L, const LightCtx &
     if (pdf == 0.f || len2(p - ctx.p) == 0.f) return false;
     ls.wi = normalize(p - ctx.p);
     return true;
+}
+
+// util/math.h:211-218
+__device__ __forceinline__ float smooth_step(float x, float a, float b) {
+    if (a == b) return (x < a) ? 0.f : 1.f;
+    const float t = clampf((x - a) / (b - a), 0.f, 1.f);
+    return t * t * (3.f - 2.f * t);
+}
+// util/sampling.h:259-266
+__device__ __forceinline__ V3 sample_uniform_sphere(float2 u) {
+    const float z = 1.f - 2.f * u.x;
+    const float r = safe_sqrt(1.f - sqr(z));
+    const float phi = 2.f * kPi * u.y;
+    float sn, cs;
+    sincosf(phi, &sn, &cs);
+    return v3(r * cs, r * sn, z);
+}
+constexpr float kUniformSpherePdf = 0.07957747154594767f; // 1 / (4 pi)
+
+// sample_li of the lights that are not emissive triangles.  Li = weight * scale * Lemit(lambda) / dist2;
+// returns false when the sample carries no radiance.  ls.n = ls.err = 0: Interaction(p) has no normal and
+// no error bounds, so spawn_ray_to leaves that end of the segment where it is (base/ray.h:51-58).
+//   DistantLight::sample_li           lights/distant_light.cu:43-49   (delta)
+//   UniformInfiniteLight::sample_li   lights/uniform_infinite_light.cu:39-48
+//   SpotLight::sample_li / I          lights/spot_light.cu:43-60,110-114   (delta)
+__device__ __forceinline__ bool light_sample_other(const LightRec &L, int type, const LightExt *ext, float scene_radius,
+                                                   const LightCtx &ctx, float2 u, LightSample &ls, float *weight, float *dist2, bool *delta) {
+    ls.err = v3(0.f, 0.f, 0.f);
+    ls.n = v3(0.f, 0.f, 0.f);
+    *weight = 1.f;
+    *dist2 = 1.f;
+    if (type == B200PT_LIGHT_DISTANT) {
+        ls.wi = normalize(v3(L.p0[0], L.p0[1], L.p0[2]));
+        ls.p = ctx.p + ls.wi * (2.f * scene_radius);
+        ls.pdf = 1.f;
+        *delta = true;
+        return true;
+    }
+    if (type == B200PT_LIGHT_UNIFORM_INFINITE) {
+        ls.wi = sample_uniform_sphere(u);
+        ls.p = ctx.p + ls.wi * (2.f * scene_radius);
+        ls.pdf = kUniformSpherePdf;
+        *delta = false;
+        return true;
+    }
+    // spot
+    const V3 p = v3(L.p0[0], L.p0[1], L.p0[2]);
+    ls.p = p;
+    ls.wi = normalize(p - ctx.p);
+    const LightExt e = ext[L.ext];
+    const V3 w = -ls.wi;
+    const V3 wl = normalize(v3(e.m[0] * w.x + e.m[1] * w.y + e.m[2] * w.z, e.m[3] * w.x + e.m[4] * w.y + e.m[5] * w.z,
+                               e.m[6] * w.x + e.m[7] * w.y + e.m[8] * w.z));
+    *weight = smooth_step(wl.z, e.cos_end, e.cos_start);
+    *dist2 = len2(p - ctx.p);
+    ls.pdf = 1.f;
+    *delta = true;
+    return *weight > 0.f;
 }
 
 // DiffuseAreaLight::l: one-sided unless two_sided

@@ -18,6 +18,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <numeric>
 #include <set>
 
@@ -45,7 +46,11 @@ struct RenderData {
     MatRec *d_materials = nullptr;
     LightRec *d_lights = nullptr;
     AliasBin *d_alias = nullptr;
+    LightExt *d_light_ext = nullptr;
     int n_lights = 0, n_materials = 0, n_spectra = 0;
+    int n_infinite = 0, infinite[4] = {0, 0, 0, 0};
+    float scene_radius = 0.f;
+    bool has_mat[WF_NMAT] = {};
     FilterTab filter = {};
     CameraRec camera = {};
     float *d_cie[3] = {nullptr, nullptr, nullptr};
@@ -97,7 +102,8 @@ static float build_pc1d(const float *f, int n, float mn, float mx, float *func, 
     return func_int;
 }
 
-__global__ void k_light_power(SpectrumTable tab, const LightRec *lights, int n, S4 lambda, S4 pdf, float *out) {
+__global__ void k_light_power(SpectrumTable tab, const LightRec *lights, const LightExt *ext, float scene_radius, int n, S4 lambda,
+                              S4 pdf, float *out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     // light_samplers/power_light_sampler.cu:15-21: phi at the wavelengths of sample_visible(0.5), which the
@@ -105,7 +111,19 @@ __global__ void k_light_power(SpectrumTable tab, const LightRec *lights, int n, 
     // visible_wavelengths_pdf, so lambda / pdf come from the host's libm (see b200pt_upload_render_data)
     const LightRec L = lights[i];
     const S4 Le = spectrum_sample(tab, L.spectrum, lambda) * L.scale;
-    const S4 phi = Le * (kPi * ((L.flags & 1) ? 2.f : 1.f) * L.area);
+    S4 phi;
+    switch (light_type(L)) {
+    case B200PT_LIGHT_DISTANT: phi = Le * sqr(scene_radius); break;                        // lights/distant_light.cu:52-55
+    case B200PT_LIGHT_UNIFORM_INFINITE:                                                     // lights/uniform_infinite_light.cu:34-37
+        phi = spectrum_sample(tab, L.spectrum, lambda) * (4.f * kPi * kPi * sqr(scene_radius) * L.scale);
+        break;
+    case B200PT_LIGHT_SPOT: {                                                               // lights/spot_light.cu:104-108
+        const LightExt e = ext[L.ext];
+        phi = Le * 2.f * kPi * ((1.f - e.cos_start) + (e.cos_start - e.cos_end) / 2.f);
+        break;
+    }
+    default: phi = Le * (kPi * ((L.flags & 1) ? 2.f : 1.f) * L.area);                       // lights/diffuse_area_light.cu:130-134
+    }
     out[i] = average(safe_div(phi, pdf));
 }
 
@@ -248,9 +266,11 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
     auto spec_ok = [&](int id) { return id >= 0 && id < desc->n_spectra; };
     for (int i = 0; i < desc->n_materials; i++) {
         const b200pt_material &m = desc->materials[i];
-        mats[i] = MatRec{m.type, m.reflectance, m.eta, m.k, m.u_roughness, m.v_roughness, m.remap_roughness, 0};
+        mats[i] = MatRec{m.type, m.reflectance, m.eta, m.k, m.u_roughness, m.v_roughness, m.remap_roughness, m.transmittance, m.scale, {0, 0, 0}};
         bool ok = true;
+        if (m.type >= 0 && m.type < WF_NMAT) r->has_mat[m.type] = true;
         if (m.type == B200PT_MAT_DIFFUSE) ok = spec_ok(m.reflectance);
+        else if (m.type == B200PT_MAT_DIFFUSE_TRANSMISSION) ok = spec_ok(m.reflectance) && spec_ok(m.transmittance);
         else if (m.type == B200PT_MAT_CONDUCTOR) ok = (spec_ok(m.eta) && spec_ok(m.k)) || (m.eta < 0 && spec_ok(m.reflectance));
         else if (m.type == B200PT_MAT_DIELECTRIC) ok = spec_ok(m.eta);
         else ok = false;
@@ -274,8 +294,40 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
     // ---- lights
     r->n_lights = desc->n_lights;
     std::vector<LightRec> lights(desc->n_lights);
+    std::vector<LightExt> ext;
+    bool any_other = false;
     for (int i = 0; i < desc->n_lights; i++) {
         const b200pt_light &l = desc->lights[i];
+        if (l.type != B200PT_LIGHT_AREA) {
+            if (l.type < 0 || l.type > B200PT_LIGHT_SPOT || !spec_ok(l.spectrum)) {
+                set_error("b200pt_scene_create: light %d is inconsistent (type %d)", i, l.type);
+                return B200PT_ERR_INVALID;
+            }
+            any_other = true;
+            LightRec &o = lights[i];
+            memset(&o, 0, sizeof(o));
+            for (int k = 0; k < 3; k++) o.p0[k] = l.v[k];
+            o.scale = l.scale;
+            o.spectrum = l.spectrum;
+            o.flags = l.type << 4;
+            o.prim = -1;
+            if (l.type == B200PT_LIGHT_SPOT) {
+                LightExt e = {};
+                for (int k = 0; k < 9; k++) e.m[k] = l.light_from_render[k];
+                e.cos_start = l.cos_falloff_start;
+                e.cos_end = l.cos_falloff_end;
+                o.ext = (int)ext.size();
+                ext.push_back(e);
+            }
+            if (l.type == B200PT_LIGHT_UNIFORM_INFINITE) {
+                if (r->n_infinite >= 4) {
+                    set_error("b200pt_scene_create: at most 4 infinite lights");
+                    return B200PT_ERR_UNSUPPORTED;
+                }
+                r->infinite[r->n_infinite++] = i;
+            }
+            continue;
+        }
         if (l.triangle < 0 || l.triangle >= desc->n_triangles || !spec_ok(l.spectrum)) {
             set_error("b200pt_scene_create: light %d is inconsistent", i);
             return B200PT_ERR_INVALID;
@@ -309,9 +361,44 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
         const float cx = dop(e1[1], e2[2], e1[2], e2[1]), cy = dop(e1[2], e2[0], e1[0], e2[2]), cz = dop(e1[0], e2[1], e1[1], e2[0]);
         o.area = std::sqrt(cx * cx + cy * cy + cz * cz) * 0.5f;
         o.prim = l.triangle;
-        o.pad = 0;
+        o.ext = 0;
+    }
+    if (any_other) {
+        // Bounds3::bounding_sphere of HLBVH::bounds() (scene_builder.cu:914-925, euclidean_space/bounds3.h:142-152):
+        // union of the triangle vertices and of the spheres' transformed boxes (transform.h:326-351)
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (int64_t t = 0; t < desc->n_triangles * 3; t++) {
+            const float *p = desc->P + 3 * (size_t)desc->indices[t];
+            for (int k = 0; k < 3; k++) {
+                lo[k] = std::min(lo[k], p[k]);
+                hi[k] = std::max(hi[k], p[k]);
+            }
+        }
+        for (int i = 0; i < desc->n_spheres; i++) {
+            const b200pt_sphere &sp = desc->spheres[i];
+            const float zmin = std::min(std::max(std::min(sp.z_min, sp.z_max), -sp.radius), sp.radius);
+            const float zmax = std::min(std::max(std::max(sp.z_min, sp.z_max), -sp.radius), sp.radius);
+            const float bmin[3] = {-sp.radius, -sp.radius, zmin}, bmax[3] = {sp.radius, sp.radius, zmax};
+            for (int a = 0; a < 3; a++) {
+                float mn = sp.render_from_object[4 * a + 3], mx = mn;
+                for (int k = 0; k < 3; k++) {
+                    const float x = sp.render_from_object[4 * a + k] * bmin[k], y = sp.render_from_object[4 * a + k] * bmax[k];
+                    mn += std::min(x, y);
+                    mx += std::max(x, y);
+                }
+                lo[a] = std::min(lo[a], mn);
+                hi[a] = std::max(hi[a], mx);
+            }
+        }
+        r->scene_radius = 0.f;
+        if (lo[0] <= hi[0]) {
+            const float c[3] = {(lo[0] + hi[0]) / 2, (lo[1] + hi[1]) / 2, (lo[2] + hi[2]) / 2};
+            const float d[3] = {c[0] - hi[0], c[1] - hi[1], c[2] - hi[2]};
+            r->scene_radius = std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+        }
     }
     if ((rc = dev_upload(r, &r->d_lights, lights.data(), lights.size(), st))) return rc;
+    if (!ext.empty() && (rc = dev_upload(r, &r->d_light_ext, ext.data(), ext.size(), st))) return rc;
     if (desc->n_lights > 0) {
         // power weights on the device (needs the spectra), alias table on the host
         float *d_w = nullptr;
@@ -328,7 +415,7 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             const float c = std::cosh(0.0072f * (hl[i] - 538));
             hp[i] = (hl[i] < 360 || hl[i] > 830) ? 0.f : 0.0039398042f / (c * c);
         }
-        k_light_power<<<(desc->n_lights + 127) / 128, 128, 0, st>>>(tab, r->d_lights, desc->n_lights, make_float4(hl[0], hl[1], hl[2], hl[3]),
+        k_light_power<<<(desc->n_lights + 127) / 128, 128, 0, st>>>(tab, r->d_lights, r->d_light_ext, r->scene_radius, desc->n_lights, make_float4(hl[0], hl[1], hl[2], hl[3]),
                                                                   make_float4(hp[0], hp[1], hp[2], hp[3]), d_w);
         CU_TRY(cudaMemcpyAsync(w.data(), d_w, w.size() * 4, cudaMemcpyDeviceToHost, st));
         CU_TRY(cudaStreamSynchronize(st));
@@ -444,7 +531,7 @@ __device__ __forceinline__ Sampler load_sampler(const WF &wf, int slot, const in
 
 __global__ void k_pass_begin(WF wf) {
     WFCounters *c = wf.c;
-    c->n_mat[0] = c->n_mat[1] = c->n_mat[2] = 0;
+    for (int m = 0; m < WF_NMAT; m++) c->n_mat[m] = 0;
     c->n_shadow = 0;
     c->ticket_closest = 0;
     c->ticket_shadow = 0;
@@ -567,8 +654,15 @@ __global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf) {
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned n_round = (n + WF_BLOCK - 1u) / WF_BLOCK * WF_BLOCK;
     unsigned n_finished = 0;
-    unsigned *const counters[4] = {&wf.c->n_mat[0], &wf.c->n_mat[1], &wf.c->n_mat[2], &wf.c->n_free};
-    int32_t *const queues[4] = {wf.q.mat[0], wf.q.mat[1], wf.q.mat[2], wf.q.free_slots};
+    unsigned *counters[WF_NMAT + 1];
+    int32_t *queues[WF_NMAT + 1];
+#pragma unroll
+    for (int m = 0; m < WF_NMAT; m++) {
+        counters[m] = &wf.c->n_mat[m];
+        queues[m] = wf.q.mat[m];
+    }
+    counters[WF_NMAT] = &wf.c->n_free;
+    queues[WF_NMAT] = wf.q.free_slots;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         const bool act = i < n && wf.pool.state[i] == ST_RAY;
         const int slot = (int)i;
@@ -598,7 +692,23 @@ __global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf) {
                 wf.pool.rng[slot] = s.state;
                 ids.z = s.dimension;
             }
-            if (!terminate && prim < 0) terminate = true; // escaped; no infinite lights on this path
+            if (!terminate && prim < 0) {
+                // escaped: infinite lights' Le, MIS-weighted against NEE (integrators/wavefront_path.cu:105-127).
+                // pdf_li(.., allow_incomplete_pdf = true) of the uniform infinite light is 0
+                // (lights/uniform_infinite_light.cu:51-58), so the weight is power_heuristic(dir_pdf, 0)
+                for (int k = 0; k < wf.n_infinite; k++) {
+                    const LightRec Lr = wf.lights[wf.infinite[k]];
+                    const S4 Le = spectrum_sample(wf.spectra, Lr.spectrum, wf.pool.lambda[slot]) * Lr.scale;
+                    if (depth == 0 || (ids.w & PF_SPECULAR)) {
+                        L = L + beta * Le;
+                    } else {
+                        const float pdf_light = Lr.pmf * 0.f;
+                        const float dir_pdf = wf.pool.misc[slot].y;
+                        L = L + beta * power_heuristic(dir_pdf, pdf_light) * Le;
+                    }
+                }
+                terminate = true;
+            }
             if (!terminate) {
                 int mat;
                 if (prim >= (int)wf.bvh.n_tris) {
@@ -645,9 +755,9 @@ __global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf) {
                 wf.pool.ids[slot] = ids;
             }
         }
-        const int cat = (act && terminate) ? 3 : route; // 0..2 material queue, 3 free list, -1 nothing
+        const int cat = (act && terminate) ? WF_NMAT : route; // material queue, WF_NMAT = free list, -1 nothing
         if (act) wf.pool.state[slot] = terminate ? ST_FREE : uint8_t(ST_MAT0 + route);
-        block_push<4>(cat, slot, counters, queues);
+        block_push<WF_NMAT + 1>(cat, slot, counters, queues);
     }
     // finished-path count: warp reduce, one atomic per warp
     for (int o = 16; o > 0; o >>= 1) n_finished += __shfl_xor_sync(0xffffffffu, n_finished, o);
@@ -766,6 +876,15 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_DIELECTRIC>(const WF &wf, c
     b.d = make_trdist(ur, vr);
 }
 
+template <>
+__device__ __forceinline__ void make_bsdf<B200PT_MAT_DIFFUSE_TRANSMISSION>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda,
+                                                                           S4 &lpdf, bool &lpdf_dirty,
+                                                                           BSDF<B200PT_MAT_DIFFUSE_TRANSMISSION> &b) {
+    // materials/diffuse_transmission_material.cu:25-31
+    b.r = clamp_s4(spectrum_sample(wf.spectra, m.reflectance, lambda) * m.scale, 0.f, 1.f);
+    b.t = clamp_s4(spectrum_sample(wf.spectra, m.transmittance, lambda) * m.scale, 0.f, 1.f);
+}
+
 // ---- gpu_evaluate_material + sample_bsdf + sample_Ld_volume, specialised per material
 template <int MAT>
 __global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf) {
@@ -828,16 +947,23 @@ __global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf) {
                 if (wf.n_lights > 0) {
                     const int li = alias_sample(wf.alias, wf.n_lights, ul);
                     const LightRec Lr = wf.lights[li];
+                    const int lt = light_type(Lr);
                     LightSample ls;
-                    if (light_sample(Lr, ctx, up, ls) && light_emits_towards(Lr, ls.n, -ls.wi)) {
-                        const S4 Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * Lr.scale;
+                    bool have, delta = false;
+                    float lw = 1.f, ld2 = 1.f;
+                    if (lt == B200PT_LIGHT_AREA) have = light_sample(Lr, ctx, up, ls) && light_emits_towards(Lr, ls.n, -ls.wi);
+                    else have = light_sample_other(Lr, lt, wf.light_ext, wf.scene_radius, ctx, up, ls, &lw, &ld2, &delta);
+                    if (have) {
+                        S4 Le;
+                        if (lt == B200PT_LIGHT_SPOT) Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * (lw * Lr.scale) / ld2;
+                        else Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * Lr.scale;
                         if (is_positive(Le) && wo_l.z != 0.f) {
                             const V3 wi_l = bsdf.frame.to_local(ls.wi);
                             const S4 f = bsdf.f(wo_l, wi_l) * absdot(ls.wi, si.ns);
                             if (is_positive(f)) {
                                 const float pdf_light = Lr.pmf * ls.pdf;
-                                const float pdf_bsdf = bsdf.pdf(wo_l, wi_l);
-                                const float w = power_heuristic(pdf_light, pdf_bsdf);
+                                // delta lights: no MIS (megakernel_path.cu:236-239)
+                                const float w = delta ? 1.f : power_heuristic(pdf_light, bsdf.pdf(wo_l, wi_l));
                                 const S4 Ld = f * (Le / pdf_light) * w;
                                 // visibility: Ray::spawn_ray_to (base/ray.h:51-58) from the surface point to the
                                 // light point, both ends offset; the segment (0, 1] of the un-normalised ray covers
@@ -926,7 +1052,9 @@ static int ensure_pool(b200pt_scene *s, int pool_size) {
     if ((rc = pool_alloc(r, &P.ids, n))) return rc;
     if ((rc = pool_alloc(r, &P.state, n))) return rc;
     WFQueues &Q = r->q;
-    int32_t **qs[] = {&Q.mat[0], &Q.mat[1], &Q.mat[2], &Q.free_slots, &Q.sh_slot};
+    for (int m = 0; m < WF_NMAT; m++)
+        if ((rc = pool_alloc(r, &Q.mat[m], r->has_mat[m] ? n : 1))) return rc;
+    int32_t **qs[] = {&Q.free_slots, &Q.sh_slot};
     for (int32_t **q : qs)
         if ((rc = pool_alloc(r, q, n))) return rc;
     if ((rc = pool_alloc(r, &Q.sh_o, n))) return rc;
@@ -1035,6 +1163,12 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     wf.materials = r->d_materials;
     wf.lights = r->d_lights;
     wf.alias = r->d_alias;
+    wf.light_ext = r->d_light_ext;
+    wf.n_infinite = r->n_infinite;
+    for (int k = 0; k < 4; k++) wf.infinite[k] = r->infinite[k];
+    wf.scene_radius = r->scene_radius;
+    int n_shade_kernels = 0;
+    for (int m = 0; m < WF_NMAT; m++) n_shade_kernels += r->has_mat[m] ? 1 : 0;
     wf.n_lights = r->n_lights;
     wf.filter = r->filter;
     wf.camera = r->camera;
@@ -1082,13 +1216,15 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
             k_logic<<<grid, WF_BLOCK, 0, st>>>(wf);
             k_generate<<<grid, WF_BLOCK, 0, st>>>(wf);
             k_after_generate<<<1, 1, 0, st>>>(wf);
-            k_shade<B200PT_MAT_DIFFUSE><<<grid, WF_BLOCK, 0, st>>>(wf);
-            k_shade<B200PT_MAT_CONDUCTOR><<<grid, WF_BLOCK, 0, st>>>(wf);
-            k_shade<B200PT_MAT_DIELECTRIC><<<grid, WF_BLOCK, 0, st>>>(wf);
+            // one shade kernel per material type PRESENT in the scene (a type without materials has no queue)
+            if (r->has_mat[B200PT_MAT_DIFFUSE]) k_shade<B200PT_MAT_DIFFUSE><<<grid, WF_BLOCK, 0, st>>>(wf);
+            if (r->has_mat[B200PT_MAT_CONDUCTOR]) k_shade<B200PT_MAT_CONDUCTOR><<<grid, WF_BLOCK, 0, st>>>(wf);
+            if (r->has_mat[B200PT_MAT_DIELECTRIC]) k_shade<B200PT_MAT_DIELECTRIC><<<grid, WF_BLOCK, 0, st>>>(wf);
+            if (r->has_mat[B200PT_MAT_DIFFUSE_TRANSMISSION]) k_shade<B200PT_MAT_DIFFUSE_TRANSMISSION><<<grid, WF_BLOCK, 0, st>>>(wf);
             if ((rc = launch_trace_wf(s, wf, true))) return rc;
             k_pass_end<<<1, 1, 0, st>>>(wf);
             passes++;
-            launches += 10;
+            launches += 7 + n_shade_kernels;
         }
         CU_TRY(cudaGetLastError());
         const int cur = int(k & 1);

@@ -18,8 +18,11 @@ namespace b200pt {
 struct MatRec {
     int32_t type, reflectance, eta, k;
     float u_rough, v_rough;
-    int32_t remap, pad;
+    int32_t remap, transmittance;
+    float scale;
+    int32_t pad[3];
 };
+constexpr int WF_NMAT = B200PT_MAT_COUNT; // one shading queue per material type
 
 struct FilterTab {
     int32_t nx, ny;
@@ -51,7 +54,7 @@ struct FilmRec {
 constexpr int PF_SPECULAR = 1, PF_ANY_NON_SPECULAR = 2;
 
 // per-slot state byte: what the next stage has to do with the slot
-enum : uint8_t { ST_IDLE = 0, ST_RAY = 1, ST_MAT0 = 2 /* + material type */, ST_FREE = 5 };
+enum : uint8_t { ST_IDLE = 0, ST_RAY = 1, ST_MAT0 = 2 /* + material type */, ST_FREE = ST_MAT0 + WF_NMAT };
 
 struct PathPool {
     float4 *ray_o;  // o.xyz, tmax (< 0: dead path, skipped by the trace kernel)
@@ -68,7 +71,7 @@ struct PathPool {
 };
 
 struct WFCounters {
-    unsigned n_mat[3];
+    unsigned n_mat[WF_NMAT];
     unsigned n_free;
     unsigned n_shadow;
     unsigned ticket_closest;
@@ -77,7 +80,7 @@ struct WFCounters {
 };
 
 struct WFQueues {
-    int32_t *mat[3];
+    int32_t *mat[WF_NMAT];
     int32_t *free_slots;
     // shadow rays: compact SoA by queue position
     float4 *sh_o, *sh_d, *sh_contrib;
@@ -97,7 +100,11 @@ struct WF {
     const MatRec *materials;
     const LightRec *lights;
     const AliasBin *alias;
+    const LightExt *light_ext;
     int32_t n_lights;
+    int32_t n_infinite;      // infinite lights looked up by escaping rays (integrators/wavefront_path.cu:105-127)
+    int32_t infinite[4];     // their light ids
+    float scene_radius;      // Bounds3::bounding_sphere of the whole scene (scene_builder.cu:914-925)
     FilterTab filter;
     CameraRec camera;
     FilmRec film;

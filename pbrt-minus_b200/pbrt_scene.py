@@ -437,9 +437,86 @@ class Scene:
             ro = p_float(p, "roughness", 0.0)
             self.materials.append({"type": 2, "reflectance": -1, "eta": eta, "k": -1, "ur": p_float(p, "uroughness", ro),
                                    "vr": p_float(p, "vroughness", ro), "remap": int(p_bool(p, "remaproughness", True))})
+        elif kind == "diffusetransmission":
+            # materials/diffuse_transmission_material.cu:8-23 (constant-float textures of 0.25 when absent)
+            r = self.spec_param(p, "reflectance", "albedo", scene_dir)
+            t = self.spec_param(p, "transmittance", "albedo", scene_dir)
+            self.materials.append({"type": 3, "reflectance": self.spec_constant(0.25) if r is None else r, "eta": -1, "k": -1,
+                                   "ur": 0.0, "vr": 0.0, "remap": 1, "transmittance": self.spec_constant(0.25) if t is None else t,
+                                   "scale": p_float(p, "scale", 1.0)})
         else:
             raise SceneError("Material '%s' is outside the hot path (SURVEY.md 8f)" % kind)
         return len(self.materials) - 1
+
+    # ---- lights that are not emissive shapes (SceneBuilder::parse_light_source, scene_builder.cu:493-504)
+    def add_light_source(self, kind, p, render_from_light, scene_dir):
+        def illum(name):
+            sid = self.spec_param(p, name, "illuminant", scene_dir)
+            if sid is None:
+                lam, val, _ = spectral.illuminant_d65()
+                sid = self.spec_piecewise(("illuminant",), lam, val)
+            return sid
+
+        def vnorm(v):
+            v = np.asarray(v, dtype=F32)
+            return (v / F32(np.sqrt(F32(F32(v[0] * v[0]) + F32(v[1] * v[1])) + F32(v[2] * v[2])))).astype(F32)
+
+        def coordinate_system(v):       # euclidean_space/vector3.h:161-167, all in fp32
+            x, y, z = (F32(c) for c in v)
+            sign = F32(np.copysign(1.0, z))
+            a = F32(F32(-1.0) / F32(sign + z))
+            b = F32(F32(x * y) * a)
+            v2 = np.array([F32(F32(1) + F32(F32(sign * F32(x * x)) * a)), F32(sign * b), F32(-sign * x)], dtype=F32)
+            v3 = np.array([b, F32(sign + F32(F32(y * y) * a)), F32(-y)], dtype=F32)
+            return v2, v3
+
+        rec = {"triangle": -1, "two_sided": 0, "v": [0.0, 0.0, 0.0], "lfr": [0.0] * 9, "cs": 0.0, "ce": 0.0}
+        frm = np.asarray(p["from"][1][:3] if "from" in p else (0, 0, 0), dtype=F32)
+        to = np.asarray(p["to"][1][:3] if "to" in p else (0, 0, 1), dtype=F32)
+        sc = F32(p_float(p, "scale", 1.0))
+        if kind == "distant":           # lights/distant_light.cu:10-41
+            L = illum("L")
+            w = vnorm((frm - to).astype(F32))
+            v1, v2 = coordinate_system(w)
+            m = np.eye(4, dtype=F32)
+            m[:3, 0], m[:3, 1], m[:3, 2] = v1, v2, w
+            final = render_from_light * Xf(m)
+            sc = F32(sc / self.photometric(L))
+            ev = p_float(p, "illuminance", -1.0)
+            if ev > 0:
+                sc = F32(sc * F32(ev))
+            rec.update({"type": 1, "spectrum": L, "scale": float(sc), "v": [float(x) for x in final.m[:3, 2]]})
+        elif kind == "infinite":        # lights/uniform_infinite_light.cu:7-32
+            if "filename" in p:
+                raise SceneError("LightSource 'infinite' with an image map is outside the hot path (SURVEY.md 8f)")
+            L = illum("L")
+            sc = F32(sc / self.photometric(L))
+            ev = p_float(p, "illuminance", -1.0)
+            if ev > 0:
+                sc = F32(np.float64(sc) * (np.float64(F32(ev)) / np.float64(F32(np.pi))))
+            rec.update({"type": 2, "spectrum": L, "scale": float(sc)})
+        elif kind == "spot":            # lights/spot_light.cu:8-41
+            I = illum("I")
+            cone, delta = F32(p_float(p, "coneangle", 30.0)), F32(p_float(p, "conedeltaangle", 5.0))
+            z = vnorm((to - frm).astype(F32))
+            x, y = coordinate_system(z)
+            m = np.eye(4, dtype=F32)
+            m[0, :3], m[1, :3], m[2, :3] = x, y, z
+            dir_to_z = Xf(m)
+            final = render_from_light * (translate(*frm) * dir_to_z.inverse())
+            sc = F32(sc / self.photometric(I))
+            rad = lambda d: F32(np.float64(F32(np.pi)) / 180.0 * np.float64(F32(d)))
+            ce, cs = F32(np.cos(np.float64(rad(cone)))), F32(np.cos(np.float64(rad(F32(cone - delta)))))
+            pw = p_float(p, "power", -1.0)
+            if pw > 0:
+                ke = 2 * np.float64(F32(np.pi)) * ((1 - np.float64(cs)) + (np.float64(cs) - np.float64(ce)) / 2)
+                sc = F32(np.float64(sc) * (np.float64(F32(pw)) / ke))
+            pos = xf_points(final.m, [[0, 0, 0]])[0]
+            rec.update({"type": 3, "spectrum": I, "scale": float(sc), "v": [float(v) for v in pos],
+                        "lfr": [float(v) for v in final.inv[:3, :3].reshape(-1)], "cs": float(cs), "ce": float(ce)})
+        else:
+            raise SceneError("LightSource '%s' is outside the hot path (SURVEY.md 8f)" % kind)
+        self.lights.append(rec)
 
     # ---- geometry
     def add_mesh(self, P, idx, material, flip, light_params, scene_dir):
@@ -519,10 +596,16 @@ class Scene:
         for i, m in enumerate(self.materials):
             mats[i].type, mats[i].reflectance, mats[i].eta, mats[i].k = m["type"], m["reflectance"], m["eta"], m["k"]
             mats[i].u_roughness, mats[i].v_roughness, mats[i].remap_roughness = m["ur"], m["vr"], m["remap"]
+            mats[i].transmittance, mats[i].scale = m.get("transmittance", -1), m.get("scale", 1.0)
         d.n_materials, d.materials = len(self.materials), mats
         lights = (api.Light * max(1, len(self.lights)))()
         for i, l in enumerate(self.lights):
             lights[i].triangle, lights[i].spectrum, lights[i].scale, lights[i].two_sided = l["triangle"], l["spectrum"], l["scale"], l["two_sided"]
+            lights[i].type = l.get("type", 0)
+            if lights[i].type:
+                lights[i].v[:] = l["v"]
+                lights[i].light_from_render[:] = l["lfr"]
+                lights[i].cos_falloff_start, lights[i].cos_falloff_end = l["cs"], l["ce"]
         d.n_lights, d.lights = len(self.lights), lights
         keep += [sph, spec, mats, lights]
         if self.camera is not None:
@@ -692,7 +775,9 @@ def load(path=None, text=None, spp=None, integrator=None):
                                    "ro": g.reverse_orientation, "swaps": swaps_handedness(rfo), "material": g.material})
             else:
                 raise SceneError("Shape '%s' is outside the hot path (SURVEY.md 8f)" % args[0])
-        elif kw in ("ObjectBegin", "ObjectEnd", "ObjectInstance", "LightSource", "MakeNamedMedium", "MediumInterface", "Texture"):
+        elif kw == "LightSource":
+            sc.add_light_source(args[0], params_of(args[1:]), render_from_world * g.ctm, scene_dir)
+        elif kw in ("ObjectBegin", "ObjectEnd", "ObjectInstance", "MakeNamedMedium", "MediumInterface", "Texture"):
             raise SceneError("directive '%s' is outside the hot path (SURVEY.md 8f)" % kw)
         elif kw in ("ColorSpace", "Option", "Attribute"):
             continue

@@ -103,6 +103,10 @@ def read_hits(path, n):
 # diffuse / conductor / dielectric materials, a ceiling grid of small emissive quads for the power
 # light sampler.  Written as one .pbrt + binary little-endian PLY files so that the reference's CLI
 # and this package's front-end read identical bits.
+# C4 in miniature: the scene behind tests/golden/films/c4tiny_96x54_1024spp.f32 (tools/make_golden.py)
+C4_TINY = dict(n_meshes=6, grid=48, n_light_quads=200, width=96, height=54, seed=7, name="c4tiny")
+
+
 def _value_noise(u, v, rng, lattice=8, octaves=4):
     """periodic 2-D value noise on [0,1)^2: seeded lattice values, smoothstep interpolation, `octaves`
     octaves of halving amplitude; result in about [-1, 1]"""

@@ -96,6 +96,56 @@ def test_materials_scene_matches_reference(b200pt, tmp_path):
     check_against_golden(b200pt, tmp_path, "materials_96x64_1024spp")
 
 
+def test_light_sources_and_diffuse_transmission_match_reference(b200pt, tmp_path):
+    """LightSource "infinite" (uniform), "distant", "spot" next to an area light, and Material "diffusetransmission"
+    (SURVEY 8f rows 1-2): escaping rays pick up the infinite light's Le with the reference's MIS weight
+    (integrators/wavefront_path.cu:105-127), delta lights skip MIS (megakernel_path.cu:236-239).  Same paths as the
+    reference, so the fp-order tolerance applies (measured relMSE 2.5e-9)."""
+    check_against_golden(b200pt, tmp_path, "lights_96x64_64spp")
+    check_against_golden(b200pt, tmp_path, "lights_96x64_1024spp")
+
+
+def test_many_lights_statistical_gate(b200pt, tmp_path):
+    """Config C4 in miniature (workloads.procedural_scene: displaced meshes from PLY files, 400 emissive triangles
+    of 64 radiance levels).  The reference builds its alias table with a full re-sort per step
+    (distribution/alias_table.cu:43-62); among equal-power lights the order is libstdc++'s introsort state, so the
+    light picked for a given random number differs from ours and the two renderers are two different unbiased
+    estimators of the same image.  Gate: relMSE <= 1.5 * tau, tau = 2 mean(sigma_p^2 / (mu_p^2 + 1e-4)) the
+    value two independent N-spp estimators would show, sigma_p^2 from 16 disjoint sample ranges of ours; at most 1.5 %
+    of the lit pixels beyond 3 sigma of the difference (0.27 % for Gaussian noise; path-traced pixels are
+    heavier-tailed and sigma comes from 16 sub-renders); mean image brightness within 0.5 %."""
+    m, ref = golden("c4tiny_96x54_1024spp")
+    path, info = b200pt.workloads.procedural_scene(str(tmp_path), **b200pt.workloads.C4_TINY)
+    assert info["emissive_triangles"] == 400
+    sc = b200pt.pbrt_scene.load(path, spp=m["spp"])
+    integ = b200pt.WavefrontPathIntegrator(sc, device=0)
+    film = integ.create_film()
+    K = 16
+    parts = []
+    for k in range(K):
+        b, e = b200pt.sample_range(m["spp"], k, K)
+        film.clear()
+        integ.render(film, sample_begin=b, sample_end=e)
+        parts.append(film.raw().astype(np.float64))
+    film.clear()
+    integ.render(film)
+    ours = film.get_pixel_rgb().astype(np.float64)
+    raw = np.stack(parts)
+    w = raw[..., 3:4]
+    xyz = np.where(w != 0, raw[..., :3] / np.where(w == 0, 1, w), 0.0)
+    M = np.asarray(b200pt.spectral.srgb_color_space()["rgb_from_xyz"], dtype=np.float64)
+    var_mean = (xyz @ M.T).var(axis=0, ddof=1) / K
+    ref = ref.astype(np.float64)
+    d = ours - ref
+    rel = float(np.mean(d ** 2 / (ref ** 2 + 1e-4)))
+    tau = float(np.mean(2.0 * var_mean / (ours ** 2 + 1e-4)))
+    lit = var_mean.max(axis=2) > 0
+    beyond = ((np.abs(d) > 3.0 * np.sqrt(2.0 * var_mean) + 1e-6).any(axis=2) & lit).sum() / max(1, lit.sum())
+    assert rel <= 1.5 * tau, "relMSE %.3e vs tau %.3e" % (rel, tau)
+    assert beyond <= 0.015, "%.4f of the lit pixels beyond 3 sigma" % beyond
+    assert abs(ours.mean() - ref.mean()) <= 0.005 * ref.mean()
+
+
 def test_cornell_converged_4096spp(b200pt, tmp_path):
     ours, ref = check_against_golden(b200pt, tmp_path, "cornell_48_4096spp", res=(48, 48))
     # the reference's megakernel integrator (one thread per pixel, same estimator) as a second oracle

@@ -22,7 +22,13 @@ CASES = [
     ("cornell_64_9spp_independent", "cornell-box-specular.pbrt", (64, 64), 9, None, "independent"),
     ("materials_96x64_64spp", "materials.pbrt", None, 64, None, None),
     ("materials_96x64_1024spp", "materials.pbrt", None, 1024, None, None),
+    # LightSource infinite / distant / spot + diffusetransmission
+    ("lights_96x64_64spp", "lights.pbrt", None, 64, None, None),
+    ("lights_96x64_1024spp", "lights.pbrt", None, 1024, None, None),
+    # C4 in miniature (workloads.procedural_scene, seed 7): many lights -> statistical gate only
+    ("c4tiny_96x54_1024spp", "@c4tiny", None, 1024, None, None),
 ]
+
 
 
 def main():
@@ -30,8 +36,18 @@ def main():
     os.makedirs(out, exist_ok=True)
     exe = os.path.join(ROOT, "oracle", "_ref", "pbrt-minus-ref")
     manifest = {}
+    only = sys.argv[1:]
     for name, scene, res, spp, integ, sampler in CASES:
-        text = open(os.path.join(ROOT, "tests", "scenes", scene)).read()
+        if only and name not in only:
+            continue
+        if scene == "@c4tiny":
+            sys.path.insert(0, ROOT)
+            import importlib
+            pkg = importlib.import_module("pbrt-minus_b200")
+            path, _ = pkg.workloads.procedural_scene(out, **pkg.workloads.C4_TINY)
+            text = open(path).read()
+        else:
+            text = open(os.path.join(ROOT, "tests", "scenes", scene)).read()
         if res:
             text = with_resolution(text, *res)
         if sampler:
@@ -53,7 +69,7 @@ def main():
         manifest[name] = {"scene": scene, "width": W, "height": H, "spp": spp, "integrator": integ or "path", "sampler": sampler or "stratified",
                           "mean": float(film.mean()), "reference_render_s": float(took.group(1)) if took else None}
         print(name, manifest[name])
-    json.dump(manifest, open(os.path.join(out, "manifest.json"), "w"), indent=1)
+    json.dump(manifest, open(os.path.join(out, "manifest_new.json" if only else "manifest.json"), "w"), indent=1)
 
 
 if __name__ == "__main__":

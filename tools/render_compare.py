@@ -39,6 +39,7 @@ def main():
     ap.add_argument("--integrator", default=None)
     ap.add_argument("--tag", default="cmp")
     args = ap.parse_args()
+    args.out = os.path.abspath(args.out)
     os.makedirs(args.out, exist_ok=True)
     pkg = importlib.import_module("pbrt-minus_b200")
     text = open(args.scene).read()
