@@ -41,7 +41,15 @@ def main():
     r = int(round(total_spp ** 0.5))
     assert r * r == total_spp, "total spp %d must be a perfect square for the stratified sampler" % total_spp
     text = with_resolution(open(args.scene).read(), *args.res)
-    sc = pkg.pbrt_scene.load(text=text, spp=total_spp)
+    # the scene is loaded from a file beside the original so that relative PLY / spectrum paths resolve
+    sp = os.path.join(os.path.dirname(os.path.abspath(args.scene)), ".render_multi_rank%d.pbrt" % rank)
+    try:
+        open(sp, "w").write(text)
+    except OSError:
+        sp = None
+    sc = pkg.pbrt_scene.load(sp, spp=total_spp) if sp else pkg.pbrt_scene.load(text=text, spp=total_spp)
+    if sp:
+        os.remove(sp)
     integ = pkg.WavefrontPathIntegrator(sc, device=local)
     film = integ.create_film()
     b, e = pkg.sample_range(total_spp, rank, world)
