@@ -63,7 +63,7 @@ typedef struct {
 
 /* ---- materials (base/material.cu:97-131) ------------------------------------------------ */
 enum { B200PT_MAT_DIFFUSE = 0, B200PT_MAT_CONDUCTOR = 1, B200PT_MAT_DIELECTRIC = 2, B200PT_MAT_DIFFUSE_TRANSMISSION = 3,
-       B200PT_MAT_COUNT = 4 };
+       B200PT_MAT_COATED_DIFFUSE = 4, B200PT_MAT_COATED_CONDUCTOR = 5, B200PT_MAT_COUNT = 6 };
 typedef struct {
     int32_t type;
     int32_t reflectance; /* spectrum id: diffuse reflectance, or conductor "reflectance" (-1: use eta/k) */
@@ -73,6 +73,14 @@ typedef struct {
     int32_t remap_roughness; /* materials/conductor_material.cu:52-75: alpha = sqrt(roughness) */
     int32_t transmittance;   /* spectrum id: diffuse-transmission "transmittance" (materials/diffuse_transmission_material.cu:8-31) */
     float scale;             /* diffuse-transmission "scale" */
+    /* coated diffuse / coated conductor (materials/coated_diffuse_material.cu, coated_conductor_material.cu; LayeredBxDF):
+     * u/v_roughness = the dielectric interface's roughness, eta = the interface's eta spectrum id,
+     * reflectance = the diffuse base (coated diffuse) or the conductor's "reflectance" (-1: use c_eta / c_k) */
+    float thickness, g;
+    int32_t albedo;          /* spectrum id of the medium albedo between the layers */
+    int32_t max_depth, n_samples;
+    float c_u_roughness, c_v_roughness; /* coated conductor: the conductor's roughness */
+    int32_t c_eta, c_k;                 /* coated conductor: the conductor's eta / k spectrum ids */
 } b200pt_material;
 
 /* ---- lights (base/light.cu:22-75), in the order the scene file creates them (= light-sampler index):

@@ -26,7 +26,10 @@ class Spectrum(C.Structure):
 class Material(C.Structure):
     _fields_ = [("type", C.c_int32), ("reflectance", C.c_int32), ("eta", C.c_int32), ("k", C.c_int32),
                 ("u_roughness", C.c_float), ("v_roughness", C.c_float), ("remap_roughness", C.c_int32),
-                ("transmittance", C.c_int32), ("scale", C.c_float)]
+                ("transmittance", C.c_int32), ("scale", C.c_float),
+                ("thickness", C.c_float), ("g", C.c_float), ("albedo", C.c_int32), ("max_depth", C.c_int32),
+                ("n_samples", C.c_int32), ("c_u_roughness", C.c_float), ("c_v_roughness", C.c_float),
+                ("c_eta", C.c_int32), ("c_k", C.c_int32)]
 
 
 class Light(C.Structure):

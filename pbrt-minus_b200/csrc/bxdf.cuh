@@ -24,7 +24,10 @@ struct BSDFSample {
     float pdf;
     uint32_t flags;
     float eta;
+    bool pdf_is_proportional; // LayeredBxDF samples: pdf is only proportional to the true density (base/bxdf.h BSDFSample)
 };
+// BxDFReflTransFlags (bxdfs/bxdf_util.h): which lobes a sample / pdf call may use
+constexpr uint32_t SF_REFLECTION = 1u, SF_TRANSMISSION = 2u, SF_ALL = 3u;
 
 __device__ __forceinline__ bool same_hemisphere(V3 a, V3 b) { return a.z * b.z > 0.f; }
 __device__ __forceinline__ float cos2_theta(V3 w) { return sqr(w.z); }
@@ -183,21 +186,21 @@ __device__ __forceinline__ S4 fr_complex4(float cos_i, S4 eta, S4 k) {
 template <int MAT>
 struct BSDF;
 
-template <>
-struct BSDF<B200PT_MAT_DIFFUSE> {
-    Frame frame;
+struct DiffuseCore {
     S4 r;
     __device__ __forceinline__ uint32_t flags() const { return is_positive(r) ? (BXDF_DIFFUSE | BXDF_REFLECTION) : 0u; }
     __device__ __forceinline__ void regularize() {}
-    __device__ __forceinline__ S4 f(V3 wo, V3 wi) const {
+    __device__ __forceinline__ S4 f(V3 wo, V3 wi, bool radiance = true) const {
         if (!same_hemisphere(wo, wi)) return s4(0.f);
         return r * kInvPi;
     }
-    __device__ __forceinline__ float pdf(V3 wo, V3 wi) const {
-        if (!same_hemisphere(wo, wi)) return 0.f;
+    __device__ __forceinline__ float pdf(V3 wo, V3 wi, uint32_t sf = SF_ALL) const {
+        if (!(sf & SF_REFLECTION) || !same_hemisphere(wo, wi)) return 0.f;
         return fabsf(wi.z) / kPi;
     }
-    __device__ __forceinline__ bool sample(V3 wo, float uc, float2 u, BSDFSample &bs) const {
+    __device__ __forceinline__ bool sample(V3 wo, float uc, float2 u, BSDFSample &bs, bool radiance = true, uint32_t sf = SF_ALL) const {
+        if (!(sf & SF_REFLECTION)) return false;
+        bs.pdf_is_proportional = false;
         V3 wi = sample_cosine_hemisphere(u);
         if (wo.z < 0.f) wi.z *= -1.f;
         bs.f = r * kInvPi;
@@ -207,6 +210,10 @@ struct BSDF<B200PT_MAT_DIFFUSE> {
         bs.eta = 1.f;
         return true;
     }
+};
+template <>
+struct BSDF<B200PT_MAT_DIFFUSE> : DiffuseCore {
+    Frame frame;
 };
 
 // DiffuseTransmissionBxDF (bxdfs/diffuse_transmission_bxdf.h:8-103)
@@ -227,6 +234,7 @@ struct BSDF<B200PT_MAT_DIFFUSE_TRANSMISSION> {
     __device__ __forceinline__ bool sample(V3 wo, float uc, float2 u, BSDFSample &bs) const {
         const float pr = max_component(r), pt = max_component(t);
         if (pr == 0.f && pt == 0.f) return false;
+        bs.pdf_is_proportional = false;
         V3 wi = sample_cosine_hemisphere(u);
         if (uc < pr / (pr + pt)) {
             if (wo.z < 0.f) wi.z *= -1.f;
@@ -244,14 +252,12 @@ struct BSDF<B200PT_MAT_DIFFUSE_TRANSMISSION> {
     }
 };
 
-template <>
-struct BSDF<B200PT_MAT_CONDUCTOR> {
-    Frame frame;
+struct ConductorCore {
     TRDist d;
     S4 eta, k;
     __device__ __forceinline__ uint32_t flags() const { return d.smooth() ? (BXDF_SPECULAR | BXDF_REFLECTION) : (BXDF_GLOSSY | BXDF_REFLECTION); }
     __device__ __forceinline__ void regularize() { d.regularize(); }
-    __device__ __forceinline__ S4 f(V3 wo, V3 wi) const {
+    __device__ __forceinline__ S4 f(V3 wo, V3 wi, bool radiance = true) const {
         if (!same_hemisphere(wo, wi) || d.smooth()) return s4(0.f);
         const float co = fabsf(wo.z), ci = fabsf(wi.z);
         if (ci == 0.f || co == 0.f) return s4(0.f);
@@ -261,15 +267,17 @@ struct BSDF<B200PT_MAT_CONDUCTOR> {
         const S4 F = fr_complex4(absdot(wo, wm), eta, k);
         return F * (d.D(wm) * d.G(wo, wi) / (4.f * ci * co));
     }
-    __device__ __forceinline__ float pdf(V3 wo, V3 wi) const {
-        if (!same_hemisphere(wo, wi) || d.smooth()) return 0.f;
+    __device__ __forceinline__ float pdf(V3 wo, V3 wi, uint32_t sf = SF_ALL) const {
+        if (!(sf & SF_REFLECTION) || !same_hemisphere(wo, wi) || d.smooth()) return 0.f;
         V3 wm = wo + wi;
         if (len2(wm) == 0.f) return 0.f;
         wm = face_forward(normalize(wm), v3(0.f, 0.f, 1.f));
         return d.pdf(wo, wm) / (4.f * absdot(wo, wm));
     }
-    __device__ __forceinline__ bool sample(V3 wo, float uc, float2 u, BSDFSample &bs) const {
+    __device__ __forceinline__ bool sample(V3 wo, float uc, float2 u, BSDFSample &bs, bool radiance = true, uint32_t sf = SF_ALL) const {
+        if (!(sf & SF_REFLECTION)) return false;
         bs.eta = 1.f;
+        bs.pdf_is_proportional = false;
         if (d.smooth()) {
             const V3 wi = v3(-wo.x, -wo.y, wo.z);
             bs.f = fr_complex4(fabsf(wi.z), eta, k) / fabsf(wi.z);
@@ -292,10 +300,12 @@ struct BSDF<B200PT_MAT_CONDUCTOR> {
         return true;
     }
 };
-
 template <>
-struct BSDF<B200PT_MAT_DIELECTRIC> {
+struct BSDF<B200PT_MAT_CONDUCTOR> : ConductorCore {
     Frame frame;
+};
+
+struct DielectricCore {
     TRDist d;
     float eta;
     __device__ __forceinline__ bool specular() const { return eta == 1.f || d.smooth(); }
@@ -316,7 +326,7 @@ struct BSDF<B200PT_MAT_DIELECTRIC> {
         if (dot(wm, wi) * ci < 0.f || dot(wm, wo) * co < 0.f) return false;
         return true;
     }
-    __device__ __forceinline__ S4 f(V3 wo, V3 wi) const {
+    __device__ __forceinline__ S4 f(V3 wo, V3 wi, bool radiance = true) const {
         if (specular()) return s4(0.f);
         V3 wm;
         float etap;
@@ -326,30 +336,34 @@ struct BSDF<B200PT_MAT_DIELECTRIC> {
         if (refl) return s4(d.D(wm) * d.G(wo, wi) * F / fabsf(4.f * wi.z * wo.z));
         const float denom = sqr(dot(wi, wm) + dot(wo, wm) / etap) * wi.z * wo.z;
         float ft = d.D(wm) * (1.f - F) * d.G(wo, wi) * fabsf(dot(wi, wm) * dot(wo, wm) / denom);
-        ft /= sqr(etap);
+        if (radiance) ft /= sqr(etap);
         return s4(ft);
     }
-    __device__ __forceinline__ float pdf(V3 wo, V3 wi) const {
+    __device__ __forceinline__ float pdf(V3 wo, V3 wi, uint32_t sf = SF_ALL) const {
         if (specular()) return 0.f;
         V3 wm;
         float etap;
         bool refl;
         if (!half_vector(wo, wi, wm, etap, refl)) return 0.f;
-        const float R = fr_dielectric(dot(wo, wm), eta), T = 1.f - R;
+        const float R0 = fr_dielectric(dot(wo, wm), eta), T0 = 1.f - R0;
+        const float R = (sf & SF_REFLECTION) ? R0 : 0.f, T = (sf & SF_TRANSMISSION) ? T0 : 0.f;
         if (R == 0.f && T == 0.f) return 0.f;
         if (refl) return d.pdf(wo, wm) / (4.f * absdot(wo, wm)) * R / (R + T);
         const float denom = sqr(dot(wi, wm) + dot(wo, wm) / etap);
         const float dwm_dwi = absdot(wi, wm) / denom;
         return d.pdf(wo, wm) * dwm_dwi * T / (R + T);
     }
-    __device__ __forceinline__ bool sample(V3 wo, float uc, float2 u, BSDFSample &bs) const {
+    // R0 / T0: Fresnel terms (they weight f); R / T: lobe selection probabilities under the sample flags
+    __device__ __forceinline__ bool sample(V3 wo, float uc, float2 u, BSDFSample &bs, bool radiance = true, uint32_t sf = SF_ALL) const {
         bs.eta = 1.f;
+        bs.pdf_is_proportional = false;
         if (specular()) {
-            const float R = fr_dielectric(wo.z, eta), T = 1.f - R;
+            const float R0 = fr_dielectric(wo.z, eta), T0 = 1.f - R0;
+            const float R = (sf & SF_REFLECTION) ? R0 : 0.f, T = (sf & SF_TRANSMISSION) ? T0 : 0.f;
             if (R == 0.f && T == 0.f) return false;
             if (uc < R / (R + T)) {
                 const V3 wi = v3(-wo.x, -wo.y, wo.z);
-                bs.f = s4(R / fabsf(wi.z));
+                bs.f = s4(R0 / fabsf(wi.z));
                 bs.wi = wi;
                 bs.pdf = R / (R + T);
                 bs.flags = BXDF_SPECULAR | BXDF_REFLECTION;
@@ -358,7 +372,9 @@ struct BSDF<B200PT_MAT_DIELECTRIC> {
             V3 wi;
             float etap;
             if (!refract(wo, v3(0.f, 0.f, 1.f), eta, &etap, &wi)) return false;
-            bs.f = s4(T / fabsf(wi.z) / sqr(etap));
+            float ft = T0 / fabsf(wi.z);
+            if (radiance) ft /= sqr(etap);
+            bs.f = s4(ft);
             bs.wi = wi;
             bs.pdf = T / (R + T);
             bs.flags = BXDF_SPECULAR | BXDF_TRANSMISSION;
@@ -366,13 +382,14 @@ struct BSDF<B200PT_MAT_DIELECTRIC> {
             return true;
         }
         const V3 wm = d.sample_wm(wo, u);
-        const float R = fr_dielectric(dot(wo, wm), eta), T = 1.f - R;
+        const float R0 = fr_dielectric(dot(wo, wm), eta), T0 = 1.f - R0;
+        const float R = (sf & SF_REFLECTION) ? R0 : 0.f, T = (sf & SF_TRANSMISSION) ? T0 : 0.f;
         if (R == 0.f && T == 0.f) return false;
         if (uc < R / (R + T)) {
             const V3 wi = reflect(wo, wm);
             if (!same_hemisphere(wo, wi)) return false;
             bs.pdf = d.pdf(wo, wm) / (4.f * absdot(wo, wm)) * R / (R + T);
-            bs.f = s4(d.D(wm) * d.G(wo, wi) * R / (4.f * wi.z * wo.z));
+            bs.f = s4(d.D(wm) * d.G(wo, wi) * R0 / (4.f * wi.z * wo.z));
             bs.wi = wi;
             bs.flags = BXDF_GLOSSY | BXDF_REFLECTION;
             return true;
@@ -384,14 +401,18 @@ struct BSDF<B200PT_MAT_DIELECTRIC> {
         const float denom = sqr(dot(wi, wm) + dot(wo, wm) / etap);
         const float dwm_dwi = absdot(wi, wm) / denom;
         bs.pdf = d.pdf(wo, wm) * dwm_dwi * T / (R + T);
-        float ft = T * d.D(wm) * d.G(wo, wi) * fabsf(dot(wi, wm) * dot(wo, wm) / (wi.z * wo.z * denom));
-        ft /= sqr(etap);
+        float ft = T0 * d.D(wm) * d.G(wo, wi) * fabsf(dot(wi, wm) * dot(wo, wm) / (wi.z * wo.z * denom));
+        if (radiance) ft /= sqr(etap);
         bs.f = s4(ft);
         bs.wi = wi;
         bs.flags = BXDF_GLOSSY | BXDF_TRANSMISSION;
         bs.eta = etap;
         return true;
     }
+};
+template <>
+struct BSDF<B200PT_MAT_DIELECTRIC> : DielectricCore {
+    Frame frame;
 };
 
 __device__ __forceinline__ bool flags_non_specular(uint32_t fl) { return (fl & (BXDF_DIFFUSE | BXDF_GLOSSY)) != 0u; }

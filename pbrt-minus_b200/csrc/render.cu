@@ -23,6 +23,7 @@
 #include <set>
 
 #include "bxdf.cuh"
+#include "layered.cuh"
 #include "common.cuh"
 #include "sampler.cuh"
 #include "sphere.cuh"
@@ -266,11 +267,17 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
     auto spec_ok = [&](int id) { return id >= 0 && id < desc->n_spectra; };
     for (int i = 0; i < desc->n_materials; i++) {
         const b200pt_material &m = desc->materials[i];
-        mats[i] = MatRec{m.type, m.reflectance, m.eta, m.k, m.u_roughness, m.v_roughness, m.remap_roughness, m.transmittance, m.scale, {0, 0, 0}};
+        mats[i] = MatRec{m.type, m.reflectance, m.eta, m.k, m.u_roughness, m.v_roughness, m.remap_roughness, m.transmittance, m.scale,
+                         m.thickness, m.g, m.albedo, m.max_depth, m.n_samples, m.c_u_roughness, m.c_v_roughness, m.c_eta, m.c_k, 0};
         bool ok = true;
         if (m.type >= 0 && m.type < WF_NMAT) r->has_mat[m.type] = true;
         if (m.type == B200PT_MAT_DIFFUSE) ok = spec_ok(m.reflectance);
         else if (m.type == B200PT_MAT_DIFFUSE_TRANSMISSION) ok = spec_ok(m.reflectance) && spec_ok(m.transmittance);
+        else if (m.type == B200PT_MAT_COATED_DIFFUSE)
+            ok = spec_ok(m.reflectance) && spec_ok(m.eta) && spec_ok(m.albedo) && m.max_depth >= 0 && m.n_samples >= 1;
+        else if (m.type == B200PT_MAT_COATED_CONDUCTOR)
+            ok = spec_ok(m.eta) && spec_ok(m.albedo) && m.max_depth >= 0 && m.n_samples >= 1 &&
+                 ((spec_ok(m.c_eta) && spec_ok(m.c_k)) || (m.c_eta < 0 && spec_ok(m.reflectance)));
         else if (m.type == B200PT_MAT_CONDUCTOR) ok = (spec_ok(m.eta) && spec_ok(m.k)) || (m.eta < 0 && spec_ok(m.reflectance));
         else if (m.type == B200PT_MAT_DIELECTRIC) ok = spec_ok(m.eta);
         else ok = false;
@@ -885,6 +892,71 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_DIFFUSE_TRANSMISSION>(const
     b.t = clamp_s4(spectrum_sample(wf.spectra, m.transmittance, lambda) * m.scale, 0.f, 1.f);
 }
 
+template <>
+struct BSDF<B200PT_MAT_COATED_DIFFUSE> : LayeredCore<DielectricCore, DiffuseCore> {
+    Frame frame;
+};
+template <>
+struct BSDF<B200PT_MAT_COATED_CONDUCTOR> : LayeredCore<DielectricCore, ConductorCore> {
+    Frame frame;
+};
+
+// the dielectric interface + slab parameters shared by the two coated materials
+template <class L>
+__device__ __forceinline__ void make_coat(const WF &wf, const MatRec &m, S4 lambda, S4 &lpdf, bool &lpdf_dirty, L &b) {
+    float ur = m.u_rough, vr = m.v_rough;
+    if (m.remap) {
+        ur = sqrtf(ur);
+        vr = sqrtf(vr);
+    }
+    float eta = spectrum_at(wf.spectra, m.eta, lambda.x);
+    if (!spectrum_is_constant(wf.spectra, m.eta)) {
+        if (!(lpdf.y == 0.f && lpdf.z == 0.f && lpdf.w == 0.f)) {
+            lpdf = make_float4(lpdf.x / 4.f, 0.f, 0.f, 0.f);
+            lpdf_dirty = true;
+        }
+    }
+    if (eta == 0.f) eta = 1.f;
+    b.top.eta = eta;
+    b.top.d = make_trdist(ur, vr);
+    // LayeredBxDF ctor (layered_bxdf.h:17-21): thickness = max(thickness, FLT_MIN)
+    b.thickness = fmaxf(m.thickness, FLT_MIN);
+    b.albedo = clamp_s4(spectrum_sample(wf.spectra, m.albedo, lambda), 0.f, 1.f);
+    b.g = clampf(m.g, -1.f, 1.f);
+    b.max_depth = m.max_depth;
+    b.n_samples = m.n_samples;
+}
+template <>
+__device__ __forceinline__ void make_bsdf<B200PT_MAT_COATED_DIFFUSE>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf,
+                                                                     bool &lpdf_dirty, BSDF<B200PT_MAT_COATED_DIFFUSE> &b) {
+    // materials/coated_diffuse_material.cu:53-86
+    b.bottom.r = clamp_s4(spectrum_sample(wf.spectra, m.reflectance, lambda), 0.f, 1.f);
+    make_coat(wf, m, lambda, lpdf, lpdf_dirty, b);
+}
+template <>
+__device__ __forceinline__ void make_bsdf<B200PT_MAT_COATED_CONDUCTOR>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf,
+                                                                       bool &lpdf_dirty, BSDF<B200PT_MAT_COATED_CONDUCTOR> &b) {
+    // materials/coated_conductor_material.cu:92-141
+    make_coat(wf, m, lambda, lpdf, lpdf_dirty, b);
+    S4 ce, ck;
+    if (m.c_eta >= 0) {
+        ce = spectrum_sample(wf.spectra, m.c_eta, lambda);
+        ck = spectrum_sample(wf.spectra, m.c_k, lambda);
+    } else {
+        const S4 r = clamp_s4(spectrum_sample(wf.spectra, m.reflectance, lambda), 0.f, 0.9999f);
+        ce = s4(1.f);
+        ck = 2.f * sqrt_s4(r) / sqrt_s4(clamp_s4(s4(1.f) + r * -1.f, 0.f, kInf));
+    }
+    b.bottom.eta = ce / b.top.eta;
+    b.bottom.k = ck / b.top.eta;
+    float ur = m.c_u_rough, vr = m.c_v_rough;
+    if (m.remap) {
+        ur = sqrtf(ur);
+        vr = sqrtf(vr);
+    }
+    b.bottom.d = make_trdist(ur, vr);
+}
+
 // ---- gpu_evaluate_material + sample_bsdf + sample_Ld_volume, specialised per material
 template <int MAT>
 __global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf) {
@@ -997,7 +1069,9 @@ __global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf) {
                 const bool spec = (bs.flags & BXDF_SPECULAR) != 0u;
                 ids.w = (ids.w & ~PF_SPECULAR) | (spec ? PF_SPECULAR : PF_ANY_NON_SPECULAR);
                 float4 misc = wf.pool.misc[slot];
-                misc.y = bs.pdf;
+                // prev_direction_pdf (wavefront_path.cu:466-467): layered samples carry a pdf that is only proportional, so
+                // BSDF::pdf is evaluated -- on the render-space wi brought back to the local frame, as BSDF::pdf does
+                misc.y = bs.pdf_is_proportional ? bsdf.pdf(wo_l, bsdf.frame.to_local(wi)) : bs.pdf;
                 wf.pool.misc[slot] = misc;
                 wf.pool.ctx0[slot] = make_float4(si.p.x, si.p.y, si.p.z, si.err.x);
                 wf.pool.ctx1[slot] = make_float4(si.n.x, si.n.y, si.n.z, si.err.y);
@@ -1221,6 +1295,8 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
             if (r->has_mat[B200PT_MAT_CONDUCTOR]) k_shade<B200PT_MAT_CONDUCTOR><<<grid, WF_BLOCK, 0, st>>>(wf);
             if (r->has_mat[B200PT_MAT_DIELECTRIC]) k_shade<B200PT_MAT_DIELECTRIC><<<grid, WF_BLOCK, 0, st>>>(wf);
             if (r->has_mat[B200PT_MAT_DIFFUSE_TRANSMISSION]) k_shade<B200PT_MAT_DIFFUSE_TRANSMISSION><<<grid, WF_BLOCK, 0, st>>>(wf);
+            if (r->has_mat[B200PT_MAT_COATED_DIFFUSE]) k_shade<B200PT_MAT_COATED_DIFFUSE><<<grid, WF_BLOCK, 0, st>>>(wf);
+            if (r->has_mat[B200PT_MAT_COATED_CONDUCTOR]) k_shade<B200PT_MAT_COATED_CONDUCTOR><<<grid, WF_BLOCK, 0, st>>>(wf);
             if ((rc = launch_trace_wf(s, wf, true))) return rc;
             k_pass_end<<<1, 1, 0, st>>>(wf);
             passes++;

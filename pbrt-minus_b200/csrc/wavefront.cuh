@@ -20,7 +20,11 @@ struct MatRec {
     float u_rough, v_rough;
     int32_t remap, transmittance;
     float scale;
-    int32_t pad[3];
+    float thickness, g;           // coated materials (layered.cuh)
+    int32_t albedo, max_depth, n_samples;
+    float c_u_rough, c_v_rough;
+    int32_t c_eta, c_k;
+    int32_t pad;
 };
 constexpr int WF_NMAT = B200PT_MAT_COUNT; // one shading queue per material type
 

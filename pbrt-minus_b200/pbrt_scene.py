@@ -444,6 +444,46 @@ class Scene:
             self.materials.append({"type": 3, "reflectance": self.spec_constant(0.25) if r is None else r, "eta": -1, "k": -1,
                                    "ur": 0.0, "vr": 0.0, "remap": 1, "transmittance": self.spec_constant(0.25) if t is None else t,
                                    "scale": p_float(p, "scale", 1.0)})
+        elif kind == "coateddiffuse":
+            # materials/coated_diffuse_material.cu:9-51
+            r = self.spec_param(p, "reflectance", "albedo", scene_dir)
+            ro = p_float(p, "roughness", 0.0)
+            self.materials.append({"type": 4, "reflectance": self.spec_constant(0.5) if r is None else r,
+                                   "eta": self.spec_constant(p_float(p, "eta", 1.5)), "k": -1,
+                                   "ur": p_float(p, "uroughness", ro), "vr": p_float(p, "vroughness", ro),
+                                   "remap": int(p_bool(p, "remaproughness", True)), "thickness": p_float(p, "thickness", 0.01),
+                                   "g": p_float(p, "g", 0.0), "albedo": self.spec_constant(p_float(p, "albedo", 0.0)),
+                                   "max_depth": p_int(p, "maxdepth", 10), "n_samples": p_int(p, "nsamples", 1)})
+        elif kind == "coatedconductor":
+            # materials/coated_conductor_material.cu:26-90
+            def rough(primary, secondary):
+                return p_float(p, primary, p_float(p, secondary, 0.0))
+            if "interface.eta" in p and p["interface.eta"][0] == "float":
+                ieta = self.spec_constant(p["interface.eta"][1][0])
+            else:
+                ieta = self.spec_param(p, "interface.eta", "unbounded", scene_dir)
+            if ieta is None:
+                ieta = self.spec_constant(1.5)
+            ceta = self.spec_param(p, "conductor.eta", "unbounded", scene_dir)
+            ck = self.spec_param(p, "conductor.k", "unbounded", scene_dir)
+            refl = self.spec_param(p, "reflectance", "albedo", scene_dir)
+            if refl is not None and (ceta is not None or ck is not None):
+                raise SceneError("coatedconductor: both reflectance and (eta, k) given")
+            if refl is None:
+                if ceta is None:
+                    ceta = self.spec_piecewise(("named", "metal-Cu-eta"), *spectral.named_spectrum("metal-Cu-eta"))
+                if ck is None:
+                    ck = self.spec_piecewise(("named", "metal-Cu-k"), *spectral.named_spectrum("metal-Cu-k"))
+            alb = self.spec_param(p, "albedo", "albedo", scene_dir)
+            self.materials.append({"type": 5, "reflectance": -1 if refl is None else refl, "eta": ieta, "k": -1,
+                                   "ur": rough("interface.uroughness", "interface.roughness"),
+                                   "vr": rough("interface.vroughness", "interface.roughness"),
+                                   "remap": int(p_bool(p, "remaproughness", True)), "thickness": p_float(p, "thickness", 0.01),
+                                   "g": p_float(p, "g", 0.0), "albedo": self.spec_constant(0.0) if alb is None else alb,
+                                   "max_depth": p_int(p, "maxdepth", 10), "n_samples": p_int(p, "nsamples", 1),
+                                   "cur": rough("conductor.uroughness", "conductor.roughness"),
+                                   "cvr": rough("conductor.vroughness", "conductor.roughness"),
+                                   "c_eta": -1 if ceta is None else ceta, "c_k": -1 if ck is None else ck})
         else:
             raise SceneError("Material '%s' is outside the hot path (SURVEY.md 8f)" % kind)
         return len(self.materials) - 1
@@ -597,6 +637,10 @@ class Scene:
             mats[i].type, mats[i].reflectance, mats[i].eta, mats[i].k = m["type"], m["reflectance"], m["eta"], m["k"]
             mats[i].u_roughness, mats[i].v_roughness, mats[i].remap_roughness = m["ur"], m["vr"], m["remap"]
             mats[i].transmittance, mats[i].scale = m.get("transmittance", -1), m.get("scale", 1.0)
+            mats[i].thickness, mats[i].g, mats[i].albedo = m.get("thickness", 0.01), m.get("g", 0.0), m.get("albedo", -1)
+            mats[i].max_depth, mats[i].n_samples = m.get("max_depth", 10), m.get("n_samples", 1)
+            mats[i].c_u_roughness, mats[i].c_v_roughness = m.get("cur", 0.0), m.get("cvr", 0.0)
+            mats[i].c_eta, mats[i].c_k = m.get("c_eta", -1), m.get("c_k", -1)
         d.n_materials, d.materials = len(self.materials), mats
         lights = (api.Light * max(1, len(self.lights)))()
         for i, l in enumerate(self.lights):

@@ -33,7 +33,7 @@ def test_lexer_and_parameters(b200pt):
     with pytest.raises(ps.SceneError):
         ps.load(text='Camera "perspective"\nWorldBegin\nFooBar 1\n')          # unknown directive is fatal
     with pytest.raises(ps.SceneError):
-        ps.load(text='Camera "perspective"\nWorldBegin\nMaterial "coateddiffuse"\n')
+        ps.load(text='Camera "perspective"\nWorldBegin\nMaterial "subsurface"\n')   # not a reference material (base/material.cu:31-87)
 
 
 def test_transforms_follow_the_reference(b200pt):

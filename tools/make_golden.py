@@ -25,6 +25,9 @@ CASES = [
     # LightSource infinite / distant / spot + diffusetransmission
     ("lights_96x64_64spp", "lights.pbrt", None, 64, None, None),
     ("lights_96x64_1024spp", "lights.pbrt", None, 1024, None, None),
+    # coated diffuse / coated conductor (LayeredBxDF)
+    ("coated_96x64_64spp", "coated.pbrt", None, 64, None, None),
+    ("coated_96x64_1024spp", "coated.pbrt", None, 1024, None, None),
     # C4 in miniature (workloads.procedural_scene, seed 7): many lights -> statistical gate only
     ("c4tiny_96x54_1024spp", "@c4tiny", None, 1024, None, None),
 ]
