@@ -959,7 +959,7 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_COATED_CONDUCTOR>(const WF 
 
 // ---- gpu_evaluate_material + sample_bsdf + sample_Ld_volume, specialised per material
 template <int MAT>
-__global__ void __launch_bounds__(WF_BLOCK) k_shade(WF wf) {
+__global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ? 1 : 2) k_shade(WF wf) {
     const unsigned n = wf.c->n_mat[MAT];
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned n_round = (n + 31u) & ~31u;

@@ -297,3 +297,27 @@ def test_hit_ids_vs_reference_hlbvh(b200pt, oracle, tmp_path):
     os.makedirs(out, exist_ok=True)
     with open(os.path.join(out, "ref_hlbvh_parity.txt"), "w") as f:
         f.write("200k-triangle soup, 480x270 primary/bounce/shadow vs reference HLBVH: mismatching ids %s\n%s\n" % (mism, r.stdout))
+
+
+def test_packed_key_build_above_16M_triangles(b200pt, oracle):
+    """N > 16 Mi: key = morton(3 * b) << ceil(log2 N) | prim, b = floor((64 - ceil(log2 N)) / 3), one 8-byte key-only sort
+    (csrc/bvh_build.cu).  17 M triangles: the sorted order is a permutation, keys strictly increase, the low bits are the
+    primitive ids, and closest-hit ids on a ray sample equal the brute-force oracle (near-ties listed as elsewhere)."""
+    n = 17_000_000
+    P, idx = b200pt.workloads.triangle_soup(n, seed=17)
+    s = b200pt.HLBVH(P, idx)
+    st = s.build_stats
+    assert st["key_bits"] == 39 and st["sort_passes"] == 5
+    prim, keys = s.sorted_order()
+    assert np.array_equal(np.bincount(prim, minlength=n), np.ones(n, dtype=np.int64))
+    assert np.all(keys[1:] > keys[:-1])
+    assert np.array_equal((keys & np.uint64((1 << 25) - 1)).astype(np.int64), prim.astype(np.int64))
+    o, d, tmax = b200pt.workloads.primary_rays(8, 6)
+    got, t, _ = s.intersect(o, d, tmax)
+    want, ot, _, t2 = oracle.closest_hit(P, idx, o, d, tmax, want_t2=True)
+    diff = got != want
+    ulps = np.abs(ot.view(np.int32).astype(np.int64) - t2.view(np.int32).astype(np.int64))
+    assert not (diff & ~(np.isfinite(t2) & (ulps <= 4))).any()
+    same = ~diff & (want >= 0)
+    assert same.sum() > 0 and np.array_equal(t[same].view(np.uint32), ot[same].view(np.uint32))
+    s.close()
