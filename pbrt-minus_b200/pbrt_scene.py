@@ -7,7 +7,8 @@ Supported (what the hot-path configs use; everything else raises SceneError like
 REPORT_FATAL_ERROR): LookAt / Translate / Scale / Rotate / Transform / ConcatTransform / Identity /
 CoordSysTransform / ReverseOrientation / AttributeBegin|End, Camera "perspective", Film "rgb",
 PixelFilter box|gaussian|mitchell|triangle, Sampler stratified|independent, Integrator path|volpath,
-Material / MakeNamedMaterial / NamedMaterial diffuse|conductor|dielectric, AreaLightSource "diffuse",
+Material / MakeNamedMaterial / NamedMaterial diffuse|conductor|dielectric|diffusetransmission|coateddiffuse|coatedconductor,
+AreaLightSource "diffuse", LightSource infinite (uniform)|distant|spot, ObjectBegin|End / ObjectInstance (flattened),
 Shape trianglemesh|sphere|plymesh (binary little-endian or ascii PLY, triangles and quads), Include.
 """
 import math
@@ -751,6 +752,28 @@ def load(path=None, text=None, spp=None, integrator=None):
             sc.max_depth = p_int(ipp, "maxdepth", 5)
             sc.regularize = p_bool(ipp, "regularize", False)
 
+    instances, instance_def = {}, None
+
+    def place_shape(rec, render_from_instance, area_light):
+        """One shape into the flat scene.  Instances (primitives/transformed_primitive.cu:20-34) are flattened: the reference
+        keeps a per-instance BVH and transforms the ray; here the instance's triangles are transformed once, by the shape's
+        render_from_object and then by render_from_instance, which gives the same surface up to fp rounding.  The orientation
+        flag of a triangle uses the handedness of the composite transform (the normal of the transformed triangle flips with
+        det, the reference's transformed normal does not); a sphere keeps the flag of its own transform, because
+        Transform::operator()(SurfaceInteraction) carries n through the instance transform without a handedness flip."""
+        rfo_x = rec["rfo"] if render_from_instance is None else render_from_instance * rec["rfo"]
+        flip = rec["ro"] ^ swaps_handedness(rfo_x.m)
+        if rec["kind"] == "mesh":
+            Pr = rec["P"] if rec["rfo"].is_identity() else xf_points(rec["rfo"].m, rec["P"])   # shapes/triangle_mesh.cu:49-78
+            if render_from_instance is not None:
+                Pr = xf_points(render_from_instance.m, Pr)
+            sc.add_mesh(Pr, rec["idx"], rec["material"], flip, area_light, scene_dir)
+        else:
+            if area_light is not None:
+                raise SceneError("emissive spheres are outside the hot path")
+            sc.spheres.append({"rfo": rfo_x.m, "ofr": rfo_x.inv, "radius": rec["radius"], "zmin": rec["zmin"], "zmax": rec["zmax"],
+                               "phimax": rec["phimax"], "ro": rec["ro"], "swaps": swaps_handedness(rec["rfo"].m), "material": rec["material"]})
+
     for kw, args in directives(text, scene_dir):
         if kw in pre:
             if kw == "Camera":
@@ -799,29 +822,46 @@ def load(path=None, text=None, spp=None, integrator=None):
         elif kw == "Shape":
             p = params_of(args[1:])
             rfo_x = render_from_world * g.ctm
-            rfo = rfo_x.m
-            flip = g.reverse_orientation ^ swaps_handedness(rfo)
             if args[0] in ("trianglemesh", "plymesh"):
                 if args[0] == "plymesh":
                     P, idx, _N = read_ply(os.path.join(scene_dir, p_str(p, "filename", "")))
                 else:
                     P = np.array(p["P"][1], dtype=F32).reshape(-1, 3)
                     idx = np.array(p["indices"][1], dtype=np.int32).reshape(-1, 3) if "indices" in p else np.array([[0, 1, 2]], np.int32)
-                is_identity = rfo_x.is_identity()
-                Pr = P if is_identity else xf_points(rfo, P)   # shapes/triangle_mesh.cu:49-78
-                sc.add_mesh(Pr, idx, g.material, flip, g.area_light, scene_dir)
+                rec = {"kind": "mesh", "P": P, "idx": idx}
             elif args[0] == "sphere":
-                if g.area_light is not None:
-                    raise SceneError("emissive spheres are outside the hot path")
                 r = p_float(p, "radius", 1.0)
-                sc.spheres.append({"rfo": rfo, "ofr": rfo_x.inv, "radius": r, "zmin": p_float(p, "zmin", -r), "zmax": p_float(p, "zmax", r),
-                                   "phimax": math.radians(min(max(p_float(p, "phimax", 360.0), 0.0), 360.0)),
-                                   "ro": g.reverse_orientation, "swaps": swaps_handedness(rfo), "material": g.material})
+                rec = {"kind": "sphere", "radius": r, "zmin": p_float(p, "zmin", -r), "zmax": p_float(p, "zmax", r),
+                       "phimax": math.radians(min(max(p_float(p, "phimax", 360.0), 0.0), 360.0))}
             else:
                 raise SceneError("Shape '%s' is outside the hot path (SURVEY.md 8f)" % args[0])
+            rec.update({"rfo": rfo_x, "ro": g.reverse_orientation, "material": g.material})
+            if instance_def is not None:
+                if g.area_light is not None:   # scene_builder.cu:653-656
+                    raise SceneError("area lights are not supported with object instancing")
+                instance_def["shapes"].append(rec)
+            else:
+                place_shape(rec, None, g.area_light)
+        elif kw == "ObjectBegin":              # scene_builder.cu:809-823
+            if instance_def is not None:
+                raise SceneError("ObjectBegin called inside of instance definition")
+            stack.append(g.copy())
+            instance_def = {"name": args[0], "shapes": []}
+        elif kw == "ObjectEnd":
+            if instance_def is None:
+                raise SceneError("ObjectEnd called before an instance defined")
+            instances[instance_def["name"]] = instance_def["shapes"]
+            instance_def = None
+            g = stack.pop()
+        elif kw == "ObjectInstance":           # scene_builder.cu:845-876
+            if args[0] not in instances:
+                raise SceneError("ObjectInstance '%s' not found" % args[0])
+            rfi = (render_from_world * g.ctm) * render_from_world.inverse()
+            for rec in instances[args[0]]:
+                place_shape(rec, None if rfi.is_identity() else rfi, None)
         elif kw == "LightSource":
             sc.add_light_source(args[0], params_of(args[1:]), render_from_world * g.ctm, scene_dir)
-        elif kw in ("ObjectBegin", "ObjectEnd", "ObjectInstance", "MakeNamedMedium", "MediumInterface", "Texture"):
+        elif kw in ("MakeNamedMedium", "MediumInterface", "Texture"):
             raise SceneError("directive '%s' is outside the hot path (SURVEY.md 8f)" % kw)
         elif kw in ("ColorSpace", "Option", "Attribute"):
             continue

@@ -28,6 +28,8 @@ CASES = [
     # coated diffuse / coated conductor (LayeredBxDF)
     ("coated_96x64_64spp", "coated.pbrt", None, 64, None, None),
     ("coated_96x64_1024spp", "coated.pbrt", None, 1024, None, None),
+    # ObjectBegin / ObjectInstance (the reference: per-instance BVH + TransformedPrimitive; here: flattened)
+    ("instances_96x64_64spp", "instances.pbrt", None, 64, None, None),
     # C4 in miniature (workloads.procedural_scene, seed 7): many lights -> statistical gate only
     ("c4tiny_96x54_1024spp", "@c4tiny", None, 1024, None, None),
 ]
