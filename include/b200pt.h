@@ -63,7 +63,8 @@ typedef struct {
 
 /* ---- materials (base/material.cu:97-131) ------------------------------------------------ */
 enum { B200PT_MAT_DIFFUSE = 0, B200PT_MAT_CONDUCTOR = 1, B200PT_MAT_DIELECTRIC = 2, B200PT_MAT_DIFFUSE_TRANSMISSION = 3,
-       B200PT_MAT_COATED_DIFFUSE = 4, B200PT_MAT_COATED_CONDUCTOR = 5, B200PT_MAT_COUNT = 6 };
+       B200PT_MAT_COATED_DIFFUSE = 4, B200PT_MAT_COATED_CONDUCTOR = 5, B200PT_MAT_COUNT = 6 /* BxDF-bearing types */,
+       B200PT_MAT_MIX = 6 /* resolved to one of its two materials at hit time (materials/mix_material.cu) */ };
 typedef struct {
     int32_t type;
     int32_t reflectance; /* spectrum id: diffuse reflectance, or conductor "reflectance" (-1: use eta/k) */
@@ -81,6 +82,7 @@ typedef struct {
     int32_t max_depth, n_samples;
     float c_u_roughness, c_v_roughness; /* coated conductor: the conductor's roughness */
     int32_t c_eta, c_k;                 /* coated conductor: the conductor's eta / k spectrum ids */
+    int32_t mix_a, mix_b;               /* mix: material ids; `scale` = "amount" in (0, 1): u < amount picks mix_a */
 } b200pt_material;
 
 /* ---- lights (base/light.cu:22-75), in the order the scene file creates them (= light-sampler index):

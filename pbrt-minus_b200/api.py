@@ -29,7 +29,7 @@ class Material(C.Structure):
                 ("transmittance", C.c_int32), ("scale", C.c_float),
                 ("thickness", C.c_float), ("g", C.c_float), ("albedo", C.c_int32), ("max_depth", C.c_int32),
                 ("n_samples", C.c_int32), ("c_u_roughness", C.c_float), ("c_v_roughness", C.c_float),
-                ("c_eta", C.c_int32), ("c_k", C.c_int32)]
+                ("c_eta", C.c_int32), ("c_k", C.c_int32), ("mix_a", C.c_int32), ("mix_b", C.c_int32)]
 
 
 class Light(C.Structure):

@@ -52,6 +52,7 @@ struct RenderData {
     int n_infinite = 0, infinite[4] = {0, 0, 0, 0};
     float scene_radius = 0.f;
     bool has_mat[WF_NMAT] = {};
+    bool has_mix = false;
     FilterTab filter = {};
     CameraRec camera = {};
     float *d_cie[3] = {nullptr, nullptr, nullptr};
@@ -268,12 +269,18 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
     for (int i = 0; i < desc->n_materials; i++) {
         const b200pt_material &m = desc->materials[i];
         mats[i] = MatRec{m.type, m.reflectance, m.eta, m.k, m.u_roughness, m.v_roughness, m.remap_roughness, m.transmittance, m.scale,
-                         m.thickness, m.g, m.albedo, m.max_depth, m.n_samples, m.c_u_roughness, m.c_v_roughness, m.c_eta, m.c_k, 0};
+                         m.thickness, m.g, m.albedo, m.max_depth, m.n_samples, m.c_u_roughness, m.c_v_roughness, m.c_eta, m.c_k, m.mix_a, m.mix_b};
         bool ok = true;
         if (m.type >= 0 && m.type < WF_NMAT) r->has_mat[m.type] = true;
         if (m.type == B200PT_MAT_DIFFUSE) ok = spec_ok(m.reflectance);
         else if (m.type == B200PT_MAT_DIFFUSE_TRANSMISSION) ok = spec_ok(m.reflectance) && spec_ok(m.transmittance);
-        else if (m.type == B200PT_MAT_COATED_DIFFUSE)
+        else if (m.type == B200PT_MAT_MIX) {
+            // materials/mix_material.cu:6-16: amount in (0, 1); the two materials must not be mixes themselves
+            // ("you should not see MixMaterial here", integrators/wavefront_path.cu:207-210)
+            ok = m.scale > 0.f && m.scale < 1.f && m.mix_a >= 0 && m.mix_a < desc->n_materials && m.mix_b >= 0 && m.mix_b < desc->n_materials &&
+                 desc->materials[m.mix_a].type != B200PT_MAT_MIX && desc->materials[m.mix_b].type != B200PT_MAT_MIX;
+            r->has_mix = true;
+        } else if (m.type == B200PT_MAT_COATED_DIFFUSE)
             ok = spec_ok(m.reflectance) && spec_ok(m.eta) && spec_ok(m.albedo) && m.max_depth >= 0 && m.n_samples >= 1;
         else if (m.type == B200PT_MAT_COATED_CONDUCTOR)
             ok = spec_ok(m.eta) && spec_ok(m.albedo) && m.max_depth >= 0 && m.n_samples >= 1 &&
@@ -654,6 +661,99 @@ __device__ __forceinline__ V3 tri_normal(V3 p0, V3 p1, V3 p2, bool flip) {
     return flip ? -n : n;
 }
 
+// what the shade stage needs of SurfaceInteraction (base/interaction.h:96-164)
+struct Isect {
+    V3 p, err;  // pi = p +- err
+    V3 n, ns;   // geometric / shading normal
+    V3 dpdu;    // shading.dpdu
+    V3 wo;
+};
+
+// Triangle::interaction_from_intersection (shapes/triangle.cu:325-465) for a mesh without per-vertex
+// normals / uvs (default uv (0,0),(1,0),(1,1)), from the 48-byte leaf record
+__device__ __forceinline__ void triangle_interaction(V3 p0, V3 p1, V3 p2, float b1, float b2, bool flip, V3 wo, Isect &si) {
+    const float b0 = 1.f - b1 - b2;
+    const V3 dp02 = p0 - p2, dp12 = p1 - p2;
+    // duv02 = (-1,-1), duv12 = (0,-1): determinant 1
+    V3 dpdu = v3(diff_of_products(-1.f, dp02.x, -1.f, dp12.x), diff_of_products(-1.f, dp02.y, -1.f, dp12.y),
+                 diff_of_products(-1.f, dp02.z, -1.f, dp12.z));
+    V3 dpdv = v3(diff_of_products(-1.f, dp12.x, 0.f, dp02.x), diff_of_products(-1.f, dp12.y, 0.f, dp02.y),
+                 diff_of_products(-1.f, dp12.z, 0.f, dp02.z));
+    if (len2(cross(dpdu, dpdv)) == 0.f) {
+        const V3 ng = cross(p2 - p0, p1 - p0);
+        coordinate_system(normalize(ng), &dpdu, &dpdv);
+    }
+    si.p = b0 * p0 + b1 * p1 + b2 * p2;
+    si.err = gamma_n(7) * (vabs(b0 * p0) + vabs(b1 * p1) + vabs(b2 * p2));
+    V3 n = normalize(cross(dp02, dp12));
+    if (flip) n = -n;
+    si.n = n;
+    si.ns = n;
+    si.dpdu = dpdu;
+    si.wo = normalize(wo);
+}
+
+// Sphere::interaction_from_intersection (shapes/sphere.h:71-125) + Transform::operator()(SurfaceInteraction)
+// (euclidean_space/transform.cu:57-97)
+__device__ __forceinline__ void sphere_interaction(const SphereRec &s, V3 ro, V3 rd, float t, V3 wo, Isect &si) {
+    // recompute the refined object-space hit point exactly as basic_intersect does
+    const V3 o = xf_point(s.ofr, ro), d = xf_vector(s.ofr, rd);
+    V3 pHit = o + t * d;
+    pHit = pHit * (s.radius / len(pHit));
+    if (pHit.x == 0.f && pHit.y == 0.f) pHit.x = 1e-5f * s.radius;
+    const float cosTheta = pHit.z / s.radius;
+    const float zRadius = sqrtf(sqr(pHit.x) + sqr(pHit.y));
+    const float cosPhi = pHit.x / zRadius, sinPhi = pHit.y / zRadius;
+    const V3 dpdu = v3(-s.phi_max * pHit.y, s.phi_max * pHit.x, 0.f);
+    const float sinTheta = safe_sqrt(1.f - sqr(cosTheta));
+    const V3 dpdv = (s.theta_z_max - s.theta_z_min) * v3(pHit.z * cosPhi, pHit.z * sinPhi, -s.radius * sinTheta);
+    const V3 perr = gamma_n(5) * vabs(pHit);
+    V3 n = normalize(cross(dpdu, dpdv));
+    if (s.flip) n = -n;
+    // to render space
+    si.p = xf_point(s.rfo, pHit);
+    si.err = xf_point_error(s.rfo, pHit, perr, false);
+    V3 nr = normalize(xf_normal(s.ofr, n));
+    V3 nsr = nr;
+    nr = face_forward(nr, nsr);
+    si.n = nr;
+    si.ns = nsr;
+    si.dpdu = xf_vector(s.rfo, dpdu);
+    si.wo = normalize(wo);
+}
+
+// SurfaceInteraction::set_intersection_properties (base/interaction.cu:41-64): a mix material is resolved at hit time by
+// u = hash_float(pi, wo) < amount (materials/mix_material.cu:18-21); pi is the Point3fi interval of the hit point
+// (euclidean_space/point3fi.h:31-34, interval.h:23-33), wo the normalised outgoing direction -- MurmurHash64A over 36 bytes
+__device__ __forceinline__ float mix_hash_float(V3 p, V3 err, V3 wo) {
+    float w[9];
+    const float pv[3] = {p.x, p.y, p.z}, ev[3] = {err.x, err.y, err.z};
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        w[2 * k] = ev[k] == 0.f ? pv[k] : next_down(pv[k] - ev[k]);
+        w[2 * k + 1] = ev[k] == 0.f ? pv[k] : next_up(pv[k] + ev[k]);
+    }
+    w[6] = wo.x; w[7] = wo.y; w[8] = wo.z;
+    const uint64_t m = 0xc6a4a7935bd1e995ULL;
+    const int r = 47;
+    uint64_t h = 0ull ^ (36ull * m);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        uint64_t kk = (uint64_t)__float_as_uint(w[2 * k]) | ((uint64_t)__float_as_uint(w[2 * k + 1]) << 32);
+        kk *= m;
+        kk ^= kk >> r;
+        kk *= m;
+        h ^= kk;
+        h *= m;
+    }
+    h ^= (uint64_t)__float_as_uint(w[8]);
+    h *= m;
+    h ^= h >> r;
+    h *= m;
+    h ^= h >> r;
+    return __fmul_rn((float)(uint32_t)h, 0x1p-32f);
+}
+
 // ---- control_logic (integrators/wavefront_path.cu:68-214)
 __global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf) {
     // one thread per pool slot, in slot order: every lane access below is a coalesced 16-byte gather
@@ -749,6 +849,22 @@ __global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf) {
                         }
                     }
                 }
+                if (wf.has_mix && wf.materials[mat].type == B200PT_MAT_MIX) {
+                    const MatRec mr = wf.materials[mat];
+                    const V3 ro = v3(wf.pool.ray_o[slot]), rd = v3(wf.pool.ray_d[slot]);
+                    Isect si;
+                    if (prim >= (int)wf.bvh.n_tris) {
+                        sphere_interaction(wf.spheres[prim - (int)wf.bvh.n_tris], ro, rd, hit.y, -rd, si);
+                    } else {
+                        const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
+                        const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                        triangle_interaction(v3(v0), v3(v1), v3(v2), hit.z, hit.w, false, -rd, si);
+                    }
+                    mat = mix_hash_float(si.p, si.err, si.wo) < mr.scale ? mr.mix_a : mr.mix_b;
+                    float4 misc = wf.pool.misc[slot];
+                    misc.z = __int_as_float(mat); // the shade stage reads the resolved material from here
+                    wf.pool.misc[slot] = misc;
+                }
                 depth += 1;
                 route = wf.materials[mat].type;
             }
@@ -769,67 +885,6 @@ __global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf) {
     // finished-path count: warp reduce, one atomic per warp
     for (int o = 16; o > 0; o >>= 1) n_finished += __shfl_xor_sync(0xffffffffu, n_finished, o);
     if ((threadIdx.x & 31) == 0 && n_finished) atomicAdd(&wf.c->finished, (unsigned long long)n_finished);
-}
-
-// what the shade stage needs of SurfaceInteraction (base/interaction.h:96-164)
-struct Isect {
-    V3 p, err;  // pi = p +- err
-    V3 n, ns;   // geometric / shading normal
-    V3 dpdu;    // shading.dpdu
-    V3 wo;
-};
-
-// Triangle::interaction_from_intersection (shapes/triangle.cu:325-465) for a mesh without per-vertex
-// normals / uvs (default uv (0,0),(1,0),(1,1)), from the 48-byte leaf record
-__device__ __forceinline__ void triangle_interaction(V3 p0, V3 p1, V3 p2, float b1, float b2, bool flip, V3 wo, Isect &si) {
-    const float b0 = 1.f - b1 - b2;
-    const V3 dp02 = p0 - p2, dp12 = p1 - p2;
-    // duv02 = (-1,-1), duv12 = (0,-1): determinant 1
-    V3 dpdu = v3(diff_of_products(-1.f, dp02.x, -1.f, dp12.x), diff_of_products(-1.f, dp02.y, -1.f, dp12.y),
-                 diff_of_products(-1.f, dp02.z, -1.f, dp12.z));
-    V3 dpdv = v3(diff_of_products(-1.f, dp12.x, 0.f, dp02.x), diff_of_products(-1.f, dp12.y, 0.f, dp02.y),
-                 diff_of_products(-1.f, dp12.z, 0.f, dp02.z));
-    if (len2(cross(dpdu, dpdv)) == 0.f) {
-        const V3 ng = cross(p2 - p0, p1 - p0);
-        coordinate_system(normalize(ng), &dpdu, &dpdv);
-    }
-    si.p = b0 * p0 + b1 * p1 + b2 * p2;
-    si.err = gamma_n(7) * (vabs(b0 * p0) + vabs(b1 * p1) + vabs(b2 * p2));
-    V3 n = normalize(cross(dp02, dp12));
-    if (flip) n = -n;
-    si.n = n;
-    si.ns = n;
-    si.dpdu = dpdu;
-    si.wo = normalize(wo);
-}
-
-// Sphere::interaction_from_intersection (shapes/sphere.h:71-125) + Transform::operator()(SurfaceInteraction)
-// (euclidean_space/transform.cu:57-97)
-__device__ __forceinline__ void sphere_interaction(const SphereRec &s, V3 ro, V3 rd, float t, V3 wo, Isect &si) {
-    // recompute the refined object-space hit point exactly as basic_intersect does
-    const V3 o = xf_point(s.ofr, ro), d = xf_vector(s.ofr, rd);
-    V3 pHit = o + t * d;
-    pHit = pHit * (s.radius / len(pHit));
-    if (pHit.x == 0.f && pHit.y == 0.f) pHit.x = 1e-5f * s.radius;
-    const float cosTheta = pHit.z / s.radius;
-    const float zRadius = sqrtf(sqr(pHit.x) + sqr(pHit.y));
-    const float cosPhi = pHit.x / zRadius, sinPhi = pHit.y / zRadius;
-    const V3 dpdu = v3(-s.phi_max * pHit.y, s.phi_max * pHit.x, 0.f);
-    const float sinTheta = safe_sqrt(1.f - sqr(cosTheta));
-    const V3 dpdv = (s.theta_z_max - s.theta_z_min) * v3(pHit.z * cosPhi, pHit.z * sinPhi, -s.radius * sinTheta);
-    const V3 perr = gamma_n(5) * vabs(pHit);
-    V3 n = normalize(cross(dpdu, dpdv));
-    if (s.flip) n = -n;
-    // to render space
-    si.p = xf_point(s.rfo, pHit);
-    si.err = xf_point_error(s.rfo, pHit, perr, false);
-    V3 nr = normalize(xf_normal(s.ofr, n));
-    V3 nsr = nr;
-    nr = face_forward(nr, nsr);
-    si.n = nr;
-    si.ns = nsr;
-    si.dpdu = xf_vector(s.rfo, dpdu);
-    si.wo = normalize(wo);
 }
 
 template <int MAT>
@@ -987,6 +1042,7 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
                 mat = int(mw & 0x7fffffffu);
                 triangle_interaction(v3(v0), v3(v1), v3(v2), hit.z, hit.w, (mw >> 31) != 0u, -rd, si);
             }
+            if (wf.has_mix && wf.materials[mat].type == B200PT_MAT_MIX) mat = __float_as_int(wf.pool.misc[slot].z);
             const MatRec m = wf.materials[mat];
             const S4 lambda = wf.pool.lambda[slot];
             S4 lpdf = wf.pool.lpdf[slot];
@@ -1241,6 +1297,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     wf.n_infinite = r->n_infinite;
     for (int k = 0; k < 4; k++) wf.infinite[k] = r->infinite[k];
     wf.scene_radius = r->scene_radius;
+    wf.has_mix = r->has_mix ? 1 : 0;
     int n_shade_kernels = 0;
     for (int m = 0; m < WF_NMAT; m++) n_shade_kernels += r->has_mat[m] ? 1 : 0;
     wf.n_lights = r->n_lights;

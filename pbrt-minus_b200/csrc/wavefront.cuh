@@ -24,7 +24,7 @@ struct MatRec {
     int32_t albedo, max_depth, n_samples;
     float c_u_rough, c_v_rough;
     int32_t c_eta, c_k;
-    int32_t pad;
+    int32_t mix_a, mix_b;         // mix material: the two material ids; `scale` holds the amount
 };
 constexpr int WF_NMAT = B200PT_MAT_COUNT; // one shading queue per material type
 
@@ -108,6 +108,7 @@ struct WF {
     int32_t n_lights;
     int32_t n_infinite;      // infinite lights looked up by escaping rays (integrators/wavefront_path.cu:105-127)
     int32_t infinite[4];     // their light ids
+    int32_t has_mix;         // some material is a mix (resolved in k_logic, materials/mix_material.cu)
     float scene_radius;      // Bounds3::bounding_sphere of the whole scene (scene_builder.cu:914-925)
     FilterTab filter;
     CameraRec camera;

@@ -407,7 +407,7 @@ class Scene:
         raise SceneError("spectrum parameter '%s' of type '%s' not supported" % (name, t))
 
     # ---- materials
-    def add_material(self, kind, p, scene_dir):
+    def add_material(self, kind, p, scene_dir, named=None):
         if kind == "diffuse":
             r = self.spec_param(p, "reflectance", "albedo", scene_dir)
             if r is None:
@@ -445,6 +445,14 @@ class Scene:
             self.materials.append({"type": 3, "reflectance": self.spec_constant(0.25) if r is None else r, "eta": -1, "k": -1,
                                    "ur": 0.0, "vr": 0.0, "remap": 1, "transmittance": self.spec_constant(0.25) if t is None else t,
                                    "scale": p_float(p, "scale", 1.0)})
+        elif kind == "mix":
+            # materials/mix_material.cu:6-16: two NAMED materials and an amount in (0, 1)
+            amount = p_float(p, "amount", 0.5)
+            names = [str(v) for v in p["materials"][1]] if "materials" in p else []
+            if not (0.0 < amount < 1.0) or len(names) != 2 or any(n not in (named or {}) for n in names):
+                raise SceneError("mix: needs \"amount\" in (0, 1) and two named materials")
+            self.materials.append({"type": 6, "reflectance": -1, "eta": -1, "k": -1, "ur": 0.0, "vr": 0.0, "remap": 1,
+                                   "scale": amount, "mix_a": named[names[0]], "mix_b": named[names[1]]})
         elif kind == "coateddiffuse":
             # materials/coated_diffuse_material.cu:9-51
             r = self.spec_param(p, "reflectance", "albedo", scene_dir)
@@ -642,6 +650,7 @@ class Scene:
             mats[i].max_depth, mats[i].n_samples = m.get("max_depth", 10), m.get("n_samples", 1)
             mats[i].c_u_roughness, mats[i].c_v_roughness = m.get("cur", 0.0), m.get("cvr", 0.0)
             mats[i].c_eta, mats[i].c_k = m.get("c_eta", -1), m.get("c_k", -1)
+            mats[i].mix_a, mats[i].mix_b = m.get("mix_a", -1), m.get("mix_b", -1)
         d.n_materials, d.materials = len(self.materials), mats
         lights = (api.Light * max(1, len(self.lights)))()
         for i, l in enumerate(self.lights):
@@ -807,10 +816,10 @@ def load(path=None, text=None, spp=None, integrator=None):
         elif kw == "ReverseOrientation":
             g.reverse_orientation = not g.reverse_orientation
         elif kw == "Material":
-            g.material = sc.add_material(args[0], params_of(args[1:]), scene_dir)
+            g.material = sc.add_material(args[0], params_of(args[1:]), scene_dir, named_mat)
         elif kw == "MakeNamedMaterial":
             p = params_of(args[1:])
-            named_mat[args[0]] = sc.add_material(p_str(p, "type", "diffuse"), p, scene_dir)
+            named_mat[args[0]] = sc.add_material(p_str(p, "type", "diffuse"), p, scene_dir, named_mat)
         elif kw == "NamedMaterial":
             if args[0] not in named_mat:
                 raise SceneError("NamedMaterial '%s' not defined" % args[0])
