@@ -755,21 +755,12 @@ __device__ __forceinline__ float mix_hash_float(V3 p, V3 err, V3 wo) {
 }
 
 // ---- control_logic (integrators/wavefront_path.cu:68-214)
-__global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf) {
+__global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
     // one thread per pool slot, in slot order: every lane access below is a coalesced 16-byte gather
     const unsigned n = (unsigned)wf.pool_size;
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned n_round = (n + WF_BLOCK - 1u) / WF_BLOCK * WF_BLOCK;
     unsigned n_finished = 0;
-    unsigned *counters[WF_NMAT + 1];
-    int32_t *queues[WF_NMAT + 1];
-#pragma unroll
-    for (int m = 0; m < WF_NMAT; m++) {
-        counters[m] = &wf.c->n_mat[m];
-        queues[m] = wf.q.mat[m];
-    }
-    counters[WF_NMAT] = &wf.c->n_free;
-    queues[WF_NMAT] = wf.q.free_slots;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         const bool act = i < n && wf.pool.state[i] == ST_RAY;
         const int slot = (int)i;
@@ -880,7 +871,7 @@ __global__ void __launch_bounds__(WF_BLOCK) k_logic(WF wf) {
         }
         const int cat = (act && terminate) ? WF_NMAT : route; // material queue, WF_NMAT = free list, -1 nothing
         if (act) wf.pool.state[slot] = terminate ? ST_FREE : uint8_t(ST_MAT0 + route);
-        block_push<WF_NMAT + 1>(cat, slot, counters, queues);
+        block_push(wf, cat, slot);
     }
     // finished-path count: warp reduce, one atomic per warp
     for (int o = 16; o > 0; o >>= 1) n_finished += __shfl_xor_sync(0xffffffffu, n_finished, o);
@@ -1298,6 +1289,10 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     for (int k = 0; k < 4; k++) wf.infinite[k] = r->infinite[k];
     wf.scene_radius = r->scene_radius;
     wf.has_mix = r->has_mix ? 1 : 0;
+    // a warp of k_trace_wf fetches new rays once this many lanes are idle: 4 is the measured best on triangle-only scenes;
+    // with spheres the per-ray start-up is longer and waiting for half a warp pays (C1: 62.0 -> 58.5 ms together with the
+    // sphere phase)
+    wf.refill_min = getenv("B200PT_WF_REFILL") ? atoi(getenv("B200PT_WF_REFILL")) : (s->n_spheres > 0 ? 16 : 4);
     int n_shade_kernels = 0;
     for (int m = 0; m < WF_NMAT; m++) n_shade_kernels += r->has_mat[m] ? 1 : 0;
     wf.n_lights = r->n_lights;

@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
 //                   NEE contribution to pool.L[slot] on retirement (one shadow ray per slot per pass,
 //                   so the add needs no atomic) -- the reference runs these traversals inline in the
 //                   shading threads (integrators/megakernel_path.cu:217-233, base/integrator_base.cu:12-71).
-template <bool SHADOW>
+template <bool SHADOW, bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
     __shared__ uint2 sm_stack_all[SM_STACK * TRACE_BLOCK];
     uint2 *const sm_stack = sm_stack_all + threadIdx.x;
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
     const long long n = SHADOW ? (long long)wf.c->n_shadow : (long long)wf.pool_size;
     unsigned *const ticket = SHADOW ? &wf.c->ticket_shadow : &wf.c->ticket_closest;
     unsigned n_live = 0;
-    constexpr int REFILL = 4;
+    const int REFILL = wf.refill_min;
     const uint32_t prmt_bias = 0x47000000u;
 
     long long ray = -1;
@@ -186,6 +186,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
     int sp = 0;
     float ht = 0, hb1 = 0, hb2 = 0;
     int hprim = -1;
+    int sph_k = 0;      // next sphere to test for this lane's ray (n_spheres: none pending)
     int skip_prim = -1; // SHADOW: the sampled light's own triangle (the reference's three visibility rays cannot reach it)
     unsigned overflow = 0;
 
@@ -224,16 +225,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                     ht = ro.w;
                     hb1 = 0.f; hb2 = 0.f;
                     hprim = -1;
-                    if (live) {
-                        for (int k = 0; k < wf.n_spheres; k++) {
-                            SphereHit sh;
-                            if (sphere_intersect(wf.spheres[k], v3(ox, oy, oz), v3(dx, dy, dz), ht, sh)) {
-                                ht = sh.t;
-                                hprim = int(wf.bvh.n_tris) + k;
-                                if (SHADOW) ng.y = 0u;
-                            }
-                        }
-                    }
+                    sph_k = live ? 0 : wf.n_spheres; // spheres are tested as a phase of their own below
                 }
             }
         }
@@ -243,10 +235,26 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
         }
 
         const bool act = ray >= 0;
-        const bool want_tri = act && tg.y != 0u;
-        const unsigned m_tri = __ballot_sync(0xffffffffu, want_tri);
-        const unsigned m_node = __ballot_sync(0xffffffffu, act && !want_tri);
-        if (__popc(m_tri) >= __popc(m_node)) {
+        const bool want_sph = SPH && act && sph_k < wf.n_spheres;
+        const bool want_tri = act && !want_sph && tg.y != 0u;
+        const int c_sph = SPH ? __popc(__ballot_sync(0xffffffffu, want_sph)) : 0;
+        const int c_tri = __popc(__ballot_sync(0xffffffffu, want_tri));
+        const int c_node = __popc(__ballot_sync(0xffffffffu, act && !want_sph && !want_tri));
+        if (c_sph > 0 && c_sph >= c_tri && c_sph >= c_node) {
+            // sphere phase (Sphere::basic_intersect in interval arithmetic is long: run it with as many lanes as want it)
+            if (want_sph) {
+                SphereHit sh;
+                if (sphere_intersect(wf.spheres[sph_k], v3(ox, oy, oz), v3(dx, dy, dz), ht, sh)) {
+                    ht = sh.t;
+                    hprim = int(wf.bvh.n_tris) + sph_k;
+                    if (SHADOW) {
+                        ng.y = 0u;
+                        sph_k = wf.n_spheres;
+                    }
+                }
+                sph_k++;
+            }
+        } else if (c_tri >= c_node) {
             if (want_tri) {
                 const int ti = __ffs(tg.y) - 1;
                 tg.y &= tg.y - 1u;
@@ -266,7 +274,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                     }
                 }
             }
-        } else if (act && !want_tri) {
+        } else if (act && !want_sph && !want_tri) {
             if (ng.y <= 0x00ffffffu && sp > 0) {
                 sp--;
                 if (sp < SM_STACK) ng = sm_stack[sp * TRACE_BLOCK];
@@ -316,16 +324,17 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
 }
 
 int launch_trace_wf(b200pt_scene *s, const WF &wf, bool shadow) {
-    static int per_sm[2] = {0, 0};
-    if (per_sm[shadow] == 0) {
+    typedef void (*K)(WF);
+    static const K kern[2][2] = {{k_trace_wf<false, false>, k_trace_wf<false, true>}, {k_trace_wf<true, false>, k_trace_wf<true, true>}};
+    static int per_sm[2][2] = {{0, 0}, {0, 0}};
+    const int sph = wf.n_spheres > 0 ? 1 : 0;
+    if (per_sm[shadow][sph] == 0) {
         int v = 0;
-        if (shadow) CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k_trace_wf<true>, TRACE_BLOCK, 0));
-        else CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, k_trace_wf<false>, TRACE_BLOCK, 0));
-        per_sm[shadow] = v < 1 ? 1 : v;
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kern[shadow][sph], TRACE_BLOCK, 0));
+        per_sm[shadow][sph] = v < 1 ? 1 : v;
     }
-    const unsigned blocks = unsigned(s->sm_count * per_sm[shadow]);
-    if (shadow) k_trace_wf<true><<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf);
-    else k_trace_wf<false><<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf);
+    const unsigned blocks = unsigned(s->sm_count * per_sm[shadow][sph]);
+    kern[shadow][sph]<<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf);
     CU_TRY(cudaGetLastError());
     return B200PT_OK;
 }

@@ -108,6 +108,7 @@ struct WF {
     int32_t n_lights;
     int32_t n_infinite;      // infinite lights looked up by escaping rays (integrators/wavefront_path.cu:105-127)
     int32_t infinite[4];     // their light ids
+    int32_t refill_min;      // k_trace_wf: a warp fetches new rays once this many lanes are idle
     int32_t has_mix;         // some material is a mix (resolved in k_logic, materials/mix_material.cu)
     float scene_radius;      // Bounds3::bounding_sphere of the whole scene (scene_builder.cu:914-925)
     FilterTab filter;
@@ -144,11 +145,12 @@ __device__ __forceinline__ int queue_claim(unsigned *counter, bool pred) {
     return pred ? int(base + __popc(m & ((1u << lane) - 1u))) : -1;
 }
 
-// block-ordered push into up to NCAT queues: the entries of one 256-slot block land contiguously and in
-// thread (= slot) order, with ONE atomicAdd per block and queue.  cat < 0: nothing to push.  Must be
-// called by every thread of the block (it synchronises); blockDim.x <= 1024.
-template <int NCAT>
-__device__ __forceinline__ void block_push(int cat, int32_t value, unsigned *const *counters, int32_t *const *queues) {
+// block-ordered push into the material queues (cat 0..WF_NMAT-1) or the free list (cat WF_NMAT): the entries of one
+// 256-slot block land contiguously and in thread (= slot) order, with ONE atomicAdd per block and queue.  cat < 0: nothing
+// to push.  Must be called by every thread of the block (it synchronises); blockDim.x <= 1024.  Queue pointers and counters
+// are read from the kernel parameter block by index (constant bank), never through a local array.
+__device__ __forceinline__ void block_push(const WF &wf, int cat, int32_t value) {
+    constexpr int NCAT = WF_NMAT + 1;
     __shared__ unsigned s_warp[NCAT][32];
     __shared__ unsigned s_base[NCAT];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = (blockDim.x + 31) >> 5;
@@ -167,10 +169,14 @@ __device__ __forceinline__ void block_push(int cat, int32_t value, unsigned *con
             s_warp[threadIdx.x][w] = total;
             total += v;
         }
-        s_base[threadIdx.x] = total ? atomicAdd(counters[threadIdx.x], total) : 0u;
+        unsigned *counter = threadIdx.x < WF_NMAT ? &wf.c->n_mat[threadIdx.x] : &wf.c->n_free;
+        s_base[threadIdx.x] = total ? atomicAdd(counter, total) : 0u;
     }
     __syncthreads();
-    if (cat >= 0) queues[cat][s_base[cat] + s_warp[cat][warp] + __popc(my_ballot & ((1u << lane) - 1u))] = value;
+    if (cat >= 0) {
+        int32_t *queue = cat < WF_NMAT ? wf.q.mat[cat] : wf.q.free_slots;
+        queue[s_base[cat] + s_warp[cat][warp] + __popc(my_ballot & ((1u << lane) - 1u))] = value;
+    }
     __syncthreads(); // the shared arrays are reused by the next call
 }
 
