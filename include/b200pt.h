@@ -142,7 +142,8 @@ typedef struct {
     const int32_t *indices;    /* [n_triangles*3] */
     const int32_t *tri_material; /* optional [n_triangles]; default 0 */
     const int32_t *tri_light;    /* optional [n_triangles]; -1 = not emissive */
-    const uint8_t *tri_flip;     /* optional [n_triangles]; reverse_orientation ^ swaps_handedness */
+    const uint8_t *tri_flip;     /* optional [n_triangles]; bit 0: reverse_orientation ^ swaps_handedness, bit 1: the triangle's
+                                  * mesh has shading normals (N), bit 2: it has uvs (shapes/triangle.cu:336-346,388-463) */
     int32_t n_spheres;
     const b200pt_sphere *spheres;
     int32_t n_spectra;

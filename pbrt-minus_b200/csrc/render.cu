@@ -359,7 +359,7 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
         }
         o.scale = l.scale;
         o.spectrum = l.spectrum;
-        o.flags = (l.two_sided ? 1 : 0) | ((desc->tri_flip && desc->tri_flip[l.triangle]) ? 2 : 0);
+        o.flags = (l.two_sided ? 1 : 0) | ((desc->tri_flip && (desc->tri_flip[l.triangle] & 1)) ? 2 : 0);
         o.pmf = 0.f;
         // Triangle::area (shapes/triangle.h:41-44) with the reference's compensated cross product
         // (euclidean_space/vector3.h:151-155, util/math.h:167-173): the alias-table layout depends on the
@@ -669,17 +669,37 @@ struct Isect {
     V3 wo;
 };
 
-// Triangle::interaction_from_intersection (shapes/triangle.cu:325-465) for a mesh without per-vertex
-// normals / uvs (default uv (0,0),(1,0),(1,1)), from the 48-byte leaf record
-__device__ __forceinline__ void triangle_interaction(V3 p0, V3 p1, V3 p2, float b1, float b2, bool flip, V3 wo, Isect &si) {
+// Triangle::interaction_from_intersection (shapes/triangle.cu:325-465) from the 48-byte leaf record; per-vertex normals and
+// uvs (flag bits of v1.w) are fetched through the primitive id and the index buffer.  Default uv (0,0),(1,0),(1,1).
+__device__ __forceinline__ void triangle_interaction(const WF &wf, V3 p0, V3 p1, V3 p2, int prim, uint32_t mw, float b1, float b2,
+                                                     V3 wo, Isect &si) {
     const float b0 = 1.f - b1 - b2;
+    const bool flip = (mw >> 31) != 0u, has_n = (mw & 0x20000000u) != 0u, has_uv = (mw & 0x40000000u) != 0u;
+    int i0 = 0, i1 = 0, i2 = 0;
+    if (has_n || has_uv) {
+        i0 = wf.idx[3 * (size_t)prim];
+        i1 = wf.idx[3 * (size_t)prim + 1];
+        i2 = wf.idx[3 * (size_t)prim + 2];
+    }
+    float2 uv0 = make_float2(0.f, 0.f), uv1 = make_float2(1.f, 0.f), uv2 = make_float2(1.f, 1.f);
+    if (has_uv) {
+        uv0 = make_float2(wf.uv[2 * (size_t)i0], wf.uv[2 * (size_t)i0 + 1]);
+        uv1 = make_float2(wf.uv[2 * (size_t)i1], wf.uv[2 * (size_t)i1 + 1]);
+        uv2 = make_float2(wf.uv[2 * (size_t)i2], wf.uv[2 * (size_t)i2 + 1]);
+    }
+    const float du02 = uv0.x - uv2.x, dv02 = uv0.y - uv2.y, du12 = uv1.x - uv2.x, dv12 = uv1.y - uv2.y;
     const V3 dp02 = p0 - p2, dp12 = p1 - p2;
-    // duv02 = (-1,-1), duv12 = (0,-1): determinant 1
-    V3 dpdu = v3(diff_of_products(-1.f, dp02.x, -1.f, dp12.x), diff_of_products(-1.f, dp02.y, -1.f, dp12.y),
-                 diff_of_products(-1.f, dp02.z, -1.f, dp12.z));
-    V3 dpdv = v3(diff_of_products(-1.f, dp12.x, 0.f, dp02.x), diff_of_products(-1.f, dp12.y, 0.f, dp02.y),
-                 diff_of_products(-1.f, dp12.z, 0.f, dp02.z));
-    if (len2(cross(dpdu, dpdv)) == 0.f) {
+    const float det = diff_of_products(du02, dv12, dv02, du12);
+    const bool degenerate = fabsf(det) < 1e-9f;
+    V3 dpdu = v3(0.f, 0.f, 0.f), dpdv = dpdu;
+    if (!degenerate) {
+        const float invdet = 1.f / det;
+        dpdu = v3(diff_of_products(dv12, dp02.x, dv02, dp12.x), diff_of_products(dv12, dp02.y, dv02, dp12.y),
+                  diff_of_products(dv12, dp02.z, dv02, dp12.z)) * invdet;
+        dpdv = v3(diff_of_products(du02, dp12.x, du12, dp02.x), diff_of_products(du02, dp12.y, du12, dp02.y),
+                  diff_of_products(du02, dp12.z, du12, dp02.z)) * invdet;
+    }
+    if (degenerate || len2(cross(dpdu, dpdv)) == 0.f) {
         const V3 ng = cross(p2 - p0, p1 - p0);
         coordinate_system(normalize(ng), &dpdu, &dpdv);
     }
@@ -691,6 +711,26 @@ __device__ __forceinline__ void triangle_interaction(V3 p0, V3 p1, V3 p2, float 
     si.ns = n;
     si.dpdu = dpdu;
     si.wo = normalize(wo);
+    if (has_n) {
+        // shading normal + tangent (:388-463), then set_shading_geometry(.., orientationIsAuthoritative = true)
+        // (base/interaction.cu:67-89): the geometric normal is flipped to the side of the shading normal
+        const V3 n0 = v3(wf.N[3 * (size_t)i0], wf.N[3 * (size_t)i0 + 1], wf.N[3 * (size_t)i0 + 2]);
+        const V3 n1 = v3(wf.N[3 * (size_t)i1], wf.N[3 * (size_t)i1 + 1], wf.N[3 * (size_t)i1 + 2]);
+        const V3 n2 = v3(wf.N[3 * (size_t)i2], wf.N[3 * (size_t)i2 + 1], wf.N[3 * (size_t)i2 + 2]);
+        V3 ns = b0 * n0 + b1 * n1 + b2 * n2;
+        ns = len2(ns) > 0.f ? normalize(ns) : n;
+        V3 ss = dpdu;
+        V3 ts = cross(ns, ss);
+        if (len2(ts) > 0.f) ss = cross(ts, ns);
+        else coordinate_system(ns, &ss, &ts);
+        si.ns = ns;
+        si.n = face_forward(n, ns);
+        while (len2(ss) > 1e16f || len2(ts) > 1e16f) {
+            ss = ss / 1e8f;
+            ts = ts / 1e8f;
+        }
+        si.dpdu = ss;
+    }
 }
 
 // Sphere::interaction_from_intersection (shapes/sphere.h:71-125) + Transform::operator()(SurfaceInteraction)
@@ -815,7 +855,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                     const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
                     const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                     const uint32_t mw = __float_as_uint(v1.w);
-                    mat = int(mw & 0x7fffffffu);
+                    mat = int(mw & 0x1fffffffu);
                     const int light = __float_as_int(v2.w);
                     if (light >= 0) {
                         // SurfaceInteraction::le -> DiffuseAreaLight::l, then MIS against NEE (:155-171)
@@ -849,7 +889,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                     } else {
                         const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
                         const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
-                        triangle_interaction(v3(v0), v3(v1), v3(v2), hit.z, hit.w, false, -rd, si);
+                        triangle_interaction(wf, v3(v0), v3(v1), v3(v2), __float_as_int(v0.w), __float_as_uint(v1.w), hit.z, hit.w, -rd, si);
                     }
                     mat = mix_hash_float(si.p, si.err, si.wo) < mr.scale ? mr.mix_a : mr.mix_b;
                     float4 misc = wf.pool.misc[slot];
@@ -1030,8 +1070,8 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
                 const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
                 const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                 const uint32_t mw = __float_as_uint(v1.w);
-                mat = int(mw & 0x7fffffffu);
-                triangle_interaction(v3(v0), v3(v1), v3(v2), hit.z, hit.w, (mw >> 31) != 0u, -rd, si);
+                mat = int(mw & 0x1fffffffu);
+                triangle_interaction(wf, v3(v0), v3(v1), v3(v2), __float_as_int(v0.w), mw, hit.z, hit.w, -rd, si);
             }
             if (wf.has_mix && wf.materials[mat].type == B200PT_MAT_MIX) mat = __float_as_int(wf.pool.misc[slot].z);
             const MatRec m = wf.materials[mat];
@@ -1280,6 +1320,9 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     wf.bvh = s->bvh;
     wf.spheres = s->d_spheres;
     wf.n_spheres = s->n_spheres;
+    wf.N = s->d_N;
+    wf.uv = s->d_uv;
+    wf.idx = s->d_idx;
     wf.spectra = SpectrumTable{r->d_spec, r->d_spec_pool, r->d_illuminant};
     wf.materials = r->d_materials;
     wf.lights = r->d_lights;

@@ -100,6 +100,10 @@ struct WF {
     BVH8 bvh;
     const SphereRec *spheres;
     int32_t n_spheres;
+    // per-vertex shading normals / uvs of the meshes that have them (render space; indexed through the triangle's
+    // primitive id and the index buffer); null when no mesh has any
+    const float *N, *uv;
+    const int32_t *idx;
     SpectrumTable spectra;
     const MatRec *materials;
     const LightRec *lights;

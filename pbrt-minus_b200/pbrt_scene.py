@@ -227,6 +227,20 @@ def xf_points(m, P):
     return out.astype(F32)
 
 
+def xf_normals(inv_m, N):
+    """Transform::operator()(Normal3f) (euclidean_space/transform.h:312-320): (inv_m^T) n, fp32"""
+    N = np.asarray(N, dtype=F32).reshape(-1, 3)
+    im = np.asarray(inv_m, dtype=F32)
+    x, y, z = N[:, 0], N[:, 1], N[:, 2]
+    cols = []
+    for c in range(3):
+        t = (im[0, c] * x).astype(F32)
+        t = _fma32(im[1, c], y, t)
+        t = _fma32(im[2, c], z, t)
+        cols.append(t)
+    return np.stack(cols, axis=1).astype(F32)
+
+
 def swaps_handedness(m):
     return float(np.linalg.det(m[:3, :3].astype(np.float64))) < 0
 
@@ -300,7 +314,12 @@ def read_ply(path):
                 del cs, isz
     P = np.stack([verts["x"], verts["y"], verts["z"]], axis=1).astype(F32)
     N = np.stack([verts["nx"], verts["ny"], verts["nz"]], axis=1).astype(F32) if "nx" in verts else None
-    return P, faces, N
+    uv = None
+    for a, b in (("u", "v"), ("s", "t"), ("texture_u", "texture_v"), ("texture_s", "texture_t")):   # shapes/tri_quad_mesh.cu
+        if a in verts and b in verts:
+            uv = np.stack([verts[a], verts[b]], axis=1).astype(F32)
+            break
+    return P, faces, N, uv
 
 
 # ------------------------------------------------------------------------------ pixel filters
@@ -344,6 +363,7 @@ class Scene:
 
     def __init__(self):
         self.P, self.idx, self.tri_material, self.tri_light, self.tri_flip = [], [], [], [], []
+        self.N, self.uv, self.any_N, self.any_uv = [], [], False, False
         self.n_verts = 0
         self.spheres, self.spectra, self.materials, self.lights = [], [], [], []
         self.camera = self.filter = self.film = None
@@ -568,16 +588,23 @@ class Scene:
         self.lights.append(rec)
 
     # ---- geometry
-    def add_mesh(self, P, idx, material, flip, light_params, scene_dir):
+    def add_mesh(self, P, idx, material, flip, light_params, scene_dir, N=None, uv=None):
         P = np.asarray(P, dtype=F32).reshape(-1, 3)
         idx = np.asarray(idx, dtype=np.int32).reshape(-1, 3)
         nt = len(idx)
+        # per-vertex shading normals / uvs ride in scene-wide arrays (zeros for meshes without); tri_flip bits 1 / 2 say
+        # which triangles use them
+        self.N.append((len(P), None if N is None else np.asarray(N, dtype=F32).reshape(-1, 3)))
+        self.uv.append((len(P), None if uv is None else np.asarray(uv, dtype=F32).reshape(-1, 2)))
+        self.any_N |= N is not None
+        self.any_uv |= uv is not None
+        attr = (2 if N is not None else 0) | (4 if uv is not None else 0)
         first_tri = sum(len(i) for i in self.idx)
         self.P.append(P)
         self.idx.append(idx + self.n_verts)
         self.n_verts += len(P)
         self.tri_material.append(np.full(nt, material, dtype=np.int32))
-        self.tri_flip.append(np.full(nt, 1 if flip else 0, dtype=np.uint8))
+        self.tri_flip.append(np.full(nt, (1 if flip else 0) | attr, dtype=np.uint8))
         tl = np.full(nt, -1, dtype=np.int32)
         if light_params is not None:
             # one DiffuseAreaLight per triangle (base/light.cu:56-75, lights/diffuse_area_light.cu:9-31)
@@ -620,6 +647,14 @@ class Scene:
         d.n_triangles, d.indices = len(idx), api._ip(idx)
         d.tri_material, d.tri_light = api._ip(tm), api._ip(tl)
         d.tri_flip = tf.ctypes.data_as(api.C.POINTER(api.C.c_uint8))
+        if self.any_N:
+            Nn = np.ascontiguousarray(np.concatenate([np.zeros((n, 3), F32) if a is None else a for n, a in self.N]), dtype=F32)
+            keep.append(Nn)
+            d.N = api._fp(Nn)
+        if self.any_uv:
+            uvn = np.ascontiguousarray(np.concatenate([np.zeros((n, 2), F32) if a is None else a for n, a in self.uv]), dtype=F32)
+            keep.append(uvn)
+            d.uv = api._fp(uvn)
         C = api.C
         sph = (api.Sphere * max(1, len(self.spheres)))()
         for i, s in enumerate(self.spheres):
@@ -774,9 +809,18 @@ def load(path=None, text=None, spp=None, integrator=None):
         flip = rec["ro"] ^ swaps_handedness(rfo_x.m)
         if rec["kind"] == "mesh":
             Pr = rec["P"] if rec["rfo"].is_identity() else xf_points(rec["rfo"].m, rec["P"])   # shapes/triangle_mesh.cu:49-78
+            Nr = rec.get("N")
+            if Nr is not None and (not rec["rfo"].is_identity() or rec["ro"]):
+                # gpu_transform<Normal3f> (shapes/triangle_mesh.cu:6-18,66-77): Transform::operator()(Normal3f) = inv_m^T n,
+                # not renormalised, negated under ReverseOrientation
+                Nr = xf_normals(rec["rfo"].inv, Nr)
+                if rec["ro"]:
+                    Nr = (-Nr).astype(F32)
             if render_from_instance is not None:
                 Pr = xf_points(render_from_instance.m, Pr)
-            sc.add_mesh(Pr, rec["idx"], rec["material"], flip, area_light, scene_dir)
+                if Nr is not None:
+                    Nr = xf_normals(render_from_instance.inv, Nr)
+            sc.add_mesh(Pr, rec["idx"], rec["material"], flip, area_light, scene_dir, N=Nr, uv=rec.get("uv"))
         else:
             if area_light is not None:
                 raise SceneError("emissive spheres are outside the hot path")
@@ -833,11 +877,17 @@ def load(path=None, text=None, spp=None, integrator=None):
             rfo_x = render_from_world * g.ctm
             if args[0] in ("trianglemesh", "plymesh"):
                 if args[0] == "plymesh":
-                    P, idx, _N = read_ply(os.path.join(scene_dir, p_str(p, "filename", "")))
+                    P, idx, N, uv = read_ply(os.path.join(scene_dir, p_str(p, "filename", "")))
                 else:
                     P = np.array(p["P"][1], dtype=F32).reshape(-1, 3)
                     idx = np.array(p["indices"][1], dtype=np.int32).reshape(-1, 3) if "indices" in p else np.array([[0, 1, 2]], np.int32)
-                rec = {"kind": "mesh", "P": P, "idx": idx}
+                    N = np.array(p["N"][1], dtype=F32).reshape(-1, 3) if "N" in p else None
+                    uv = np.array(p["uv"][1], dtype=F32).reshape(-1, 2) if "uv" in p else None
+                if N is not None and len(N) != len(P):
+                    N = None
+                if uv is not None and len(uv) != len(P):
+                    uv = None
+                rec = {"kind": "mesh", "P": P, "idx": idx, "N": N, "uv": uv}
             elif args[0] == "sphere":
                 r = p_float(p, "radius", 1.0)
                 rec = {"kind": "sphere", "radius": r, "zmin": p_float(p, "zmin", -r), "zmax": p_float(p, "zmax", r),

@@ -107,14 +107,14 @@ def test_ply_reader(b200pt, tmp_path):
     a.write_text("ply\nformat ascii 1.0\nelement vertex 4\nproperty float x\nproperty float y\nproperty float z\n"
                  "element face 1\nproperty list uchar int vertex_indices\nend_header\n" +
                  "".join("%g %g %g\n" % tuple(p) for p in P) + "4 0 1 2 3\n")
-    Pa, ia, _ = ps.read_ply(str(a))
+    Pa, ia, _, _ = ps.read_ply(str(a))
     assert np.array_equal(Pa, P) and ia.tolist() == [[0, 1, 2], [0, 2, 3]]
     b = tmp_path / "b.ply"
     hdr = ("ply\nformat binary_little_endian 1.0\nelement vertex 4\nproperty float x\nproperty float y\nproperty float z\n"
            "element face 2\nproperty list uchar int vertex_indices\nend_header\n").encode()
     faces = b"".join(bytes([3]) + np.int32(t).tobytes() for t in ([0, 1, 2], [0, 2, 3]))
     b.write_bytes(hdr + P.tobytes() + faces)
-    Pb, ib, _ = ps.read_ply(str(b))
+    Pb, ib, _, _ = ps.read_ply(str(b))
     assert np.array_equal(Pb, P) and ib.tolist() == [[0, 1, 2], [0, 2, 3]]
 
 

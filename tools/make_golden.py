@@ -32,6 +32,9 @@ CASES = [
     ("instances_96x64_64spp", "instances.pbrt", None, 64, None, None),
     # Material "mix" (hash-resolved at hit time: statistical gate)
     ("mix_96x64_1024spp", "mix.pbrt", None, 1024, None, None),
+    # per-vertex shading normals + uvs (incl. a mirrored instance and ReverseOrientation); one coated sheet -> statistical in part
+    ("normals_96x64_64spp", "normals.pbrt", None, 64, None, None),
+    ("normals_96x64_1024spp", "normals.pbrt", None, 1024, None, None),
     # C4 in miniature (workloads.procedural_scene, seed 7): many lights -> statistical gate only
     ("c4tiny_96x54_1024spp", "@c4tiny", None, 1024, None, None),
 ]
