@@ -64,7 +64,8 @@ typedef struct {
 /* ---- materials (base/material.cu:97-131) ------------------------------------------------ */
 enum { B200PT_MAT_DIFFUSE = 0, B200PT_MAT_CONDUCTOR = 1, B200PT_MAT_DIELECTRIC = 2, B200PT_MAT_DIFFUSE_TRANSMISSION = 3,
        B200PT_MAT_COATED_DIFFUSE = 4, B200PT_MAT_COATED_CONDUCTOR = 5, B200PT_MAT_COUNT = 6 /* BxDF-bearing types */,
-       B200PT_MAT_MIX = 6 /* resolved to one of its two materials at hit time (materials/mix_material.cu) */ };
+       B200PT_MAT_MIX = 6 /* resolved to one of its two materials at hit time (materials/mix_material.cu) */,
+       B200PT_MAT_INTERFACE = 7 /* Material "interface": no material, the surface only separates media (base/material.cu:34-36) */ };
 typedef struct {
     int32_t type;
     int32_t reflectance; /* spectrum id: diffuse reflectance, or conductor "reflectance" (-1: use eta/k) */
@@ -115,7 +116,14 @@ typedef struct {
     float camera_from_raster[16]; /* row-major 4x4 */
     float render_from_camera[16];
     float lens_radius, focal_distance;
+    int32_t medium;               /* CameraBase::medium (cameras/camera_base.h:99): medium id of camera rays, -1 = vacuum */
 } b200pt_camera;
+
+/* ---- homogeneous media (medium/homogeneous_medium.{h,cu}): sigma_a / sigma_s spectra times "scale", HG phase function */
+typedef struct {
+    int32_t sigma_a, sigma_s; /* spectrum ids */
+    float scale, g;
+} b200pt_medium;
 
 /* ---- pixel filter, tabulated for importance sampling (filters/filter_sampler.{h,cu}) ----- */
 typedef struct {
@@ -152,6 +160,12 @@ typedef struct {
     const b200pt_material *materials;
     int32_t n_lights;
     const b200pt_light *lights;
+    int32_t n_media;
+    const b200pt_medium *media;
+    /* optional [n_triangles], media scenes only: 0 = SimplePrimitive (a spawned ray keeps the medium of the incoming ray,
+     * primitives/simple_primitive.h:28-37); 0xffffffff = GeometricPrimitive without a medium transition (spawned rays get no
+     * medium, primitives/geometric_primitive.cu:20-29); else a MediumInterface: (interior + 1) | (exterior + 1) << 16, 0 = vacuum */
+    const uint32_t *tri_medium;
     const b200pt_camera *camera; /* may be NULL for traversal-only scenes */
     const b200pt_filter *filter;
     const b200pt_film_desc *film;

@@ -47,7 +47,11 @@ class Sphere(C.Structure):
 
 class Camera(C.Structure):
     _fields_ = [("camera_from_raster", C.c_float * 16), ("render_from_camera", C.c_float * 16),
-                ("lens_radius", C.c_float), ("focal_distance", C.c_float)]
+                ("lens_radius", C.c_float), ("focal_distance", C.c_float), ("medium", C.c_int32)]
+
+
+class Medium(C.Structure):
+    _fields_ = [("sigma_a", C.c_int32), ("sigma_s", C.c_int32), ("scale", C.c_float), ("g", C.c_float)]
 
 
 class Filter(C.Structure):
@@ -71,6 +75,7 @@ class SceneDesc(C.Structure):
                 ("n_spectra", C.c_int32), ("spectra", C.POINTER(Spectrum)),
                 ("n_materials", C.c_int32), ("materials", C.POINTER(Material)),
                 ("n_lights", C.c_int32), ("lights", C.POINTER(Light)),
+                ("n_media", C.c_int32), ("media", C.POINTER(Medium)), ("tri_medium", C.POINTER(C.c_uint32)),
                 ("camera", C.POINTER(Camera)), ("filter", C.POINTER(Filter)), ("film", C.POINTER(FilmDesc))]
 
 

@@ -27,6 +27,7 @@
 #include "common.cuh"
 #include "sampler.cuh"
 #include "sphere.cuh"
+#include "traverse.cuh"
 #include "wavefront.cuh"
 
 struct b200pt_film {
@@ -53,6 +54,9 @@ struct RenderData {
     float scene_radius = 0.f;
     bool has_mat[WF_NMAT] = {};
     bool has_mix = false;
+    MediumRec *d_media = nullptr;      // media scenes only
+    uint32_t *d_tri_medium = nullptr;
+    int n_media = 0, camera_medium = -1;
     FilterTab filter = {};
     CameraRec camera = {};
     float *d_cie[3] = {nullptr, nullptr, nullptr};
@@ -287,6 +291,7 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
                  ((spec_ok(m.c_eta) && spec_ok(m.c_k)) || (m.c_eta < 0 && spec_ok(m.reflectance)));
         else if (m.type == B200PT_MAT_CONDUCTOR) ok = (spec_ok(m.eta) && spec_ok(m.k)) || (m.eta < 0 && spec_ok(m.reflectance));
         else if (m.type == B200PT_MAT_DIELECTRIC) ok = spec_ok(m.eta);
+        else if (m.type == B200PT_MAT_INTERFACE) ok = desc->n_media > 0; // only meaningful between media
         else ok = false;
         if (!ok) {
             set_error("b200pt_scene_create: material %d is inconsistent (type %d)", i, m.type);
@@ -304,6 +309,43 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
     if (desc->n_materials == 0) {
         set_error("b200pt_scene_create: a render scene needs at least one material");
         return B200PT_ERR_INVALID;
+    }
+    // ---- media
+    r->n_media = desc->n_media;
+    r->camera_medium = desc->n_media > 0 ? desc->camera->medium : -1;
+    if (desc->n_media > 0) {
+        if (!desc->media || (desc->n_triangles > 0 && !desc->tri_medium)) {
+            set_error("b200pt_scene_create: n_media > 0 needs media and tri_medium");
+            return B200PT_ERR_INVALID;
+        }
+        std::vector<MediumRec> med(desc->n_media);
+        for (int i = 0; i < desc->n_media; i++) {
+            const b200pt_medium &m = desc->media[i];
+            if (!spec_ok(m.sigma_a) || !spec_ok(m.sigma_s)) {
+                set_error("b200pt_scene_create: medium %d: bad spectrum id", i);
+                return B200PT_ERR_INVALID;
+            }
+            med[i] = MediumRec{m.sigma_a, m.sigma_s, m.scale, m.g};
+        }
+        auto med_ok = [&](uint32_t id1) { return id1 <= (uint32_t)desc->n_media; };
+        for (int64_t i = 0; i < desc->n_triangles; i++) {
+            const uint32_t c = desc->tri_medium[i];
+            if (c != 0u && c != 0xffffffffu && !(med_ok(c & 0xffffu) && med_ok(c >> 16))) {
+                set_error("b200pt_scene_create: triangle %lld has medium code 0x%x", (long long)i, c);
+                return B200PT_ERR_INVALID;
+            }
+        }
+        if (r->camera_medium < -1 || r->camera_medium >= desc->n_media) {
+            set_error("b200pt_scene_create: camera medium %d", r->camera_medium);
+            return B200PT_ERR_INVALID;
+        }
+        for (int i = 0; i < desc->n_spheres; i++)
+            if (desc->materials[desc->spheres[i].material].type == B200PT_MAT_INTERFACE) {
+                set_error("b200pt_scene_create: interface spheres are not supported");
+                return B200PT_ERR_UNSUPPORTED;
+            }
+        if ((rc = dev_upload(r, &r->d_media, med.data(), med.size(), st))) return rc;
+        if ((rc = dev_upload(r, &r->d_tri_medium, desc->tri_medium, (size_t)desc->n_triangles, st))) return rc;
     }
     // ---- lights
     r->n_lights = desc->n_lights;
@@ -632,6 +674,10 @@ __global__ void __launch_bounds__(WF_BLOCK) k_generate(WF wf) {
             wf.pool.rng[slot] = s.state;
             // depth 0, next_time_russian_roulette = 8 (util/russian_roulette.h:5)
             wf.pool.ids[slot] = make_int4(pixel, sample, s.dimension, 8 << 16);
+            if (wf.has_media) { // PathState::reset_path (:508-518); camera rays start in the camera's medium (cameras/perspective.cu:85)
+                wf.pool.mtp[slot] = s4(1.f);
+                wf.pool.vol[slot] = make_float4(0.f, __int_as_float(wf.camera_medium), 0.f, 0.f);
+            }
             wf.pool.state[slot] = ST_RAY;
         }
     }
@@ -794,7 +840,189 @@ __device__ __forceinline__ float mix_hash_float(V3 p, V3 err, V3 wo) {
     return __fmul_rn((float)(uint32_t)h, 0x1p-32f);
 }
 
+// ---- media ------------------------------------------------------------------------------------------------------------
+// DenselySampledSpectrum(spectrum, scale)::sample (spectra/densely_sampled_spectrum.h:10-14,46-66): the medium's sigma
+// spectra are tabulated at integer nanometres as spectrum(l) * scale and looked up with a lerp; evaluated here on the fly
+__device__ __forceinline__ float medium_sigma_at(const SpectrumTable &tab, int id, float scale, float lambda) {
+    const float fl = floorf(lambda), ce = ceilf(lambda);
+    if (fl < 360.f || ce > 830.f) return 0.f;
+    return lerpf(lambda - fl, spectrum_at(tab, id, fl) * scale, spectrum_at(tab, id, ce) * scale);
+}
+__device__ __forceinline__ S4 medium_sigma(const SpectrumTable &tab, int id, float scale, S4 l) {
+    return make_float4(medium_sigma_at(tab, id, scale, l.x), medium_sigma_at(tab, id, scale, l.y), medium_sigma_at(tab, id, scale, l.z),
+                       medium_sigma_at(tab, id, scale, l.w));
+}
+// Medium::sample_sigma_t (medium/homogeneous_medium.cu:43-47)
+__device__ __forceinline__ S4 medium_sigma_t(const WF &wf, int medium, S4 lambda) {
+    const MediumRec M = wf.media[medium];
+    return medium_sigma(wf.spectra, M.sigma_a, M.scale, lambda) + medium_sigma(wf.spectra, M.sigma_s, M.scale, lambda);
+}
+__device__ __forceinline__ S4 exp_s4(S4 a) { return make_float4(expf(a.x), expf(a.y), expf(a.z), expf(a.w)); }
+
+// Interaction::get_medium(w) (base/interaction.h:60-66) for a hit on triangle `prim_id` (< 0: a sphere, always a
+// SimplePrimitive here): a medium transition picks exterior / interior by the side of the GEOMETRIC normal, a SimplePrimitive
+// hands on the medium of the ray that hit it, a GeometricPrimitive without transition has no medium at all
+// (primitives/geometric_primitive.cu:27, base/interaction.cu:59-63)
+__device__ __forceinline__ int surface_medium(const WF &wf, int prim_id, V3 n, V3 w, int ray_medium) {
+    if (prim_id < 0) return ray_medium;
+    const uint32_t code = wf.tri_medium[prim_id];
+    if (code == 0u) return ray_medium;
+    if (code == 0xffffffffu) return -1;
+    return dot(n, w) > 0.f ? int(code >> 16) - 1 : int(code & 0xffffu) - 1;
+}
+
+constexpr int VOL_BLOCK = 128;
+
+// IntegratorBase::compute_transmittance (base/integrator_base.cu:22-71) from a point INSIDE a medium (no normal, no error
+// bounds) to the light sample: march the normalised shadow ray from hit to hit, attenuating by the medium of each segment;
+// any surface with a material blocks, material-less interfaces are crossed (normal := ray direction, so the far side is
+// the interface's exterior, or whatever a plain primitive hands on).
+__device__ __forceinline__ S4 volume_transmittance(const WF &wf, V3 p0, int medium, const LightSample &ls, S4 lambda, uint2 *sm_stack,
+                                                   unsigned *overflow) {
+    const float epsilon_distance = len(p0 - ls.p) * 1e-4f;
+    const V3 pf = p0; // offset_ray_origin with n = 0 moves nothing (base/ray.h:30-49)
+    const V3 pt = offset_ray_origin(ls.p, ls.err, ls.n, pf - ls.p);
+    V3 o = pf;
+    const V3 d = normalize(pt - pf);
+    bool previous_self_intersection = false;
+    S4 T = s4(1.f);
+    for (int depth = 0; depth < 128; depth++) { // MAX_VOLUME_BOUNCES (base/integrator_base.h:21)
+        const float distance_to_light = len(ls.p - o);
+        const float t_max = (float)((1.0 - (double)1e-4f) * (double)distance_to_light);
+        RayHit h;
+        TraceCounters ctr;
+        traverse_bvh8<false, false, true>(wf.bvh, o.x, o.y, o.z, d.x, d.y, d.z, t_max, sm_stack, VOL_BLOCK, h, ctr, overflow);
+        bool sphere_closer = false;
+        for (int k = 0; k < wf.n_spheres; k++) {
+            SphereHit sh;
+            if (sphere_intersect(wf.spheres[k], o, d, h.t, sh)) {
+                sphere_closer = true;
+                break;
+            }
+        }
+        const bool hit = sphere_closer || h.prim >= 0;
+        // a sphere always carries a material here, so a sphere in front of the triangle hit ends the walk with 0 whatever
+        // its exact distance; otherwise next_t is the triangle hit
+        const float next_t = hit ? h.t : distance_to_light;
+        if (medium >= 0) T = T * exp_s4(medium_sigma_t(wf, medium, lambda) * (-next_t));
+        if (!hit) return T;
+        if (sphere_closer) return s4(0.f);
+        const float4 *tp = wf.bvh.tris + 3 * (size_t)h.prim;
+        const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+        const uint32_t mw = __float_as_uint(v1.w);
+        if (wf.materials[mw & 0x1fffffffu].type != B200PT_MAT_INTERFACE) return s4(0.f);
+        // interaction.n = d; shadow_ray = interaction.spawn_ray(d)
+        const float b1 = h.b1, b2 = h.b2, b0 = 1.f - b1 - b2;
+        const V3 q0 = v3(v0), q1 = v3(v1), q2 = v3(v2);
+        const V3 p = b0 * q0 + b1 * q1 + b2 * q2;
+        const V3 err = gamma_n(7) * (vabs(b0 * q0) + vabs(b1 * q1) + vabs(b2 * q2));
+        o = offset_ray_origin(p, err, d, d);
+        medium = surface_medium(wf, __float_as_int(v0.w), d, d, medium);
+        if (h.t < epsilon_distance) {
+            if (previous_self_intersection) o = o + epsilon_distance * d; // forced offset against self-intersection
+            previous_self_intersection = true;
+        } else {
+            previous_self_intersection = false;
+        }
+    }
+    return s4(0.f); // the reference aborts here (REPORT_FATAL_ERROR)
+}
+
+// ---- volume_scatter (integrators/wavefront_path.cu:368-436) + the volume branch of sample_Ld_volume
+// (integrators/megakernel_path.cu:185-264) -- runs between the closest-hit trace and the logic stage, over every traced slot:
+// ray_cast clears in_volume for all of them (:361), rays inside a medium then either pass through to their hit
+// (multi_transmittance_pdf *= exp(-sigma_t t_max)) or scatter: the origin moves to the scattering point, direct light is
+// gathered THROUGH interfaces with the transmittance walk above, and a new direction is drawn from the phase function.
+__global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
+    __shared__ uint2 s_stack[SM_STACK * VOL_BLOCK];
+    const unsigned n = (unsigned)wf.pool_size;
+    const unsigned stride = gridDim.x * blockDim.x;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        if (wf.pool.state[i] != ST_RAY) continue;
+        const int slot = (int)i;
+        int4 ids = wf.pool.ids[slot];
+        const bool was_in_volume = (ids.w & PF_IN_VOLUME) != 0;
+        ids.w &= ~PF_IN_VOLUME;
+        float4 vol = wf.pool.vol[slot];
+        const int medium = __float_as_int(vol.y);
+        const float4 ro4 = wf.pool.ray_o[slot];
+        if (medium < 0 || ro4.w < 0.f) {
+            if (was_in_volume) wf.pool.ids[slot] = ids;
+            continue;
+        }
+        const float4 rd4 = wf.pool.ray_d[slot];
+        const V3 ro = v3(ro4), rd = v3(rd4);
+        const S4 lambda = wf.pool.lambda[slot];
+        const MediumRec M = wf.media[medium];
+        const S4 sigma_s = medium_sigma(wf.spectra, M.sigma_s, M.scale, lambda);
+        const S4 sigma_t = medium_sigma(wf.spectra, M.sigma_a, M.scale, lambda) + sigma_s;
+        const float4 hit = wf.pool.hit[slot];
+        const float t_max = __float_as_int(hit.x) >= 0 ? hit.y : kInf;
+        Sampler s = load_sampler(wf, slot, ids);
+        const float t = -logf(1.f - s.get_1d()) / average(sigma_t); // sample_exponential (util/sampling.h:67-69)
+        if (t >= t_max) {
+            // pass through the medium
+            wf.pool.mtp[slot] = wf.pool.mtp[slot] * exp_s4(sigma_t * (-t_max));
+        } else {
+            const V3 o = ro + rd * t;
+            S4 beta = wf.pool.beta[slot] * (sigma_s / sigma_t);
+            // -- sample_Ld_volume(medium_interaction, nullptr, ..): ctx = the bare point
+            const LightCtx ctx{o, v3(0.f, 0.f, 0.f), v3(0.f, 0.f, 0.f), v3(0.f, 0.f, 0.f)};
+            const float ul = s.get_1d();
+            const float2 up = s.get_2d();
+            if (wf.n_lights > 0) {
+                const int li = alias_sample(wf.alias, wf.n_lights, ul);
+                const LightRec Lr = wf.lights[li];
+                const int lt = light_type(Lr);
+                LightSample ls;
+                bool have, delta = false;
+                float lw = 1.f, ld2 = 1.f;
+                if (lt == B200PT_LIGHT_AREA) have = light_sample(Lr, ctx, up, ls) && light_emits_towards(Lr, ls.n, -ls.wi);
+                else have = light_sample_other(Lr, lt, wf.light_ext, wf.scene_radius, ctx, up, ls, &lw, &ld2, &delta);
+                if (have) {
+                    S4 Le;
+                    if (lt == B200PT_LIGHT_SPOT) Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * (lw * Lr.scale) / ld2;
+                    else Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * Lr.scale;
+                    if (is_positive(Le) && ls.pdf != 0.f) {
+                        const S4 T = volume_transmittance(wf, o, medium, ls, lambda, s_stack + threadIdx.x, &wf.c->stack_overflow);
+                        const float pdf_light = Lr.pmf * ls.pdf;
+                        const S4 contribution = Le / pdf_light * T;
+                        // the phase function is SAMPLED here, not evaluated towards the light (megakernel_path.cu:247-263)
+                        float ppdf;
+                        (void)sample_henyey_greenstein(-rd, M.g, s.get_2d(), &ppdf);
+                        S4 Ld;
+                        if (delta) Ld = contribution * ppdf;
+                        else Ld = contribution * (power_heuristic(pdf_light, ppdf * average(T)) * ppdf);
+                        wf.pool.L[slot] = wf.pool.L[slot] + beta * Ld;
+                    }
+                }
+            }
+            float ppdf;
+            const V3 wi = sample_henyey_greenstein(-rd, M.g, s.get_2d(), &ppdf);
+            beta = beta * (ppdf / ppdf); // rho / pdf
+            wf.pool.beta[slot] = beta;
+            float4 misc = wf.pool.misc[slot];
+            misc.y = ppdf;
+            wf.pool.misc[slot] = misc;
+            wf.pool.ctx0[slot] = make_float4(o.x, o.y, o.z, 0.f);
+            wf.pool.ctx1[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+            wf.pool.ctx2[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+            wf.pool.ray_o[slot] = make_float4(o.x, o.y, o.z, kInf);
+            wf.pool.ray_d[slot] = make_float4(wi.x, wi.y, wi.z, 0.f);
+            wf.pool.mtp[slot] = s4(1.f);
+            vol.x += 1.f;
+            wf.pool.vol[slot] = vol;
+            // not re-traced at once: the logic stage first applies russian roulette and the depth limit (:431-432)
+            ids.w = (ids.w & ~PF_SPECULAR) | PF_ANY_NON_SPECULAR | PF_IN_VOLUME;
+        }
+        ids.z = s.dimension;
+        wf.pool.ids[slot] = ids;
+        wf.pool.rng[slot] = s.state;
+    }
+}
+
 // ---- control_logic (integrators/wavefront_path.cu:68-214)
+template <bool MEDIA>
 __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
     // one thread per pool slot, in slot order: every lane access below is a coalesced 16-byte gather
     const unsigned n = (unsigned)wf.pool_size;
@@ -805,10 +1033,15 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
         const bool act = i < n && wf.pool.state[i] == ST_RAY;
         const int slot = (int)i;
         int route = -1; // route: material type, or -1
-        bool terminate = false;
+        bool terminate = false, stay = false; // stay: the slot keeps ST_RAY (scattered in a medium / crossed an interface)
         if (act) {
             int4 ids = wf.pool.ids[slot];
-            int depth = (ids.w >> 8) & 0xff, next_rr = (ids.w >> 16) & 0xff;
+            int next_rr = (ids.w >> 16) & 0xff;
+            // depth is a float in the reference (integrators/wavefront_path.h:40-41) because a material-less interface counts
+            // 0.3 of a bounce; without media it only ever holds small integers and lives in the flags word
+            float4 vol = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (MEDIA) vol = wf.pool.vol[slot];
+            float depth = MEDIA ? vol.x : float((ids.w >> 8) & 0xff);
             S4 beta = wf.pool.beta[slot];
             S4 L = wf.pool.L[slot];
             const float4 hit = wf.pool.hit[slot];
@@ -830,7 +1063,13 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                 wf.pool.rng[slot] = s.state;
                 ids.z = s.dimension;
             }
-            if (!terminate && prim < 0) {
+            // a path that scattered inside a medium this pass (k_volume) has a new ray and a stale hit record: it goes
+            // straight back to the trace stage (:99-103).  One that russian roulette just zeroed would be retired by the
+            // next logic stage with the same L, so it is retired now.
+            const bool in_volume = MEDIA && (ids.w & PF_IN_VOLUME) && !terminate;
+            if (in_volume) stay = true;
+            const float dir_pdf_scale = MEDIA ? average(wf.pool.mtp[slot]) : 1.f; // multi_transmittance_pdf.average() (:118,165)
+            if (!terminate && !stay && prim < 0) {
                 // escaped: infinite lights' Le, MIS-weighted against NEE (integrators/wavefront_path.cu:105-127).
                 // pdf_li(.., allow_incomplete_pdf = true) of the uniform infinite light is 0
                 // (lights/uniform_infinite_light.cu:51-58), so the weight is power_heuristic(dir_pdf, 0)
@@ -841,13 +1080,32 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                         L = L + beta * Le;
                     } else {
                         const float pdf_light = Lr.pmf * 0.f;
-                        const float dir_pdf = wf.pool.misc[slot].y;
+                        const float dir_pdf = wf.pool.misc[slot].y * dir_pdf_scale;
                         L = L + beta * power_heuristic(dir_pdf, pdf_light) * Le;
                     }
                 }
                 terminate = true;
             }
-            if (!terminate) {
+            if (!terminate && !stay && MEDIA && prim < (int)wf.bvh.n_tris) {
+                const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
+                const float4 v1 = __ldg(tp + 1);
+                const uint32_t mw = __float_as_uint(v1.w);
+                if (wf.materials[mw & 0x1fffffffu].type == B200PT_MAT_INTERFACE) {
+                    // material-less interface (:146-151, gpu_evaluate_interface_material :303-320): 0.3 of a bounce, the ray
+                    // carries on in the same direction from the far side, in the medium found there
+                    const float4 v0 = __ldg(tp), v2 = __ldg(tp + 2);
+                    const V3 rd = v3(wf.pool.ray_d[slot]);
+                    Isect si;
+                    triangle_interaction(wf, v3(v0), v3(v1), v3(v2), __float_as_int(v0.w), mw, hit.z, hit.w, -rd, si);
+                    const V3 o = offset_ray_origin(si.p, si.err, si.n, rd);
+                    wf.pool.ray_o[slot] = make_float4(o.x, o.y, o.z, kInf);
+                    vol.x = depth + 0.3f;
+                    vol.y = __int_as_float(surface_medium(wf, __float_as_int(v0.w), si.n, rd, __float_as_int(vol.y)));
+                    wf.pool.vol[slot] = vol;
+                    stay = true;
+                }
+            }
+            if (!terminate && !stay) {
                 int mat;
                 if (prim >= (int)wf.bvh.n_tris) {
                     mat = wf.spheres[prim - (int)wf.bvh.n_tris].material;
@@ -872,7 +1130,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                                     const float4 c0 = wf.pool.ctx0[slot], c1 = wf.pool.ctx1[slot], c2 = wf.pool.ctx2[slot];
                                     const LightCtx ctx{v3(c0), v3(c0.w, c1.w, c2.w), v3(c1), v3(c2)};
                                     const float pdf_light = Lr.pmf * light_pdf(Lr, ctx, rd);
-                                    const float dir_pdf = wf.pool.misc[slot].y;
+                                    const float dir_pdf = wf.pool.misc[slot].y * dir_pdf_scale;
                                     L = L + beta * Le * power_heuristic(dir_pdf, pdf_light);
                                 }
                                 dirty_L = true;
@@ -896,7 +1154,11 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                     misc.z = __int_as_float(mat); // the shade stage reads the resolved material from here
                     wf.pool.misc[slot] = misc;
                 }
-                depth += 1;
+                depth += 1.f;
+                if (MEDIA) {
+                    vol.x = depth;
+                    wf.pool.vol[slot] = vol;
+                }
                 route = wf.materials[mat].type;
             }
             if (terminate) {
@@ -905,12 +1167,12 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                 n_finished++;
             } else {
                 if (dirty_L) wf.pool.L[slot] = L;
-                ids.w = (ids.w & 0xff) | (depth << 8) | (next_rr << 16);
+                ids.w = (ids.w & 0xff) | ((MEDIA ? 0 : (int)depth) << 8) | (next_rr << 16);
                 wf.pool.ids[slot] = ids;
             }
         }
-        const int cat = (act && terminate) ? WF_NMAT : route; // material queue, WF_NMAT = free list, -1 nothing
-        if (act) wf.pool.state[slot] = terminate ? ST_FREE : uint8_t(ST_MAT0 + route);
+        const int cat = (act && terminate) ? WF_NMAT : route; // material queue, WF_NMAT = free list, -1 nothing (the slot stays a ray)
+        if (act && !stay) wf.pool.state[slot] = terminate ? ST_FREE : uint8_t(ST_MAT0 + route);
         block_push(wf, cat, slot);
     }
     // finished-path count: warp reduce, one atomic per warp
@@ -1044,7 +1306,7 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_COATED_CONDUCTOR>(const WF 
 }
 
 // ---- gpu_evaluate_material + sample_bsdf + sample_Ld_volume, specialised per material
-template <int MAT>
+template <int MAT, bool MEDIA>
 __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ? 1 : 2) k_shade(WF wf) {
     const unsigned n = wf.c->n_mat[MAT];
     const unsigned stride = gridDim.x * blockDim.x;
@@ -1061,7 +1323,7 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
             const float4 hit = wf.pool.hit[slot];
             const int prim = __float_as_int(hit.x);
             Isect si;
-            int mat;
+            int mat, prim_id = -1;
             if (prim >= (int)wf.bvh.n_tris) {
                 const SphereRec &sp = wf.spheres[prim - (int)wf.bvh.n_tris];
                 sphere_interaction(sp, ro, rd, hit.y, -rd, si);
@@ -1071,9 +1333,12 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
                 const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                 const uint32_t mw = __float_as_uint(v1.w);
                 mat = int(mw & 0x1fffffffu);
-                triangle_interaction(wf, v3(v0), v3(v1), v3(v2), __float_as_int(v0.w), mw, hit.z, hit.w, -rd, si);
+                prim_id = __float_as_int(v0.w);
+                triangle_interaction(wf, v3(v0), v3(v1), v3(v2), prim_id, mw, hit.z, hit.w, -rd, si);
             }
             if (wf.has_mix && wf.materials[mat].type == B200PT_MAT_MIX) mat = __float_as_int(wf.pool.misc[slot].z);
+            float4 vol = make_float4(0.f, 0.f, 0.f, 0.f); // media scenes: .y = medium of the ray that arrived here
+            if (MEDIA) vol = wf.pool.vol[slot];
             const MatRec m = wf.materials[mat];
             const S4 lambda = wf.pool.lambda[slot];
             S4 lpdf = wf.pool.lpdf[slot];
@@ -1121,15 +1386,27 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
                             const S4 f = bsdf.f(wo_l, wi_l) * absdot(ls.wi, si.ns);
                             if (is_positive(f)) {
                                 const float pdf_light = Lr.pmf * ls.pdf;
-                                // delta lights: no MIS (megakernel_path.cu:236-239)
-                                const float w = delta ? 1.f : power_heuristic(pdf_light, bsdf.pdf(wo_l, wi_l));
-                                const S4 Ld = f * (Le / pdf_light) * w;
                                 // visibility: Ray::spawn_ray_to (base/ray.h:51-58) from the surface point to the
                                 // light point, both ends offset; the segment (0, 1] of the un-normalised ray covers
                                 // the union of the reference's three visibility rays (integrator_base.cu:12-14,24-33)
                                 const V3 pf = offset_ray_origin(si.p, si.err, si.n, ls.p - si.p);
                                 const V3 pt = offset_ray_origin(ls.p, ls.err, ls.n, pf - ls.p);
                                 const V3 sd = pt - pf;
+                                // compute_transmittance (base/integrator_base.cu:22-71) for a surface point: `unoccluded` lets
+                                // nothing through, interfaces included, so whenever the sample survives the walk was one
+                                // segment from pf to the light point inside the medium on that side of the surface
+                                float pdf_bsdf = delta ? 0.f : bsdf.pdf(wo_l, wi_l);
+                                if (MEDIA) {
+                                    const int sm = surface_medium(wf, prim_id, si.n, sd, __float_as_int(vol.y));
+                                    if (sm >= 0) {
+                                        const S4 T = exp_s4(medium_sigma_t(wf, sm, lambda) * (-len(ls.p - pf)));
+                                        Le = Le * T;
+                                        pdf_bsdf *= average(T);
+                                    }
+                                }
+                                // delta lights: no MIS (megakernel_path.cu:236-239)
+                                const float w = delta ? 1.f : power_heuristic(pdf_light, pdf_bsdf);
+                                const S4 Ld = f * (Le / pdf_light) * w;
                                 shadow = true;
                                 sh_o = make_float4(pf.x, pf.y, pf.z, 1.f);
                                 sh_d = make_float4(sd.x, sd.y, sd.z, __int_as_float(Lr.prim)); // .w: primitive to skip
@@ -1167,6 +1444,11 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
                 const V3 o = offset_ray_origin(si.p, si.err, si.n, wi);
                 wf.pool.ray_o[slot] = make_float4(o.x, o.y, o.z, kInf);
                 wf.pool.ray_d[slot] = make_float4(wi.x, wi.y, wi.z, 0.f);
+                if (MEDIA) {
+                    vol.y = __int_as_float(surface_medium(wf, prim_id, si.n, wi, __float_as_int(vol.y)));
+                    wf.pool.vol[slot] = vol;
+                    wf.pool.mtp[slot] = s4(1.f); // :463
+                }
             }
             ids.z = s.dimension;
             wf.pool.ids[slot] = ids;
@@ -1209,6 +1491,11 @@ static int ensure_pool(b200pt_scene *s, int pool_size) {
     float4 **lanes[] = {&P.ray_o, &P.ray_d, &P.hit, &P.beta, &P.L, &P.lambda, &P.lpdf, &P.ctx0, &P.ctx1, &P.ctx2, &P.misc};
     for (float4 **l : lanes)
         if ((rc = pool_alloc(r, l, n))) return rc;
+    P.mtp = P.vol = nullptr;
+    if (r->n_media > 0) { // two more lanes, media scenes only
+        if ((rc = pool_alloc(r, &P.mtp, n))) return rc;
+        if ((rc = pool_alloc(r, &P.vol, n))) return rc;
+    }
     if ((rc = pool_alloc(r, &P.rng, n))) return rc;
     if ((rc = pool_alloc(r, &P.ids, n))) return rc;
     if ((rc = pool_alloc(r, &P.state, n))) return rc;
@@ -1332,6 +1619,10 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     for (int k = 0; k < 4; k++) wf.infinite[k] = r->infinite[k];
     wf.scene_radius = r->scene_radius;
     wf.has_mix = r->has_mix ? 1 : 0;
+    wf.media = r->d_media;
+    wf.tri_medium = r->d_tri_medium;
+    wf.has_media = r->n_media > 0 ? 1 : 0;
+    wf.camera_medium = r->camera_medium;
     // a warp of k_trace_wf fetches new rays once this many lanes are idle: 4 is the measured best on triangle-only scenes;
     // with spheres the per-ray start-up is longer and waiting for half a warp pays (C1: 62.0 -> 58.5 ms together with the
     // sphere phase)
@@ -1382,20 +1673,40 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
         for (int b = 0; b < batch; b++) {
             k_pass_begin<<<1, 1, 0, st>>>(wf);
             if ((rc = launch_trace_wf(s, wf, false))) return rc;
-            k_logic<<<grid, WF_BLOCK, 0, st>>>(wf);
+            if (wf.has_media) k_volume<<<grid, VOL_BLOCK, 0, st>>>(wf);
+            if (wf.has_media) k_logic<true><<<grid, WF_BLOCK, 0, st>>>(wf);
+            else k_logic<false><<<grid, WF_BLOCK, 0, st>>>(wf);
             k_generate<<<grid, WF_BLOCK, 0, st>>>(wf);
             k_after_generate<<<1, 1, 0, st>>>(wf);
             // one shade kernel per material type PRESENT in the scene (a type without materials has no queue)
-            if (r->has_mat[B200PT_MAT_DIFFUSE]) k_shade<B200PT_MAT_DIFFUSE><<<grid, WF_BLOCK, 0, st>>>(wf);
-            if (r->has_mat[B200PT_MAT_CONDUCTOR]) k_shade<B200PT_MAT_CONDUCTOR><<<grid, WF_BLOCK, 0, st>>>(wf);
-            if (r->has_mat[B200PT_MAT_DIELECTRIC]) k_shade<B200PT_MAT_DIELECTRIC><<<grid, WF_BLOCK, 0, st>>>(wf);
-            if (r->has_mat[B200PT_MAT_DIFFUSE_TRANSMISSION]) k_shade<B200PT_MAT_DIFFUSE_TRANSMISSION><<<grid, WF_BLOCK, 0, st>>>(wf);
-            if (r->has_mat[B200PT_MAT_COATED_DIFFUSE]) k_shade<B200PT_MAT_COATED_DIFFUSE><<<grid, WF_BLOCK, 0, st>>>(wf);
-            if (r->has_mat[B200PT_MAT_COATED_CONDUCTOR]) k_shade<B200PT_MAT_COATED_CONDUCTOR><<<grid, WF_BLOCK, 0, st>>>(wf);
+            if (r->has_mat[B200PT_MAT_DIFFUSE]) {
+                if (wf.has_media) k_shade<B200PT_MAT_DIFFUSE, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else k_shade<B200PT_MAT_DIFFUSE, false><<<grid, WF_BLOCK, 0, st>>>(wf);
+            }
+            if (r->has_mat[B200PT_MAT_CONDUCTOR]) {
+                if (wf.has_media) k_shade<B200PT_MAT_CONDUCTOR, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else k_shade<B200PT_MAT_CONDUCTOR, false><<<grid, WF_BLOCK, 0, st>>>(wf);
+            }
+            if (r->has_mat[B200PT_MAT_DIELECTRIC]) {
+                if (wf.has_media) k_shade<B200PT_MAT_DIELECTRIC, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else k_shade<B200PT_MAT_DIELECTRIC, false><<<grid, WF_BLOCK, 0, st>>>(wf);
+            }
+            if (r->has_mat[B200PT_MAT_DIFFUSE_TRANSMISSION]) {
+                if (wf.has_media) k_shade<B200PT_MAT_DIFFUSE_TRANSMISSION, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else k_shade<B200PT_MAT_DIFFUSE_TRANSMISSION, false><<<grid, WF_BLOCK, 0, st>>>(wf);
+            }
+            if (r->has_mat[B200PT_MAT_COATED_DIFFUSE]) {
+                if (wf.has_media) k_shade<B200PT_MAT_COATED_DIFFUSE, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else k_shade<B200PT_MAT_COATED_DIFFUSE, false><<<grid, WF_BLOCK, 0, st>>>(wf);
+            }
+            if (r->has_mat[B200PT_MAT_COATED_CONDUCTOR]) {
+                if (wf.has_media) k_shade<B200PT_MAT_COATED_CONDUCTOR, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else k_shade<B200PT_MAT_COATED_CONDUCTOR, false><<<grid, WF_BLOCK, 0, st>>>(wf);
+            }
             if ((rc = launch_trace_wf(s, wf, true))) return rc;
             k_pass_end<<<1, 1, 0, st>>>(wf);
             passes++;
-            launches += 7 + n_shade_kernels;
+            launches += 7 + n_shade_kernels + (wf.has_media ? 1 : 0);
         }
         CU_TRY(cudaGetLastError());
         const int cur = int(k & 1);

@@ -99,8 +99,9 @@ __device__ __forceinline__ uint32_t intersect_node8(const float4 &n0, const floa
     return hitmask;
 }
 
-// sm_stack: this thread's column of the CTA's shared stack, addressed as sm_stack[depth * stride]
-template <bool ANY, bool COUNT>
+// sm_stack: this thread's column of the CTA's shared stack, addressed as sm_stack[depth * stride].
+// hit.prim = the triangle's primitive id, or (SLOT) its leaf-order record index.
+template <bool ANY, bool COUNT, bool SLOT = false>
 __device__ __forceinline__ bool traverse_bvh8(const BVH8 &bvh, float ox, float oy, float oz, float dx, float dy, float dz,
                                               float t_max, uint2 *sm_stack, int stride, RayHit &hit, TraceCounters &ctr,
                                               unsigned *overflow_flag) {
@@ -156,7 +157,7 @@ __device__ __forceinline__ bool traverse_bvh8(const BVH8 &bvh, float ox, float o
                 hit.t = th.t;
                 hit.b1 = th.b1;
                 hit.b2 = th.b2;
-                hit.prim = __float_as_int(v0.w);
+                hit.prim = SLOT ? int(tg.x + ti) : __float_as_int(v0.w);
                 if (ANY) return true;
             }
         }

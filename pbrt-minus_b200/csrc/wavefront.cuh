@@ -28,6 +28,11 @@ struct MatRec {
 };
 constexpr int WF_NMAT = B200PT_MAT_COUNT; // one shading queue per material type
 
+struct MediumRec { // medium/homogeneous_medium.h: two DenselySampledSpectrum(spectrum, scale) + HGPhaseFunction(g)
+    int32_t sigma_a, sigma_s;
+    float scale, g;
+};
+
 struct FilterTab {
     int32_t nx, ny;
     float min_x, max_x, min_y, max_y;
@@ -55,7 +60,7 @@ struct FilmRec {
 
 // flags word of a path (ids.w): bit 0 specular_bounce, bit 1 any_non_specular_bounces,
 // bits 8..15 depth, bits 16..23 next_time_russian_roulette
-constexpr int PF_SPECULAR = 1, PF_ANY_NON_SPECULAR = 2;
+constexpr int PF_SPECULAR = 1, PF_ANY_NON_SPECULAR = 2, PF_IN_VOLUME = 4;
 
 // per-slot state byte: what the next stage has to do with the slot
 enum : uint8_t { ST_IDLE = 0, ST_RAY = 1, ST_MAT0 = 2 /* + material type */, ST_FREE = ST_MAT0 + WF_NMAT };
@@ -69,6 +74,8 @@ struct PathPool {
     float4 *ctx1;   //                          n.xyz, err.y
     float4 *ctx2;   //                          ns.xyz, err.z
     float4 *misc;   // filter_weight, prev_direction_pdf, -, -
+    float4 *mtp;    // media scenes only: multi_transmittance_pdf (integrators/wavefront_path.h:37)
+    float4 *vol;    // media scenes only: depth (a FLOAT: +0.3 per interface bounce), medium id of the ray (int bits), -, -
     uint64_t *rng;  // PCG32 state (inc is re-derived from the pixel index)
     int4 *ids;      // pixel, sample, sampler dimension, flags
     uint8_t *state; // ST_*
@@ -104,6 +111,11 @@ struct WF {
     // primitive id and the index buffer); null when no mesh has any
     const float *N, *uv;
     const int32_t *idx;
+    // media (null / 0 when the scene has none): table, per-triangle medium code by primitive id (b200pt.h: tri_medium),
+    // camera medium
+    const MediumRec *media;
+    const uint32_t *tri_medium;
+    int32_t has_media, camera_medium;
     SpectrumTable spectra;
     const MatRec *materials;
     const LightRec *lights;

@@ -364,6 +364,7 @@ class Scene:
     def __init__(self):
         self.P, self.idx, self.tri_material, self.tri_light, self.tri_flip = [], [], [], [], []
         self.N, self.uv, self.any_N, self.any_uv = [], [], False, False
+        self.media, self.tri_medium, self.camera_medium = [], [], -1
         self.n_verts = 0
         self.spheres, self.spectra, self.materials, self.lights = [], [], [], []
         self.camera = self.filter = self.film = None
@@ -465,6 +466,9 @@ class Scene:
             self.materials.append({"type": 3, "reflectance": self.spec_constant(0.25) if r is None else r, "eta": -1, "k": -1,
                                    "ur": 0.0, "vr": 0.0, "remap": 1, "transmittance": self.spec_constant(0.25) if t is None else t,
                                    "scale": p_float(p, "scale", 1.0)})
+        elif kind == "interface":
+            # base/material.cu:34-36: no material at all; the surface only separates media
+            self.materials.append({"type": 7, "reflectance": -1, "eta": -1, "k": -1, "ur": 0.0, "vr": 0.0, "remap": 1})
         elif kind == "mix":
             # materials/mix_material.cu:6-16: two NAMED materials and an amount in (0, 1)
             amount = p_float(p, "amount", 0.5)
@@ -516,6 +520,18 @@ class Scene:
         else:
             raise SceneError("Material '%s' is outside the hot path (SURVEY.md 8f)" % kind)
         return len(self.materials) - 1
+
+    # ---- media (Medium::create, medium/homogeneous_medium.cu:15-41)
+    def add_medium(self, p, scene_dir):
+        if p_str(p, "type", "homogeneous") != "homogeneous":
+            raise SceneError("only homogeneous media (medium/homogeneous_medium.h)")
+        if "Le" in p and p_float(p, "Lescale", 1.0) != 0:
+            raise SceneError("illuminating volume not implemented (homogeneous_medium.cu:25-30)")
+        sa = self.spec_param(p, "sigma_a", "unbounded", scene_dir)
+        ss = self.spec_param(p, "sigma_s", "unbounded", scene_dir)
+        self.media.append({"sigma_a": self.spec_constant(1.0) if sa is None else sa, "sigma_s": self.spec_constant(1.0) if ss is None else ss,
+                           "scale": p_float(p, "scale", 1.0), "g": p_float(p, "g", 0.0)})
+        return len(self.media) - 1
 
     # ---- lights that are not emissive shapes (SceneBuilder::parse_light_source, scene_builder.cu:493-504)
     def add_light_source(self, kind, p, render_from_light, scene_dir):
@@ -588,7 +604,7 @@ class Scene:
         self.lights.append(rec)
 
     # ---- geometry
-    def add_mesh(self, P, idx, material, flip, light_params, scene_dir, N=None, uv=None):
+    def add_mesh(self, P, idx, material, flip, light_params, scene_dir, N=None, uv=None, medium_code=0):
         P = np.asarray(P, dtype=F32).reshape(-1, 3)
         idx = np.asarray(idx, dtype=np.int32).reshape(-1, 3)
         nt = len(idx)
@@ -605,6 +621,7 @@ class Scene:
         self.n_verts += len(P)
         self.tri_material.append(np.full(nt, material, dtype=np.int32))
         self.tri_flip.append(np.full(nt, (1 if flip else 0) | attr, dtype=np.uint8))
+        self.tri_medium.append(np.full(nt, medium_code, dtype=np.uint32))
         tl = np.full(nt, -1, dtype=np.int32)
         if light_params is not None:
             # one DiffuseAreaLight per triangle (base/light.cu:56-75, lights/diffuse_area_light.cu:9-31)
@@ -697,8 +714,17 @@ class Scene:
                 lights[i].cos_falloff_start, lights[i].cos_falloff_end = l["cs"], l["ce"]
         d.n_lights, d.lights = len(self.lights), lights
         keep += [sph, spec, mats, lights]
+        if self.media:
+            med = (api.Medium * len(self.media))()
+            for i, m in enumerate(self.media):
+                med[i].sigma_a, med[i].sigma_s, med[i].scale, med[i].g = m["sigma_a"], m["sigma_s"], m["scale"], m["g"]
+            tmed = np.ascontiguousarray(np.concatenate(self.tri_medium) if self.idx else np.zeros(0, np.uint32), dtype=np.uint32)
+            d.n_media, d.media = len(self.media), med
+            d.tri_medium = tmed.ctypes.data_as(api.C.POINTER(api.C.c_uint32))
+            keep += [med, tmed]
         if self.camera is not None:
             cam = api.Camera()
+            cam.medium = self.camera_medium
             cam.camera_from_raster[:] = [float(v) for v in self.camera["cfr"].reshape(-1)]
             cam.render_from_camera[:] = [float(v) for v in self.camera["rfc"].reshape(-1)]
             cam.lens_radius, cam.focal_distance = self.camera["lens_radius"], self.camera["focal_distance"]
@@ -725,10 +751,12 @@ class _GState:
         self.reverse_orientation = False
         self.material = 0
         self.area_light = None
+        self.medium_interface = None   # (interior id, exterior id), -1 = vacuum
 
     def copy(self):
         g = _GState()
         g.ctm, g.reverse_orientation, g.material, g.area_light = self.ctm.copy(), self.reverse_orientation, self.material, self.area_light
+        g.medium_interface = self.medium_interface
         return g
 
 
@@ -785,6 +813,8 @@ def load(path=None, text=None, spp=None, integrator=None):
         cfr = (screen_from_camera.inverse() * Xf(raster_from_screen.m).inverse()).m
         sc.camera = {"cfr": cfr, "rfc": rfc, "lens_radius": p_float(cp, "lensradius", 0.0),
                      "focal_distance": p_float(cp, "focaldistance", 1e6)}
+        if g.medium_interface is not None:      # build_camera (scene_builder.cu:166-171)
+            sc.camera_medium = g.medium_interface[1]
         sp = pre["Sampler"]
         if sp:
             sc.sampler = sp[0] if sp[0] in ("independent", "stratified") else "stratified"
@@ -797,6 +827,7 @@ def load(path=None, text=None, spp=None, integrator=None):
             sc.regularize = p_bool(ipp, "regularize", False)
 
     instances, instance_def = {}, None
+    named_medium = {}
 
     def place_shape(rec, render_from_instance, area_light):
         """One shape into the flat scene.  Instances (primitives/transformed_primitive.cu:20-34) are flattened: the reference
@@ -820,10 +851,14 @@ def load(path=None, text=None, spp=None, integrator=None):
                 Pr = xf_points(render_from_instance.m, Pr)
                 if Nr is not None:
                     Nr = xf_normals(render_from_instance.inv, Nr)
-            sc.add_mesh(Pr, rec["idx"], rec["material"], flip, area_light, scene_dir, N=Nr, uv=rec.get("uv"))
+            sc.add_mesh(Pr, rec["idx"], rec["material"], flip, area_light, scene_dir, N=Nr, uv=rec.get("uv"), medium_code=rec.get("mcode", 0))
         else:
             if area_light is not None:
                 raise SceneError("emissive spheres are outside the hot path")
+            if rec.get("mcode", 0) != 0:
+                raise SceneError("spheres on a medium transition are outside the hot path")
+            if sc.materials[rec["material"]]["type"] == 7:
+                raise SceneError("interface spheres are outside the hot path")
             sc.spheres.append({"rfo": rfo_x.m, "ofr": rfo_x.inv, "radius": rec["radius"], "zmin": rec["zmin"], "zmax": rec["zmax"],
                                "phimax": rec["phimax"], "ro": rec["ro"], "swaps": swaps_handedness(rec["rfo"].m), "material": rec["material"]})
 
@@ -894,7 +929,16 @@ def load(path=None, text=None, spp=None, integrator=None):
                        "phimax": math.radians(min(max(p_float(p, "phimax", 360.0), 0.0), 360.0))}
             else:
                 raise SceneError("Shape '%s' is outside the hot path (SURVEY.md 8f)" % args[0])
-            rec.update({"rfo": rfo_x, "ro": g.reverse_orientation, "material": g.material})
+            # parse_shape (scene_builder.cu:631-676): SimplePrimitive unless the shape is emissive or sits on a medium transition
+            mi = g.medium_interface
+            transition = mi is not None and mi[0] != mi[1]
+            if g.area_light is None and not transition:
+                mcode = 0
+            elif transition:
+                mcode = (mi[0] + 1) | ((mi[1] + 1) << 16)
+            else:
+                mcode = 0xFFFFFFFF
+            rec.update({"rfo": rfo_x, "ro": g.reverse_orientation, "material": g.material, "mcode": mcode})
             if instance_def is not None:
                 if g.area_light is not None:   # scene_builder.cu:653-656
                     raise SceneError("area lights are not supported with object instancing")
@@ -920,7 +964,17 @@ def load(path=None, text=None, spp=None, integrator=None):
                 place_shape(rec, None if rfi.is_identity() else rfi, None)
         elif kw == "LightSource":
             sc.add_light_source(args[0], params_of(args[1:]), render_from_world * g.ctm, scene_dir)
-        elif kw in ("MakeNamedMedium", "MediumInterface", "Texture"):
+        elif kw == "MakeNamedMedium":           # scene_builder.cu:362-365
+            named_medium[args[0]] = sc.add_medium(params_of(args[1:]), scene_dir)
+        elif kw == "MediumInterface":           # scene_builder.cu:434-464
+            names = [a for a in args if isinstance(a, str)]
+            if len(names) != 2:
+                raise SceneError("MediumInterface takes two names")
+            for nm in names:
+                if nm and nm not in named_medium:
+                    raise SceneError("medium '%s' not defined" % nm)
+            g.medium_interface = tuple(named_medium[nm] if nm else -1 for nm in names)
+        elif kw in ("Texture",):
             raise SceneError("directive '%s' is outside the hot path (SURVEY.md 8f)" % kw)
         elif kw in ("ColorSpace", "Option", "Attribute"):
             continue

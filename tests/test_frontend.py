@@ -121,7 +121,7 @@ def test_ply_reader(b200pt, tmp_path):
 def test_ctypes_layout_matches_header(b200pt, tmp_path):
     """sizeof of every struct crossing the boundary, as gcc sees include/b200pt.h, equals the ctypes mirror"""
     names = ["b200pt_spectrum", "b200pt_material", "b200pt_light", "b200pt_sphere", "b200pt_camera", "b200pt_filter",
-             "b200pt_film_desc", "b200pt_scene_desc", "b200pt_build_stats", "b200pt_render_opts", "b200pt_render_stats"]
+             "b200pt_film_desc", "b200pt_scene_desc", "b200pt_build_stats", "b200pt_render_opts", "b200pt_render_stats", "b200pt_medium"]
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include "b200pt.h"\nint main(void){' +
                    "".join('printf("%%zu\\n", sizeof(%s));' % n for n in names) + "return 0;}\n")
@@ -130,8 +130,33 @@ def test_ctypes_layout_matches_header(b200pt, tmp_path):
     sizes = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     A = b200pt.api
     mirror = [A.Spectrum, A.Material, A.Light, A.Sphere, A.Camera, A.Filter, A.FilmDesc, A.SceneDesc, A.BuildStats, A.RenderOpts,
-              A.RenderStats]
+              A.RenderStats, A.Medium]
     assert sizes == [ctypes.sizeof(m) for m in mirror]
+
+
+def test_media_front_end(b200pt):
+    """MakeNamedMedium / MediumInterface / Material "interface" (scene_builder.cu:166-171,631-676): per-triangle medium codes
+    as include/b200pt.h defines them, camera medium = the exterior of the MediumInterface current at WorldBegin"""
+    ps = b200pt.pbrt_scene
+    sc = ps.load(os.path.join(ROOT, "tests", "scenes", "media.pbrt"))
+    assert len(sc.media) == 2 and sc.camera_medium == -1
+    assert sc.media[0]["g"] == pytest.approx(0.3) and sc.media[1]["scale"] == 2.0
+    codes = np.concatenate(sc.tri_medium)
+    per_shape = [int(codes[i]) for i in (0, 2, 4, 6, 18, 30)]
+    # light (GeometricPrimitive, no transition), floor, wall, fog box (interior fog, exterior vacuum), block (fog|fog is no
+    # transition: SimplePrimitive), dye tank
+    assert per_shape == [0xFFFFFFFF, 0, 0, 1, 0, 2]
+    assert [m["type"] for m in sc.materials][3] == 7
+    quad = 'Shape "trianglemesh" "integer indices" [0 1 2] "point3 P" [0 0 0 1 0 0 0 1 0]\n'
+    head = 'Camera "perspective"\n'
+    inside = ps.load(text='MakeNamedMedium "m" "string type" ["homogeneous"]\nMediumInterface "" "m"\n' + head + "WorldBegin\n" + quad)
+    assert inside.camera_medium == 0 and inside.media[0]["scale"] == 1.0
+    with pytest.raises(ps.SceneError):
+        ps.load(text=head + 'WorldBegin\nMediumInterface "nope" ""\n' + quad)
+    with pytest.raises(ps.SceneError):
+        ps.load(text=head + 'WorldBegin\nMakeNamedMedium "m" "string type" ["uniformgrid"]\n')
+    with pytest.raises(ps.SceneError):   # spheres on a transition are outside the hot path
+        ps.load(text=head + 'WorldBegin\nMakeNamedMedium "m" "string type" ["homogeneous"]\nMediumInterface "m" ""\nShape "sphere"\n')
 
 
 def test_sample_ranges_tile(b200pt):

@@ -35,6 +35,9 @@ CASES = [
     # per-vertex shading normals + uvs (incl. a mirrored instance and ReverseOrientation); one coated sheet -> statistical in part
     ("normals_96x64_64spp", "normals.pbrt", None, 64, None, None),
     ("normals_96x64_1024spp", "normals.pbrt", None, 1024, None, None),
+    # homogeneous media, interface surfaces, a dielectric tank of coloured medium (volume_scatter + transmittance walks)
+    ("media_96x64_64spp", "media.pbrt", None, 64, None, None),
+    ("media_96x64_1024spp", "media.pbrt", None, 1024, None, None),
     # C4 in miniature (workloads.procedural_scene, seed 7): many lights -> statistical gate only
     ("c4tiny_96x54_1024spp", "@c4tiny", None, 1024, None, None),
 ]
