@@ -923,6 +923,16 @@ def load(path=None, text=None, spp=None, integrator=None):
                 if uv is not None and len(uv) != len(P):
                     uv = None
                 rec = {"kind": "mesh", "P": P, "idx": idx, "N": N, "uv": uv}
+            elif args[0] == "loopsubdiv":        # base/shape.cu:65-74: the limit mesh enters as a triangle mesh with normals
+                from . import loop_subdiv
+                if "indices" not in p or "P" not in p:
+                    raise SceneError("loopsubdiv needs indices and P")
+                levels = int(p["levels"][1][0]) if "levels" in p else 3
+                try:
+                    P, idx, N = loop_subdiv.loop_subdivide(levels, p["indices"][1], p["P"][1])
+                except ValueError as ex:
+                    raise SceneError(str(ex))
+                rec = {"kind": "mesh", "P": P, "idx": idx, "N": N, "uv": None}
             elif args[0] == "sphere":
                 r = p_float(p, "radius", 1.0)
                 rec = {"kind": "sphere", "radius": r, "zmin": p_float(p, "zmin", -r), "zmax": p_float(p, "zmax", r),

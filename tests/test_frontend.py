@@ -159,6 +159,43 @@ def test_media_front_end(b200pt):
         ps.load(text=head + 'WorldBegin\nMakeNamedMedium "m" "string type" ["homogeneous"]\nMediumInterface "m" ""\nShape "sphere"\n')
 
 
+def test_loop_subdivision_mesh_producer(b200pt):
+    """pbrt-minus_b200/loop_subdiv.py against what shapes/loop_subdivide.cu guarantees: 4^levels faces, V - E + F preserved,
+    the symmetric octahedron stays symmetric and converges to a sphere-like limit surface, a flat regular sheet stays flat with
+    its boundary on the original outline, normals of a flat sheet are parallel"""
+    import importlib
+    ls = importlib.import_module("pbrt-minus_b200.loop_subdiv")
+    P = [0, 0, 1, 1, 0, 0, 0, 1, 0, -1, 0, 0, 0, -1, 0, 0, 0, -1]
+    I = [0, 1, 2, 0, 2, 3, 0, 3, 4, 0, 4, 1, 5, 2, 1, 5, 3, 2, 5, 4, 3, 5, 1, 4]
+    for levels in (0, 1, 3):
+        Pl, idx, N = ls.loop_subdivide(levels, I, P)
+        assert idx.shape == (8 * 4 ** levels, 3) and Pl.dtype == np.float32 and idx.dtype == np.int32
+        edges = {tuple(sorted((int(t[k]), int(t[(k + 1) % 3])))) for t in idx for k in range(3)}
+        assert len(Pl) - len(edges) + len(idx) == 2                       # closed genus-0 surface
+        assert idx.min() == 0 and idx.max() == len(Pl) - 1
+    r = np.linalg.norm(Pl, axis=1)
+    assert 0.40 < r.min() and r.max() <= 0.5 + 1e-6                        # the six original vertices end at 0.5
+    assert np.allclose(sorted(map(tuple, np.round(np.abs(Pl), 5))), sorted(map(tuple, np.round(np.abs(Pl[:, [1, 2, 0]]), 5))))
+    cosang = np.einsum("ij,ij->i", N, Pl) / (np.linalg.norm(N, axis=1) * r)
+    assert (np.abs(cosang) > 0.93).all() and (np.sign(cosang) == np.sign(cosang[0])).all()
+    # flat 4x4 regular grid
+    g = [(x, y, 0) for y in range(4) for x in range(4)]
+    gi = []
+    for y in range(3):
+        for x in range(3):
+            a = y * 4 + x
+            gi += [a, a + 1, a + 5, a, a + 5, a + 4]
+    Pl, idx, N = ls.loop_subdivide(2, gi, np.array(g, np.float32).ravel())
+    assert idx.shape == (18 * 16, 3) and np.abs(Pl[:, 2]).max() == 0
+    assert Pl[:, :2].min() >= 0 and Pl[:, :2].max() <= 3
+    assert np.abs(N[:, :2]).max() < 1e-5 and (N[:, 2] != 0).all() and (np.sign(N[:, 2]) == np.sign(N[0, 2])).all()
+    ps = b200pt.pbrt_scene
+    sc = ps.load(os.path.join(ROOT, "tests", "scenes", "loopsubdiv.pbrt"))
+    assert sum(len(i) for i in sc.idx) == 4 + 8 * 64 + 4 * 64 + 18 * 16
+    with pytest.raises(ps.SceneError):
+        ps.load(text='Camera "perspective"\nWorldBegin\nShape "loopsubdiv" "integer indices" [0 1 2] "point3 P" [0 0 0 1 0 0 0 1 0 5 5 5]\n')
+
+
 def test_sample_ranges_tile(b200pt):
     for spp in (1, 4, 16, 1024, 4096, 4097):
         for world in (1, 2, 3, 4, 8):

@@ -40,6 +40,9 @@ CASES = [
     ("media_96x64_1024spp", "media.pbrt", None, 1024, None, None),
     # camera inside a haze, spot / distant / infinite lights, spheres (the reference aborts on a NaN pixel at 1024 spp)
     ("media2_96x64_64spp", "media2.pbrt", None, 64, None, None),
+    # Loop subdivision surfaces (closed valence-4 / valence-3 meshes, an open sheet), limit normals
+    ("loopsubdiv_96x64_64spp", "loopsubdiv.pbrt", None, 64, None, None),
+    ("loopsubdiv_96x64_1024spp", "loopsubdiv.pbrt", None, 1024, None, None),
     # C4 in miniature (workloads.procedural_scene, seed 7): many lights -> statistical gate only
     ("c4tiny_96x54_1024spp", "@c4tiny", None, 1024, None, None),
 ]
