@@ -109,6 +109,7 @@ typedef struct {
     int32_t reverse_orientation, transform_swaps_handedness;
     int32_t material; /* material id */
     int32_t light;    /* -1: spheres as emitters are not supported */
+    int32_t kind;     /* 0 sphere (shapes/sphere.{h,cu}); 1 disk (shapes/disk.{h,cu}): z_min = height, z_max = inner radius */
 } b200pt_sphere;
 
 /* ---- camera (cameras/perspective.cu:7-86) ------------------------------------------------ */

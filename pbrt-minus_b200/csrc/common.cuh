@@ -51,6 +51,7 @@ struct SphereRec {
     float theta_z_min, theta_z_max;
     int flip; // reverse_orientation ^ transform_swaps_handedness
     int material;
+    int kind; // 0 sphere; 1 disk: z_min = height, z_max = inner radius
 };
 
 struct RenderData; // render.cu

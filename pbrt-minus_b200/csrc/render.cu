@@ -215,6 +215,15 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             o.phi_max = sp.phi_max;
             o.flip = (sp.reverse_orientation != 0) ^ (sp.transform_swaps_handedness != 0);
             o.material = sp.material;
+            o.kind = sp.kind;
+            if (sp.kind == 1) { // Disk (shapes/disk.cu:7-20): height, inner radius as given
+                o.z_min = sp.z_min;
+                o.z_max = sp.z_max;
+                o.theta_z_min = o.theta_z_max = 0.f;
+            } else if (sp.kind != 0) {
+                set_error("b200pt_scene_create: quadric %d has kind %d", i, sp.kind);
+                return B200PT_ERR_INVALID;
+            }
             if (sp.light >= 0) {
                 set_error("b200pt_scene_create: emissive spheres are not supported");
                 return B200PT_ERR_UNSUPPORTED;
@@ -434,7 +443,9 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             const b200pt_sphere &sp = desc->spheres[i];
             const float zmin = std::min(std::max(std::min(sp.z_min, sp.z_max), -sp.radius), sp.radius);
             const float zmax = std::min(std::max(std::max(sp.z_min, sp.z_max), -sp.radius), sp.radius);
-            const float bmin[3] = {-sp.radius, -sp.radius, zmin}, bmax[3] = {sp.radius, sp.radius, zmax};
+            // Sphere::bounds / Disk::bounds (shapes/disk.h:23-26: the square around the disk at z = height)
+            const float bmin[3] = {-sp.radius, -sp.radius, sp.kind == 1 ? sp.z_min : zmin},
+                        bmax[3] = {sp.radius, sp.radius, sp.kind == 1 ? sp.z_min : zmax};
             for (int a = 0; a < 3; a++) {
                 float mn = sp.render_from_object[4 * a + 3], mx = mn;
                 for (int k = 0; k < 3; k++) {
@@ -781,7 +792,36 @@ __device__ __forceinline__ void triangle_interaction(const WF &wf, V3 p0, V3 p1,
 
 // Sphere::interaction_from_intersection (shapes/sphere.h:71-125) + Transform::operator()(SurfaceInteraction)
 // (euclidean_space/transform.cu:57-97)
+// Disk::interaction_from_intersection (shapes/disk.cu:133-153): the hit point is recomputed as disk_intersect does it
+__device__ __forceinline__ void disk_interaction(const SphereRec &s, V3 ro, V3 rd, float t, V3 wo, Isect &si) {
+    Iv oi[3];
+    xf_point_iv(s.ofr, iv(ro.x), iv(ro.y), iv(ro.z), oi);
+    const V3 dc = xf_vector(s.ofr, rd), de = xf_vector_error(s.ofr, rd);
+    const V3 o = iv_mid3(oi);
+    const V3 d = v3(iv_mid(iv_err(dc.x, de.x)), iv_mid(iv_err(dc.y, de.y)), iv_mid(iv_err(dc.z, de.z)));
+    V3 pHit = o + t * d;
+    const float rHit = sqrtf(sqr(pHit.x) + sqr(pHit.y));
+    const V3 dpdu = v3(-s.phi_max * pHit.y, s.phi_max * pHit.x, 0.f);
+    const V3 dpdv = v3(pHit.x, pHit.y, 0.f) * (s.z_max - s.radius) / rHit;
+    pHit.z = s.z_min;
+    V3 n = normalize(cross(dpdu, dpdv));
+    if (s.flip) n = -n;
+    Iv pi[3]; // Point3fi(pHit, pError = 0) through the interval transform
+    xf_point_iv(s.rfo, iv(pHit.x), iv(pHit.y), iv(pHit.z), pi);
+    si.p = iv_mid3(pi);
+    si.err = iv_err3(pi);
+    const V3 nr = normalize(xf_normal(s.ofr, n));
+    si.n = nr;
+    si.ns = nr;
+    si.dpdu = xf_vector(s.rfo, dpdu);
+    si.wo = normalize(wo);
+}
+
 __device__ __forceinline__ void sphere_interaction(const SphereRec &s, V3 ro, V3 rd, float t, V3 wo, Isect &si) {
+    if (s.kind == 1) {
+        disk_interaction(s, ro, rd, t, wo, si);
+        return;
+    }
     // recompute the refined object-space hit point exactly as basic_intersect does
     const V3 o = xf_point(s.ofr, ro), d = xf_vector(s.ofr, rd);
     V3 pHit = o + t * d;

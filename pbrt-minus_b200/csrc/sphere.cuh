@@ -5,7 +5,8 @@
 //   Interval                             euclidean_space/interval.h (directed rounding: the reference's
 //                                        device build uses __fadd_rd/__fadd_ru etc., util/bit_arithmetic.h)
 //   Transform on Point3fi / Vector3fi    euclidean_space/transform.h:270-427
-// Spheres are few (one in the reference's shipped scene) and are tested linearly beside the BVH.
+//   Disk::basic_intersect                shapes/disk.cu:99-131
+// Spheres / disks are few (one in the reference's shipped scene) and are tested linearly beside the BVH.
 #pragma once
 
 #include "common.cuh"
@@ -90,6 +91,18 @@ __device__ __forceinline__ V3 xf_vector_error(const float *m, V3 v) {
               g3 * (fabsf(m[8] * v.x) + fabsf(m[9] * v.y) + fabsf(m[10] * v.z)));
 }
 
+// Transform::operator()(Point3<T>) with T = Interval (euclidean_space/transform.h:255-268): the reference has no dedicated
+// Point3fi overload for the FORWARD direction, so the ray origin brought to object space and the hit point brought to render
+// space go through plain interval arithmetic, term by term from the left.  The bounds this gives are tighter than the
+// gamma(3) formula of apply_inverse; for a disk (zero thickness, zero pError) they decide whether a spawned ray clears the
+// surface, so they are reproduced as they are.
+__device__ __forceinline__ void xf_point_iv(const float *m, Iv px, Iv py, Iv pz, Iv out[3]) {
+#pragma unroll
+    for (int r = 0; r < 3; r++) out[r] = m[4 * r] * px + m[4 * r + 1] * py + m[4 * r + 2] * pz + iv(m[4 * r + 3]);
+}
+__device__ __forceinline__ V3 iv_mid3(const Iv v[3]) { return v3(iv_mid(v[0]), iv_mid(v[1]), iv_mid(v[2])); }
+__device__ __forceinline__ V3 iv_err3(const Iv v[3]) { return v3((v[0].hi - v[0].lo) / 2.f, (v[1].hi - v[1].lo) / 2.f, (v[2].hi - v[2].lo) / 2.f); }
+
 __device__ __forceinline__ bool sphere_clip(const SphereRec &s, V3 &pHit, float &phi) {
     if (pHit.x == 0.f && pHit.y == 0.f) pHit.x = 1e-5f * s.radius;
     phi = atan2f(pHit.y, pHit.x);
@@ -97,7 +110,32 @@ __device__ __forceinline__ bool sphere_clip(const SphereRec &s, V3 &pHit, float 
     return (s.z_min > -s.radius && pHit.z < s.z_min) || (s.z_max < s.radius && pHit.z > s.z_max) || phi > s.phi_max;
 }
 
+// Disk::basic_intersect (shapes/disk.cu:99-131): the plane z = height in object space, from the MIDPOINTS of the transformed
+// origin / direction intervals; inside [inner radius, radius] and phi <= phi_max
+__device__ __forceinline__ bool disk_intersect(const SphereRec &s, V3 ro, V3 rd, float t_max, SphereHit &hit) {
+    Iv oi[3];
+    xf_point_iv(s.ofr, iv(ro.x), iv(ro.y), iv(ro.z), oi);
+    const V3 dc = xf_vector(s.ofr, rd), de = xf_vector_error(s.ofr, rd);
+    const V3 o = iv_mid3(oi);
+    const V3 d = v3(iv_mid(iv_err(dc.x, de.x)), iv_mid(iv_err(dc.y, de.y)), iv_mid(iv_err(dc.z, de.z)));
+    if (d.z == 0.f) return false;
+    const float height = s.z_min, inner = s.z_max;
+    const float t = (height - o.z) / d.z;
+    if (t <= 0.f || t >= t_max) return false;
+    const V3 pHit = o + t * d;
+    const float dist2 = sqr(pHit.x) + sqr(pHit.y);
+    if (dist2 > sqr(s.radius) || dist2 < sqr(inner)) return false;
+    float phi = atan2f(pHit.y, pHit.x);
+    if (phi < 0.f) phi += 2.f * kPi;
+    if (phi > s.phi_max) return false;
+    hit.t = t;
+    hit.p_obj = pHit;
+    hit.phi = phi;
+    return true;
+}
+
 __device__ __forceinline__ bool sphere_intersect(const SphereRec &s, V3 ro, V3 rd, float t_max, SphereHit &hit) {
+    if (s.kind == 1) return disk_intersect(s, ro, rd, t_max, hit);
     const V3 o = xf_point(s.ofr, ro), d = xf_vector(s.ofr, rd);
     const V3 oe = xf_point_error(s.ofr, ro, v3(0.f, 0.f, 0.f), true), de = xf_vector_error(s.ofr, rd);
     const Iv ox = iv_err(o.x, oe.x), oy = iv_err(o.y, oe.y), oz = iv_err(o.z, oe.z);

@@ -679,7 +679,7 @@ class Scene:
             sph[i].object_from_render[:] = [float(v) for v in s["ofr"].reshape(-1)]
             sph[i].radius, sph[i].z_min, sph[i].z_max, sph[i].phi_max = s["radius"], s["zmin"], s["zmax"], s["phimax"]
             sph[i].reverse_orientation, sph[i].transform_swaps_handedness = int(s["ro"]), int(s["swaps"])
-            sph[i].material, sph[i].light = s["material"], -1
+            sph[i].material, sph[i].light, sph[i].kind = s["material"], -1, s.get("kind", 0)
         d.n_spheres, d.spheres = len(self.spheres), sph
         spec = (api.Spectrum * max(1, len(self.spectra)))()
         for i, s in enumerate(self.spectra):
@@ -860,7 +860,8 @@ def load(path=None, text=None, spp=None, integrator=None):
             if sc.materials[rec["material"]]["type"] == 7:
                 raise SceneError("interface spheres are outside the hot path")
             sc.spheres.append({"rfo": rfo_x.m, "ofr": rfo_x.inv, "radius": rec["radius"], "zmin": rec["zmin"], "zmax": rec["zmax"],
-                               "phimax": rec["phimax"], "ro": rec["ro"], "swaps": swaps_handedness(rec["rfo"].m), "material": rec["material"]})
+                               "phimax": rec["phimax"], "ro": rec["ro"], "swaps": swaps_handedness(rec["rfo"].m), "material": rec["material"],
+                               "kind": 1 if rec["kind"] == "disk" else 0})
 
     for kw, args in directives(text, scene_dir):
         if kw in pre:
@@ -937,8 +938,12 @@ def load(path=None, text=None, spp=None, integrator=None):
                 r = p_float(p, "radius", 1.0)
                 rec = {"kind": "sphere", "radius": r, "zmin": p_float(p, "zmin", -r), "zmax": p_float(p, "zmax", r),
                        "phimax": math.radians(min(max(p_float(p, "phimax", 360.0), 0.0), 360.0))}
+            elif args[0] == "disk":              # Disk::Disk (shapes/disk.cu:7-20); rides in the sphere record: zmin = height, zmax = inner radius
+                rec = {"kind": "disk", "radius": p_float(p, "radius", 1.0), "zmin": p_float(p, "height", 0.0),
+                       "zmax": p_float(p, "innerradius", 0.0),
+                       "phimax": math.radians(min(max(p_float(p, "phimax", 360.0), 0.0), 360.0))}
             else:
-                raise SceneError("Shape '%s' is outside the hot path (SURVEY.md 8f)" % args[0])
+                raise SceneError("Shape '%s' is not a reference shape (base/shape.cu:9-79)" % args[0])
             # parse_shape (scene_builder.cu:631-676): SimplePrimitive unless the shape is emissive or sits on a medium transition
             mi = g.medium_interface
             transition = mi is not None and mi[0] != mi[1]

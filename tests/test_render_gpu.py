@@ -143,6 +143,15 @@ def test_loop_subdivision_matches_reference(b200pt, tmp_path):
     check_against_golden(b200pt, tmp_path, "loopsubdiv_96x64_1024spp")
 
 
+def test_disk_shape_matches_reference(b200pt, tmp_path):
+    """Shape "disk" (shapes/disk.{h,cu}): plane hit from the midpoints of the interval-transformed ray, annulus / phimax clipping,
+    hit point back to render space through the reference's interval arithmetic (zero pError: the bounds are only the rounding
+    of the transform, which makes the big floor disk shadow itself in a band -- reproduced).  Disks ride in the quadric list
+    beside the BVH.  Measured relMSE 2.2e-6 (64 spp) / 1.3e-7 (1024 spp)."""
+    check_against_golden(b200pt, tmp_path, "disk_96x64_64spp")
+    check_against_golden(b200pt, tmp_path, "disk_96x64_1024spp")
+
+
 def test_mix_material_statistical_gate(b200pt, tmp_path):
     """Material "mix" (materials/mix_material.cu, base/interaction.cu:41-64): the material of a hit is chosen by
     hash_float(pi, wo) < amount -- a hash of the BITS of the hit interval and direction, so (as for the coated materials) the

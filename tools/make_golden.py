@@ -43,6 +43,9 @@ CASES = [
     # Loop subdivision surfaces (closed valence-4 / valence-3 meshes, an open sheet), limit normals
     ("loopsubdiv_96x64_64spp", "loopsubdiv.pbrt", None, 64, None, None),
     ("loopsubdiv_96x64_1024spp", "loopsubdiv.pbrt", None, 1024, None, None),
+    # Shape "disk": annuli, partial sweeps, mirrored / squashed / quarter-turned
+    ("disk_96x64_64spp", "disk.pbrt", None, 64, None, None),
+    ("disk_96x64_1024spp", "disk.pbrt", None, 1024, None, None),
     # C4 in miniature (workloads.procedural_scene, seed 7): many lights -> statistical gate only
     ("c4tiny_96x54_1024spp", "@c4tiny", None, 1024, None, None),
 ]
