@@ -1,6 +1,7 @@
 // api.cu -- the C-ABI of libb200pt.so (include/b200pt.h): scene upload, accelerator build,
 // batched traversal, device buffer helpers.  Errors come back as status codes with a
 // thread-local message; nothing here exits, throws across the boundary or runs on the CPU.
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -196,6 +197,9 @@ B200PT_API void b200pt_scene_destroy(b200pt_scene *s) {
         if (p) cudaFree(p);
     for (void *p : s->user_allocs) cudaFree(p);
     if (s->stream) cudaStreamDestroy(s->stream);
+    if (s->stream_h2d) cudaStreamDestroy(s->stream_h2d);
+    if (s->stream_d2h) cudaStreamDestroy(s->stream_d2h);
+    for (cudaEvent_t e : s->pipe_events) cudaEventDestroy(e);
     delete s;
 }
 
@@ -273,20 +277,43 @@ B200PT_API int b200pt_trace(b200pt_scene *s, const float *o_xyz, const float *d_
     int32_t *d_prim = (int32_t *)(base + n16 * 76);
     float *d_t = (float *)(base + n16 * 80);
     float *d_b = (float *)(base + n16 * 84);
-    CU_TRY(cudaMemcpyAsync(d_o, o_xyz, n * 12, cudaMemcpyHostToDevice, s->stream));
-    CU_TRY(cudaMemcpyAsync(d_d, d_xyz, n * 12, cudaMemcpyHostToDevice, s->stream));
-    CU_TRY(cudaMemcpyAsync(d_tmax, tmax, n * 4, cudaMemcpyHostToDevice, s->stream));
+    // Three-stage pipeline over chunks of the batch: the copy-in of chunk k+1 (H2D engine), the traversal of chunk k and the
+    // copy-out of chunk k-1 (D2H engine) run at the same time; with pinned host buffers a batch costs about
+    // max(copy-in, traversal, copy-out) instead of their sum.  Pageable buffers still work (the copies then block the host).
+    static const int64_t chunk_env = getenv("B200PT_TRACE_CHUNK") ? atoll(getenv("B200PT_TRACE_CHUNK")) : 0;
+    const int64_t chunk = chunk_env > 0 ? chunk_env : (int64_t)1 << 19;
+    const int n_chunks = (int)((n + chunk - 1) / chunk);
+    if (!s->stream_h2d) CU_TRY(cudaStreamCreateWithFlags(&s->stream_h2d, cudaStreamNonBlocking));
+    if (!s->stream_d2h) CU_TRY(cudaStreamCreateWithFlags(&s->stream_d2h, cudaStreamNonBlocking));
+    while ((int)s->pipe_events.size() < 2 * n_chunks) {
+        cudaEvent_t e;
+        CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        s->pipe_events.push_back(e);
+    }
     const int tb = 256;
-    const unsigned grid = unsigned((n + tb - 1) / tb);
-    k_pack_rays<<<grid, tb, 0, s->stream>>>(d_o, d_d, d_tmax, n, d_rays);
-    int rc = launch_trace(s, d_rays, n, any_hit, d_hits);
-    if (rc) return rc;
+    for (int c = 0; c < n_chunks; c++) {
+        const int64_t c0 = c * chunk, nc = std::min(chunk, n - c0);
+        cudaEvent_t ev_in = s->pipe_events[2 * c], ev_done = s->pipe_events[2 * c + 1];
+        CU_TRY(cudaMemcpyAsync(d_o + 3 * c0, o_xyz + 3 * c0, nc * 12, cudaMemcpyHostToDevice, s->stream_h2d));
+        CU_TRY(cudaMemcpyAsync(d_d + 3 * c0, d_xyz + 3 * c0, nc * 12, cudaMemcpyHostToDevice, s->stream_h2d));
+        CU_TRY(cudaMemcpyAsync(d_tmax + c0, tmax + c0, nc * 4, cudaMemcpyHostToDevice, s->stream_h2d));
+        CU_TRY(cudaEventRecord(ev_in, s->stream_h2d));
+        CU_TRY(cudaStreamWaitEvent(s->stream, ev_in, 0));
+        const unsigned grid = unsigned((nc + tb - 1) / tb);
+        k_pack_rays<<<grid, tb, 0, s->stream>>>(d_o + 3 * c0, d_d + 3 * c0, d_tmax + c0, nc, d_rays + 2 * c0);
+        int rc = launch_trace(s, d_rays + 2 * c0, nc, any_hit, d_hits + c0, c > 0);
+        if (rc) return rc;
+        k_unpack_hits<<<grid, tb, 0, s->stream>>>(d_hits + c0, nc, d_prim + c0, d_t + c0, d_b + 2 * c0);
+        CU_TRY(cudaEventRecord(ev_done, s->stream));
+        CU_TRY(cudaStreamWaitEvent(s->stream_d2h, ev_done, 0));
+        if (prim_out) CU_TRY(cudaMemcpyAsync(prim_out + c0, d_prim + c0, nc * 4, cudaMemcpyDeviceToHost, s->stream_d2h));
+        if (t_out) CU_TRY(cudaMemcpyAsync(t_out + c0, d_t + c0, nc * 4, cudaMemcpyDeviceToHost, s->stream_d2h));
+        if (b1b2_out) CU_TRY(cudaMemcpyAsync(b1b2_out + 2 * c0, d_b + 2 * c0, nc * 8, cudaMemcpyDeviceToHost, s->stream_d2h));
+    }
     s->last_counts[2] = n;
-    k_unpack_hits<<<grid, tb, 0, s->stream>>>(d_hits, n, d_prim, d_t, d_b);
-    if (prim_out) CU_TRY(cudaMemcpyAsync(prim_out, d_prim, n * 4, cudaMemcpyDeviceToHost, s->stream));
-    if (t_out) CU_TRY(cudaMemcpyAsync(t_out, d_t, n * 4, cudaMemcpyDeviceToHost, s->stream));
-    if (b1b2_out) CU_TRY(cudaMemcpyAsync(b1b2_out, d_b, n * 8, cudaMemcpyDeviceToHost, s->stream));
-    return check_trace_status(s);
+    const int rc = check_trace_status(s); // synchronises the traversal stream
+    CU_TRY(cudaStreamSynchronize(s->stream_d2h));
+    return rc;
 }
 
 B200PT_API int b200pt_trace_set_counting(b200pt_scene *s, int enable) {

@@ -62,6 +62,9 @@ struct b200pt_scene {
     int device = 0;
     int sm_count = 148;
     cudaStream_t stream = nullptr;
+    // b200pt_trace (host buffers): copy-in / copy-out streams and per-chunk events of the three-stage pipeline
+    cudaStream_t stream_h2d = nullptr, stream_d2h = nullptr;
+    std::vector<cudaEvent_t> pipe_events;
 
     // geometry as uploaded (render space)
     int64_t n_vertices = 0, n_triangles = 0;
@@ -102,7 +105,9 @@ struct b200pt_scene {
 namespace b200pt {
 
 int build_bvh(b200pt_scene *s, b200pt_build_stats *stats);
-int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev);
+// keep_status: leave the node / triangle / overflow counters as they are (a later chunk of the same batch); the work ticket is
+// always reset
+int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev, bool keep_status = false);
 void free_render(b200pt_scene *s);
 int ensure_scratch(b200pt_scene *s, size_t bytes);
 

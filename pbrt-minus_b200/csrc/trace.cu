@@ -347,7 +347,7 @@ static TraceKernel pick_kernel(bool any_hit, bool counting) {
                    : (counting ? k_trace<false, true, REFILL> : k_trace<false, false, REFILL>);
 }
 
-int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev) {
+int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev, bool keep_status) {
     if (!s->built) {
         set_error("b200pt_trace: call b200pt_bvh_build first");
         return B200PT_ERR_STATE;
@@ -360,7 +360,7 @@ int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, 
     p.n = n;
     p.counters = s->d_trace_counters;
     p.prmt_bias = 0x47000000u;
-    CU_TRY(cudaMemsetAsync(s->d_trace_counters, 0, 4 * sizeof(unsigned long long), s->stream));
+    CU_TRY(cudaMemsetAsync(s->d_trace_counters, 0, (keep_status ? 1 : 4) * sizeof(unsigned long long), s->stream));
 
     // tuning knobs (defaults are the measured best)
     static const int refill = getenv("B200PT_REFILL") ? atoi(getenv("B200PT_REFILL")) : 4;
