@@ -84,7 +84,34 @@ typedef struct {
     float c_u_roughness, c_v_roughness; /* coated conductor: the conductor's roughness */
     int32_t c_eta, c_k;                 /* coated conductor: the conductor's eta / k spectrum ids */
     int32_t mix_a, mix_b;               /* mix: material ids; `scale` = "amount" in (0, 1): u < amount picks mix_a */
+    /* spectrum TEXTURES (base/spectrum_texture.cu) for "reflectance" / "transmittance": texture id + 1, 0 = none (the spectrum
+     * id above is used).  diffuse, diffusetransmission, coateddiffuse, and conductor / coatedconductor in reflectance mode */
+    int32_t reflectance_tex1, transmittance_tex1;
 } b200pt_material;
+
+/* ---- textures (textures/, base/{spectrum,float}_texture.cu) ---------------------------------------------------------------
+ * A texture is a node of a small expression tree over images and constants, evaluated at the hit's (u, v) and normal.
+ * "uv" mapping only (textures/texture_mapping_2d.cu:114-124); images are looked up bilinearly with "repeat" wrapping
+ * (MIPMap::filter = GPUImage::bilerp, textures/mipmap.cu:22-25), flipped in t, scaled, optionally inverted, clamped,
+ * and turned into an RGBAlbedoSpectrum per lookup (textures/spectrum_image_texture.cu:17-32). */
+enum { B200PT_TEX_CONSTANT = 0,       /* a: spectrum id */
+       B200PT_TEX_IMAGE = 1,          /* a: image id; f[0] scale, f[1] invert (0/1); map = su sv du dv */
+       B200PT_TEX_SCALE = 2,          /* a: texture; f[0] scale (textures/spectrum_scaled_texture.cu) */
+       B200PT_TEX_MIX = 3,            /* a, b: textures; c: float texture of the amount or -1, then f[0] (spectrum_mix_texture.cu) */
+       B200PT_TEX_DIRECTION_MIX = 4,  /* a, b: textures; f[0..2]: unit direction in render space (spectrum_direction_mix_texture.cu) */
+       B200PT_TEX_FLOAT_CONSTANT = 16, /* f[0] */
+       B200PT_TEX_FLOAT_IMAGE = 17,    /* a: image id (red channel... see float_image_texture.h); f[0] scale, f[1] invert */
+       B200PT_TEX_FLOAT_SCALE = 18 };  /* a, b: float textures, product (textures/float_scaled_texture.cu) */
+typedef struct {
+    int32_t type, a, b, c;
+    float f[4];
+    float map[4]; /* UVMapping: su, sv, du, dv */
+} b200pt_texture;
+
+typedef struct {
+    int32_t width, height;
+    const float *rgb; /* [height*width*3] linear RGB, top row first (GPUImage::init_png, textures/gpu_image.cu:194-222) */
+} b200pt_image;
 
 /* ---- lights (base/light.cu:22-75), in the order the scene file creates them (= light-sampler index):
  *      one DiffuseAreaLight per emissive triangle; DistantLight (lights/distant_light.cu), UniformInfiniteLight
@@ -167,6 +194,13 @@ typedef struct {
      * primitives/simple_primitive.h:28-37); 0xffffffff = GeometricPrimitive without a medium transition (spawned rays get no
      * medium, primitives/geometric_primitive.cu:20-29); else a MediumInterface: (interior + 1) | (exterior + 1) << 16, 0 = vacuum */
     const uint32_t *tri_medium;
+    int32_t n_textures;
+    const b200pt_texture *textures;
+    int32_t n_images;
+    const b200pt_image *images;
+    /* needed when n_images > 0: the Simpson tables of the RGB-to-spectrum fit in fp64, [3*283 rgb_tbl | 3 white | 283 lambda01]
+     * (spectrum_util/rgb_to_spectrum_data.cu:172-212); the coefficient table itself is fitted on the device */
+    const double *rgb2spec_fit;
     const b200pt_camera *camera; /* may be NULL for traversal-only scenes */
     const b200pt_filter *filter;
     const b200pt_film_desc *film;

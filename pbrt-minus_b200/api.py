@@ -29,7 +29,7 @@ class Material(C.Structure):
                 ("transmittance", C.c_int32), ("scale", C.c_float),
                 ("thickness", C.c_float), ("g", C.c_float), ("albedo", C.c_int32), ("max_depth", C.c_int32),
                 ("n_samples", C.c_int32), ("c_u_roughness", C.c_float), ("c_v_roughness", C.c_float),
-                ("c_eta", C.c_int32), ("c_k", C.c_int32), ("mix_a", C.c_int32), ("mix_b", C.c_int32)]
+                ("c_eta", C.c_int32), ("c_k", C.c_int32), ("mix_a", C.c_int32), ("mix_b", C.c_int32), ("reflectance_tex1", C.c_int32), ("transmittance_tex1", C.c_int32)]
 
 
 class Light(C.Structure):
@@ -66,6 +66,14 @@ class FilmDesc(C.Structure):
                 ("illuminant", C.POINTER(C.c_float))]
 
 
+class Texture(C.Structure):
+    _fields_ = [("type", C.c_int32), ("a", C.c_int32), ("b", C.c_int32), ("c", C.c_int32), ("f", C.c_float * 4), ("map", C.c_float * 4)]
+
+
+class Image(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("rgb", C.POINTER(C.c_float))]
+
+
 class SceneDesc(C.Structure):
     _fields_ = [("n_vertices", C.c_int64), ("P", C.POINTER(C.c_float)), ("N", C.POINTER(C.c_float)),
                 ("uv", C.POINTER(C.c_float)), ("n_triangles", C.c_int64), ("indices", C.POINTER(C.c_int32)),
@@ -76,6 +84,8 @@ class SceneDesc(C.Structure):
                 ("n_materials", C.c_int32), ("materials", C.POINTER(Material)),
                 ("n_lights", C.c_int32), ("lights", C.POINTER(Light)),
                 ("n_media", C.c_int32), ("media", C.POINTER(Medium)), ("tri_medium", C.POINTER(C.c_uint32)),
+                ("n_textures", C.c_int32), ("textures", C.POINTER(Texture)), ("n_images", C.c_int32), ("images", C.POINTER(Image)),
+                ("rgb2spec_fit", C.POINTER(C.c_double)),
                 ("camera", C.POINTER(Camera)), ("filter", C.POINTER(Filter)), ("film", C.POINTER(FilmDesc))]
 
 

@@ -54,6 +54,7 @@ struct RenderData {
     float scene_radius = 0.f;
     bool has_mat[WF_NMAT] = {};
     bool has_mix = false;
+    TexTables tex = {};                // textures: records, images, the fitted RGB-to-spectrum table
     MediumRec *d_media = nullptr;      // media scenes only
     uint32_t *d_tri_medium = nullptr;
     int n_media = 0, camera_medium = -1;
@@ -83,6 +84,8 @@ static int dev_upload(RenderData *r, T **dst, const T *src, size_t count, cudaSt
     *dst = (T *)p;
     return B200PT_OK;
 }
+
+int build_rgb2spec(b200pt_scene *s, const double *fit, double **d_coeff_out, double **d_znodes_out, std::vector<void *> &allocs); // rgb2spec.cu
 
 void free_render(b200pt_scene *s) {
     if (!s->render) return;
@@ -282,11 +285,17 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
     for (int i = 0; i < desc->n_materials; i++) {
         const b200pt_material &m = desc->materials[i];
         mats[i] = MatRec{m.type, m.reflectance, m.eta, m.k, m.u_roughness, m.v_roughness, m.remap_roughness, m.transmittance, m.scale,
-                         m.thickness, m.g, m.albedo, m.max_depth, m.n_samples, m.c_u_roughness, m.c_v_roughness, m.c_eta, m.c_k, m.mix_a, m.mix_b};
+                         m.thickness, m.g, m.albedo, m.max_depth, m.n_samples, m.c_u_roughness, m.c_v_roughness, m.c_eta, m.c_k, m.mix_a, m.mix_b,
+                         m.reflectance_tex1, m.transmittance_tex1};
+        if (m.reflectance_tex1 < 0 || m.reflectance_tex1 > desc->n_textures || m.transmittance_tex1 < 0 || m.transmittance_tex1 > desc->n_textures) {
+            set_error("b200pt_scene_create: material %d names a texture that does not exist", i);
+            return B200PT_ERR_INVALID;
+        }
         bool ok = true;
         if (m.type >= 0 && m.type < WF_NMAT) r->has_mat[m.type] = true;
-        if (m.type == B200PT_MAT_DIFFUSE) ok = spec_ok(m.reflectance);
-        else if (m.type == B200PT_MAT_DIFFUSE_TRANSMISSION) ok = spec_ok(m.reflectance) && spec_ok(m.transmittance);
+        auto refl_ok = [&]() { return spec_ok(m.reflectance) || m.reflectance_tex1 > 0; };
+        if (m.type == B200PT_MAT_DIFFUSE) ok = refl_ok();
+        else if (m.type == B200PT_MAT_DIFFUSE_TRANSMISSION) ok = refl_ok() && (spec_ok(m.transmittance) || m.transmittance_tex1 > 0);
         else if (m.type == B200PT_MAT_MIX) {
             // materials/mix_material.cu:6-16: amount in (0, 1); the two materials must not be mixes themselves
             // ("you should not see MixMaterial here", integrators/wavefront_path.cu:207-210)
@@ -294,11 +303,11 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
                  desc->materials[m.mix_a].type != B200PT_MAT_MIX && desc->materials[m.mix_b].type != B200PT_MAT_MIX;
             r->has_mix = true;
         } else if (m.type == B200PT_MAT_COATED_DIFFUSE)
-            ok = spec_ok(m.reflectance) && spec_ok(m.eta) && spec_ok(m.albedo) && m.max_depth >= 0 && m.n_samples >= 1;
+            ok = refl_ok() && spec_ok(m.eta) && spec_ok(m.albedo) && m.max_depth >= 0 && m.n_samples >= 1;
         else if (m.type == B200PT_MAT_COATED_CONDUCTOR)
             ok = spec_ok(m.eta) && spec_ok(m.albedo) && m.max_depth >= 0 && m.n_samples >= 1 &&
-                 ((spec_ok(m.c_eta) && spec_ok(m.c_k)) || (m.c_eta < 0 && spec_ok(m.reflectance)));
-        else if (m.type == B200PT_MAT_CONDUCTOR) ok = (spec_ok(m.eta) && spec_ok(m.k)) || (m.eta < 0 && spec_ok(m.reflectance));
+                 ((spec_ok(m.c_eta) && spec_ok(m.c_k)) || (m.c_eta < 0 && refl_ok()));
+        else if (m.type == B200PT_MAT_CONDUCTOR) ok = (spec_ok(m.eta) && spec_ok(m.k)) || (m.eta < 0 && refl_ok());
         else if (m.type == B200PT_MAT_DIELECTRIC) ok = spec_ok(m.eta);
         else if (m.type == B200PT_MAT_INTERFACE) ok = desc->n_media > 0; // only meaningful between media
         else ok = false;
@@ -355,6 +364,62 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             }
         if ((rc = dev_upload(r, &r->d_media, med.data(), med.size(), st))) return rc;
         if ((rc = dev_upload(r, &r->d_tri_medium, desc->tri_medium, (size_t)desc->n_triangles, st))) return rc;
+    }
+    // ---- textures and their images
+    if (desc->n_textures > 0) {
+        if (!desc->textures || (desc->n_images > 0 && (!desc->images || !desc->rgb2spec_fit))) {
+            set_error("b200pt_scene_create: n_textures > 0 needs textures (and images + rgb2spec_fit when n_images > 0)");
+            return B200PT_ERR_INVALID;
+        }
+        std::vector<TexRec> tex(desc->n_textures);
+        for (int i = 0; i < desc->n_textures; i++) {
+            const b200pt_texture &t = desc->textures[i];
+            TexRec &o = tex[i];
+            o.type = t.type; o.a = t.a; o.b = t.b; o.c = t.c;
+            for (int k = 0; k < 4; k++) { o.f[k] = t.f[k]; o.map[k] = t.map[k]; }
+            // children must come BEFORE their parent (the front-end creates them in that order): no cycles, bounded walks
+            auto child_ok = [&](int id) { return id >= 0 && id < i; };
+            bool ok = true;
+            switch (t.type) {
+            case B200PT_TEX_CONSTANT: ok = spec_ok(t.a); break;
+            case B200PT_TEX_IMAGE: case B200PT_TEX_FLOAT_IMAGE: ok = t.a >= 0 && t.a < desc->n_images; break;
+            case B200PT_TEX_SCALE: ok = child_ok(t.a); break;
+            case B200PT_TEX_MIX: ok = child_ok(t.a) && child_ok(t.b) && (t.c < 0 || child_ok(t.c)); break;
+            case B200PT_TEX_DIRECTION_MIX: ok = child_ok(t.a) && child_ok(t.b); break;
+            case B200PT_TEX_FLOAT_CONSTANT: break;
+            case B200PT_TEX_FLOAT_SCALE: ok = child_ok(t.a) && child_ok(t.b); break;
+            default: ok = false;
+            }
+            if (!ok) {
+                set_error("b200pt_scene_create: texture %d (type %d) is inconsistent", i, t.type);
+                return B200PT_ERR_INVALID;
+            }
+        }
+        TexRec *d_tex = nullptr;
+        if ((rc = dev_upload(r, &d_tex, tex.data(), tex.size(), st))) return rc;
+        r->tex.tex = d_tex;
+        if (desc->n_images > 0) {
+            std::vector<ImageRec> imgs(desc->n_images);
+            for (int i = 0; i < desc->n_images; i++) {
+                const b200pt_image &im = desc->images[i];
+                if (im.width <= 0 || im.height <= 0 || !im.rgb) {
+                    set_error("b200pt_scene_create: image %d is empty", i);
+                    return B200PT_ERR_INVALID;
+                }
+                float *d_rgb = nullptr;
+                if ((rc = dev_upload(r, &d_rgb, im.rgb, (size_t)im.width * im.height * 3, st))) return rc;
+                imgs[i] = ImageRec{im.width, im.height, d_rgb};
+            }
+            ImageRec *d_imgs = nullptr;
+            if ((rc = dev_upload(r, &d_imgs, imgs.data(), imgs.size(), st))) return rc;
+            CU_TRY(cudaStreamSynchronize(st)); // imgs is a local
+            r->tex.images = d_imgs;
+            double *d_coeff = nullptr, *d_z = nullptr;
+            if ((rc = build_rgb2spec(s, desc->rgb2spec_fit, &d_coeff, &d_z, r->allocs))) return rc;
+            r->tex.coeff = d_coeff;
+            r->tex.z_nodes = d_z;
+        }
+        CU_TRY(cudaStreamSynchronize(st)); // tex is a local
     }
     // ---- lights
     r->n_lights = desc->n_lights;
@@ -724,6 +789,7 @@ struct Isect {
     V3 n, ns;   // geometric / shading normal
     V3 dpdu;    // shading.dpdu
     V3 wo;
+    float u, v; // surface parameterisation at the hit (texture lookups)
 };
 
 // Triangle::interaction_from_intersection (shapes/triangle.cu:325-465) from the 48-byte leaf record; per-vertex normals and
@@ -762,6 +828,8 @@ __device__ __forceinline__ void triangle_interaction(const WF &wf, V3 p0, V3 p1,
     }
     si.p = b0 * p0 + b1 * p1 + b2 * p2;
     si.err = gamma_n(7) * (vabs(b0 * p0) + vabs(b1 * p1) + vabs(b2 * p2));
+    si.u = b0 * uv0.x + b1 * uv1.x + b2 * uv2.x; // uvHit (shapes/triangle.cu:372)
+    si.v = b0 * uv0.y + b1 * uv1.y + b2 * uv2.y;
     V3 n = normalize(cross(dp02, dp12));
     if (flip) n = -n;
     si.n = n;
@@ -803,6 +871,12 @@ __device__ __forceinline__ void disk_interaction(const SphereRec &s, V3 ro, V3 r
     const float rHit = sqrtf(sqr(pHit.x) + sqr(pHit.y));
     const V3 dpdu = v3(-s.phi_max * pHit.y, s.phi_max * pHit.x, 0.f);
     const V3 dpdv = v3(pHit.x, pHit.y, 0.f) * (s.z_max - s.radius) / rHit;
+    {
+        float phi = atan2f(pHit.y, pHit.x);
+        if (phi < 0.f) phi += 2.f * kPi;
+        si.u = phi / s.phi_max;
+        si.v = (s.radius - rHit) / (s.radius - s.z_max);
+    }
     pHit.z = s.z_min;
     V3 n = normalize(cross(dpdu, dpdv));
     if (s.flip) n = -n;
@@ -828,6 +902,12 @@ __device__ __forceinline__ void sphere_interaction(const SphereRec &s, V3 ro, V3
     pHit = pHit * (s.radius / len(pHit));
     if (pHit.x == 0.f && pHit.y == 0.f) pHit.x = 1e-5f * s.radius;
     const float cosTheta = pHit.z / s.radius;
+    {
+        float phi = atan2f(pHit.y, pHit.x);
+        if (phi < 0.f) phi += 2.f * kPi;
+        si.u = phi / s.phi_max;
+        si.v = (acosf(clampf(cosTheta, -1.f, 1.f)) - s.theta_z_min) / (s.theta_z_max - s.theta_z_min);
+    }
     const float zRadius = sqrtf(sqr(pHit.x) + sqr(pHit.y));
     const float cosPhi = pHit.x / zRadius, sinPhi = pHit.y / zRadius;
     const V3 dpdu = v3(-s.phi_max * pHit.y, s.phi_max * pHit.x, 0.f);
@@ -1220,19 +1300,26 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
     if ((threadIdx.x & 31) == 0 && n_finished) atomicAdd(&wf.c->finished, (unsigned long long)n_finished);
 }
 
+// "reflectance" / "transmittance" of a material: a spectrum, or a spectrum texture evaluated at the hit
+// (`ext`: a compile-time constant of the calling kernel -- the plain shade kernels carry no texture code at all)
+__device__ __forceinline__ S4 material_spectrum(const WF &wf, int spectrum, int tex1, const Isect &si, S4 lambda, bool ext) {
+    if (ext && tex1 > 0) return tex_eval(wf.tex, wf.spectra, tex1 - 1, TexCtx{si.u, si.v, si.n}, lambda);
+    return spectrum_sample(wf.spectra, spectrum, lambda);
+}
+
 template <int MAT>
-__device__ __forceinline__ void make_bsdf(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf, bool &lpdf_dirty,
+__device__ __forceinline__ void make_bsdf(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf, bool &lpdf_dirty, bool ext,
                                           BSDF<MAT> &b);
 
 template <>
 __device__ __forceinline__ void make_bsdf<B200PT_MAT_DIFFUSE>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf,
-                                                              bool &lpdf_dirty, BSDF<B200PT_MAT_DIFFUSE> &b) {
+                                                              bool &lpdf_dirty, bool ext, BSDF<B200PT_MAT_DIFFUSE> &b) {
     // materials/diffuse_material.cu:17-22
-    b.r = clamp_s4(spectrum_sample(wf.spectra, m.reflectance, lambda), 0.f, 1.f);
+    b.r = clamp_s4(material_spectrum(wf, m.reflectance, m.reflectance_tex1, si, lambda, ext), 0.f, 1.f);
 }
 template <>
 __device__ __forceinline__ void make_bsdf<B200PT_MAT_CONDUCTOR>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf,
-                                                                bool &lpdf_dirty, BSDF<B200PT_MAT_CONDUCTOR> &b) {
+                                                                bool &lpdf_dirty, bool ext, BSDF<B200PT_MAT_CONDUCTOR> &b) {
     // materials/conductor_material.cu:52-75
     float ur = m.u_rough, vr = m.v_rough;
     if (m.remap) {
@@ -1243,7 +1330,7 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_CONDUCTOR>(const WF &wf, co
         b.eta = spectrum_sample(wf.spectra, m.eta, lambda);
         b.k = spectrum_sample(wf.spectra, m.k, lambda);
     } else {
-        const S4 r = clamp_s4(spectrum_sample(wf.spectra, m.reflectance, lambda), 0.f, 0.9999f);
+        const S4 r = clamp_s4(material_spectrum(wf, m.reflectance, m.reflectance_tex1, si, lambda, ext), 0.f, 0.9999f);
         b.eta = s4(1.f);
         b.k = 2.f * sqrt_s4(r) / sqrt_s4(clamp_s4(s4(1.f) + r * -1.f, 0.f, kInf));
     }
@@ -1251,7 +1338,7 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_CONDUCTOR>(const WF &wf, co
 }
 template <>
 __device__ __forceinline__ void make_bsdf<B200PT_MAT_DIELECTRIC>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf,
-                                                                 bool &lpdf_dirty, BSDF<B200PT_MAT_DIELECTRIC> &b) {
+                                                                 bool &lpdf_dirty, bool ext, BSDF<B200PT_MAT_DIELECTRIC> &b) {
     // materials/dielectric_material.cu:39-66
     float eta = spectrum_at(wf.spectra, m.eta, lambda.x);
     if (!spectrum_is_constant(wf.spectra, m.eta)) {
@@ -1273,11 +1360,11 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_DIELECTRIC>(const WF &wf, c
 
 template <>
 __device__ __forceinline__ void make_bsdf<B200PT_MAT_DIFFUSE_TRANSMISSION>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda,
-                                                                           S4 &lpdf, bool &lpdf_dirty,
+                                                                           S4 &lpdf, bool &lpdf_dirty, bool ext,
                                                                            BSDF<B200PT_MAT_DIFFUSE_TRANSMISSION> &b) {
     // materials/diffuse_transmission_material.cu:25-31
-    b.r = clamp_s4(spectrum_sample(wf.spectra, m.reflectance, lambda) * m.scale, 0.f, 1.f);
-    b.t = clamp_s4(spectrum_sample(wf.spectra, m.transmittance, lambda) * m.scale, 0.f, 1.f);
+    b.r = clamp_s4(material_spectrum(wf, m.reflectance, m.reflectance_tex1, si, lambda, ext) * m.scale, 0.f, 1.f);
+    b.t = clamp_s4(material_spectrum(wf, m.transmittance, m.transmittance_tex1, si, lambda, ext) * m.scale, 0.f, 1.f);
 }
 
 template <>
@@ -1291,7 +1378,7 @@ struct BSDF<B200PT_MAT_COATED_CONDUCTOR> : LayeredCore<DielectricCore, Conductor
 
 // the dielectric interface + slab parameters shared by the two coated materials
 template <class L>
-__device__ __forceinline__ void make_coat(const WF &wf, const MatRec &m, S4 lambda, S4 &lpdf, bool &lpdf_dirty, L &b) {
+__device__ __forceinline__ void make_coat(const WF &wf, const MatRec &m, S4 lambda, S4 &lpdf, bool &lpdf_dirty, bool ext, L &b) {
     float ur = m.u_rough, vr = m.v_rough;
     if (m.remap) {
         ur = sqrtf(ur);
@@ -1316,22 +1403,22 @@ __device__ __forceinline__ void make_coat(const WF &wf, const MatRec &m, S4 lamb
 }
 template <>
 __device__ __forceinline__ void make_bsdf<B200PT_MAT_COATED_DIFFUSE>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf,
-                                                                     bool &lpdf_dirty, BSDF<B200PT_MAT_COATED_DIFFUSE> &b) {
+                                                                     bool &lpdf_dirty, bool ext, BSDF<B200PT_MAT_COATED_DIFFUSE> &b) {
     // materials/coated_diffuse_material.cu:53-86
-    b.bottom.r = clamp_s4(spectrum_sample(wf.spectra, m.reflectance, lambda), 0.f, 1.f);
-    make_coat(wf, m, lambda, lpdf, lpdf_dirty, b);
+    b.bottom.r = clamp_s4(material_spectrum(wf, m.reflectance, m.reflectance_tex1, si, lambda, ext), 0.f, 1.f);
+    make_coat(wf, m, lambda, lpdf, lpdf_dirty, ext, b);
 }
 template <>
 __device__ __forceinline__ void make_bsdf<B200PT_MAT_COATED_CONDUCTOR>(const WF &wf, const MatRec &m, const Isect &si, S4 lambda, S4 &lpdf,
-                                                                       bool &lpdf_dirty, BSDF<B200PT_MAT_COATED_CONDUCTOR> &b) {
+                                                                       bool &lpdf_dirty, bool ext, BSDF<B200PT_MAT_COATED_CONDUCTOR> &b) {
     // materials/coated_conductor_material.cu:92-141
-    make_coat(wf, m, lambda, lpdf, lpdf_dirty, b);
+    make_coat(wf, m, lambda, lpdf, lpdf_dirty, ext, b);
     S4 ce, ck;
     if (m.c_eta >= 0) {
         ce = spectrum_sample(wf.spectra, m.c_eta, lambda);
         ck = spectrum_sample(wf.spectra, m.c_k, lambda);
     } else {
-        const S4 r = clamp_s4(spectrum_sample(wf.spectra, m.reflectance, lambda), 0.f, 0.9999f);
+        const S4 r = clamp_s4(material_spectrum(wf, m.reflectance, m.reflectance_tex1, si, lambda, ext), 0.f, 0.9999f);
         ce = s4(1.f);
         ck = 2.f * sqrt_s4(r) / sqrt_s4(clamp_s4(s4(1.f) + r * -1.f, 0.f, kInf));
     }
@@ -1346,8 +1433,11 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_COATED_CONDUCTOR>(const WF 
 }
 
 // ---- gpu_evaluate_material + sample_bsdf + sample_Ld_volume, specialised per material
-template <int MAT, bool MEDIA>
+// EXT: the extended variant of a shade kernel -- media (when the scene has any) and textured materials; scenes with neither
+// run the plain one, which carries none of that code
+template <int MAT, bool EXT>
 __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ? 1 : 2) k_shade(WF wf) {
+    const bool MEDIA = EXT && wf.has_media;
     const unsigned n = wf.c->n_mat[MAT];
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned n_round = (n + 31u) & ~31u;
@@ -1387,7 +1477,7 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
             BSDF<MAT> bsdf;
             // BSDF(ns, dpdus) (base/bsdf.h:16-17): Frame::from_xz(normalize(dpdus), ns)
             bsdf.frame = frame_from_xz(normalize(si.dpdu), si.ns);
-            make_bsdf<MAT>(wf, m, si, lambda, lpdf, lpdf_dirty, bsdf);
+            make_bsdf<MAT>(wf, m, si, lambda, lpdf, lpdf_dirty, EXT, bsdf);
             if (lpdf_dirty) wf.pool.lpdf[slot] = lpdf;
             if (wf.regularize && (ids.w & PF_ANY_NON_SPECULAR)) bsdf.regularize();
             const uint32_t flags = bsdf.flags();
@@ -1659,6 +1749,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     for (int k = 0; k < 4; k++) wf.infinite[k] = r->infinite[k];
     wf.scene_radius = r->scene_radius;
     wf.has_mix = r->has_mix ? 1 : 0;
+    wf.tex = r->tex;
     wf.media = r->d_media;
     wf.tri_medium = r->d_tri_medium;
     wf.has_media = r->n_media > 0 ? 1 : 0;
@@ -1667,6 +1758,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     // with spheres the per-ray start-up is longer and waiting for half a warp pays (C1: 62.0 -> 58.5 ms together with the
     // sphere phase)
     wf.refill_min = getenv("B200PT_WF_REFILL") ? atoi(getenv("B200PT_WF_REFILL")) : (s->n_spheres > 0 ? 16 : 4);
+    const bool ext_shade = wf.has_media || r->tex.tex != nullptr;
     int n_shade_kernels = 0;
     for (int m = 0; m < WF_NMAT; m++) n_shade_kernels += r->has_mat[m] ? 1 : 0;
     wf.n_lights = r->n_lights;
@@ -1720,27 +1812,27 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
             k_after_generate<<<1, 1, 0, st>>>(wf);
             // one shade kernel per material type PRESENT in the scene (a type without materials has no queue)
             if (r->has_mat[B200PT_MAT_DIFFUSE]) {
-                if (wf.has_media) k_shade<B200PT_MAT_DIFFUSE, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                if (ext_shade) k_shade<B200PT_MAT_DIFFUSE, true><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_shade<B200PT_MAT_DIFFUSE, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
             if (r->has_mat[B200PT_MAT_CONDUCTOR]) {
-                if (wf.has_media) k_shade<B200PT_MAT_CONDUCTOR, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                if (ext_shade) k_shade<B200PT_MAT_CONDUCTOR, true><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_shade<B200PT_MAT_CONDUCTOR, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
             if (r->has_mat[B200PT_MAT_DIELECTRIC]) {
-                if (wf.has_media) k_shade<B200PT_MAT_DIELECTRIC, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                if (ext_shade) k_shade<B200PT_MAT_DIELECTRIC, true><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_shade<B200PT_MAT_DIELECTRIC, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
             if (r->has_mat[B200PT_MAT_DIFFUSE_TRANSMISSION]) {
-                if (wf.has_media) k_shade<B200PT_MAT_DIFFUSE_TRANSMISSION, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                if (ext_shade) k_shade<B200PT_MAT_DIFFUSE_TRANSMISSION, true><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_shade<B200PT_MAT_DIFFUSE_TRANSMISSION, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
             if (r->has_mat[B200PT_MAT_COATED_DIFFUSE]) {
-                if (wf.has_media) k_shade<B200PT_MAT_COATED_DIFFUSE, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                if (ext_shade) k_shade<B200PT_MAT_COATED_DIFFUSE, true><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_shade<B200PT_MAT_COATED_DIFFUSE, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
             if (r->has_mat[B200PT_MAT_COATED_CONDUCTOR]) {
-                if (wf.has_media) k_shade<B200PT_MAT_COATED_CONDUCTOR, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                if (ext_shade) k_shade<B200PT_MAT_COATED_CONDUCTOR, true><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_shade<B200PT_MAT_COATED_CONDUCTOR, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
             if ((rc = launch_trace_wf(s, wf, true))) return rc;

@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "light.cuh"
 #include "spectrum.cuh"
+#include "texture.cuh"
 
 namespace b200pt {
 
@@ -25,6 +26,7 @@ struct MatRec {
     float c_u_rough, c_v_rough;
     int32_t c_eta, c_k;
     int32_t mix_a, mix_b;         // mix material: the two material ids; `scale` holds the amount
+    int32_t reflectance_tex1, transmittance_tex1; // spectrum texture id + 1 (0: the spectrum id is used)
 };
 constexpr int WF_NMAT = B200PT_MAT_COUNT; // one shading queue per material type
 
@@ -116,6 +118,7 @@ struct WF {
     const MediumRec *media;
     const uint32_t *tri_medium;
     int32_t has_media, camera_medium;
+    TexTables tex;           // spectrum / float textures (all null when the scene has none)
     SpectrumTable spectra;
     const MatRec *materials;
     const LightRec *lights;

@@ -227,6 +227,18 @@ def xf_points(m, P):
     return out.astype(F32)
 
 
+def xf_vectors(m, V):
+    """Transform::operator()(Vector3f) (euclidean_space/transform.h:306-310), fp32 with the reference's FMA chain"""
+    V = np.asarray(V, dtype=F32).reshape(-1, 3)
+    out = np.zeros_like(V)
+    for r in range(3):
+        acc = (np.float64(m[r, 0]) * V[:, 0].astype(np.float64)).astype(F32)
+        acc = (np.float64(m[r, 1]) * V[:, 1].astype(np.float64) + acc.astype(np.float64)).astype(F32)
+        acc = (np.float64(m[r, 2]) * V[:, 2].astype(np.float64) + acc.astype(np.float64)).astype(F32)
+        out[:, r] = acc
+    return out
+
+
 def xf_normals(inv_m, N):
     """Transform::operator()(Normal3f) (euclidean_space/transform.h:312-320): (inv_m^T) n, fp32"""
     N = np.asarray(N, dtype=F32).reshape(-1, 3)
@@ -365,6 +377,7 @@ class Scene:
         self.P, self.idx, self.tri_material, self.tri_light, self.tri_flip = [], [], [], [], []
         self.N, self.uv, self.any_N, self.any_uv = [], [], False, False
         self.media, self.tri_medium, self.camera_medium = [], [], -1
+        self.textures, self.images, self.named_spec_tex, self.named_float_tex, self._image_ids = [], [], {}, {}, {}
         self.n_verts = 0
         self.spheres, self.spectra, self.materials, self.lights = [], [], [], []
         self.camera = self.filter = self.film = None
@@ -410,6 +423,10 @@ class Scene:
         if name not in p:
             return None
         t, v = p[name]
+        if t == "texture":          # resolved by material_texture(); the spectrum slot gets a placeholder
+            if name not in ("reflectance", "transmittance"):
+                raise SceneError("a texture for '%s' is outside the hot path" % name)
+            return self.spec_constant(0.5)
         if t == "rgb":
             return self.spec_rgb(v[:3], kind)
         if t == "spectrum":
@@ -427,8 +444,124 @@ class Scene:
             return self.spec_constant(v[0])
         raise SceneError("spectrum parameter '%s' of type '%s' not supported" % (name, t))
 
+    # ---- textures (SceneBuilder::parse_texture, scene_builder.cu:679-708; {Spectrum,Float}Texture::create)
+    def _tex(self, type_, a=-1, b=-1, c=-1, f=(0, 0, 0, 0), mapping=(1, 1, 0, 0)):
+        self.textures.append({"type": type_, "a": a, "b": b, "c": c, "f": [float(v) for v in f], "map": [float(v) for v in mapping]})
+        return len(self.textures) - 1
+
+    def load_image(self, path):
+        """GPUImage::init_png (textures/gpu_image.cu:194-222): 8-bit RGBA through the sRGB decoding table, top row first"""
+        if path in self._image_ids:
+            return self._image_ids[path]
+        if not path.lower().endswith(".png"):
+            raise SceneError("image textures: only .png is read here ('%s'); .exr / .pfm / .tga are outside the hot path" % path)
+        if not os.path.exists(path):
+            raise SceneError("image '%s' not found" % path)
+        from PIL import Image
+        im = Image.open(path)
+        if im.mode in ("I;16", "I;16B", "I"):
+            raise SceneError("16-bit PNG textures are not supported")
+        px = np.asarray(im.convert("RGBA"), dtype=np.uint8)[:, :, :3]
+        c = np.arange(256, dtype=np.float64) / 255.0
+        lut = np.where(c <= 0.04045, c / 12.92, ((c + 0.055) / 1.055) ** 2.4).astype(F32)
+        self.images.append(np.ascontiguousarray(lut[px], dtype=F32))
+        self._image_ids[path] = len(self.images) - 1
+        return self._image_ids[path]
+
+    def spectrum_texture_param(self, p, key, scene_dir, default=None):
+        """ParameterDictionary::get_spectrum_texture (parameter_dictionary.cu:276-330): a named texture, or a constant one"""
+        if key in p:
+            t, v = p[key]
+            if t == "texture":
+                if str(v[0]) not in self.named_spec_tex:
+                    raise SceneError("spectrum texture '%s' not defined" % v[0])
+                return self.named_spec_tex[str(v[0])]
+            return self._tex(0, a=self.spec_param(p, key, "albedo", scene_dir))
+        return None if default is None else self._tex(0, a=self.spec_constant(default))
+
+    def float_texture_param(self, p, key, default):
+        if key in p:
+            t, v = p[key]
+            if t == "texture":
+                if str(v[0]) not in self.named_float_tex:
+                    raise SceneError("float texture '%s' not defined" % v[0])
+                return self.named_float_tex[str(v[0])]
+            return self._tex(16, f=(float(v[0]), 0, 0, 0))
+        return self._tex(16, f=(default, 0, 0, 0))
+
+    def _image_node(self, type_, p, scene_dir):
+        if p_str(p, "mapping", "uv") != "uv":
+            raise SceneError("texture mapping '%s': only \"uv\" is on the hot path" % p_str(p, "mapping", "uv"))
+        if p_str(p, "wrap", "repeat") != "repeat":
+            raise SceneError("texture wrap '%s': the reference implements \"repeat\" only (gpu_image.cu:56-66)" % p_str(p, "wrap", "repeat"))
+        if p_str(p, "filter", "bilinear") not in ("ewa", "bilinear", "trilinear", "point"):
+            raise SceneError("unknown texture filter")       # every filter is a bilerp in the reference (mipmap.cu:22-25)
+        img = self.load_image(os.path.join(scene_dir, p_str(p, "filename", "")))
+        return self._tex(type_, a=img, f=(p_float(p, "scale", 1.0), 1.0 if p_bool(p, "invert", False) else 0.0, 0, 0),
+                         mapping=(p_float(p, "uscale", 1.0), p_float(p, "vscale", 1.0), p_float(p, "udelta", 0.0), p_float(p, "vdelta", 0.0)))
+
+    def add_texture(self, name, color_type, tex_type, p, render_from_texture, scene_dir):
+        if color_type == "float":
+            if tex_type == "constant":
+                tid = self._tex(16, f=(p_float(p, "value", 1.0), 0, 0, 0))
+            elif tex_type == "imagemap":
+                tid = self._image_node(17, p, scene_dir)
+            elif tex_type == "scale":
+                tid = self._tex(18, a=self.float_texture_param(p, "scale", 1.0), b=self.float_texture_param(p, "tex", 1.0))
+            else:
+                raise SceneError("float texture '%s' is not a reference texture (base/float_texture.cu:7-35)" % tex_type)
+            self.named_float_tex[name] = tid
+            return
+        if color_type != "spectrum":
+            raise SceneError("Texture colour type '%s' (scene_builder.cu:706-707)" % color_type)
+        if tex_type == "constant":
+            v = self.spec_param(p, "value", "albedo", scene_dir)
+            tid = self._tex(0, a=self.spec_constant(1.0) if v is None else v)
+        elif tex_type == "imagemap":
+            tid = self._image_node(1, p, scene_dir)
+        elif tex_type == "scale":
+            t = self.spectrum_texture_param(p, "tex", scene_dir)
+            if t is None:
+                raise SceneError("scale texture without \"tex\"")
+            tid = self._tex(2, a=t, f=(p_float(p, "scale", 1.0), 0, 0, 0))
+        elif tex_type == "mix":
+            t1 = self.spectrum_texture_param(p, "tex1", scene_dir, 0.0)
+            t2 = self.spectrum_texture_param(p, "tex2", scene_dir, 1.0)
+            tid = self._tex(3, a=t1, b=t2, c=self.float_texture_param(p, "amount", 0.5))
+        elif tex_type == "directionmix":
+            t1 = self.spectrum_texture_param(p, "tex1", scene_dir, 0.0)
+            t2 = self.spectrum_texture_param(p, "tex2", scene_dir, 1.0)
+            d = np.asarray(p["dir"][1][:3] if "dir" in p else (0, 1, 0), dtype=F32)
+            d = xf_vectors(render_from_texture.m, d.reshape(1, 3))[0]
+            d = (d / F32(np.sqrt(F32(F32(d[0] * d[0]) + F32(d[1] * d[1])) + F32(d[2] * d[2])))).astype(F32)
+            tid = self._tex(4, a=t1, b=t2, f=(d[0], d[1], d[2], 0))
+        elif tex_type == "checkerboard":
+            raise SceneError("checkerboard texture: its filter width comes from ray differentials the reference never initialises "
+                             "(SURVEY.md a28); not reproduced")
+        else:
+            raise SceneError("spectrum texture '%s' is not a reference texture (base/spectrum_texture.cu:9-58)" % tex_type)
+        self.named_spec_tex[name] = tid
+
+    def material_texture(self, p, key):
+        """texture id + 1 when the material parameter names a texture, else 0"""
+        if key in p and p[key][0] == "texture":
+            name = str(p[key][1][0])
+            if name not in self.named_spec_tex:
+                raise SceneError("spectrum texture '%s' not defined" % name)
+            return self.named_spec_tex[name] + 1
+        return 0
+
     # ---- materials
     def add_material(self, kind, p, scene_dir, named=None):
+        n_before = len(self.materials)
+        self._add_material(kind, p, scene_dir, named)
+        if len(self.materials) > n_before:
+            m = self.materials[-1]
+            m["reflectance_tex1"] = self.material_texture(p, "reflectance") if m["type"] in (0, 1, 3, 4, 5) else 0
+            m["transmittance_tex1"] = self.material_texture(p, "transmittance") if m["type"] == 3 else 0
+        return len(self.materials) - 1
+
+    def _add_material(self, kind, p, scene_dir, named=None):
         if kind == "diffuse":
             r = self.spec_param(p, "reflectance", "albedo", scene_dir)
             if r is None:
@@ -703,6 +836,7 @@ class Scene:
             mats[i].c_u_roughness, mats[i].c_v_roughness = m.get("cur", 0.0), m.get("cvr", 0.0)
             mats[i].c_eta, mats[i].c_k = m.get("c_eta", -1), m.get("c_k", -1)
             mats[i].mix_a, mats[i].mix_b = m.get("mix_a", -1), m.get("mix_b", -1)
+            mats[i].reflectance_tex1, mats[i].transmittance_tex1 = m.get("reflectance_tex1", 0), m.get("transmittance_tex1", 0)
         d.n_materials, d.materials = len(self.materials), mats
         lights = (api.Light * max(1, len(self.lights)))()
         for i, l in enumerate(self.lights):
@@ -722,6 +856,25 @@ class Scene:
             d.n_media, d.media = len(self.media), med
             d.tri_medium = tmed.ctypes.data_as(api.C.POINTER(api.C.c_uint32))
             keep += [med, tmed]
+        if self.textures:
+            tex = (api.Texture * len(self.textures))()
+            for i, t in enumerate(self.textures):
+                tex[i].type, tex[i].a, tex[i].b, tex[i].c = t["type"], t["a"], t["b"], t["c"]
+                tex[i].f[:] = t["f"]
+                tex[i].map[:] = t["map"]
+            d.n_textures, d.textures = len(self.textures), tex
+            keep.append(tex)
+            if self.images:
+                imgs = (api.Image * len(self.images))()
+                for i, im in enumerate(self.images):
+                    imgs[i].height, imgs[i].width = im.shape[0], im.shape[1]
+                    imgs[i].rgb = api._fp(im)
+                rgb_tbl, white, lam01 = spectral._fit_tables()
+                fit = np.ascontiguousarray(np.concatenate([np.asarray(rgb_tbl, np.float64).ravel(), np.asarray(white, np.float64).ravel(),
+                                                           np.asarray(lam01, np.float64).ravel()]))
+                d.n_images, d.images = len(self.images), imgs
+                d.rgb2spec_fit = fit.ctypes.data_as(api.C.POINTER(api.C.c_double))
+                keep += [imgs, fit]
         if self.camera is not None:
             cam = api.Camera()
             cam.medium = self.camera_medium
@@ -760,11 +913,13 @@ class _GState:
         return g
 
 
-def load(path=None, text=None, spp=None, integrator=None):
-    """SceneBuilder::parse_file + preprocess (scene/scene_builder.cu:741-966) -> Scene."""
+def load(path=None, text=None, spp=None, integrator=None, scene_dir=None):
+    """SceneBuilder::parse_file + preprocess (scene/scene_builder.cu:741-966) -> Scene.  `scene_dir`: where relative file names
+    (PLY meshes, spectra, images) of a scene given as text are looked up."""
     if text is None:
         text = open(path).read()
-    scene_dir = os.path.dirname(os.path.abspath(path)) if path else os.getcwd()
+    if scene_dir is None:
+        scene_dir = os.path.dirname(os.path.abspath(path)) if path else os.getcwd()
     sc = Scene()
     g, stack = _GState(), []
     named_cs, named_mat = {}, {}
@@ -897,6 +1052,10 @@ def load(path=None, text=None, spp=None, integrator=None):
             g.reverse_orientation = not g.reverse_orientation
         elif kw == "Material":
             g.material = sc.add_material(args[0], params_of(args[1:]), scene_dir, named_mat)
+        elif kw == "Texture":
+            if len(args) < 3:
+                raise SceneError("Texture needs a name, a colour type and a class")
+            sc.add_texture(str(args[0]), str(args[1]), str(args[2]), params_of(args[3:]), render_from_world * g.ctm, scene_dir)
         elif kw == "MakeNamedMaterial":
             p = params_of(args[1:])
             named_mat[args[0]] = sc.add_material(p_str(p, "type", "diffuse"), p, scene_dir, named_mat)

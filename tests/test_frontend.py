@@ -121,7 +121,7 @@ def test_ply_reader(b200pt, tmp_path):
 def test_ctypes_layout_matches_header(b200pt, tmp_path):
     """sizeof of every struct crossing the boundary, as gcc sees include/b200pt.h, equals the ctypes mirror"""
     names = ["b200pt_spectrum", "b200pt_material", "b200pt_light", "b200pt_sphere", "b200pt_camera", "b200pt_filter",
-             "b200pt_film_desc", "b200pt_scene_desc", "b200pt_build_stats", "b200pt_render_opts", "b200pt_render_stats", "b200pt_medium"]
+             "b200pt_film_desc", "b200pt_scene_desc", "b200pt_build_stats", "b200pt_render_opts", "b200pt_render_stats", "b200pt_medium", "b200pt_texture", "b200pt_image"]
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include "b200pt.h"\nint main(void){' +
                    "".join('printf("%%zu\\n", sizeof(%s));' % n for n in names) + "return 0;}\n")
@@ -130,7 +130,7 @@ def test_ctypes_layout_matches_header(b200pt, tmp_path):
     sizes = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     A = b200pt.api
     mirror = [A.Spectrum, A.Material, A.Light, A.Sphere, A.Camera, A.Filter, A.FilmDesc, A.SceneDesc, A.BuildStats, A.RenderOpts,
-              A.RenderStats, A.Medium]
+              A.RenderStats, A.Medium, A.Texture, A.Image]
     assert sizes == [ctypes.sizeof(m) for m in mirror]
 
 
@@ -194,6 +194,36 @@ def test_loop_subdivision_mesh_producer(b200pt):
     assert sum(len(i) for i in sc.idx) == 4 + 8 * 64 + 4 * 64 + 18 * 16
     with pytest.raises(ps.SceneError):
         ps.load(text='Camera "perspective"\nWorldBegin\nShape "loopsubdiv" "integer indices" [0 1 2] "point3 P" [0 0 0 1 0 0 0 1 0 5 5 5]\n')
+
+
+def test_texture_front_end(b200pt, tmp_path):
+    """Texture directive -> texture records (children before parents), images through the sRGB table, materials naming textures"""
+    ps = b200pt.pbrt_scene
+    sc = ps.load(os.path.join(ROOT, "tests", "scenes", "textures.pbrt"))
+    assert len(sc.images) == 2 and sc.images[0].shape == (16, 32, 3) and sc.images[0].dtype == np.float32
+    assert sc.images[0].min() == 0.0 and sc.images[0].max() == 1.0
+    assert abs(float(sc.images[0][5, 5, 0]) - 0.5775804) < 1e-6          # sRGB 200 -> linear (SRGBToLinearLUT[200])
+    T = sc.textures
+    for i, t in enumerate(T):
+        kids = [t["a"], t["b"]] if t["type"] in (3, 4, 18) else [t["a"]] if t["type"] == 2 else []
+        kids += [t["c"]] if t["type"] == 3 and t["c"] >= 0 else []
+        assert all(0 <= k < i for k in kids)
+    named = sc.named_spec_tex
+    assert T[named["tiled"]]["map"] == [3.0, 2.5, 0.25, -0.1] and T[named["tiled"]]["f"][0] == pytest.approx(0.8)
+    assert T[named["negative"]]["f"][1] == 1.0 and T[named["updown"]]["type"] == 4 and T[named["updown"]]["f"][:3] == [0.0, 1.0, 0.0]
+    assert T[sc.named_float_tex["softmask"]]["type"] == 18
+    mats = sc.materials
+    assert [m["reflectance_tex1"] > 0 for m in mats] == [False, True, True, True, True, True, True]
+    assert mats[5]["transmittance_tex1"] == named["dim"] + 1 and mats[6]["type"] == 1 and mats[6]["eta"] == -1
+    d = sc.to_desc()
+    assert d.n_textures == len(T) and d.n_images == 2 and bool(d.rgb2spec_fit)
+    head = 'Camera "perspective"\nWorldBegin\n'
+    for bad in ('Texture "t" "spectrum" "checkerboard"', 'Texture "t" "spectrum" "imagemap" "string filename" ["nope.png"]',
+                'Texture "t" "spectrum" "imagemap" "string filename" ["x.exr"]', 'Texture "t" "spectrum" "wrinkled"',
+                'Material "diffuse" "texture reflectance" ["undefined"]', 'Texture "t" "float" "mix"',
+                'Texture "t" "spectrum" "imagemap" "string filename" ["textures/colours.png"] "string mapping" ["planar"]'):
+        with pytest.raises(ps.SceneError):
+            ps.load(text=head + bad + "\n", scene_dir=os.path.join(ROOT, "tests", "scenes"))
 
 
 def test_sample_ranges_tile(b200pt):

@@ -46,6 +46,9 @@ CASES = [
     # Shape "disk": annuli, partial sweeps, mirrored / squashed / quarter-turned
     ("disk_96x64_64spp", "disk.pbrt", None, 64, None, None),
     ("disk_96x64_1024spp", "disk.pbrt", None, 1024, None, None),
+    # image / procedural textures (needs tests/scenes/textures/ beside the scene copy)
+    ("textures_96x64_64spp", "textures.pbrt", None, 64, None, None),
+    ("textures_96x64_1024spp", "textures.pbrt", None, 1024, None, None),
     # C4 in miniature (workloads.procedural_scene, seed 7): many lights -> statistical gate only
     ("c4tiny_96x54_1024spp", "@c4tiny", None, 1024, None, None),
 ]
@@ -58,6 +61,8 @@ def main():
     exe = os.path.join(ROOT, "oracle", "_ref", "pbrt-minus-ref")
     manifest = {}
     only = sys.argv[1:]
+    import shutil
+    shutil.copytree(os.path.join(ROOT, "tests", "scenes", "textures"), os.path.join(out, "textures"), dirs_exist_ok=True)
     for name, scene, res, spp, integ, sampler in CASES:
         if only and name not in only:
             continue
