@@ -116,7 +116,9 @@ typedef struct {
 /* ---- lights (base/light.cu:22-75), in the order the scene file creates them (= light-sampler index):
  *      one DiffuseAreaLight per emissive triangle; DistantLight (lights/distant_light.cu), UniformInfiniteLight
  *      (lights/uniform_infinite_light.cu) and SpotLight (lights/spot_light.cu) from "LightSource" */
-enum { B200PT_LIGHT_AREA = 0, B200PT_LIGHT_DISTANT = 1, B200PT_LIGHT_UNIFORM_INFINITE = 2, B200PT_LIGHT_SPOT = 3 };
+enum { B200PT_LIGHT_AREA = 0, B200PT_LIGHT_DISTANT = 1, B200PT_LIGHT_UNIFORM_INFINITE = 2, B200PT_LIGHT_SPOT = 3,
+       B200PT_LIGHT_IMAGE_INFINITE = 4 /* lights/image_infinite_light.cu: `image` in the equal-area octahedral parameterisation;
+                                          needs rgb2spec_fit; at most one per scene */ };
 typedef struct {
     int32_t triangle;  /* AREA: index into the triangle array; other types: -1 */
     int32_t spectrum;  /* Lemit / I spectrum id */
@@ -126,6 +128,8 @@ typedef struct {
     float v[3];        /* DISTANT: render_from_light(0,0,1) (not normalised); SPOT: render_from_light(0,0,0) */
     float light_from_render[9]; /* SPOT: upper 3x3 of the inverse transform, row-major (Transform::apply_inverse) */
     float cos_falloff_start, cos_falloff_end; /* SPOT */
+    int32_t image;               /* IMAGE_INFINITE: image id */
+    float render_from_light[9];  /* IMAGE_INFINITE: upper 3x3 of the transform (light_from_render holds its inverse) */
 } b200pt_light;
 
 /* ---- spheres (shapes/sphere.h:71-125); intersected in object space ----------------------- */

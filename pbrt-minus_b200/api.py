@@ -35,7 +35,8 @@ class Material(C.Structure):
 class Light(C.Structure):
     _fields_ = [("triangle", C.c_int32), ("spectrum", C.c_int32), ("scale", C.c_float), ("two_sided", C.c_int32),
                 ("type", C.c_int32), ("v", C.c_float * 3), ("light_from_render", C.c_float * 9),
-                ("cos_falloff_start", C.c_float), ("cos_falloff_end", C.c_float)]
+                ("cos_falloff_start", C.c_float), ("cos_falloff_end", C.c_float),
+                ("image", C.c_int32), ("render_from_light", C.c_float * 9)]
 
 
 class Sphere(C.Structure):

@@ -22,13 +22,13 @@ struct LightRec { // 64 B
     float p0[3], p1[3], p2[3]; // AREA: vertices.  DISTANT: p0 = render_from_light(0,0,1).  SPOT: p0 = position
     float scale;      // already divided by the photometric integral
     int32_t spectrum; // Lemit
-    int32_t flags;    // bit 0: two_sided, bit 1: flip normal (reverse_orientation ^ swaps_handedness), bits 4..5: B200PT_LIGHT_*
+    int32_t flags;    // bit 0: two_sided, bit 1: flip normal (reverse_orientation ^ swaps_handedness), bits 4..6: B200PT_LIGHT_*
     float pmf;        // power_light_sampler pdfs[idx]
     float area;
     int32_t prim;     // primitive (triangle) index of this light: its own shadow rays skip it (-1: none)
     int32_t ext;      // SPOT: index into the LightExt array
 };
-__device__ __host__ __forceinline__ int light_type(const LightRec &L) { return (L.flags >> 4) & 3; }
+__device__ __host__ __forceinline__ int light_type(const LightRec &L) { return (L.flags >> 4) & 7; }
 
 struct LightExt { // 48 B, spot lights only (lights/spot_light.h)
     float m[9];   // upper 3x3 of light_from_render

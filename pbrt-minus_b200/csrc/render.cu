@@ -55,6 +55,8 @@ struct RenderData {
     bool has_mat[WF_NMAT] = {};
     bool has_mix = false;
     TexTables tex = {};                // textures: records, images, the fitted RGB-to-spectrum table
+    std::vector<ImageRec> h_images;    // device pointers of the uploaded images
+    EnvMap env = {};                   // image infinite light (env.light = -1: none)
     MediumRec *d_media = nullptr;      // media scenes only
     uint32_t *d_tri_medium = nullptr;
     int n_media = 0, camera_medium = -1;
@@ -112,20 +114,31 @@ static float build_pc1d(const float *f, int n, float mn, float mx, float *func, 
 }
 
 __global__ void k_light_power(SpectrumTable tab, const LightRec *lights, const LightExt *ext, float scene_radius, int n, S4 lambda,
-                              S4 pdf, float *out) {
+                              S4 pdf, float *out, EnvMap env, TexTables tex) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     // light_samplers/power_light_sampler.cu:15-21: phi at the wavelengths of sample_visible(0.5), which the
     // reference evaluates on the HOST; the 4th wavelength sits within an ulp of the 830 nm cut-off of
     // visible_wavelengths_pdf, so lambda / pdf come from the host's libm (see b200pt_upload_render_data)
     const LightRec L = lights[i];
-    const S4 Le = spectrum_sample(tab, L.spectrum, lambda) * L.scale;
+    const S4 Le = L.spectrum >= 0 ? spectrum_sample(tab, L.spectrum, lambda) * L.scale : s4(0.f);
     S4 phi;
     switch (light_type(L)) {
     case B200PT_LIGHT_DISTANT: phi = Le * sqr(scene_radius); break;                        // lights/distant_light.cu:52-55
     case B200PT_LIGHT_UNIFORM_INFINITE:                                                     // lights/uniform_infinite_light.cu:34-37
         phi = spectrum_sample(tab, L.spectrum, lambda) * (4.f * kPi * kPi * sqr(scene_radius) * L.scale);
         break;
+    case B200PT_LIGHT_IMAGE_INFINITE: {                                                     // lights/image_infinite_light.cu:118-135
+        S4 sum = s4(0.f);
+        for (int x = 0; x < env.width; x++)
+            for (int y = 0; y < env.height; y++) {
+                V3 rgb = env_fetch(env, x, y);
+                rgb = v3(fmaxf(rgb.x, 0.f), fmaxf(rgb.y, 0.f), fmaxf(rgb.z, 0.f));
+                sum = sum + rgb_illuminant_sample(tex, tab, rgb, lambda);
+            }
+        phi = sum * (4.f * kPi * kPi * sqr(scene_radius) * env.scale) / (float)(env.width * env.height);
+        break;
+    }
     case B200PT_LIGHT_SPOT: {                                                               // lights/spot_light.cu:104-108
         const LightExt e = ext[L.ext];
         phi = Le * 2.f * kPi * ((1.f - e.cos_start) + (e.cos_start - e.cos_end) / 2.f);
@@ -365,10 +378,36 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
         if ((rc = dev_upload(r, &r->d_media, med.data(), med.size(), st))) return rc;
         if ((rc = dev_upload(r, &r->d_tri_medium, desc->tri_medium, (size_t)desc->n_triangles, st))) return rc;
     }
-    // ---- textures and their images
+    // ---- images (textures, the image infinite light) and the RGB-to-spectrum table their lookups need
+    r->env.light = -1;
+    if (desc->n_images > 0) {
+        if (!desc->images || !desc->rgb2spec_fit) {
+            set_error("b200pt_scene_create: n_images > 0 needs images and rgb2spec_fit");
+            return B200PT_ERR_INVALID;
+        }
+        r->h_images.resize(desc->n_images);
+        for (int i = 0; i < desc->n_images; i++) {
+            const b200pt_image &im = desc->images[i];
+            if (im.width <= 0 || im.height <= 0 || !im.rgb) {
+                set_error("b200pt_scene_create: image %d is empty", i);
+                return B200PT_ERR_INVALID;
+            }
+            float *d_rgb = nullptr;
+            if ((rc = dev_upload(r, &d_rgb, im.rgb, (size_t)im.width * im.height * 3, st))) return rc;
+            r->h_images[i] = ImageRec{im.width, im.height, d_rgb};
+        }
+        ImageRec *d_imgs = nullptr;
+        if ((rc = dev_upload(r, &d_imgs, r->h_images.data(), r->h_images.size(), st))) return rc;
+        r->tex.images = d_imgs;
+        double *d_coeff = nullptr, *d_z = nullptr;
+        if ((rc = build_rgb2spec(s, desc->rgb2spec_fit, &d_coeff, &d_z, r->allocs))) return rc;
+        r->tex.coeff = d_coeff;
+        r->tex.z_nodes = d_z;
+    }
+    // ---- textures
     if (desc->n_textures > 0) {
-        if (!desc->textures || (desc->n_images > 0 && (!desc->images || !desc->rgb2spec_fit))) {
-            set_error("b200pt_scene_create: n_textures > 0 needs textures (and images + rgb2spec_fit when n_images > 0)");
+        if (!desc->textures) {
+            set_error("b200pt_scene_create: n_textures > 0 but textures == NULL");
             return B200PT_ERR_INVALID;
         }
         std::vector<TexRec> tex(desc->n_textures);
@@ -398,27 +437,6 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
         TexRec *d_tex = nullptr;
         if ((rc = dev_upload(r, &d_tex, tex.data(), tex.size(), st))) return rc;
         r->tex.tex = d_tex;
-        if (desc->n_images > 0) {
-            std::vector<ImageRec> imgs(desc->n_images);
-            for (int i = 0; i < desc->n_images; i++) {
-                const b200pt_image &im = desc->images[i];
-                if (im.width <= 0 || im.height <= 0 || !im.rgb) {
-                    set_error("b200pt_scene_create: image %d is empty", i);
-                    return B200PT_ERR_INVALID;
-                }
-                float *d_rgb = nullptr;
-                if ((rc = dev_upload(r, &d_rgb, im.rgb, (size_t)im.width * im.height * 3, st))) return rc;
-                imgs[i] = ImageRec{im.width, im.height, d_rgb};
-            }
-            ImageRec *d_imgs = nullptr;
-            if ((rc = dev_upload(r, &d_imgs, imgs.data(), imgs.size(), st))) return rc;
-            CU_TRY(cudaStreamSynchronize(st)); // imgs is a local
-            r->tex.images = d_imgs;
-            double *d_coeff = nullptr, *d_z = nullptr;
-            if ((rc = build_rgb2spec(s, desc->rgb2spec_fit, &d_coeff, &d_z, r->allocs))) return rc;
-            r->tex.coeff = d_coeff;
-            r->tex.z_nodes = d_z;
-        }
         CU_TRY(cudaStreamSynchronize(st)); // tex is a local
     }
     // ---- lights
@@ -429,7 +447,7 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
     for (int i = 0; i < desc->n_lights; i++) {
         const b200pt_light &l = desc->lights[i];
         if (l.type != B200PT_LIGHT_AREA) {
-            if (l.type < 0 || l.type > B200PT_LIGHT_SPOT || !spec_ok(l.spectrum)) {
+            if (l.type < 0 || l.type > B200PT_LIGHT_IMAGE_INFINITE || (l.type != B200PT_LIGHT_IMAGE_INFINITE && !spec_ok(l.spectrum))) {
                 set_error("b200pt_scene_create: light %d is inconsistent (type %d)", i, l.type);
                 return B200PT_ERR_INVALID;
             }
@@ -449,7 +467,64 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
                 o.ext = (int)ext.size();
                 ext.push_back(e);
             }
-            if (l.type == B200PT_LIGHT_UNIFORM_INFINITE) {
+            if (l.type == B200PT_LIGHT_IMAGE_INFINITE) {
+                // ImageInfiniteLight ctor (lights/image_infinite_light.cu:8-60): per-pixel luminance, pixels below 0.001 of the
+                // maximum dropped, Distribution2D = an alias table over the column sums + one per column
+                if (l.image < 0 || l.image >= desc->n_images || r->env.light >= 0) {
+                    set_error("b200pt_scene_create: light %d: bad image id, or a second image infinite light", i);
+                    return B200PT_ERR_INVALID;
+                }
+                const b200pt_image &im = desc->images[l.image];
+                const int W = im.width, H = im.height;
+                std::vector<float> lum((size_t)W * H); // [x][y]
+                float max_lum = 0.f;
+                for (int x = 0; x < W; x++)
+                    for (int y = 0; y < H; y++) {
+                        const float *px = im.rgb + 3 * ((size_t)y * W + x);
+                        const float v = (std::max(px[0], 0.f) + std::max(px[1], 0.f) + std::max(px[2], 0.f)) / 3;
+                        lum[(size_t)x * H + y] = v;
+                        max_lum = std::max(max_lum, v);
+                    }
+                if (!(max_lum > 0.f)) {
+                    set_error("b200pt_scene_create: light %d: the image is black", i);
+                    return B200PT_ERR_INVALID;
+                }
+                const double threshold = 0.001 * max_lum;
+                for (float &v : lum)
+                    if (v < threshold) v = 0.f;
+                std::vector<float> col(W), ypdf((size_t)W * H), xpdf;
+                std::vector<AliasBin> ybins((size_t)W * H), xbins;
+                for (int x = 0; x < W; x++) {
+                    float sum = 0.f;
+                    for (int y = 0; y < H; y++) sum += lum[(size_t)x * H + y];
+                    col[x] = sum;
+                    std::vector<float> vals(lum.begin() + (size_t)x * H, lum.begin() + (size_t)(x + 1) * H), pd;
+                    std::vector<AliasBin> bn;
+                    build_alias(vals, bn, pd);
+                    std::copy(bn.begin(), bn.end(), ybins.begin() + (size_t)x * H);
+                    std::copy(pd.begin(), pd.end(), ypdf.begin() + (size_t)x * H);
+                }
+                build_alias(col, xbins, xpdf);
+                AliasBin *d_xb = nullptr, *d_yb = nullptr;
+                float *d_xp = nullptr, *d_yp = nullptr;
+                if ((rc = dev_upload(r, &d_xb, xbins.data(), xbins.size(), st))) return rc;
+                if ((rc = dev_upload(r, &d_xp, xpdf.data(), xpdf.size(), st))) return rc;
+                if ((rc = dev_upload(r, &d_yb, ybins.data(), ybins.size(), st))) return rc;
+                if ((rc = dev_upload(r, &d_yp, ypdf.data(), ypdf.size(), st))) return rc;
+                CU_TRY(cudaStreamSynchronize(st));
+                EnvMap &E = r->env;
+                E.light = i;
+                E.width = W;
+                E.height = H;
+                E.rgb = r->h_images[l.image].rgb;
+                E.xb = d_xb; E.xp = d_xp; E.yb = d_yb; E.yp = d_yp;
+                for (int k = 0; k < 9; k++) {
+                    E.rfl[k] = l.render_from_light[k];
+                    E.lfr[k] = l.light_from_render[k];
+                }
+                E.scale = l.scale;
+            }
+            if (l.type == B200PT_LIGHT_UNIFORM_INFINITE || l.type == B200PT_LIGHT_IMAGE_INFINITE) {
                 if (r->n_infinite >= 4) {
                     set_error("b200pt_scene_create: at most 4 infinite lights");
                     return B200PT_ERR_UNSUPPORTED;
@@ -548,7 +623,7 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             hp[i] = (hl[i] < 360 || hl[i] > 830) ? 0.f : 0.0039398042f / (c * c);
         }
         k_light_power<<<(desc->n_lights + 127) / 128, 128, 0, st>>>(tab, r->d_lights, r->d_light_ext, r->scene_radius, desc->n_lights, make_float4(hl[0], hl[1], hl[2], hl[3]),
-                                                                  make_float4(hp[0], hp[1], hp[2], hp[3]), d_w);
+                                                                  make_float4(hp[0], hp[1], hp[2], hp[3]), d_w, r->env, r->tex);
         CU_TRY(cudaMemcpyAsync(w.data(), d_w, w.size() * 4, cudaMemcpyDeviceToHost, st));
         CU_TRY(cudaStreamSynchronize(st));
         std::vector<AliasBin> bins;
@@ -960,6 +1035,25 @@ __device__ __forceinline__ float mix_hash_float(V3 p, V3 err, V3 wo) {
     return __fmul_rn((float)(uint32_t)h, 0x1p-32f);
 }
 
+// ImageInfiniteLight::sample_li (lights/image_infinite_light.cu:84-103): the far point sits 2 R along the (un-normalised) wi
+__device__ __forceinline__ bool env_nee(const WF &wf, V3 p, float2 u, S4 lambda, LightSample &ls, S4 &Le) {
+    V3 wi;
+    float pdf;
+    env_sample(wf.env, wf.tex, wf.spectra, u, lambda, &wi, &pdf, &Le);
+    ls.wi = wi;
+    ls.pdf = pdf;
+    ls.p = p + wi * (2.f * wf.scene_radius);
+    ls.err = v3(0.f, 0.f, 0.f);
+    ls.n = v3(0.f, 0.f, 0.f);
+    return true;
+}
+
+// escaping ray against the image infinite light: Le and pdf_li (only in the ENV instantiations of k_logic)
+__device__ __forceinline__ void env_escape(const WF &wf, V3 d, S4 lambda, S4 *Le, float *pdf) {
+    *Le = env_le(wf.env, wf.tex, wf.spectra, d, lambda);
+    *pdf = env_pdf(wf.env, d);
+}
+
 // ---- media ------------------------------------------------------------------------------------------------------------
 // DenselySampledSpectrum(spectrum, scale)::sample (spectra/densely_sampled_spectrum.h:10-14,46-66): the medium's sigma
 // spectra are tabulated at integer nanometres as spectrum(l) * scale and looked up with a lerp; evaluated here on the fly
@@ -1097,11 +1191,15 @@ __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
                 LightSample ls;
                 bool have, delta = false;
                 float lw = 1.f, ld2 = 1.f;
+                S4 Le_env = s4(0.f);
+                const bool is_env = lt == B200PT_LIGHT_IMAGE_INFINITE;
                 if (lt == B200PT_LIGHT_AREA) have = light_sample(Lr, ctx, up, ls) && light_emits_towards(Lr, ls.n, -ls.wi);
+                else if (is_env) have = env_nee(wf, ctx.p, up, lambda, ls, Le_env);
                 else have = light_sample_other(Lr, lt, wf.light_ext, wf.scene_radius, ctx, up, ls, &lw, &ld2, &delta);
                 if (have) {
                     S4 Le;
-                    if (lt == B200PT_LIGHT_SPOT) Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * (lw * Lr.scale) / ld2;
+                    if (is_env) Le = Le_env;
+                    else if (lt == B200PT_LIGHT_SPOT) Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * (lw * Lr.scale) / ld2;
                     else Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * Lr.scale;
                     if (is_positive(Le) && ls.pdf != 0.f) {
                         const S4 T = volume_transmittance(wf, o, medium, ls, lambda, s_stack + threadIdx.x, &wf.c->stack_overflow);
@@ -1142,7 +1240,7 @@ __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
 }
 
 // ---- control_logic (integrators/wavefront_path.cu:68-214)
-template <bool MEDIA>
+template <bool MEDIA, bool ENV>
 __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
     // one thread per pool slot, in slot order: every lane access below is a coalesced 16-byte gather
     const unsigned n = (unsigned)wf.pool_size;
@@ -1195,11 +1293,14 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                 // (lights/uniform_infinite_light.cu:51-58), so the weight is power_heuristic(dir_pdf, 0)
                 for (int k = 0; k < wf.n_infinite; k++) {
                     const LightRec Lr = wf.lights[wf.infinite[k]];
-                    const S4 Le = spectrum_sample(wf.spectra, Lr.spectrum, wf.pool.lambda[slot]) * Lr.scale;
+                    S4 Le;
+                    float pdf_li = 0.f;
+                    if (ENV && light_type(Lr) == B200PT_LIGHT_IMAGE_INFINITE) env_escape(wf, v3(wf.pool.ray_d[slot]), wf.pool.lambda[slot], &Le, &pdf_li);
+                    else Le = spectrum_sample(wf.spectra, Lr.spectrum, wf.pool.lambda[slot]) * Lr.scale;
                     if (depth == 0 || (ids.w & PF_SPECULAR)) {
                         L = L + beta * Le;
                     } else {
-                        const float pdf_light = Lr.pmf * 0.f;
+                        const float pdf_light = Lr.pmf * pdf_li;
                         const float dir_pdf = wf.pool.misc[slot].y * dir_pdf_scale;
                         L = L + beta * power_heuristic(dir_pdf, pdf_light) * Le;
                     }
@@ -1505,11 +1606,15 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
                     LightSample ls;
                     bool have, delta = false;
                     float lw = 1.f, ld2 = 1.f;
+                    S4 Le_env = s4(0.f);
+                    const bool is_env = EXT && lt == B200PT_LIGHT_IMAGE_INFINITE; // such scenes run the extended kernels
                     if (lt == B200PT_LIGHT_AREA) have = light_sample(Lr, ctx, up, ls) && light_emits_towards(Lr, ls.n, -ls.wi);
+                    else if (is_env) have = env_nee(wf, ctx.p, up, lambda, ls, Le_env);
                     else have = light_sample_other(Lr, lt, wf.light_ext, wf.scene_radius, ctx, up, ls, &lw, &ld2, &delta);
                     if (have) {
                         S4 Le;
-                        if (lt == B200PT_LIGHT_SPOT) Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * (lw * Lr.scale) / ld2;
+                        if (is_env) Le = Le_env;
+                        else if (lt == B200PT_LIGHT_SPOT) Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * (lw * Lr.scale) / ld2;
                         else Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * Lr.scale;
                         if (is_positive(Le) && wo_l.z != 0.f) {
                             const V3 wi_l = bsdf.frame.to_local(ls.wi);
@@ -1750,6 +1855,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     wf.scene_radius = r->scene_radius;
     wf.has_mix = r->has_mix ? 1 : 0;
     wf.tex = r->tex;
+    wf.env = r->env;
     wf.media = r->d_media;
     wf.tri_medium = r->d_tri_medium;
     wf.has_media = r->n_media > 0 ? 1 : 0;
@@ -1758,7 +1864,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     // with spheres the per-ray start-up is longer and waiting for half a warp pays (C1: 62.0 -> 58.5 ms together with the
     // sphere phase)
     wf.refill_min = getenv("B200PT_WF_REFILL") ? atoi(getenv("B200PT_WF_REFILL")) : (s->n_spheres > 0 ? 16 : 4);
-    const bool ext_shade = wf.has_media || r->tex.tex != nullptr;
+    const bool ext_shade = wf.has_media || r->tex.tex != nullptr || r->env.light >= 0;
     int n_shade_kernels = 0;
     for (int m = 0; m < WF_NMAT; m++) n_shade_kernels += r->has_mat[m] ? 1 : 0;
     wf.n_lights = r->n_lights;
@@ -1806,8 +1912,13 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
             k_pass_begin<<<1, 1, 0, st>>>(wf);
             if ((rc = launch_trace_wf(s, wf, false))) return rc;
             if (wf.has_media) k_volume<<<grid, VOL_BLOCK, 0, st>>>(wf);
-            if (wf.has_media) k_logic<true><<<grid, WF_BLOCK, 0, st>>>(wf);
-            else k_logic<false><<<grid, WF_BLOCK, 0, st>>>(wf);
+            if (r->env.light >= 0) {
+                if (wf.has_media) k_logic<true, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else k_logic<false, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+            } else {
+                if (wf.has_media) k_logic<true, false><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else k_logic<false, false><<<grid, WF_BLOCK, 0, st>>>(wf);
+            }
             k_generate<<<grid, WF_BLOCK, 0, st>>>(wf);
             k_after_generate<<<1, 1, 0, st>>>(wf);
             // one shade kernel per material type PRESENT in the scene (a type without materials has no queue)

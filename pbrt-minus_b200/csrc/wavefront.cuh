@@ -13,6 +13,7 @@
 #include "light.cuh"
 #include "spectrum.cuh"
 #include "texture.cuh"
+#include "envmap.cuh"
 
 namespace b200pt {
 
@@ -119,6 +120,7 @@ struct WF {
     const uint32_t *tri_medium;
     int32_t has_media, camera_medium;
     TexTables tex;           // spectrum / float textures (all null when the scene has none)
+    EnvMap env;              // the image infinite light (env.light < 0: none)
     SpectrumTable spectra;
     const MatRec *materials;
     const LightRec *lights;

@@ -705,8 +705,17 @@ class Scene:
                 sc = F32(sc * F32(ev))
             rec.update({"type": 1, "spectrum": L, "scale": float(sc), "v": [float(x) for x in final.m[:3, 2]]})
         elif kind == "infinite":        # lights/uniform_infinite_light.cu:7-32
-            if "filename" in p:
-                raise SceneError("LightSource 'infinite' with an image map is outside the hot path (SURVEY.md 8f)")
+            if "filename" in p:         # lights/image_infinite_light.cu:62-75 (base/light.cu:30-36)
+                if not os.environ.get("B200PT_ENVMAP"):
+                    raise SceneError("LightSource 'infinite' with an image map: built, parity not yet verified (set B200PT_ENVMAP=1)")
+                img = self.load_image(os.path.join(scene_dir, p_str(p, "filename", "")))
+                d65 = self.spec_piecewise(("illuminant",), *spectral.illuminant_d65()[:2])
+                sc = F32(sc / self.photometric(d65))
+                m, inv = render_from_light.m, render_from_light.inv
+                rec.update({"type": 4, "spectrum": -1, "scale": float(sc), "image": img,
+                            "lfr": [float(x) for x in inv[:3, :3].reshape(-1)], "rfl": [float(x) for x in m[:3, :3].reshape(-1)]})
+                self.lights.append(rec)
+                return
             L = illum("L")
             sc = F32(sc / self.photometric(L))
             ev = p_float(p, "illuminance", -1.0)
@@ -846,6 +855,9 @@ class Scene:
                 lights[i].v[:] = l["v"]
                 lights[i].light_from_render[:] = l["lfr"]
                 lights[i].cos_falloff_start, lights[i].cos_falloff_end = l["cs"], l["ce"]
+                if lights[i].type == 4:
+                    lights[i].image = l["image"]
+                    lights[i].render_from_light[:] = l["rfl"]
         d.n_lights, d.lights = len(self.lights), lights
         keep += [sph, spec, mats, lights]
         if self.media:
@@ -856,6 +868,17 @@ class Scene:
             d.n_media, d.media = len(self.media), med
             d.tri_medium = tmed.ctypes.data_as(api.C.POINTER(api.C.c_uint32))
             keep += [med, tmed]
+        if self.images:
+            imgs = (api.Image * len(self.images))()
+            for i, im in enumerate(self.images):
+                imgs[i].height, imgs[i].width = im.shape[0], im.shape[1]
+                imgs[i].rgb = api._fp(im)
+            rgb_tbl, white, lam01 = spectral._fit_tables()
+            fit = np.ascontiguousarray(np.concatenate([np.asarray(rgb_tbl, np.float64).ravel(), np.asarray(white, np.float64).ravel(),
+                                                       np.asarray(lam01, np.float64).ravel()]))
+            d.n_images, d.images = len(self.images), imgs
+            d.rgb2spec_fit = fit.ctypes.data_as(api.C.POINTER(api.C.c_double))
+            keep += [imgs, fit]
         if self.textures:
             tex = (api.Texture * len(self.textures))()
             for i, t in enumerate(self.textures):
@@ -864,17 +887,6 @@ class Scene:
                 tex[i].map[:] = t["map"]
             d.n_textures, d.textures = len(self.textures), tex
             keep.append(tex)
-            if self.images:
-                imgs = (api.Image * len(self.images))()
-                for i, im in enumerate(self.images):
-                    imgs[i].height, imgs[i].width = im.shape[0], im.shape[1]
-                    imgs[i].rgb = api._fp(im)
-                rgb_tbl, white, lam01 = spectral._fit_tables()
-                fit = np.ascontiguousarray(np.concatenate([np.asarray(rgb_tbl, np.float64).ravel(), np.asarray(white, np.float64).ravel(),
-                                                           np.asarray(lam01, np.float64).ravel()]))
-                d.n_images, d.images = len(self.images), imgs
-                d.rgb2spec_fit = fit.ctypes.data_as(api.C.POINTER(api.C.c_double))
-                keep += [imgs, fit]
         if self.camera is not None:
             cam = api.Camera()
             cam.medium = self.camera_medium
