@@ -706,8 +706,6 @@ class Scene:
             rec.update({"type": 1, "spectrum": L, "scale": float(sc), "v": [float(x) for x in final.m[:3, 2]]})
         elif kind == "infinite":        # lights/uniform_infinite_light.cu:7-32
             if "filename" in p:         # lights/image_infinite_light.cu:62-75 (base/light.cu:30-36)
-                if not os.environ.get("B200PT_ENVMAP"):
-                    raise SceneError("LightSource 'infinite' with an image map: built, parity not yet verified (set B200PT_ENVMAP=1)")
                 img = self.load_image(os.path.join(scene_dir, p_str(p, "filename", "")))
                 d65 = self.spec_piecewise(("illuminant",), *spectral.illuminant_d65()[:2])
                 sc = F32(sc / self.photometric(d65))

@@ -163,6 +163,17 @@ def test_textures_match_reference(b200pt, tmp_path):
     check_against_golden(b200pt, tmp_path, "textures_96x64_1024spp")
 
 
+def test_image_infinite_light_matches_reference(b200pt, tmp_path):
+    """LightSource "infinite" with an image (lights/image_infinite_light.cu): equal-area octahedral map under a
+    rotated light transform, importance sampling through the reference's Distribution2D (an alias table over the column sums
+    and one per column, a sample = a whole pixel), bilinear lookups with the octahedral wrap for escaping rays (MIS against
+    pdf_li), every texel an RGBIlluminantSpectrum through the device-fitted RGB-to-spectrum table, the light's power integrated
+    on the device for the light sampler it shares with an area light.  The test image has pairwise distinct luminances and
+    column sums: the alias tables are then independent of sort tie order.  Measured relMSE 6.3e-12 (64 spp) / 2.1e-9 (1024 spp)."""
+    check_against_golden(b200pt, tmp_path, "envmap_96x64_64spp")
+    check_against_golden(b200pt, tmp_path, "envmap_96x64_1024spp")
+
+
 def test_mix_material_statistical_gate(b200pt, tmp_path):
     """Material "mix" (materials/mix_material.cu, base/interaction.cu:41-64): the material of a hit is chosen by
     hash_float(pi, wo) < amount -- a hash of the BITS of the hit interval and direction, so (as for the coated materials) the

@@ -49,6 +49,9 @@ CASES = [
     # image / procedural textures (needs tests/scenes/textures/ beside the scene copy)
     ("textures_96x64_64spp", "textures.pbrt", None, 64, None, None),
     ("textures_96x64_1024spp", "textures.pbrt", None, 1024, None, None),
+    # image infinite light (octahedral environment map)
+    ("envmap_96x64_64spp", "envmap.pbrt", None, 64, None, None),
+    ("envmap_96x64_1024spp", "envmap.pbrt", None, 1024, None, None),
     # C4 in miniature (workloads.procedural_scene, seed 7): many lights -> statistical gate only
     ("c4tiny_96x54_1024spp", "@c4tiny", None, 1024, None, None),
 ]
