@@ -740,6 +740,7 @@ __global__ void k_pass_begin(WF wf) {
     WFCounters *c = wf.c;
     for (int m = 0; m < WF_NMAT; m++) c->n_mat[m] = 0;
     c->n_shadow = 0;
+    c->n_vol = 0;
     c->ticket_closest = 0;
     c->ticket_shadow = 0;
 }
@@ -1147,37 +1148,64 @@ __device__ __forceinline__ S4 volume_transmittance(const WF &wf, V3 p0, int medi
 // ray_cast clears in_volume for all of them (:361), rays inside a medium then either pass through to their hit
 // (multi_transmittance_pdf *= exp(-sigma_t t_max)) or scatter: the origin moves to the scattering point, direct light is
 // gathered THROUGH interfaces with the transmittance walk above, and a new direction is drawn from the phase function.
+// Two launches: k_volume<0> visits every traced slot, samples the free-flight distance and either lets the path pass or
+// queues it; k_volume<1> runs the scattering work (the NEE transmittance walk is a per-thread traversal) densely over that
+// queue instead of in whichever lanes of a warp happened to scatter.
+template <int PHASE>
 __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
-    __shared__ uint2 s_stack[SM_STACK * VOL_BLOCK];
-    const unsigned n = (unsigned)wf.pool_size;
+    __shared__ uint2 s_stack[PHASE == 1 ? SM_STACK * VOL_BLOCK : 1];
+    const unsigned n = PHASE == 0 ? (unsigned)wf.pool_size : wf.c->n_vol;
     const unsigned stride = gridDim.x * blockDim.x;
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        if (wf.pool.state[i] != ST_RAY) continue;
-        const int slot = (int)i;
-        int4 ids = wf.pool.ids[slot];
-        const bool was_in_volume = (ids.w & PF_IN_VOLUME) != 0;
-        ids.w &= ~PF_IN_VOLUME;
-        float4 vol = wf.pool.vol[slot];
-        const int medium = __float_as_int(vol.y);
-        const float4 ro4 = wf.pool.ray_o[slot];
-        if (medium < 0 || ro4.w < 0.f) {
-            if (was_in_volume) wf.pool.ids[slot] = ids;
+    const unsigned n_round = (n + 31u) & ~31u;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        if (PHASE == 0) {
+            bool scatter = false;
+            if (i < n && wf.pool.state[i] == ST_RAY) {
+                const int slot = (int)i;
+                int4 ids = wf.pool.ids[slot];
+                const bool was_in_volume = (ids.w & PF_IN_VOLUME) != 0;
+                ids.w &= ~PF_IN_VOLUME;
+                float4 vol = wf.pool.vol[slot];
+                const int medium = __float_as_int(vol.y);
+                const float4 ro4 = wf.pool.ray_o[slot];
+                if (medium < 0 || ro4.w < 0.f) {
+                    if (was_in_volume) wf.pool.ids[slot] = ids;
+                } else {
+                    const S4 lambda = wf.pool.lambda[slot];
+                    const S4 sigma_t = medium_sigma_t(wf, medium, lambda);
+                    const float4 hit = wf.pool.hit[slot];
+                    const float t_max = __float_as_int(hit.x) >= 0 ? hit.y : kInf;
+                    Sampler s = load_sampler(wf, slot, ids);
+                    const float t = -logf(1.f - s.get_1d()) / average(sigma_t); // sample_exponential (util/sampling.h:67-69)
+                    if (t >= t_max) {
+                        // pass through the medium
+                        wf.pool.mtp[slot] = wf.pool.mtp[slot] * exp_s4(sigma_t * (-t_max));
+                    } else {
+                        scatter = true;
+                        vol.z = t;
+                        wf.pool.vol[slot] = vol;
+                    }
+                    ids.z = s.dimension;
+                    wf.pool.ids[slot] = ids;
+                    wf.pool.rng[slot] = s.state;
+                }
+            }
+            queue_push(&wf.c->n_vol, wf.q.vol, (int)i, scatter);
             continue;
         }
-        const float4 rd4 = wf.pool.ray_d[slot];
-        const V3 ro = v3(ro4), rd = v3(rd4);
+        if (i >= n) continue;
+        const int slot = wf.q.vol[i];
+        int4 ids = wf.pool.ids[slot];
+        float4 vol = wf.pool.vol[slot];
+        const int medium = __float_as_int(vol.y);
+        const float t = vol.z;
+        const V3 ro = v3(wf.pool.ray_o[slot]), rd = v3(wf.pool.ray_d[slot]);
         const S4 lambda = wf.pool.lambda[slot];
         const MediumRec M = wf.media[medium];
         const S4 sigma_s = medium_sigma(wf.spectra, M.sigma_s, M.scale, lambda);
         const S4 sigma_t = medium_sigma(wf.spectra, M.sigma_a, M.scale, lambda) + sigma_s;
-        const float4 hit = wf.pool.hit[slot];
-        const float t_max = __float_as_int(hit.x) >= 0 ? hit.y : kInf;
         Sampler s = load_sampler(wf, slot, ids);
-        const float t = -logf(1.f - s.get_1d()) / average(sigma_t); // sample_exponential (util/sampling.h:67-69)
-        if (t >= t_max) {
-            // pass through the medium
-            wf.pool.mtp[slot] = wf.pool.mtp[slot] * exp_s4(sigma_t * (-t_max));
-        } else {
+        {
             const V3 o = ro + rd * t;
             S4 beta = wf.pool.beta[slot] * (sigma_s / sigma_t);
             // -- sample_Ld_volume(medium_interaction, nullptr, ..): ctx = the bare point
@@ -1727,9 +1755,11 @@ static int ensure_pool(b200pt_scene *s, int pool_size) {
     for (float4 **l : lanes)
         if ((rc = pool_alloc(r, l, n))) return rc;
     P.mtp = P.vol = nullptr;
-    if (r->n_media > 0) { // two more lanes, media scenes only
+    r->q.vol = nullptr;
+    if (r->n_media > 0) { // two more lanes and the scatter queue, media scenes only
         if ((rc = pool_alloc(r, &P.mtp, n))) return rc;
         if ((rc = pool_alloc(r, &P.vol, n))) return rc;
+        if ((rc = pool_alloc(r, &r->q.vol, n))) return rc;
     }
     if ((rc = pool_alloc(r, &P.rng, n))) return rc;
     if ((rc = pool_alloc(r, &P.ids, n))) return rc;
@@ -1911,7 +1941,10 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
         for (int b = 0; b < batch; b++) {
             k_pass_begin<<<1, 1, 0, st>>>(wf);
             if ((rc = launch_trace_wf(s, wf, false))) return rc;
-            if (wf.has_media) k_volume<<<grid, VOL_BLOCK, 0, st>>>(wf);
+            if (wf.has_media) {
+                k_volume<0><<<grid, VOL_BLOCK, 0, st>>>(wf);
+                k_volume<1><<<grid, VOL_BLOCK, 0, st>>>(wf);
+            }
             if (r->env.light >= 0) {
                 if (wf.has_media) k_logic<true, true><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_logic<false, true><<<grid, WF_BLOCK, 0, st>>>(wf);
@@ -1949,7 +1982,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
             if ((rc = launch_trace_wf(s, wf, true))) return rc;
             k_pass_end<<<1, 1, 0, st>>>(wf);
             passes++;
-            launches += 7 + n_shade_kernels + (wf.has_media ? 1 : 0);
+            launches += 7 + n_shade_kernels + (wf.has_media ? 2 : 0);
         }
         CU_TRY(cudaGetLastError());
         const int cur = int(k & 1);

@@ -78,7 +78,7 @@ struct PathPool {
     float4 *ctx2;   //                          ns.xyz, err.z
     float4 *misc;   // filter_weight, prev_direction_pdf, -, -
     float4 *mtp;    // media scenes only: multi_transmittance_pdf (integrators/wavefront_path.h:37)
-    float4 *vol;    // media scenes only: depth (a FLOAT: +0.3 per interface bounce), medium id of the ray (int bits), -, -
+    float4 *vol;    // media scenes only: depth (a FLOAT: +0.3 per interface bounce), medium id of the ray (int bits), free-flight distance of a queued scatter, -
     uint64_t *rng;  // PCG32 state (inc is re-derived from the pixel index)
     int4 *ids;      // pixel, sample, sampler dimension, flags
     uint8_t *state; // ST_*
@@ -91,11 +91,13 @@ struct WFCounters {
     unsigned ticket_closest;
     unsigned long long next_path, finished, rays_closest, rays_shadow;
     unsigned stack_overflow, ticket_shadow;
+    unsigned n_vol; // media: paths that scatter this pass (k_volume<0> -> k_volume<1>)
 };
 
 struct WFQueues {
     int32_t *mat[WF_NMAT];
     int32_t *free_slots;
+    int32_t *vol; // media scenes only: slots that scatter inside a medium this pass
     // shadow rays: compact SoA by queue position
     float4 *sh_o, *sh_d, *sh_contrib;
     int32_t *sh_slot;
