@@ -265,6 +265,20 @@ int b200pt_bvh_debug_sorted(b200pt_scene *scene, int32_t *prim_order_out, uint64
  * t_out[n] (inf on miss), b1b2_out[n*2] barycentrics b1,b2 of the hit. */
 int b200pt_trace(b200pt_scene *scene, const float *o_xyz, const float *d_xyz, const float *tmax,
                  int64_t n, int any_hit, int32_t *prim_out, float *t_out, float *b1b2_out);
+/* Several ray sets in ONE call (an integrator's closest-hit + shadow batches of a bounce): the sets share one
+ * copy-in / traverse / copy-out pipeline, so the copy-in of a set overlaps the traversal and the copy-out of the
+ * one before it and the pipeline fills and drains once per call instead of once per set.  Same per-set meaning as
+ * b200pt_trace; outputs passed as NULL are not copied back (an any-hit caller usually wants prim_out only). */
+typedef struct {
+    const float *o_xyz, *d_xyz, *tmax; /* [n*3], [n*3], [n] */
+    int64_t n;
+    int32_t any_hit;
+    int32_t reserved;
+    int32_t *prim_out; /* [n] or NULL */
+    float *t_out;      /* [n] or NULL */
+    float *b1b2_out;   /* [n*2] or NULL */
+} b200pt_ray_set;
+int b200pt_trace_batch(b200pt_scene *scene, const b200pt_ray_set *sets, int n_sets);
 /* Device form: rays_dev = n x {ox,oy,oz,tmax, dx,dy,dz,0} (32 B), hits_dev = n x
  * {prim (int bits), t, b1, b2} (16 B).  Asynchronous on the scene's stream unless sync != 0. */
 int b200pt_trace_device(b200pt_scene *scene, const void *rays_dev, int64_t n, int any_hit,
@@ -273,6 +287,10 @@ int b200pt_trace_device(b200pt_scene *scene, const void *rays_dev, int64_t n, in
  * out[0] = BVH8 nodes fetched, out[1] = triangles tested, out[2] = rays. */
 int b200pt_trace_set_counting(b200pt_scene *scene, int enable);
 int b200pt_trace_counters(b200pt_scene *scene, int64_t out[3]);
+/* Scheduling knobs of the traversal kernels (they change speed, never results): key 0 = idle lanes before a warp
+ * of k_trace refills (1/4/8/16), 1 = triangle tests per triangle phase (1..3), 2 = resident CTAs per SM cap
+ * (0 = occupancy limit), 3 / 4 = the same two knobs for the wavefront integrator's trace kernels (0 = default). */
+int b200pt_trace_tune(b200pt_scene *scene, int key, int value);
 void *b200pt_scene_stream(b200pt_scene *scene); /* cudaStream_t the scene launches on */
 int b200pt_scene_sync(b200pt_scene *scene);
 

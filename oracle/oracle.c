@@ -540,3 +540,309 @@ ORACLE_API void oracle_sampler_stream(int kind, int spp, const int32_t *pixel, c
         }
     }
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Host BVH for the oracle: the reference's traversal loop on the CPU.
+ *
+ * The reference's HLBVH cannot run on the host (every array is cudaMallocManaged and the build
+ * is kernels), so the oracle builds its OWN binary tree -- Morton-ordered triangles (the codes
+ * of util/math.h:183-208 widened to 21 bits per axis), split where the highest differing code
+ * bit changes, leaves of <= 4 triangles, boxes refitted bottom-up -- and walks it with the
+ * reference's loop: pop, slab test against the current best t (Bounds3::fast_intersect,
+ * euclidean_space/bounds3.h:155-203, incl. the 1 + 2*gamma(3) widening evaluated in double),
+ * leaf: every primitive against best_t in stored order, interior: push far then near
+ * (accelerator/hlbvh.cu:459-516; any hit: :407-456).  Hit ids are argmin t under the reference's
+ * watertight triangle test, whatever the tree; exact ties go to the last visited candidate, so a
+ * checker comparing two trees must treat rays with |dt| of a few ulp as near-ties.
+ *
+ * Used (a) as the checker at full workload sizes, where brute force does not finish, and (b) as
+ * bench.py's cpu_baseline: a real multi-threaded CPU traversal of the same rays.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+    float lo[3], hi[3];
+    int32_t left;  /* interior: index of the left child, right = left + 1; leaf: first primitive slot */
+    int32_t count; /* 0 = interior, else number of primitives */
+    int32_t axis;  /* interior: axis of the split bit (child order by ray direction sign) */
+} obvh_node;
+
+typedef struct {
+    const float *P;
+    const int32_t *idx;
+    int64_t nt;
+    int32_t *order; /* triangle ids in Morton order */
+    obvh_node *nodes;
+    int64_t n_nodes;
+} obvh;
+
+static inline uint64_t spread21(uint64_t x) {
+    x &= 0x1fffffull;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+typedef struct {
+    uint64_t key;
+    int32_t prim;
+} obvh_key;
+
+static void obvh_sort(obvh_key *a, obvh_key *tmp, int64_t n) { /* LSD radix sort, 8 x 8-bit digits */
+    for (int pass = 0; pass < 8; pass++) {
+        int64_t count[257];
+        memset(count, 0, sizeof count);
+        const int sh = 8 * pass;
+        for (int64_t i = 0; i < n; i++) count[((a[i].key >> sh) & 0xff) + 1]++;
+        for (int k = 0; k < 256; k++) count[k + 1] += count[k];
+        for (int64_t i = 0; i < n; i++) tmp[count[(a[i].key >> sh) & 0xff]++] = a[i];
+        obvh_key *t = a;
+        a = tmp;
+        tmp = t;
+    }
+}
+
+static inline void obvh_tri_box(const obvh *b, int32_t prim, float *lo, float *hi) {
+    for (int k = 0; k < 3; k++) {
+        lo[k] = INFINITY;
+        hi[k] = -INFINITY;
+    }
+    for (int v = 0; v < 3; v++) {
+        const float *p = b->P + 3 * (int64_t)b->idx[3 * (int64_t)prim + v];
+        for (int k = 0; k < 3; k++) {
+            if (p[k] < lo[k]) lo[k] = p[k];
+            if (p[k] > hi[k]) hi[k] = p[k];
+        }
+    }
+}
+
+/* builds the subtree over sorted slots [first, last] into node `me`; children are allocated as an adjacent pair */
+static void obvh_build_range(obvh *b, const obvh_key *keys, int64_t root_first, int64_t root_last) {
+    typedef struct {
+        int64_t first, last;
+        int32_t node;
+        int bit;
+    } item;
+    int64_t cap = 256, sp = 0;
+    item *stack = (item *)malloc(cap * sizeof(item));
+    stack[sp++] = (item){root_first, root_last, 0, 62};
+    while (sp > 0) {
+        item it = stack[--sp];
+        obvh_node *nd = &b->nodes[it.node];
+        const int64_t n = it.last - it.first + 1;
+        int64_t split = -1;
+        int bit = it.bit;
+        if (n > 4) {
+            /* highest bit at or below `bit` in which the first and last key differ */
+            const uint64_t diff = keys[it.first].key ^ keys[it.last].key;
+            while (bit >= 0 && !((diff >> bit) & 1)) bit--;
+            if (bit >= 0) { /* first slot whose key has the bit set (keys are sorted) */
+                int64_t lo = it.first, hi = it.last;
+                while (lo < hi) {
+                    const int64_t mid = (lo + hi) / 2;
+                    if ((keys[mid].key >> bit) & 1) hi = mid;
+                    else lo = mid + 1;
+                }
+                split = lo;
+            } else if (n > 16) { /* identical codes: halve */
+                split = it.first + n / 2;
+                bit = 0;
+            }
+        }
+        if (split < 0) {
+            nd->left = (int32_t)it.first;
+            nd->count = (int32_t)n;
+            nd->axis = 0;
+            continue;
+        }
+        const int32_t l = (int32_t)b->n_nodes;
+        b->n_nodes += 2;
+        nd->left = l;
+        nd->count = 0;
+        nd->axis = bit % 3; /* x lowest in each 3-bit group */
+        if (sp + 2 > cap) {
+            cap *= 2;
+            stack = (item *)realloc(stack, cap * sizeof(item));
+        }
+        stack[sp++] = (item){it.first, split - 1, l, bit - 1};
+        stack[sp++] = (item){split, it.last, l + 1, bit - 1};
+    }
+    free(stack);
+}
+
+ORACLE_API void oracle_bvh_free(void *h) {
+    obvh *b = (obvh *)h;
+    if (!b) return;
+    free(b->order);
+    free(b->nodes);
+    free(b);
+}
+
+ORACLE_API void *oracle_bvh_build(const float *P, const int32_t *idx, int64_t nt) {
+    obvh *b = (obvh *)calloc(1, sizeof(obvh));
+    b->P = P;
+    b->idx = idx;
+    b->nt = nt;
+    if (nt <= 0) return b;
+    float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    float *cen = (float *)malloc(sizeof(float) * 3 * nt);
+    for (int64_t t = 0; t < nt; t++) {
+        float lo[3], hi[3];
+        obvh_tri_box(b, (int32_t)t, lo, hi);
+        for (int k = 0; k < 3; k++) {
+            const float c = 0.5f * (lo[k] + hi[k]);
+            cen[3 * t + k] = c;
+            if (c < clo[k]) clo[k] = c;
+            if (c > chi[k]) chi[k] = c;
+        }
+    }
+    obvh_key *keys = (obvh_key *)malloc(sizeof(obvh_key) * nt), *tmp = (obvh_key *)malloc(sizeof(obvh_key) * nt);
+    for (int64_t t = 0; t < nt; t++) {
+        uint64_t code = 0;
+        for (int k = 0; k < 3; k++) {
+            const double ext = (double)chi[k] - (double)clo[k];
+            double f = ext > 0 ? ((double)cen[3 * t + k] - (double)clo[k]) / ext : 0.0;
+            int64_t q = (int64_t)(f * 2097152.0);
+            if (q > 2097151) q = 2097151;
+            if (q < 0) q = 0;
+            code |= spread21((uint64_t)q) << k;
+        }
+        keys[t].key = code;
+        keys[t].prim = (int32_t)t;
+    }
+    free(cen);
+    obvh_sort(keys, tmp, nt); /* 8 passes: the sorted data ends up back in `keys` */
+    free(tmp);
+    b->nodes = (obvh_node *)malloc(sizeof(obvh_node) * (size_t)(2 * nt + 1));
+    b->n_nodes = 1;
+    obvh_build_range(b, keys, 0, nt - 1);
+    b->order = (int32_t *)malloc(sizeof(int32_t) * nt);
+    for (int64_t t = 0; t < nt; t++) b->order[t] = keys[t].prim;
+    free(keys);
+    /* refit: children always have larger indices than their parent, so one backward sweep does it */
+    for (int64_t i = b->n_nodes - 1; i >= 0; i--) {
+        obvh_node *nd = &b->nodes[i];
+        if (nd->count > 0) {
+            for (int k = 0; k < 3; k++) {
+                nd->lo[k] = INFINITY;
+                nd->hi[k] = -INFINITY;
+            }
+            for (int32_t s = 0; s < nd->count; s++) {
+                float lo[3], hi[3];
+                obvh_tri_box(b, b->order[nd->left + s], lo, hi);
+                for (int k = 0; k < 3; k++) {
+                    if (lo[k] < nd->lo[k]) nd->lo[k] = lo[k];
+                    if (hi[k] > nd->hi[k]) nd->hi[k] = hi[k];
+                }
+            }
+        } else {
+            const obvh_node *l = &b->nodes[nd->left], *r = &b->nodes[nd->left + 1];
+            for (int k = 0; k < 3; k++) {
+                nd->lo[k] = l->lo[k] < r->lo[k] ? l->lo[k] : r->lo[k];
+                nd->hi[k] = l->hi[k] > r->hi[k] ? l->hi[k] : r->hi[k];
+            }
+        }
+    }
+    return b;
+}
+
+/* euclidean_space/bounds3.h:155-203 */
+static inline int obvh_slab(const obvh_node *nd, const float *o, float ray_t_max, const float *inv, const int *neg) {
+    const double widen = 1.0 + 2.0 * (double)gamma_f(3);
+    const float *bmin = nd->lo, *bmax = nd->hi;
+    float t_min = ((neg[0] ? bmax[0] : bmin[0]) - o[0]) * inv[0];
+    float t_max = ((neg[0] ? bmin[0] : bmax[0]) - o[0]) * inv[0];
+    float ty_min = ((neg[1] ? bmax[1] : bmin[1]) - o[1]) * inv[1];
+    float ty_max = ((neg[1] ? bmin[1] : bmax[1]) - o[1]) * inv[1];
+    t_max = (float)((double)t_max * widen);
+    ty_max = (float)((double)ty_max * widen);
+    if (t_min > ty_max || ty_min > t_max) return 0;
+    if (ty_min > t_min) t_min = ty_min;
+    if (ty_max < t_max) t_max = ty_max;
+    float tz_min = ((neg[2] ? bmax[2] : bmin[2]) - o[2]) * inv[2];
+    float tz_max = ((neg[2] ? bmin[2] : bmax[2]) - o[2]) * inv[2];
+    tz_max = (float)((double)tz_max * widen);
+    if (t_min > tz_max || tz_min > t_max) return 0;
+    if (tz_min > t_min) t_min = tz_min;
+    if (tz_max < t_max) t_max = tz_max;
+    return t_min < ray_t_max && t_max > 0.0f;
+}
+
+typedef struct {
+    const obvh *b;
+    const float *ro, *rd, *tmax;
+    int32_t *prim;
+    float *t_out, *b12;
+    int32_t *occluded;
+} obvh_ctx;
+
+static void obvh_ray(const obvh_ctx *c, int64_t r, int any) {
+    const obvh *b = c->b;
+    const float *o = c->ro + 3 * r, *d = c->rd + 3 * r;
+    float best_t = c->tmax[r], bb1 = 0, bb2 = 0;
+    int32_t best = -1;
+    if (b->nt > 0) {
+        /* accelerator/hlbvh.cu:468-474: 1.0 / d in double, rounded to float */
+        const float inv[3] = {(float)(1.0 / (double)d[0]), (float)(1.0 / (double)d[1]), (float)(1.0 / (double)d[2])};
+        const int neg[3] = {inv[0] < 0.0f, inv[1] < 0.0f, inv[2] < 0.0f};
+        int32_t stack[192];
+        int sp = 0;
+        stack[sp++] = 0;
+        while (sp > 0) {
+            const obvh_node *nd = &b->nodes[stack[--sp]];
+            if (!obvh_slab(nd, o, best_t, inv, neg)) continue;
+            if (nd->count > 0) {
+                for (int32_t s = 0; s < nd->count; s++) {
+                    const int32_t k = b->order[nd->left + s];
+                    float h[4];
+                    if (!oracle_intersect_triangle(o, d, best_t, b->P + 3 * (int64_t)b->idx[3 * (int64_t)k],
+                                                   b->P + 3 * (int64_t)b->idx[3 * (int64_t)k + 1],
+                                                   b->P + 3 * (int64_t)b->idx[3 * (int64_t)k + 2], h))
+                        continue;
+                    best_t = h[3];
+                    best = k;
+                    bb1 = h[1];
+                    bb2 = h[2];
+                    if (any) {
+                        sp = 0;
+                        break;
+                    }
+                }
+                continue;
+            }
+            if (sp + 2 > 192) continue; /* cannot happen: depth <= 63 + log2(16) */
+            if (neg[nd->axis]) {
+                stack[sp++] = nd->left;
+                stack[sp++] = nd->left + 1;
+            } else {
+                stack[sp++] = nd->left + 1;
+                stack[sp++] = nd->left;
+            }
+        }
+    }
+    if (any) {
+        c->occluded[r] = best >= 0;
+    } else {
+        c->prim[r] = best;
+        c->t_out[r] = best >= 0 ? best_t : INFINITY;
+        c->b12[2 * r] = bb1;
+        c->b12[2 * r + 1] = bb2;
+    }
+}
+static void obvh_closest_body(int64_t r, void *vc) { obvh_ray((const obvh_ctx *)vc, r, 0); }
+static void obvh_any_body(int64_t r, void *vc) { obvh_ray((const obvh_ctx *)vc, r, 1); }
+
+ORACLE_API void oracle_bvh_closest_hit(void *h, const float *ro, const float *rd, const float *tmax, int64_t nrays,
+                                       int32_t *prim, float *t_out, float *b12) {
+    obvh_ctx c = {(const obvh *)h, ro, rd, tmax, prim, t_out, b12, NULL};
+    parallel_for(nrays, 256, obvh_closest_body, &c);
+}
+
+ORACLE_API void oracle_bvh_any_hit(void *h, const float *ro, const float *rd, const float *tmax, int64_t nrays,
+                                   int32_t *occluded) {
+    obvh_ctx c = {(const obvh *)h, ro, rd, tmax, NULL, NULL, NULL, occluded};
+    parallel_for(nrays, 256, obvh_any_body, &c);
+}
+
+ORACLE_API int64_t oracle_bvh_node_count(void *h) { return h ? ((const obvh *)h)->n_nodes : 0; }

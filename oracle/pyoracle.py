@@ -49,6 +49,16 @@ def lib():
         L.oracle_permutation_element.restype = C.c_int32
         L.oracle_sampler_stream.argtypes = [C.c_int, C.c_int, ip, ip, C.c_int, ip, C.c_int, fp]
         L.oracle_sampler_stream.restype = None
+        L.oracle_bvh_build.argtypes = [fp, ip, i64]
+        L.oracle_bvh_build.restype = C.c_void_p
+        L.oracle_bvh_free.argtypes = [C.c_void_p]
+        L.oracle_bvh_free.restype = None
+        L.oracle_bvh_closest_hit.argtypes = [C.c_void_p, fp, fp, fp, i64, ip, fp, fp]
+        L.oracle_bvh_closest_hit.restype = None
+        L.oracle_bvh_any_hit.argtypes = [C.c_void_p, fp, fp, fp, i64, ip]
+        L.oracle_bvh_any_hit.restype = None
+        L.oracle_bvh_node_count.argtypes = [C.c_void_p]
+        L.oracle_bvh_node_count.restype = i64
         L.oracle_set_threads.argtypes = [C.c_int]
         L.oracle_get_threads.restype = C.c_int
         _lib = L
@@ -115,3 +125,65 @@ def sampler_stream(kind, spp, pixel, sample, pattern):
     out = np.empty((len(pixel), per), np.float32)
     lib().oracle_sampler_stream(kind, spp, _ip(pixel), _ip(sample), len(pixel), _ip(pattern), len(pattern), _fp(out))
     return out
+
+
+class HostBVH:
+    """The oracle's own host BVH (oracle.c: Morton-split binary tree walked with the reference's loop and
+    predicates).  Same answers as the brute-force functions above (argmin t; exact ties may resolve to a different
+    candidate), at sizes where brute force does not finish."""
+
+    def __init__(self, P, idx):
+        self.P, self.idx = _f(P), _i(idx)          # the C side keeps pointers into these
+        self.h = lib().oracle_bvh_build(_fp(self.P), _ip(self.idx), self.idx.reshape(-1, 3).shape[0])
+
+    def closest_hit(self, o, d, tmax):
+        o, d = _f(o), _f(d)
+        n = o.reshape(-1, 3).shape[0]
+        tmax = _f(np.broadcast_to(np.asarray(tmax, dtype=np.float32), (n,)))
+        prim = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        b = np.empty((n, 2), np.float32)
+        lib().oracle_bvh_closest_hit(self.h, _fp(o), _fp(d), _fp(tmax), n, _ip(prim), _fp(t), _fp(b))
+        return prim, t, b
+
+    def any_hit(self, o, d, tmax):
+        o, d = _f(o), _f(d)
+        n = o.reshape(-1, 3).shape[0]
+        tmax = _f(np.broadcast_to(np.asarray(tmax, dtype=np.float32), (n,)))
+        occ = np.empty(n, np.int32)
+        lib().oracle_bvh_any_hit(self.h, _fp(o), _fp(d), _fp(tmax), n, _ip(occ))
+        return occ.astype(bool)
+
+    def node_count(self):
+        return int(lib().oracle_bvh_node_count(self.h))
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().oracle_bvh_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def compare_closest(P, idx, o, d, tmax, prim, t, ref_prim, ref_t, ulps=4):
+    """Hit-id comparison of two closest-hit results over the same rays: returns (mismatches, near_ties).  A ray whose
+    two answers differ is a NEAR TIE, not a mismatch, when the other side's primitive is itself accepted by the
+    reference's triangle test at a t within `ulps` ulp of the checker's t (visit order decides those)."""
+    prim, ref_prim = np.asarray(prim), np.asarray(ref_prim)
+    diff = np.nonzero(prim != ref_prim)[0]
+    if diff.size == 0:
+        return 0, 0
+    o, d = _f(o).reshape(-1, 3), _f(d).reshape(-1, 3)
+    tmax = np.broadcast_to(np.asarray(tmax, dtype=np.float32), (len(prim),))
+    near = 0
+    cand = diff[(prim[diff] >= 0) & (ref_prim[diff] >= 0)]
+    if cand.size:
+        ok, bt = intersect_pairs(P, idx, prim[cand], o[cand], d[cand], tmax[cand])
+        t_mine = bt[:, 3]
+        du = np.abs(t_mine.view(np.int32).astype(np.int64) - np.asarray(ref_t)[cand].view(np.int32).astype(np.int64))
+        near = int((ok & (du <= ulps)).sum())
+    return int(diff.size - near), near

@@ -116,11 +116,18 @@ class RenderStats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class RaySet(C.Structure):
+    """b200pt_ray_set (include/b200pt.h)"""
+    _fields_ = [("o_xyz", C.POINTER(C.c_float)), ("d_xyz", C.POINTER(C.c_float)), ("tmax", C.POINTER(C.c_float)),
+                ("n", C.c_int64), ("any_hit", C.c_int32), ("reserved", C.c_int32),
+                ("prim_out", C.POINTER(C.c_int32)), ("t_out", C.POINTER(C.c_float)), ("b1b2_out", C.POINTER(C.c_float))]
+
+
 # every symbol include/b200pt.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "b200pt_abi_version", "b200pt_last_error", "b200pt_device_count",
     "b200pt_scene_create", "b200pt_scene_destroy", "b200pt_bvh_build", "b200pt_bvh_debug_sorted",
-    "b200pt_trace", "b200pt_trace_device", "b200pt_trace_set_counting", "b200pt_trace_counters",
+    "b200pt_trace", "b200pt_trace_batch", "b200pt_trace_device", "b200pt_trace_set_counting", "b200pt_trace_counters", "b200pt_trace_tune",
     "b200pt_scene_stream", "b200pt_scene_sync",
     "b200pt_device_alloc", "b200pt_device_free", "b200pt_copy_to_device", "b200pt_copy_to_host",
     "b200pt_film_create", "b200pt_film_destroy", "b200pt_film_clear", "b200pt_render", "b200pt_film_reduce",
@@ -148,9 +155,11 @@ def load_library():
     lib.b200pt_bvh_build.argtypes = [vp, C.POINTER(BuildStats)]
     lib.b200pt_bvh_debug_sorted.argtypes = [vp, ip, C.POINTER(C.c_uint64)]
     lib.b200pt_trace.argtypes = [vp, fp, fp, fp, i64, i32, ip, fp, fp]
+    lib.b200pt_trace_batch.argtypes = [vp, C.POINTER(RaySet), i32]
     lib.b200pt_trace_device.argtypes = [vp, vp, i64, i32, vp, i32]
     lib.b200pt_trace_set_counting.argtypes = [vp, i32]
     lib.b200pt_trace_counters.argtypes = [vp, C.POINTER(i64)]
+    lib.b200pt_trace_tune.argtypes = [vp, i32, i32]
     lib.b200pt_scene_stream.argtypes = [vp]
     lib.b200pt_scene_stream.restype = vp
     lib.b200pt_scene_sync.argtypes = [vp]

@@ -35,6 +35,8 @@ def _compile(src):
     r = subprocess.run([NVCC] + FLAGS + ["-c", spath, "-o", obj], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed on %s:\n%s" % (src, r.stdout))
+    with open(obj[:-2] + ".ptxas.log", "w") as f:   # registers / spills per kernel (-Xptxas -v), one log per source
+        f.write(r.stdout)
     return obj, r.stdout
 
 
@@ -44,9 +46,6 @@ def build(verbose=False):
         results = list(ex.map(_compile, _sources()))
     objs = [o for o, _ in results]
     log = "".join(l for _, l in results)
-    if log:
-        with open(os.path.join(OBJ, "ptxas.log"), "w") as f:
-            f.write(log)
     if (not os.path.exists(LIB)) or any(os.path.getmtime(o) > os.path.getmtime(LIB) for o in objs):
         r = subprocess.run([NVCC, "-shared", "-o", LIB] + objs + ["-lcudart_static", "-ldl", "-lpthread", "-lrt"],
                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)

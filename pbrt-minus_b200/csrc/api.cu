@@ -35,28 +35,6 @@ static int upload(T **dst, const T *src, size_t count, cudaStream_t st, int64_t 
     return B200PT_OK;
 }
 
-// host rays (o[n*3], d[n*3], tmax[n]) -> packed 2 x float4
-__global__ void k_pack_rays(const float *__restrict__ o, const float *__restrict__ d, const float *__restrict__ tmax,
-                            long long n, float4 *__restrict__ rays) {
-    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    rays[2 * i] = make_float4(o[3 * i], o[3 * i + 1], o[3 * i + 2], tmax[i]);
-    rays[2 * i + 1] = make_float4(d[3 * i], d[3 * i + 1], d[3 * i + 2], 0.f);
-}
-
-__global__ void k_unpack_hits(const float4 *__restrict__ hits, long long n, int32_t *__restrict__ prim,
-                              float *__restrict__ t, float *__restrict__ b12) {
-    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float4 h = hits[i];
-    if (prim) prim[i] = __float_as_int(h.x);
-    if (t) t[i] = h.y;
-    if (b12) {
-        b12[2 * i] = h.z;
-        b12[2 * i + 1] = h.w;
-    }
-}
-
 __global__ void k_probe_triangle(const float *__restrict__ o, const float *__restrict__ d, const float *__restrict__ tmax,
                                  const float *__restrict__ tri, long long n, int32_t *__restrict__ hit,
                                  float *__restrict__ bt) {
@@ -177,6 +155,7 @@ B200PT_API int b200pt_scene_create(const b200pt_scene_desc *desc, int device, b2
         set_error("b200pt_scene_create: out of device memory");
         return fail(B200PT_ERR_CUDA);
     }
+    cudaMemsetAsync(s->d_trace_counters, 0, 4 * sizeof(unsigned long long), s->stream);
     if ((rc = b200pt_upload_render_data(s, desc))) return fail(rc);
     if (cudaStreamSynchronize(s->stream) != cudaSuccess) {
         set_error("b200pt_scene_create: upload failed");
@@ -233,6 +212,9 @@ static int check_trace_status(b200pt_scene *s) {
     s->last_counts[0] = (int64_t)c[1];
     s->last_counts[1] = (int64_t)c[2];
     if (c[3]) {
+        // the overflow word is sticky on the device (any launch since the last look may have set it): reading clears it
+        CU_TRY(cudaMemsetAsync(s->d_trace_counters + 3, 0, sizeof(unsigned long long), s->stream));
+        CU_TRY(cudaStreamSynchronize(s->stream));
         set_error("b200pt_trace: traversal stack overflow (tree deeper than %d groups)", 96);
         return B200PT_ERR_STATE;
     }
@@ -252,73 +234,112 @@ B200PT_API int b200pt_trace_device(b200pt_scene *s, const void *rays_dev, int64_
     return B200PT_OK;
 }
 
+// Host-buffer traversal.  A three-stage pipeline over chunks of ALL the sets of the call: the copy-in of chunk k+1 (H2D
+// engine), the traversal of chunk k and the copy-out of chunk k-1 (D2H engine) run at the same time, so with pinned host
+// buffers a call costs about max(copy-in, traversal, copy-out) + one chunk of fill and drain, instead of their sum per set.
+// The trace kernel reads the caller's array layout and writes the caller's output layout directly (TraceHostIO): there is
+// no repacking pass.  Pageable buffers still work (the copies then block the host).  One synchronisation, at the end.
+B200PT_API int b200pt_trace_batch(b200pt_scene *s, const b200pt_ray_set *sets, int n_sets) {
+    if (!s || n_sets < 0 || (n_sets > 0 && !sets)) {
+        set_error("b200pt_trace_batch: null argument");
+        return B200PT_ERR_INVALID;
+    }
+    int64_t total = 0;
+    for (int i = 0; i < n_sets; i++) {
+        const b200pt_ray_set &rs = sets[i];
+        if (rs.n < 0 || (rs.n > 0 && (!rs.o_xyz || !rs.d_xyz || !rs.tmax))) {
+            set_error("b200pt_trace_batch: ray set %d: null argument", i);
+            return B200PT_ERR_INVALID;
+        }
+        total += (rs.n + 3) & ~int64_t(3);
+    }
+    if (!s->built) {
+        set_error("b200pt_trace: call b200pt_bvh_build first");
+        return B200PT_ERR_STATE;
+    }
+    if (total == 0) return B200PT_OK;
+    CU_TRY(cudaSetDevice(s->device));
+    // scratch layout (every array 16-byte aligned, sets back to back): o | d | tmax | prim | t | b12
+    const size_t T = (size_t)total;
+    int rc0 = ensure_scratch(s, T * (12 + 12 + 4 + 4 + 4 + 8));
+    if (rc0) return rc0;
+    char *base = (char *)s->d_scratch;
+    float *d_o = (float *)base;
+    float *d_d = (float *)(base + T * 12);
+    float *d_tmax = (float *)(base + T * 24);
+    int32_t *d_prim = (int32_t *)(base + T * 28);
+    float *d_t = (float *)(base + T * 32);
+    float *d_b = (float *)(base + T * 36);
+    static const int64_t chunk_env = getenv("B200PT_TRACE_CHUNK") ? atoll(getenv("B200PT_TRACE_CHUNK")) : 0;
+    const int64_t chunk = chunk_env > 0 ? chunk_env : (int64_t)1 << 19;
+    int n_chunks = 0;
+    for (int i = 0; i < n_sets; i++) n_chunks += (int)((sets[i].n + chunk - 1) / chunk);
+    if (!s->stream_h2d) CU_TRY(cudaStreamCreateWithFlags(&s->stream_h2d, cudaStreamNonBlocking));
+    if (!s->stream_d2h) CU_TRY(cudaStreamCreateWithFlags(&s->stream_d2h, cudaStreamNonBlocking));
+    while ((int)s->pipe_events.size() < 2 * n_chunks + 1) {
+        cudaEvent_t e;
+        CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        s->pipe_events.push_back(e);
+    }
+    // the scratch may still be read by the copy-out of the previous call's last chunk only if that call failed half way;
+    // a finished call has synchronised both streams.  The copy-in stream must not run ahead of a scratch re-allocation:
+    // ensure_scratch synchronises s->stream, and the other two streams are idle between calls.
+    int c = 0;
+    int64_t off = 0; // ray offset of the set inside the scratch arrays
+    for (int i = 0; i < n_sets; i++) {
+        const b200pt_ray_set &rs = sets[i];
+        for (int64_t c0 = 0; c0 < rs.n; c0 += chunk, c++) {
+            const int64_t nc = std::min(chunk, rs.n - c0), g0 = off + c0;
+            cudaEvent_t ev_in = s->pipe_events[2 * c], ev_done = s->pipe_events[2 * c + 1];
+            CU_TRY(cudaMemcpyAsync(d_o + 3 * g0, rs.o_xyz + 3 * c0, nc * 12, cudaMemcpyHostToDevice, s->stream_h2d));
+            CU_TRY(cudaMemcpyAsync(d_d + 3 * g0, rs.d_xyz + 3 * c0, nc * 12, cudaMemcpyHostToDevice, s->stream_h2d));
+            CU_TRY(cudaMemcpyAsync(d_tmax + g0, rs.tmax + c0, nc * 4, cudaMemcpyHostToDevice, s->stream_h2d));
+            CU_TRY(cudaEventRecord(ev_in, s->stream_h2d));
+            CU_TRY(cudaStreamWaitEvent(s->stream, ev_in, 0));
+            const TraceHostIO io = {d_o + 3 * g0, d_d + 3 * g0, d_tmax + g0, rs.prim_out ? d_prim + g0 : nullptr,
+                                    rs.t_out ? d_t + g0 : nullptr, rs.b1b2_out ? d_b + 2 * g0 : nullptr};
+            int rc = launch_trace(s, nullptr, nc, rs.any_hit, nullptr, c > 0, &io);
+            if (rc) return rc;
+            CU_TRY(cudaEventRecord(ev_done, s->stream));
+            CU_TRY(cudaStreamWaitEvent(s->stream_d2h, ev_done, 0));
+            if (rs.prim_out) CU_TRY(cudaMemcpyAsync(rs.prim_out + c0, d_prim + g0, nc * 4, cudaMemcpyDeviceToHost, s->stream_d2h));
+            if (rs.t_out) CU_TRY(cudaMemcpyAsync(rs.t_out + c0, d_t + g0, nc * 4, cudaMemcpyDeviceToHost, s->stream_d2h));
+            if (rs.b1b2_out) CU_TRY(cudaMemcpyAsync(rs.b1b2_out + 2 * c0, d_b + 2 * g0, nc * 8, cudaMemcpyDeviceToHost, s->stream_d2h));
+        }
+        off += (rs.n + 3) & ~int64_t(3);
+    }
+    s->last_counts[2] = total;
+    const int rc = check_trace_status(s); // synchronises the traversal stream
+    CU_TRY(cudaStreamSynchronize(s->stream_d2h));
+    return rc;
+}
+
 B200PT_API int b200pt_trace(b200pt_scene *s, const float *o_xyz, const float *d_xyz, const float *tmax, int64_t n,
                             int any_hit, int32_t *prim_out, float *t_out, float *b1b2_out) {
     if (!s || n < 0 || (n > 0 && (!o_xyz || !d_xyz || !tmax))) {
         set_error("b200pt_trace: null argument");
         return B200PT_ERR_INVALID;
     }
-    if (!s->built) {
-        set_error("b200pt_trace: call b200pt_bvh_build first");
-        return B200PT_ERR_STATE;
-    }
-    if (n == 0) return B200PT_OK;
-    CU_TRY(cudaSetDevice(s->device));
-    // scratch layout (all 16-byte aligned): rays | hits | o | d | tmax | prim | t | b
-    const size_t n16 = (size_t(n) + 3) & ~size_t(3);
-    int rc0 = ensure_scratch(s, n16 * (32 + 16 + 12 + 12 + 4 + 4 + 4 + 8));
-    if (rc0) return rc0;
-    char *base = (char *)s->d_scratch;
-    float4 *d_rays = (float4 *)base;
-    float4 *d_hits = (float4 *)(base + n16 * 32);
-    float *d_o = (float *)(base + n16 * 48);
-    float *d_d = (float *)(base + n16 * 60);
-    float *d_tmax = (float *)(base + n16 * 72);
-    int32_t *d_prim = (int32_t *)(base + n16 * 76);
-    float *d_t = (float *)(base + n16 * 80);
-    float *d_b = (float *)(base + n16 * 84);
-    // Three-stage pipeline over chunks of the batch: the copy-in of chunk k+1 (H2D engine), the traversal of chunk k and the
-    // copy-out of chunk k-1 (D2H engine) run at the same time; with pinned host buffers a batch costs about
-    // max(copy-in, traversal, copy-out) instead of their sum.  Pageable buffers still work (the copies then block the host).
-    static const int64_t chunk_env = getenv("B200PT_TRACE_CHUNK") ? atoll(getenv("B200PT_TRACE_CHUNK")) : 0;
-    const int64_t chunk = chunk_env > 0 ? chunk_env : (int64_t)1 << 19;
-    const int n_chunks = (int)((n + chunk - 1) / chunk);
-    if (!s->stream_h2d) CU_TRY(cudaStreamCreateWithFlags(&s->stream_h2d, cudaStreamNonBlocking));
-    if (!s->stream_d2h) CU_TRY(cudaStreamCreateWithFlags(&s->stream_d2h, cudaStreamNonBlocking));
-    while ((int)s->pipe_events.size() < 2 * n_chunks) {
-        cudaEvent_t e;
-        CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        s->pipe_events.push_back(e);
-    }
-    const int tb = 256;
-    for (int c = 0; c < n_chunks; c++) {
-        const int64_t c0 = c * chunk, nc = std::min(chunk, n - c0);
-        cudaEvent_t ev_in = s->pipe_events[2 * c], ev_done = s->pipe_events[2 * c + 1];
-        CU_TRY(cudaMemcpyAsync(d_o + 3 * c0, o_xyz + 3 * c0, nc * 12, cudaMemcpyHostToDevice, s->stream_h2d));
-        CU_TRY(cudaMemcpyAsync(d_d + 3 * c0, d_xyz + 3 * c0, nc * 12, cudaMemcpyHostToDevice, s->stream_h2d));
-        CU_TRY(cudaMemcpyAsync(d_tmax + c0, tmax + c0, nc * 4, cudaMemcpyHostToDevice, s->stream_h2d));
-        CU_TRY(cudaEventRecord(ev_in, s->stream_h2d));
-        CU_TRY(cudaStreamWaitEvent(s->stream, ev_in, 0));
-        const unsigned grid = unsigned((nc + tb - 1) / tb);
-        k_pack_rays<<<grid, tb, 0, s->stream>>>(d_o + 3 * c0, d_d + 3 * c0, d_tmax + c0, nc, d_rays + 2 * c0);
-        int rc = launch_trace(s, d_rays + 2 * c0, nc, any_hit, d_hits + c0, c > 0);
-        if (rc) return rc;
-        k_unpack_hits<<<grid, tb, 0, s->stream>>>(d_hits + c0, nc, d_prim + c0, d_t + c0, d_b + 2 * c0);
-        CU_TRY(cudaEventRecord(ev_done, s->stream));
-        CU_TRY(cudaStreamWaitEvent(s->stream_d2h, ev_done, 0));
-        if (prim_out) CU_TRY(cudaMemcpyAsync(prim_out + c0, d_prim + c0, nc * 4, cudaMemcpyDeviceToHost, s->stream_d2h));
-        if (t_out) CU_TRY(cudaMemcpyAsync(t_out + c0, d_t + c0, nc * 4, cudaMemcpyDeviceToHost, s->stream_d2h));
-        if (b1b2_out) CU_TRY(cudaMemcpyAsync(b1b2_out + 2 * c0, d_b + 2 * c0, nc * 8, cudaMemcpyDeviceToHost, s->stream_d2h));
-    }
-    s->last_counts[2] = n;
-    const int rc = check_trace_status(s); // synchronises the traversal stream
-    CU_TRY(cudaStreamSynchronize(s->stream_d2h));
-    return rc;
+    const b200pt_ray_set one = {o_xyz, d_xyz, tmax, n, any_hit, 0, prim_out, t_out, b1b2_out};
+    return b200pt_trace_batch(s, &one, 1);
 }
 
 B200PT_API int b200pt_trace_set_counting(b200pt_scene *s, int enable) {
     if (!s) return B200PT_ERR_INVALID;
     s->counting = enable != 0;
+    return B200PT_OK;
+}
+
+B200PT_API int b200pt_trace_tune(b200pt_scene *s, int key, int value) {
+    if (!s || value < 0) return B200PT_ERR_INVALID;
+    switch (key) {
+    case 0: s->tune_refill = value < 1 ? 1 : value; break;
+    case 1: s->tune_tri_steps = value < 1 ? 1 : (value > 3 ? 3 : value); break;
+    case 2: s->tune_ctas_per_sm = value; break;
+    case 3: s->tune_wf_refill = value; break;
+    case 4: s->tune_wf_tri_steps = value > 3 ? 3 : value; break;
+    default: set_error("b200pt_trace_tune: unknown key %d", key); return B200PT_ERR_INVALID;
+    }
     return B200PT_OK;
 }
 

@@ -22,6 +22,7 @@
 
 #include "common.cuh"
 #include "sort.cuh"
+#include "triangle.cuh"
 
 namespace b200pt {
 
@@ -464,11 +465,12 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
                 const TriVerts tv = load_tri(a.P, a.idx, prim);
                 float4 *dst = a.tris + 3 * (size_t)(tri_base + tri_off + k);
                 dst[0] = make_float4(tv.a.x, tv.a.y, tv.a.z, __int_as_float((int)prim));
-                // v1.w = material id | has-uv << 30 | has-normals << 29 | flip << 31 (b200pt.h: tri_flip bits 2, 1, 0), v2.w = light id (-1: none)
+                // v1.w = material id | degenerate << 28 | has-uv << 30 | has-normals << 29 | flip << 31 (b200pt.h: tri_flip bits 2, 1, 0), v2.w = light id (-1: none)
                 const uint32_t mat = (a.tri_material ? (uint32_t)a.tri_material[prim] : 0u) |
                                      (a.tri_flip ? ((uint32_t(a.tri_flip[prim]) & 1u) << 31 | (uint32_t(a.tri_flip[prim]) & 6u) << 28) : 0u);
                 const int light = a.tri_light ? a.tri_light[prim] : -1;
-                dst[1] = make_float4(tv.b.x, tv.b.y, tv.b.z, __uint_as_float(mat));
+                const uint32_t degen = triangle_is_degenerate(tv.a.x, tv.a.y, tv.a.z, tv.b.x, tv.b.y, tv.b.z, tv.c.x, tv.c.y, tv.c.z) ? kTriDegenerate : 0u;
+                dst[1] = make_float4(tv.b.x, tv.b.y, tv.b.z, __uint_as_float(mat | degen));
                 dst[2] = make_float4(tv.c.x, tv.c.y, tv.c.z, __int_as_float(light));
             }
             tri_off += tcount[i];

@@ -43,6 +43,12 @@ struct BVH8 {
     int64_t n_tris = 0;
 };
 
+// flag word of a leaf-order triangle record (v1.w): material id in the low 28 bits, then
+//  bit 28 degenerate triangle (Triangle::intersect_triangle's first reject, shapes/triangle.cu:218, evaluated once at build),
+//  bit 29 has per-vertex normals, bit 30 has per-vertex uvs, bit 31 flip the geometric normal
+constexpr uint32_t kTriMaterialMask = 0x0fffffffu;
+constexpr uint32_t kTriDegenerate = 0x10000000u;
+
 // Device-side sphere record for the (few) quadrics of a scene: tested linearly beside the BVH.
 struct SphereRec {
     float rfo[12]; // render_from_object, rows 0..2
@@ -52,6 +58,9 @@ struct SphereRec {
     int flip; // reverse_orientation ^ transform_swaps_handedness
     int material;
     int kind; // 0 sphere; 1 disk: z_min = height, z_max = inner radius
+    // render-space AABB of the quadric, padded: a ray that misses it cannot pass the interval-arithmetic test, so the
+    // trace kernels skip that (long) test for most rays
+    float box_lo[3], box_hi[3];
 };
 
 struct RenderData; // render.cu
@@ -92,6 +101,9 @@ struct b200pt_scene {
     // traversal
     unsigned long long *d_trace_counters = nullptr; // [0] ray ticket, [1] nodes, [2] tris, [3] err
     bool counting = false;
+    // k_trace tuning (b200pt_trace_tune): lanes idle before a warp refills, triangle tests per triangle phase, CTA cap per SM
+    int tune_refill = 4, tune_tri_steps = 1, tune_ctas_per_sm = 0;
+    int tune_wf_refill = 0, tune_wf_tri_steps = 0; // wavefront trace kernels; 0 = the built-in default
     int64_t last_counts[3] = {0, 0, 0};
     int64_t device_bytes = 0;
 
@@ -107,7 +119,14 @@ namespace b200pt {
 int build_bvh(b200pt_scene *s, b200pt_build_stats *stats);
 // keep_status: leave the node / triangle / overflow counters as they are (a later chunk of the same batch); the work ticket is
 // always reset
-int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev, bool keep_status = false);
+// caller-layout device arrays of one chunk (b200pt_trace_batch): o[n*3], d[n*3], tmax[n] in; prim[n], t[n], b12[n*2] out (any may be null)
+struct TraceHostIO {
+    const float *o, *d, *tmax;
+    int32_t *prim;
+    float *t, *b12;
+};
+int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev, bool keep_status = false,
+                 const TraceHostIO *io = nullptr);
 void free_render(b200pt_scene *s);
 int ensure_scratch(b200pt_scene *s, size_t bytes);
 

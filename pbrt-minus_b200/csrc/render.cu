@@ -51,6 +51,7 @@ struct RenderData {
     LightExt *d_light_ext = nullptr;
     int n_lights = 0, n_materials = 0, n_spectra = 0;
     int n_infinite = 0, infinite[4] = {0, 0, 0, 0};
+    int n_area_lights = 0; // emissive triangles (k_emit runs only when there are any)
     float scene_radius = 0.f;
     bool has_mat[WF_NMAT] = {};
     bool has_mix = false;
@@ -74,6 +75,7 @@ struct RenderData {
     WFCounters *d_counters = nullptr;
     WFCounters *h_counters = nullptr; // pinned
     std::vector<void *> pool_allocs;
+    std::vector<b200pt_film *> films;  // live films of this scene (their accumulators die with the scene)
 };
 
 template <typename T>
@@ -91,6 +93,13 @@ int build_rgb2spec(b200pt_scene *s, const double *fit, double **d_coeff_out, dou
 
 void free_render(b200pt_scene *s) {
     if (!s->render) return;
+    // films outlive neither their scene nor its device context: free the accumulators here and leave dead handles
+    // behind, so a later b200pt_film_* call on one returns B200PT_ERR_STATE instead of touching freed memory
+    for (b200pt_film *f : s->render->films) {
+        if (f->d_accum) cudaFree(f->d_accum);
+        f->d_accum = nullptr;
+        f->scene = nullptr;
+    }
     for (void *p : s->render->allocs) cudaFree(p);
     for (void *p : s->render->pool_allocs) cudaFree(p);
     if (s->render->d_counters) cudaFree(s->render->d_counters);
@@ -240,6 +249,28 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
                 set_error("b200pt_scene_create: quadric %d has kind %d", i, sp.kind);
                 return B200PT_ERR_INVALID;
             }
+            {   // padded render-space box (Transform::operator()(Bounds3f), euclidean_space/transform.h:326-351)
+                const float bmin[3] = {-sp.radius, -sp.radius, sp.kind == 1 ? sp.z_min : o.z_min},
+                            bmax[3] = {sp.radius, sp.radius, sp.kind == 1 ? sp.z_min : o.z_max};
+                float ext = 0.f, mag = 0.f;
+                for (int a = 0; a < 3; a++) {
+                    float mn = sp.render_from_object[4 * a + 3], mx = mn;
+                    for (int k = 0; k < 3; k++) {
+                        const float x = sp.render_from_object[4 * a + k] * bmin[k], y = sp.render_from_object[4 * a + k] * bmax[k];
+                        mn += std::min(x, y);
+                        mx += std::max(x, y);
+                    }
+                    o.box_lo[a] = mn;
+                    o.box_hi[a] = mx;
+                    ext = std::max(ext, mx - mn);
+                    mag = std::max(mag, std::max(std::fabs(mn), std::fabs(mx)));
+                }
+                const float pad = 1e-3f * ext + 1e-5f * mag + 1e-30f;
+                for (int a = 0; a < 3; a++) {
+                    o.box_lo[a] -= pad;
+                    o.box_hi[a] += pad;
+                }
+            }
             if (sp.light >= 0) {
                 set_error("b200pt_scene_create: emissive spheres are not supported");
                 return B200PT_ERR_UNSUPPORTED;
@@ -253,6 +284,12 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
     const b200pt_film_desc &fd = *desc->film;
     if (fd.width <= 0 || fd.height <= 0 || !fd.cie_x || !fd.cie_y || !fd.cie_z || !fd.illuminant) {
         set_error("b200pt_scene_create: incomplete film description");
+        return B200PT_ERR_INVALID;
+    }
+    // ---- array pointers the counts promise (a bad description comes back as a status code, never as a fault)
+    if (desc->n_spectra < 0 || desc->n_materials < 0 || desc->n_lights < 0 || (desc->n_spectra > 0 && !desc->spectra) ||
+        (desc->n_materials > 0 && !desc->materials) || (desc->n_lights > 0 && !desc->lights)) {
+        set_error("b200pt_scene_create: a spectra / materials / lights count is > 0 but its array is NULL");
         return B200PT_ERR_INVALID;
     }
     // ---- spectra
@@ -341,6 +378,21 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
         set_error("b200pt_scene_create: a render scene needs at least one material");
         return B200PT_ERR_INVALID;
     }
+    for (int i = 0; i < desc->n_spheres; i++)
+        if (desc->spheres[i].material < 0 || desc->spheres[i].material >= desc->n_materials) {
+            set_error("b200pt_scene_create: quadric %d has material id %d", i, desc->spheres[i].material);
+            return B200PT_ERR_INVALID;
+        }
+    // every emissive triangle must name an area light that names it back (k_logic reads lights[tri_light[t]])
+    if (desc->tri_light)
+        for (int64_t t = 0; t < desc->n_triangles; t++) {
+            const int32_t li = desc->tri_light[t];
+            if (li == -1) continue;
+            if (li < 0 || li >= desc->n_lights || desc->lights[li].type != B200PT_LIGHT_AREA || desc->lights[li].triangle != t) {
+                set_error("b200pt_scene_create: tri_light[%lld] = %d is not an area light on that triangle", (long long)t, li);
+                return B200PT_ERR_INVALID;
+            }
+        }
     // ---- media
     r->n_media = desc->n_media;
     r->camera_medium = desc->n_media > 0 ? desc->camera->medium : -1;
@@ -542,6 +594,7 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             return B200PT_ERR_INVALID;
         }
         LightRec &o = lights[i];
+        r->n_area_lights++;
         const int32_t *v = desc->indices + 3 * (size_t)l.triangle;
         for (int k = 0; k < 3; k++) {
             o.p0[k] = desc->P[3 * (size_t)v[0] + k];
@@ -736,17 +789,6 @@ __device__ __forceinline__ Sampler load_sampler(const WF &wf, int slot, const in
     return s;
 }
 
-__global__ void k_pass_begin(WF wf) {
-    WFCounters *c = wf.c;
-    for (int m = 0; m < WF_NMAT; m++) c->n_mat[m] = 0;
-    c->n_shadow = 0;
-    c->n_vol = 0;
-    c->ticket_closest = 0;
-    c->ticket_shadow = 0;
-}
-// runs between the stages that fill the free list (k_logic) and the one that drains it (k_generate)
-__global__ void k_after_generate(WF wf) { wf.c->n_free = 0; }
-__global__ void k_pass_end(WF wf) { wf.c->rays_shadow += wf.c->n_shadow; }
 
 __global__ void k_init_pool(WF wf) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -756,14 +798,34 @@ __global__ void k_init_pool(WF wf) {
     }
     if (i == 0) {
         WFCounters z = {};
-        z.n_free = (unsigned)wf.pool_size;
+        z.p[0].n_free = (unsigned)wf.pool_size; // pass 0 generates into every slot
         *wf.c = z;
     }
 }
 
+// RGBFilm::add_sample + PixelSensor::to_sensor_rgb (film/rgb_film.cu:63-80, film/pixel_sensor.h:19-26)
+__device__ __forceinline__ void film_add(const WF &wf, int pixel, S4 L, S4 lambda, S4 lpdf, float weight) {
+    if (weight == 0.f) return;
+    const S4 sp = safe_div(L, lpdf);
+    const S4 xb = make_float4(dense_lookup(wf.film.cie_x, lambda.x), dense_lookup(wf.film.cie_x, lambda.y),
+                              dense_lookup(wf.film.cie_x, lambda.z), dense_lookup(wf.film.cie_x, lambda.w));
+    const S4 yb = make_float4(dense_lookup(wf.film.cie_y, lambda.x), dense_lookup(wf.film.cie_y, lambda.y),
+                              dense_lookup(wf.film.cie_y, lambda.z), dense_lookup(wf.film.cie_y, lambda.w));
+    const S4 zb = make_float4(dense_lookup(wf.film.cie_z, lambda.x), dense_lookup(wf.film.cie_z, lambda.y),
+                              dense_lookup(wf.film.cie_z, lambda.z), dense_lookup(wf.film.cie_z, lambda.w));
+    const float X = wf.film.imaging_ratio * average(xb * sp), Y = wf.film.imaging_ratio * average(yb * sp),
+                Z = wf.film.imaging_ratio * average(zb * sp);
+    // one 128-bit vector reduction per finished path (sm_90+), instead of the reference's
+    // sort-by-pixel on the CPU + serial per-pixel adds
+    atomicAdd(wf.film.accum + pixel, make_float4(weight * X, weight * Y, weight * Z, weight));
+}
+
 // ---- gpu_generate_new_path (integrators/wavefront_path.cu:245-287)
+// The free list is also where finished paths meet the film: k_logic only MARKS a finished path (state ST_FREE, slot pushed
+// here); its radiance is added to the film by the thread that recycles the slot -- a dense pass over the free list instead
+// of a few lanes of every warp of k_logic (RGBFilm::add_sample needs 12 table lookups per path).
 __global__ void __launch_bounds__(WF_BLOCK) k_generate(WF wf) {
-    const unsigned n = wf.c->n_free;
+    const unsigned n = wf.c->p[wf.parity].n_free;
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned n_round = (n + 31u) & ~31u;
     const int lane = threadIdx.x & 31;
@@ -776,9 +838,14 @@ __global__ void __launch_bounds__(WF_BLOCK) k_generate(WF wf) {
         base = __shfl_sync(0xffffffffu, base, 0);
         const long long id = (long long)base + __popc(m & ((1u << lane) - 1u));
         const bool live = have_slot && id < wf.total_paths;
-        if (have_slot && !live) wf.pool.state[wf.q.free_slots[i]] = ST_IDLE; // no paths left: the slot retires
+        int slot = -1;
+        if (have_slot) {
+            slot = wf.q.free_slots[i];
+            if (wf.pool.state[slot] == ST_FREE) // write_frame_buffer (:216-234) for the path that finished in this slot
+                film_add(wf, wf.pool.ids[slot].x, wf.pool.L[slot], wf.pool.lambda[slot], wf.pool.lpdf[slot], wf.pool.misc[slot].x);
+            if (!live) wf.pool.state[slot] = ST_IDLE; // no paths left: the slot retires
+        }
         if (live) {
-            const int slot = wf.q.free_slots[i];
             const int pixel = int(id % wf.n_pixels);
             const int sample = wf.sample_begin + int(id / wf.n_pixels);
             const int px = pixel % wf.film.width, py = pixel / wf.film.width;
@@ -833,23 +900,6 @@ __global__ void __launch_bounds__(WF_BLOCK) k_generate(WF wf) {
             wf.pool.state[slot] = ST_RAY;
         }
     }
-}
-
-// RGBFilm::add_sample + PixelSensor::to_sensor_rgb (film/rgb_film.cu:63-80, film/pixel_sensor.h:19-26)
-__device__ __forceinline__ void film_add(const WF &wf, int pixel, S4 L, S4 lambda, S4 lpdf, float weight) {
-    if (weight == 0.f) return;
-    const S4 sp = safe_div(L, lpdf);
-    const S4 xb = make_float4(dense_lookup(wf.film.cie_x, lambda.x), dense_lookup(wf.film.cie_x, lambda.y),
-                              dense_lookup(wf.film.cie_x, lambda.z), dense_lookup(wf.film.cie_x, lambda.w));
-    const S4 yb = make_float4(dense_lookup(wf.film.cie_y, lambda.x), dense_lookup(wf.film.cie_y, lambda.y),
-                              dense_lookup(wf.film.cie_y, lambda.z), dense_lookup(wf.film.cie_y, lambda.w));
-    const S4 zb = make_float4(dense_lookup(wf.film.cie_z, lambda.x), dense_lookup(wf.film.cie_z, lambda.y),
-                              dense_lookup(wf.film.cie_z, lambda.z), dense_lookup(wf.film.cie_z, lambda.w));
-    const float X = wf.film.imaging_ratio * average(xb * sp), Y = wf.film.imaging_ratio * average(yb * sp),
-                Z = wf.film.imaging_ratio * average(zb * sp);
-    // one 128-bit vector reduction per finished path (sm_90+), instead of the reference's
-    // sort-by-pixel on the CPU + serial per-pixel adds
-    atomicAdd(wf.film.accum + pixel, make_float4(weight * X, weight * Y, weight * Z, weight));
 }
 
 // geometric normal of a leaf-record triangle as Triangle::interaction_from_intersection sets it
@@ -1125,7 +1175,7 @@ __device__ __forceinline__ S4 volume_transmittance(const WF &wf, V3 p0, int medi
         const float4 *tp = wf.bvh.tris + 3 * (size_t)h.prim;
         const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
         const uint32_t mw = __float_as_uint(v1.w);
-        if (wf.materials[mw & 0x1fffffffu].type != B200PT_MAT_INTERFACE) return s4(0.f);
+        if (wf.materials[mw & kTriMaterialMask].type != B200PT_MAT_INTERFACE) return s4(0.f);
         // interaction.n = d; shadow_ray = interaction.spawn_ray(d)
         const float b1 = h.b1, b2 = h.b2, b0 = 1.f - b1 - b2;
         const V3 q0 = v3(v0), q1 = v3(v1), q2 = v3(v2);
@@ -1154,7 +1204,8 @@ __device__ __forceinline__ S4 volume_transmittance(const WF &wf, V3 p0, int medi
 template <int PHASE>
 __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
     __shared__ uint2 s_stack[PHASE == 1 ? SM_STACK * VOL_BLOCK : 1];
-    const unsigned n = PHASE == 0 ? (unsigned)wf.pool_size : wf.c->n_vol;
+    if (wf.c->finished >= (unsigned long long)wf.total_paths) return;
+    const unsigned n = PHASE == 0 ? (unsigned)wf.pool_size : wf.c->p[wf.parity].n_vol;
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned n_round = (n + 31u) & ~31u;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
@@ -1190,7 +1241,7 @@ __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
                     wf.pool.rng[slot] = s.state;
                 }
             }
-            queue_push(&wf.c->n_vol, wf.q.vol, (int)i, scatter);
+            queue_push(&wf.c->p[wf.parity].n_vol, wf.q.vol, (int)i, scatter);
             continue;
         }
         if (i >= n) continue;
@@ -1271,6 +1322,8 @@ __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
 template <bool MEDIA, bool ENV>
 __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
     // one thread per pool slot, in slot order: every lane access below is a coalesced 16-byte gather
+    if (blockIdx.x == 0 && threadIdx.x == 0) wf.c->p[wf.parity ^ 1] = WFPass{}; // the next pass starts with empty queues
+    if (wf.c->finished >= (unsigned long long)wf.total_paths) return;
     const unsigned n = (unsigned)wf.pool_size;
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned n_round = (n + WF_BLOCK - 1u) / WF_BLOCK * WF_BLOCK;
@@ -1280,6 +1333,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
         const int slot = (int)i;
         int route = -1; // route: material type, or -1
         bool terminate = false, stay = false; // stay: the slot keeps ST_RAY (scattered in a medium / crossed an interface)
+        int emit = 0; // 1: the hit triangle is emissive (k_emit adds its Le), | 2: added raw (camera ray / specular bounce)
         if (act) {
             int4 ids = wf.pool.ids[slot];
             int next_rr = (ids.w >> 16) & 0xff;
@@ -1332,6 +1386,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                         const float dir_pdf = wf.pool.misc[slot].y * dir_pdf_scale;
                         L = L + beta * power_heuristic(dir_pdf, pdf_light) * Le;
                     }
+                    dirty_L = true;
                 }
                 terminate = true;
             }
@@ -1339,7 +1394,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                 const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
                 const float4 v1 = __ldg(tp + 1);
                 const uint32_t mw = __float_as_uint(v1.w);
-                if (wf.materials[mw & 0x1fffffffu].type == B200PT_MAT_INTERFACE) {
+                if (wf.materials[mw & kTriMaterialMask].type == B200PT_MAT_INTERFACE) {
                     // material-less interface (:146-151, gpu_evaluate_interface_material :303-320): 0.3 of a bounce, the ray
                     // carries on in the same direction from the far side, in the medium found there
                     const float4 v0 = __ldg(tp), v2 = __ldg(tp + 2);
@@ -1360,32 +1415,11 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                     mat = wf.spheres[prim - (int)wf.bvh.n_tris].material;
                 } else {
                     const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
-                    const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                    const float4 v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                     const uint32_t mw = __float_as_uint(v1.w);
-                    mat = int(mw & 0x1fffffffu);
-                    const int light = __float_as_int(v2.w);
-                    if (light >= 0) {
-                        // SurfaceInteraction::le -> DiffuseAreaLight::l, then MIS against NEE (:155-171)
-                        const LightRec Lr = wf.lights[light];
-                        const V3 n = tri_normal(v3(v0), v3(v1), v3(v2), (mw >> 31) != 0u);
-                        const V3 rd = v3(wf.pool.ray_d[slot]);
-                        if (light_emits_towards(Lr, n, -rd)) {
-                            const S4 lambda = wf.pool.lambda[slot];
-                            const S4 Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * Lr.scale;
-                            if (is_positive(Le)) {
-                                if (depth == 0 || (ids.w & PF_SPECULAR)) {
-                                    L = L + beta * Le;
-                                } else {
-                                    const float4 c0 = wf.pool.ctx0[slot], c1 = wf.pool.ctx1[slot], c2 = wf.pool.ctx2[slot];
-                                    const LightCtx ctx{v3(c0), v3(c0.w, c1.w, c2.w), v3(c1), v3(c2)};
-                                    const float pdf_light = Lr.pmf * light_pdf(Lr, ctx, rd);
-                                    const float dir_pdf = wf.pool.misc[slot].y * dir_pdf_scale;
-                                    L = L + beta * Le * power_heuristic(dir_pdf, pdf_light);
-                                }
-                                dirty_L = true;
-                            }
-                        }
-                    }
+                    mat = int(mw & kTriMaterialMask);
+                    // emitted radiance (:155-171) is added by k_emit, densely over the few slots that hit a light
+                    if (__float_as_int(v2.w) >= 0) emit = 1 | ((depth == 0 || (ids.w & PF_SPECULAR)) ? 2 : 0);
                 }
                 if (wf.has_mix && wf.materials[mat].type == B200PT_MAT_MIX) {
                     const MatRec mr = wf.materials[mat];
@@ -1410,12 +1444,10 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                 }
                 route = wf.materials[mat].type;
             }
+            if (dirty_L) wf.pool.L[slot] = L;
             if (terminate) {
-                const float fw = wf.pool.misc[slot].x;
-                film_add(wf, ids.x, L, wf.pool.lambda[slot], wf.pool.lpdf[slot], fw);
-                n_finished++;
+                n_finished++; // its radiance goes to the film when k_generate recycles the slot
             } else {
-                if (dirty_L) wf.pool.L[slot] = L;
                 ids.w = (ids.w & 0xff) | ((MEDIA ? 0 : (int)depth) << 8) | (next_rr << 16);
                 wf.pool.ids[slot] = ids;
             }
@@ -1423,10 +1455,46 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
         const int cat = (act && terminate) ? WF_NMAT : route; // material queue, WF_NMAT = free list, -1 nothing (the slot stays a ray)
         if (act && !stay) wf.pool.state[slot] = terminate ? ST_FREE : uint8_t(ST_MAT0 + route);
         block_push(wf, cat, slot);
+        queue_push(&wf.c->p[wf.parity].n_emit, wf.q.emit, slot | ((emit & 2) ? int(0x80000000u) : 0), emit != 0);
     }
     // finished-path count: warp reduce, one atomic per warp
     for (int o = 16; o > 0; o >>= 1) n_finished += __shfl_xor_sync(0xffffffffu, n_finished, o);
     if ((threadIdx.x & 31) == 0 && n_finished) atomicAdd(&wf.c->finished, (unsigned long long)n_finished);
+}
+
+// ---- emitted radiance at a hit on an area light: SurfaceInteraction::le -> DiffuseAreaLight::l, MIS against NEE
+// (integrators/wavefront_path.cu:155-171).  Runs over the emit queue of the pass, after k_logic (which found the hits)
+// and before the shade kernels (which move beta on).
+__global__ void __launch_bounds__(WF_BLOCK) k_emit(WF wf) {
+    const unsigned n = wf.c->p[wf.parity].n_emit;
+    const unsigned stride = gridDim.x * blockDim.x;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const int e = wf.q.emit[i];
+        const int slot = e & 0x7fffffff;
+        const bool raw = e < 0;
+        const float4 hit = wf.pool.hit[slot];
+        const float4 *tp = wf.bvh.tris + 3 * (size_t)__float_as_int(hit.x);
+        const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+        const LightRec Lr = wf.lights[__float_as_int(v2.w)];
+        const V3 n_g = tri_normal(v3(v0), v3(v1), v3(v2), (__float_as_uint(v1.w) >> 31) != 0u);
+        const V3 rd = v3(wf.pool.ray_d[slot]);
+        if (!light_emits_towards(Lr, n_g, -rd)) continue;
+        const S4 Le = spectrum_sample(wf.spectra, Lr.spectrum, wf.pool.lambda[slot]) * Lr.scale;
+        if (!is_positive(Le)) continue;
+        const S4 beta = wf.pool.beta[slot];
+        S4 L = wf.pool.L[slot];
+        if (raw) {
+            L = L + beta * Le;
+        } else {
+            const float4 c0 = wf.pool.ctx0[slot], c1 = wf.pool.ctx1[slot], c2 = wf.pool.ctx2[slot];
+            const LightCtx ctx{v3(c0), v3(c0.w, c1.w, c2.w), v3(c1), v3(c2)};
+            const float pdf_light = Lr.pmf * light_pdf(Lr, ctx, rd);
+            const float dir_pdf_scale = wf.has_media ? average(wf.pool.mtp[slot]) : 1.f; // multi_transmittance_pdf.average() (:165)
+            const float dir_pdf = wf.pool.misc[slot].y * dir_pdf_scale;
+            L = L + beta * Le * power_heuristic(dir_pdf, pdf_light);
+        }
+        wf.pool.L[slot] = L;
+    }
 }
 
 // "reflectance" / "transmittance" of a material: a spectrum, or a spectrum texture evaluated at the hit
@@ -1567,7 +1635,7 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_COATED_CONDUCTOR>(const WF 
 template <int MAT, bool EXT>
 __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ? 1 : 2) k_shade(WF wf) {
     const bool MEDIA = EXT && wf.has_media;
-    const unsigned n = wf.c->n_mat[MAT];
+    const unsigned n = wf.c->p[wf.parity].n_mat[MAT];
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned n_round = (n + 31u) & ~31u;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
@@ -1591,7 +1659,7 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
                 const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
                 const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                 const uint32_t mw = __float_as_uint(v1.w);
-                mat = int(mw & 0x1fffffffu);
+                mat = int(mw & kTriMaterialMask);
                 prim_id = __float_as_int(v0.w);
                 triangle_interaction(wf, v3(v0), v3(v1), v3(v2), prim_id, mw, hit.z, hit.w, -rd, si);
             }
@@ -1718,7 +1786,7 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
             wf.pool.rng[slot] = s.state;
             wf.pool.state[slot] = ST_RAY; // traced and judged by the next pass (dead paths: tmax < 0)
         }
-        const int spos = queue_claim(&wf.c->n_shadow, shadow);
+        const int spos = queue_claim(&wf.c->p[wf.parity].n_shadow, shadow);
         if (spos >= 0) {
             wf.q.sh_o[spos] = sh_o;
             wf.q.sh_d[spos] = sh_d;
@@ -1767,7 +1835,7 @@ static int ensure_pool(b200pt_scene *s, int pool_size) {
     WFQueues &Q = r->q;
     for (int m = 0; m < WF_NMAT; m++)
         if ((rc = pool_alloc(r, &Q.mat[m], r->has_mat[m] ? n : 1))) return rc;
-    int32_t **qs[] = {&Q.free_slots, &Q.sh_slot};
+    int32_t **qs[] = {&Q.free_slots, &Q.sh_slot, &Q.emit};
     for (int32_t **q : qs)
         if ((rc = pool_alloc(r, q, n))) return rc;
     if ((rc = pool_alloc(r, &Q.sh_o, n))) return rc;
@@ -1807,19 +1875,39 @@ B200PT_API int b200pt_film_create(b200pt_scene *s, b200pt_film **out) {
     }
     cudaMemsetAsync(f->d_accum, 0, bytes, s->stream);
     cudaStreamSynchronize(s->stream);
+    s->render->films.push_back(f);
     *out = f;
+    return B200PT_OK;
+}
+
+// a film whose scene has been destroyed is a dead handle: only b200pt_film_destroy may still be called on it
+static int film_alive(const b200pt_film *film, const char *who) {
+    if (!film) {
+        set_error("%s: null film", who);
+        return B200PT_ERR_INVALID;
+    }
+    if (!film->scene || !film->d_accum) {
+        set_error("%s: the film's scene has been destroyed", who);
+        return B200PT_ERR_STATE;
+    }
     return B200PT_OK;
 }
 
 B200PT_API void b200pt_film_destroy(b200pt_film *film) {
     if (!film) return;
-    if (film->scene) cudaSetDevice(film->scene->device);
-    if (film->d_accum) cudaFree(film->d_accum);
+    if (film->scene) {
+        cudaSetDevice(film->scene->device);
+        if (film->scene->render) {
+            std::vector<b200pt_film *> &v = film->scene->render->films;
+            v.erase(std::remove(v.begin(), v.end(), film), v.end());
+        }
+        if (film->d_accum) cudaFree(film->d_accum);
+    }
     delete film;
 }
 
 B200PT_API int b200pt_film_clear(b200pt_film *film) {
-    if (!film) return B200PT_ERR_INVALID;
+    if (int rc = film_alive(film, "b200pt_film_clear")) return rc;
     CU_TRY(cudaSetDevice(film->scene->device));
     CU_TRY(cudaMemsetAsync(film->d_accum, 0, (size_t)film->width * film->height * sizeof(float4), film->scene->stream));
     CU_TRY(cudaStreamSynchronize(film->scene->stream));
@@ -1831,6 +1919,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
         set_error("b200pt_render: null argument");
         return B200PT_ERR_INVALID;
     }
+    if (int rc = film_alive(film, "b200pt_render")) return rc;
     if (!s->render || !s->render->have_render || film->scene != s) {
         set_error("b200pt_render: scene has no render description, or the film belongs to another scene");
         return B200PT_ERR_STATE;
@@ -1893,7 +1982,8 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     // a warp of k_trace_wf fetches new rays once this many lanes are idle: 4 is the measured best on triangle-only scenes;
     // with spheres the per-ray start-up is longer and waiting for half a warp pays (C1: 62.0 -> 58.5 ms together with the
     // sphere phase)
-    wf.refill_min = getenv("B200PT_WF_REFILL") ? atoi(getenv("B200PT_WF_REFILL")) : (s->n_spheres > 0 ? 16 : 4);
+    wf.refill_min = s->tune_wf_refill > 0 ? s->tune_wf_refill : (s->n_spheres > 0 ? 16 : 4);
+    wf.tri_steps = s->tune_wf_tri_steps > 0 ? s->tune_wf_tri_steps : 1;
     const bool ext_shade = wf.has_media || r->tex.tex != nullptr || r->env.light >= 0;
     int n_shade_kernels = 0;
     for (int m = 0; m < WF_NMAT; m++) n_shade_kernels += r->has_mat[m] ? 1 : 0;
@@ -1939,7 +2029,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     bool done = total == 0;
     for (long long k = 0; !done; k++) {
         for (int b = 0; b < batch; b++) {
-            k_pass_begin<<<1, 1, 0, st>>>(wf);
+            wf.parity = int(passes & 1);
             if ((rc = launch_trace_wf(s, wf, false))) return rc;
             if (wf.has_media) {
                 k_volume<0><<<grid, VOL_BLOCK, 0, st>>>(wf);
@@ -1952,8 +2042,8 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
                 if (wf.has_media) k_logic<true, false><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_logic<false, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
+            if (r->n_area_lights > 0) k_emit<<<grid, WF_BLOCK, 0, st>>>(wf);
             k_generate<<<grid, WF_BLOCK, 0, st>>>(wf);
-            k_after_generate<<<1, 1, 0, st>>>(wf);
             // one shade kernel per material type PRESENT in the scene (a type without materials has no queue)
             if (r->has_mat[B200PT_MAT_DIFFUSE]) {
                 if (ext_shade) k_shade<B200PT_MAT_DIFFUSE, true><<<grid, WF_BLOCK, 0, st>>>(wf);
@@ -1980,9 +2070,8 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
                 else k_shade<B200PT_MAT_COATED_CONDUCTOR, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
             if ((rc = launch_trace_wf(s, wf, true))) return rc;
-            k_pass_end<<<1, 1, 0, st>>>(wf);
             passes++;
-            launches += 7 + n_shade_kernels + (wf.has_media ? 2 : 0);
+            launches += 4 + n_shade_kernels + (wf.has_media ? 2 : 0) + (r->n_area_lights > 0 ? 1 : 0);
         }
         CU_TRY(cudaGetLastError());
         const int cur = int(k & 1);
@@ -2065,7 +2154,8 @@ __global__ void k_probe_sampler(int kind, int spp, int sqrt_spp, const int32_t *
 } // namespace b200pt
 
 B200PT_API int b200pt_film_read_raw(b200pt_film *film, float *xyzw_out) {
-    if (!film || !xyzw_out) return B200PT_ERR_INVALID;
+    if (!xyzw_out) return B200PT_ERR_INVALID;
+    if (int rc = film_alive(film, "b200pt_film_read_raw")) return rc;
     b200pt_scene *s = film->scene;
     CU_TRY(cudaSetDevice(s->device));
     CU_TRY(cudaMemcpyAsync(xyzw_out, film->d_accum, (size_t)film->width * film->height * sizeof(float4), cudaMemcpyDeviceToHost, s->stream));
@@ -2074,7 +2164,8 @@ B200PT_API int b200pt_film_read_raw(b200pt_film *film, float *xyzw_out) {
 }
 
 B200PT_API int b200pt_film_read(b200pt_film *film, float *rgb_out) {
-    if (!film || !rgb_out) return B200PT_ERR_INVALID;
+    if (!rgb_out) return B200PT_ERR_INVALID;
+    if (int rc = film_alive(film, "b200pt_film_read")) return rc;
     b200pt_scene *s = film->scene;
     CU_TRY(cudaSetDevice(s->device));
     const long long n = (long long)film->width * film->height;
@@ -2097,6 +2188,7 @@ B200PT_API int b200pt_film_reduce(b200pt_film *film, void *comm, int root, void 
         set_error("b200pt_film_reduce: null argument");
         return B200PT_ERR_INVALID;
     }
+    if (int rc = film_alive(film, "b200pt_film_reduce")) return rc;
     typedef int (*nccl_reduce_t)(const void *, void *, size_t, int, int, int, void *, cudaStream_t);
     static nccl_reduce_t fn = nullptr;
     if (!fn) {
@@ -2113,6 +2205,7 @@ B200PT_API int b200pt_film_reduce(b200pt_film *film, void *comm, int root, void 
     b200pt_scene *s = film->scene;
     CU_TRY(cudaSetDevice(s->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+    if (st != s->stream) CU_TRY(cudaStreamSynchronize(s->stream)); // the render that filled the film ran on the scene's stream
     const size_t count = (size_t)film->width * film->height * 4;
     // ncclFloat32 = 7, ncclSum = 0
     const int rc = fn(film->d_accum, film->d_accum, count, 7, 0, root, comm, st);
@@ -2124,7 +2217,7 @@ B200PT_API int b200pt_film_reduce(b200pt_film *film, void *comm, int root, void 
     return B200PT_OK;
 }
 
-B200PT_API void *b200pt_film_device_ptr(b200pt_film *film) { return film ? (void *)film->d_accum : nullptr; }
+B200PT_API void *b200pt_film_device_ptr(b200pt_film *film) { return (film && film->scene) ? (void *)film->d_accum : nullptr; }
 B200PT_API int b200pt_film_dims(b200pt_film *film, int32_t *w, int32_t *h) {
     if (!film) return B200PT_ERR_INVALID;
     if (w) *w = film->width;

@@ -31,9 +31,16 @@ struct TraceParams {
     long long n;
     unsigned long long *counters; // [0] ticket, [1] nodes, [2] tris, [3] overflow flag
     uint32_t prmt_bias;           // 0x47000000 (32768.0f), passed as a parameter so PRMT keeps an immediate selector
+    // caller-layout I/O (b200pt_trace / b200pt_trace_batch): when `o` is set the kernel reads the caller's o[n*3] / d[n*3] /
+    // tmax[n] and writes prim[n] / t[n] / b12[n*2] itself -- no repacking passes on either side of the traversal
+    const float *o, *d, *tmax;
+    int32_t *prim_out;
+    float *t_out, *b12_out;
 };
 
-template <bool ANY, bool COUNT, int REFILL>
+// TRI_STEPS: triangle tests a lane runs per triangle phase (a lane whose leaf slot holds several triangles does not
+// need one vote round per triangle)
+template <bool ANY, bool COUNT, int REFILL, int TRI_STEPS>
 __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
     __shared__ uint2 sm_stack_all[SM_STACK * TRACE_BLOCK];
     uint2 *const sm_stack = sm_stack_all + threadIdx.x;
@@ -44,7 +51,8 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
 
     long long ray = -1; // this lane's ray index, -1 = idle
     bool exhausted = false;
-    float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 0, idx = 0, idy = 0, idz = 0;
+    float ox = 0, oy = 0, oz = 0, idx = 0, idy = 0, idz = 0;
+    RayShear rs = {0.f, 0.f, 0.f, 2}; // ray-only part of the watertight test, evaluated once per ray
     uint32_t octinv4 = 0;
     uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
     int sp = 0;
@@ -66,10 +74,18 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
                 const long long r = (long long)base + __popc(idle & lt_mask);
                 if (r < p.n) {
                     ray = r;
-                    const float4 ro = __ldg(p.rays + 2 * r), rd = __ldg(p.rays + 2 * r + 1);
+                    float4 ro, rd;
+                    if (p.o) {
+                        const float *po = p.o + 3 * r, *pd = p.d + 3 * r;
+                        ro = make_float4(__ldg(po), __ldg(po + 1), __ldg(po + 2), __ldg(p.tmax + r));
+                        rd = make_float4(__ldg(pd), __ldg(pd + 1), __ldg(pd + 2), 0.f);
+                    } else {
+                        ro = __ldg(p.rays + 2 * r);
+                        rd = __ldg(p.rays + 2 * r + 1);
+                    }
                     ox = ro.x; oy = ro.y; oz = ro.z;
-                    dx = rd.x; dy = rd.y; dz = rd.z;
-                    idx = safe_rcp_dir(dx); idy = safe_rcp_dir(dy); idz = safe_rcp_dir(dz);
+                    idx = safe_rcp_dir(rd.x); idy = safe_rcp_dir(rd.y); idz = safe_rcp_dir(rd.z);
+                    rs = ray_shear(rd.x, rd.y, rd.z);
                     octinv4 = ((idx < 0.f ? 0u : 4u) | (idy < 0.f ? 0u : 2u) | (idz < 0.f ? 0u : 1u)) * 0x01010101u;
                     ng = make_uint2(0u, have_tree ? 0x80000000u : 0u);
                     tg = make_uint2(0u, 0u);
@@ -91,21 +107,25 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
         const unsigned m_node = __ballot_sync(0xffffffffu, act && !want_tri);
         if (__popc(m_tri) >= __popc(m_node)) {
             if (want_tri) {
-                const int ti = __ffs(tg.y) - 1;
-                tg.y &= tg.y - 1u;
-                const float4 *tp = p.bvh.tris + 3 * size_t(tg.x + ti);
-                const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
-                if (COUNT) n_tris++;
-                TriHit th;
-                if (intersect_triangle(ox, oy, oz, dx, dy, dz, ht, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, th)) {
-                    ht = th.t;
-                    hb1 = th.b1;
-                    hb2 = th.b2;
-                    hprim = __float_as_int(v0.w);
-                    if (ANY) { // first accepted candidate ends the ray
-                        tg.y = 0u;
-                        ng.y = 0u;
-                        sp = 0;
+#pragma unroll 1
+                for (int step = 0; step < TRI_STEPS && tg.y != 0u; step++) {
+                    const int ti = __ffs(tg.y) - 1;
+                    tg.y &= tg.y - 1u;
+                    const float4 *tp = p.bvh.tris + 3 * size_t(tg.x + ti);
+                    const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                    if (COUNT) n_tris++;
+                    TriHit th;
+                    if (!(__float_as_uint(v1.w) & kTriDegenerate) &&
+                        intersect_triangle_sheared(ox, oy, oz, rs, ht, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, th)) {
+                        ht = th.t;
+                        hb1 = th.b1;
+                        hb2 = th.b2;
+                        hprim = __float_as_int(v0.w);
+                        if (ANY) { // first accepted candidate ends the ray
+                            tg.y = 0u;
+                            ng.y = 0u;
+                            sp = 0;
+                        }
                     }
                 }
             }
@@ -137,8 +157,15 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
                 ng.y = (hitmask & 0xff000000u) | (__float_as_uint(n0.w) >> 24);
                 tg.y = hitmask & 0x00ffffffu;
             } else { // nothing left: retire the ray
-                if (ANY) p.hits[ray] = make_float4(__int_as_float(hprim >= 0 ? 1 : 0), 0.f, 0.f, 0.f);
-                else p.hits[ray] = make_float4(__int_as_float(hprim), hprim >= 0 ? ht : kInf, hb1, hb2);
+                if (p.o) {
+                    if (p.prim_out) p.prim_out[ray] = ANY ? (hprim >= 0 ? 1 : 0) : hprim;
+                    if (p.t_out) p.t_out[ray] = (ANY || hprim < 0) ? (ANY ? 0.f : kInf) : ht;
+                    if (p.b12_out) *reinterpret_cast<float2 *>(p.b12_out + 2 * ray) = ANY ? make_float2(0.f, 0.f) : make_float2(hb1, hb2);
+                } else if (ANY) {
+                    p.hits[ray] = make_float4(__int_as_float(hprim >= 0 ? 1 : 0), 0.f, 0.f, 0.f);
+                } else {
+                    p.hits[ray] = make_float4(__int_as_float(hprim), hprim >= 0 ? ht : kInf, hb1, hb2);
+                }
                 ray = -1;
             }
         }
@@ -147,7 +174,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
         atomicAdd(p.counters + 1, (unsigned long long)n_nodes);
         atomicAdd(p.counters + 2, (unsigned long long)n_tris);
     }
-    if (overflow) p.counters[3] = 1ull;
+    if (overflow) p.counters[3] = 1ull; // sticky: cleared when the host reads it (check_trace_status)
 }
 
 // ---- queue-driven form used by the wavefront integrator (render.cu) ---------------------------
@@ -161,6 +188,21 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
 //                   NEE contribution to pool.L[slot] on retirement (one shadow ray per slot per pass,
 //                   so the add needs no atomic) -- the reference runs these traversals inline in the
 //                   shading threads (integrators/megakernel_path.cu:217-233, base/integrator_base.cu:12-71).
+// first quadric at or after k whose padded box the ray (o, 1/d, [0, t_max]) touches; n when there is none
+__device__ __forceinline__ int next_sphere(const SphereRec *sph, int n, int k, float ox, float oy, float oz, float idx, float idy,
+                                           float idz, float t_max) {
+    for (; k < n; k++) {
+        const float *lo = sph[k].box_lo, *hi = sph[k].box_hi;
+        const float x0 = (__ldg(lo) - ox) * idx, x1 = (__ldg(hi) - ox) * idx;
+        const float y0 = (__ldg(lo + 1) - oy) * idy, y1 = (__ldg(hi + 1) - oy) * idy;
+        const float z0 = (__ldg(lo + 2) - oz) * idz, z1 = (__ldg(hi + 2) - oz) * idz;
+        const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.f));
+        const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
+        if (tn <= tf * 1.00001f + 1e-30f) break;
+    }
+    return k;
+}
+
 template <bool SHADOW, bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
     __shared__ uint2 sm_stack_all[SM_STACK * TRACE_BLOCK];
@@ -171,16 +213,21 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
     const bool have_tree = wf.bvh.n_nodes > 0;
     // closest hit: every pool slot in slot order (coalesced gathers), live ones have state ST_RAY;
     // shadow: the compact shadow queue
-    const long long n = SHADOW ? (long long)wf.c->n_shadow : (long long)wf.pool_size;
-    unsigned *const ticket = SHADOW ? &wf.c->ticket_shadow : &wf.c->ticket_closest;
+    if (wf.c->finished >= (unsigned long long)wf.total_paths) return; // a look-ahead pass after the last path retired
+    WFPass &pc = wf.c->p[wf.parity];
+    const long long n = SHADOW ? (long long)pc.n_shadow : (long long)wf.pool_size;
+    unsigned *const ticket = SHADOW ? &pc.ticket_shadow : &pc.ticket_closest;
+    if (SHADOW && blockIdx.x == 0 && threadIdx.x == 0) wf.c->rays_shadow += (unsigned long long)n;
     unsigned n_live = 0;
     const int REFILL = wf.refill_min;
+    const int tri_steps = wf.tri_steps;
     const uint32_t prmt_bias = 0x47000000u;
 
     long long ray = -1;
     int slot = -1;
     bool exhausted = false;
     float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 0, idx = 0, idy = 0, idz = 0;
+    RayShear rs = {0.f, 0.f, 0.f, 2};
     uint32_t octinv4 = 0;
     uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
     int sp = 0;
@@ -217,6 +264,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                     ox = ro.x; oy = ro.y; oz = ro.z;
                     dx = rd.x; dy = rd.y; dz = rd.z;
                     idx = safe_rcp_dir(dx); idy = safe_rcp_dir(dy); idz = safe_rcp_dir(dz);
+                    rs = ray_shear(dx, dy, dz);
                     octinv4 = ((idx < 0.f ? 0u : 4u) | (idy < 0.f ? 0u : 2u) | (idz < 0.f ? 0u : 1u)) * 0x01010101u;
                     const bool live = ro.w >= 0.f; // tmax < 0 marks a dead path: report a miss
                     ng = make_uint2(0u, (have_tree && live) ? 0x80000000u : 0u);
@@ -225,7 +273,8 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                     ht = ro.w;
                     hb1 = 0.f; hb2 = 0.f;
                     hprim = -1;
-                    sph_k = live ? 0 : wf.n_spheres; // spheres are tested as a phase of their own below
+                    // spheres are tested as a phase of their own below, and only those whose box the ray touches
+                    sph_k = (SPH && live) ? next_sphere(wf.spheres, wf.n_spheres, 0, ox, oy, oz, idx, idy, idz, ht) : wf.n_spheres;
                 }
             }
         }
@@ -252,25 +301,28 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                         sph_k = wf.n_spheres;
                     }
                 }
-                sph_k++;
+                sph_k = next_sphere(wf.spheres, wf.n_spheres, sph_k + 1, ox, oy, oz, idx, idy, idz, ht);
             }
         } else if (c_tri >= c_node) {
             if (want_tri) {
-                const int ti = __ffs(tg.y) - 1;
-                tg.y &= tg.y - 1u;
-                const float4 *tp = wf.bvh.tris + 3 * size_t(tg.x + ti);
-                const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
-                TriHit th;
-                if ((!SHADOW || __float_as_int(v0.w) != skip_prim) &&
-                    intersect_triangle(ox, oy, oz, dx, dy, dz, ht, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, th)) {
-                    ht = th.t;
-                    hb1 = th.b1;
-                    hb2 = th.b2;
-                    hprim = int(tg.x + ti);
-                    if (SHADOW) {
-                        tg.y = 0u;
-                        ng.y = 0u;
-                        sp = 0;
+#pragma unroll 1
+                for (int step = 0; step < tri_steps && tg.y != 0u; step++) {
+                    const int ti = __ffs(tg.y) - 1;
+                    tg.y &= tg.y - 1u;
+                    const float4 *tp = wf.bvh.tris + 3 * size_t(tg.x + ti);
+                    const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                    TriHit th;
+                    if ((!SHADOW || __float_as_int(v0.w) != skip_prim) && !(__float_as_uint(v1.w) & kTriDegenerate) &&
+                        intersect_triangle_sheared(ox, oy, oz, rs, ht, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, th)) {
+                        ht = th.t;
+                        hb1 = th.b1;
+                        hb2 = th.b2;
+                        hprim = int(tg.x + ti);
+                        if (SHADOW) {
+                            tg.y = 0u;
+                            ng.y = 0u;
+                            sp = 0;
+                        }
                     }
                 }
             }
@@ -341,13 +393,20 @@ int launch_trace_wf(b200pt_scene *s, const WF &wf, bool shadow) {
 
 typedef void (*TraceKernel)(TraceParams);
 
+template <int REFILL, int TRI_STEPS>
+static TraceKernel pick_kernel2(bool any_hit, bool counting) {
+    return any_hit ? (counting ? k_trace<true, true, REFILL, TRI_STEPS> : k_trace<true, false, REFILL, TRI_STEPS>)
+                   : (counting ? k_trace<false, true, REFILL, TRI_STEPS> : k_trace<false, false, REFILL, TRI_STEPS>);
+}
 template <int REFILL>
-static TraceKernel pick_kernel(bool any_hit, bool counting) {
-    return any_hit ? (counting ? k_trace<true, true, REFILL> : k_trace<true, false, REFILL>)
-                   : (counting ? k_trace<false, true, REFILL> : k_trace<false, false, REFILL>);
+static TraceKernel pick_kernel(bool any_hit, bool counting, int tri_steps) {
+    return tri_steps <= 1 ? pick_kernel2<REFILL, 1>(any_hit, counting)
+         : tri_steps == 2 ? pick_kernel2<REFILL, 2>(any_hit, counting)
+                          : pick_kernel2<REFILL, 3>(any_hit, counting);
 }
 
-int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev, bool keep_status) {
+int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev, bool keep_status,
+                 const TraceHostIO *io) {
     if (!s->built) {
         set_error("b200pt_trace: call b200pt_bvh_build first");
         return B200PT_ERR_STATE;
@@ -357,23 +416,30 @@ int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, 
     p.bvh = s->bvh;
     p.rays = (const float4 *)rays_dev;
     p.hits = (float4 *)hits_dev;
+    p.o = io ? io->o : nullptr;
+    p.d = io ? io->d : nullptr;
+    p.tmax = io ? io->tmax : nullptr;
+    p.prim_out = io ? io->prim : nullptr;
+    p.t_out = io ? io->t : nullptr;
+    p.b12_out = io ? io->b12 : nullptr;
     p.n = n;
     p.counters = s->d_trace_counters;
     p.prmt_bias = 0x47000000u;
-    CU_TRY(cudaMemsetAsync(s->d_trace_counters, 0, (keep_status ? 1 : 4) * sizeof(unsigned long long), s->stream));
+    // per launch: the work ticket and (unless this is a later chunk of one batch) the visit counters.  The overflow word
+    // [3] is STICKY across launches -- back-to-back asynchronous launches must not wipe an earlier launch's report; it is
+    // cleared when the host reads it (check_trace_status).
+    CU_TRY(cudaMemsetAsync(s->d_trace_counters, 0, (keep_status ? 1 : 3) * sizeof(unsigned long long), s->stream));
 
-    // tuning knobs (defaults are the measured best)
-    static const int refill = getenv("B200PT_REFILL") ? atoi(getenv("B200PT_REFILL")) : 4;
-    static const int cta_per_sm_cap = getenv("B200PT_TRACE_CTAS") ? atoi(getenv("B200PT_TRACE_CTAS")) : 0;
-    TraceKernel kern = refill <= 1 ? pick_kernel<1>(any_hit, s->counting)
-                     : refill <= 4 ? pick_kernel<4>(any_hit, s->counting)
-                     : refill <= 8 ? pick_kernel<8>(any_hit, s->counting)
-                     : refill <= 16 ? pick_kernel<16>(any_hit, s->counting)
-                                    : pick_kernel<32>(any_hit, s->counting);
+    // tuning knobs (defaults are the measured best; b200pt_trace_tune overrides them per scene)
+    const int refill = s->tune_refill, tri_steps = s->tune_tri_steps;
+    TraceKernel kern = refill <= 1 ? pick_kernel<1>(any_hit, s->counting, tri_steps)
+                     : refill <= 4 ? pick_kernel<4>(any_hit, s->counting, tri_steps)
+                     : refill <= 8 ? pick_kernel<8>(any_hit, s->counting, tri_steps)
+                                   : pick_kernel<16>(any_hit, s->counting, tri_steps);
     int per_sm = 0;
     CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TRACE_BLOCK, 0));
     if (per_sm < 1) per_sm = 1;
-    if (cta_per_sm_cap > 0 && per_sm > cta_per_sm_cap) per_sm = cta_per_sm_cap;
+    if (s->tune_ctas_per_sm > 0 && per_sm > s->tune_ctas_per_sm) per_sm = s->tune_ctas_per_sm;
     long long blocks = (long long)s->sm_count * per_sm;
     const long long needed = (n + TRACE_BLOCK - 1) / TRACE_BLOCK;
     if (blocks > needed) blocks = needed;

@@ -33,51 +33,57 @@ struct TriHit {
 #define B200PT_GAMMA3 __uint_as_float(0x34400002u)
 #define B200PT_GAMMA5 __uint_as_float(0x34A00003u)
 
-__device__ __forceinline__ bool intersect_triangle(float ox, float oy, float oz, float dirx,
-                                                   float diry, float dirz, float t_max, float p0x_,
-                                                   float p0y_, float p0z_, float p1x_, float p1y_,
-                                                   float p1z_, float p2x_, float p2y_, float p2z_,
-                                                   TriHit &out) {
-    // :218 degenerate triangle: |(p2-p0) x (p1-p0)|^2 == 0
-    {
-        const float ax = __fsub_rn(p2x_, p0x_), ay = __fsub_rn(p2y_, p0y_), az = __fsub_rn(p2z_, p0z_);
-        const float bx = __fsub_rn(p1x_, p0x_), by = __fsub_rn(p1y_, p0y_), bz = __fsub_rn(p1z_, p0z_);
-        const float cx = dop(ay, bz, az, by);
-        const float cy = dop(az, bx, ax, bz);
-        const float cz = dop(ax, by, ay, bx);
-        const float sq = __fmaf_rn(cz, cz, __fmaf_rn(cx, cx, __fmul_rn(cy, cy)));
-        if (sq == 0.0f) return false;
-    }
+// :218 degenerate triangle: |(p2-p0) x (p1-p0)|^2 == 0.  Depends on the triangle alone: the accelerator build
+// evaluates it once per triangle and stores the answer as a flag bit of the leaf record (bvh_build.cu).
+__device__ __forceinline__ bool triangle_is_degenerate(float p0x, float p0y, float p0z, float p1x, float p1y, float p1z,
+                                                       float p2x, float p2y, float p2z) {
+    const float ax = __fsub_rn(p2x, p0x), ay = __fsub_rn(p2y, p0y), az = __fsub_rn(p2z, p0z);
+    const float bx = __fsub_rn(p1x, p0x), by = __fsub_rn(p1y, p0y), bz = __fsub_rn(p1z, p0z);
+    const float cx = dop(ay, bz, az, by);
+    const float cy = dop(az, bx, ax, bz);
+    const float cz = dop(ax, by, ay, bx);
+    const float sq = __fmaf_rn(cz, cz, __fmaf_rn(cx, cx, __fmul_rn(cy, cy)));
+    return sq == 0.0f;
+}
+
+// :229-249 the ray-only part of the test: the permutation that makes the largest |d| component z
+// (vector3.h:103-105) and the shear constants -- three IEEE divides that depend on the direction alone, so the
+// trace kernels evaluate them once per ray (at ray fetch) instead of once per (ray, triangle) pair.
+struct RayShear {
+    float Sx, Sy, Sz;
+    int kz;
+};
+
+__device__ __forceinline__ RayShear ray_shear(float dirx, float diry, float dirz) {
+    const float adx = fabsf(dirx), ady = fabsf(diry), adz = fabsf(dirz);
+    RayShear r;
+    r.kz = (adx > ady) ? ((adx > adz) ? 0 : 2) : ((ady > adz) ? 1 : 2);
+    const float dx = r.kz == 0 ? diry : (r.kz == 1 ? dirz : dirx); // kx = kz + 1
+    const float dy = r.kz == 0 ? dirz : (r.kz == 1 ? dirx : diry); // ky = kx + 1
+    const float dz = r.kz == 0 ? dirx : (r.kz == 1 ? diry : dirz);
+    r.Sx = __fdiv_rn(-dx, dz);
+    r.Sy = __fdiv_rn(-dy, dz);
+    r.Sz = __fdiv_rn(1.0f, dz);
+    return r;
+}
+
+// the per-(ray, triangle) part; the caller has rejected degenerate triangles (leaf-record flag)
+__device__ __forceinline__ bool intersect_triangle_sheared(float ox, float oy, float oz, const RayShear &rs, float t_max,
+                                                           float p0x_, float p0y_, float p0z_, float p1x_, float p1y_,
+                                                           float p1z_, float p2x_, float p2y_, float p2z_, TriHit &out) {
     // :224-226 translate to the ray origin
     const float q0x = __fsub_rn(p0x_, ox), q0y = __fsub_rn(p0y_, oy), q0z = __fsub_rn(p0z_, oz);
     const float q1x = __fsub_rn(p1x_, ox), q1y = __fsub_rn(p1y_, oy), q1z = __fsub_rn(p1z_, oz);
     const float q2x = __fsub_rn(p2x_, ox), q2y = __fsub_rn(p2y_, oy), q2z = __fsub_rn(p2z_, oz);
 
-    // :229-238 permute so the largest |d| component is z (vector3.h:103-105)
-    const float adx = fabsf(dirx), ady = fabsf(diry), adz = fabsf(dirz);
-    const int kz = (adx > ady) ? ((adx > adz) ? 0 : 2) : ((ady > adz) ? 1 : 2);
-    float dx, dy, dz, p0x, p0y, p0z, p1x, p1y, p1z, p2x, p2y, p2z;
-    if (kz == 0) { // kx = 1, ky = 2
-        dx = diry; dy = dirz; dz = dirx;
-        p0x = q0y; p0y = q0z; p0z = q0x;
-        p1x = q1y; p1y = q1z; p1z = q1x;
-        p2x = q2y; p2y = q2z; p2z = q2x;
-    } else if (kz == 1) { // kx = 2, ky = 0
-        dx = dirz; dy = dirx; dz = diry;
-        p0x = q0z; p0y = q0x; p0z = q0y;
-        p1x = q1z; p1y = q1x; p1z = q1y;
-        p2x = q2z; p2y = q2x; p2z = q2y;
-    } else { // kx = 0, ky = 1
-        dx = dirx; dy = diry; dz = dirz;
-        p0x = q0x; p0y = q0y; p0z = q0z;
-        p1x = q1x; p1y = q1y; p1z = q1z;
-        p2x = q2x; p2y = q2y; p2z = q2z;
-    }
+    // :229-238 permute (selects, no divergence: kz differs from lane to lane)
+    const bool k0 = rs.kz == 0, k1 = rs.kz == 1;
+    float p0x = k0 ? q0y : (k1 ? q0z : q0x), p0y = k0 ? q0z : (k1 ? q0x : q0y), p0z = k0 ? q0x : (k1 ? q0y : q0z);
+    float p1x = k0 ? q1y : (k1 ? q1z : q1x), p1y = k0 ? q1z : (k1 ? q1x : q1y), p1z = k0 ? q1x : (k1 ? q1y : q1z);
+    float p2x = k0 ? q2y : (k1 ? q2z : q2x), p2y = k0 ? q2z : (k1 ? q2x : q2y), p2z = k0 ? q2x : (k1 ? q2y : q2z);
 
     // :241-249 shear
-    const float Sx = __fdiv_rn(-dx, dz);
-    const float Sy = __fdiv_rn(-dy, dz);
-    const float Sz = __fdiv_rn(1.0f, dz);
+    const float Sx = rs.Sx, Sy = rs.Sy, Sz = rs.Sz;
     p0x = __fmaf_rn(Sx, p0z, p0x);
     p0y = __fmaf_rn(Sy, p0z, p0y);
     p1x = __fmaf_rn(Sx, p1z, p1x);
@@ -140,6 +146,15 @@ __device__ __forceinline__ bool intersect_triangle(float ox, float oy, float oz,
     out.b2 = b2;
     out.t = t;
     return true;
+}
+
+// the whole predicate as the reference evaluates it per call (probe entry point, light sampling, per-thread walks)
+__device__ __forceinline__ bool intersect_triangle(float ox, float oy, float oz, float dirx, float diry, float dirz,
+                                                   float t_max, float p0x, float p0y, float p0z, float p1x, float p1y,
+                                                   float p1z, float p2x, float p2y, float p2z, TriHit &out) {
+    if (triangle_is_degenerate(p0x, p0y, p0z, p1x, p1y, p1z, p2x, p2y, p2z)) return false;
+    const RayShear rs = ray_shear(dirx, diry, dirz);
+    return intersect_triangle_sheared(ox, oy, oz, rs, t_max, p0x, p0y, p0z, p1x, p1y, p1z, p2x, p2y, p2z, out);
 }
 
 } // namespace b200pt

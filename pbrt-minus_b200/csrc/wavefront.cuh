@@ -84,20 +84,28 @@ struct PathPool {
     uint8_t *state; // ST_*
 };
 
-struct WFCounters {
+// Queue sizes and work tickets of ONE pass.  There are two sets, used by alternate passes (wf.parity): every count is
+// produced and consumed inside its pass, so the logic stage of pass p clears the set of pass p + 1 and no separate
+// "reset the counters" launches are needed between the stages.
+struct WFPass {
     unsigned n_mat[WF_NMAT];
     unsigned n_free;
     unsigned n_shadow;
-    unsigned ticket_closest;
+    unsigned n_emit; // hits on emissive triangles this pass (k_logic -> k_emit)
+    unsigned n_vol;  // media: paths that scatter this pass (k_volume<0> -> k_volume<1>)
+    unsigned ticket_closest, ticket_shadow;
+};
+struct WFCounters {
+    WFPass p[2];
     unsigned long long next_path, finished, rays_closest, rays_shadow;
-    unsigned stack_overflow, ticket_shadow;
-    unsigned n_vol; // media: paths that scatter this pass (k_volume<0> -> k_volume<1>)
+    unsigned stack_overflow;
 };
 
 struct WFQueues {
     int32_t *mat[WF_NMAT];
     int32_t *free_slots;
     int32_t *vol; // media scenes only: slots that scatter inside a medium this pass
+    int32_t *emit; // slots whose ray hit an emissive triangle this pass
     // shadow rays: compact SoA by queue position
     float4 *sh_o, *sh_d, *sh_contrib;
     int32_t *sh_slot;
@@ -107,6 +115,7 @@ struct WF {
     PathPool pool;
     WFQueues q;
     WFCounters *c;
+    int32_t parity; // which WFPass set this pass uses
     int32_t pool_size;
     // scene
     BVH8 bvh;
@@ -132,6 +141,7 @@ struct WF {
     int32_t n_infinite;      // infinite lights looked up by escaping rays (integrators/wavefront_path.cu:105-127)
     int32_t infinite[4];     // their light ids
     int32_t refill_min;      // k_trace_wf: a warp fetches new rays once this many lanes are idle
+    int32_t tri_steps;       // k_trace_wf: triangle tests a lane runs per triangle phase
     int32_t has_mix;         // some material is a mix (resolved in k_logic, materials/mix_material.cu)
     float scene_radius;      // Bounds3::bounding_sphere of the whole scene (scene_builder.cu:914-925)
     FilterTab filter;
@@ -192,7 +202,8 @@ __device__ __forceinline__ void block_push(const WF &wf, int cat, int32_t value)
             s_warp[threadIdx.x][w] = total;
             total += v;
         }
-        unsigned *counter = threadIdx.x < WF_NMAT ? &wf.c->n_mat[threadIdx.x] : &wf.c->n_free;
+        WFPass &pc = wf.c->p[wf.parity];
+        unsigned *counter = threadIdx.x < WF_NMAT ? &pc.n_mat[threadIdx.x] : &pc.n_free;
         s_base[threadIdx.x] = total ? atomicAdd(counter, total) : 0u;
     }
     __syncthreads();

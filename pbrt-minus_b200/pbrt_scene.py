@@ -1056,8 +1056,9 @@ def load(path=None, text=None, spp=None, integrator=None, scene_dir=None):
         elif kw == "ConcatTransform":
             g.ctm = g.ctm * Xf(np.array(args[0], dtype=F32).reshape(4, 4).T)
         elif kw == "CoordSysTransform":
-            if args[0] in named_cs:
-                g.ctm = named_cs[args[0]].copy()
+            if args[0] not in named_cs:   # fatal in the reference too (scene/scene_builder.cu:309-314)
+                raise SceneError("CoordSysTransform: unknown coordinate system %r" % (args[0],))
+            g.ctm = named_cs[args[0]].copy()
         elif kw == "ReverseOrientation":
             g.reverse_orientation = not g.reverse_orientation
         elif kw == "Material":

@@ -109,3 +109,49 @@ def test_bruteforce_semantics(oracle):
     assert prim[0] == 1 and t[0] == 1.0 and t2[0] == 1.0
     assert oracle.any_hit(P, idx, [[0.25, 0.25, 0]], [[0, 0, 1]], 0.5)[0] == False  # noqa: E712
     assert oracle.any_hit(P, idx, [[0.25, 0.25, 0]], [[0, 0, 1]], 1.5)[0] == True  # noqa: E712
+
+
+def test_host_bvh_equals_bruteforce(oracle, b200pt):
+    """the oracle's host BVH (the reference's traversal loop over the oracle's own tree) gives the brute-force answers:
+    ids and t bit-exact for closest hit, the same flags for any hit -- on a soup, on coincident triangles (exact ties are
+    near ties by definition) and on an empty scene"""
+    wl = b200pt.workloads
+    P, idx = wl.triangle_soup(30000, seed=3)
+    o, d, tm = wl.primary_rays(120, 80)
+    prim, t, b, t2 = oracle.closest_hit(P, idx, o, d, tm, want_t2=True)
+    bvh = oracle.HostBVH(P, idx)
+    assert bvh.node_count() > 1000
+    p2, t2b, b2 = bvh.closest_hit(o, d, tm)
+    mism, near = oracle.compare_closest(P, idx, o, d, tm, p2, t2b, prim, t)
+    assert mism == 0
+    same = p2 == prim
+    assert same.sum() >= len(prim) - near
+    assert np.array_equal(t[same].view(np.uint32), t2b[same].view(np.uint32))
+    assert np.array_equal(b[same], b2[same])
+    bo, bd, bt = wl.bounce_rays(P, idx, o, d, prim, t, seed=7)
+    pb, tb, _ = oracle.closest_hit(P, idx, bo, bd, bt)
+    pb2, tb2, _ = bvh.closest_hit(bo, bd, bt)
+    assert oracle.compare_closest(P, idx, bo, bd, bt, pb2, tb2, pb, tb)[0] == 0
+    so, sd, st = wl.shadow_rays(P, idx, o, d, prim, t, seed=11)
+    assert np.array_equal(oracle.any_hit(P, idx, so, sd, st), bvh.any_hit(so, sd, st))
+    # a finite t_max is honoured exactly as by brute force (the cut sits right at the first hit: both sides of the
+    # inclusive `tScaled > t_max * det` reject, shapes/triangle.cu:284-290, get exercised)
+    hit = prim >= 0
+    for tm2 in (t[hit], np.nextafter(t[hit], np.float32(0)), t[hit] * np.float32(1.5)):
+        pa, ta, _ = oracle.closest_hit(P, idx, o[hit], d[hit], tm2)
+        pb3, tb3, _ = bvh.closest_hit(o[hit], d[hit], tm2)
+        assert oracle.compare_closest(P, idx, o[hit], d[hit], tm2, pb3, tb3, pa, ta)[0] == 0
+    # coincident triangles: whichever is reported, the comparison calls it a near tie, not a mismatch
+    Pc = np.array([[0, 0, 1], [1, 0, 1], [0, 1, 1]] * 2 + [[0, 0, 2], [1, 0, 2], [0, 1, 2]], np.float32)
+    ic = np.arange(9, dtype=np.int32).reshape(3, 3)
+    bc = oracle.HostBVH(Pc, ic)
+    pc, tc, _ = bc.closest_hit([[0.25, 0.25, 0]], [[0, 0, 1]], np.inf)
+    assert pc[0] in (0, 1) and tc[0] == 1.0
+    assert oracle.compare_closest(Pc, ic, [[0.25, 0.25, 0]], [[0, 0, 1]], np.inf, np.array([0]), np.array([1.0], np.float32), np.array([1]),
+                                  np.array([1.0], np.float32)) == (0, 1)
+    assert oracle.compare_closest(Pc, ic, [[0.25, 0.25, 0]], [[0, 0, 1]], np.inf, np.array([2]), np.array([2.0], np.float32), np.array([1]),
+                                  np.array([1.0], np.float32)) == (1, 0)
+    # empty scene
+    be = oracle.HostBVH(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.int32))
+    pe, te, _ = be.closest_hit(o[:5], d[:5], np.inf)
+    assert (pe == -1).all() and np.isinf(te).all()
