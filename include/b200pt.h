@@ -117,10 +117,12 @@ typedef struct {
  *      one DiffuseAreaLight per emissive triangle; DistantLight (lights/distant_light.cu), UniformInfiniteLight
  *      (lights/uniform_infinite_light.cu) and SpotLight (lights/spot_light.cu) from "LightSource" */
 enum { B200PT_LIGHT_AREA = 0, B200PT_LIGHT_DISTANT = 1, B200PT_LIGHT_UNIFORM_INFINITE = 2, B200PT_LIGHT_SPOT = 3,
-       B200PT_LIGHT_IMAGE_INFINITE = 4 /* lights/image_infinite_light.cu: `image` in the equal-area octahedral parameterisation;
-                                          needs rgb2spec_fit; at most one per scene */ };
+       B200PT_LIGHT_IMAGE_INFINITE = 4, /* lights/image_infinite_light.cu: `image` in the equal-area octahedral parameterisation;
+                                          needs rgb2spec_fit; at most one per scene */
+       B200PT_LIGHT_SPHERE_AREA = 5 /* DiffuseAreaLight over Shape "sphere" (Sphere::sample / Sphere::pdf, shapes/sphere.cu:162-280):
+                                       `triangle` holds the index into the spheres array, whose `light` names this light back */ };
 typedef struct {
-    int32_t triangle;  /* AREA: index into the triangle array; other types: -1 */
+    int32_t triangle;  /* AREA: index into the triangle array; SPHERE_AREA: index into the spheres array; other types: -1 */
     int32_t spectrum;  /* Lemit / I spectrum id */
     float scale;       /* already divided by the photometric integral (and times illuminance / power factors) */
     int32_t two_sided;
@@ -139,7 +141,7 @@ typedef struct {
     float radius, z_min, z_max, phi_max; /* phi_max in radians; theta range derived from z */
     int32_t reverse_orientation, transform_swaps_handedness;
     int32_t material; /* material id */
-    int32_t light;    /* -1: spheres as emitters are not supported */
+    int32_t light;    /* -1: not emissive; else the index of its B200PT_LIGHT_SPHERE_AREA light (spheres only, not disks) */
     int32_t kind;     /* 0 sphere (shapes/sphere.{h,cu}); 1 disk (shapes/disk.{h,cu}): z_min = height, z_max = inner radius */
 } b200pt_sphere;
 

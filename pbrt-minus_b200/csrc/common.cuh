@@ -58,6 +58,7 @@ struct SphereRec {
     int flip; // reverse_orientation ^ transform_swaps_handedness
     int material;
     int kind; // 0 sphere; 1 disk: z_min = height, z_max = inner radius
+    int light; // -1, or the light id of this emissive sphere
     // render-space AABB of the quadric, padded: a ray that misses it cannot pass the interval-arithmetic test, so the
     // trace kernels skip that (long) test for most rays
     float box_lo[3], box_hi[3];

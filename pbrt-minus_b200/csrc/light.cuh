@@ -13,6 +13,7 @@
 
 #include "common.cuh"
 #include "sampler.cuh"
+#include "sphere.cuh"
 #include "triangle.cuh"
 #include "vecmath.cuh"
 
@@ -315,6 +316,100 @@ __device__ __forceinline__ float light_pdf(const LightRec &L, const LightCtx &ct
         pdf *= bilinear_pdf(u, w);
     }
     return pdf;
+}
+
+// ---- DiffuseAreaLight over Shape "sphere": Sphere::sample(ctx, u) / Sphere::pdf(ctx, wi) (shapes/sphere.cu:162-280) -----------
+// LightRec of such a light: prim = n_triangles + sphere index (the shadow ray's own-primitive skip), ext = sphere index,
+// area = Sphere::area() (shapes/sphere.h:23-25), flags bit 1 = reverse_orientation (the sampled normal flips on it alone).
+// Like the reference, the cone branch treats `radius` as a render-space length (a scaled sphere light is sampled as if unscaled).
+
+// Sphere::sample(u) (shapes/sphere.cu:131-160): uniform over the FULL sphere's area, used when the reference point is inside
+__device__ __forceinline__ void sphere_sample_area(const SphereRec &S, bool reverse, float2 u, V3 *p, V3 *err, V3 *n) {
+    V3 pObj = S.radius * sample_uniform_sphere(u);
+    pObj = pObj * (S.radius / len(pObj));
+    const V3 pObjErr = gamma_n(5) * vabs(pObj);
+    V3 nr = normalize(xf_normal(S.ofr, pObj));
+    if (reverse) nr = -nr;
+    *p = xf_point(S.rfo, pObj);
+    *err = xf_point_error(S.rfo, pObj, pObjErr, false);
+    *n = nr;
+}
+
+__device__ __forceinline__ bool sphere_light_sample(const SphereRec &S, const LightRec &L, const LightCtx &ctx, float2 u, LightSample &ls) {
+    const V3 pCenter = v3(S.rfo[3], S.rfo[7], S.rfo[11]); // render_from_object(0, 0, 0)
+    const V3 pOrigin = offset_ray_origin(ctx.p, ctx.err, ctx.n, pCenter - ctx.p);
+    const bool reverse = (L.flags & 2) != 0;
+    if (len2(pOrigin - pCenter) <= sqr(S.radius)) {
+        // inside: sample by area, convert to solid angle
+        V3 p, err, n;
+        sphere_sample_area(S, reverse, u, &p, &err, &n);
+        V3 wi = p - ctx.p;
+        if (len2(wi) == 0.f) return false;
+        wi = normalize(wi);
+        float pdf = 1.f / L.area;
+        pdf *= len2(ctx.p - p) / absdot(n, -wi);
+        if (isinf(pdf)) return false;
+        ls.p = p; ls.err = err; ls.n = n; ls.pdf = pdf; ls.wi = wi;
+        return pdf != 0.f;
+    }
+    // uniform inside the subtended cone
+    const float sinThetaMax = S.radius / len(ctx.p - pCenter);
+    const float sin2ThetaMax = sqr(sinThetaMax);
+    const float cosThetaMax = safe_sqrt(1.f - sin2ThetaMax);
+    float oneMinusCosThetaMax = 1.f - cosThetaMax;
+    float cosTheta = (cosThetaMax - 1.f) * u.x + 1.f;
+    float sin2Theta = 1.f - sqr(cosTheta);
+    if (sin2ThetaMax < 0.00068523f) { // sin^2(1.5 deg): Taylor expansion for small angles
+        sin2Theta = sin2ThetaMax * u.x;
+        cosTheta = sqrtf(1.f - sin2Theta);
+        oneMinusCosThetaMax = sin2ThetaMax / 2.f;
+    }
+    const float cosAlpha = sin2Theta / sinThetaMax + cosTheta * safe_sqrt(1.f - sin2Theta / sqr(sinThetaMax));
+    const float sinAlpha = safe_sqrt(1.f - sqr(cosAlpha));
+    const float phi = u.y * 2.f * kPi;
+    float sp, cp;
+    sincosf(phi, &sp, &cp);
+    const V3 w = v3(clampf(sinAlpha, -1.f, 1.f) * cp, clampf(sinAlpha, -1.f, 1.f) * sp, clampf(cosAlpha, -1.f, 1.f)); // SphericalDirection
+    Frame fr;
+    fr.z = normalize(pCenter - ctx.p);
+    coordinate_system(fr.z, &fr.x, &fr.y);
+    V3 n = fr.from_local(-w);
+    const V3 p = pCenter + S.radius * n;
+    if (reverse) n = -n;
+    ls.p = p;
+    ls.err = gamma_n(5) * vabs(p);
+    ls.n = n;
+    ls.pdf = 1.f / (2.f * kPi * oneMinusCosThetaMax);
+    if (ls.pdf == 0.f || len2(p - ctx.p) == 0.f) return false;
+    ls.wi = normalize(p - ctx.p);
+    return true;
+}
+
+// normal of a sphere hit as Sphere::interaction_from_intersection leaves it in Interaction::n (shapes/sphere.h:71-125):
+// needed by Sphere::pdf's inside branch
+__device__ __forceinline__ V3 sphere_hit_normal(const SphereRec &S, V3 pObj) {
+    V3 n = normalize(xf_normal(S.ofr, pObj));
+    return S.flip ? -n : n;
+}
+
+__device__ __forceinline__ float sphere_light_pdf(const SphereRec &S, const LightRec &L, const LightCtx &ctx, V3 wi) {
+    const V3 pCenter = v3(S.rfo[3], S.rfo[7], S.rfo[11]);
+    const V3 pOrigin = offset_ray_origin(ctx.p, ctx.err, ctx.n, pCenter - ctx.p);
+    if (len2(pOrigin - pCenter) <= sqr(S.radius)) {
+        const V3 o = offset_ray_origin(ctx.p, ctx.err, ctx.n, wi);
+        SphereHit sh;
+        if (!sphere_intersect(S, o, wi, kInf, sh)) return 0.f;
+        const V3 ph = xf_point(S.rfo, sh.p_obj);
+        const V3 n = sphere_hit_normal(S, sh.p_obj);
+        float pdf = len2(ctx.p - ph) / (L.area * absdot(n, -wi));
+        if (isinf(pdf)) pdf = 0.f;
+        return pdf;
+    }
+    const float sin2ThetaMax = S.radius * S.radius / len2(ctx.p - pCenter);
+    const float cosThetaMax = safe_sqrt(1.f - sin2ThetaMax);
+    float oneMinusCosThetaMax = 1.f - cosThetaMax;
+    if (sin2ThetaMax < 0.00068523f) oneMinusCosThetaMax = sin2ThetaMax / 2.f;
+    return (float)(1.0 / (2.0 * (double)kPi * (double)oneMinusCosThetaMax));
 }
 
 // AliasTable::sample (distribution/alias_table.cu:70-87): the second variate is a hash of the first

@@ -271,9 +271,20 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
                     o.box_hi[a] += pad;
                 }
             }
+            o.light = sp.light;
             if (sp.light >= 0) {
-                set_error("b200pt_scene_create: emissive spheres are not supported");
-                return B200PT_ERR_UNSUPPORTED;
+                if (sp.kind != 0) {
+                    set_error("b200pt_scene_create: emissive disks are not supported");
+                    return B200PT_ERR_UNSUPPORTED;
+                }
+                if (sp.light >= desc->n_lights || !desc->lights || desc->lights[sp.light].type != B200PT_LIGHT_SPHERE_AREA ||
+                    desc->lights[sp.light].triangle != i) {
+                    set_error("b200pt_scene_create: quadric %d: light %d is not a sphere area light on it", i, sp.light);
+                    return B200PT_ERR_INVALID;
+                }
+            } else if (sp.light != -1) {
+                set_error("b200pt_scene_create: quadric %d has light id %d", i, sp.light);
+                return B200PT_ERR_INVALID;
             }
         }
         CU_TRY(cudaMalloc((void **)&s->d_spheres, recs.size() * sizeof(SphereRec)));
@@ -498,6 +509,26 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
     bool any_other = false;
     for (int i = 0; i < desc->n_lights; i++) {
         const b200pt_light &l = desc->lights[i];
+        if (l.type == B200PT_LIGHT_SPHERE_AREA) {
+            if (l.triangle < 0 || l.triangle >= desc->n_spheres || !spec_ok(l.spectrum) || desc->spheres[l.triangle].light != i ||
+                desc->spheres[l.triangle].kind != 0) {
+                set_error("b200pt_scene_create: light %d is not consistent with the sphere it names", i);
+                return B200PT_ERR_INVALID;
+            }
+            const b200pt_sphere &sp = desc->spheres[l.triangle];
+            LightRec &o = lights[i];
+            memset(&o, 0, sizeof(o));
+            o.scale = l.scale;
+            o.spectrum = l.spectrum;
+            o.flags = (l.two_sided ? 1 : 0) | (sp.reverse_orientation ? 2 : 0) | (B200PT_LIGHT_SPHERE_AREA << 4);
+            const float zmin = std::min(std::max(std::min(sp.z_min, sp.z_max), -sp.radius), sp.radius);
+            const float zmax = std::min(std::max(std::max(sp.z_min, sp.z_max), -sp.radius), sp.radius);
+            o.area = sp.phi_max * sp.radius * (zmax - zmin); // Sphere::area (shapes/sphere.h:23-25)
+            o.prim = (int32_t)desc->n_triangles + l.triangle;  // what this light's own shadow rays skip
+            o.ext = l.triangle;
+            r->n_area_lights++;
+            continue;
+        }
         if (l.type != B200PT_LIGHT_AREA) {
             if (l.type < 0 || l.type > B200PT_LIGHT_IMAGE_INFINITE || (l.type != B200PT_LIGHT_IMAGE_INFINITE && !spec_ok(l.spectrum))) {
                 set_error("b200pt_scene_create: light %d is inconsistent (type %d)", i, l.type);
@@ -1273,6 +1304,7 @@ __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
                 S4 Le_env = s4(0.f);
                 const bool is_env = lt == B200PT_LIGHT_IMAGE_INFINITE;
                 if (lt == B200PT_LIGHT_AREA) have = light_sample(Lr, ctx, up, ls) && light_emits_towards(Lr, ls.n, -ls.wi);
+                    else if (lt == B200PT_LIGHT_SPHERE_AREA) have = sphere_light_sample(wf.spheres[Lr.ext], Lr, ctx, up, ls) && light_emits_towards(Lr, ls.n, -ls.wi);
                 else if (is_env) have = env_nee(wf, ctx.p, up, lambda, ls, Le_env);
                 else have = light_sample_other(Lr, lt, wf.light_ext, wf.scene_radius, ctx, up, ls, &lw, &ld2, &delta);
                 if (have) {
@@ -1413,6 +1445,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                 int mat;
                 if (prim >= (int)wf.bvh.n_tris) {
                     mat = wf.spheres[prim - (int)wf.bvh.n_tris].material;
+                    if (wf.spheres[prim - (int)wf.bvh.n_tris].light >= 0) emit = 1 | ((depth == 0 || (ids.w & PF_SPECULAR)) ? 2 : 0);
                 } else {
                     const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
                     const float4 v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
@@ -1473,11 +1506,23 @@ __global__ void __launch_bounds__(WF_BLOCK) k_emit(WF wf) {
         const int slot = e & 0x7fffffff;
         const bool raw = e < 0;
         const float4 hit = wf.pool.hit[slot];
-        const float4 *tp = wf.bvh.tris + 3 * (size_t)__float_as_int(hit.x);
-        const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
-        const LightRec Lr = wf.lights[__float_as_int(v2.w)];
-        const V3 n_g = tri_normal(v3(v0), v3(v1), v3(v2), (__float_as_uint(v1.w) >> 31) != 0u);
+        const int prim = __float_as_int(hit.x);
         const V3 rd = v3(wf.pool.ray_d[slot]);
+        const bool on_sphere = prim >= (int)wf.bvh.n_tris;
+        LightRec Lr;
+        V3 n_g;
+        if (on_sphere) {
+            const SphereRec &sp = wf.spheres[prim - (int)wf.bvh.n_tris];
+            Lr = wf.lights[sp.light];
+            Isect si;
+            sphere_interaction(sp, v3(wf.pool.ray_o[slot]), rd, hit.y, -rd, si);
+            n_g = si.n;
+        } else {
+            const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
+            const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+            Lr = wf.lights[__float_as_int(v2.w)];
+            n_g = tri_normal(v3(v0), v3(v1), v3(v2), (__float_as_uint(v1.w) >> 31) != 0u);
+        }
         if (!light_emits_towards(Lr, n_g, -rd)) continue;
         const S4 Le = spectrum_sample(wf.spectra, Lr.spectrum, wf.pool.lambda[slot]) * Lr.scale;
         if (!is_positive(Le)) continue;
@@ -1488,7 +1533,7 @@ __global__ void __launch_bounds__(WF_BLOCK) k_emit(WF wf) {
         } else {
             const float4 c0 = wf.pool.ctx0[slot], c1 = wf.pool.ctx1[slot], c2 = wf.pool.ctx2[slot];
             const LightCtx ctx{v3(c0), v3(c0.w, c1.w, c2.w), v3(c1), v3(c2)};
-            const float pdf_light = Lr.pmf * light_pdf(Lr, ctx, rd);
+            const float pdf_light = Lr.pmf * (on_sphere ? sphere_light_pdf(wf.spheres[Lr.ext], Lr, ctx, rd) : light_pdf(Lr, ctx, rd));
             const float dir_pdf_scale = wf.has_media ? average(wf.pool.mtp[slot]) : 1.f; // multi_transmittance_pdf.average() (:165)
             const float dir_pdf = wf.pool.misc[slot].y * dir_pdf_scale;
             L = L + beta * Le * power_heuristic(dir_pdf, pdf_light);
@@ -1705,6 +1750,7 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
                     S4 Le_env = s4(0.f);
                     const bool is_env = EXT && lt == B200PT_LIGHT_IMAGE_INFINITE; // such scenes run the extended kernels
                     if (lt == B200PT_LIGHT_AREA) have = light_sample(Lr, ctx, up, ls) && light_emits_towards(Lr, ls.n, -ls.wi);
+                    else if (lt == B200PT_LIGHT_SPHERE_AREA) have = sphere_light_sample(wf.spheres[Lr.ext], Lr, ctx, up, ls) && light_emits_towards(Lr, ls.n, -ls.wi);
                     else if (is_env) have = env_nee(wf, ctx.p, up, lambda, ls, Le_env);
                     else have = light_sample_other(Lr, lt, wf.light_ext, wf.scene_radius, ctx, up, ls, &lw, &ld2, &delta);
                     if (have) {

@@ -293,7 +293,9 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
             // sphere phase (Sphere::basic_intersect in interval arithmetic is long: run it with as many lanes as want it)
             if (want_sph) {
                 SphereHit sh;
-                if (sphere_intersect(wf.spheres[sph_k], v3(ox, oy, oz), v3(dx, dy, dz), ht, sh)) {
+                // SHADOW: the sampled sphere light itself is skipped, like the sampled light's own triangle
+                if ((!SHADOW || int(wf.bvh.n_tris) + sph_k != skip_prim) &&
+                    sphere_intersect(wf.spheres[sph_k], v3(ox, oy, oz), v3(dx, dy, dz), ht, sh)) {
                     ht = sh.t;
                     hprim = int(wf.bvh.n_tris) + sph_k;
                     if (SHADOW) {

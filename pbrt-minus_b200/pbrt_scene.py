@@ -765,17 +765,28 @@ class Scene:
         tl = np.full(nt, -1, dtype=np.int32)
         if light_params is not None:
             # one DiffuseAreaLight per triangle (base/light.cu:56-75, lights/diffuse_area_light.cu:9-31)
-            L = self.spec_param(light_params, "L", "illuminant", scene_dir)
-            if L is None:
-                lam, val, _ = spectral.illuminant_d65()
-                L = self.spec_piecewise(("illuminant",), lam, val)
-            sc = F32(p_float(light_params, "scale", 1.0))
-            sc = F32(sc / self.photometric(L))
-            two = p_bool(light_params, "twosided", False)
+            L, sc, two = self.area_light_params(light_params, scene_dir)
             for k in range(nt):
                 tl[k] = len(self.lights)
                 self.lights.append({"triangle": first_tri + k, "spectrum": L, "scale": float(sc), "two_sided": int(two)})
         self.tri_light.append(tl)
+
+    def area_light_params(self, light_params, scene_dir):
+        """DiffuseAreaLight ctor (lights/diffuse_area_light.cu:9-31): Lemit (default: the colour space's illuminant), scale
+        divided by the photometric integral of Lemit, twosided"""
+        L = self.spec_param(light_params, "L", "illuminant", scene_dir)
+        if L is None:
+            lam, val, _ = spectral.illuminant_d65()
+            L = self.spec_piecewise(("illuminant",), lam, val)
+        sc = F32(p_float(light_params, "scale", 1.0))
+        sc = F32(sc / self.photometric(L))
+        return L, sc, p_bool(light_params, "twosided", False)
+
+    def add_sphere_light(self, sphere_index, light_params, scene_dir):
+        """one DiffuseAreaLight over the whole sphere (base/light.cu:56-75: Shape "sphere" is a single shape)"""
+        L, sc, two = self.area_light_params(light_params, scene_dir)
+        self.lights.append({"triangle": sphere_index, "spectrum": L, "scale": float(sc), "two_sided": int(two), "type": 5})
+        return len(self.lights) - 1
 
     def photometric(self, spec_id):
         """Spectrum::to_photometric (base/spectrum.cu:115-120): RGB illuminants use the illuminant's integral."""
@@ -819,7 +830,9 @@ class Scene:
             sph[i].object_from_render[:] = [float(v) for v in s["ofr"].reshape(-1)]
             sph[i].radius, sph[i].z_min, sph[i].z_max, sph[i].phi_max = s["radius"], s["zmin"], s["zmax"], s["phimax"]
             sph[i].reverse_orientation, sph[i].transform_swaps_handedness = int(s["ro"]), int(s["swaps"])
-            sph[i].material, sph[i].light, sph[i].kind = s["material"], -1, s.get("kind", 0)
+            sph[i].material, sph[i].light, sph[i].kind = s["material"], s.get("light", -1), s.get("kind", 0)
+            if s.get("light", -1) >= 0 and self.media:
+                raise SceneError("emissive spheres in scenes with media are outside the hot path")
         d.n_spheres, d.spheres = len(self.spheres), sph
         spec = (api.Spectrum * max(1, len(self.spectra)))()
         for i, s in enumerate(self.spectra):
@@ -849,6 +862,8 @@ class Scene:
         for i, l in enumerate(self.lights):
             lights[i].triangle, lights[i].spectrum, lights[i].scale, lights[i].two_sided = l["triangle"], l["spectrum"], l["scale"], l["two_sided"]
             lights[i].type = l.get("type", 0)
+            if lights[i].type == 5:
+                continue                       # sphere area light: `triangle` is the sphere index
             if lights[i].type:
                 lights[i].v[:] = l["v"]
                 lights[i].light_from_render[:] = l["lfr"]
@@ -1018,15 +1033,17 @@ def load(path=None, text=None, spp=None, integrator=None, scene_dir=None):
                     Nr = xf_normals(render_from_instance.inv, Nr)
             sc.add_mesh(Pr, rec["idx"], rec["material"], flip, area_light, scene_dir, N=Nr, uv=rec.get("uv"), medium_code=rec.get("mcode", 0))
         else:
-            if area_light is not None:
-                raise SceneError("emissive spheres are outside the hot path")
-            if rec.get("mcode", 0) != 0:
+            if area_light is not None and rec["kind"] == "disk":
+                raise SceneError("emissive disks are outside the hot path")
+            if rec.get("mcode", 0) != 0 and not (area_light is not None and rec["mcode"] == 0xFFFFFFFF):
                 raise SceneError("spheres on a medium transition are outside the hot path")
             if sc.materials[rec["material"]]["type"] == 7:
                 raise SceneError("interface spheres are outside the hot path")
             sc.spheres.append({"rfo": rfo_x.m, "ofr": rfo_x.inv, "radius": rec["radius"], "zmin": rec["zmin"], "zmax": rec["zmax"],
                                "phimax": rec["phimax"], "ro": rec["ro"], "swaps": swaps_handedness(rec["rfo"].m), "material": rec["material"],
                                "kind": 1 if rec["kind"] == "disk" else 0})
+            if area_light is not None:
+                sc.spheres[-1]["light"] = sc.add_sphere_light(len(sc.spheres) - 1, area_light, scene_dir)
 
     for kw, args in directives(text, scene_dir):
         if kw in pre:

@@ -8,10 +8,12 @@ Tolerance (floating point, BASELINE.json: "converged images within a stated relM
 mean within 3 sigma"): because the sampler stack, the random-number consumption order and the light
 selection are reproduced exactly, ours and the reference trace the SAME paths and differ only by fp32
 evaluation order (FMA contraction, libm ulps) except at discontinuities, where an ulp decides which
-surface a ray hits.  Stated bounds:
-    relMSE(ours, ref) = mean((ours - ref)^2 / (ref^2 + 1e-4)) <= 1e-4      (measured: 2e-7 .. 2e-6)
-    at least 97 % of pixels within 1 % (+1e-3 absolute) of the reference   (measured: >= 99.4 %)
-and for the converged (4096 spp) image additionally |ours - ref| <= 3 sigma_p sqrt(2/N) on >= 99 % of
+surface a ray hits.  Stated bounds, PER GOLDEN FILM (tests/golden/films/tolerances.json, written by
+tools/measure_golden.py on the B200 box):
+    relMSE(ours, ref) = mean((ours - ref)^2 / (ref^2 + 1e-4)) <= 10 x the value measured for that film
+                        (measured: 6e-12 .. 4e-5; floor 1e-9), never more than 1e-4
+    fraction of pixels within 1 % (+1e-3 absolute) of the reference >= measured - 0.01, never less than 0.97
+and for the converged (4096 spp) images additionally |ours - ref| <= 3 sigma_p sqrt(2/N) on >= 99 % of
 pixels, sigma_p from 16 independent sub-renders of ours.
 """
 import json
@@ -25,8 +27,10 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GOLD = os.path.join(ROOT, "tests", "golden", "films")
 MANIFEST = json.load(open(os.path.join(GOLD, "manifest.json")))
-REL_MSE_TOL = 1e-4
+REL_MSE_TOL = 1e-4   # ceiling; the per-film bounds below are much tighter
 FRAC_TOL = 0.97
+_tol_path = os.path.join(GOLD, "tolerances.json")
+TOLERANCES = json.load(open(_tol_path)) if os.path.exists(_tol_path) else {}
 
 
 def scene_text(name, res=None, sampler=None, edits=()):
@@ -73,12 +77,16 @@ def render(b200pt, text, spp, tmp_path, sample_begin=0, sample_end=None, pool_si
 
 def check_against_golden(b200pt, tmp_path, name, res=None, sampler=None):
     m, ref = golden(name)
-    ours, st = render(b200pt, scene_text(m["scene"], res, sampler), m["spp"], tmp_path)
+    edits = [tuple(e) for e in m.get("edits", [])]     # the text edits tools/make_golden.py applied for the reference run
+    ours, st = render(b200pt, scene_text(m["scene"], res, sampler, edits), m["spp"], tmp_path)
     assert ours.shape == ref.shape and not np.isnan(ours).any()
     assert st["paths"] == m["width"] * m["height"] * m["spp"]
     r, f = rel_mse(ours, ref), frac_close(ours, ref)
-    assert r <= REL_MSE_TOL, "relMSE %.3e vs the reference film" % r
-    assert f >= FRAC_TOL, "only %.4f of the pixels within 1%% of the reference" % f
+    tol = TOLERANCES.get(name, {})
+    r_tol = min(REL_MSE_TOL, tol.get("relMSE_tol", REL_MSE_TOL))
+    f_tol = max(FRAC_TOL, tol.get("frac_close_tol", FRAC_TOL))
+    assert r <= r_tol, "relMSE %.3e vs the reference film (bound %.1e)" % (r, r_tol)
+    assert f >= f_tol, "only %.4f of the pixels within 1%% of the reference (bound %.4f)" % (f, f_tol)
     return ours, ref
 
 
@@ -104,6 +112,56 @@ def test_light_sources_and_diffuse_transmission_match_reference(b200pt, tmp_path
     reference, so the fp-order tolerance applies (measured relMSE 2.5e-9)."""
     check_against_golden(b200pt, tmp_path, "lights_96x64_64spp")
     check_against_golden(b200pt, tmp_path, "lights_96x64_1024spp")
+
+
+def test_russian_roulette_matches_reference(b200pt, tmp_path):
+    """russian_roulette (util/russian_roulette.h:12-29) is reached only for 8 <= depth < max_depth
+    (integrators/wavefront_path.cu:89-97): maxdepth 12 makes it fire at depths 8..11, with its own sampler draw and the
+    next_time_russian_roulette bump.  The cornell box and the materials scene (specular chains through glass reach depth 8
+    often); same paths as the reference, so the fp-order tolerance applies."""
+    check_against_golden(b200pt, tmp_path, "cornell_64_64spp_maxdepth12", res=(64, 64))
+    check_against_golden(b200pt, tmp_path, "materials_96x64_64spp_maxdepth12")
+
+
+def test_thin_lens_camera_matches_reference(b200pt, tmp_path):
+    """PerspectiveCamera::generate_ray with lensradius > 0 (cameras/perspective.cu:72-80): concentric disk sample of the
+    lens (one more get_2d per camera ray), focus plane at focaldistance / d.z."""
+    check_against_golden(b200pt, tmp_path, "cornell_64_64spp_lens", res=(64, 64))
+    check_against_golden(b200pt, tmp_path, "materials_96x64_64spp_lens")
+
+
+def test_regularize_matches_reference(b200pt, tmp_path):
+    """Integrator "bool regularize" (integrators/wavefront_path.cu:446-447): after the first non-specular bounce every
+    BSDF is regularised (TrowbridgeReitzDistribution::regularize, util/scattering.h:216-224: alpha < 0.3 doubled and clamped
+    to [0.1, 0.3]) -- the materials scene has smooth and rough dielectrics and conductors behind diffuse bounces."""
+    check_against_golden(b200pt, tmp_path, "materials_96x64_64spp_regularize")
+    check_against_golden(b200pt, tmp_path, "cornell_64_64spp_regularize", res=(64, 64))
+
+
+def test_emissive_spheres_match_reference(b200pt, tmp_path):
+    """DiffuseAreaLight over Shape "sphere": Sphere::sample(ctx, u) (uniform in the subtended cone, the small-angle Taylor
+    branch for the far light) and Sphere::pdf for MIS when a BSDF-sampled ray hits the sphere (shapes/sphere.cu:162-280),
+    sharing the power light sampler with an emissive triangle; seen directly, in a mirror and through glass."""
+    check_against_golden(b200pt, tmp_path, "spherelight_96x64_64spp")
+    check_against_golden(b200pt, tmp_path, "spherelight_96x64_1024spp")
+
+
+def test_cornell_480x270_converged_4096spp(b200pt, tmp_path):
+    """config C3's image between the 48x48 golden and full HD: 480x270 at 4096 spp against the reference's film, relMSE +
+    the per-pixel 3 sigma gate (sigma_p from 16 disjoint sample ranges of ours, which also exercises the sample partition)"""
+    ours, ref = check_against_golden(b200pt, tmp_path, "cornell_480x270_4096spp", res=(480, 270))
+    text = scene_text("cornell-box-specular.pbrt", (480, 270))
+    subs = []
+    for k in range(16):
+        raw, _ = render(b200pt, text, 4096, tmp_path, sample_begin=256 * k, sample_end=256 * (k + 1), raw=True)
+        subs.append(raw)
+    subs = np.stack(subs).astype(np.float64)
+    M = np.asarray(b200pt.spectral.srgb_color_space()["rgb_from_xyz"])
+    means = np.einsum("ij,khwj->khwi", M, subs[..., :3] / np.where(subs[..., 3:] != 0, subs[..., 3:], 1))
+    sigma_mean = means.std(axis=0, ddof=1) / 4.0
+    ok = np.abs(ours - ref) <= 3.0 * sigma_mean * np.sqrt(2.0) + 1e-6
+    assert ok.mean() >= 0.99, "only %.4f of the pixel channels within 3 sigma" % ok.mean()
+    assert abs(ours.mean() - ref.mean()) <= 1e-4 * ref.mean()
 
 
 def test_shading_normals_and_uvs_match_reference(b200pt, tmp_path):
@@ -308,3 +366,69 @@ def test_error_behaviour(b200pt, tmp_path):
     with pytest.raises(b200pt.B200ptError):
         b200pt.Film(accel)
     accel.close()
+
+
+def test_bad_scene_descriptions_come_back_as_status_codes(b200pt, tmp_path):
+    """include/b200pt.h: a bad description is a status code, never a device fault -- ids that index tables on the host or
+    on the device are range-checked at b200pt_scene_create"""
+    import ctypes as C
+    p = os.path.join(str(tmp_path), "scene.pbrt")
+    open(p, "w").write(scene_text("cornell-box-specular.pbrt", (8, 8)))
+
+    def create(mutate):
+        sc = b200pt.pbrt_scene.load(p, spp=4)
+        d = sc.to_desc()
+        mutate(d)
+        h = C.c_void_p()
+        rc = b200pt.load_library().b200pt_scene_create(C.byref(d), 0, C.byref(h))
+        if rc == 0:
+            b200pt.load_library().b200pt_scene_destroy(h)
+        return rc, b200pt.load_library().b200pt_last_error().decode()
+
+    assert create(lambda d: None)[0] == 0
+
+    def bad_sphere_material(d):
+        d.spheres[0].material = d.n_materials
+    rc, msg = create(bad_sphere_material)
+    assert rc == -1 and "material" in msg
+
+    def tri_light_out_of_range(d):
+        d.tri_light[0] = d.n_lights
+    rc, msg = create(tri_light_out_of_range)
+    assert rc == -1 and "tri_light" in msg
+
+    def tri_light_names_another_triangles_light(d):
+        tl = np.ctypeslib.as_array(d.tri_light, shape=(d.n_triangles,))
+        k = int(np.nonzero(tl >= 0)[0][0])
+        other = int(np.nonzero(tl < 0)[0][0])
+        d.tri_light[other] = int(tl[k])       # a non-emissive triangle claims an existing area light
+    rc, msg = create(tri_light_names_another_triangles_light)
+    assert rc == -1 and "tri_light" in msg
+
+    for field in ("spectra", "materials", "lights"):
+        def null_array(d, field=field):
+            setattr(d, field, None)
+        rc, msg = create(null_array)
+        assert rc == -1 and "NULL" in msg, field
+
+    def sphere_claims_a_triangle_light(d):
+        d.spheres[0].light = 0
+    rc, msg = create(sphere_claims_a_triangle_light)
+    assert rc == -1
+
+
+def test_film_outlives_its_scene_safely(b200pt, tmp_path):
+    """a film whose scene has been destroyed is a dead handle: every call on it reports B200PT_ERR_STATE, destroy still works"""
+    p = os.path.join(str(tmp_path), "scene.pbrt")
+    open(p, "w").write(scene_text("cornell-box-specular.pbrt", (8, 8)))
+    sc = b200pt.pbrt_scene.load(p, spp=4)
+    integ = b200pt.WavefrontPathIntegrator(sc, device=0)
+    film = integ.create_film()
+    integ.render(film)
+    integ.close()                                   # b200pt_scene_destroy with a live film
+    with pytest.raises(b200pt.B200ptError) as e:
+        film.get_pixel_rgb()
+    assert e.value.code == -4
+    with pytest.raises(b200pt.B200ptError):
+        film.clear()
+    film.close()

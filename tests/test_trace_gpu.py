@@ -299,6 +299,94 @@ def test_hit_ids_vs_reference_hlbvh(b200pt, oracle, tmp_path):
         f.write("200k-triangle soup, 480x270 primary/bounce/shadow vs reference HLBVH: mismatching ids %s\n%s\n" % (mism, r.stdout))
 
 
+def test_c2_size_hit_ids_vs_reference_hlbvh_and_oracle_bvh(b200pt, oracle, tmp_path):
+    """BASELINE.json config 2 at its FULL size: 10 M-triangle soup, 1920x1080 primary + diffuse-bounce + shadow ray sets.
+    Hit ids bit-exact against (a) the REFERENCE's own HLBVH traversal (oracle/_ref/ref_trace: its build, its slab test, its
+    Primitive::intersect; accelerator/hlbvh.cu:459-516) and (b) the oracle's host BVH over the same rays; the only rays
+    allowed to differ are near ties (the other side's primitive is itself accepted within 4 ulp of t: visit order decides,
+    and the reference's own intra-treelet order is non-deterministic, hlbvh.cu:67).  t equal to the last bit on equal ids.
+    Also checks b200pt_trace_batch (one pipelined call for the three sets) against the one-set calls."""
+    import ctypes as C
+    wl = b200pt.workloads
+    P, idx = wl.triangle_soup(10_000_000)
+    s = b200pt.HLBVH(P, idx)
+    o, d, tmax = wl.primary_rays(1920, 1080)
+    prim, t, b = s.intersect(o, d, tmax)
+    bo, bd, bt = wl.bounce_rays(P, idx, o, d, prim, t, seed=7)
+    so, sd, stm = wl.shadow_rays(P, idx, o, d, prim, t, seed=11)
+    sets = (("primary", (o, d, tmax), 0), ("bounce", (bo, bd, bt), 0), ("shadow", (so, sd, stm), 1))
+    ours = {"primary": (prim, t)}
+    p2, t2, _ = s.intersect(bo, bd, bt)
+    ours["bounce"] = (p2, t2)
+    ours["shadow"] = (s.fast_intersect(so, sd, stm), None)
+    # ---- one batched call gives the same answers
+    fp, ip = C.POINTER(C.c_float), C.POINTER(C.c_int32)
+    batch = (b200pt.api.RaySet * 3)()
+    keep = []
+    for i, (name, (ro, rd, rt), any_hit) in enumerate(sets):
+        ro, rd, rt = (np.ascontiguousarray(a, dtype=np.float32) for a in (ro, rd, rt))
+        n = len(rt)
+        pr = np.full(n, -7, np.int32)
+        tt = np.full(n, -7, np.float32)
+        keep.append((ro, rd, rt, pr, tt))
+        batch[i].o_xyz, batch[i].d_xyz, batch[i].tmax = ro.ctypes.data_as(fp), rd.ctypes.data_as(fp), rt.ctypes.data_as(fp)
+        batch[i].n, batch[i].any_hit = n, any_hit
+        batch[i].prim_out = pr.ctypes.data_as(ip)
+        batch[i].t_out = None if any_hit else tt.ctypes.data_as(fp)
+    assert s.lib.b200pt_trace_batch(s.handle, batch, 3) == 0, s.lib.b200pt_last_error()
+    for (name, _, any_hit), (_, _, _, pr, tt) in zip(sets, keep):
+        if any_hit:
+            assert np.array_equal(pr.astype(bool), ours[name][0])
+            assert (tt == -7).all()                   # an output passed as NULL is not written
+        else:
+            assert np.array_equal(pr, ours[name][0]) and np.array_equal(tt.view(np.uint32), ours[name][1].view(np.uint32))
+    # ---- (b) the oracle's host BVH, all rays
+    bvh = oracle.HostBVH(P, idx)
+    report = {}
+    for name, (ro, rd, rt), any_hit in sets:
+        if any_hit:
+            m = int((bvh.any_hit(ro, rd, rt) != ours[name][0]).sum())
+            report[name + " vs oracle BVH"] = {"rays": len(rt), "mismatches": m}
+            assert m == 0
+        else:
+            op, ot, _ = bvh.closest_hit(ro, rd, rt)
+            mism, near = oracle.compare_closest(P, idx, ro, rd, rt, ours[name][0], ours[name][1], op, ot)
+            same = (ours[name][0] == op) & (op >= 0)
+            assert np.array_equal(ours[name][1][same].view(np.uint32), ot[same].view(np.uint32))
+            report[name + " vs oracle BVH"] = {"rays": len(rt), "mismatches": mism, "near_ties": near}
+            assert mism == 0 and near < 1e-4 * len(rt)
+    bvh.close()
+    # ---- (a) the reference's own HLBVH
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_trace")
+    if os.path.exists(exe):
+        wl.write_soup(tmp_path / "soup.bin", P, idx)
+        jobs = []
+        for name, (ro, rd, rt), any_hit in sets:
+            wl.write_rays(tmp_path / (name + ".rays"), ro, rd, rt)
+            jobs.append("%s:%s:%s" % ("any" if any_hit else "closest", tmp_path / (name + ".rays"), tmp_path / (name + ".out")))
+        r = subprocess.run([exe, str(tmp_path / "soup.bin")] + jobs, capture_output=True, text=True, timeout=1800)
+        assert r.returncode == 0, r.stdout + r.stderr
+        for name, (ro, rd, rt), any_hit in sets:
+            rprim, rtt = wl.read_hits(tmp_path / (name + ".out"), len(rt))
+            if any_hit:
+                m = int((rprim.astype(bool) != ours[name][0]).sum())
+                report[name + " vs reference HLBVH"] = {"rays": len(rt), "mismatches": m}
+                assert m == 0
+            else:
+                mism, near = oracle.compare_closest(P, idx, ro, rd, rt, ours[name][0], ours[name][1], rprim, rtt)
+                same = (ours[name][0] == rprim) & (rprim >= 0)
+                assert np.array_equal(ours[name][1][same].view(np.uint32), rtt[same].view(np.uint32))
+                report[name + " vs reference HLBVH"] = {"rays": len(rt), "mismatches": mism, "near_ties": near}
+                assert mism == 0 and near < 1e-4 * len(rt)
+    else:
+        report["reference HLBVH"] = "oracle/_ref/ref_trace not prebuilt"
+    out = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    import json
+    json.dump({"config": "C2: 10M-triangle soup, 1920x1080 primary + bounce + shadow", "report": report}, open(os.path.join(out, "c2_hit_id_parity.json"), "w"), indent=1)
+    s.close()
+
+
 def test_packed_key_build_above_16M_triangles(b200pt, oracle):
     """N > 16 Mi: key = morton(3 * b) << ceil(log2 N) | prim, b = floor((64 - ceil(log2 N)) / 3), one 8-byte key-only sort
     (csrc/bvh_build.cu).  17 M triangles: the sorted order is a permutation, keys strictly increase, the low bits are the

@@ -54,8 +54,28 @@ CASES = [
     ("envmap_96x64_1024spp", "envmap.pbrt", None, 1024, None, None),
     # C4 in miniature (workloads.procedural_scene, seed 7): many lights -> statistical gate only
     ("c4tiny_96x54_1024spp", "@c4tiny", None, 1024, None, None),
+    # ---- round 2 ------------------------------------------------------------------------------------------------------
+    # russian roulette (util/russian_roulette.h:12-29) fires only for 8 <= depth < maxdepth: maxdepth 12
+    ("cornell_64_64spp_maxdepth12", "cornell-box-specular.pbrt", (64, 64), 64, None, None, [('Integrator "path"', 'Integrator "path" "integer maxdepth" [12]')]),
+    ("materials_96x64_64spp_maxdepth12", "materials.pbrt", None, 64, None, None, [('"integer maxdepth" [7]', '"integer maxdepth" [12]')]),
+    # thin-lens camera (cameras/perspective.cu:72-80)
+    ("cornell_64_64spp_lens", "cornell-box-specular.pbrt", (64, 64), 64, None, None,
+     [('Camera "perspective" "float fov" [37.5]', 'Camera "perspective" "float fov" [37.5] "float lensradius" [12] "float focaldistance" [900]')]),
+    ("materials_96x64_64spp_lens", "materials.pbrt", None, 64, None, None,
+     [('Camera "perspective" "float fov" [40]', 'Camera "perspective" "float fov" [40] "float lensradius" [0.05] "float focaldistance" [6]')]),
+    # "bool regularize" (integrators/wavefront_path.cu:446-447, util/scattering.h:216-224)
+    ("materials_96x64_64spp_regularize", "materials.pbrt", None, 64, None, None, [('"integer maxdepth" [7]', '"integer maxdepth" [7] "bool regularize" [true]')]),
+    ("cornell_64_64spp_regularize", "cornell-box-specular.pbrt", (64, 64), 64, None, None, [('Integrator "path"', 'Integrator "path" "bool regularize" [true]')]),
+    # C3's image at a size between 48x48 and full HD, converged: 480x270 at 4096 spp (about a minute of reference time)
+    ("cornell_480x270_4096spp", "cornell-box-specular.pbrt", (480, 270), 4096, None, None),
+    # emissive spheres (Sphere::sample / Sphere::pdf, shapes/sphere.cu:162-280)
+    ("spherelight_96x64_64spp", "spherelight.pbrt", None, 64, None, None),
+    ("spherelight_96x64_1024spp", "spherelight.pbrt", None, 1024, None, None),
 ]
 
+
+
+ROUND2_START = [c[0] for c in CASES].index("cornell_64_64spp_maxdepth12")
 
 
 def main():
@@ -66,8 +86,13 @@ def main():
     only = sys.argv[1:]
     import shutil
     shutil.copytree(os.path.join(ROOT, "tests", "scenes", "textures"), os.path.join(out, "textures"), dirs_exist_ok=True)
-    for name, scene, res, spp, integ, sampler in CASES:
-        if only and name not in only:
+    for case in CASES:
+        name, scene, res, spp, integ, sampler = case[:6]
+        edits = case[6] if len(case) > 6 else []
+        if only == ["round2"]:
+            if CASES.index(case) < ROUND2_START:
+                continue
+        elif only and name not in only:
             continue
         if scene == "@c4tiny":
             sys.path.insert(0, ROOT)
@@ -81,6 +106,9 @@ def main():
             text = with_resolution(text, *res)
         if sampler:
             text = text.replace("WorldBegin", 'Sampler "%s"\nWorldBegin' % sampler, 1)
+        for a, b in edits:
+            assert a in text, (name, a)
+            text = text.replace(a, b)
         sp = os.path.join(out, name + ".pbrt")
         open(sp, "w").write(text)
         png = os.path.join(out, name + ".png")
@@ -95,7 +123,7 @@ def main():
         film = np.fromfile(png + ".f32", dtype=np.float32).reshape(H, W, 3)
         os.replace(png + ".f32", os.path.join(out, name + ".f32"))
         took = re.search(r"rendering took\s+([0-9.]+)", r.stdout)
-        manifest[name] = {"scene": scene, "width": W, "height": H, "spp": spp, "integrator": integ or "path", "sampler": sampler or "stratified",
+        manifest[name] = {"scene": scene, "width": W, "height": H, "spp": spp, "integrator": integ or "path", "sampler": sampler or "stratified", "edits": [list(e) for e in edits],
                           "mean": float(film.mean()), "reference_render_s": float(took.group(1)) if took else None}
         print(name, manifest[name])
     json.dump(manifest, open(os.path.join(out, "manifest_new.json" if only else "manifest.json"), "w"), indent=1)

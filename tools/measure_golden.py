@@ -1,0 +1,41 @@
+#!/usr/bin/env python3
+"""Measure relMSE / fraction-of-close-pixels of every exact-parity golden film (tests/golden/films) on the GPU box and
+write tests/golden/films/tolerances.json: per golden, the relMSE bound the tests enforce = 10 x the measured value
+(floor 1e-9), and the close-pixel fraction bound = measured - 0.01.  python tools/measure_golden.py [--write]"""
+import importlib
+import json
+import os
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+STATISTICAL = ("coated_", "mix_", "c4tiny_")   # compared as two unbiased estimators (tests: statistical_gate)
+
+
+def main():
+    import test_render_gpu as T
+    pkg = importlib.import_module("pbrt-minus_b200")
+    out = {}
+    with tempfile.TemporaryDirectory() as td:
+        for name, m in T.MANIFEST.items():
+            if name.startswith(STATISTICAL) or m["integrator"] != "path":
+                continue
+            _, ref = T.golden(name)
+            res = (m["width"], m["height"]) if m["scene"].startswith("cornell") else None
+            sampler = m["sampler"] if m["sampler"] != "stratified" else None
+            text = T.scene_text(m["scene"], res, sampler, [tuple(e) for e in m.get("edits", [])])
+            ours, st = T.render(pkg, text, m["spp"], td)
+            r, f = T.rel_mse(ours, ref), T.frac_close(ours, ref)
+            out[name] = {"relMSE_measured": r, "frac_close_measured": f, "relMSE_tol": max(10.0 * r, 1e-9),
+                         "frac_close_tol": round(max(0.0, f - 0.01), 4), "ms": round(st["ms_total"], 2)}
+            print(name, json.dumps(out[name]), flush=True)
+    dst = os.path.join(ROOT, "tests", "golden", "films", "tolerances.json") if "--write" in sys.argv else os.path.join(ROOT, "gpurun_out", "tolerances.json")
+    json.dump(out, open(dst, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
