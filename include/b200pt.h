@@ -175,9 +175,24 @@ typedef struct {
     const float *illuminant;             /* 471 samples: colour-space illuminant (D65), normalised */
 } b200pt_film_desc;
 
+/* ---- object instancing (ObjectBegin / ObjectInstance, scene/scene_builder.cu:809-876; primitives/transformed_primitive.cu):
+ *      an object is a contiguous range of the triangle array whose vertices are in the OBJECT's space; it gets its own BVH8, built
+ *      once, and every instance reaches it through a ray transformed by the reference's Transform::apply_inverse(Ray, &t_max) and
+ *      brings the hit back with Transform::operator()(SurfaceInteraction).  Triangles before the first object range are the
+ *      top-level (render-space) triangles.  Object triangles cannot be emissive or sit on a medium transition
+ *      (scene_builder.cu:651-656). */
+typedef struct {
+    int64_t first_triangle, n_triangles;
+} b200pt_object;
+typedef struct {
+    int32_t object;
+    float render_from_instance[16]; /* row-major 4x4 */
+    float instance_from_render[16];
+} b200pt_instance;
+
 typedef struct {
     int64_t n_vertices;
-    const float *P;            /* [n_vertices*3] render-space positions */
+    const float *P;            /* [n_vertices*3] render-space positions (object space for the triangles of an object) */
     const float *N;            /* optional [n_vertices*3] shading normals */
     const float *uv;           /* optional [n_vertices*2] */
     int64_t n_triangles;
@@ -210,6 +225,10 @@ typedef struct {
     const b200pt_camera *camera; /* may be NULL for traversal-only scenes */
     const b200pt_filter *filter;
     const b200pt_film_desc *film;
+    int32_t n_objects;           /* instanced objects: ranges [first, first + n) tile the END of the triangle array, in order */
+    const b200pt_object *objects;
+    int32_t n_instances;
+    const b200pt_instance *instances;
 } b200pt_scene_desc;
 
 typedef struct {
@@ -291,7 +310,8 @@ int b200pt_trace_set_counting(b200pt_scene *scene, int enable);
 int b200pt_trace_counters(b200pt_scene *scene, int64_t out[3]);
 /* Scheduling knobs of the traversal kernels (they change speed, never results): key 0 = idle lanes before a warp
  * of k_trace refills (1/4/8/16), 1 = triangle tests per triangle phase (1..3), 2 = resident CTAs per SM cap
- * (0 = occupancy limit), 3 / 4 = the same two knobs for the wavefront integrator's trace kernels (0 = default). */
+ * (0 = occupancy limit), 3 / 4 = the same two knobs for the wavefront integrator's trace kernels (0 = default),
+ * 5 = resident CTAs per SM the plain shade kernels' register allocation is held to (0 = default, 3, 4). */
 int b200pt_trace_tune(b200pt_scene *scene, int key, int value);
 void *b200pt_scene_stream(b200pt_scene *scene); /* cudaStream_t the scene launches on */
 int b200pt_scene_sync(b200pt_scene *scene);

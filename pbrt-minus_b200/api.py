@@ -75,6 +75,14 @@ class Image(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("rgb", C.POINTER(C.c_float))]
 
 
+class Object(C.Structure):
+    _fields_ = [("first_triangle", C.c_int64), ("n_triangles", C.c_int64)]
+
+
+class Instance(C.Structure):
+    _fields_ = [("object", C.c_int32), ("render_from_instance", C.c_float * 16), ("instance_from_render", C.c_float * 16)]
+
+
 class SceneDesc(C.Structure):
     _fields_ = [("n_vertices", C.c_int64), ("P", C.POINTER(C.c_float)), ("N", C.POINTER(C.c_float)),
                 ("uv", C.POINTER(C.c_float)), ("n_triangles", C.c_int64), ("indices", C.POINTER(C.c_int32)),
@@ -87,7 +95,8 @@ class SceneDesc(C.Structure):
                 ("n_media", C.c_int32), ("media", C.POINTER(Medium)), ("tri_medium", C.POINTER(C.c_uint32)),
                 ("n_textures", C.c_int32), ("textures", C.POINTER(Texture)), ("n_images", C.c_int32), ("images", C.POINTER(Image)),
                 ("rgb2spec_fit", C.POINTER(C.c_double)),
-                ("camera", C.POINTER(Camera)), ("filter", C.POINTER(Filter)), ("film", C.POINTER(FilmDesc))]
+                ("camera", C.POINTER(Camera)), ("filter", C.POINTER(Filter)), ("film", C.POINTER(FilmDesc)),
+                ("n_objects", C.c_int32), ("objects", C.POINTER(Object)), ("n_instances", C.c_int32), ("instances", C.POINTER(Instance))]
 
 
 class BuildStats(C.Structure):

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cmath>
 #include <cstring>
 
 #include "common.cuh"
@@ -136,6 +137,44 @@ B200PT_API int b200pt_scene_create(const b200pt_scene_desc *desc, int device, b2
     }
     s->n_vertices = desc->n_vertices;
     s->n_triangles = desc->n_triangles;
+    // ---- instanced objects: ranges that tile the end of the triangle array
+    s->n_top_triangles = desc->n_triangles;
+    if (desc->n_objects < 0 || desc->n_instances < 0 || (desc->n_objects > 0 && !desc->objects) || (desc->n_instances > 0 && !desc->instances)) {
+        set_error("b200pt_scene_create: objects / instances count without an array");
+        return fail(B200PT_ERR_INVALID);
+    }
+    if (desc->n_objects > 0) {
+        int64_t next = desc->objects[0].first_triangle;
+        s->n_top_triangles = next;
+        for (int i = 0; i < desc->n_objects; i++) {
+            const b200pt_object &o = desc->objects[i];
+            if (o.first_triangle != next || o.n_triangles <= 0 || o.first_triangle < 0) {
+                set_error("b200pt_scene_create: object %d: ranges must be non-empty and tile the end of the triangle array in order", i);
+                return fail(B200PT_ERR_INVALID);
+            }
+            next += o.n_triangles;
+            HostObject h;
+            h.first_triangle = o.first_triangle;
+            h.n_triangles = o.n_triangles;
+            s->objects.push_back(h);
+        }
+        if (next != desc->n_triangles) {
+            set_error("b200pt_scene_create: object ranges end at triangle %lld of %lld", (long long)next, (long long)desc->n_triangles);
+            return fail(B200PT_ERR_INVALID);
+        }
+        for (int64_t t = s->n_top_triangles; t < desc->n_triangles; t++)
+            if ((desc->tri_light && desc->tri_light[t] != -1) || (desc->tri_medium && desc->tri_medium[t] != 0u)) {
+                set_error("b200pt_scene_create: triangle %lld of an instanced object is emissive or on a medium transition", (long long)t);
+                return fail(B200PT_ERR_INVALID);
+            }
+    }
+    for (int i = 0; i < desc->n_instances; i++) {
+        if (desc->instances[i].object < 0 || desc->instances[i].object >= desc->n_objects) {
+            set_error("b200pt_scene_create: instance %d names object %d", i, desc->instances[i].object);
+            return fail(B200PT_ERR_INVALID);
+        }
+        s->instances.push_back(desc->instances[i]);
+    }
     // index sanity (a bad index would fault on the device)
     for (int64_t i = 0; i < desc->n_triangles * 3; i++) {
         const int32_t v = desc->indices[i];
@@ -151,11 +190,11 @@ B200PT_API int b200pt_scene_create(const b200pt_scene_desc *desc, int device, b2
     if ((rc = upload(&s->d_tri_material, desc->tri_material, size_t(desc->n_triangles), s->stream, &s->device_bytes))) return fail(rc);
     if ((rc = upload(&s->d_tri_light, desc->tri_light, size_t(desc->n_triangles), s->stream, &s->device_bytes))) return fail(rc);
     if ((rc = upload(&s->d_tri_flip, desc->tri_flip, size_t(desc->n_triangles), s->stream, &s->device_bytes))) return fail(rc);
-    if (cudaMalloc((void **)&s->d_trace_counters, 4 * sizeof(unsigned long long)) != cudaSuccess) {
+    if (cudaMalloc((void **)&s->d_trace_counters, kTraceCounterWords * sizeof(unsigned long long)) != cudaSuccess) {
         set_error("b200pt_scene_create: out of device memory");
         return fail(B200PT_ERR_CUDA);
     }
-    cudaMemsetAsync(s->d_trace_counters, 0, 4 * sizeof(unsigned long long), s->stream);
+    cudaMemsetAsync(s->d_trace_counters, 0, kTraceCounterWords * sizeof(unsigned long long), s->stream);
     if ((rc = b200pt_upload_render_data(s, desc))) return fail(rc);
     if (cudaStreamSynchronize(s->stream) != cudaSuccess) {
         set_error("b200pt_scene_create: upload failed");
@@ -170,7 +209,7 @@ B200PT_API void b200pt_scene_destroy(b200pt_scene *s) {
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     free_render(s);
-    void *ptrs[] = {s->d_scratch, s->d_P, s->d_N, s->d_uv, s->d_idx, s->d_tri_material, s->d_tri_light, s->d_tri_flip, s->d_spheres,
+    void *ptrs[] = {s->d_instances, s->d_scratch, s->d_P, s->d_N, s->d_uv, s->d_idx, s->d_tri_material, s->d_tri_light, s->d_tri_flip, s->d_spheres,
                     s->d_nodes, s->d_tris, s->d_sorted_keys, s->d_sorted_prim, s->d_trace_counters};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -178,6 +217,7 @@ B200PT_API void b200pt_scene_destroy(b200pt_scene *s) {
     if (s->stream) cudaStreamDestroy(s->stream);
     if (s->stream_h2d) cudaStreamDestroy(s->stream_h2d);
     if (s->stream_d2h) cudaStreamDestroy(s->stream_d2h);
+    if (s->stream2) cudaStreamDestroy(s->stream2);
     for (cudaEvent_t e : s->pipe_events) cudaEventDestroy(e);
     delete s;
 }
@@ -190,6 +230,52 @@ B200PT_API int b200pt_bvh_build(b200pt_scene *s, b200pt_build_stats *stats_out) 
     CU_TRY(cudaSetDevice(s->device));
     return build_bvh(s, stats_out);
 }
+
+namespace b200pt {
+// InstRec array: object roots are known once the build has run; the instance box is the transformed object box
+// (TransformedPrimitive::bounds, primitives/transformed_primitive.cu:9-12), padded like the quadric boxes
+int finish_instances(b200pt_scene *s) {
+    if (s->d_instances) {
+        cudaFree(s->d_instances);
+        s->d_instances = nullptr;
+    }
+    if (s->instances.empty()) return B200PT_OK;
+    std::vector<InstRec> recs(s->instances.size());
+    for (size_t i = 0; i < recs.size(); i++) {
+        const b200pt_instance &in = s->instances[i];
+        const HostObject &ob = s->objects[in.object];
+        InstRec &r = recs[i];
+        for (int k = 0; k < 12; k++) {
+            r.rfi[k] = in.render_from_instance[k];
+            r.ifr[k] = in.instance_from_render[k];
+        }
+        r.root_node = (int32_t)ob.root_node;
+        r.object = in.object;
+        float ext = 0.f, mag = 0.f;
+        for (int a = 0; a < 3; a++) {
+            float mn = in.render_from_instance[4 * a + 3], mx = mn;
+            for (int k = 0; k < 3; k++) {
+                const float x = in.render_from_instance[4 * a + k] * ob.box[k], y = in.render_from_instance[4 * a + k] * ob.box[3 + k];
+                mn += std::min(x, y);
+                mx += std::max(x, y);
+            }
+            r.box_lo[a] = mn;
+            r.box_hi[a] = mx;
+            ext = std::max(ext, mx - mn);
+            mag = std::max(mag, std::max(std::fabs(mn), std::fabs(mx)));
+        }
+        const float pad = 1e-3f * ext + 1e-5f * mag + 1e-30f;
+        for (int a = 0; a < 3; a++) {
+            r.box_lo[a] -= pad;
+            r.box_hi[a] += pad;
+        }
+    }
+    CU_TRY(cudaMalloc((void **)&s->d_instances, recs.size() * sizeof(InstRec)));
+    CU_TRY(cudaMemcpyAsync(s->d_instances, recs.data(), recs.size() * sizeof(InstRec), cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    return B200PT_OK;
+}
+} // namespace b200pt
 
 B200PT_API int b200pt_bvh_debug_sorted(b200pt_scene *s, int32_t *prim_order_out, uint64_t *keys_out) {
     if (!s || !s->built) {
@@ -238,7 +324,9 @@ B200PT_API int b200pt_trace_device(b200pt_scene *s, const void *rays_dev, int64_
 // engine), the traversal of chunk k and the copy-out of chunk k-1 (D2H engine) run at the same time, so with pinned host
 // buffers a call costs about max(copy-in, traversal, copy-out) + one chunk of fill and drain, instead of their sum per set.
 // The trace kernel reads the caller's array layout and writes the caller's output layout directly (TraceHostIO): there is
-// no repacking pass.  Pageable buffers still work (the copies then block the host).  One synchronisation, at the end.
+// no repacking pass.  Consecutive chunks alternate between two traversal streams, each with its own work ticket: while the
+// last warps of chunk k finish their rays, the CTAs of chunk k+1 already occupy the SM slots the others have left, so the
+// per-launch tail of a persistent kernel is hidden instead of paid once per chunk.  Pageable buffers still work (the copies then block the host).  One synchronisation, at the end.
 B200PT_API int b200pt_trace_batch(b200pt_scene *s, const b200pt_ray_set *sets, int n_sets) {
     if (!s || n_sets < 0 || (n_sets > 0 && !sets)) {
         set_error("b200pt_trace_batch: null argument");
@@ -256,6 +344,10 @@ B200PT_API int b200pt_trace_batch(b200pt_scene *s, const b200pt_ray_set *sets, i
     if (!s->built) {
         set_error("b200pt_trace: call b200pt_bvh_build first");
         return B200PT_ERR_STATE;
+    }
+    if (!s->instances.empty()) {
+        set_error("b200pt_trace: scenes with object instances are traced by the wavefront integrator only");
+        return B200PT_ERR_UNSUPPORTED;
     }
     if (total == 0) return B200PT_OK;
     CU_TRY(cudaSetDevice(s->device));
@@ -276,6 +368,9 @@ B200PT_API int b200pt_trace_batch(b200pt_scene *s, const b200pt_ray_set *sets, i
     for (int i = 0; i < n_sets; i++) n_chunks += (int)((sets[i].n + chunk - 1) / chunk);
     if (!s->stream_h2d) CU_TRY(cudaStreamCreateWithFlags(&s->stream_h2d, cudaStreamNonBlocking));
     if (!s->stream_d2h) CU_TRY(cudaStreamCreateWithFlags(&s->stream_d2h, cudaStreamNonBlocking));
+    if (!s->stream2) CU_TRY(cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking));
+    static const bool one_stream = getenv("B200PT_TRACE_ONE_STREAM") != nullptr;
+    const bool two = !one_stream && !s->counting; // the visit counters are per launch: counting runs keep one stream
     while ((int)s->pipe_events.size() < 2 * n_chunks + 1) {
         cudaEvent_t e;
         CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -295,12 +390,13 @@ B200PT_API int b200pt_trace_batch(b200pt_scene *s, const b200pt_ray_set *sets, i
             CU_TRY(cudaMemcpyAsync(d_d + 3 * g0, rs.d_xyz + 3 * c0, nc * 12, cudaMemcpyHostToDevice, s->stream_h2d));
             CU_TRY(cudaMemcpyAsync(d_tmax + g0, rs.tmax + c0, nc * 4, cudaMemcpyHostToDevice, s->stream_h2d));
             CU_TRY(cudaEventRecord(ev_in, s->stream_h2d));
-            CU_TRY(cudaStreamWaitEvent(s->stream, ev_in, 0));
+            cudaStream_t cs = (two && (c & 1)) ? s->stream2 : s->stream;
+            CU_TRY(cudaStreamWaitEvent(cs, ev_in, 0));
             const TraceHostIO io = {d_o + 3 * g0, d_d + 3 * g0, d_tmax + g0, rs.prim_out ? d_prim + g0 : nullptr,
                                     rs.t_out ? d_t + g0 : nullptr, rs.b1b2_out ? d_b + 2 * g0 : nullptr};
-            int rc = launch_trace(s, nullptr, nc, rs.any_hit, nullptr, c > 0, &io);
+            int rc = launch_trace(s, nullptr, nc, rs.any_hit, nullptr, c > 0, &io, two ? c : -1, cs);
             if (rc) return rc;
-            CU_TRY(cudaEventRecord(ev_done, s->stream));
+            CU_TRY(cudaEventRecord(ev_done, cs));
             CU_TRY(cudaStreamWaitEvent(s->stream_d2h, ev_done, 0));
             if (rs.prim_out) CU_TRY(cudaMemcpyAsync(rs.prim_out + c0, d_prim + g0, nc * 4, cudaMemcpyDeviceToHost, s->stream_d2h));
             if (rs.t_out) CU_TRY(cudaMemcpyAsync(rs.t_out + c0, d_t + g0, nc * 4, cudaMemcpyDeviceToHost, s->stream_d2h));
@@ -309,7 +405,8 @@ B200PT_API int b200pt_trace_batch(b200pt_scene *s, const b200pt_ray_set *sets, i
         off += (rs.n + 3) & ~int64_t(3);
     }
     s->last_counts[2] = total;
-    const int rc = check_trace_status(s); // synchronises the traversal stream
+    CU_TRY(cudaStreamSynchronize(s->stream2));
+    const int rc = check_trace_status(s); // synchronises the first traversal stream
     CU_TRY(cudaStreamSynchronize(s->stream_d2h));
     return rc;
 }
@@ -338,6 +435,7 @@ B200PT_API int b200pt_trace_tune(b200pt_scene *s, int key, int value) {
     case 2: s->tune_ctas_per_sm = value; break;
     case 3: s->tune_wf_refill = value; break;
     case 4: s->tune_wf_tri_steps = value > 3 ? 3 : value; break;
+    case 5: s->tune_shade_occ = value; break;
     default: set_error("b200pt_trace_tune: unknown key %d", key); return B200PT_ERR_INVALID;
     }
     return B200PT_OK;

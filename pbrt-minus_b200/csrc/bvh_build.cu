@@ -184,14 +184,19 @@ __global__ void __launch_bounds__(256) k_unpack_prims(const uint64_t *__restrict
 
 // ------------------------------------------------------------------------ BVH2 (build only)
 // Node ids: interior i in [0, n-1), leaf k -> (n-1) + k (k = position in sorted order).
+// One 32-byte record per node, i.e. ONE memory sector: everything the refit and the collapse want to know about a node comes
+// with its box.
+//   rec[2i]     = { lo.x, lo.y, lo.z, A }    A = gamma | left-is-leaf << 30 | right-is-leaf << 31   (interior; leaves: -1)
+//   rec[2i + 1] = { hi.x, hi.y, hi.z, B }    B = first | min(count, 4) - 1 << 30                    (first = first sorted position covered)
+// gamma = split position of the radix tree: the children are gamma / gamma + 1, as interior ids or as leaves n - 1 + gamma (+ 1).
 struct Bvh2 {
-    float4 *lo;    // xyz = box min, w = left child id (int bits)
-    float4 *hi;    // xyz = box max, w = right child id
-    int2 *range;   // interior: [first, last] sorted positions covered
+    float4 *rec;
     int32_t *parent;
     uint32_t *arrive;
     int32_t n; // leaves
 };
+__device__ __forceinline__ int bvh2_left(uint32_t A, int n) { return int(A & 0x3fffffffu) + ((A & 0x40000000u) ? n - 1 : 0); }
+__device__ __forceinline__ int bvh2_right(uint32_t A, int n) { return int(A & 0x3fffffffu) + 1 + ((A & 0x80000000u) ? n - 1 : 0); }
 
 __device__ __forceinline__ int delta_fn(const uint64_t *__restrict__ keys, int n, int i, uint64_t ki, int j) {
     if (j < 0 || j >= n) return -1;
@@ -227,14 +232,17 @@ __global__ void __launch_bounds__(256) k_emit_hierarchy(const uint64_t *__restri
     const int first = min(i, j), last = max(i, j);
     const int left = (first == gamma) ? (n - 1 + gamma) : gamma;
     const int right = (last == gamma + 1) ? (n - 1 + gamma + 1) : (gamma + 1);
-    t.lo[i].w = __int_as_float(left);
-    t.hi[i].w = __int_as_float(right);
-    t.range[i] = make_int2(first, last);
+    const uint32_t A = uint32_t(gamma) | (first == gamma ? 0x40000000u : 0u) | (last == gamma + 1 ? 0x80000000u : 0u);
+    const uint32_t B = uint32_t(first) | (uint32_t(min(last - first + 1, 4) - 1) << 30);
+    t.rec[2 * i].w = __uint_as_float(A);
+    t.rec[2 * i + 1].w = __uint_as_float(B);
     t.parent[left] = i;
     t.parent[right] = i;
     if (i == 0) t.parent[0] = -1;
 }
 
+// Bottom-up boxes.  One thread per leaf; at every interior node the first child to arrive stops, the second carries on -- with
+// its own box still in registers, so a node costs ONE sector read (the sibling's record) besides its own record.
 __global__ void __launch_bounds__(256) k_refit(const float *__restrict__ P, const int32_t *__restrict__ idx,
                                                const uint32_t *__restrict__ sorted_prim, Bvh2 t) {
     const int n = t.n;
@@ -243,20 +251,23 @@ __global__ void __launch_bounds__(256) k_refit(const float *__restrict__ P, cons
     const TriVerts tv = load_tri(P, idx, sorted_prim[k]);
     float3 lo, hi;
     tri_bounds(tv, lo, hi);
-    const int leaf = n - 1 + k;
-    t.lo[leaf] = make_float4(lo.x, lo.y, lo.z, __int_as_float(-1));
-    t.hi[leaf] = make_float4(hi.x, hi.y, hi.z, __int_as_float(-1));
-    int cur = (n > 1) ? t.parent[leaf] : -1;
+    int me = n - 1 + k;
+    t.rec[2 * me] = make_float4(lo.x, lo.y, lo.z, __int_as_float(-1));
+    t.rec[2 * me + 1] = make_float4(hi.x, hi.y, hi.z, __uint_as_float(uint32_t(k)));
+    int cur = (n > 1) ? t.parent[me] : -1;
     while (cur >= 0) {
         __threadfence();
         if (atomicAdd(&t.arrive[cur], 1u) == 0u) return; // first arrival: the sibling finishes the job
         __threadfence();
-        const int l = __float_as_int(__ldcg(&t.lo[cur].w)), r = __float_as_int(__ldcg(&t.hi[cur].w));
-        const float4 llo = __ldcg(&t.lo[l]), lhi = __ldcg(&t.hi[l]);
-        const float4 rlo = __ldcg(&t.lo[r]), rhi = __ldcg(&t.hi[r]);
-        float4 *plo = &t.lo[cur], *phi = &t.hi[cur];
-        plo->x = fminf(llo.x, rlo.x); plo->y = fminf(llo.y, rlo.y); plo->z = fminf(llo.z, rlo.z);
-        phi->x = fmaxf(lhi.x, rhi.x); phi->y = fmaxf(lhi.y, rhi.y); phi->z = fmaxf(lhi.z, rhi.z);
+        const uint32_t A = __float_as_uint(__ldcg(&t.rec[2 * cur].w)), B = __float_as_uint(__ldcg(&t.rec[2 * cur + 1].w));
+        const int l = bvh2_left(A, n), r = bvh2_right(A, n);
+        const int sib = (l == me) ? r : l;
+        const float4 slo = __ldcg(&t.rec[2 * sib]), shi = __ldcg(&t.rec[2 * sib + 1]);
+        lo = make_float3(fminf(lo.x, slo.x), fminf(lo.y, slo.y), fminf(lo.z, slo.z));
+        hi = make_float3(fmaxf(hi.x, shi.x), fmaxf(hi.y, shi.y), fmaxf(hi.z, shi.z));
+        t.rec[2 * cur] = make_float4(lo.x, lo.y, lo.z, __uint_as_float(A));
+        t.rec[2 * cur + 1] = make_float4(hi.x, hi.y, hi.z, __uint_as_float(B));
+        me = cur;
         cur = t.parent[cur];
     }
 }
@@ -270,6 +281,7 @@ struct CollapseArgs {
     const int32_t *tri_material; // optional per-triangle ids, carried in the w lanes of the leaf record
     const int32_t *tri_light;
     const uint8_t *tri_flip;
+    int32_t prim_offset; // global id of the range's first triangle (the per-triangle arrays above are offset the same way)
     float4 *nodes; // BVH8 out
     float4 *tris;  // re-laid-out triangles out
     const int2 *q_in; // (bvh2 node, bvh8 node index)
@@ -294,16 +306,25 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
 
     int c[8];
     float area[8];
+    float clo[8][3], chi[8][3];
+    uint32_t cA[8], cB[8];
     int cnt;
+    auto load_child = [&](int slot, int id) {
+        const float4 lo = a.t.rec[2 * id], hi = a.t.rec[2 * id + 1];
+        c[slot] = id;
+        clo[slot][0] = lo.x; clo[slot][1] = lo.y; clo[slot][2] = lo.z;
+        chi[slot][0] = hi.x; chi[slot][1] = hi.y; chi[slot][2] = hi.z;
+        cA[slot] = __float_as_uint(lo.w);
+        cB[slot] = __float_as_uint(hi.w);
+        area[slot] = (id >= n - 1) ? -1.f : half_area(lo, hi);
+    };
     if (root2 >= n - 1) { // single-leaf tree (n == 1)
-        c[0] = root2;
-        area[0] = -1.f;
+        load_child(0, root2);
         cnt = 1;
     } else {
-        c[0] = __float_as_int(a.t.lo[root2].w);
-        c[1] = __float_as_int(a.t.hi[root2].w);
-        area[0] = (c[0] >= n - 1) ? -1.f : half_area(a.t.lo[c[0]], a.t.hi[c[0]]);
-        area[1] = (c[1] >= n - 1) ? -1.f : half_area(a.t.lo[c[1]], a.t.hi[c[1]]);
+        const uint32_t A = __float_as_uint(a.t.rec[2 * root2].w);
+        load_child(0, bvh2_left(A, n));
+        load_child(1, bvh2_right(A, n));
         cnt = 2;
     }
     // open the interior child with the largest surface area until the treelet has 8 leaves
@@ -316,22 +337,16 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
                 best = i;
             }
         if (best < 0) break;
-        const int l = __float_as_int(a.t.lo[c[best]].w), r = __float_as_int(a.t.hi[c[best]].w);
-        c[best] = l;
-        area[best] = (l >= n - 1) ? -1.f : half_area(a.t.lo[l], a.t.hi[l]);
-        c[cnt] = r;
-        area[cnt] = (r >= n - 1) ? -1.f : half_area(a.t.lo[r], a.t.hi[r]);
+        const uint32_t A = cA[best];
+        load_child(best, bvh2_left(A, n));
+        load_child(cnt, bvh2_right(A, n));
         cnt++;
     }
 
-    // child boxes, triangle counts, node box
-    float clo[8][3], chi[8][3];
+    // triangle counts, node box (the child boxes came with the records above)
     int tcount[8], tfirst[8];
     float nlo[3] = {kInf, kInf, kInf}, nhi[3] = {-kInf, -kInf, -kInf};
     for (int i = 0; i < cnt; i++) {
-        const float4 lo = a.t.lo[c[i]], hi = a.t.hi[c[i]];
-        clo[i][0] = lo.x; clo[i][1] = lo.y; clo[i][2] = lo.z;
-        chi[i][0] = hi.x; chi[i][1] = hi.y; chi[i][2] = hi.z;
         for (int k = 0; k < 3; k++) {
             nlo[k] = fminf(nlo[k], clo[i][k]);
             nhi[k] = fmaxf(nhi[k], chi[i][k]);
@@ -340,9 +355,8 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
             tfirst[i] = c[i] - (n - 1);
             tcount[i] = 1;
         } else {
-            const int2 rg = a.t.range[c[i]];
-            tfirst[i] = rg.x;
-            tcount[i] = rg.y - rg.x + 1;
+            tfirst[i] = int(cB[i] & 0x3fffffffu);
+            tcount[i] = int(cB[i] >> 30) + 1; // 4 stands for "more than 3": an interior child of the BVH8 node
         }
     }
 
@@ -464,7 +478,7 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
                 const uint32_t prim = a.sorted_prim[tfirst[i] + k];
                 const TriVerts tv = load_tri(a.P, a.idx, prim);
                 float4 *dst = a.tris + 3 * (size_t)(tri_base + tri_off + k);
-                dst[0] = make_float4(tv.a.x, tv.a.y, tv.a.z, __int_as_float((int)prim));
+                dst[0] = make_float4(tv.a.x, tv.a.y, tv.a.z, __int_as_float((int)prim + a.prim_offset));
                 // v1.w = material id | degenerate << 28 | has-uv << 30 | has-normals << 29 | flip << 31 (b200pt.h: tri_flip bits 2, 1, 0), v2.w = light id (-1: none)
                 const uint32_t mat = (a.tri_material ? (uint32_t)a.tri_material[prim] : 0u) |
                                      (a.tri_flip ? ((uint32_t(a.tri_flip[prim]) & 1u) << 31 | (uint32_t(a.tri_flip[prim]) & 6u) << 28) : 0u);
@@ -500,10 +514,10 @@ __global__ void k_collapse_advance(unsigned int *counters, int parity) {
     counters[4 + parity] = 0;
 }
 
-__global__ void k_seed_queue(int2 *q, unsigned int *counters, int root2) {
-    q[0] = make_int2(root2, 0);
-    counters[0] = 1; // node 0 = root
-    counters[1] = 0;
+__global__ void k_seed_queue(int2 *q, unsigned int *counters, int root2, unsigned node_base, unsigned leaf_base) {
+    q[0] = make_int2(root2, (int)node_base);
+    counters[0] = node_base + 1; // the first node of the range = its root
+    counters[1] = leaf_base;
     counters[2] = 0;
     counters[3] = 0;
     counters[4] = 1; // one item in queue 0
@@ -529,27 +543,19 @@ struct Arena {
 };
 } // namespace
 
-int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
-    const int64_t n = s->n_triangles;
+// One BVH8 over the triangles [first, first + n) of the scene (their ids in the leaf records stay GLOBAL), written into the
+// shared node / leaf-record arrays starting at node_base / leaf_base: the top-level tree of the scene, or the tree of one
+// instanced object (scene_builder.cu:809-876 keeps one HLBVH per object definition too).
+struct RangeOut {
+    unsigned n_nodes = 0;
+    float box[6] = {0, 0, 0, 0, 0, 0}; // bounds of the range's triangles
+};
+
+static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_base, unsigned node_capacity, unsigned leaf_base,
+                       bool keep_sorted, b200pt_build_stats &bs, RangeOut &out) {
     cudaStream_t st = s->stream;
-    b200pt_build_stats bs = {};
-    bs.n_triangles = n;
-    if (s->d_nodes) { cudaFree(s->d_nodes); s->d_nodes = nullptr; }
-    if (s->d_tris) { cudaFree(s->d_tris); s->d_tris = nullptr; }
-    if (s->d_sorted_keys) { cudaFree(s->d_sorted_keys); s->d_sorted_keys = nullptr; }
-    if (s->d_sorted_prim) { cudaFree(s->d_sorted_prim); s->d_sorted_prim = nullptr; }
-    s->bvh = BVH8();
-    s->built = false;
-    if (n == 0) {
-        s->built = true;
-        if (stats) *stats = bs;
-        return B200PT_OK;
-    }
-    if (n > (int64_t(1) << 30)) {
-        set_error("b200pt_bvh_build: %lld triangles exceed the 2^30 limit", (long long)n);
-        return B200PT_ERR_UNSUPPORTED;
-    }
-    const auto wall0 = std::chrono::steady_clock::now();
+    const float *range_P = s->d_P;
+    const int32_t *range_idx = s->d_idx + 3 * first;
     // key layout: the reference's 30-bit code above a 32-bit primitive id (N <= 16 Mi), else the widest Morton
     // code that fits above ceil(log2 N) primitive-id bits; both sort as 8-byte keys with no payload
     const bool key30 = n <= (int64_t(1) << 24);
@@ -561,7 +567,6 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
     }
     const int sort_lo = prim_bits, sort_hi = prim_bits + ((3 * axis_bits + 7) / 8) * 8;
     const int n_passes = (sort_hi - sort_lo) / 8;
-    bs.key_bits = 3 * axis_bits;
 
     cudaEvent_t ev[7];
     for (auto &e : ev) CU_TRY(cudaEventCreate(&e));
@@ -570,16 +575,29 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
         ~EvFree() { for (int i = 0; i < 7; i++) cudaEventDestroy(e[i]); }
     } evfree{ev};
 
-    // ---- all memory up front: outputs (kept) and one scratch arena (freed on return)
-    const unsigned node_capacity = unsigned(n / 2 + 64);
-    CU_TRY(cudaMalloc(&s->d_sorted_keys, n * sizeof(uint64_t)));
-    CU_TRY(cudaMalloc(&s->d_sorted_prim, n * sizeof(uint32_t)));
-    CU_TRY(cudaMalloc(&s->d_nodes, size_t(node_capacity) * 5 * sizeof(float4)));
-    CU_TRY(cudaMalloc(&s->d_tris, size_t(n) * 3 * sizeof(float4)));
+    uint64_t *d_sorted_keys = nullptr;
+    uint32_t *d_sorted_prim = nullptr;
+    struct SortedFree { // the sorted order of the top-level range is kept for the build-stage parity tests; other ranges drop it
+        uint64_t **k;
+        uint32_t **p;
+        bool keep;
+        ~SortedFree() {
+            if (!keep) {
+                if (*k) cudaFree(*k);
+                if (*p) cudaFree(*p);
+            }
+        }
+    } sorted_free{&d_sorted_keys, &d_sorted_prim, keep_sorted};
+    CU_TRY(cudaMalloc(&d_sorted_keys, n * sizeof(uint64_t)));
+    CU_TRY(cudaMalloc(&d_sorted_prim, n * sizeof(uint32_t)));
+    if (keep_sorted) {
+        s->d_sorted_keys = d_sorted_keys;
+        s->d_sorted_prim = d_sorted_prim;
+    }
     Arena tmp;
     {
         const size_t sz = Arena::pad(12 * 4) * 2 + Arena::pad(n * 8) + Arena::pad(256 * sort_tiles(n) * 4) +
-                          Arena::pad(sort_scan_tmp_words(n) * 4) + 2 * Arena::pad(2 * n * sizeof(float4)) + Arena::pad(n * sizeof(int2)) +
+                          Arena::pad(sort_scan_tmp_words(n) * 4) + Arena::pad(4 * n * sizeof(float4)) +
                           Arena::pad(2 * n * 4) + Arena::pad(n * 4) + 2 * Arena::pad(n * sizeof(int2)) + Arena::pad(8 * 4);
         CU_TRY(cudaMalloc(&tmp.base, sz));
         tmp.size = sz;
@@ -592,15 +610,13 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
     uint64_t *d_keys_tmp;
     tmp.take(&d_keys_tmp, n);
     // the sort ping-pongs between two buffers; the one the last pass writes is the kept output
-    sb.keys[n_passes & 1] = s->d_sorted_keys;
+    sb.keys[n_passes & 1] = d_sorted_keys;
     sb.keys[(n_passes & 1) ^ 1] = d_keys_tmp;
     tmp.take(&sb.tile_hist, 256 * sort_tiles(n));
     tmp.take(&sb.scan_tmp, sort_scan_tmp_words(n));
     Bvh2 t;
     t.n = int32_t(n);
-    tmp.take(&t.lo, 2 * n);
-    tmp.take(&t.hi, 2 * n);
-    tmp.take(&t.range, n);
+    tmp.take(&t.rec, 4 * n);
     tmp.take(&t.parent, 2 * n);
     tmp.take(&t.arrive, n);
     int2 *q[2];
@@ -618,29 +634,29 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
     CU_TRY(cudaEventRecord(ev[0], st));
     // 1. centroid box + Morton keys
     k_init_reduction<<<1, 32, 0, st>>>(d_red);
-    k_centroid_bounds<<<std::min<int64_t>(grid_n, s->sm_count * 16), tb, 0, st>>>(s->d_P, s->d_idx, n, d_red);
+    k_centroid_bounds<<<std::min<int64_t>(grid_n, s->sm_count * 16), tb, 0, st>>>(range_P, range_idx, n, d_red);
     k_cubify<<<1, 1, 0, st>>>(d_red, d_boxes);
-    if (key30) k_morton<true><<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
-    else k_morton<false><<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
+    if (key30) k_morton<true><<<grid_n, tb, 0, st>>>(range_P, range_idx, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
+    else k_morton<false><<<grid_n, tb, 0, st>>>(range_P, range_idx, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
     CU_TRY(cudaEventRecord(ev[1], st));
     // 2. LSD radix sort (key-only)
     const int res = radix_sort_u64(sb, n, sort_lo, sort_hi, st, &bs.sort_passes);
-    if (sb.keys[res] != s->d_sorted_keys) {
+    if (sb.keys[res] != d_sorted_keys) {
         set_error("b200pt_bvh_build: sort ended in the wrong buffer");
         return B200PT_ERR_STATE;
     }
-    k_unpack_prims<<<grid_n, tb, 0, st>>>(s->d_sorted_keys, n, key30 ? 0xffffffffu : uint32_t((uint64_t(1) << prim_bits) - 1), s->d_sorted_prim);
+    k_unpack_prims<<<grid_n, tb, 0, st>>>(d_sorted_keys, n, key30 ? 0xffffffffu : uint32_t((uint64_t(1) << prim_bits) - 1), d_sorted_prim);
     CU_TRY(cudaEventRecord(ev[2], st));
     // 3. hierarchy emission
     CU_TRY(cudaMemsetAsync(t.arrive, 0, n * sizeof(uint32_t), st));
-    if (n > 1) k_emit_hierarchy<<<int((n - 1 + tb - 1) / tb), tb, 0, st>>>(s->d_sorted_keys, t);
+    if (n > 1) k_emit_hierarchy<<<int((n - 1 + tb - 1) / tb), tb, 0, st>>>(d_sorted_keys, t);
     CU_TRY(cudaEventRecord(ev[3], st));
     // 4. refit
-    k_refit<<<grid_n, tb, 0, st>>>(s->d_P, s->d_idx, s->d_sorted_prim, t);
+    k_refit<<<grid_n, tb, 0, st>>>(range_P, range_idx, d_sorted_prim, t);
     CU_TRY(cudaEventRecord(ev[4], st));
     // 5. work-queue collapse to BVH8: levels are enqueued in batches, queue sizes stay on the device
-    k_seed_queue<<<1, 1, 0, st>>>(q[0], d_counters, 0 /* leaf id n-1+0 == 0 when n == 1 */);
-    unsigned int h_counters[8] = {1, 0, 0, 0, 1, 0, 0, 0};
+    k_seed_queue<<<1, 1, 0, st>>>(q[0], d_counters, 0 /* leaf id n-1+0 == 0 when n == 1 */, node_base, leaf_base);
+    unsigned int h_counters[8] = {node_base + 1, leaf_base, 0, 0, 1, 0, 0, 0};
     int parity = 0, levels = 0;
     const int collapse_grid = s->sm_count * 16;
     while (true) {
@@ -648,12 +664,13 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
         for (int b = 0; b < batch; b++) {
             CollapseArgs a;
             a.t = t;
-            a.P = s->d_P;
-            a.idx = s->d_idx;
-            a.sorted_prim = s->d_sorted_prim;
-            a.tri_material = s->d_tri_material;
-            a.tri_light = s->d_tri_light;
-            a.tri_flip = s->d_tri_flip;
+            a.P = range_P;
+            a.idx = range_idx;
+            a.prim_offset = (int32_t)first;
+            a.sorted_prim = d_sorted_prim;
+            a.tri_material = s->d_tri_material ? s->d_tri_material + first : nullptr;
+            a.tri_light = s->d_tri_light ? s->d_tri_light + first : nullptr;
+            a.tri_flip = s->d_tri_flip ? s->d_tri_flip + first : nullptr;
             a.nodes = s->d_nodes;
             a.tris = s->d_tris;
             a.q_in = q[parity];
@@ -682,32 +699,82 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
     float boxes[12];
     CU_TRY(cudaMemcpyAsync(boxes, d_boxes, sizeof(boxes), cudaMemcpyDeviceToHost, st));
     CU_TRY(cudaStreamSynchronize(st));
-    for (int k = 0; k < 6; k++) s->scene_bounds[k] = boxes[6 + k];
-
-    bs.n_bvh2_nodes = 2 * n - 1;
-    bs.n_bvh8_nodes = h_counters[0];
-    bs.collapse_levels = int32_t(h_counters[3]);
-    if (int64_t(h_counters[1]) != n) {
-        set_error("b200pt_bvh_build: %u of %lld triangles placed", h_counters[1], (long long)n);
+    for (int k = 0; k < 6; k++) out.box[k] = boxes[6 + k];
+    out.n_nodes = h_counters[0] - node_base;
+    if (int64_t(h_counters[1]) - leaf_base != n) {
+        set_error("b200pt_bvh_build: %lld of %lld triangles placed", (long long)(int64_t(h_counters[1]) - leaf_base), (long long)n);
         return B200PT_ERR_STATE;
     }
-    CU_TRY(cudaEventElapsedTime(&bs.ms_bounds_morton, ev[0], ev[1]));
-    CU_TRY(cudaEventElapsedTime(&bs.ms_sort, ev[1], ev[2]));
-    CU_TRY(cudaEventElapsedTime(&bs.ms_emit, ev[2], ev[3]));
-    CU_TRY(cudaEventElapsedTime(&bs.ms_refit, ev[3], ev[4]));
-    CU_TRY(cudaEventElapsedTime(&bs.ms_collapse, ev[4], ev[5]));
-    CU_TRY(cudaEventElapsedTime(&bs.ms_total, ev[0], ev[5]));
-    bs.ms_wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+    float ms[6];
+    for (int k = 0; k < 5; k++) CU_TRY(cudaEventElapsedTime(&ms[k], ev[k], ev[k + 1]));
+    CU_TRY(cudaEventElapsedTime(&ms[5], ev[0], ev[5]));
+    bs.ms_bounds_morton += ms[0];
+    bs.ms_sort += ms[1];
+    bs.ms_emit += ms[2];
+    bs.ms_refit += ms[3];
+    bs.ms_collapse += ms[4];
+    bs.ms_total += ms[5];
+    bs.n_bvh2_nodes += 2 * n - 1;
+    bs.collapse_levels = std::max(bs.collapse_levels, int32_t(h_counters[3]));
+    bs.key_bits = std::max(bs.key_bits, 3 * axis_bits);
+    return B200PT_OK;
+}
 
+int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
+    const int64_t n = s->n_triangles;
+    b200pt_build_stats bs = {};
+    bs.n_triangles = n;
+    if (s->d_nodes) { cudaFree(s->d_nodes); s->d_nodes = nullptr; }
+    if (s->d_tris) { cudaFree(s->d_tris); s->d_tris = nullptr; }
+    if (s->d_sorted_keys) { cudaFree(s->d_sorted_keys); s->d_sorted_keys = nullptr; }
+    if (s->d_sorted_prim) { cudaFree(s->d_sorted_prim); s->d_sorted_prim = nullptr; }
+    s->bvh = BVH8();
+    s->built = false;
+    if (n == 0) {
+        s->built = true;
+        if (stats) *stats = bs;
+        return B200PT_OK;
+    }
+    if (n > (int64_t(1) << 30)) {
+        set_error("b200pt_bvh_build: %lld triangles exceed the 2^30 limit", (long long)n);
+        return B200PT_ERR_UNSUPPORTED;
+    }
+    const auto wall0 = std::chrono::steady_clock::now();
+    // ranges: the top-level triangles [0, n_top), then one range per instanced object (b200pt_scene_desc.objects)
+    const int64_t n_top = s->objects.empty() ? n : s->n_top_triangles;
+    size_t cap = size_t(n_top / 2 + 64);
+    for (const auto &o : s->objects) cap += size_t(o.n_triangles / 2 + 64);
+    const unsigned node_capacity = unsigned(cap);
+    CU_TRY(cudaMalloc(&s->d_nodes, size_t(node_capacity) * 5 * sizeof(float4)));
+    CU_TRY(cudaMalloc(&s->d_tris, size_t(n) * 3 * sizeof(float4)));
+    unsigned node_base = 0;
+    RangeOut ro;
+    if (n_top > 0) {
+        const int rc = build_range(s, 0, n_top, 0, node_capacity, 0, true, bs, ro);
+        if (rc) return rc;
+        node_base = ro.n_nodes;
+        for (int k = 0; k < 6; k++) s->scene_bounds[k] = ro.box[k];
+    }
+    s->n_top_nodes = node_base;
+    for (auto &o : s->objects) {
+        RangeOut oo;
+        const int rc = build_range(s, o.first_triangle, o.n_triangles, node_base, node_capacity, unsigned(o.first_triangle), false, bs, oo);
+        if (rc) return rc;
+        o.root_node = node_base;
+        for (int k = 0; k < 6; k++) o.box[k] = oo.box[k];
+        node_base += oo.n_nodes;
+    }
+    bs.n_bvh8_nodes = node_base;
+    bs.ms_wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - wall0).count();
     s->bvh.nodes = s->d_nodes;
     s->bvh.tris = s->d_tris;
-    s->bvh.n_nodes = bs.n_bvh8_nodes;
+    s->bvh.n_nodes = s->n_top_nodes; // the top-level tree; object trees are entered through their instances
     s->bvh.n_tris = n;
     s->key_bits = bs.key_bits;
     s->built = true;
     bs.device_bytes = int64_t(node_capacity) * 80 + n * 48 + n * 12;
     if (stats) *stats = bs;
-    return B200PT_OK;
+    return finish_instances(s);
 }
 
 } // namespace b200pt

@@ -64,6 +64,19 @@ struct SphereRec {
     float box_lo[3], box_hi[3];
 };
 
+// Device-side record of one object instance: the transforms and where its object's BVH8 starts in the shared node array.
+struct InstRec {
+    float rfi[12]; // render_from_instance, rows 0..2
+    float ifr[12]; // instance_from_render
+    int32_t root_node, object;
+    float box_lo[3], box_hi[3]; // render-space AABB of the transformed object box, padded
+};
+struct HostObject {
+    int64_t first_triangle = 0, n_triangles = 0;
+    unsigned root_node = 0;
+    float box[6] = {0, 0, 0, 0, 0, 0}; // object-space bounds of its triangles (filled by the build)
+};
+
 struct RenderData; // render.cu
 
 } // namespace b200pt
@@ -74,6 +87,7 @@ struct b200pt_scene {
     cudaStream_t stream = nullptr;
     // b200pt_trace (host buffers): copy-in / copy-out streams and per-chunk events of the three-stage pipeline
     cudaStream_t stream_h2d = nullptr, stream_d2h = nullptr;
+    cudaStream_t stream2 = nullptr; // second traversal stream: consecutive chunks alternate, so a chunk's CTAs fill the tail of the one before
     std::vector<cudaEvent_t> pipe_events;
 
     // geometry as uploaded (render space)
@@ -88,6 +102,13 @@ struct b200pt_scene {
     int32_t n_spheres = 0;
     b200pt::SphereRec *d_spheres = nullptr;
 
+    // instancing (b200pt_scene_desc.objects / instances)
+    int64_t n_top_triangles = 0;
+    unsigned n_top_nodes = 0;
+    std::vector<b200pt::HostObject> objects;
+    std::vector<b200pt_instance> instances;
+    b200pt::InstRec *d_instances = nullptr;
+
     // accelerator
     bool built = false;
     b200pt::BVH8 bvh;
@@ -100,11 +121,12 @@ struct b200pt_scene {
     float scene_bounds[6] = {0, 0, 0, 0, 0, 0};
 
     // traversal
-    unsigned long long *d_trace_counters = nullptr; // [0] ray ticket, [1] nodes, [2] tris, [3] err
+    unsigned long long *d_trace_counters = nullptr; // [0] ray ticket, [1] nodes, [2] tris, [3] err, [4..11] tickets of pipelined chunks
     bool counting = false;
     // k_trace tuning (b200pt_trace_tune): lanes idle before a warp refills, triangle tests per triangle phase, CTA cap per SM
     int tune_refill = 4, tune_tri_steps = 1, tune_ctas_per_sm = 0;
     int tune_wf_refill = 0, tune_wf_tri_steps = 0; // wavefront trace kernels; 0 = the built-in default
+    int tune_shade_occ = 0;                        // shade kernels: CTAs per SM the register allocation is held to (0 = default)
     int64_t last_counts[3] = {0, 0, 0};
     int64_t device_bytes = 0;
 
@@ -118,6 +140,7 @@ struct b200pt_scene {
 namespace b200pt {
 
 int build_bvh(b200pt_scene *s, b200pt_build_stats *stats);
+int finish_instances(b200pt_scene *s); // after the build: instance records (object roots and boxes) to the device
 // keep_status: leave the node / triangle / overflow counters as they are (a later chunk of the same batch); the work ticket is
 // always reset
 // caller-layout device arrays of one chunk (b200pt_trace_batch): o[n*3], d[n*3], tmax[n] in; prim[n], t[n], b12[n*2] out (any may be null)
@@ -126,8 +149,11 @@ struct TraceHostIO {
     int32_t *prim;
     float *t, *b12;
 };
+// ticket_slot / stream: a pipelined chunk (b200pt_trace_batch) runs on its own stream with its own work ticket, so that it
+// can be resident together with the chunk before it
 int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev, bool keep_status = false,
-                 const TraceHostIO *io = nullptr);
+                 const TraceHostIO *io = nullptr, int ticket_slot = -1, cudaStream_t stream = nullptr);
+constexpr int kTraceCounterWords = 12, kTraceTicketRing = 8;
 void free_render(b200pt_scene *s);
 int ensure_scratch(b200pt_scene *s, size_t bytes);
 

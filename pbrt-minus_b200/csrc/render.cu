@@ -1677,8 +1677,9 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_COATED_CONDUCTOR>(const WF 
 // ---- gpu_evaluate_material + sample_bsdf + sample_Ld_volume, specialised per material
 // EXT: the extended variant of a shade kernel -- media (when the scene has any) and textured materials; scenes with neither
 // run the plain one, which carries none of that code
-template <int MAT, bool EXT>
-__global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ? 1 : 2) k_shade(WF wf) {
+// OCC: resident CTAs per SM the register allocation is held to (0: 2 for the plain materials, 1 for the layered ones)
+template <int MAT, bool EXT, int OCC = 0>
+__global__ void __launch_bounds__(WF_BLOCK, OCC ? OCC : ((MAT >= B200PT_MAT_COATED_DIFFUSE) ? 1 : 2)) k_shade(WF wf) {
     const bool MEDIA = EXT && wf.has_media;
     const unsigned n = wf.c->p[wf.parity].n_mat[MAT];
     const unsigned stride = gridDim.x * blockDim.x;
@@ -1716,6 +1717,20 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
             S4 lpdf = wf.pool.lpdf[slot];
             bool lpdf_dirty = false;
             int4 ids = wf.pool.ids[slot];
+            // All four sampler draws of this vertex are taken HERE, before the geometry and the BSDF are set up: each draw is a
+            // long chain of dependent integer operations (MurmurHash of (pixel, dimension), Kensler permutation, a modulo by spp)
+            // that depends on nothing but the path's ids, so the four chains overlap with one another and with the memory
+            // latency of the triangle / material / light records instead of running one after the other between them.  The
+            // consumption order is the reference's: NEE draws get_1d + get_2d before any early-out, then BSDF sampling draws
+            // get_1d + get_2d (megakernel_path.cu:201-207, wavefront_path.cu:458-459); a specular BSDF skips NEE, and then
+            // the first two draws ARE the BSDF's.
+            Sampler s = load_sampler(wf, slot, ids);
+            const float draw_a = s.get_1d();
+            const float2 draw_b = s.get_2d();
+            const uint64_t state_ab = s.state;
+            const int dim_ab = s.dimension;
+            const float draw_c = s.get_1d();
+            const float2 draw_d = s.get_2d();
             BSDF<MAT> bsdf;
             // BSDF(ns, dpdus) (base/bsdf.h:16-17): Frame::from_xz(normalize(dpdus), ns)
             bsdf.frame = frame_from_xz(normalize(si.dpdu), si.ns);
@@ -1724,12 +1739,16 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
             if (wf.regularize && (ids.w & PF_ANY_NON_SPECULAR)) bsdf.regularize();
             const uint32_t flags = bsdf.flags();
             S4 beta = wf.pool.beta[slot];
-            Sampler s = load_sampler(wf, slot, ids);
+            const bool nee = flags_non_specular(flags);
+            if (!nee) { // the sampler stands after two draws
+                s.state = state_ab;
+                s.dimension = dim_ab;
+            }
             const V3 wo = si.wo;
             const V3 wo_l = bsdf.frame.to_local(wo);
 
             // ---- next-event estimation (MegakernelPathIntegrator::sample_Ld_volume, megakernel_path.cu:185-264)
-            if (flags_non_specular(flags)) {
+            if (nee) {
                 LightCtx ctx{si.p, si.err, si.n, si.ns};
                 if ((flags & BXDF_REFLECTION) && !(flags & BXDF_TRANSMISSION)) {
                     ctx.p = offset_ray_origin(si.p, si.err, si.n, wo);
@@ -1738,8 +1757,8 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
                     ctx.p = offset_ray_origin(si.p, si.err, si.n, -wo);
                     ctx.err = v3(0.f, 0.f, 0.f);
                 }
-                const float ul = s.get_1d();
-                const float2 up = s.get_2d(); // both drawn before any early-out, as the reference does
+                const float ul = draw_a;
+                const float2 up = draw_b; // both drawn before any early-out, as the reference does
                 if (wf.n_lights > 0) {
                     const int li = alias_sample(wf.alias, wf.n_lights, ul);
                     const LightRec Lr = wf.lights[li];
@@ -1795,8 +1814,8 @@ __global__ void __launch_bounds__(WF_BLOCK, (MAT >= B200PT_MAT_COATED_DIFFUSE) ?
             }
 
             // ---- BSDF sampling (WavefrontPathIntegrator::sample_bsdf, wavefront_path.cu:456-474)
-            const float uc = s.get_1d();
-            const float2 u2 = s.get_2d();
+            const float uc = nee ? draw_c : draw_a;
+            const float2 u2 = nee ? draw_d : draw_b;
             BSDFSample bs;
             bool ok = wo_l.z != 0.f && flags != 0u && bsdf.sample(wo_l, uc, u2, bs);
             if (ok) ok = is_positive(bs.f) && bs.pdf != 0.f && bs.wi.z != 0.f;
@@ -2062,6 +2081,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
         }
     } guard{ev0, ev1, ev_poll[0], ev_poll[1]};
 
+    const int shade_occ = s->tune_shade_occ;
     const int grid = s->sm_count * 8; // stage kernels: grid-stride over the pool / device-side queue counts
     CU_TRY(cudaEventRecord(ev0, st));
     k_init_pool<<<(pool_size + 255) / 256, 256, 0, st>>>(wf);
@@ -2093,14 +2113,20 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
             // one shade kernel per material type PRESENT in the scene (a type without materials has no queue)
             if (r->has_mat[B200PT_MAT_DIFFUSE]) {
                 if (ext_shade) k_shade<B200PT_MAT_DIFFUSE, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else if (shade_occ == 3) k_shade<B200PT_MAT_DIFFUSE, false, 3><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else if (shade_occ == 4) k_shade<B200PT_MAT_DIFFUSE, false, 4><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_shade<B200PT_MAT_DIFFUSE, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
             if (r->has_mat[B200PT_MAT_CONDUCTOR]) {
                 if (ext_shade) k_shade<B200PT_MAT_CONDUCTOR, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else if (shade_occ == 3) k_shade<B200PT_MAT_CONDUCTOR, false, 3><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else if (shade_occ == 4) k_shade<B200PT_MAT_CONDUCTOR, false, 4><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_shade<B200PT_MAT_CONDUCTOR, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
             if (r->has_mat[B200PT_MAT_DIELECTRIC]) {
                 if (ext_shade) k_shade<B200PT_MAT_DIELECTRIC, true><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else if (shade_occ == 3) k_shade<B200PT_MAT_DIELECTRIC, false, 3><<<grid, WF_BLOCK, 0, st>>>(wf);
+                else if (shade_occ == 4) k_shade<B200PT_MAT_DIELECTRIC, false, 4><<<grid, WF_BLOCK, 0, st>>>(wf);
                 else k_shade<B200PT_MAT_DIELECTRIC, false><<<grid, WF_BLOCK, 0, st>>>(wf);
             }
             if (r->has_mat[B200PT_MAT_DIFFUSE_TRANSMISSION]) {

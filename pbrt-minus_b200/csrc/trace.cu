@@ -29,7 +29,8 @@ struct TraceParams {
     const float4 *rays;
     float4 *hits;
     long long n;
-    unsigned long long *counters; // [0] ticket, [1] nodes, [2] tris, [3] overflow flag
+    unsigned long long *counters; // [1] nodes, [2] tris, [3] overflow flag
+    unsigned long long *ticket;   // the work ticket of this launch
     uint32_t prmt_bias;           // 0x47000000 (32768.0f), passed as a parameter so PRMT keeps an immediate selector
     // caller-layout I/O (b200pt_trace / b200pt_trace_batch): when `o` is set the kernel reads the caller's o[n*3] / d[n*3] /
     // tmax[n] and writes prim[n] / t[n] / b12[n*2] itself -- no repacking passes on either side of the traversal
@@ -67,7 +68,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
             const int n_idle = __popc(idle);
             const int leader = __ffs(idle) - 1;
             unsigned long long base = 0;
-            if (lane == leader) base = atomicAdd(p.counters, (unsigned long long)n_idle);
+            if (lane == leader) base = atomicAdd(p.ticket, (unsigned long long)n_idle);
             base = __shfl_sync(0xffffffffu, base, leader);
             if ((long long)base + n_idle >= p.n) exhausted = true;
             if (ray < 0) {
@@ -408,7 +409,7 @@ static TraceKernel pick_kernel(bool any_hit, bool counting, int tri_steps) {
 }
 
 int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, void *hits_dev, bool keep_status,
-                 const TraceHostIO *io) {
+                 const TraceHostIO *io, int ticket_slot, cudaStream_t stream) {
     if (!s->built) {
         set_error("b200pt_trace: call b200pt_bvh_build first");
         return B200PT_ERR_STATE;
@@ -426,11 +427,14 @@ int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, 
     p.b12_out = io ? io->b12 : nullptr;
     p.n = n;
     p.counters = s->d_trace_counters;
+    p.ticket = s->d_trace_counters + (ticket_slot >= 0 ? 4 + ticket_slot % kTraceTicketRing : 0);
     p.prmt_bias = 0x47000000u;
+    if (!stream) stream = s->stream;
     // per launch: the work ticket and (unless this is a later chunk of one batch) the visit counters.  The overflow word
     // [3] is STICKY across launches -- back-to-back asynchronous launches must not wipe an earlier launch's report; it is
     // cleared when the host reads it (check_trace_status).
-    CU_TRY(cudaMemsetAsync(s->d_trace_counters, 0, (keep_status ? 1 : 3) * sizeof(unsigned long long), s->stream));
+    if (ticket_slot >= 0) CU_TRY(cudaMemsetAsync(p.ticket, 0, sizeof(unsigned long long), stream));
+    else CU_TRY(cudaMemsetAsync(s->d_trace_counters, 0, (keep_status ? 1 : 3) * sizeof(unsigned long long), stream));
 
     // tuning knobs (defaults are the measured best; b200pt_trace_tune overrides them per scene)
     const int refill = s->tune_refill, tri_steps = s->tune_tri_steps;
@@ -445,7 +449,7 @@ int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, 
     long long blocks = (long long)s->sm_count * per_sm;
     const long long needed = (n + TRACE_BLOCK - 1) / TRACE_BLOCK;
     if (blocks > needed) blocks = needed;
-    kern<<<(unsigned)blocks, TRACE_BLOCK, 0, s->stream>>>(p);
+    kern<<<(unsigned)blocks, TRACE_BLOCK, 0, stream>>>(p);
     CU_TRY(cudaGetLastError());
     return B200PT_OK;
 }

@@ -333,6 +333,59 @@ def test_cornell_converged_4096spp(b200pt, tmp_path):
     assert np.allclose(total, full, rtol=2e-4, atol=1e-3)
 
 
+_MP_WORKER = r'''
+import importlib, json, os, sys
+import numpy as np, torch, torch.distributed as dist
+root, scene_path, out_path, spp = sys.argv[1], sys.argv[2], sys.argv[3], int(sys.argv[4])
+sys.path.insert(0, root)
+pkg = importlib.import_module("pbrt-minus_b200")
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+sc = pkg.pbrt_scene.load(scene_path, spp=spp)
+integ = pkg.WavefrontPathIntegrator(sc, device=0)          # both ranks share GPU 0 (the test box has one)
+film = integ.create_film()
+b, e = pkg.sample_range(spp, rank, world)                  # the multi-GPU split: disjoint sample ranges of every pixel
+integ.render(film, sample_begin=b, sample_end=e)
+part = torch.from_numpy(film.raw().astype(np.float32))
+dist.reduce(part, dst=0, op=dist.ReduceOp.SUM)             # what b200pt_film_reduce does with ncclReduce between GPUs
+if rank == 0:
+    film.clear()
+    integ.render(film)
+    full = film.raw()
+    w = part.numpy()[..., 3:]
+    a = np.where(w != 0, part.numpy()[..., :3] / np.where(w == 0, 1, w), 0)
+    wf = full[..., 3:]
+    bb = np.where(wf != 0, full[..., :3] / np.where(wf == 0, 1, wf), 0)
+    rel = float(np.mean((a - bb) ** 2 / (bb ** 2 + 1e-4)))
+    json.dump({"world": world, "relMSE": rel, "max_abs_raw": float(np.abs(part.numpy() - full).max()),
+               "ranges": [pkg.sample_range(spp, k, world) for k in range(world)]}, open(out_path, "w"))
+film.close()
+integ.close()
+dist.barrier()
+dist.destroy_process_group()
+'''
+
+
+def test_world2_sample_partition_and_film_sum_equal_the_single_render(b200pt, tmp_path):
+    """SURVEY 8e with the REAL renderer: two processes (torchrun, gloo -- the GPU test box has one device, and NCCL refuses two
+    ranks on one GPU) each render their sample range of every pixel through b200pt_render, the raw films are summed onto rank 0
+    as b200pt_film_reduce's ncclReduce would, and the sum equals the film of one process rendering every sample (up to fp32
+    summation order).  The NCCL form of the same thing runs inside bench.py's timed render leg at N > 1 (`film_check`)."""
+    import subprocess
+    import sys
+    p = os.path.join(str(tmp_path), "scene.pbrt")
+    open(p, "w").write(scene_text("cornell-box-specular.pbrt", (48, 32)))
+    w = os.path.join(str(tmp_path), "worker.py")
+    open(w, "w").write(_MP_WORKER)
+    out = os.path.join(str(tmp_path), "out.json")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29671", w, ROOT, p, out, "16"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-500:] + r.stderr[-2000:]
+    res = json.load(open(out))
+    assert res["world"] == 2 and res["ranges"] == [[0, 8], [8, 16]]
+    assert res["relMSE"] <= 1e-10 and res["max_abs_raw"] <= 1e-3
+
+
 def test_pool_size_does_not_change_the_image(b200pt, tmp_path):
     text = scene_text("cornell-box-specular.pbrt", (40, 24))
     a, sa = render(b200pt, text, 16, tmp_path, pool_size=1024)

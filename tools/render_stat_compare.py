@@ -94,6 +94,12 @@ def main():
                           "relMSE_over_tau": float(rel.mean() / max(tau.mean(), 1e-30)),
                           "gate_relMSE": bool(rel.mean() <= args.slack * tau.mean()),
                           "pixels_excluded_reference_nonfinite_or_gt_1e4": int((~finite).sum()),
+                          # the excluded pixels, listed: (x, y, reference rgb, ours rgb); the reference's own fireflies / NaNs
+                          "excluded_pixels": [{"x": int(x), "y": int(y), "ref": [float(v) for v in ref[y, x]], "ours": [float(v) for v in ours[y, x]]}
+                                              for y, x in list(zip(*np.nonzero(~finite)))[:64]],
+                          "mean_rgb_ref_without_excluded": [float(v) for v in ref[finite].reshape(-1, 3).mean(0)],
+                          "mean_rgb_ours_without_excluded": [float(v) for v in ours[finite].reshape(-1, 3).mean(0)],
+                          "max_abs_diff_without_excluded": float(np.abs(d[finite]).max()),
                           "frac_pixels_beyond_3sigma": float(out3.sum() / max(1, lit.sum())),
                           "z_rms": float(np.sqrt((z ** 2).mean())), "z_p50": float(np.median(z)),
                           "identical_pixels_frac": float((np.abs(d).max(axis=2) == 0).mean()),
