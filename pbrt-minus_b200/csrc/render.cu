@@ -1018,6 +1018,41 @@ __device__ __forceinline__ void triangle_interaction(const WF &wf, V3 p0, V3 p1,
 // Sphere::interaction_from_intersection (shapes/sphere.h:71-125) + Transform::operator()(SurfaceInteraction)
 // (euclidean_space/transform.cu:57-97)
 // Disk::interaction_from_intersection (shapes/disk.cu:133-153): the hit point is recomputed as disk_intersect does it
+// Transform::operator()(SurfaceInteraction) (euclidean_space/transform.cu:56-97): the interaction found in an object instance's
+// space, brought to render space as TransformedPrimitive::intersect does (primitives/transformed_primitive.cu:31-33).  pi goes
+// through plain interval arithmetic (the generic Point3<Interval> operator), normals through the inverse transpose, and the two
+// normals are re-faced towards each other at the end.
+__device__ __forceinline__ void instance_to_render(const InstRec &I, Isect &si) {
+    Iv pi[3];
+    xf_point_iv(I.rfi, iv_err(si.p.x, si.err.x), iv_err(si.p.y, si.err.y), iv_err(si.p.z, si.err.z), pi);
+    si.p = iv_mid3(pi);
+    si.err = iv_err3(pi);
+    V3 n = normalize(xf_normal(I.ifr, si.n));
+    V3 ns = normalize(xf_normal(I.ifr, si.ns));
+    si.wo = normalize(xf_vector(I.rfi, si.wo));
+    si.dpdu = xf_vector(I.rfi, si.dpdu);
+    n = face_forward(n, ns);
+    ns = face_forward(ns, n);
+    si.n = n;
+    si.ns = ns;
+}
+
+// the hit of slot `slot` on leaf-record triangle `prim`: interaction in render space, through the hit's instance if it has one
+__device__ __forceinline__ void hit_triangle_interaction(const WF &wf, int slot, const float4 *tp, float4 hit, V3 ro, V3 rd, Isect &si) {
+    const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+    const int inst = wf.n_instances > 0 ? wf.pool.inst[slot] : -1;
+    if (inst < 0) {
+        triangle_interaction(wf, v3(v0), v3(v1), v3(v2), __float_as_int(v0.w), __float_as_uint(v1.w), hit.z, hit.w, -rd, si);
+        return;
+    }
+    const InstRec &I = wf.instances[inst];
+    V3 oi, di;
+    float dt;
+    instance_ray(I.ifr, ro, rd, &oi, &di, &dt);
+    triangle_interaction(wf, v3(v0), v3(v1), v3(v2), __float_as_int(v0.w), __float_as_uint(v1.w), hit.z, hit.w, -di, si);
+    instance_to_render(I, si);
+}
+
 __device__ __forceinline__ void disk_interaction(const SphereRec &s, V3 ro, V3 rd, float t, V3 wo, Isect &si) {
     Iv oi[3];
     xf_point_iv(s.ofr, iv(ro.x), iv(ro.y), iv(ro.z), oi);
@@ -1461,9 +1496,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                     if (prim >= (int)wf.bvh.n_tris) {
                         sphere_interaction(wf.spheres[prim - (int)wf.bvh.n_tris], ro, rd, hit.y, -rd, si);
                     } else {
-                        const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
-                        const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
-                        triangle_interaction(wf, v3(v0), v3(v1), v3(v2), __float_as_int(v0.w), __float_as_uint(v1.w), hit.z, hit.w, -rd, si);
+                        hit_triangle_interaction(wf, slot, wf.bvh.tris + 3 * (size_t)prim, hit, ro, rd, si);
                     }
                     mat = mix_hash_float(si.p, si.err, si.wo) < mr.scale ? mr.mix_a : mr.mix_b;
                     float4 misc = wf.pool.misc[slot];
@@ -1703,11 +1736,9 @@ __global__ void __launch_bounds__(WF_BLOCK, OCC ? OCC : ((MAT >= B200PT_MAT_COAT
                 mat = sp.material;
             } else {
                 const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
-                const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
-                const uint32_t mw = __float_as_uint(v1.w);
-                mat = int(mw & kTriMaterialMask);
-                prim_id = __float_as_int(v0.w);
-                triangle_interaction(wf, v3(v0), v3(v1), v3(v2), prim_id, mw, hit.z, hit.w, -rd, si);
+                mat = int(__float_as_uint(__ldg(&tp[1].w)) & kTriMaterialMask);
+                prim_id = __float_as_int(__ldg(&tp[0].w));
+                hit_triangle_interaction(wf, slot, tp, hit, ro, rd, si);
             }
             if (wf.has_mix && wf.materials[mat].type == B200PT_MAT_MIX) mat = __float_as_int(wf.pool.misc[slot].z);
             float4 vol = make_float4(0.f, 0.f, 0.f, 0.f); // media scenes: .y = medium of the ray that arrived here
@@ -1894,6 +1925,8 @@ static int ensure_pool(b200pt_scene *s, int pool_size) {
         if ((rc = pool_alloc(r, &P.vol, n))) return rc;
         if ((rc = pool_alloc(r, &r->q.vol, n))) return rc;
     }
+    P.inst = nullptr;
+    if (!s->instances.empty() && (rc = pool_alloc(r, &P.inst, n))) return rc;
     if ((rc = pool_alloc(r, &P.rng, n))) return rc;
     if ((rc = pool_alloc(r, &P.ids, n))) return rc;
     if ((rc = pool_alloc(r, &P.state, n))) return rc;
@@ -2026,6 +2059,12 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     wf.bvh = s->bvh;
     wf.spheres = s->d_spheres;
     wf.n_spheres = s->n_spheres;
+    wf.instances = s->d_instances;
+    wf.n_instances = (int32_t)s->instances.size();
+    if (wf.n_instances > 0 && r->n_media > 0) {
+        set_error("b200pt_render: object instances in scenes with media are not supported");
+        return B200PT_ERR_UNSUPPORTED;
+    }
     wf.N = s->d_N;
     wf.uv = s->d_uv;
     wf.idx = s->d_idx;

@@ -103,6 +103,34 @@ __device__ __forceinline__ void xf_point_iv(const float *m, Iv px, Iv py, Iv pz,
 __device__ __forceinline__ V3 iv_mid3(const Iv v[3]) { return v3(iv_mid(v[0]), iv_mid(v[1]), iv_mid(v[2])); }
 __device__ __forceinline__ V3 iv_err3(const Iv v[3]) { return v3((v[0].hi - v[0].lo) / 2.f, (v[1].hi - v[1].lo) / 2.f, (v[2].hi - v[2].lo) / 2.f); }
 
+// Transform::apply_inverse(Ray, &t_max) (euclidean_space/transform.cu:36-54, transform.h:380-420): a render-space ray into the
+// space of an object instance (TransformedPrimitive::intersect, primitives/transformed_primitive.cu:20-34).  The origin is an
+// exact point, transformed with the (m00 x + m01 y) + (m02 z + m03) association and pushed along the ray to the edge of its
+// error bound; t_max shrinks by the same dt.  The direction is NOT renormalised: t means the same along both rays (up to dt).
+__device__ __forceinline__ void instance_ray(const float *inv, V3 o, V3 d, V3 *oi, V3 *di, float *dt) {
+    const V3 p = v3((inv[0] * o.x + inv[1] * o.y) + (inv[2] * o.z + inv[3]), (inv[4] * o.x + inv[5] * o.y) + (inv[6] * o.z + inv[7]),
+                    (inv[8] * o.x + inv[9] * o.y) + (inv[10] * o.z + inv[11]));
+    const float g3 = gamma_n(3);
+    const V3 e = v3(g3 * (fabsf(inv[0] * o.x) + fabsf(inv[1] * o.y) + fabsf(inv[2] * o.z)),
+                    g3 * (fabsf(inv[4] * o.x) + fabsf(inv[5] * o.y) + fabsf(inv[6] * o.z)),
+                    g3 * (fabsf(inv[8] * o.x) + fabsf(inv[9] * o.y) + fabsf(inv[10] * o.z)));
+    const V3 dd = xf_vector(inv, d);
+    // Point3fi(p, e): the interval [p - e, p + e] with outward rounding; its midpoint and half width are what the ray uses
+    const Iv ix = iv_err(p.x, e.x), iy = iv_err(p.y, e.y), iz = iv_err(p.z, e.z);
+    V3 po = v3(iv_mid(ix), iv_mid(iy), iv_mid(iz));
+    const float l2 = len2(dd);
+    *dt = 0.f;
+    if (l2 > 0.f) {
+        const V3 oerr = v3((ix.hi - ix.lo) / 2.f, (iy.hi - iy.lo) / 2.f, (iz.hi - iz.lo) / 2.f);
+        *dt = dot(vabs(dd), oerr) / l2;
+        // Point3fi += Vector3f * dt, then to_point3f(): interval arithmetic, midpoint
+        const Iv jx = ix + iv(dd.x * *dt), jy = iy + iv(dd.y * *dt), jz = iz + iv(dd.z * *dt);
+        po = v3(iv_mid(jx), iv_mid(jy), iv_mid(jz));
+    }
+    *oi = po;
+    *di = dd;
+}
+
 __device__ __forceinline__ bool sphere_clip(const SphereRec &s, V3 &pHit, float &phi) {
     if (pHit.x == 0.f && pHit.y == 0.f) pHit.x = 1e-5f * s.radius;
     phi = atan2f(pHit.y, pHit.x);

@@ -204,7 +204,27 @@ __device__ __forceinline__ int next_sphere(const SphereRec *sph, int n, int k, f
     return k;
 }
 
-template <bool SHADOW, bool SPH>
+// first instance at or after k whose padded render-space box the ray touches; n when there is none
+__device__ __forceinline__ int next_instance(const InstRec *inst, int n, int k, V3 o, V3 d, float t_max) {
+    const float idx = safe_rcp_dir(d.x), idy = safe_rcp_dir(d.y), idz = safe_rcp_dir(d.z);
+    for (; k < n; k++) {
+        const float *lo = inst[k].box_lo, *hi = inst[k].box_hi;
+        const float x0 = (__ldg(lo) - o.x) * idx, x1 = (__ldg(hi) - o.x) * idx;
+        const float y0 = (__ldg(lo + 1) - o.y) * idy, y1 = (__ldg(hi + 1) - o.y) * idy;
+        const float z0 = (__ldg(lo + 2) - o.z) * idz, z1 = (__ldg(hi + 2) - o.z) * idz;
+        const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.f));
+        const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
+        if (tn <= tf * 1.00001f + 1e-30f) break;
+    }
+    return k;
+}
+
+// INST: the scene has object instances (two-level traversal).  A ray first walks the top-level tree (and the quadrics); when
+// that is exhausted it visits, one after the other, every instance whose box it touches: the ray is taken into the instance's
+// space with the reference's Transform::apply_inverse(Ray, &t_max) (t_max = best t so far minus the origin shift) and walks
+// the OBJECT's tree -- built once, shared by all its instances -- from that tree's root.  Hits keep the instance-space t, as
+// TransformedPrimitive::intersect returns it (primitives/transformed_primitive.cu:20-34).
+template <bool SHADOW, bool SPH, bool INST>
 __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
     __shared__ uint2 sm_stack_all[SM_STACK * TRACE_BLOCK];
     uint2 *const sm_stack = sm_stack_all + threadIdx.x;
@@ -234,6 +254,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
     int sp = 0;
     float ht = 0, hb1 = 0, hb2 = 0;
     int hprim = -1;
+    int cur_inst = -1, hinst = -1; // INST: the instance whose object tree the lane is in (-1: top level); instance of the best hit
     int sph_k = 0;      // next sphere to test for this lane's ray (n_spheres: none pending)
     int skip_prim = -1; // SHADOW: the sampled light's own triangle (the reference's three visibility rays cannot reach it)
     unsigned overflow = 0;
@@ -274,6 +295,8 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                     ht = ro.w;
                     hb1 = 0.f; hb2 = 0.f;
                     hprim = -1;
+                    cur_inst = -1;
+                    hinst = -1;
                     // spheres are tested as a phase of their own below, and only those whose box the ray touches
                     sph_k = (SPH && live) ? next_sphere(wf.spheres, wf.n_spheres, 0, ox, oy, oz, idx, idy, idz, ht) : wf.n_spheres;
                 }
@@ -321,6 +344,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                         hb1 = th.b1;
                         hb2 = th.b2;
                         hprim = int(tg.x + ti);
+                        if (INST) hinst = cur_inst;
                         if (SHADOW) {
                             tg.y = 0u;
                             ng.y = 0u;
@@ -356,7 +380,42 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                 ng.y = (hitmask & 0xff000000u) | (__float_as_uint(n0.w) >> 24);
                 tg.y = hitmask & 0x00ffffffu;
             } else {
-                if (SHADOW) {
+                bool retire = true;
+                if (INST && !(SHADOW && hprim >= 0)) {
+                    // this tree is exhausted: on to the next instance the ray can reach, if any
+                    float4 ro4, rd4;
+                    if (SHADOW) {
+                        ro4 = __ldg(wf.q.sh_o + ray);
+                        rd4 = __ldg(wf.q.sh_d + ray);
+                    } else {
+                        ro4 = wf.pool.ray_o[slot];
+                        rd4 = wf.pool.ray_d[slot];
+                    }
+                    const V3 ro = v3(ro4.x, ro4.y, ro4.z), rd = v3(rd4.x, rd4.y, rd4.z);
+                    const int ni = ro4.w >= 0.f ? next_instance(wf.instances, wf.n_instances, cur_inst + 1, ro, rd, ht) : wf.n_instances;
+                    if (ni < wf.n_instances) {
+                        // the best t so far is a t along the ray of the space it was found in; like the reference, it is handed to the
+                        // next primitive as it is (best_t = intersection->t_hit, accelerator/hlbvh.cu:499) and shifted by that ray's dt
+                        const InstRec &I = wf.instances[ni];
+                        V3 oi, di;
+                        float dt;
+                        instance_ray(I.ifr, ro, rd, &oi, &di, &dt);
+                        ox = oi.x; oy = oi.y; oz = oi.z;
+                        if (SPH) { dx = di.x; dy = di.y; dz = di.z; }
+                        idx = safe_rcp_dir(di.x); idy = safe_rcp_dir(di.y); idz = safe_rcp_dir(di.z);
+                        rs = ray_shear(di.x, di.y, di.z);
+                        octinv4 = ((idx < 0.f ? 0u : 4u) | (idy < 0.f ? 0u : 2u) | (idz < 0.f ? 0u : 1u)) * 0x01010101u;
+                        ht = ht - dt;
+                        ng = make_uint2((uint32_t)I.root_node, 0x80000000u);
+                        tg = make_uint2(0u, 0u);
+                        sp = 0;
+                        cur_inst = ni;
+                        retire = false;
+                    }
+                }
+                if (!retire) {
+                    // carries on in the instance's object tree
+                } else if (SHADOW) {
                     if (hprim < 0) {
                         const int s2 = __ldg(wf.q.sh_slot + ray);
                         const float4 c = __ldg(wf.q.sh_contrib + ray);
@@ -366,8 +425,9 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                     }
                 } else {
                     wf.pool.hit[slot] = make_float4(__int_as_float(hprim), hprim >= 0 ? ht : kInf, hb1, hb2);
+                    if (INST) wf.pool.inst[slot] = hinst;
                 }
-                ray = -1;
+                if (retire) ray = -1;
             }
         }
     }
@@ -380,16 +440,19 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
 
 int launch_trace_wf(b200pt_scene *s, const WF &wf, bool shadow) {
     typedef void (*K)(WF);
-    static const K kern[2][2] = {{k_trace_wf<false, false>, k_trace_wf<false, true>}, {k_trace_wf<true, false>, k_trace_wf<true, true>}};
-    static int per_sm[2][2] = {{0, 0}, {0, 0}};
-    const int sph = wf.n_spheres > 0 ? 1 : 0;
-    if (per_sm[shadow][sph] == 0) {
+    static const K kern[2][2][2] = {{{k_trace_wf<false, false, false>, k_trace_wf<false, false, true>},
+                                     {k_trace_wf<false, true, false>, k_trace_wf<false, true, true>}},
+                                    {{k_trace_wf<true, false, false>, k_trace_wf<true, false, true>},
+                                     {k_trace_wf<true, true, false>, k_trace_wf<true, true, true>}}};
+    static int per_sm[2][2][2] = {{{0, 0}, {0, 0}}, {{0, 0}, {0, 0}}};
+    const int sph = wf.n_spheres > 0 ? 1 : 0, inst = wf.n_instances > 0 ? 1 : 0;
+    if (per_sm[shadow][sph][inst] == 0) {
         int v = 0;
-        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kern[shadow][sph], TRACE_BLOCK, 0));
-        per_sm[shadow][sph] = v < 1 ? 1 : v;
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kern[shadow][sph][inst], TRACE_BLOCK, 0));
+        per_sm[shadow][sph][inst] = v < 1 ? 1 : v;
     }
-    const unsigned blocks = unsigned(s->sm_count * per_sm[shadow][sph]);
-    kern[shadow][sph]<<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf);
+    const unsigned blocks = unsigned(s->sm_count * per_sm[shadow][sph][inst]);
+    kern[shadow][sph][inst]<<<blocks, TRACE_BLOCK, 0, s->stream>>>(wf);
     CU_TRY(cudaGetLastError());
     return B200PT_OK;
 }

@@ -82,6 +82,7 @@ struct PathPool {
     uint64_t *rng;  // PCG32 state (inc is re-derived from the pixel index)
     int4 *ids;      // pixel, sample, sampler dimension, flags
     uint8_t *state; // ST_*
+    int32_t *inst;  // scenes with object instances only: the instance the hit belongs to (-1: top level)
 };
 
 // Queue sizes and work tickets of ONE pass.  There are two sets, used by alternate passes (wf.parity): every count is
@@ -121,6 +122,8 @@ struct WF {
     BVH8 bvh;
     const SphereRec *spheres;
     int32_t n_spheres;
+    const InstRec *instances; // object instances: each reaches its object's BVH8 through a transformed ray
+    int32_t n_instances;
     // per-vertex shading normals / uvs of the meshes that have them (render space; indexed through the triangle's
     // primitive id and the index buffer); null when no mesh has any
     const float *N, *uv;

@@ -771,6 +771,33 @@ class Scene:
                 self.lights.append({"triangle": first_tri + k, "spectrum": L, "scale": float(sc), "two_sided": int(two)})
         self.tri_light.append(tl)
 
+    # ---- object instancing (two-level: one BVH8 per object, a transformed ray per instance)
+    def add_instance(self, name, mesh_recs, rfi, scene_dir):
+        """ObjectInstance of an object's MESHES (scene_builder.cu:845-876, primitives/transformed_primitive.cu): the object's
+        triangles are stored once, in the object's own space, at the end of the triangle array (finalize_objects); each
+        instance is a transform.  `mesh_recs` are the shape records of the object definition."""
+        if not hasattr(self, "objects"):
+            self.objects, self.object_index, self.instances = [], {}, []
+        if name not in self.object_index:
+            self.object_index[name] = len(self.objects)
+            self.objects.append({"name": name, "meshes": mesh_recs})
+        self.instances.append({"object": self.object_index[name], "rfi": rfi})
+
+    def finalize_objects(self, scene_dir):
+        """append the instanced objects' triangles after the top-level ones and record their ranges"""
+        for ob in getattr(self, "objects", []):
+            first = sum(len(i) for i in self.idx)
+            for rec in ob["meshes"]:
+                Pr = rec["P"] if rec["rfo"].is_identity() else xf_points(rec["rfo"].m, rec["P"])
+                Nr = rec.get("N")
+                if Nr is not None and (not rec["rfo"].is_identity() or rec["ro"]):
+                    Nr = xf_normals(rec["rfo"].inv, Nr)
+                    if rec["ro"]:
+                        Nr = (-Nr).astype(F32)
+                flip = rec["ro"] ^ swaps_handedness(rec["rfo"].m)
+                self.add_mesh(Pr, rec["idx"], rec["material"], flip, None, scene_dir, N=Nr, uv=rec.get("uv"), medium_code=0)
+            ob["first"], ob["count"] = first, sum(len(i) for i in self.idx) - first
+
     def area_light_params(self, light_params, scene_dir):
         """DiffuseAreaLight ctor (lights/diffuse_area_light.cu:9-31): Lemit (default: the colour space's illuminant), scale
         divided by the photometric integral of Lemit, twosided"""
@@ -873,6 +900,22 @@ class Scene:
                     lights[i].render_from_light[:] = l["rfl"]
         d.n_lights, d.lights = len(self.lights), lights
         keep += [sph, spec, mats, lights]
+        objs = [o for o in getattr(self, "objects", []) if o.get("count", 0) > 0]
+        if objs:
+            if self.media:
+                raise SceneError("object instances in scenes with media are outside the hot path")
+            oa = (api.Object * len(objs))()
+            for i, o in enumerate(objs):
+                oa[i].first_triangle, oa[i].n_triangles = o["first"], o["count"]
+            remap = {id(o): i for i, o in enumerate(objs)}
+            live = [n for n in self.instances if id(self.objects[n["object"]]) in remap]
+            ia = (api.Instance * max(1, len(live)))()
+            for i, n in enumerate(live):
+                ia[i].object = remap[id(self.objects[n["object"]])]
+                ia[i].render_from_instance[:] = [float(v) for v in n["rfi"].m.reshape(-1)]
+                ia[i].instance_from_render[:] = [float(v) for v in n["rfi"].inv.reshape(-1)]
+            d.n_objects, d.objects, d.n_instances, d.instances = len(objs), oa, len(live), ia
+            keep += [oa, ia]
         if self.media:
             med = (api.Medium * len(self.media))()
             for i, m in enumerate(self.media):
@@ -938,9 +981,10 @@ class _GState:
         return g
 
 
-def load(path=None, text=None, spp=None, integrator=None, scene_dir=None):
+def load(path=None, text=None, spp=None, integrator=None, scene_dir=None, flatten_instances=False):
     """SceneBuilder::parse_file + preprocess (scene/scene_builder.cu:741-966) -> Scene.  `scene_dir`: where relative file names
-    (PLY meshes, spectra, images) of a scene given as text are looked up."""
+    (PLY meshes, spectra, images) of a scene given as text are looked up.  `flatten_instances`: copy every ObjectInstance's
+    triangles into the flat render-space scene instead of the two-level form (one BVH8 per object + a transform per instance)."""
     if text is None:
         text = open(path).read()
     if scene_dir is None:
@@ -1162,8 +1206,12 @@ def load(path=None, text=None, spp=None, integrator=None, scene_dir=None):
             if args[0] not in instances:
                 raise SceneError("ObjectInstance '%s' not found" % args[0])
             rfi = (render_from_world * g.ctm) * render_from_world.inverse()
+            meshes = [rec for rec in instances[args[0]] if rec["kind"] == "mesh"]
+            if meshes and not flatten_instances:
+                sc.add_instance(args[0], meshes, rfi, scene_dir)     # two-level: the object's tree is shared by its instances
             for rec in instances[args[0]]:
-                place_shape(rec, None if rfi.is_identity() else rfi, None)
+                if rec["kind"] != "mesh" or flatten_instances:       # quadrics ride in the flat list under the composite transform
+                    place_shape(rec, None if rfi.is_identity() else rfi, None)
         elif kw == "LightSource":
             sc.add_light_source(args[0], params_of(args[1:]), render_from_world * g.ctm, scene_dir)
         elif kw == "MakeNamedMedium":           # scene_builder.cu:362-365
@@ -1184,6 +1232,7 @@ def load(path=None, text=None, spp=None, integrator=None, scene_dir=None):
             raise SceneError("unknown directive '%s'" % kw)   # scene_builder.cu:467-468
     if sc.camera is None:
         raise SceneError("no WorldBegin")
+    sc.finalize_objects(scene_dir)
     # spp: CLI --spp > Sampler "integer pixelsamples" > 4 (scene_builder.cu:249-251,402-404)
     sc.spp = spp if spp is not None else (sc.spp if sc.spp is not None else 4)
     if integrator is not None:

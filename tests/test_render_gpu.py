@@ -251,6 +251,66 @@ def test_object_instances_match_reference(b200pt, tmp_path):
     check_against_golden(b200pt, tmp_path, "instances_96x64_64spp")
 
 
+def _instanced_scene_text(n_side=6, grid=24):
+    """one bumpy blob mesh (2 * grid^2 triangles), instanced n_side^2 times under rotations, non-uniform scales and a mirror"""
+    u = np.linspace(0, np.pi, grid + 1)
+    v = np.linspace(0, 2 * np.pi, grid + 1)
+    U, V = np.meshgrid(u, v, indexing="ij")
+    R = 0.4 * (1 + 0.15 * np.sin(5 * U) * np.cos(4 * V))
+    P = np.stack([R * np.sin(U) * np.cos(V), R * np.cos(U), R * np.sin(U) * np.sin(V)], -1).reshape(-1, 3)
+    idx = []
+    for i in range(grid):
+        for j in range(grid):
+            a, b, c, d = i * (grid + 1) + j, i * (grid + 1) + j + 1, (i + 1) * (grid + 1) + j, (i + 1) * (grid + 1) + j + 1
+            idx += [a, c, b, b, c, d]
+    mesh = 'Shape "trianglemesh" "integer indices" [%s] "point3 P" [%s]' % (" ".join(map(str, idx)), " ".join("%.6g" % x for x in P.reshape(-1)))
+    out = ['LookAt 0 4.5 -9  0 0.6 0  0 1 0', 'Camera "perspective" "float fov" [38]',
+           'Film "rgb" "string filename" ["inst.png"] "integer xresolution" [96] "integer yresolution" [64]', 'Integrator "path" "integer maxdepth" [4]',
+           'WorldBegin', 'Material "diffuse" "rgb reflectance" [0.6 0.6 0.6]',
+           'Shape "trianglemesh" "integer indices" [0 1 2 2 3 0] "point3 P" [-8 0 -8  8 0 -8  8 0 8  -8 0 8]',
+           'AttributeBegin', 'AreaLightSource "diffuse" "rgb L" [1 1 1] "float scale" [14]', 'Translate 0 6 0',
+           'Shape "trianglemesh" "integer indices" [0 2 1 0 3 2] "point3 P" [-2 0 -2  2 0 -2  2 0 2  -2 0 2]', 'AttributeEnd',
+           'ObjectBegin "blob"', 'Material "conductor" "spectrum eta" ["metal-Cu-eta"] "spectrum k" ["metal-Cu-k"] "float roughness" [0.15]', mesh,
+           'Material "diffuse" "rgb reflectance" [0.3 0.5 0.7]', 'Translate 0 0.55 0', 'Scale 0.4 0.4 0.4', mesh, 'ObjectEnd']
+    k = 0
+    for i in range(n_side):
+        for j in range(n_side):
+            x, z = (i - (n_side - 1) / 2) * 1.3, (j - (n_side - 1) / 2) * 1.3
+            out += ['AttributeBegin', 'Translate %.4f 0.45 %.4f' % (x, z), 'Rotate %d 0 1 0' % (37 * k % 360), 'Rotate %d 1 0 0' % (11 * k % 40),
+                    'Scale %.3f %.3f %.3f' % (0.8 + 0.05 * (k % 5), (1.0 + 0.1 * (k % 3)) * (-1 if k % 7 == 3 else 1), 0.9),
+                    'ObjectInstance "blob"', 'AttributeEnd']
+            k += 1
+    return "\n".join(out) + "\n"
+
+
+def test_two_level_instancing_matches_flattened_and_shares_geometry(b200pt, tmp_path):
+    """ObjectBegin / ObjectInstance as the reference keeps them (scene_builder.cu:809-876, primitives/transformed_primitive.cu):
+    ONE BVH8 per object, built once, reached per instance through Transform::apply_inverse(Ray, &t_max) with the hit brought
+    back by Transform::operator()(SurfaceInteraction).  36 instances (rotated, non-uniformly scaled, one in seven mirrored) of a
+    two-mesh object: the triangle array holds the object once, and the image equals the one rendered from the flattened
+    (instances copied into render space) form of the same scene up to the rounding of transformed rays vs transformed vertices."""
+    text = _instanced_scene_text()
+    p = os.path.join(str(tmp_path), "inst.pbrt")
+    open(p, "w").write(text)
+    two = b200pt.pbrt_scene.load(p, spp=64)
+    flat = b200pt.pbrt_scene.load(p, spp=64, flatten_instances=True)
+    d2, df = two.to_desc(), flat.to_desc()
+    assert d2.n_objects == 1 and d2.n_instances == 36 and d2.objects[0].n_triangles == 2 * 2 * 24 * 24
+    assert d2.n_triangles == 4 + d2.objects[0].n_triangles and df.n_triangles == 4 + 36 * d2.objects[0].n_triangles
+    imgs = []
+    for sc in (two, flat):
+        integ = b200pt.WavefrontPathIntegrator(sc, device=0)
+        film = integ.create_film()
+        integ.render(film)
+        imgs.append(film.get_pixel_rgb())
+        film.close()
+        integ.close()
+    assert np.isfinite(imgs[0]).all()
+    r, f = rel_mse(imgs[0], imgs[1]), frac_close(imgs[0], imgs[1])
+    assert r <= 2e-4 and f >= 0.985, (r, f)
+    assert abs(imgs[0].mean() - imgs[1].mean()) <= 2e-3 * imgs[1].mean()
+
+
 def test_many_lights_statistical_gate(b200pt, tmp_path):
     """Config C4 in miniature (workloads.procedural_scene: displaced meshes from PLY files, 400 emissive triangles
     of 64 radiance levels).  The reference builds its alias table with a full re-sort per step
