@@ -336,6 +336,10 @@ void *b200pt_film_device_ptr(b200pt_film *film); /* float4[W*H] accumulators (fo
 int b200pt_film_dims(b200pt_film *film, int32_t *width, int32_t *height);
 /* rgb_out[W*H*3] = output_rgb_from_sensor_rgb * (xyz_sum / weight_sum) (film/rgb_film.cu:107-122) */
 int b200pt_film_read(b200pt_film *film, float *rgb_out);
+/* The 8-bit image Film::write_to_png encodes (base/film.cu:57-99): rgba_out[W*H*4] = SRGBColorEncoding::from_linear of the
+ * output RGB (the reference's minimax sRGB curve, spectrum_util/color_encoding.h:6-45), alpha 255; converted on the device.
+ * nan_pixels_out (may be NULL): pixels with a NaN component (the reference aborts on them; here they are written as 0). */
+int b200pt_film_read_srgb8(b200pt_film *film, uint8_t *rgba_out, int32_t *nan_pixels_out);
 /* raw accumulators: xyzw_out[W*H*4] */
 int b200pt_film_read_raw(b200pt_film *film, float *xyzw_out);
 

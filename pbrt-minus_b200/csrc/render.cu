@@ -2244,6 +2244,47 @@ __global__ void k_film_resolve(const float4 *accum, long long n, const float *M,
     rgb[3 * i + 2] = M[6] * x + M[7] * y + M[8] * z;
 }
 
+// Film::write_to_png's pixel loop on the device (base/film.cu:57-99): get_pixel_rgb, then SRGBColorEncoding::from_linear
+// (spectrum_util/color_encoding.h:6-45) -- the reference's sRGB curve is the minimax rational approximation, evaluated on the
+// HOST there (each pixel read through managed memory); rgba[4i..] = {r, g, b, 255}; nan_count += pixels with a NaN component
+__device__ __forceinline__ float linear_to_srgb(float v) {
+    if (v <= 0.0031308f) return 12.92f * v;
+    const float s = safe_sqrt(v);
+    float p = -0.016202083165206348f;
+    p = fmaf(s, p, 0.7551545191665577f);
+    p = fmaf(s, p, 2.0041169284241644f);
+    p = fmaf(s, p, 0.7642611304733891f);
+    p = fmaf(s, p, 0.03453868659826638f);
+    p = fmaf(s, p, -0.0016829072605308378f);
+    float q = 1.f;
+    q = fmaf(s, q, 1.8970238036421054f);
+    q = fmaf(s, q, 0.6085338522168684f);
+    q = fmaf(s, q, 0.03467195408529984f);
+    q = fmaf(s, q, -0.00004375359692957097f);
+    q = fmaf(s, q, 4.178892964897981e-7f);
+    return p / q * v;
+}
+__device__ __forceinline__ unsigned char srgb8_from_linear(float v) {
+    if (!(v > 0.f)) return 0; // also NaN (the reference aborts on NaN pixels; here they are counted and written as 0)
+    if (v >= 1.f) return 255;
+    const double r = round(255.0 * (double)linear_to_srgb(v));
+    return (unsigned char)(r < 0.0 ? 0.0 : (r > 255.0 ? 255.0 : r));
+}
+__global__ void k_film_srgb8(const float4 *accum, long long n, const float *M, uchar4 *rgba, unsigned *nan_count) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = accum[i];
+    float x = a.x, y = a.y, z = a.z;
+    if (a.w != 0.f) {
+        x /= a.w;
+        y /= a.w;
+        z /= a.w;
+    }
+    const float r = M[0] * x + M[1] * y + M[2] * z, g = M[3] * x + M[4] * y + M[5] * z, b = M[6] * x + M[7] * y + M[8] * z;
+    if (isnan(r) || isnan(g) || isnan(b)) atomicAdd(nan_count, 1u);
+    rgba[i] = make_uchar4(srgb8_from_linear(r), srgb8_from_linear(g), srgb8_from_linear(b), 255);
+}
+
 __global__ void k_probe_sampler(int kind, int spp, int sqrt_spp, const int32_t *__restrict__ pixel,
                                 const int32_t *__restrict__ sample, int npairs, const int32_t *__restrict__ pattern, int ndraw,
                                 int per, float *__restrict__ out) {
@@ -2288,6 +2329,28 @@ B200PT_API int b200pt_film_read(b200pt_film *film, float *rgb_out) {
     k_film_resolve<<<unsigned((n + 255) / 256), 256, 0, s->stream>>>(film->d_accum, n, d_M, d_rgb);
     CU_TRY(cudaMemcpyAsync(rgb_out, d_rgb, (size_t)n * 12, cudaMemcpyDeviceToHost, s->stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
+    return B200PT_OK;
+}
+
+B200PT_API int b200pt_film_read_srgb8(b200pt_film *film, uint8_t *rgba_out, int32_t *nan_pixels_out) {
+    if (!rgba_out) return B200PT_ERR_INVALID;
+    if (int rc = film_alive(film, "b200pt_film_read_srgb8")) return rc;
+    b200pt_scene *s = film->scene;
+    CU_TRY(cudaSetDevice(s->device));
+    const long long n = (long long)film->width * film->height;
+    int rc = ensure_scratch(s, (size_t)n * 4 + 128);
+    if (rc) return rc;
+    float *d_M = (float *)s->d_scratch;
+    unsigned *d_nan = (unsigned *)(d_M + 12);
+    uchar4 *d_rgba = (uchar4 *)(d_M + 16);
+    unsigned h_nan = 0;
+    CU_TRY(cudaMemcpyAsync(d_M, s->render->out_rgb, 9 * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+    CU_TRY(cudaMemsetAsync(d_nan, 0, sizeof(unsigned), s->stream));
+    k_film_srgb8<<<unsigned((n + 255) / 256), 256, 0, s->stream>>>(film->d_accum, n, d_M, d_rgba, d_nan);
+    CU_TRY(cudaMemcpyAsync(rgba_out, d_rgba, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaMemcpyAsync(&h_nan, d_nan, sizeof(unsigned), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    if (nan_pixels_out) *nan_pixels_out = (int32_t)h_nan;
     return B200PT_OK;
 }
 

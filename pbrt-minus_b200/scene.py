@@ -200,10 +200,21 @@ class Film:
     def reduce(self, nccl_comm, root=0, stream=None):
         _check(self.lib.b200pt_film_reduce(self.handle, nccl_comm, int(root), stream))
 
+    def srgb8(self):
+        """[H, W, 4] uint8: the reference's 8-bit sRGB pixels (Film::write_to_png, base/film.cu:57-99), encoded on the device;
+        also returns the number of NaN pixels"""
+        out = np.empty((self.height, self.width, 4), dtype=np.uint8)
+        nan = C.c_int32(0)
+        _check(self.lib.b200pt_film_read_srgb8(self.handle, out.ctypes.data_as(C.POINTER(C.c_uint8)), C.byref(nan)))
+        return out, nan.value
+
     def write_to_png(self, path):
-        """Film::write_to_png (base/film.cu:57-99): sRGB-encode, clamp, 8 bit."""
+        """Film::write_to_png (base/film.cu:57-99): sRGB-encode on the device, 8 bit; raises on NaN pixels as the reference aborts."""
         from . import png
-        png.write_png(path, srgb8(self.get_pixel_rgb()))
+        rgba, nan = self.srgb8()
+        if nan:
+            raise api.B200ptError(-4, "Film.write_to_png: %d pixels carry NaN components" % nan)
+        png.write_png(path, rgba[..., :3])
 
     def close(self):
         if getattr(self, "handle", None):
