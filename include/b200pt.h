@@ -87,11 +87,14 @@ typedef struct {
     /* spectrum TEXTURES (base/spectrum_texture.cu) for "reflectance" / "transmittance": texture id + 1, 0 = none (the spectrum
      * id above is used).  diffuse, diffusetransmission, coateddiffuse, and conductor / coatedconductor in reflectance mode */
     int32_t reflectance_tex1, transmittance_tex1;
+    /* FLOAT textures (base/float_texture.cu) for "uroughness" / "vroughness" ("roughness" sets both) of conductor and dielectric
+     * materials (materials/conductor_material.cu:35-44, dielectric_material.cu:20-31): texture id + 1, 0 = the constants above */
+    int32_t u_roughness_tex1, v_roughness_tex1;
 } b200pt_material;
 
 /* ---- textures (textures/, base/{spectrum,float}_texture.cu) ---------------------------------------------------------------
  * A texture is a node of a small expression tree over images and constants, evaluated at the hit's (u, v) and normal.
- * "uv" mapping only (textures/texture_mapping_2d.cu:114-124); images are looked up bilinearly with "repeat" wrapping
+ * Image textures find (s, t) through a uv, planar, spherical or cylindrical mapping (textures/texture_mapping_2d.cu); images are looked up bilinearly with "repeat" wrapping
  * (MIPMap::filter = GPUImage::bilerp, textures/mipmap.cu:22-25), flipped in t, scaled, optionally inverted, clamped,
  * and turned into an RGBAlbedoSpectrum per lookup (textures/spectrum_image_texture.cu:17-32). */
 enum { B200PT_TEX_CONSTANT = 0,       /* a: spectrum id */
@@ -102,10 +105,14 @@ enum { B200PT_TEX_CONSTANT = 0,       /* a: spectrum id */
        B200PT_TEX_FLOAT_CONSTANT = 16, /* f[0] */
        B200PT_TEX_FLOAT_IMAGE = 17,    /* a: image id (red channel... see float_image_texture.h); f[0] scale, f[1] invert */
        B200PT_TEX_FLOAT_SCALE = 18 };  /* a, b: float textures, product (textures/float_scaled_texture.cu) */
+enum { B200PT_MAP_UV = 0, B200PT_MAP_PLANAR = 1, B200PT_MAP_SPHERICAL = 2, B200PT_MAP_CYLINDRICAL = 3 };
 typedef struct {
     int32_t type, a, b, c;
     float f[4];
-    float map[4]; /* UVMapping: su, sv, du, dv */
+    float map[4]; /* UVMapping: su, sv, du, dv;  PlanarMapping: -, -, udelta, vdelta (textures/texture_mapping_2d.cu) */
+    int32_t mapping;               /* B200PT_MAP_*: how an image texture finds (s, t) at a hit */
+    float texture_from_render[12]; /* planar / spherical / cylindrical: rows 0..2 of the inverse of the Texture directive's CTM */
+    float v1[3], v2[3];            /* PlanarMapping: s = udelta + p . v1, t = vdelta + p . v2 */
 } b200pt_texture;
 
 typedef struct {

@@ -29,7 +29,8 @@ class Material(C.Structure):
                 ("transmittance", C.c_int32), ("scale", C.c_float),
                 ("thickness", C.c_float), ("g", C.c_float), ("albedo", C.c_int32), ("max_depth", C.c_int32),
                 ("n_samples", C.c_int32), ("c_u_roughness", C.c_float), ("c_v_roughness", C.c_float),
-                ("c_eta", C.c_int32), ("c_k", C.c_int32), ("mix_a", C.c_int32), ("mix_b", C.c_int32), ("reflectance_tex1", C.c_int32), ("transmittance_tex1", C.c_int32)]
+                ("c_eta", C.c_int32), ("c_k", C.c_int32), ("mix_a", C.c_int32), ("mix_b", C.c_int32), ("reflectance_tex1", C.c_int32), ("transmittance_tex1", C.c_int32),
+                ("u_roughness_tex1", C.c_int32), ("v_roughness_tex1", C.c_int32)]
 
 
 class Light(C.Structure):
@@ -68,7 +69,8 @@ class FilmDesc(C.Structure):
 
 
 class Texture(C.Structure):
-    _fields_ = [("type", C.c_int32), ("a", C.c_int32), ("b", C.c_int32), ("c", C.c_int32), ("f", C.c_float * 4), ("map", C.c_float * 4)]
+    _fields_ = [("type", C.c_int32), ("a", C.c_int32), ("b", C.c_int32), ("c", C.c_int32), ("f", C.c_float * 4), ("map", C.c_float * 4),
+                ("mapping", C.c_int32), ("texture_from_render", C.c_float * 12), ("v1", C.c_float * 3), ("v2", C.c_float * 3)]
 
 
 class Image(C.Structure):

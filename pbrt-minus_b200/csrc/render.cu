@@ -347,8 +347,9 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
         const b200pt_material &m = desc->materials[i];
         mats[i] = MatRec{m.type, m.reflectance, m.eta, m.k, m.u_roughness, m.v_roughness, m.remap_roughness, m.transmittance, m.scale,
                          m.thickness, m.g, m.albedo, m.max_depth, m.n_samples, m.c_u_roughness, m.c_v_roughness, m.c_eta, m.c_k, m.mix_a, m.mix_b,
-                         m.reflectance_tex1, m.transmittance_tex1};
-        if (m.reflectance_tex1 < 0 || m.reflectance_tex1 > desc->n_textures || m.transmittance_tex1 < 0 || m.transmittance_tex1 > desc->n_textures) {
+                         m.reflectance_tex1, m.transmittance_tex1, m.u_roughness_tex1, m.v_roughness_tex1};
+        if (m.reflectance_tex1 < 0 || m.reflectance_tex1 > desc->n_textures || m.transmittance_tex1 < 0 || m.transmittance_tex1 > desc->n_textures ||
+            m.u_roughness_tex1 < 0 || m.u_roughness_tex1 > desc->n_textures || m.v_roughness_tex1 < 0 || m.v_roughness_tex1 > desc->n_textures) {
             set_error("b200pt_scene_create: material %d names a texture that does not exist", i);
             return B200PT_ERR_INVALID;
         }
@@ -479,6 +480,13 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             TexRec &o = tex[i];
             o.type = t.type; o.a = t.a; o.b = t.b; o.c = t.c;
             for (int k = 0; k < 4; k++) { o.f[k] = t.f[k]; o.map[k] = t.map[k]; }
+            o.mapping = t.mapping;
+            for (int k = 0; k < 12; k++) o.tfr[k] = t.texture_from_render[k];
+            for (int k = 0; k < 3; k++) { o.v1[k] = t.v1[k]; o.v2[k] = t.v2[k]; }
+            if (t.mapping < B200PT_MAP_UV || t.mapping > B200PT_MAP_CYLINDRICAL) {
+                set_error("b200pt_scene_create: texture %d: unknown mapping %d", i, t.mapping);
+                return B200PT_ERR_INVALID;
+            }
             // children must come BEFORE their parent (the front-end creates them in that order): no cycles, bounded walks
             auto child_ok = [&](int id) { return id >= 0 && id < i; };
             bool ok = true;
@@ -1578,7 +1586,7 @@ __global__ void __launch_bounds__(WF_BLOCK) k_emit(WF wf) {
 // "reflectance" / "transmittance" of a material: a spectrum, or a spectrum texture evaluated at the hit
 // (`ext`: a compile-time constant of the calling kernel -- the plain shade kernels carry no texture code at all)
 __device__ __forceinline__ S4 material_spectrum(const WF &wf, int spectrum, int tex1, const Isect &si, S4 lambda, bool ext) {
-    if (ext && tex1 > 0) return tex_eval(wf.tex, wf.spectra, tex1 - 1, TexCtx{si.u, si.v, si.n}, lambda);
+    if (ext && tex1 > 0) return tex_eval(wf.tex, wf.spectra, tex1 - 1, TexCtx{si.u, si.v, si.n, si.p}, lambda);
     return spectrum_sample(wf.spectra, spectrum, lambda);
 }
 
@@ -1597,6 +1605,8 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_CONDUCTOR>(const WF &wf, co
                                                                 bool &lpdf_dirty, bool ext, BSDF<B200PT_MAT_CONDUCTOR> &b) {
     // materials/conductor_material.cu:52-75
     float ur = m.u_rough, vr = m.v_rough;
+    if (ext && m.u_rough_tex1 > 0) ur = ftex_eval(wf.tex, m.u_rough_tex1 - 1, TexCtx{si.u, si.v, si.n, si.p});
+    if (ext && m.v_rough_tex1 > 0) vr = ftex_eval(wf.tex, m.v_rough_tex1 - 1, TexCtx{si.u, si.v, si.n, si.p});
     if (m.remap) {
         ur = sqrtf(ur);
         vr = sqrtf(vr);
@@ -1625,6 +1635,8 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_DIELECTRIC>(const WF &wf, c
     }
     if (eta == 0.f) eta = 1.f;
     float ur = m.u_rough, vr = m.v_rough;
+    if (ext && m.u_rough_tex1 > 0) ur = ftex_eval(wf.tex, m.u_rough_tex1 - 1, TexCtx{si.u, si.v, si.n, si.p});
+    if (ext && m.v_rough_tex1 > 0) vr = ftex_eval(wf.tex, m.v_rough_tex1 - 1, TexCtx{si.u, si.v, si.n, si.p});
     if (m.remap) {
         ur = sqrtf(ur);
         vr = sqrtf(vr);

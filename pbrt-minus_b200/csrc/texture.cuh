@@ -19,6 +19,9 @@ struct TexRec {
     int32_t type, a, b, c;
     float f[4];
     float map[4];
+    int32_t mapping;
+    float tfr[12];
+    float v1[3], v2[3];
 };
 struct ImageRec {
     int32_t width, height;
@@ -33,6 +36,7 @@ struct TexTables {
 struct TexCtx {
     float u, v;
     V3 n;
+    V3 p; // render-space hit point (planar / spherical / cylindrical mappings)
 };
 
 __device__ __forceinline__ int tex_mod(int a, int b) {
@@ -60,8 +64,29 @@ __device__ __forceinline__ V3 image_bilerp(const ImageRec &im, float s, float t)
 
 // image lookup at the mapped, t-flipped coordinates
 __device__ __forceinline__ V3 image_lookup(const TexTables &T, const TexRec &r, const TexCtx &ctx) {
-    const float s = r.map[0] * ctx.u + r.map[2];
-    float t = r.map[1] * ctx.v + r.map[3];
+    float s, t;
+    if (r.mapping == B200PT_MAP_UV) { // UVMapping::map (textures/texture_mapping_2d.cu:114-124)
+        s = r.map[0] * ctx.u + r.map[2];
+        t = r.map[1] * ctx.v + r.map[3];
+    } else {
+        // textureFromRender(ctx.p): Transform::operator()(Point3f)
+        const float *m = r.tfr;
+        const V3 pt = v3(m[0] * ctx.p.x + m[1] * ctx.p.y + m[2] * ctx.p.z + m[3], m[4] * ctx.p.x + m[5] * ctx.p.y + m[6] * ctx.p.z + m[7],
+                         m[8] * ctx.p.x + m[9] * ctx.p.y + m[10] * ctx.p.z + m[11]);
+        if (r.mapping == B200PT_MAP_PLANAR) { // PlanarMapping::map (:27-42)
+            s = r.map[2] + dot(pt, v3(r.v1[0], r.v1[1], r.v1[2]));
+            t = r.map[3] + dot(pt, v3(r.v2[0], r.v2[1], r.v2[2]));
+        } else if (r.mapping == B200PT_MAP_SPHERICAL) { // SphericalMapping::map (:44-72): theta / pi, phi / 2 pi of the direction
+            const V3 vec = normalize(pt);
+            float phi = atan2f(vec.y, vec.x);
+            if (phi < 0.f) phi += 2.f * kPi;
+            s = acosf(clampf(vec.z, -1.f, 1.f)) * kInvPi;
+            t = phi * (0.5f * kInvPi);
+        } else { // CylindricalMapping::map (:4-25)
+            s = (kPi + atan2f(pt.y, pt.x)) * (0.5f * kInvPi);
+            t = pt.z;
+        }
+    }
     t = (float)(1.0 - (double)t);
     return image_bilerp(T.images[r.a], s, t);
 }

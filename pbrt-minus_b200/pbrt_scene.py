@@ -91,7 +91,8 @@ def params_of(args):
 
 
 def p_float(p, name, default):
-    return float(p[name][1][0]) if name in p else default
+    # a parameter that names a texture ("texture roughness" ["name"]) is picked up by the caller's *_tex1 fields
+    return float(p[name][1][0]) if name in p and p[name][0] != "texture" else default
 
 
 def p_int(p, name, default):
@@ -445,8 +446,10 @@ class Scene:
         raise SceneError("spectrum parameter '%s' of type '%s' not supported" % (name, t))
 
     # ---- textures (SceneBuilder::parse_texture, scene_builder.cu:679-708; {Spectrum,Float}Texture::create)
-    def _tex(self, type_, a=-1, b=-1, c=-1, f=(0, 0, 0, 0), mapping=(1, 1, 0, 0)):
-        self.textures.append({"type": type_, "a": a, "b": b, "c": c, "f": [float(v) for v in f], "map": [float(v) for v in mapping]})
+    def _tex(self, type_, a=-1, b=-1, c=-1, f=(0, 0, 0, 0), mapping=(1, 1, 0, 0), kind=0, tfr=None, v1=(1, 0, 0), v2=(0, 1, 0)):
+        self.textures.append({"type": type_, "a": a, "b": b, "c": c, "f": [float(v) for v in f], "map": [float(v) for v in mapping],
+                              "mapping": int(kind), "tfr": [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0] if tfr is None else [float(v) for v in tfr],
+                              "v1": [float(v) for v in v1], "v2": [float(v) for v in v2]})
         return len(self.textures) - 1
 
     def load_image(self, path):
@@ -489,23 +492,35 @@ class Scene:
             return self._tex(16, f=(float(v[0]), 0, 0, 0))
         return self._tex(16, f=(default, 0, 0, 0))
 
-    def _image_node(self, type_, p, scene_dir):
-        if p_str(p, "mapping", "uv") != "uv":
-            raise SceneError("texture mapping '%s': only \"uv\" is on the hot path" % p_str(p, "mapping", "uv"))
+    def _image_node(self, type_, p, scene_dir, render_from_texture=None):
+        # TextureMapping2D::create (textures/texture_mapping_2d.cu:86-133)
+        mapping = p_str(p, "mapping", "uv")
+        kinds = {"uv": 0, "planar": 1, "spherical": 2, "cylindrical": 3}
+        if mapping not in kinds:
+            raise SceneError("mapping `%s` not implemented (texture_mapping_2d.cu:129-132)" % mapping)
+        extra = {}
+        if mapping != "uv":
+            if render_from_texture is None:
+                raise SceneError("texture mapping '%s' needs the Texture directive's transform" % mapping)
+            extra = {"kind": kinds[mapping], "tfr": render_from_texture.inv[:3, :].reshape(-1)}
+            if mapping == "planar":
+                extra["v1"] = p["v1"][1][:3] if "v1" in p else (1, 0, 0)
+                extra["v2"] = p["v2"][1][:3] if "v2" in p else (0, 1, 0)
         if p_str(p, "wrap", "repeat") != "repeat":
             raise SceneError("texture wrap '%s': the reference implements \"repeat\" only (gpu_image.cu:56-66)" % p_str(p, "wrap", "repeat"))
         if p_str(p, "filter", "bilinear") not in ("ewa", "bilinear", "trilinear", "point"):
             raise SceneError("unknown texture filter")       # every filter is a bilerp in the reference (mipmap.cu:22-25)
         img = self.load_image(os.path.join(scene_dir, p_str(p, "filename", "")))
         return self._tex(type_, a=img, f=(p_float(p, "scale", 1.0), 1.0 if p_bool(p, "invert", False) else 0.0, 0, 0),
-                         mapping=(p_float(p, "uscale", 1.0), p_float(p, "vscale", 1.0), p_float(p, "udelta", 0.0), p_float(p, "vdelta", 0.0)))
+                         mapping=(p_float(p, "uscale", 1.0), p_float(p, "vscale", 1.0), p_float(p, "udelta", 0.0), p_float(p, "vdelta", 0.0)),
+                         **extra)
 
     def add_texture(self, name, color_type, tex_type, p, render_from_texture, scene_dir):
         if color_type == "float":
             if tex_type == "constant":
                 tid = self._tex(16, f=(p_float(p, "value", 1.0), 0, 0, 0))
             elif tex_type == "imagemap":
-                tid = self._image_node(17, p, scene_dir)
+                tid = self._image_node(17, p, scene_dir, render_from_texture)
             elif tex_type == "scale":
                 tid = self._tex(18, a=self.float_texture_param(p, "scale", 1.0), b=self.float_texture_param(p, "tex", 1.0))
             else:
@@ -518,7 +533,7 @@ class Scene:
             v = self.spec_param(p, "value", "albedo", scene_dir)
             tid = self._tex(0, a=self.spec_constant(1.0) if v is None else v)
         elif tex_type == "imagemap":
-            tid = self._image_node(1, p, scene_dir)
+            tid = self._image_node(1, p, scene_dir, render_from_texture)
         elif tex_type == "scale":
             t = self.spectrum_texture_param(p, "tex", scene_dir)
             if t is None:
@@ -536,8 +551,11 @@ class Scene:
             d = (d / F32(np.sqrt(F32(F32(d[0] * d[0]) + F32(d[1] * d[1])) + F32(d[2] * d[2])))).astype(F32)
             tid = self._tex(4, a=t1, b=t2, f=(d[0], d[1], d[2], 0))
         elif tex_type == "checkerboard":
-            raise SceneError("checkerboard texture: its filter width comes from ray differentials the reference never initialises "
-                             "(SURVEY.md a28); not reproduced")
+            # CameraBase::minPosDifferentialX/Y, minDirDifferentialX/Y (cameras/camera_base.h:96-97) are never assigned and
+            # Vector3's default constructor fills NaN (euclidean_space/vector3.h:12), so approximate_dp_dxy hands NaN
+            # differentials to checkerboard(): its weight is NaN and the reference aborts on the NaN pixels it writes
+            raise SceneError("checkerboard texture: in the reference its filter width is NaN (uninitialised camera differentials), "
+                             "every textured pixel is NaN and the render aborts; nothing to reproduce")
         else:
             raise SceneError("spectrum texture '%s' is not a reference texture (base/spectrum_texture.cu:9-58)" % tex_type)
         self.named_spec_tex[name] = tid
@@ -559,6 +577,10 @@ class Scene:
             m = self.materials[-1]
             m["reflectance_tex1"] = self.material_texture(p, "reflectance") if m["type"] in (0, 1, 3, 4, 5) else 0
             m["transmittance_tex1"] = self.material_texture(p, "transmittance") if m["type"] == 3 else 0
+            if m["type"] in (1, 2):   # conductor_material.cu:35-44, dielectric_material.cu:20-31: "uroughness" else "roughness"
+                for fld, key in (("ur_tex1", "uroughness"), ("vr_tex1", "vroughness")):
+                    k = key if key in p else "roughness"
+                    m[fld] = self.float_texture_param(p, k, 0.0) + 1 if k in p and p[k][0] == "texture" else 0
         return len(self.materials) - 1
 
     def _add_material(self, kind, p, scene_dir, named=None):
@@ -884,6 +906,7 @@ class Scene:
             mats[i].c_eta, mats[i].c_k = m.get("c_eta", -1), m.get("c_k", -1)
             mats[i].mix_a, mats[i].mix_b = m.get("mix_a", -1), m.get("mix_b", -1)
             mats[i].reflectance_tex1, mats[i].transmittance_tex1 = m.get("reflectance_tex1", 0), m.get("transmittance_tex1", 0)
+            mats[i].u_roughness_tex1, mats[i].v_roughness_tex1 = m.get("ur_tex1", 0), m.get("vr_tex1", 0)
         d.n_materials, d.materials = len(self.materials), mats
         lights = (api.Light * max(1, len(self.lights)))()
         for i, l in enumerate(self.lights):
@@ -941,6 +964,9 @@ class Scene:
                 tex[i].type, tex[i].a, tex[i].b, tex[i].c = t["type"], t["a"], t["b"], t["c"]
                 tex[i].f[:] = t["f"]
                 tex[i].map[:] = t["map"]
+                tex[i].mapping = t["mapping"]
+                tex[i].texture_from_render[:] = t["tfr"]
+                tex[i].v1[:], tex[i].v2[:] = t["v1"], t["v2"]
             d.n_textures, d.textures = len(self.textures), tex
             keep.append(tex)
         if self.camera is not None:

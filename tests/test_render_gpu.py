@@ -221,6 +221,49 @@ def test_textures_match_reference(b200pt, tmp_path):
     check_against_golden(b200pt, tmp_path, "textures_96x64_1024spp")
 
 
+def test_texture_mappings_and_roughness_textures_match_reference(b200pt, tmp_path):
+    """"string mapping" planar / spherical / cylindrical (textures/texture_mapping_2d.cu:4-72), each in the space of the Texture
+    directive's own CTM, and float textures on "roughness" / "uroughness" / "vroughness" of conductor and dielectric materials
+    (materials/conductor_material.cu:35-44, dielectric_material.cu:20-31)."""
+    check_against_golden(b200pt, tmp_path, "textures2_96x64_64spp")
+    check_against_golden(b200pt, tmp_path, "textures2_96x64_1024spp")
+
+
+def test_device_srgb8_equals_the_reference_encoding(b200pt, tmp_path):
+    """b200pt_film_read_srgb8: Film::write_to_png's pixel loop on the device (base/film.cu:57-99) with the reference's minimax
+    sRGB curve (spectrum_util/color_encoding.h:6-45), against a float64 restatement of that curve on the host"""
+    p = os.path.join(str(tmp_path), "scene.pbrt")
+    open(p, "w").write(scene_text("cornell-box-specular.pbrt", (64, 40)))
+    sc = b200pt.pbrt_scene.load(p, spp=16)
+    integ = b200pt.WavefrontPathIntegrator(sc, device=0)
+    film = integ.create_film()
+    integ.render(film)
+    rgb = film.get_pixel_rgb().astype(np.float32)
+    rgba, nan = film.srgb8()
+    assert nan == 0 and rgba.shape == (40, 64, 4) and (rgba[..., 3] == 255).all()
+
+    def curve(v):
+        v = v.astype(np.float32)
+        s = np.sqrt(np.maximum(v, 0)).astype(np.float32)
+        pc = [-0.0016829072605308378, 0.03453868659826638, 0.7642611304733891, 2.0041169284241644, 0.7551545191665577, -0.016202083165206348]
+        qc = [4.178892964897981e-7, -0.00004375359692957097, 0.03467195408529984, 0.6085338522168684, 1.8970238036421054, 1.0]
+        pv = np.zeros_like(s, dtype=np.float64)
+        qv = np.zeros_like(s, dtype=np.float64)
+        for c in reversed(pc):
+            pv = pv * s + c
+        for c in reversed(qc):
+            qv = qv * s + c
+        hi = pv / qv * v
+        return np.where(v <= 0.0031308, 12.92 * v, hi)
+    want = np.where(rgb <= 0, 0, np.where(rgb >= 1, 255, np.clip(np.round(255.0 * curve(rgb)), 0, 255)))
+    d = np.abs(rgba[..., :3].astype(np.int32) - want.astype(np.int32))
+    assert d.max() <= 1 and (d != 0).mean() < 1e-3       # fp32 vs fp64 evaluation may move a value sitting on a rounding boundary
+    film.write_to_png(os.path.join(str(tmp_path), "out.png"))
+    assert os.path.getsize(os.path.join(str(tmp_path), "out.png")) > 100
+    film.close()
+    integ.close()
+
+
 def test_image_infinite_light_matches_reference(b200pt, tmp_path):
     """LightSource "infinite" with an image (lights/image_infinite_light.cu): equal-area octahedral map under a
     rotated light transform, importance sampling through the reference's Distribution2D (an alias table over the column sums

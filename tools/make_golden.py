@@ -71,6 +71,9 @@ CASES = [
     # emissive spheres (Sphere::sample / Sphere::pdf, shapes/sphere.cu:162-280)
     ("spherelight_96x64_64spp", "spherelight.pbrt", None, 64, None, None),
     ("spherelight_96x64_1024spp", "spherelight.pbrt", None, 1024, None, None),
+    # planar / spherical / cylindrical texture mappings, float textures on conductor / dielectric roughness
+    ("textures2_96x64_64spp", "textures2.pbrt", None, 64, None, None),
+    ("textures2_96x64_1024spp", "textures2.pbrt", None, 1024, None, None),
 ]
 
 
