@@ -118,6 +118,36 @@ def gen_light_debug():
     return path
 
 
+def gen_bridge_scene_builder():
+    """Generated copy of scene/scene_builder.cu whose wavefront branch of SceneBuilder::render calls libb200pt.so through
+    pbrt-minus_b200/bridge/b200pt_bridge.h instead of WavefrontPathIntegrator::render + Film::write_to_png
+    (scene_builder.cu:1036-1043).  The reference has no accessor API for the objects its parser builds, so this ONE translation
+    unit is compiled with the access specifiers opened (every non-pbrt header is included before the macros)."""
+    src = open(os.path.join(REF, "src/pbrt/scene/scene_builder.cu")).read()
+    old = "        wavefront_path_integrator->render(film, preview);\n\n        film->write_to_png(output_filename);\n"
+    assert src.count(old) == 1, "reference scene_builder.cu changed; update the bridge injection"
+    new = "        b200pt_bridge_render(*this); // [b200pt bridge] the wavefront path integrator, through libb200pt.so\n"
+    std = ["algorithm", "atomic", "chrono", "cmath", "condition_variable", "cstring", "filesystem", "fstream", "functional", "iomanip",
+           "iostream", "iterator", "limits", "map", "memory", "mutex", "numbers", "numeric", "optional", "queue", "ranges", "set",
+           "sstream", "stack", "string", "thread", "vector", "stdint.h", "cuda_fp16.h", "cuda/std/variant", "cuda/std/tuple",
+           "cuda/std/optional", "ext/lodepng/lodepng.h", "pbrt/gpu/macro.h", "pbrt/gpu/gpu_memory_allocator.h", "pbrt/util/bit_arithmetic.h"]
+    head = "// GENERATED by oracle/ref_build/build_ref.py from the reference's scene/scene_builder.cu -- do not edit\n"
+    head += "".join("#include <%s>\n" % h for h in std)
+    head += ("// the reference keeps the objects its parser builds behind private members and offers no accessors; this translation\n"
+             "// unit has no kernels, so it is compiled by the host compiler alone with -fno-access-control (see build_ref.py)\n"
+             "#include <cuda_runtime.h>\n#include <math.h>\nusing std::isnan;\nusing std::isinf;\nusing std::isfinite;\nusing std::min;\nusing std::max;\n"
+             "template <typename T> T atomicAdd(T *address, T value) { T old = *address; *address += value; return old; } // device-only in the reference\n"
+             "class SceneBuilder;\nvoid b200pt_bridge_render(const SceneBuilder &sb);\n")
+    tail = ('\n#include "b200pt_bridge.h"\n'
+            "void b200pt_bridge_render(const SceneBuilder &sb) { B200ptBridge::render(sb); }\n")
+    os.makedirs(GEN, exist_ok=True)
+    path = os.path.join(GEN, "scene_builder_b200.cu")
+    text = head + src.replace(old, new) + tail
+    if not os.path.exists(path) or open(path).read() != text:
+        open(path, "w").write(text)
+    return path
+
+
 def build_probe():
     """Host-only probe of the reference's integer paths -> tests/golden/ref_probe.json."""
     os.makedirs(OUT, exist_ok=True)
@@ -182,6 +212,25 @@ def main():
         dbg_o = compile_one((gen_light_debug(), os.path.join(OBJ, "gen_power_light_sampler_debug.o"), []))
         lib_dbg = [o for o in lib if not o.endswith("src_pbrt_light_samplers_power_light_sampler.o")] + [dbg_o]
         run(link + main_o + lib_dbg + tail + ["-o", os.path.join(OUT, "pbrt-minus-ref-debug")])
+    if args.only in ("", "cli", "bridge"):
+        # pbrt-minus-b200: the reference's own front-end (lexer, parser, constructors) driving libb200pt.so through the bridge
+        lib_dir = os.path.join(REPO, "pbrt-minus_b200")
+        if os.path.exists(os.path.join(lib_dir, "libb200pt.so")):
+            extra = ["-I" + os.path.join(REPO, "include"), "-I" + os.path.join(lib_dir, "bridge")]
+            bridge_src = gen_bridge_scene_builder()
+            bridge_o = os.path.join(OBJ, "gen_scene_builder_b200.o")
+            hdr = os.path.join(lib_dir, "bridge", "b200pt_bridge.h")
+            if newer(bridge_src, bridge_o) or newer(hdr, bridge_o) or newer(os.path.join(REPO, "include", "b200pt.h"), bridge_o):
+                # host-only translation unit (no kernels, no __global__): g++ with access checks off, CUDA headers for the
+                # __host__ __device__ annotations and cuda::std::variant; same ABI as the nvcc-compiled objects it links with
+                run([os.environ.get("CXX", "g++"), "-std=c++20", "-O2", "-w", "-fno-access-control", "-fpermissive", "-x", "c++", "-fPIC",
+                     "-I/usr/local/cuda/include", "-I" + os.path.join(HERE, "shims"), "-I" + os.path.join(REF, "src")] + extra +
+                    ["-c", bridge_src, "-o", bridge_o])
+            lib_b = [o for o in lib if not o.endswith("src_pbrt_scene_scene_builder.o")] + [bridge_o]
+            run(link + main_o + lib_b + tail + ["-L" + lib_dir, "-lb200pt", "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/../../pbrt-minus_b200",
+                                                 "-o", os.path.join(OUT, "pbrt-minus-b200")])
+        else:
+            print("pbrt-minus_b200/libb200pt.so not built yet: skipping oracle/_ref/pbrt-minus-b200")
     for h in harness:
         name = os.path.basename(h)[len("harness_"):-2]
         if args.only in ("", name.replace("ref_", "")):

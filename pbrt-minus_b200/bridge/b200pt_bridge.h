@@ -1,0 +1,428 @@
+// b200pt_bridge.h -- the reference-side binding of libb200pt.so (include/b200pt.h).
+//
+// This is the code a pbrt-minus maintainer adds to the reference to switch its wavefront path integrator over to the
+// B200-native core: it is #included at the end of (a generated copy of) scene/scene_builder.cu, and SceneBuilder::render
+// calls B200ptBridge::render(*this) where the reference calls
+//     wavefront_path_integrator->render(film, preview); film->write_to_png(output_filename);
+// (scene/scene_builder.cu:1036-1043).  Everything up to that point is the reference's own, unmodified front-end: its lexer,
+// its parser, its ParameterDictionary, its shape / material / light / camera / filter / film constructors.  The bridge only
+// READS the objects those constructors built (the reference has no accessor API, so the generated copy of scene_builder.cu
+// is compiled with the access specifiers opened), lays them out as a b200pt_scene_desc, and calls the C-ABI:
+//     b200pt_scene_create -> b200pt_bvh_build           (replaces HLBVH::HLBVH,                    scene_builder.cu:912)
+//     b200pt_film_create  -> b200pt_render              (replaces WavefrontPathIntegrator::render,  :1041)
+//     b200pt_film_read_srgb8 / b200pt_film_read          (replaces Film::write_to_png's pixel loop,  base/film.cu:57-99)
+// What it carries over: triangle meshes (with normals / uvs), spheres and disks, diffuse / conductor / dielectric /
+// diffusetransmission materials with constant textures, every reference spectrum class, diffuse area lights on triangles and
+// spheres, the perspective camera, any pixel filter (tabulated through Filter::evaluate), the RGB film.  Anything else
+// (instances, media, image textures, the other light types) is refused with a message naming it: the Python front-end
+// (pbrt-minus_b200/pbrt_scene.py) covers those.
+//
+// Built by oracle/ref_build/build_ref.py into oracle/_ref/pbrt-minus-b200 (it links the reference's objects, so it lives with
+// them); exercised by tests/test_bridge_gpu.py.
+#pragma once
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "b200pt.h"
+
+#include <pbrt/base/camera.h>
+#include <pbrt/base/film.h>
+#include <pbrt/base/filter.h>
+#include <pbrt/base/float_texture.h>
+#include <pbrt/base/light.h>
+#include <pbrt/base/material.h>
+#include <pbrt/base/primitive.h>
+#include <pbrt/base/shape.h>
+#include <pbrt/base/spectrum.h>
+#include <pbrt/base/spectrum_texture.h>
+#include <pbrt/cameras/perspective.h>
+#include <pbrt/integrators/wavefront_path.h>
+#include <pbrt/lights/diffuse_area_light.h>
+#include <pbrt/materials/conductor_material.h>
+#include <pbrt/materials/dielectric_material.h>
+#include <pbrt/materials/diffuse_material.h>
+#include <pbrt/materials/diffuse_transmission_material.h>
+#include <pbrt/primitives/geometric_primitive.h>
+#include <pbrt/primitives/simple_primitive.h>
+#include <pbrt/shapes/disk.h>
+#include <pbrt/shapes/sphere.h>
+#include <pbrt/shapes/triangle.h>
+#include <pbrt/shapes/triangle_mesh.h>
+#include <pbrt/spectra/constant_spectrum.h>
+#include <pbrt/spectra/densely_sampled_spectrum.h>
+#include <pbrt/spectra/piecewise_linear_spectrum.h>
+#include <pbrt/spectra/rgb_albedo_spectrum.h>
+#include <pbrt/spectra/rgb_illuminant_spectrum.h>
+#include <pbrt/spectra/rgb_unbounded_spectrum.h>
+#include <pbrt/spectrum_util/global_spectra.h>
+#include <pbrt/spectrum_util/rgb_color_space.h>
+#include <pbrt/textures/float_constant_texture.h>
+#include <pbrt/textures/spectrum_constant_texture.h>
+#include <ext/lodepng/lodepng.h>
+
+struct B200ptBridge {
+    [[noreturn]] static void refuse(const char *what) {
+        fprintf(stderr, "\nb200pt bridge: %s is not carried over by the C++ bridge (use the Python front-end for it)\n", what);
+        exit(2);
+    }
+    static void check(int rc, const char *call) {
+        if (rc != B200PT_OK) {
+            fprintf(stderr, "\nb200pt bridge: %s failed (%d): %s\n", call, rc, b200pt_last_error());
+            exit(1);
+        }
+    }
+    static void matrix16(const Transform &t, bool inverse, float out[16]) {
+        const auto &m = inverse ? t.inv_m : t.m;
+        for (int r = 0; r < 4; r++)
+            for (int c = 0; c < 4; c++) out[4 * r + c] = (float)m.val[r][c];
+    }
+
+    // ---- spectra: every reference class has a one-to-one b200pt_spectrum type
+    std::vector<b200pt_spectrum> spectra;
+    std::vector<std::vector<float>> spectrum_store; // lambda / value arrays the records point into
+    std::map<const Spectrum *, int> spectrum_ids;
+
+    std::vector<float> dense(const Spectrum *s) {
+        std::vector<float> v(471);
+        for (int l = 360; l <= 830; l++) v[l - 360] = (float)(*s)((Real)l);
+        return v;
+    }
+    int spectrum(const Spectrum *s) {
+        if (!s) refuse("a null spectrum");
+        auto it = spectrum_ids.find(s);
+        if (it != spectrum_ids.end()) return it->second;
+        b200pt_spectrum o = {};
+        switch (s->type) {
+        case Spectrum::Type::constant:
+            o.type = B200PT_SPEC_CONSTANT;
+            o.c[0] = (float)static_cast<const ConstantSpectrum *>(s->ptr)->c;
+            break;
+        case Spectrum::Type::rgb_albedo: {
+            const auto *p = static_cast<const RGBAlbedoSpectrum *>(s->ptr);
+            o.type = B200PT_SPEC_RGB_ALBEDO;
+            o.c[0] = p->rsp.c0; o.c[1] = p->rsp.c1; o.c[2] = p->rsp.c2;
+            break;
+        }
+        case Spectrum::Type::rgb_unbounded: {
+            const auto *p = static_cast<const RGBUnboundedSpectrum *>(s->ptr);
+            o.type = B200PT_SPEC_RGB_UNBOUNDED;
+            o.c[0] = p->rsp.c0; o.c[1] = p->rsp.c1; o.c[2] = p->rsp.c2; o.c[3] = p->scale;
+            break;
+        }
+        case Spectrum::Type::rgb_illuminant: {
+            const auto *p = static_cast<const RGBIlluminantSpectrum *>(s->ptr);
+            o.type = B200PT_SPEC_RGB_ILLUMINANT; // times the colour space's illuminant, which the film description carries
+            o.c[0] = p->rsp.c0; o.c[1] = p->rsp.c1; o.c[2] = p->rsp.c2; o.c[3] = p->scale;
+            break;
+        }
+        case Spectrum::Type::piecewise_linear: {
+            const auto *p = static_cast<const PiecewiseLinearSpectrum *>(s->ptr);
+            o.type = B200PT_SPEC_PIECEWISE;
+            o.n = p->size;
+            spectrum_store.emplace_back(p->lambdas, p->lambdas + p->size);
+            spectrum_store.emplace_back(p->values, p->values + p->size);
+            break;
+        }
+        default: // densely sampled, black body: tabulated at the integer wavelengths the reference's own dense tables use
+            o.type = B200PT_SPEC_DENSE;
+            o.n = 471;
+            spectrum_store.push_back(dense(s));
+        }
+        spectra.push_back(o);
+        spectrum_ids[s] = (int)spectra.size() - 1;
+        return (int)spectra.size() - 1;
+    }
+    // pointers into spectrum_store are taken once the vectors no longer grow
+    void fix_spectrum_pointers() {
+        size_t k = 0;
+        for (auto &o : spectra) {
+            if (o.type == B200PT_SPEC_PIECEWISE) {
+                o.lambda = spectrum_store[k].data();
+                o.value = spectrum_store[k + 1].data();
+                k += 2;
+            } else if (o.type == B200PT_SPEC_DENSE) {
+                o.value = spectrum_store[k].data();
+                k += 1;
+            }
+        }
+    }
+
+    int constant_texture(const SpectrumTexture *t) {
+        if (!t) return -1;
+        if (t->type != SpectrumTexture::Type::constant) refuse("a non-constant spectrum texture");
+        return spectrum(static_cast<const SpectrumConstantTexture *>(t->ptr)->value);
+    }
+    float constant_float(const FloatTexture *t) {
+        if (!t) return 0.f;
+        if (t->type != FloatTexture::Type::constant) refuse("a non-constant float texture");
+        return (float)static_cast<const FloatConstantTexture *>(t->ptr)->value;
+    }
+
+    // ---- materials (base/material.cu:97-131)
+    std::vector<b200pt_material> materials;
+    std::map<const Material *, int> material_ids;
+    int material(const Material *m) {
+        if (!m) refuse("a primitive without a material (medium interface)");
+        auto it = material_ids.find(m);
+        if (it != material_ids.end()) return it->second;
+        b200pt_material o = {};
+        o.reflectance = o.eta = o.k = o.transmittance = o.albedo = o.c_eta = o.c_k = -1;
+        o.remap_roughness = 1;
+        switch (m->type) {
+        case Material::Type::diffuse:
+            o.type = B200PT_MAT_DIFFUSE;
+            o.reflectance = constant_texture(static_cast<const DiffuseMaterial *>(m->ptr)->reflectance);
+            break;
+        case Material::Type::conductor: {
+            const auto *p = static_cast<const ConductorMaterial *>(m->ptr);
+            o.type = B200PT_MAT_CONDUCTOR;
+            if (p->reflectance) o.reflectance = constant_texture(p->reflectance);
+            else {
+                o.eta = constant_texture(p->eta);
+                o.k = constant_texture(p->k);
+            }
+            o.u_roughness = constant_float(p->uRoughness);
+            o.v_roughness = constant_float(p->vRoughness);
+            o.remap_roughness = p->remapRoughness ? 1 : 0;
+            break;
+        }
+        case Material::Type::dielectric: {
+            const auto *p = static_cast<const DielectricMaterial *>(m->ptr);
+            o.type = B200PT_MAT_DIELECTRIC;
+            o.eta = spectrum(p->eta);
+            o.u_roughness = constant_float(p->uRoughness);
+            o.v_roughness = constant_float(p->vRoughness);
+            o.remap_roughness = p->remapRoughness ? 1 : 0;
+            break;
+        }
+        case Material::Type::diffuse_transmission: {
+            const auto *p = static_cast<const DiffuseTransmissionMaterial *>(m->ptr);
+            o.type = B200PT_MAT_DIFFUSE_TRANSMISSION;
+            o.reflectance = constant_texture(p->reflectance);
+            o.transmittance = constant_texture(p->transmittance);
+            o.scale = (float)p->scale;
+            break;
+        }
+        default: refuse("a coated / mix material");
+        }
+        materials.push_back(o);
+        material_ids[m] = (int)materials.size() - 1;
+        return (int)materials.size() - 1;
+    }
+
+    // ---- geometry
+    std::vector<float> P, N, UV;
+    std::vector<int32_t> indices, tri_material, tri_light;
+    std::vector<uint8_t> tri_flip;
+    std::vector<b200pt_sphere> spheres;
+    std::map<const Shape *, int> triangle_of_shape, sphere_of_shape;
+    bool any_n = false, any_uv = false;
+
+    void add_shape(const Shape *shape, const Material *mat) {
+        const int mid = material(mat);
+        if (shape->type == Shape::Type::triangle) {
+            const auto *tri = static_cast<const Triangle *>(shape->ptr);
+            const TriangleMesh *mesh = tri->mesh;
+            const int *v = mesh->vertex_indices + 3 * tri->triangle_idx;
+            triangle_of_shape[shape] = (int)tri_material.size();
+            for (int k = 0; k < 3; k++) { // one private vertex triple per triangle: positions are already in render space
+                indices.push_back((int32_t)(P.size() / 3));
+                const Point3f p = mesh->p[v[k]];
+                P.push_back(p.x); P.push_back(p.y); P.push_back(p.z);
+                if (mesh->n) { N.push_back(mesh->n[v[k]].x); N.push_back(mesh->n[v[k]].y); N.push_back(mesh->n[v[k]].z); }
+                else { N.push_back(0); N.push_back(0); N.push_back(0); }
+                if (mesh->uv) { UV.push_back(mesh->uv[v[k]].x); UV.push_back(mesh->uv[v[k]].y); }
+                else { UV.push_back(0); UV.push_back(0); }
+            }
+            any_n |= mesh->n != nullptr;
+            any_uv |= mesh->uv != nullptr;
+            tri_material.push_back(mid);
+            tri_light.push_back(-1);
+            tri_flip.push_back((uint8_t)(((mesh->reverse_orientation ^ mesh->transform_swaps_handedness) ? 1 : 0) | (mesh->n ? 2 : 0) |
+                                         (mesh->uv ? 4 : 0)));
+            return;
+        }
+        b200pt_sphere s = {};
+        s.material = mid;
+        s.light = -1;
+        if (shape->type == Shape::Type::sphere) {
+            const auto *q = static_cast<const Sphere *>(shape->ptr);
+            matrix16(q->render_from_object, false, s.render_from_object);
+            matrix16(q->object_from_render, false, s.object_from_render);
+            s.radius = (float)q->radius; s.z_min = (float)q->z_min; s.z_max = (float)q->z_max; s.phi_max = (float)q->phi_max;
+            s.reverse_orientation = q->reverse_orientation;
+            s.transform_swaps_handedness = q->transform_swaps_handedness;
+            s.kind = 0;
+        } else {
+            const auto *q = static_cast<const Disk *>(shape->ptr);
+            matrix16(q->render_from_object, false, s.render_from_object);
+            matrix16(q->object_from_render, false, s.object_from_render);
+            s.radius = (float)q->radius; s.z_min = (float)q->height; s.z_max = (float)q->inner_radius; s.phi_max = (float)q->phi_max;
+            s.reverse_orientation = q->reverse_orientation;
+            s.transform_swaps_handedness = q->transform_swaps_handedness;
+            s.kind = 1;
+        }
+        sphere_of_shape[shape] = (int)spheres.size();
+        spheres.push_back(s);
+    }
+
+    static void render(const SceneBuilder &sb);
+};
+
+// ---- SceneBuilder::render's wavefront branch, through the C-ABI -----------------------------------------------------------
+inline void B200ptBridge::render(const SceneBuilder &sb) {
+    B200ptBridge b;
+    // lights first: the light-sampler index of a light is its position in gpu_lights (scene_builder.cu:914-935)
+    std::map<const Light *, int> light_ids;
+    for (size_t i = 0; i < sb.gpu_lights.size(); i++) light_ids[sb.gpu_lights[i]] = (int)i;
+    std::vector<b200pt_light> lights(sb.gpu_lights.size());
+
+    // primitives, in the order the parser created them (= the reference's primitive indices)
+    for (const Primitive *prim : sb.gpu_primitives) {
+        const Shape *shape = nullptr;
+        const Material *mat = nullptr;
+        const Light *area = nullptr;
+        if (prim->type == Primitive::Type::simple) {
+            const auto *sp = static_cast<const SimplePrimitive *>(prim->ptr);
+            shape = sp->shape;
+            mat = sp->material;
+        } else if (prim->type == Primitive::Type::geometric) {
+            const auto *gp = static_cast<const GeometricPrimitive *>(prim->ptr);
+            shape = gp->shape_ptr;
+            mat = gp->material;
+            area = gp->area_light;
+            if (gp->medium_interface) refuse("a MediumInterface");
+        } else {
+            refuse("an ObjectInstance");
+        }
+        b.add_shape(shape, mat);
+        if (area) {
+            const int li = light_ids.at(area);
+            if (area->type != Light::Type::diffuse_area_light) refuse("an area light that is not a DiffuseAreaLight");
+            const auto *dal = static_cast<const DiffuseAreaLight *>(area->ptr);
+            b200pt_light L = {};
+            L.spectrum = b.spectrum(dal->Lemit);
+            L.scale = (float)dal->scale; // already divided by the photometric integral (lights/diffuse_area_light.cu:17-26)
+            L.two_sided = dal->two_sided ? 1 : 0;
+            if (shape->type == Shape::Type::triangle) {
+                L.type = B200PT_LIGHT_AREA;
+                L.triangle = b.triangle_of_shape.at(shape);
+                b.tri_light[L.triangle] = li;
+            } else if (shape->type == Shape::Type::sphere) {
+                L.type = B200PT_LIGHT_SPHERE_AREA;
+                L.triangle = b.sphere_of_shape.at(shape);
+                b.spheres[L.triangle].light = li;
+            } else {
+                refuse("an emissive disk");
+            }
+            lights[li] = L;
+        }
+    }
+    for (size_t i = 0; i < sb.gpu_lights.size(); i++)
+        if (sb.gpu_lights[i]->type != Light::Type::diffuse_area_light) refuse("a LightSource (distant / infinite / spot)");
+
+    // camera (cameras/perspective.cu:7-63), pixel filter tabulated as FilterSampler's constructor does (filters/filter_sampler.cu:4-20)
+    b200pt_camera cam = {};
+    cam.medium = -1;
+    cuda::std::visit(
+        [&](auto &x) {
+            matrix16(x.camera_from_raster, false, cam.camera_from_raster);
+            matrix16(x.camera_base.camera_transform.render_from_camera, false, cam.render_from_camera);
+            cam.lens_radius = (float)x.lens_radius;
+            cam.focal_distance = (float)x.focal_distance;
+        },
+        *sb.integrator_base->camera);
+    const Filter &filter = *sb.integrator_base->filter;
+    const auto radius = filter.get_radius();
+    const Bounds2f domain(Point2f(-radius), Point2f(radius));
+    const int nx = static_cast<int>(32 * radius.x), ny = static_cast<int>(32 * radius.y);
+    std::vector<float> ftab((size_t)nx * ny);
+    for (int y = 0; y < ny; ++y)
+        for (int x = 0; x < nx; ++x) ftab[(size_t)y * nx + x] = (float)filter.evaluate(domain.lerp(Point2f((x + 0.5f) / nx, (y + 0.5f) / ny)));
+    b200pt_filter flt = {(float)radius.x, (float)radius.y, nx, ny, ftab.data()};
+
+    // film / sensor (film/rgb_film.cu:27-47): CIE XYZ sensor, imaging ratio 1, output = the colour space's rgb_from_xyz
+    const auto res = sb.film->get_resolution();
+    const GlobalSpectra *gs = sb.global_spectra;
+    const std::vector<float> cie_x = b.dense(gs->cie_xyz[0]), cie_y = b.dense(gs->cie_xyz[1]), cie_z = b.dense(gs->cie_xyz[2]);
+    const std::vector<float> illum = b.dense(gs->rgb_color_space->illuminant);
+    b200pt_film_desc fd = {};
+    fd.width = res.x;
+    fd.height = res.y;
+    fd.cie_x = cie_x.data();
+    fd.cie_y = cie_y.data();
+    fd.cie_z = cie_z.data();
+    fd.illuminant = illum.data();
+    fd.imaging_ratio = 1.f;
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) fd.output_rgb_from_sensor_rgb[3 * r + c] = (float)gs->rgb_color_space->rgb_from_xyz.val[r][c];
+
+    b.fix_spectrum_pointers();
+    b200pt_scene_desc d = {};
+    d.n_vertices = (int64_t)(b.P.size() / 3);
+    d.P = b.P.data();
+    d.N = b.any_n ? b.N.data() : nullptr;
+    d.uv = b.any_uv ? b.UV.data() : nullptr;
+    d.n_triangles = (int64_t)b.tri_material.size();
+    d.indices = b.indices.data();
+    d.tri_material = b.tri_material.data();
+    d.tri_light = b.tri_light.data();
+    d.tri_flip = b.tri_flip.data();
+    d.n_spheres = (int32_t)b.spheres.size();
+    d.spheres = b.spheres.data();
+    d.n_spectra = (int32_t)b.spectra.size();
+    d.spectra = b.spectra.data();
+    d.n_materials = (int32_t)b.materials.size();
+    d.materials = b.materials.data();
+    d.n_lights = (int32_t)lights.size();
+    d.lights = lights.data();
+    d.camera = &cam;
+    d.filter = &flt;
+    d.film = &fd;
+
+    b200pt_scene *scene = nullptr;
+    b200pt_film *film = nullptr;
+    check(b200pt_scene_create(&d, 0, &scene), "b200pt_scene_create");
+    b200pt_build_stats bs = {};
+    check(b200pt_bvh_build(scene, &bs), "b200pt_bvh_build");
+    printf("b200pt BVH building: %lld primitives, %.3f ms on the device (%lld BVH8 nodes)\n", (long long)bs.n_triangles, bs.ms_total,
+           (long long)bs.n_bvh8_nodes);
+    check(b200pt_film_create(scene, &film), "b200pt_film_create");
+    b200pt_render_opts o = {};
+    o.spp_total = sb.samples_per_pixel.value();
+    o.sample_begin = 0;
+    o.sample_end = o.spp_total;
+    o.max_depth = sb.wavefront_path_integrator->max_depth;
+    o.regularize = sb.wavefront_path_integrator->regularize ? 1 : 0;
+    o.sampler = sb.sampler_type == "independent" ? 1 : 0;
+    b200pt_render_stats st = {};
+    check(b200pt_render(scene, film, &o, &st), "b200pt_render");
+    printf("b200pt wavefront pathtracing: %.3f ms on the device, %lld paths, %lld + %lld rays, %lld passes\n", st.ms_total,
+           (long long)st.paths, (long long)st.rays_closest, (long long)st.rays_shadow, (long long)st.passes);
+
+    // Film::write_to_png (base/film.cu:57-99) + the float film next to it (as oracle/_ref/pbrt-minus-ref writes it)
+    std::vector<unsigned char> rgba((size_t)res.x * res.y * 4);
+    int32_t nan_pixels = 0;
+    check(b200pt_film_read_srgb8(film, rgba.data(), &nan_pixels), "b200pt_film_read_srgb8");
+    if (nan_pixels > 0) {
+        fprintf(stderr, "b200pt bridge: %d pixels carry NAN components\n", nan_pixels);
+        exit(1);
+    }
+    if (unsigned error = lodepng::encode(sb.output_filename, rgba, res.x, res.y); error) {
+        fprintf(stderr, "lodepng::encoder error %u: %s\n", error, lodepng_error_text(error));
+        exit(1);
+    }
+    std::vector<float> rgb((size_t)res.x * res.y * 3);
+    check(b200pt_film_read(film, rgb.data()), "b200pt_film_read");
+    if (FILE *fp = fopen((sb.output_filename + ".f32").c_str(), "wb")) {
+        fwrite(rgb.data(), sizeof(float), rgb.size(), fp);
+        fclose(fp);
+    }
+    b200pt_film_destroy(film);
+    b200pt_scene_destroy(scene);
+}
