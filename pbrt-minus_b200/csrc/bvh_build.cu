@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "sort.cuh"
@@ -176,10 +177,31 @@ __global__ void __launch_bounds__(256) k_morton(const float *__restrict__ P, con
     }
 }
 
-__global__ void __launch_bounds__(256) k_unpack_prims(const uint64_t *__restrict__ keys, int64_t n, uint32_t mask,
-                                                      uint32_t *__restrict__ prims) {
-    const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (t < n) prims[t] = uint32_t(keys[t]) & mask;
+// The ONE random gather of the build: sorted position k -> primitive -> index triple -> vertices and per-triangle ids, written
+// as the 48-byte leaf record {v0 | prim, v1 | material word, v2 | light} in SORTED order.  The refit reads its leaf boxes from
+// these records and the collapse copies them into BVH8 leaf order, both as contiguous runs.
+//   v1.w = material id | degenerate << 28 | has-normals << 29 | has-uv << 30 | flip << 31 (b200pt.h: tri_flip bits 1, 2, 0)
+struct GatherArgs {
+    const float *P;
+    const int32_t *idx;
+    const int32_t *tri_material, *tri_light;
+    const uint8_t *tri_flip;
+    int32_t prim_offset; // global id of the range's first triangle
+};
+__global__ void __launch_bounds__(256) k_gather_sorted(const uint64_t *__restrict__ keys, int64_t n, uint32_t mask, GatherArgs g,
+                                                       uint32_t *__restrict__ prims, float4 *__restrict__ rec) {
+    const int64_t k = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (k >= n) return;
+    const uint32_t prim = uint32_t(keys[k]) & mask;
+    prims[k] = prim;
+    const TriVerts tv = load_tri(g.P, g.idx, prim);
+    const uint32_t flip = g.tri_flip ? uint32_t(g.tri_flip[prim]) : 0u;
+    const uint32_t mat = (g.tri_material ? (uint32_t)g.tri_material[prim] : 0u) | ((flip & 1u) << 31) | ((flip & 6u) << 28) |
+                         (triangle_is_degenerate(tv.a.x, tv.a.y, tv.a.z, tv.b.x, tv.b.y, tv.b.z, tv.c.x, tv.c.y, tv.c.z) ? kTriDegenerate : 0u);
+    const int light = g.tri_light ? g.tri_light[prim] : -1;
+    rec[3 * k] = make_float4(tv.a.x, tv.a.y, tv.a.z, __int_as_float((int)prim + g.prim_offset));
+    rec[3 * k + 1] = make_float4(tv.b.x, tv.b.y, tv.b.z, __uint_as_float(mat));
+    rec[3 * k + 2] = make_float4(tv.c.x, tv.c.y, tv.c.z, __int_as_float(light));
 }
 
 // ------------------------------------------------------------------------ BVH2 (build only)
@@ -191,6 +213,8 @@ __global__ void __launch_bounds__(256) k_unpack_prims(const uint64_t *__restrict
 // gamma = split position of the radix tree: the children are gamma / gamma + 1, as interior ids or as leaves n - 1 + gamma (+ 1).
 struct Bvh2 {
     float4 *rec;
+    uint32_t *nodeA, *nodeB; // the A / B words as the emission writes them (coalesced); the refit composes the records
+    int32_t *last;           // interior: last sorted position covered
     int32_t *parent;
     uint32_t *arrive;
     int32_t n; // leaves
@@ -234,32 +258,27 @@ __global__ void __launch_bounds__(256) k_emit_hierarchy(const uint64_t *__restri
     const int right = (last == gamma + 1) ? (n - 1 + gamma + 1) : (gamma + 1);
     const uint32_t A = uint32_t(gamma) | (first == gamma ? 0x40000000u : 0u) | (last == gamma + 1 ? 0x80000000u : 0u);
     const uint32_t B = uint32_t(first) | (uint32_t(min(last - first + 1, 4) - 1) << 30);
-    t.rec[2 * i].w = __uint_as_float(A);
-    t.rec[2 * i + 1].w = __uint_as_float(B);
+    t.nodeA[i] = A;
+    t.nodeB[i] = B;
+    t.last[i] = last;
     t.parent[left] = i;
     t.parent[right] = i;
     if (i == 0) t.parent[0] = -1;
 }
 
-// Bottom-up boxes.  One thread per leaf; at every interior node the first child to arrive stops, the second carries on -- with
-// its own box still in registers, so a node costs ONE sector read (the sibling's record) besides its own record.
-__global__ void __launch_bounds__(256) k_refit(const float *__restrict__ P, const int32_t *__restrict__ idx,
-                                               const uint32_t *__restrict__ sorted_prim, Bvh2 t) {
-    const int n = t.n;
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    const TriVerts tv = load_tri(P, idx, sorted_prim[k]);
-    float3 lo, hi;
-    tri_bounds(tv, lo, hi);
-    int me = n - 1 + k;
-    t.rec[2 * me] = make_float4(lo.x, lo.y, lo.z, __int_as_float(-1));
-    t.rec[2 * me + 1] = make_float4(hi.x, hi.y, hi.z, __uint_as_float(uint32_t(k)));
-    int cur = (n > 1) ? t.parent[me] : -1;
+// Bottom-up boxes.  A warp owns 32 consecutive sorted leaves and the 32 interior nodes of the same indices (interior node i
+// covers a range that starts or ends at leaf i).  Every interior node whose range lies INSIDE the warp's 32 leaves is a union
+// of a contiguous run of the warp's own leaf boxes: the warp builds a 6-level sparse table of those boxes with shuffles and
+// each lane answers its node's range query with two table entries -- no atomics, no fences, no memory round trips for the
+// bottom ~5 levels of the tree, which hold 15/16 of all nodes.  Only the roots of those in-warp subtrees (a handful per warp)
+// climb on through the arrival counters: the first child to arrive stops, the second carries on with its box in registers.
+__device__ __forceinline__ void refit_climb(const Bvh2 &t, int n, int me, float3 lo, float3 hi) {
+    int cur = t.parent[me];
     while (cur >= 0) {
         __threadfence();
         if (atomicAdd(&t.arrive[cur], 1u) == 0u) return; // first arrival: the sibling finishes the job
         __threadfence();
-        const uint32_t A = __float_as_uint(__ldcg(&t.rec[2 * cur].w)), B = __float_as_uint(__ldcg(&t.rec[2 * cur + 1].w));
+        const uint32_t A = t.nodeA[cur], B = t.nodeB[cur];
         const int l = bvh2_left(A, n), r = bvh2_right(A, n);
         const int sib = (l == me) ? r : l;
         const float4 slo = __ldcg(&t.rec[2 * sib]), shi = __ldcg(&t.rec[2 * sib + 1]);
@@ -272,16 +291,142 @@ __global__ void __launch_bounds__(256) k_refit(const float *__restrict__ P, cons
     }
 }
 
+constexpr int REFIT_BLOCK = 512; // leaves (and interior nodes) per CTA (two 24-byte tables of that many entries fit in 48 KB)
+struct Box6 {
+    float lx, ly, lz, hx, hy, hz;
+};
+__device__ __forceinline__ Box6 box_union(const Box6 &a, const Box6 &b) {
+    return Box6{fminf(a.lx, b.lx), fminf(a.ly, b.ly), fminf(a.lz, b.lz), fmaxf(a.hx, b.hx), fmaxf(a.hy, b.hy), fmaxf(a.hz, b.hz)};
+}
+__device__ __forceinline__ Box6 box_shfl(const Box6 &a, int src) {
+    return Box6{__shfl_sync(0xffffffffu, a.lx, src), __shfl_sync(0xffffffffu, a.ly, src), __shfl_sync(0xffffffffu, a.lz, src),
+                __shfl_sync(0xffffffffu, a.hx, src), __shfl_sync(0xffffffffu, a.hy, src), __shfl_sync(0xffffffffu, a.hz, src)};
+}
+
+// A CTA owns 512 consecutive sorted leaves and the interior nodes of the same indices.  The box of ANY interior node whose range
+// lies inside those 512 leaves is the union of three pieces, each a table lookup:
+//   the tail of the first warp's leaves (suffix unions), whole warps in between (a sparse table over the 16 warp boxes),
+//   the head of the last warp's leaves (prefix unions);  a range inside one warp uses that warp's own sparse table (registers).
+// That covers the bottom ~9 levels of the tree -- all but a few nodes in a thousand -- with shuffles and shared memory.
+// Only the roots of those in-CTA subtrees climb on through the arrival counters (k_refit_climb).
+__global__ void __launch_bounds__(REFIT_BLOCK) k_refit(const float4 *__restrict__ tri_sorted, Bvh2 t, int32_t *__restrict__ roots,
+                                                       unsigned *__restrict__ n_roots) {
+    __shared__ Box6 s_suffix[REFIT_BLOCK]; // [warp * 32 + j] = union of that warp's leaves j..31
+    __shared__ Box6 s_prefix[REFIT_BLOCK]; //                  = union of that warp's leaves 0..j
+    __shared__ Box6 s_warp[6][32];         // sparse table over the 32 whole-warp boxes: [k][w] = warps w .. w + 2^k - 1
+    const int n = t.n;
+    const int g = blockIdx.x * REFIT_BLOCK + threadIdx.x; // leaf g and interior node g
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cta_base = blockIdx.x * REFIT_BLOCK, base = g - lane;
+    const bool have_leaf = g < n;
+    Box6 leaf = {kInf, kInf, kInf, -kInf, -kInf, -kInf};
+    if (have_leaf) {
+        const float4 r0 = tri_sorted[3 * (size_t)g], r1 = tri_sorted[3 * (size_t)g + 1], r2 = tri_sorted[3 * (size_t)g + 2];
+        TriVerts tv;
+        tv.a = make_float3(r0.x, r0.y, r0.z);
+        tv.b = make_float3(r1.x, r1.y, r1.z);
+        tv.c = make_float3(r2.x, r2.y, r2.z);
+        float3 lo, hi;
+        tri_bounds(tv, lo, hi);
+        leaf = Box6{lo.x, lo.y, lo.z, hi.x, hi.y, hi.z};
+        const int id = n - 1 + g;
+        t.rec[2 * id] = make_float4(lo.x, lo.y, lo.z, __int_as_float(-1));
+        t.rec[2 * id + 1] = make_float4(hi.x, hi.y, hi.z, __uint_as_float(uint32_t(g)));
+    }
+    // interior node g and its range
+    const bool have_node = g < n - 1;
+    uint32_t A = 0, B = 0;
+    int first = 0, last = 0;
+    if (have_node) {
+        A = t.nodeA[g];
+        B = t.nodeB[g];
+        first = int(B & 0x3fffffffu);
+        last = t.last[g];
+    }
+    const bool in_warp = have_node && first >= base && last <= base + 31;
+    const bool in_cta = have_node && first >= cta_base && last <= cta_base + REFIT_BLOCK - 1;
+    // ---- per-warp: sparse table in registers (answers in-warp ranges), prefix / suffix unions to shared memory
+    Box6 node = {kInf, kInf, kInf, -kInf, -kInf, -kInf};
+    {
+        const int len = last - first + 1;
+        const int klevel = in_warp ? 31 - __clz(len) : -1;
+        const int qa = first - base, qb = last - base - (in_warp ? (1 << klevel) : 0) + 1;
+        Box6 tab = leaf;
+#pragma unroll
+        for (int k = 0; k < 6; k++) { // a range of exactly 32 leaves sits at level 5
+            const Box6 qa_box = box_shfl(tab, klevel == k ? qa : lane), qb_box = box_shfl(tab, klevel == k ? qb : lane);
+            if (klevel == k) node = box_union(qa_box, qb_box);
+            if (k == 5) break;
+            const int step = 1 << k;
+            const Box6 up = box_shfl(tab, (lane + step) & 31);
+            if (lane + step < 32) tab = box_union(tab, up);
+        }
+        // inclusive prefix and suffix unions of the warp's 32 leaf boxes
+        Box6 pre = leaf, suf = leaf;
+#pragma unroll
+        for (int step = 1; step < 32; step <<= 1) {
+            const Box6 a = box_shfl(pre, (lane - step) & 31), b = box_shfl(suf, (lane + step) & 31);
+            if (lane >= step) pre = box_union(pre, a);
+            if (lane + step < 32) suf = box_union(suf, b);
+        }
+        s_prefix[threadIdx.x] = pre;
+        s_suffix[threadIdx.x] = suf;
+        if (lane == 0) s_warp[0][warp] = suf; // suffix from lane 0 = the whole warp
+    }
+    __syncthreads();
+    if (warp == 0) { // sparse table over the warp boxes
+        Box6 tab = lane < REFIT_BLOCK / 32 ? s_warp[0][lane] : Box6{kInf, kInf, kInf, -kInf, -kInf, -kInf};
+#pragma unroll
+        for (int k = 1; k < 6; k++) {
+            const int step = 1 << (k - 1);
+            const Box6 up = box_shfl(tab, (lane + step) & 31);
+            if (lane + step < 32) tab = box_union(tab, up);
+            s_warp[k][lane] = tab;
+        }
+    }
+    __syncthreads();
+    if (in_cta && !in_warp) { // spans warps: tail of the first warp, whole warps in between, head of the last warp
+        const int fa = first - cta_base, la = last - cta_base;
+        const int wf = fa >> 5, wl = la >> 5;
+        node = box_union(s_suffix[fa], s_prefix[la]);
+        if (wl - wf >= 2) {
+            const int w0 = wf + 1, cnt = wl - wf - 1;
+            const int k = 31 - __clz(cnt);
+            node = box_union(node, box_union(s_warp[k][w0], s_warp[k][w0 + cnt - (1 << k)]));
+        }
+    }
+    if (in_cta) {
+        t.rec[2 * g] = make_float4(node.lx, node.ly, node.lz, __uint_as_float(A));
+        t.rec[2 * g + 1] = make_float4(node.hx, node.hy, node.hz, __uint_as_float(B));
+    }
+    if (n <= 1) return;
+    // roots of the in-CTA subtrees climb on: an element whose parent's range leaves the CTA's 512 leaves
+    auto parent_inside = [&](int me) {
+        const int p = t.parent[me];
+        if (p < 0) return false;
+        const int pf = int(t.nodeB[p] & 0x3fffffffu), pl = t.last[p];
+        return pf >= cta_base && pl <= cta_base + REFIT_BLOCK - 1;
+    };
+    // (they are handed to k_refit_climb through a list: a CTA that waited for its few climbers would hold its 512 thread slots
+    // for the length of a dependent chain of atomics, and the kernel would run at a fifth of its occupancy)
+    if (have_leaf && !parent_inside(n - 1 + g)) roots[atomicAdd(n_roots, 1u)] = n - 1 + g;
+    if (in_cta && !parent_inside(g)) roots[atomicAdd(n_roots, 1u)] = g;
+}
+
+// the upper part of the tree: one thread per in-CTA subtree root, arrival counters up to the root
+__global__ void __launch_bounds__(128) k_refit_climb(Bvh2 t, const int32_t *__restrict__ roots, const unsigned *__restrict__ n_roots) {
+    const unsigned count = *n_roots;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const int me = roots[i];
+        const float4 lo = t.rec[2 * me], hi = t.rec[2 * me + 1];
+        refit_climb(t, t.n, me, make_float3(lo.x, lo.y, lo.z), make_float3(hi.x, hi.y, hi.z));
+    }
+}
+
 // ------------------------------------------------------------------- BVH8 work-queue collapse
 struct CollapseArgs {
     Bvh2 t;
-    const float *P;
-    const int32_t *idx;
-    const uint32_t *sorted_prim;
-    const int32_t *tri_material; // optional per-triangle ids, carried in the w lanes of the leaf record
-    const int32_t *tri_light;
-    const uint8_t *tri_flip;
-    int32_t prim_offset; // global id of the range's first triangle (the per-triangle arrays above are offset the same way)
+    const float4 *tri_sorted; // leaf records in sorted order (k_gather_sorted)
     float4 *nodes; // BVH8 out
     float4 *tris;  // re-laid-out triangles out
     const int2 *q_in; // (bvh2 node, bvh8 node index)
@@ -293,6 +438,9 @@ struct CollapseArgs {
     int parity;
     unsigned int node_capacity;
 };
+
+// 2^e as a double, e in the normal range (here [-127, 127])
+__device__ __forceinline__ double pow2_double(int e) { return __longlong_as_double((long long)(e + 1023) << 52); }
 
 __device__ __forceinline__ float half_area(const float4 &lo, const float4 &hi) {
     const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
@@ -362,39 +510,47 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
 
     // octant-ordered slots: slot s prefers the child farthest along (+-x, +-y, +-z) by the bits
     // of s (4 = +x, 2 = +y, 1 = +z); traversal visits slots in (slot ^ octant) order, so near
-    // children of any ray octant come first.  Greedy assignment on the 8x8 cost table.
+    // children of any ray octant come first.  The best score a child can get is the L1 norm of its offset from
+    // the node centre (in its own octant's slot): children are taken in the order of that norm, largest first,
+    // and each gets the best slot still free -- 64 score evaluations per node instead of the 512 of a greedy
+    // search over all (child, slot) pairs, with the same outcome whenever the octants do not collide.
     int slot_of[8];
     {
         const float pcx = 0.5f * (nlo[0] + nhi[0]), pcy = 0.5f * (nlo[1] + nhi[1]), pcz = 0.5f * (nlo[2] + nhi[2]);
-        float ccx[8], ccy[8], ccz[8];
+        float ccx[8], ccy[8], ccz[8], norm[8];
         for (int i = 0; i < cnt; i++) {
             ccx[i] = 0.5f * (clo[i][0] + chi[i][0]) - pcx;
             ccy[i] = 0.5f * (clo[i][1] + chi[i][1]) - pcy;
             ccz[i] = 0.5f * (clo[i][2] + chi[i][2]) - pcz;
+            const float l1 = fabsf(ccx[i]) + fabsf(ccy[i]) + fabsf(ccz[i]);
+            norm[i] = (l1 == l1) ? l1 : -1.f; // non-finite centroids go last
             slot_of[i] = -1;
         }
-        unsigned used_slots = 0;
+        unsigned used_slots = 0, done = 0;
         for (int round = 0; round < cnt; round++) {
+            int bi = 0;
+            float bn = -kInf;
+            for (int i = 0; i < cnt; i++)
+                if (!(done & (1u << i)) && norm[i] > bn) {
+                    bn = norm[i];
+                    bi = i;
+                }
+            if (bn == -kInf) // every remaining norm is NaN-like: first child left
+                for (int i = cnt - 1; i >= 0; i--)
+                    if (!(done & (1u << i))) bi = i;
+            done |= 1u << bi;
+            const float ax = ccx[bi], ay = ccy[bi], az = ccz[bi];
             float best = -kInf;
-            int bi = -1, bs = -1;
-            for (int i = 0; i < cnt; i++) {
-                if (slot_of[i] >= 0) continue;
-                for (int s = 0; s < 8; s++) {
-                    if (used_slots & (1u << s)) continue;
-                    const float cost = ((s & 4) ? ccx[i] : -ccx[i]) + ((s & 2) ? ccy[i] : -ccy[i]) + ((s & 1) ? ccz[i] : -ccz[i]);
-                    if (cost > best) {
-                        best = cost;
-                        bi = i;
-                        bs = s;
-                    }
+            int bs = -1;
+#pragma unroll
+            for (int sl = 0; sl < 8; sl++) {
+                const float cost = ((sl & 4) ? ax : -ax) + ((sl & 2) ? ay : -ay) + ((sl & 1) ? az : -az);
+                if (!(used_slots & (1u << sl)) && cost > best) {
+                    best = cost;
+                    bs = sl;
                 }
             }
-            if (bi < 0) { // non-finite centroids: first free child / slot
-                for (int i = cnt - 1; i >= 0; i--)
-                    if (slot_of[i] < 0) bi = i;
-                for (int s2 = 7; s2 >= 0; s2--)
-                    if (!(used_slots & (1u << s2))) bs = s2;
-            }
+            if (bs < 0) bs = __ffs(~used_slots & 0xffu) - 1; // non-finite scores: first free slot
             slot_of[bi] = bs;
             used_slots |= 1u << bs;
         }
@@ -434,13 +590,16 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
         const double ext = (double)nhi[k] - (double)nlo[k];
         int ek = -100;
         if (ext > 0) {
-            ek = (int)ceil(log2(ext / 255.0));
-            while (ldexp(255.0, ek) < ext) ek++;
+            // smallest ek with 255 * 2^ek >= ext: ceil(log2(ext / 255)) from the binary exponent (frexp: x = m 2^k, m in [0.5, 1))
+            int kx;
+            const double m = frexp(ext / 255.0, &kx);
+            ek = (m == 0.5) ? kx - 1 : kx;
             ek = max(-100, min(127, ek));
+            while (ek < 127 && 255.0 * pow2_double(ek) < ext) ek++; // the division above rounds: make the bound exact
         }
         e[k] = ek;
-        scale[k] = ldexp(1.0, ek);
-        inv_scale[k] = ldexp(1.0, -ek);
+        scale[k] = pow2_double(ek);
+        inv_scale[k] = pow2_double(-ek);
     }
 
     unsigned char meta[8], qlo[3][8], qhi[3][8];
@@ -474,18 +633,12 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
         } else {
             const unsigned unary = (1u << tcount[i]) - 1u; // 1, 3, 7
             meta[s] = (unsigned char)((unary << 5) | (unsigned)tri_off);
-            for (int k = 0; k < tcount[i]; k++) {
-                const uint32_t prim = a.sorted_prim[tfirst[i] + k];
-                const TriVerts tv = load_tri(a.P, a.idx, prim);
+            for (int k = 0; k < tcount[i]; k++) { // the leaf records exist already, in sorted order: a contiguous run moves over
+                const float4 *src = a.tri_sorted + 3 * (size_t)(tfirst[i] + k);
                 float4 *dst = a.tris + 3 * (size_t)(tri_base + tri_off + k);
-                dst[0] = make_float4(tv.a.x, tv.a.y, tv.a.z, __int_as_float((int)prim + a.prim_offset));
-                // v1.w = material id | degenerate << 28 | has-uv << 30 | has-normals << 29 | flip << 31 (b200pt.h: tri_flip bits 2, 1, 0), v2.w = light id (-1: none)
-                const uint32_t mat = (a.tri_material ? (uint32_t)a.tri_material[prim] : 0u) |
-                                     (a.tri_flip ? ((uint32_t(a.tri_flip[prim]) & 1u) << 31 | (uint32_t(a.tri_flip[prim]) & 6u) << 28) : 0u);
-                const int light = a.tri_light ? a.tri_light[prim] : -1;
-                const uint32_t degen = triangle_is_degenerate(tv.a.x, tv.a.y, tv.a.z, tv.b.x, tv.b.y, tv.b.z, tv.c.x, tv.c.y, tv.c.z) ? kTriDegenerate : 0u;
-                dst[1] = make_float4(tv.b.x, tv.b.y, tv.b.z, __uint_as_float(mat | degen));
-                dst[2] = make_float4(tv.c.x, tv.c.y, tv.c.z, __int_as_float(light));
+                dst[0] = src[0];
+                dst[1] = src[1];
+                dst[2] = src[2];
             }
             tri_off += tcount[i];
         }
@@ -597,7 +750,7 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
     Arena tmp;
     {
         const size_t sz = Arena::pad(12 * 4) * 2 + Arena::pad(n * 8) + Arena::pad(256 * sort_tiles(n) * 4) +
-                          Arena::pad(sort_scan_tmp_words(n) * 4) + Arena::pad(4 * n * sizeof(float4)) +
+                          Arena::pad(sort_scan_tmp_words(n) * 4) + Arena::pad(4 * n * sizeof(float4)) + 3 * Arena::pad(n * 4) + Arena::pad(3 * n * sizeof(float4)) +
                           Arena::pad(2 * n * 4) + Arena::pad(n * 4) + 2 * Arena::pad(n * sizeof(int2)) + Arena::pad(8 * 4);
         CU_TRY(cudaMalloc(&tmp.base, sz));
         tmp.size = sz;
@@ -614,9 +767,14 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
     sb.keys[(n_passes & 1) ^ 1] = d_keys_tmp;
     tmp.take(&sb.tile_hist, 256 * sort_tiles(n));
     tmp.take(&sb.scan_tmp, sort_scan_tmp_words(n));
+    float4 *d_tri_sorted;
+    tmp.take(&d_tri_sorted, 3 * n);
     Bvh2 t;
     t.n = int32_t(n);
     tmp.take(&t.rec, 4 * n);
+    tmp.take(&t.nodeA, n);
+    tmp.take(&t.nodeB, n);
+    tmp.take(&t.last, n);
     tmp.take(&t.parent, 2 * n);
     tmp.take(&t.arrive, n);
     int2 *q[2];
@@ -624,6 +782,9 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
     tmp.take(&q[0], n);
     tmp.take(&q[1], n);
     tmp.take(&d_counters, 8);
+    // the refit's root list lives in the collapse's second queue (2 n ints; the collapse starts after the refit is done)
+    int32_t *d_roots = reinterpret_cast<int32_t *>(q[1]);
+    unsigned *d_n_roots = d_counters + 7;
     if (tmp.used > tmp.size) {
         set_error("b200pt_bvh_build: scratch arena overrun");
         return B200PT_ERR_STATE;
@@ -645,32 +806,42 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
         set_error("b200pt_bvh_build: sort ended in the wrong buffer");
         return B200PT_ERR_STATE;
     }
-    k_unpack_prims<<<grid_n, tb, 0, st>>>(d_sorted_keys, n, key30 ? 0xffffffffu : uint32_t((uint64_t(1) << prim_bits) - 1), d_sorted_prim);
+    {
+        GatherArgs ga;
+        ga.P = range_P;
+        ga.idx = range_idx;
+        ga.tri_material = s->d_tri_material ? s->d_tri_material + first : nullptr;
+        ga.tri_light = s->d_tri_light ? s->d_tri_light + first : nullptr;
+        ga.tri_flip = s->d_tri_flip ? s->d_tri_flip + first : nullptr;
+        ga.prim_offset = (int32_t)first;
+        k_gather_sorted<<<grid_n, tb, 0, st>>>(d_sorted_keys, n, key30 ? 0xffffffffu : uint32_t((uint64_t(1) << prim_bits) - 1), ga, d_sorted_prim,
+                                               d_tri_sorted);
+    }
     CU_TRY(cudaEventRecord(ev[2], st));
     // 3. hierarchy emission
     CU_TRY(cudaMemsetAsync(t.arrive, 0, n * sizeof(uint32_t), st));
     if (n > 1) k_emit_hierarchy<<<int((n - 1 + tb - 1) / tb), tb, 0, st>>>(d_sorted_keys, t);
     CU_TRY(cudaEventRecord(ev[3], st));
     // 4. refit
-    k_refit<<<grid_n, tb, 0, st>>>(range_P, range_idx, d_sorted_prim, t);
+    CU_TRY(cudaMemsetAsync(d_n_roots, 0, sizeof(unsigned), st));
+    k_refit<<<int((n + REFIT_BLOCK - 1) / REFIT_BLOCK), REFIT_BLOCK, 0, st>>>(d_tri_sorted, t, d_roots, d_n_roots);
+    k_refit_climb<<<s->sm_count * 8, 128, 0, st>>>(t, d_roots, d_n_roots);
     CU_TRY(cudaEventRecord(ev[4], st));
     // 5. work-queue collapse to BVH8: levels are enqueued in batches, queue sizes stay on the device
     k_seed_queue<<<1, 1, 0, st>>>(q[0], d_counters, 0 /* leaf id n-1+0 == 0 when n == 1 */, node_base, leaf_base);
     unsigned int h_counters[8] = {node_base + 1, leaf_base, 0, 0, 1, 0, 0, 0};
     int parity = 0, levels = 0;
     const int collapse_grid = s->sm_count * 16;
+    // resident CTAs per SM are capped through a dynamic shared-memory request: each thread of k_collapse_level keeps ~600 B of
+    // indexed per-child state in local memory, and too many resident threads push that state out of L1 into L2 / DRAM
+    static const int collapse_smem = getenv("B200PT_COLLAPSE_SMEM") ? atoi(getenv("B200PT_COLLAPSE_SMEM")) : 0;
+    if (collapse_smem > 48 * 1024) cudaFuncSetAttribute(k_collapse_level, cudaFuncAttributeMaxDynamicSharedMemorySize, collapse_smem);
     while (true) {
         const int batch = levels == 0 ? 12 : 6;
         for (int b = 0; b < batch; b++) {
             CollapseArgs a;
             a.t = t;
-            a.P = range_P;
-            a.idx = range_idx;
-            a.prim_offset = (int32_t)first;
-            a.sorted_prim = d_sorted_prim;
-            a.tri_material = s->d_tri_material ? s->d_tri_material + first : nullptr;
-            a.tri_light = s->d_tri_light ? s->d_tri_light + first : nullptr;
-            a.tri_flip = s->d_tri_flip ? s->d_tri_flip + first : nullptr;
+            a.tri_sorted = d_tri_sorted;
             a.nodes = s->d_nodes;
             a.tris = s->d_tris;
             a.q_in = q[parity];
@@ -678,7 +849,7 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
             a.counters = d_counters;
             a.parity = parity;
             a.node_capacity = node_capacity;
-            k_collapse_level<<<collapse_grid, 128, 0, st>>>(a);
+            k_collapse_level<<<collapse_grid, 128, collapse_smem, st>>>(a);
             k_collapse_advance<<<1, 1, 0, st>>>(d_counters, parity);
             parity ^= 1;
             levels++;
