@@ -449,7 +449,7 @@ def run_ours(args):
         try:
             tj = json.load(open(prof))
             roofline["traffic"] = tj.get("k_trace_dram_bytes_per_launch")
-            roofline["ncu"] = {k2: tj[k2] for k2 in ("commit", "source", "issue_slots_busy_pct", "threads_per_inst", "warp_inst_per_ray") if k2 in tj}
+            roofline["ncu"] = {k2: tj[k2] for k2 in ("commit", "source", "issue_slots_busy_pct", "threads_per_inst", "warp_inst_per_ray", "alu_pipe_pct", "fma_pipe_pct", "note") if k2 in tj}
         except Exception:
             pass
 

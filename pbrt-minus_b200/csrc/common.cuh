@@ -124,7 +124,7 @@ struct b200pt_scene {
     unsigned long long *d_trace_counters = nullptr; // [0] ray ticket, [1] nodes, [2] tris, [3] err, [4..11] tickets of pipelined chunks
     bool counting = false;
     // k_trace tuning (b200pt_trace_tune): lanes idle before a warp refills, triangle tests per triangle phase, CTA cap per SM
-    int tune_refill = 4, tune_tri_steps = 1, tune_ctas_per_sm = 0;
+    int tune_refill = 4, tune_tri_steps = 3, tune_ctas_per_sm = 0;
     int tune_wf_refill = 0, tune_wf_tri_steps = 0; // wavefront trace kernels; 0 = the built-in default
     int tune_shade_occ = 0;                        // shade kernels: CTAs per SM the register allocation is held to (0 = default)
     int64_t last_counts[3] = {0, 0, 0};

@@ -2099,7 +2099,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     // with spheres the per-ray start-up is longer and waiting for half a warp pays (C1: 62.0 -> 58.5 ms together with the
     // sphere phase)
     wf.refill_min = s->tune_wf_refill > 0 ? s->tune_wf_refill : (s->n_spheres > 0 ? 16 : 4);
-    wf.tri_steps = s->tune_wf_tri_steps > 0 ? s->tune_wf_tri_steps : 1;
+    wf.tri_steps = s->tune_wf_tri_steps > 0 ? s->tune_wf_tri_steps : 2;
     const bool ext_shade = wf.has_media || r->tex.tex != nullptr || r->env.light >= 0;
     int n_shade_kernels = 0;
     for (int m = 0; m < WF_NMAT; m++) n_shade_kernels += r->has_mat[m] ? 1 : 0;

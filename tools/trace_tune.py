@@ -62,7 +62,7 @@ def main():
             hits[name] = hb.download(np.uint32, n * 4).copy()
         return res, hits
 
-    base_cfg = (4, 1, 0)
+    base_cfg = (4, 3, 0)
     _, base_hits = run(base_cfg)
     rows = []
     total_rays = sum(n for _, _, n, _, _ in dev)
@@ -75,7 +75,7 @@ def main():
                "ms_total": round(ms, 4), "Mrays_s": round(total_rays / ms / 1e3, 1), "hits_identical_to_default": bool(same)}
         rows.append(row)
         print(json.dumps(row), flush=True)
-    scene.tune(refill=4, tri_steps=1, ctas_per_sm=0)
+    scene.tune(refill=4, tri_steps=3, ctas_per_sm=0)
     best = max(rows, key=lambda r: r["Mrays_s"])
     print("best:", json.dumps(best))
     if args.out:
