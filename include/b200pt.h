@@ -318,7 +318,8 @@ int b200pt_trace_counters(b200pt_scene *scene, int64_t out[3]);
 /* Scheduling knobs of the traversal kernels (they change speed, never results): key 0 = idle lanes before a warp
  * of k_trace refills (1/4/8/16), 1 = triangle tests per triangle phase (1..3), 2 = resident CTAs per SM cap
  * (0 = occupancy limit), 3 / 4 = the same two knobs for the wavefront integrator's trace kernels (0 = default),
- * 5 = resident CTAs per SM the plain shade kernels' register allocation is held to (0 = default, 3, 4). */
+ * 5 = resident CTAs per SM the plain shade kernels' register allocation is held to (0 = default, 3, 4),
+ * 6 = k_trace with a one-deep triangle stash (0 / 1). */
 int b200pt_trace_tune(b200pt_scene *scene, int key, int value);
 void *b200pt_scene_stream(b200pt_scene *scene); /* cudaStream_t the scene launches on */
 int b200pt_scene_sync(b200pt_scene *scene);

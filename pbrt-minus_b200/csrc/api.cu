@@ -436,6 +436,7 @@ B200PT_API int b200pt_trace_tune(b200pt_scene *s, int key, int value) {
     case 3: s->tune_wf_refill = value; break;
     case 4: s->tune_wf_tri_steps = value > 3 ? 3 : value; break;
     case 5: s->tune_shade_occ = value; break;
+    case 6: s->tune_stash = value != 0; break;
     default: set_error("b200pt_trace_tune: unknown key %d", key); return B200PT_ERR_INVALID;
     }
     return B200PT_OK;

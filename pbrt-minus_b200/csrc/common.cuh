@@ -126,6 +126,7 @@ struct b200pt_scene {
     // k_trace tuning (b200pt_trace_tune): lanes idle before a warp refills, triangle tests per triangle phase, CTA cap per SM
     int tune_refill = 4, tune_tri_steps = 3, tune_ctas_per_sm = 0;
     int tune_wf_refill = 0, tune_wf_tri_steps = 0; // wavefront trace kernels; 0 = the built-in default
+    int tune_stash = 0;                            // k_trace with a one-deep triangle stash (k_trace_stash)
     int tune_shade_occ = 0;                        // shade kernels: CTAs per SM the register allocation is held to (0 = default)
     int64_t last_counts[3] = {0, 0, 0};
     int64_t device_bytes = 0;

@@ -178,6 +178,159 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(TraceParams p) {
     if (overflow) p.counters[3] = 1ull; // sticky: cleared when the host reads it (check_trace_status)
 }
 
+// k_trace with a one-deep triangle STASH.  In k_trace a lane that found triangle work waits for a triangle phase, and a triangle
+// phase runs as soon as the triangle lanes outnumber the node lanes -- both phases run with about half the warp.  Here a lane
+// keeps walking nodes with its triangle group set aside (one more group fits in the stash), and a triangle phase starts only
+// when three quarters of the live lanes hold triangle work (or nobody can do node work): both long code paths run with most of
+// the warp.  The price is a best-t that is up to two node steps stale when the next nodes are culled.  Same results: the
+// triangle test and the argmin over t do not depend on the order of the tests (exact ties aside).
+template <bool ANY, bool COUNT, int REFILL, int TRI_STEPS>
+__global__ void __launch_bounds__(TRACE_BLOCK) k_trace_stash(TraceParams p) {
+    __shared__ uint2 sm_stack_all[SM_STACK * TRACE_BLOCK];
+    uint2 *const sm_stack = sm_stack_all + threadIdx.x;
+    uint2 lstack[LOCAL_STACK];
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const bool have_tree = p.bvh.n_nodes > 0;
+
+    long long ray = -1; // this lane's ray index, -1 = idle
+    bool exhausted = false;
+    float ox = 0, oy = 0, oz = 0, idx = 0, idy = 0, idz = 0;
+    RayShear rs = {0.f, 0.f, 0.f, 2}; // ray-only part of the watertight test, evaluated once per ray
+    uint32_t octinv4 = 0;
+    uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u), ts = make_uint2(0u, 0u); // ts: the stashed triangle group
+    int sp = 0;
+    float ht = 0, hb1 = 0, hb2 = 0;
+    int hprim = -1;
+    unsigned n_nodes = 0, n_tris = 0, overflow = 0;
+
+    while (true) {
+        // ---- warp-aggregated fetch of new rays into idle lanes
+        const unsigned idle = __ballot_sync(0xffffffffu, ray < 0);
+        if (!exhausted && (__popc(idle) >= REFILL || idle == 0xffffffffu)) {
+            const int n_idle = __popc(idle);
+            const int leader = __ffs(idle) - 1;
+            unsigned long long base = 0;
+            if (lane == leader) base = atomicAdd(p.ticket, (unsigned long long)n_idle);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if ((long long)base + n_idle >= p.n) exhausted = true;
+            if (ray < 0) {
+                const long long r = (long long)base + __popc(idle & lt_mask);
+                if (r < p.n) {
+                    ray = r;
+                    float4 ro, rd;
+                    if (p.o) {
+                        const float *po = p.o + 3 * r, *pd = p.d + 3 * r;
+                        ro = make_float4(__ldg(po), __ldg(po + 1), __ldg(po + 2), __ldg(p.tmax + r));
+                        rd = make_float4(__ldg(pd), __ldg(pd + 1), __ldg(pd + 2), 0.f);
+                    } else {
+                        ro = __ldg(p.rays + 2 * r);
+                        rd = __ldg(p.rays + 2 * r + 1);
+                    }
+                    ox = ro.x; oy = ro.y; oz = ro.z;
+                    idx = safe_rcp_dir(rd.x); idy = safe_rcp_dir(rd.y); idz = safe_rcp_dir(rd.z);
+                    rs = ray_shear(rd.x, rd.y, rd.z);
+                    octinv4 = ((idx < 0.f ? 0u : 4u) | (idy < 0.f ? 0u : 2u) | (idz < 0.f ? 0u : 1u)) * 0x01010101u;
+                    ng = make_uint2(0u, have_tree ? 0x80000000u : 0u);
+                    tg = make_uint2(0u, 0u);
+                    ts = make_uint2(0u, 0u);
+                    sp = 0;
+                    ht = ro.w;
+                    hb1 = 0.f; hb2 = 0.f;
+                    hprim = -1;
+                }
+            }
+        }
+        if (__ballot_sync(0xffffffffu, ray >= 0) == 0u) break;
+
+        // ---- phase vote
+        const bool act = ray >= 0;
+        const bool want_tri = act && tg.y != 0u;                          // tg is non-empty whenever ts is
+        const bool has_node = act && (ng.y > 0x00ffffffu || sp > 0);
+        const bool can_node = act && !(want_tri && ts.y != 0u) && (has_node || !want_tri); // incl. lanes that only have to retire
+        const int c_live = __popc(__ballot_sync(0xffffffffu, act));
+        const int c_tri = __popc(__ballot_sync(0xffffffffu, want_tri));
+        const int c_node = __popc(__ballot_sync(0xffffffffu, can_node));
+        if (c_node == 0 || 4 * c_tri >= 3 * c_live) {
+            if (want_tri) {
+#pragma unroll 1
+                for (int step = 0; step < TRI_STEPS && tg.y != 0u; step++) {
+                    const int ti = __ffs(tg.y) - 1;
+                    tg.y &= tg.y - 1u;
+                    const float4 *tp = p.bvh.tris + 3 * size_t(tg.x + ti);
+                    const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                    if (COUNT) n_tris++;
+                    TriHit th;
+                    if (!(__float_as_uint(v1.w) & kTriDegenerate) &&
+                        intersect_triangle_sheared(ox, oy, oz, rs, ht, v0.x, v0.y, v0.z, v1.x, v1.y, v1.z, v2.x, v2.y, v2.z, th)) {
+                        ht = th.t;
+                        hb1 = th.b1;
+                        hb2 = th.b2;
+                        hprim = __float_as_int(v0.w);
+                        if (ANY) { // first accepted candidate ends the ray
+                            tg.y = 0u;
+                            ts.y = 0u;
+                            ng.y = 0u;
+                            sp = 0;
+                        }
+                    }
+                }
+                if (tg.y == 0u) { // the stashed group moves up
+                    tg = ts;
+                    ts.y = 0u;
+                }
+            }
+        } else if (can_node) {
+            if (ng.y <= 0x00ffffffu && sp > 0) {
+                sp--;
+                if (sp < SM_STACK) ng = sm_stack[sp * TRACE_BLOCK];
+                else if (sp < SM_STACK + LOCAL_STACK) ng = lstack[sp - SM_STACK];
+                else ng = make_uint2(0u, 0u);
+            }
+            if (ng.y > 0x00ffffffu) {
+                const uint32_t hits = ng.y;
+                const int child_bit = 31 - __clz(hits);
+                ng.y &= ~(1u << child_bit);
+                if (ng.y > 0x00ffffffu) {
+                    if (sp < SM_STACK) sm_stack[sp * TRACE_BLOCK] = ng;
+                    else if (sp < SM_STACK + LOCAL_STACK) lstack[sp - SM_STACK] = ng;
+                    else overflow = 1u;
+                    sp++;
+                }
+                const uint32_t slot = (uint32_t(child_bit) - 24u) ^ (octinv4 & 0xffu);
+                const uint32_t rel = __popc(hits & 0xffu & ((1u << slot) - 1u));
+                const float4 *np = p.bvh.nodes + 5 * size_t(ng.x + rel);
+                const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+                if (COUNT) n_nodes++;
+                const uint32_t hitmask = intersect_node8(n0, n1, n2, n3, n4, ox, oy, oz, idx, idy, idz, octinv4, ht, p.prmt_bias);
+                ng.x = __float_as_uint(n1.x);
+                ng.y = (hitmask & 0xff000000u) | (__float_as_uint(n0.w) >> 24);
+                const uint2 tn = make_uint2(__float_as_uint(n1.y), hitmask & 0x00ffffffu);
+                if (tn.y != 0u) {
+                    if (tg.y == 0u) tg = tn;
+                    else ts = tn; // can_node guarantees the stash was free
+                }
+            } else { // nothing left: retire the ray
+                if (p.o) {
+                    if (p.prim_out) p.prim_out[ray] = ANY ? (hprim >= 0 ? 1 : 0) : hprim;
+                    if (p.t_out) p.t_out[ray] = (ANY || hprim < 0) ? (ANY ? 0.f : kInf) : ht;
+                    if (p.b12_out) *reinterpret_cast<float2 *>(p.b12_out + 2 * ray) = ANY ? make_float2(0.f, 0.f) : make_float2(hb1, hb2);
+                } else if (ANY) {
+                    p.hits[ray] = make_float4(__int_as_float(hprim >= 0 ? 1 : 0), 0.f, 0.f, 0.f);
+                } else {
+                    p.hits[ray] = make_float4(__int_as_float(hprim), hprim >= 0 ? ht : kInf, hb1, hb2);
+                }
+                ray = -1;
+            }
+        }
+    }
+    if (COUNT) {
+        atomicAdd(p.counters + 1, (unsigned long long)n_nodes);
+        atomicAdd(p.counters + 2, (unsigned long long)n_tris);
+    }
+    if (overflow) p.counters[3] = 1ull; // sticky: cleared when the host reads it (check_trace_status)
+}
+
 // ---- queue-driven form used by the wavefront integrator (render.cu) ---------------------------
 // Same traversal loop; what differs from k_trace: the ray count and the ray list come from DEVICE
 // memory (queue + counter written by the previous stage, no host round trip), rays are gathered from
@@ -464,6 +617,13 @@ static TraceKernel pick_kernel2(bool any_hit, bool counting) {
     return any_hit ? (counting ? k_trace<true, true, REFILL, TRI_STEPS> : k_trace<true, false, REFILL, TRI_STEPS>)
                    : (counting ? k_trace<false, true, REFILL, TRI_STEPS> : k_trace<false, false, REFILL, TRI_STEPS>);
 }
+static TraceKernel pick_stash_kernel(bool any_hit, bool counting, int tri_steps) {
+    if (tri_steps <= 1) return any_hit ? (counting ? k_trace_stash<true, true, 4, 1> : k_trace_stash<true, false, 4, 1>)
+                                       : (counting ? k_trace_stash<false, true, 4, 1> : k_trace_stash<false, false, 4, 1>);
+    return any_hit ? (counting ? k_trace_stash<true, true, 4, 3> : k_trace_stash<true, false, 4, 3>)
+                   : (counting ? k_trace_stash<false, true, 4, 3> : k_trace_stash<false, false, 4, 3>);
+}
+
 template <int REFILL>
 static TraceKernel pick_kernel(bool any_hit, bool counting, int tri_steps) {
     return tri_steps <= 1 ? pick_kernel2<REFILL, 1>(any_hit, counting)
@@ -505,6 +665,7 @@ int launch_trace(b200pt_scene *s, const void *rays_dev, int64_t n, int any_hit, 
                      : refill <= 4 ? pick_kernel<4>(any_hit, s->counting, tri_steps)
                      : refill <= 8 ? pick_kernel<8>(any_hit, s->counting, tri_steps)
                                    : pick_kernel<16>(any_hit, s->counting, tri_steps);
+    if (s->tune_stash) kern = pick_stash_kernel(any_hit, s->counting, tri_steps);
     int per_sm = 0;
     CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TRACE_BLOCK, 0));
     if (per_sm < 1) per_sm = 1;

@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--refill", default="1,4,8,16")
     ap.add_argument("--tri-steps", default="1,2,3")
     ap.add_argument("--ctas", default="0")
+    ap.add_argument("--stash", default="0,1")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     pkg = importlib.import_module("pbrt-minus_b200")
@@ -45,7 +46,7 @@ def main():
         dev.append((name, any_hit, len(o), rb, hb))
 
     def run(cfg):
-        scene.tune(refill=cfg[0], tri_steps=cfg[1], ctas_per_sm=cfg[2])
+        scene.tune(refill=cfg[0], tri_steps=cfg[1], ctas_per_sm=cfg[2], stash=cfg[3] if len(cfg) > 3 else 0)
         res = {}
         hits = {}
         for name, any_hit, n, rb, hb in dev:
@@ -62,20 +63,20 @@ def main():
             hits[name] = hb.download(np.uint32, n * 4).copy()
         return res, hits
 
-    base_cfg = (4, 3, 0)
+    base_cfg = (4, 3, 0, 0)
     _, base_hits = run(base_cfg)
     rows = []
     total_rays = sum(n for _, _, n, _, _ in dev)
     for cfg in itertools.product([int(x) for x in args.refill.split(",")], [int(x) for x in args.tri_steps.split(",")],
-                                 [int(x) for x in args.ctas.split(",")]):
+                                 [int(x) for x in args.ctas.split(",")], [int(x) for x in args.stash.split(",")]):
         res, hits = run(cfg)
         same = all(np.array_equal(hits[k], base_hits[k]) for k in hits)
         ms = sum(res.values())
-        row = {"refill": cfg[0], "tri_steps": cfg[1], "ctas_per_sm": cfg[2], "ms": {k: round(v, 4) for k, v in res.items()},
+        row = {"refill": cfg[0], "tri_steps": cfg[1], "ctas_per_sm": cfg[2], "stash": cfg[3], "ms": {k: round(v, 4) for k, v in res.items()},
                "ms_total": round(ms, 4), "Mrays_s": round(total_rays / ms / 1e3, 1), "hits_identical_to_default": bool(same)}
         rows.append(row)
         print(json.dumps(row), flush=True)
-    scene.tune(refill=4, tri_steps=3, ctas_per_sm=0)
+    scene.tune(refill=4, tri_steps=3, ctas_per_sm=0, stash=0)
     best = max(rows, key=lambda r: r["Mrays_s"])
     print("best:", json.dumps(best))
     if args.out:
