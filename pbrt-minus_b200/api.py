@@ -137,7 +137,7 @@ class RaySet(C.Structure):
 # every symbol include/b200pt.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "b200pt_abi_version", "b200pt_last_error", "b200pt_device_count",
-    "b200pt_scene_create", "b200pt_scene_destroy", "b200pt_bvh_build", "b200pt_bvh_debug_sorted",
+    "b200pt_scene_create", "b200pt_scene_destroy", "b200pt_bvh_build", "b200pt_bvh_debug_sorted", "b200pt_bvh_validate",
     "b200pt_trace", "b200pt_trace_batch", "b200pt_trace_device", "b200pt_trace_set_counting", "b200pt_trace_counters", "b200pt_trace_tune",
     "b200pt_scene_stream", "b200pt_scene_sync",
     "b200pt_device_alloc", "b200pt_device_free", "b200pt_copy_to_device", "b200pt_copy_to_host",
@@ -165,6 +165,7 @@ def load_library():
     lib.b200pt_scene_destroy.restype = None
     lib.b200pt_bvh_build.argtypes = [vp, C.POINTER(BuildStats)]
     lib.b200pt_bvh_debug_sorted.argtypes = [vp, ip, C.POINTER(C.c_uint64)]
+    lib.b200pt_bvh_validate.argtypes = [vp, C.POINTER(i64)]
     lib.b200pt_trace.argtypes = [vp, fp, fp, fp, i64, i32, ip, fp, fp]
     lib.b200pt_trace_batch.argtypes = [vp, C.POINTER(RaySet), i32]
     lib.b200pt_trace_device.argtypes = [vp, vp, i64, i32, vp, i32]

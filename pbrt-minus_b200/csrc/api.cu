@@ -277,6 +277,15 @@ int finish_instances(b200pt_scene *s) {
 }
 } // namespace b200pt
 
+B200PT_API int b200pt_bvh_validate(b200pt_scene *s, int64_t out[3]) {
+    if (!s || !out || !s->built) {
+        set_error("b200pt_bvh_validate: build first");
+        return B200PT_ERR_STATE;
+    }
+    CU_TRY(cudaSetDevice(s->device));
+    return validate_bvh(s, out);
+}
+
 B200PT_API int b200pt_bvh_debug_sorted(b200pt_scene *s, int32_t *prim_order_out, uint64_t *keys_out) {
     if (!s || !s->built) {
         set_error("b200pt_bvh_debug_sorted: build first");

@@ -677,6 +677,80 @@ __global__ void k_seed_queue(int2 *q, unsigned int *counters, int root2, unsigne
     counters[5] = 0;
 }
 
+// ------------------------------------------------------------------------------ structural validation
+// Direct check of what the traversal relies on (b200pt_bvh_validate): every child box of every BVH8 node, dequantised the way
+// intersect_node8 reads it (p + q * 2^e, mins from qlo, maxes from qhi), contains
+//   - all vertices of the triangles of a leaf child, and
+//   - the whole box of an inner child's node (the union of that node's own dequantised child boxes);
+// and every triangle slot is referenced by exactly one leaf child.  out[0] = boxes that fail, out[1] = triangle references,
+// out[2] = nodes visited.  One thread per node.
+__global__ void __launch_bounds__(128) k_validate(const float4 *__restrict__ nodes, const float4 *__restrict__ tris, unsigned first_node,
+                                                  unsigned n_nodes, unsigned long long *out) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    const float4 *np = nodes + 5 * size_t(first_node + i);
+    const float4 n0 = np[0], n1 = np[1], n2 = np[2], n3 = np[3], n4 = np[4];
+    const uint32_t eb = __float_as_uint(n0.w);
+    const double sx = __uint_as_float((eb & 0xffu) << 23), sy = __uint_as_float(((eb >> 8) & 0xffu) << 23), sz = __uint_as_float(((eb >> 16) & 0xffu) << 23);
+    auto byte_of = [](float lo, float hi, int s) { return (__float_as_uint(s < 4 ? lo : hi) >> (8 * (s & 3))) & 0xffu; };
+    unsigned long long bad = 0, refs = 0;
+    const uint32_t child_base = __float_as_uint(n1.x), tri_base = __float_as_uint(n1.y), imask = eb >> 24;
+    for (int s = 0; s < 8; s++) {
+        const uint32_t meta = byte_of(n1.z, n1.w, s);
+        if (meta == 0u) continue;
+        // exact in double: a float plus an 8-bit multiple of a power of two
+        const double lo[3] = {n0.x + byte_of(n2.x, n2.y, s) * sx, n0.y + byte_of(n2.z, n2.w, s) * sy, n0.z + byte_of(n3.x, n3.y, s) * sz};
+        const double hi[3] = {n0.x + byte_of(n3.z, n3.w, s) * sx, n0.y + byte_of(n4.x, n4.y, s) * sy, n0.z + byte_of(n4.z, n4.w, s) * sz};
+        bool ok = true;
+        if (imask & (1u << s)) {
+            if ((meta >> 5) != 1u || (meta & 0x1fu) != 24u + s) ok = false;
+            const uint32_t rel = __popc(imask & ((1u << s) - 1u));
+            const float4 *cp = nodes + 5 * size_t(child_base + rel);
+            const float4 c0 = cp[0], c1 = cp[1], c2 = cp[2], c3 = cp[3], c4 = cp[4];
+            const uint32_t ceb = __float_as_uint(c0.w);
+            const double cs[3] = {__uint_as_float((ceb & 0xffu) << 23), __uint_as_float(((ceb >> 8) & 0xffu) << 23), __uint_as_float(((ceb >> 16) & 0xffu) << 23)};
+            for (int t = 0; t < 8; t++) {
+                if (byte_of(c1.z, c1.w, t) == 0u) continue;
+                const double clo[3] = {c0.x + byte_of(c2.x, c2.y, t) * cs[0], c0.y + byte_of(c2.z, c2.w, t) * cs[1], c0.z + byte_of(c3.x, c3.y, t) * cs[2]};
+                const double chi[3] = {c0.x + byte_of(c3.z, c3.w, t) * cs[0], c0.y + byte_of(c4.x, c4.y, t) * cs[1], c0.z + byte_of(c4.z, c4.w, t) * cs[2]};
+                // mins: exact (the child's grid starts at its own box minimum, which this box bounds); maxes: the child rounds its
+                // own boxes up on ITS grid, so they may pass the parent's bound by less than one child step
+                for (int a = 0; a < 3; a++)
+                    if (clo[a] < lo[a] || chi[a] >= hi[a] + cs[a]) ok = false;
+            }
+        } else {
+            const int off = meta & 0x1f, count = __popc(meta >> 5);
+            if (off + count > 24) ok = false;
+            for (int k = 0; k < count; k++) {
+                const float4 *tp = tris + 3 * size_t(tri_base + off + k);
+                for (int v = 0; v < 3; v++) {
+                    const float4 q = tp[v];
+                    if (q.x < lo[0] || q.x > hi[0] || q.y < lo[1] || q.y > hi[1] || q.z < lo[2] || q.z > hi[2]) ok = false;
+                }
+                refs++;
+            }
+        }
+        if (!ok) bad++;
+    }
+    if (bad) atomicAdd(out, bad);
+    if (refs) atomicAdd(out + 1, refs);
+    atomicAdd(out + 2, 1ull);
+}
+
+int validate_bvh(b200pt_scene *s, int64_t out[3]) {
+    unsigned long long *d = nullptr;
+    CU_TRY(cudaMalloc(&d, 3 * sizeof(unsigned long long)));
+    CU_TRY(cudaMemsetAsync(d, 0, 3 * sizeof(unsigned long long), s->stream));
+    const unsigned n_all = s->n_nodes_total; // the top-level tree and every object tree: node indices are dense
+    if (n_all > 0) k_validate<<<(n_all + 127) / 128, 128, 0, s->stream>>>(s->d_nodes, s->d_tris, 0, n_all, d);
+    unsigned long long h[3] = {0, 0, 0};
+    CU_TRY(cudaMemcpyAsync(h, d, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    cudaFree(d);
+    for (int k = 0; k < 3; k++) out[k] = (int64_t)h[k];
+    return B200PT_OK;
+}
+
 // ------------------------------------------------------------------------------ host driver
 namespace {
 // one cudaMalloc for all build scratch, carved into 256-byte aligned pieces (every cudaMalloc costs
@@ -936,6 +1010,7 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
         node_base += oo.n_nodes;
     }
     bs.n_bvh8_nodes = node_base;
+    s->n_nodes_total = node_base;
     bs.ms_wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - wall0).count();
     s->bvh.nodes = s->d_nodes;
     s->bvh.tris = s->d_tris;

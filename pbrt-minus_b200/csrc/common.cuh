@@ -104,7 +104,7 @@ struct b200pt_scene {
 
     // instancing (b200pt_scene_desc.objects / instances)
     int64_t n_top_triangles = 0;
-    unsigned n_top_nodes = 0;
+    unsigned n_top_nodes = 0, n_nodes_total = 0;
     std::vector<b200pt::HostObject> objects;
     std::vector<b200pt_instance> instances;
     b200pt::InstRec *d_instances = nullptr;
@@ -141,6 +141,7 @@ struct b200pt_scene {
 namespace b200pt {
 
 int build_bvh(b200pt_scene *s, b200pt_build_stats *stats);
+int validate_bvh(b200pt_scene *s, int64_t out[3]);
 int finish_instances(b200pt_scene *s); // after the build: instance records (object roots and boxes) to the device
 // keep_status: leave the node / triangle / overflow counters as they are (a later chunk of the same batch); the work ticket is
 // always reset

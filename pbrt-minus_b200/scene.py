@@ -69,6 +69,12 @@ class HLBVH:
         self.build_stats = st.as_dict()
         return self.build_stats
 
+    def validate(self):
+        """b200pt_bvh_validate: {bad_boxes, triangle_refs, nodes} -- a conservative tree has bad_boxes == 0"""
+        out = (C.c_int64 * 3)()
+        _check(self.lib.b200pt_bvh_validate(self.handle, out))
+        return {"bad_boxes": out[0], "triangle_refs": out[1], "nodes": out[2]}
+
     def sorted_order(self):
         prim = np.empty(self.n_triangles, dtype=np.int32)
         keys = np.empty(self.n_triangles, dtype=np.uint64)

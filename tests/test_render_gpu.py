@@ -61,12 +61,14 @@ def frac_close(a, b):
     return float((np.abs(a - b).max(axis=2) <= 0.01 * lum + 1e-3).mean())
 
 
-def render(b200pt, text, spp, tmp_path, sample_begin=0, sample_end=None, pool_size=0, raw=False):
+def render(b200pt, text, spp, tmp_path, sample_begin=0, sample_end=None, pool_size=0, raw=False, tune=None):
     p = os.path.join(str(tmp_path), "scene.pbrt")
     open(p, "w").write(text)
     # relative file names (PLY meshes, images) resolve against tests/scenes, where the scene text came from
     sc = b200pt.pbrt_scene.load(p, spp=spp, scene_dir=os.path.join(ROOT, "tests", "scenes"))
     integ = b200pt.WavefrontPathIntegrator(sc, device=0)
+    if tune:
+        integ.accel.tune(**tune)
     film = integ.create_film()
     st = integ.render(film, sample_begin=sample_begin, sample_end=sample_end, pool_size=pool_size)
     out = film.raw() if raw else film.get_pixel_rgb()

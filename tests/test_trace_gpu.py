@@ -387,6 +387,25 @@ def test_c2_size_hit_ids_vs_reference_hlbvh_and_oracle_bvh(b200pt, oracle, tmp_p
     s.close()
 
 
+@pytest.mark.parametrize("n_tris,seed", [(1, 0), (3, 1), (9, 2), (1000, 3), (200_000, 4), (3_000_000, 5)])
+def test_bvh8_is_conservative(b200pt, n_tris, seed):
+    """The quantised tree itself, not only its answers: every child box, dequantised the way the traversal reads it, contains
+    the vertices of the triangles (leaf child) / the child boxes of the node (inner child) it stands for, every triangle slot is
+    referenced exactly once, and every node is reachable (b200pt_bvh_validate walks all nodes)."""
+    P, idx = b200pt.workloads.triangle_soup(n_tris, seed=seed)
+    if n_tris >= 1000:   # a few degenerate and huge triangles, and a far outlier, to stress the grid exponents
+        P = P.copy()
+        P[0:3] = P[0]
+        P[3:6] = P[3:6] * np.float32(50.0)
+        P[6:9] += np.float32(1e4)
+    s = b200pt.HLBVH(P, idx)
+    v = s.validate()
+    assert v["bad_boxes"] == 0
+    assert v["triangle_refs"] == n_tris
+    assert v["nodes"] == s.build_stats["n_bvh8_nodes"]
+    s.close()
+
+
 def test_packed_key_build_above_16M_triangles(b200pt, oracle):
     """N > 16 Mi: key = morton(3 * b) << ceil(log2 N) | prim, b = floor((64 - ceil(log2 N)) / 3), one 8-byte key-only sort
     (csrc/bvh_build.cu).  17 M triangles: the sorted order is a permutation, keys strictly increase, the low bits are the
