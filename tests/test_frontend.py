@@ -221,7 +221,7 @@ def test_texture_front_end(b200pt, tmp_path):
     for bad in ('Texture "t" "spectrum" "checkerboard"', 'Texture "t" "spectrum" "imagemap" "string filename" ["nope.png"]',
                 'Texture "t" "spectrum" "imagemap" "string filename" ["x.exr"]', 'Texture "t" "spectrum" "wrinkled"',
                 'Material "diffuse" "texture reflectance" ["undefined"]', 'Texture "t" "float" "mix"',
-                'Texture "t" "spectrum" "imagemap" "string filename" ["textures/colours.png"] "string mapping" ["planar"]'):
+                'Texture "t" "spectrum" "imagemap" "string filename" ["textures/colours.png"] "string mapping" ["hexagonal"]'):
         with pytest.raises(ps.SceneError):
             ps.load(text=head + bad + "\n", scene_dir=os.path.join(ROOT, "tests", "scenes"))
 
