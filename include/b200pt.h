@@ -352,6 +352,13 @@ int b200pt_film_read(b200pt_film *film, float *rgb_out);
  * output RGB (the reference's minimax sRGB curve, spectrum_util/color_encoding.h:6-45), alpha 255; converted on the device.
  * nan_pixels_out (may be NULL): pixels with a NaN component (the reference aborts on them; here they are written as 0). */
 int b200pt_film_read_srgb8(b200pt_film *film, uint8_t *rgba_out, int32_t *nan_pixels_out);
+/* No counterpart in the reference: added for callers that may not allocate device
+ * memory (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same result as b200pt_film_read_srgb8,
+ * but the 8-bit image is staged in a file-scope device array of the library instead of the scene's growable scratch buffer:
+ * the call makes no cudaMalloc / cudaFree.  Limit: films of at most 2,097,152 pixels (1920x1080 fits); a larger film is refused
+ * with B200PT_ERR_INVALID.  Every GPU that loads the library holds the array (8 MiB + 256 B) until the process exits; all calls
+ * share it, so two calls that overlap on one GPU race -- serialise them. */
+int b200pt_film_read_srgb8_static(b200pt_film *film, uint8_t *rgba_out, int32_t *nan_pixels_out);
 /* raw accumulators: xyzw_out[W*H*4] */
 int b200pt_film_read_raw(b200pt_film *film, float *xyzw_out);
 

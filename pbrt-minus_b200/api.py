@@ -142,7 +142,7 @@ SYMBOLS = [
     "b200pt_scene_stream", "b200pt_scene_sync",
     "b200pt_device_alloc", "b200pt_device_free", "b200pt_copy_to_device", "b200pt_copy_to_host",
     "b200pt_film_create", "b200pt_film_destroy", "b200pt_film_clear", "b200pt_render", "b200pt_film_reduce",
-    "b200pt_film_device_ptr", "b200pt_film_dims", "b200pt_film_read", "b200pt_film_read_srgb8", "b200pt_film_read_raw",
+    "b200pt_film_device_ptr", "b200pt_film_dims", "b200pt_film_read", "b200pt_film_read_srgb8", "b200pt_film_read_srgb8_static", "b200pt_film_read_raw",
     "b200pt_probe_sampler", "b200pt_probe_triangle",
 ]
 
@@ -191,6 +191,7 @@ def load_library():
     lib.b200pt_film_read.argtypes = [vp, fp]
     lib.b200pt_film_read_raw.argtypes = [vp, fp]
     lib.b200pt_film_read_srgb8.argtypes = [vp, C.POINTER(C.c_uint8), ip]
+    lib.b200pt_film_read_srgb8_static.argtypes = [vp, C.POINTER(C.c_uint8), ip]
     lib.b200pt_probe_sampler.argtypes = [vp, i32, i32, ip, ip, i32, ip, i32, fp]
     lib.b200pt_probe_triangle.argtypes = [vp, fp, fp, fp, fp, i64, ip, fp]
     _lib = lib

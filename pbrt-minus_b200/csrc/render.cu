@@ -19,6 +19,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <numeric>
 #include <set>
 
@@ -2361,6 +2362,87 @@ B200PT_API int b200pt_film_read_srgb8(b200pt_film *film, uint8_t *rgba_out, int3
     k_film_srgb8<<<unsigned((n + 255) / 256), 256, 0, s->stream>>>(film->d_accum, n, d_M, d_rgba, d_nan);
     CU_TRY(cudaMemcpyAsync(rgba_out, d_rgba, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
     CU_TRY(cudaMemcpyAsync(&h_nan, d_nan, sizeof(unsigned), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    if (nan_pixels_out) *nan_pixels_out = (int32_t)h_nan;
+    return B200PT_OK;
+}
+
+// ---- b200pt_film_read_srgb8_static: the sRGB8 conversion for callers that may not allocate -----------------------------------
+// No counterpart in the reference.  b200pt_film_read_srgb8 stages its 8-bit image
+// in the scene's scratch buffer, which ensure_scratch() grows with cudaMalloc.  This variant stages it in a file-scope device
+// array instead: every GPU that loads the library holds the array (8 MiB + 256 B) until the process exits, every call shares it,
+// and it keeps the last call's pixels -- the NaN counter is cleared per call, the pixels of the film are overwritten before
+// they are copied out, and two calls that overlap on one GPU race.  The host never uses the array's name as an address: the
+// device address comes from cudaGetSymbolAddress, once per device, with that device current.
+namespace b200pt {
+constexpr long long kStaticFilmMaxPixels = 1ll << 21; // 2,097,152 pixels: a 1920x1080 film fits
+constexpr size_t kStaticFilmHeader = 256;             // [0, 4): NaN-pixel counter; the RGBA bytes start at 256
+static __device__ __align__(256) unsigned char g_film_static_scratch[kStaticFilmHeader + 4 * kStaticFilmMaxPixels];
+
+struct Mat3 {
+    float m[9];
+};
+
+__global__ void k_film_srgb8_static(const float4 *accum, long long n, Mat3 M, unsigned char *scratch) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned *nan_count = (unsigned *)scratch;
+    uchar4 *rgba = (uchar4 *)(scratch + kStaticFilmHeader);
+    const float4 a = accum[i];
+    float x = a.x, y = a.y, z = a.z;
+    if (a.w != 0.f) {
+        x /= a.w;
+        y /= a.w;
+        z /= a.w;
+    }
+    const float r = M.m[0] * x + M.m[1] * y + M.m[2] * z, g = M.m[3] * x + M.m[4] * y + M.m[5] * z, b = M.m[6] * x + M.m[7] * y + M.m[8] * z;
+    if (isnan(r) || isnan(g) || isnan(b)) atomicAdd(nan_count, 1u);
+    rgba[i] = make_uchar4(srgb8_from_linear(r), srgb8_from_linear(g), srgb8_from_linear(b), 255);
+}
+
+// device address of g_film_static_scratch on `device` (current): looked up once per device
+static int film_static_scratch(int device, unsigned char **out) {
+    constexpr int kMaxDevices = 64;
+    static unsigned char *ptr[kMaxDevices] = {};
+    static std::mutex lock;
+    if (device < 0 || device >= kMaxDevices) {
+        set_error("b200pt_film_read_srgb8_static: device %d out of range", device);
+        return B200PT_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> g(lock);
+    if (!ptr[device]) {
+        unsigned char *p = nullptr;
+        CU_TRY(cudaGetSymbolAddress((void **)&p, g_film_static_scratch));
+        ptr[device] = p;
+    }
+    *out = ptr[device];
+    return B200PT_OK;
+}
+} // namespace b200pt
+
+B200PT_API int b200pt_film_read_srgb8_static(b200pt_film *film, uint8_t *rgba_out, int32_t *nan_pixels_out) {
+    if (!rgba_out) return B200PT_ERR_INVALID;
+    if (int rc = film_alive(film, "b200pt_film_read_srgb8_static")) return rc;
+    b200pt_scene *s = film->scene;
+    const long long n = (long long)film->width * film->height;
+    if (n > kStaticFilmMaxPixels) {
+        set_error("b200pt_film_read_srgb8_static: the film has %lld pixels, the static staging array holds %lld (use b200pt_film_read_srgb8)",
+                  n, kStaticFilmMaxPixels);
+        return B200PT_ERR_INVALID;
+    }
+    CU_TRY(cudaSetDevice(s->device));
+    unsigned char *scratch = nullptr;
+    if (int rc = film_static_scratch(s->device, &scratch)) return rc;
+    Mat3 M;
+    for (int k = 0; k < 9; k++) M.m[k] = s->render->out_rgb[k];
+    unsigned h_nan = 0;
+    CU_TRY(cudaMemsetAsync(scratch, 0, sizeof(unsigned), s->stream));
+    if (n > 0) {
+        k_film_srgb8_static<<<unsigned((n + 255) / 256), 256, 0, s->stream>>>(film->d_accum, n, M, scratch);
+        CU_TRY(cudaGetLastError());
+        CU_TRY(cudaMemcpyAsync(rgba_out, scratch + kStaticFilmHeader, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
+    }
+    CU_TRY(cudaMemcpyAsync(&h_nan, scratch, sizeof(unsigned), cudaMemcpyDeviceToHost, s->stream));
     CU_TRY(cudaStreamSynchronize(s->stream));
     if (nan_pixels_out) *nan_pixels_out = (int32_t)h_nan;
     return B200PT_OK;

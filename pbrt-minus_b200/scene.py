@@ -214,6 +214,13 @@ class Film:
         _check(self.lib.b200pt_film_read_srgb8(self.handle, out.ctypes.data_as(C.POINTER(C.c_uint8)), C.byref(nan)))
         return out, nan.value
 
+    def srgb8_static(self):
+        """srgb8() through b200pt_film_read_srgb8_static: no device allocation, films of at most 2,097,152 pixels"""
+        out = np.empty((self.height, self.width, 4), dtype=np.uint8)
+        nan = C.c_int32(0)
+        _check(self.lib.b200pt_film_read_srgb8_static(self.handle, out.ctypes.data_as(C.POINTER(C.c_uint8)), C.byref(nan)))
+        return out, nan.value
+
     def write_to_png(self, path):
         """Film::write_to_png (base/film.cu:57-99): sRGB-encode on the device, 8 bit; raises on NaN pixels as the reference aborts."""
         from . import png
