@@ -1217,17 +1217,17 @@ constexpr int VOL_BLOCK = 128;
 // bounds) to the light sample: march the normalised shadow ray from hit to hit, attenuating by the medium of each segment;
 // any surface with a material blocks, material-less interfaces are crossed (normal := ray direction, so the far side is
 // the interface's exterior, or whatever a plain primitive hands on).
-__device__ __forceinline__ S4 volume_transmittance(const WF &wf, V3 p0, int medium, const LightSample &ls, S4 lambda, uint2 *sm_stack,
+// p0: the scattering point (offset_ray_origin with n = 0 moves nothing, base/ray.h:30-49); pt: the light point offset towards
+// p0 (it fixes the direction of the walk); lp: the light point itself (the distances).
+__device__ __forceinline__ S4 volume_transmittance(const WF &wf, V3 p0, int medium, V3 pt, V3 lp, S4 lambda, uint2 *sm_stack,
                                                    unsigned *overflow) {
-    const float epsilon_distance = len(p0 - ls.p) * 1e-4f;
-    const V3 pf = p0; // offset_ray_origin with n = 0 moves nothing (base/ray.h:30-49)
-    const V3 pt = offset_ray_origin(ls.p, ls.err, ls.n, pf - ls.p);
-    V3 o = pf;
-    const V3 d = normalize(pt - pf);
+    const float epsilon_distance = len(p0 - lp) * 1e-4f;
+    V3 o = p0;
+    const V3 d = normalize(pt - p0);
     bool previous_self_intersection = false;
     S4 T = s4(1.f);
     for (int depth = 0; depth < 128; depth++) { // MAX_VOLUME_BOUNCES (base/integrator_base.h:21)
-        const float distance_to_light = len(ls.p - o);
+        const float distance_to_light = len(lp - o);
         const float t_max = (float)((1.0 - (double)1e-4f) * (double)distance_to_light);
         RayHit h;
         TraceCounters ctr;
@@ -1273,12 +1273,13 @@ __device__ __forceinline__ S4 volume_transmittance(const WF &wf, V3 p0, int medi
 // ray_cast clears in_volume for all of them (:361), rays inside a medium then either pass through to their hit
 // (multi_transmittance_pdf *= exp(-sigma_t t_max)) or scatter: the origin moves to the scattering point, direct light is
 // gathered THROUGH interfaces with the transmittance walk above, and a new direction is drawn from the phase function.
-// Two launches: k_volume<0> visits every traced slot, samples the free-flight distance and either lets the path pass or
-// queues it; k_volume<1> runs the scattering work (the NEE transmittance walk is a per-thread traversal) densely over that
-// queue instead of in whichever lanes of a warp happened to scatter.
+// Three launches: k_volume<0> visits every traced slot, samples the free-flight distance and either lets the path pass or
+// queues it; k_volume<1> runs the scattering work densely over that queue instead of in whichever lanes of a warp happened to
+// scatter, and leaves the NEE sample of each scattering point as a transmittance REQUEST (position i of the shadow-queue
+// arrays, which are empty at this point of a pass, plus two lanes of their own); k_transmit walks those segments from
+// interface to interface and adds the surviving light.  Round 1 ran the walk inline: 163 registers, 17 % of the warp slots.
 template <int PHASE>
 __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
-    __shared__ uint2 s_stack[PHASE == 1 ? SM_STACK * VOL_BLOCK : 1];
     if (wf.c->finished >= (unsigned long long)wf.total_paths) return;
     const unsigned n = PHASE == 0 ? (unsigned)wf.pool_size : wf.c->p[wf.parity].n_vol;
     const unsigned stride = gridDim.x * blockDim.x;
@@ -1331,6 +1332,7 @@ __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
         const S4 sigma_s = medium_sigma(wf.spectra, M.sigma_s, M.scale, lambda);
         const S4 sigma_t = medium_sigma(wf.spectra, M.sigma_a, M.scale, lambda) + sigma_s;
         Sampler s = load_sampler(wf, slot, ids);
+        bool requested = false;
         {
             const V3 o = ro + rd * t;
             S4 beta = wf.pool.beta[slot] * (sigma_s / sigma_t);
@@ -1357,16 +1359,17 @@ __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
                     else if (lt == B200PT_LIGHT_SPOT) Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * (lw * Lr.scale) / ld2;
                     else Le = spectrum_sample(wf.spectra, Lr.spectrum, lambda) * Lr.scale;
                     if (is_positive(Le) && ls.pdf != 0.f) {
-                        const S4 T = volume_transmittance(wf, o, medium, ls, lambda, s_stack + threadIdx.x, &wf.c->stack_overflow);
                         const float pdf_light = Lr.pmf * ls.pdf;
-                        const S4 contribution = Le / pdf_light * T;
                         // the phase function is SAMPLED here, not evaluated towards the light (megakernel_path.cu:247-263)
                         float ppdf;
                         (void)sample_henyey_greenstein(-rd, M.g, s.get_2d(), &ppdf);
-                        S4 Ld;
-                        if (delta) Ld = contribution * ppdf;
-                        else Ld = contribution * (power_heuristic(pdf_light, ppdf * average(T)) * ppdf);
-                        wf.pool.L[slot] = wf.pool.L[slot] + beta * Ld;
+                        const V3 pt = offset_ray_origin(ls.p, ls.err, ls.n, o - ls.p);
+                        wf.q.sh_o[i] = make_float4(o.x, o.y, o.z, __int_as_float(medium));
+                        wf.q.sh_d[i] = make_float4(pt.x, pt.y, pt.z, pdf_light);
+                        wf.q.sh_contrib[i] = make_float4(ls.p.x, ls.p.y, ls.p.z, delta ? -ppdf : ppdf);
+                        wf.q.tr_a[i] = Le / pdf_light;
+                        wf.q.tr_beta[i] = beta;
+                        requested = true;
                     }
                 }
             }
@@ -1388,9 +1391,35 @@ __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
             // not re-traced at once: the logic stage first applies russian roulette and the depth limit (:431-432)
             ids.w = (ids.w & ~PF_SPECULAR) | PF_ANY_NON_SPECULAR | PF_IN_VOLUME;
         }
+        if (!requested) wf.q.sh_o[i] = make_float4(0.f, 0.f, 0.f, __int_as_float(-2)); // medium -2: no request at this position
         ids.z = s.dimension;
         wf.pool.ids[slot] = ids;
         wf.pool.rng[slot] = s.state;
+    }
+}
+
+// the transmittance requests of k_volume<1>, one thread per scattering point of this pass
+__global__ void __launch_bounds__(VOL_BLOCK) k_transmit(WF wf) {
+    __shared__ uint2 s_stack[SM_STACK * VOL_BLOCK];
+    if (wf.c->finished >= (unsigned long long)wf.total_paths) return;
+    const unsigned n = wf.c->p[wf.parity].n_vol;
+    const unsigned stride = gridDim.x * blockDim.x;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float4 r0 = wf.q.sh_o[i];
+        const int medium = __float_as_int(r0.w);
+        if (medium < -1) continue; // no light sample at this scattering point
+        const float4 r1 = wf.q.sh_d[i], r2 = wf.q.sh_contrib[i];
+        const int slot = wf.q.vol[i];
+        const S4 lambda = wf.pool.lambda[slot];
+        const S4 T = volume_transmittance(wf, v3(r0), medium, v3(r1), v3(r2), lambda, s_stack + threadIdx.x, &wf.c->stack_overflow);
+        const float pdf_light = r1.w;
+        const bool delta = signbit(r2.w); // the phase pdf is positive: its sign carries "delta light, no MIS"
+        const float ppdf = fabsf(r2.w);
+        const S4 contribution = wf.q.tr_a[i] * T;
+        S4 Ld;
+        if (delta) Ld = contribution * ppdf;
+        else Ld = contribution * (power_heuristic(pdf_light, ppdf * average(T)) * ppdf);
+        wf.pool.L[slot] = wf.pool.L[slot] + wf.q.tr_beta[i] * Ld;
     }
 }
 
@@ -1933,10 +1962,13 @@ static int ensure_pool(b200pt_scene *s, int pool_size) {
         if ((rc = pool_alloc(r, l, n))) return rc;
     P.mtp = P.vol = nullptr;
     r->q.vol = nullptr;
+    r->q.tr_a = r->q.tr_beta = nullptr;
     if (r->n_media > 0) { // two more lanes and the scatter queue, media scenes only
         if ((rc = pool_alloc(r, &P.mtp, n))) return rc;
         if ((rc = pool_alloc(r, &P.vol, n))) return rc;
         if ((rc = pool_alloc(r, &r->q.vol, n))) return rc;
+        if ((rc = pool_alloc(r, &r->q.tr_a, n))) return rc;
+        if ((rc = pool_alloc(r, &r->q.tr_beta, n))) return rc;
     }
     P.inst = nullptr;
     if (!s->instances.empty() && (rc = pool_alloc(r, &P.inst, n))) return rc;
@@ -2152,6 +2184,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
             if (wf.has_media) {
                 k_volume<0><<<grid, VOL_BLOCK, 0, st>>>(wf);
                 k_volume<1><<<grid, VOL_BLOCK, 0, st>>>(wf);
+                k_transmit<<<grid, VOL_BLOCK, 0, st>>>(wf);
             }
             if (r->env.light >= 0) {
                 if (wf.has_media) k_logic<true, true><<<grid, WF_BLOCK, 0, st>>>(wf);
@@ -2195,7 +2228,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
             }
             if ((rc = launch_trace_wf(s, wf, true))) return rc;
             passes++;
-            launches += 4 + n_shade_kernels + (wf.has_media ? 2 : 0) + (r->n_area_lights > 0 ? 1 : 0);
+            launches += 4 + n_shade_kernels + (wf.has_media ? 3 : 0) + (r->n_area_lights > 0 ? 1 : 0);
         }
         CU_TRY(cudaGetLastError());
         const int cur = int(k & 1);

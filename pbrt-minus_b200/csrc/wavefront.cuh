@@ -107,6 +107,7 @@ struct WFQueues {
     int32_t *mat[WF_NMAT];
     int32_t *free_slots;
     int32_t *vol; // media scenes only: slots that scatter inside a medium this pass
+    S4 *tr_a, *tr_beta; // media scenes only: Le / pdf_light and beta of the transmittance request at the same queue position
     int32_t *emit; // slots whose ray hit an emissive triangle this pass
     // shadow rays: compact SoA by queue position
     float4 *sh_o, *sh_d, *sh_contrib;

@@ -23,8 +23,11 @@ def main():
     ap.add_argument("--sweep", action="store_true")
     ap.add_argument("--pool", type=int, default=0)
     ap.add_argument("--occ", default="0", help="comma list of shade_occ values to try")
+    ap.add_argument("--lib", default="", help="A/B runs: another build of libb200pt.so to load instead of the in-tree one")
     args = ap.parse_args()
     pkg = importlib.import_module("pbrt-minus_b200")
+    if args.lib:
+        pkg.api.LIB_PATH = os.path.abspath(args.lib)
     text = open(args.scene).read()
     if args.res:
         text = re.sub(r'("integer xresolution"\s*\[\s*)\d+', r"\g<1>%d" % args.res[0], text)
@@ -48,7 +51,7 @@ def main():
     for r, t, occ in [(r, t, int(o)) for r, t in configs for o in args.occ.split(",")]:
         integ.accel.tune(wf_refill=r, wf_tri_steps=t, shade_occ=occ)
         ms, st = run()
-        print(json.dumps({"wf_refill": r, "wf_tri_steps": t, "shade_occ": occ, "ms": round(ms, 3), "Msamples_s": round(st["paths"] / ms / 1e3, 1),
+        print(json.dumps({"lib": os.path.basename(args.lib) or "libb200pt.so", "mean": round(float(film.get_pixel_rgb().mean()), 6), "wf_refill": r, "wf_tri_steps": t, "shade_occ": occ, "ms": round(ms, 3), "Msamples_s": round(st["paths"] / ms / 1e3, 1),
                           "Mrays_s": round((st["rays_closest"] + st["rays_shadow"]) / ms / 1e3, 1), "passes": st["passes"],
                           "launches": st["kernel_launches"]}), flush=True)
     film.close()
