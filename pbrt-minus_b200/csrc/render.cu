@@ -1436,7 +1436,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         const bool act = i < n && wf.pool.state[i] == ST_RAY;
         const int slot = (int)i;
-        int route = -1; // route: material type, or -1
+        int route = -1, route_prim = -1, route_mat = 0; // route: material type, or -1; the hit primitive and its (resolved) material
         bool terminate = false, stay = false; // stay: the slot keeps ST_RAY (scattered in a medium / crossed an interface)
         int emit = 0; // 1: the hit triangle is emissive (k_emit adds its Le), | 2: added raw (camera ray / specular bounce)
         if (act) {
@@ -1537,9 +1537,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                         hit_triangle_interaction(wf, slot, wf.bvh.tris + 3 * (size_t)prim, hit, ro, rd, si);
                     }
                     mat = mix_hash_float(si.p, si.err, si.wo) < mr.scale ? mr.mix_a : mr.mix_b;
-                    float4 misc = wf.pool.misc[slot];
-                    misc.z = __int_as_float(mat); // the shade stage reads the resolved material from here
-                    wf.pool.misc[slot] = misc;
+                    // the resolved material travels to the shade stage in the material queue entry
                 }
                 depth += 1.f;
                 if (MEDIA) {
@@ -1547,6 +1545,8 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                     wf.pool.vol[slot] = vol;
                 }
                 route = wf.materials[mat].type;
+                route_prim = prim;
+                route_mat = mat;
             }
             if (dirty_L) wf.pool.L[slot] = L;
             if (terminate) {
@@ -1558,7 +1558,7 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
         }
         const int cat = (act && terminate) ? WF_NMAT : route; // material queue, WF_NMAT = free list, -1 nothing (the slot stays a ray)
         if (act && !stay) wf.pool.state[slot] = terminate ? ST_FREE : uint8_t(ST_MAT0 + route);
-        block_push(wf, cat, slot);
+        block_push(wf, cat, slot, make_int2(route_prim, route_mat));
         queue_push(&wf.c->p[wf.parity].n_emit, wf.q.emit, slot | ((emit & 2) ? int(0x80000000u) : 0), emit != 0);
     }
     // finished-path count: warp reduce, one atomic per warp
@@ -1766,26 +1766,26 @@ __global__ void __launch_bounds__(WF_BLOCK, OCC ? OCC : ((MAT >= B200PT_MAT_COAT
         float4 sh_o = make_float4(0, 0, 0, 0), sh_d = sh_o, sh_c = sh_o;
         if (act) {
             slot = wf.q.mat[MAT][i];
+            // the logic stage left the primitive and the material (a mix already resolved) beside the slot: every load below
+            // depends on this one queue read only
+            const int2 pm = wf.q.mat_pm[MAT][i];
+            const int prim = pm.x, mat = pm.y;
+            const MatRec m = wf.materials[mat];
             const float4 ro4 = wf.pool.ray_o[slot], rd4 = wf.pool.ray_d[slot];
             const V3 ro = v3(ro4), rd = v3(rd4);
             const float4 hit = wf.pool.hit[slot];
-            const int prim = __float_as_int(hit.x);
             Isect si;
-            int mat, prim_id = -1;
+            int prim_id = -1;
             if (prim >= (int)wf.bvh.n_tris) {
                 const SphereRec &sp = wf.spheres[prim - (int)wf.bvh.n_tris];
                 sphere_interaction(sp, ro, rd, hit.y, -rd, si);
-                mat = sp.material;
             } else {
                 const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
-                mat = int(__float_as_uint(__ldg(&tp[1].w)) & kTriMaterialMask);
                 prim_id = __float_as_int(__ldg(&tp[0].w));
                 hit_triangle_interaction(wf, slot, tp, hit, ro, rd, si);
             }
-            if (wf.has_mix && wf.materials[mat].type == B200PT_MAT_MIX) mat = __float_as_int(wf.pool.misc[slot].z);
             float4 vol = make_float4(0.f, 0.f, 0.f, 0.f); // media scenes: .y = medium of the ray that arrived here
             if (MEDIA) vol = wf.pool.vol[slot];
-            const MatRec m = wf.materials[mat];
             const S4 lambda = wf.pool.lambda[slot];
             S4 lpdf = wf.pool.lpdf[slot];
             bool lpdf_dirty = false;
@@ -1976,8 +1976,10 @@ static int ensure_pool(b200pt_scene *s, int pool_size) {
     if ((rc = pool_alloc(r, &P.ids, n))) return rc;
     if ((rc = pool_alloc(r, &P.state, n))) return rc;
     WFQueues &Q = r->q;
-    for (int m = 0; m < WF_NMAT; m++)
+    for (int m = 0; m < WF_NMAT; m++) {
         if ((rc = pool_alloc(r, &Q.mat[m], r->has_mat[m] ? n : 1))) return rc;
+        if ((rc = pool_alloc(r, &Q.mat_pm[m], r->has_mat[m] ? n : 1))) return rc;
+    }
     int32_t **qs[] = {&Q.free_slots, &Q.sh_slot, &Q.emit};
     for (int32_t **q : qs)
         if ((rc = pool_alloc(r, q, n))) return rc;

@@ -105,6 +105,8 @@ struct WFCounters {
 
 struct WFQueues {
     int32_t *mat[WF_NMAT];
+    int2 *mat_pm[WF_NMAT]; // {primitive, resolved material id} of the entry at the same position: the shade kernels start their
+                           // pool, triangle and material loads together instead of chasing slot -> hit -> triangle -> material
     int32_t *free_slots;
     int32_t *vol; // media scenes only: slots that scatter inside a medium this pass
     S4 *tr_a, *tr_beta; // media scenes only: Le / pdf_light and beta of the transmittance request at the same queue position
@@ -187,7 +189,7 @@ __device__ __forceinline__ int queue_claim(unsigned *counter, bool pred) {
 // 256-slot block land contiguously and in thread (= slot) order, with ONE atomicAdd per block and queue.  cat < 0: nothing
 // to push.  Must be called by every thread of the block (it synchronises); blockDim.x <= 1024.  Queue pointers and counters
 // are read from the kernel parameter block by index (constant bank), never through a local array.
-__device__ __forceinline__ void block_push(const WF &wf, int cat, int32_t value) {
+__device__ __forceinline__ void block_push(const WF &wf, int cat, int32_t value, int2 pm) {
     constexpr int NCAT = WF_NMAT + 1;
     __shared__ unsigned s_warp[NCAT][32];
     __shared__ unsigned s_base[NCAT];
@@ -214,7 +216,9 @@ __device__ __forceinline__ void block_push(const WF &wf, int cat, int32_t value)
     __syncthreads();
     if (cat >= 0) {
         int32_t *queue = cat < WF_NMAT ? wf.q.mat[cat] : wf.q.free_slots;
-        queue[s_base[cat] + s_warp[cat][warp] + __popc(my_ballot & ((1u << lane) - 1u))] = value;
+        const unsigned pos = s_base[cat] + s_warp[cat][warp] + __popc(my_ballot & ((1u << lane) - 1u));
+        queue[pos] = value;
+        if (cat < WF_NMAT) wf.q.mat_pm[cat][pos] = pm;
     }
     __syncthreads(); // the shared arrays are reused by the next call
 }
