@@ -285,7 +285,8 @@ int b200pt_bvh_build(b200pt_scene *scene, b200pt_build_stats *stats_out);
 int b200pt_bvh_debug_sorted(b200pt_scene *scene, int32_t *prim_order_out, uint64_t *keys_out);
 /* Structural check of the built BVH8 (all trees of the scene): out[0] = child boxes that do NOT contain what they bound (the
  * vertices of a leaf child's triangles; an inner child's own child boxes, up to that child's grid step), out[1] = triangle
- * slots referenced by leaf children (must equal n_triangles), out[2] = nodes visited.  A conservative tree has out[0] == 0. */
+ * slots referenced by leaf children (must equal n_triangles, plus n_instances in a scene with instances: the leaf records of
+ * the tree over the instance boxes are one proxy per instance), out[2] = nodes visited.  A conservative tree has out[0] == 0. */
 int b200pt_bvh_validate(b200pt_scene *scene, int64_t out[3]);
 /* Host walk statistics of the built BVH8 (node / triangle visit counts for a ray set are
  * accumulated on the device by b200pt_trace when counters_out is non-NULL). */

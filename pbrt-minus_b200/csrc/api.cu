@@ -241,6 +241,7 @@ int finish_instances(b200pt_scene *s) {
     }
     if (s->instances.empty()) return B200PT_OK;
     std::vector<InstRec> recs(s->instances.size());
+    s->inst_boxes.assign(6 * s->instances.size(), 0.f);
     for (size_t i = 0; i < recs.size(); i++) {
         const b200pt_instance &in = s->instances[i];
         const HostObject &ob = s->objects[in.object];
@@ -268,6 +269,8 @@ int finish_instances(b200pt_scene *s) {
         for (int a = 0; a < 3; a++) {
             r.box_lo[a] -= pad;
             r.box_hi[a] += pad;
+            s->inst_boxes[6 * i + a] = r.box_lo[a];
+            s->inst_boxes[6 * i + 3 + a] = r.box_hi[a];
         }
     }
     CU_TRY(cudaMalloc((void **)&s->d_instances, recs.size() * sizeof(InstRec)));

@@ -18,6 +18,7 @@
 //                       in node order and pushes the interior children on the next queue.
 #include <algorithm>
 #include <chrono>
+#include <vector>
 #include <cmath>
 #include <cstdlib>
 
@@ -778,11 +779,15 @@ struct RangeOut {
     float box[6] = {0, 0, 0, 0, 0, 0}; // bounds of the range's triangles
 };
 
+// proxies: the range is not scene geometry but the instance-box proxies (finish_instances): their own vertex / index buffers, no
+// per-triangle attributes; `first` still gives the ids written into the leaf records
 static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_base, unsigned node_capacity, unsigned leaf_base,
-                       bool keep_sorted, b200pt_build_stats &bs, RangeOut &out) {
+                       bool keep_sorted, b200pt_build_stats &bs, RangeOut &out, const float *proxy_P = nullptr,
+                       const int32_t *proxy_idx = nullptr) {
     cudaStream_t st = s->stream;
-    const float *range_P = s->d_P;
-    const int32_t *range_idx = s->d_idx + 3 * first;
+    const bool proxies = proxy_P != nullptr;
+    const float *range_P = proxies ? proxy_P : s->d_P;
+    const int32_t *range_idx = proxies ? proxy_idx : s->d_idx + 3 * first;
     // key layout: the reference's 30-bit code above a 32-bit primitive id (N <= 16 Mi), else the widest Morton
     // code that fits above ceil(log2 N) primitive-id bits; both sort as 8-byte keys with no payload
     const bool key30 = n <= (int64_t(1) << 24);
@@ -884,9 +889,9 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
         GatherArgs ga;
         ga.P = range_P;
         ga.idx = range_idx;
-        ga.tri_material = s->d_tri_material ? s->d_tri_material + first : nullptr;
-        ga.tri_light = s->d_tri_light ? s->d_tri_light + first : nullptr;
-        ga.tri_flip = s->d_tri_flip ? s->d_tri_flip + first : nullptr;
+        ga.tri_material = (s->d_tri_material && !proxies) ? s->d_tri_material + first : nullptr;
+        ga.tri_light = (s->d_tri_light && !proxies) ? s->d_tri_light + first : nullptr;
+        ga.tri_flip = (s->d_tri_flip && !proxies) ? s->d_tri_flip + first : nullptr;
         ga.prim_offset = (int32_t)first;
         k_gather_sorted<<<grid_n, tb, 0, st>>>(d_sorted_keys, n, key30 ? 0xffffffffu : uint32_t((uint64_t(1) << prim_bits) - 1), ga, d_sorted_prim,
                                                d_tri_sorted);
@@ -987,11 +992,13 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
     const auto wall0 = std::chrono::steady_clock::now();
     // ranges: the top-level triangles [0, n_top), then one range per instanced object (b200pt_scene_desc.objects)
     const int64_t n_top = s->objects.empty() ? n : s->n_top_triangles;
+    const int64_t n_inst = (int64_t)s->instances.size();
     size_t cap = size_t(n_top / 2 + 64);
     for (const auto &o : s->objects) cap += size_t(o.n_triangles / 2 + 64);
+    if (n_inst > 0) cap += size_t(n_inst / 2 + 64); // the tree over the instance boxes
     const unsigned node_capacity = unsigned(cap);
     CU_TRY(cudaMalloc(&s->d_nodes, size_t(node_capacity) * 5 * sizeof(float4)));
-    CU_TRY(cudaMalloc(&s->d_tris, size_t(n) * 3 * sizeof(float4)));
+    CU_TRY(cudaMalloc(&s->d_tris, size_t(n + n_inst) * 3 * sizeof(float4))); // + one proxy leaf record per instance
     unsigned node_base = 0;
     RangeOut ro;
     if (n_top > 0) {
@@ -1009,6 +1016,34 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
         for (int k = 0; k < 6; k++) o.box[k] = oo.box[k];
         node_base += oo.n_nodes;
     }
+    // the instance tree: one proxy triangle per instance whose bounds are the instance's padded render-space box
+    // ((lo, hi, (lo.x, hi.y, lo.z)) has exactly that AABB), built like any other range; its leaf records hold n + instance index
+    s->inst_root_node = -1;
+    if (int rc = finish_instances(s)) return rc;
+    if (n_inst > 0) {
+        std::vector<float> pv(size_t(n_inst) * 9);
+        std::vector<int32_t> pi(size_t(n_inst) * 3);
+        for (int64_t i = 0; i < n_inst; i++) {
+            const float *b = &s->inst_boxes[6 * i];
+            const float v[9] = {b[0], b[1], b[2], b[3], b[4], b[5], b[0], b[4], b[2]};
+            for (int k = 0; k < 9; k++) pv[9 * i + k] = v[k];
+            for (int k = 0; k < 3; k++) pi[3 * i + k] = int32_t(3 * i + k);
+        }
+        float *d_pv = nullptr;
+        int32_t *d_pi = nullptr;
+        CU_TRY(cudaMalloc(&d_pv, pv.size() * sizeof(float)));
+        CU_TRY(cudaMalloc(&d_pi, pi.size() * sizeof(int32_t)));
+        CU_TRY(cudaMemcpyAsync(d_pv, pv.data(), pv.size() * sizeof(float), cudaMemcpyHostToDevice, s->stream));
+        CU_TRY(cudaMemcpyAsync(d_pi, pi.data(), pi.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s->stream));
+        RangeOut io;
+        b200pt_build_stats ibs = {}; // the proxy tree's stage times are not part of the triangle build's figures
+        const int rc = build_range(s, n, n_inst, node_base, node_capacity, unsigned(n), false, ibs, io, d_pv, d_pi);
+        cudaFree(d_pv);
+        cudaFree(d_pi);
+        if (rc) return rc;
+        s->inst_root_node = (int32_t)node_base;
+        node_base += io.n_nodes;
+    }
     bs.n_bvh8_nodes = node_base;
     s->n_nodes_total = node_base;
     bs.ms_wall = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - wall0).count();
@@ -1020,7 +1055,7 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
     s->built = true;
     bs.device_bytes = int64_t(node_capacity) * 80 + n * 48 + n * 12;
     if (stats) *stats = bs;
-    return finish_instances(s);
+    return B200PT_OK;
 }
 
 } // namespace b200pt

@@ -105,6 +105,8 @@ struct b200pt_scene {
     // instancing (b200pt_scene_desc.objects / instances)
     int64_t n_top_triangles = 0;
     unsigned n_top_nodes = 0, n_nodes_total = 0;
+    int32_t inst_root_node = -1;   // root of the BVH8 over the instance boxes (proxy leaf records at [n_triangles, +n_instances))
+    std::vector<float> inst_boxes; // padded render-space box of every instance, 6 floats each (finish_instances)
     std::vector<b200pt::HostObject> objects;
     std::vector<b200pt_instance> instances;
     b200pt::InstRec *d_instances = nullptr;

@@ -2108,6 +2108,7 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     wf.n_spheres = s->n_spheres;
     wf.instances = s->d_instances;
     wf.n_instances = (int32_t)s->instances.size();
+    wf.inst_root = s->inst_root_node;
     if (wf.n_instances > 0 && r->n_media > 0) {
         set_error("b200pt_render: object instances in scenes with media are not supported");
         return B200PT_ERR_UNSUPPORTED;

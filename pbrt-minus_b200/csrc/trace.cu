@@ -357,26 +357,28 @@ __device__ __forceinline__ int next_sphere(const SphereRec *sph, int n, int k, f
     return k;
 }
 
-// first instance at or after k whose padded render-space box the ray touches; n when there is none
-__device__ __forceinline__ int next_instance(const InstRec *inst, int n, int k, V3 o, V3 d, float t_max) {
-    const float idx = safe_rcp_dir(d.x), idy = safe_rcp_dir(d.y), idz = safe_rcp_dir(d.z);
-    for (; k < n; k++) {
-        const float *lo = inst[k].box_lo, *hi = inst[k].box_hi;
-        const float x0 = (__ldg(lo) - o.x) * idx, x1 = (__ldg(hi) - o.x) * idx;
-        const float y0 = (__ldg(lo + 1) - o.y) * idy, y1 = (__ldg(hi + 1) - o.y) * idy;
-        const float z0 = (__ldg(lo + 2) - o.z) * idz, z1 = (__ldg(hi + 2) - o.z) * idz;
-        const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.f));
-        const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
-        if (tn <= tf * 1.00001f + 1e-30f) break;
-    }
-    return k;
+// does the ray (o, 1/d, [0, t_max]) touch the instance's padded render-space box?  (a leaf child of the instance tree bounds up to
+// three proxies with ONE box: each candidate is tested against its own)
+__device__ __forceinline__ bool ray_touches_instance(const InstRec &I, float ox, float oy, float oz, float idx, float idy, float idz,
+                                                     float t_max) {
+    const float *lo = I.box_lo, *hi = I.box_hi;
+    const float x0 = (__ldg(lo) - ox) * idx, x1 = (__ldg(hi) - ox) * idx;
+    const float y0 = (__ldg(lo + 1) - oy) * idy, y1 = (__ldg(hi + 1) - oy) * idy;
+    const float z0 = (__ldg(lo + 2) - oz) * idz, z1 = (__ldg(hi + 2) - oz) * idz;
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.f));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
+    return tn <= tf * 1.00001f + 1e-30f;
 }
 
-// INST: the scene has object instances (two-level traversal).  A ray first walks the top-level tree (and the quadrics); when
-// that is exhausted it visits, one after the other, every instance whose box it touches: the ray is taken into the instance's
+// INST: the scene has object instances (two-level traversal).  A ray first walks the top-level tree of the scene's own
+// triangles (and the quadrics); when that is exhausted it walks the INSTANCE TREE -- a BVH8 over the instances' padded
+// render-space boxes whose leaf records are proxies carrying the instance index -- with the same node steps.  A proxy the ray
+// touches suspends that walk (its pending groups go onto the stack, base_sp marks them), the ray is taken into the instance's
 // space with the reference's Transform::apply_inverse(Ray, &t_max) (t_max = best t so far minus the origin shift) and walks
-// the OBJECT's tree -- built once, shared by all its instances -- from that tree's root.  Hits keep the instance-space t, as
+// the OBJECT's tree -- built once, shared by all its instances -- from that tree's root; when the object tree is exhausted
+// the render-space ray comes back and the instance tree carries on.  Hits keep the instance-space t, as
 // TransformedPrimitive::intersect returns it (primitives/transformed_primitive.cu:20-34).
+// cur_inst: -1 in the scene's tree, -2 in the instance tree, >= 0 in that instance's object tree.
 template <bool SHADOW, bool SPH, bool INST>
 __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
     __shared__ uint2 sm_stack_all[SM_STACK * TRACE_BLOCK];
@@ -407,7 +409,8 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
     int sp = 0;
     float ht = 0, hb1 = 0, hb2 = 0;
     int hprim = -1;
-    int cur_inst = -1, hinst = -1; // INST: the instance whose object tree the lane is in (-1: top level); instance of the best hit
+    int cur_inst = -1, hinst = -1; // INST: where the lane is (see above); instance of the best hit
+    int base_sp = 0;               // INST: stack entries below this belong to the suspended instance-tree walk
     int sph_k = 0;      // next sphere to test for this lane's ray (n_spheres: none pending)
     int skip_prim = -1; // SHADOW: the sampled light's own triangle (the reference's three visibility rays cannot reach it)
     unsigned overflow = 0;
@@ -450,6 +453,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                     hprim = -1;
                     cur_inst = -1;
                     hinst = -1;
+                    base_sp = 0;
                     // spheres are tested as a phase of their own below, and only those whose box the ray touches
                     sph_k = (SPH && live) ? next_sphere(wf.spheres, wf.n_spheres, 0, ox, oy, oz, idx, idy, idz, ht) : wf.n_spheres;
                 }
@@ -483,7 +487,43 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                 sph_k = next_sphere(wf.spheres, wf.n_spheres, sph_k + 1, ox, oy, oz, idx, idy, idz, ht);
             }
         } else if (c_tri >= c_node) {
-            if (want_tri) {
+            if (INST && want_tri && cur_inst == -2) {
+                // a proxy of the instance tree: enter the instance if the ray touches its own box
+                const int ti = __ffs(tg.y) - 1;
+                tg.y &= tg.y - 1u;
+                const int ni = __float_as_int(__ldg(&wf.bvh.tris[3 * size_t(tg.x + ti)].w)) - int(wf.bvh.n_tris);
+                const InstRec &I = wf.instances[ni];
+                if (ray_touches_instance(I, ox, oy, oz, idx, idy, idz, ht)) {
+                    // suspend the instance-tree walk: the rest of this leaf group and of the node group wait on the stack
+                    if (tg.y != 0u) {
+                        if (sp < SM_STACK) sm_stack[sp * TRACE_BLOCK] = tg;
+                        else if (sp < SM_STACK + LOCAL_STACK) lstack[sp - SM_STACK] = tg;
+                        else overflow = 1u;
+                        sp++;
+                    }
+                    if (ng.y > 0x00ffffffu) {
+                        if (sp < SM_STACK) sm_stack[sp * TRACE_BLOCK] = ng;
+                        else if (sp < SM_STACK + LOCAL_STACK) lstack[sp - SM_STACK] = ng;
+                        else overflow = 1u;
+                        sp++;
+                    }
+                    base_sp = sp;
+                    // the best t so far is a t along the ray of the space it was found in; like the reference, it is handed to the
+                    // next primitive as it is (best_t = intersection->t_hit, accelerator/hlbvh.cu:499) and shifted by that ray's dt
+                    V3 oi, di;
+                    float dt;
+                    instance_ray(I.ifr, v3(ox, oy, oz), v3(dx, dy, dz), &oi, &di, &dt);
+                    ox = oi.x; oy = oi.y; oz = oi.z;
+                    dx = di.x; dy = di.y; dz = di.z;
+                    idx = safe_rcp_dir(di.x); idy = safe_rcp_dir(di.y); idz = safe_rcp_dir(di.z);
+                    rs = ray_shear(di.x, di.y, di.z);
+                    octinv4 = ((idx < 0.f ? 0u : 4u) | (idy < 0.f ? 0u : 2u) | (idz < 0.f ? 0u : 1u)) * 0x01010101u;
+                    ht = ht - dt;
+                    ng = make_uint2((uint32_t)I.root_node, 0x80000000u);
+                    tg = make_uint2(0u, 0u);
+                    cur_inst = ni;
+                }
+            } else if (want_tri) {
 #pragma unroll 1
                 for (int step = 0; step < tri_steps && tg.y != 0u; step++) {
                     const int ti = __ffs(tg.y) - 1;
@@ -507,13 +547,19 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
                 }
             }
         } else if (act && !want_sph && !want_tri) {
-            if (ng.y <= 0x00ffffffu && sp > 0) {
+            if (ng.y <= 0x00ffffffu && sp > (INST ? base_sp : 0)) {
                 sp--;
                 if (sp < SM_STACK) ng = sm_stack[sp * TRACE_BLOCK];
                 else if (sp < SM_STACK + LOCAL_STACK) ng = lstack[sp - SM_STACK];
                 else ng = make_uint2(0u, 0u);
+                if (INST && ng.y <= 0x00ffffffu) { // a suspended group of proxies: back to the triangle phase
+                    tg = ng;
+                    ng = make_uint2(0u, 0u);
+                }
             }
-            if (ng.y > 0x00ffffffu) {
+            if (INST && tg.y != 0u) {
+                // nothing to do in this node phase
+            } else if (ng.y > 0x00ffffffu) {
                 const uint32_t hits = ng.y;
                 const int child_bit = 31 - __clz(hits);
                 ng.y &= ~(1u << child_bit);
@@ -535,39 +581,38 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_trace_wf(WF wf) {
             } else {
                 bool retire = true;
                 if (INST && !(SHADOW && hprim >= 0)) {
-                    // this tree is exhausted: on to the next instance the ray can reach, if any
-                    float4 ro4, rd4;
-                    if (SHADOW) {
-                        ro4 = __ldg(wf.q.sh_o + ray);
-                        rd4 = __ldg(wf.q.sh_d + ray);
-                    } else {
-                        ro4 = wf.pool.ray_o[slot];
-                        rd4 = wf.pool.ray_d[slot];
-                    }
-                    const V3 ro = v3(ro4.x, ro4.y, ro4.z), rd = v3(rd4.x, rd4.y, rd4.z);
-                    const int ni = ro4.w >= 0.f ? next_instance(wf.instances, wf.n_instances, cur_inst + 1, ro, rd, ht) : wf.n_instances;
-                    if (ni < wf.n_instances) {
-                        // the best t so far is a t along the ray of the space it was found in; like the reference, it is handed to the
-                        // next primitive as it is (best_t = intersection->t_hit, accelerator/hlbvh.cu:499) and shifted by that ray's dt
-                        const InstRec &I = wf.instances[ni];
-                        V3 oi, di;
-                        float dt;
-                        instance_ray(I.ifr, ro, rd, &oi, &di, &dt);
-                        ox = oi.x; oy = oi.y; oz = oi.z;
-                        if (SPH) { dx = di.x; dy = di.y; dz = di.z; }
-                        idx = safe_rcp_dir(di.x); idy = safe_rcp_dir(di.y); idz = safe_rcp_dir(di.z);
-                        rs = ray_shear(di.x, di.y, di.z);
+                    if (cur_inst >= 0) {
+                        // the object's tree is exhausted: the render-space ray comes back and the instance tree carries on
+                        float4 ro4, rd4;
+                        if (SHADOW) {
+                            ro4 = __ldg(wf.q.sh_o + ray);
+                            rd4 = __ldg(wf.q.sh_d + ray);
+                        } else {
+                            ro4 = wf.pool.ray_o[slot];
+                            rd4 = wf.pool.ray_d[slot];
+                        }
+                        ox = ro4.x; oy = ro4.y; oz = ro4.z;
+                        dx = rd4.x; dy = rd4.y; dz = rd4.z;
+                        idx = safe_rcp_dir(dx); idy = safe_rcp_dir(dy); idz = safe_rcp_dir(dz);
+                        rs = ray_shear(dx, dy, dz);
                         octinv4 = ((idx < 0.f ? 0u : 4u) | (idy < 0.f ? 0u : 2u) | (idz < 0.f ? 0u : 1u)) * 0x01010101u;
-                        ht = ht - dt;
-                        ng = make_uint2((uint32_t)I.root_node, 0x80000000u);
-                        tg = make_uint2(0u, 0u);
-                        sp = 0;
-                        cur_inst = ni;
+                        cur_inst = -2;
+                        base_sp = 0;
                         retire = false;
+                    } else if (cur_inst == -1 && wf.inst_root >= 0) {
+                        // the scene's own tree is exhausted: on to the tree over the instances (dead paths skip it)
+                        const float w = SHADOW ? __ldg(wf.q.sh_o + ray).w : wf.pool.ray_o[slot].w;
+                        if (w >= 0.f) {
+                            ng = make_uint2((uint32_t)wf.inst_root, 0x80000000u);
+                            tg = make_uint2(0u, 0u);
+                            sp = 0;
+                            cur_inst = -2;
+                            retire = false;
+                        }
                     }
                 }
                 if (!retire) {
-                    // carries on in the instance's object tree
+                    // carries on in the instance tree
                 } else if (SHADOW) {
                     if (hprim < 0) {
                         const int s2 = __ldg(wf.q.sh_slot + ray);

@@ -128,6 +128,7 @@ struct WF {
     int32_t n_spheres;
     const InstRec *instances; // object instances: each reaches its object's BVH8 through a transformed ray
     int32_t n_instances;
+    int32_t inst_root;       // root node of the BVH8 over the instance boxes (-1: no instances)
     // per-vertex shading normals / uvs of the meshes that have them (render space; indexed through the triangle's
     // primitive id and the index buffer); null when no mesh has any
     const float *N, *uv;

@@ -296,7 +296,7 @@ def test_object_instances_match_reference(b200pt, tmp_path):
     check_against_golden(b200pt, tmp_path, "instances_96x64_64spp")
 
 
-def _instanced_scene_text(n_side=6, grid=24):
+def _instanced_scene_text(n_side=6, grid=24, spacing=1.3):
     """one bumpy blob mesh (2 * grid^2 triangles), instanced n_side^2 times under rotations, non-uniform scales and a mirror"""
     u = np.linspace(0, np.pi, grid + 1)
     v = np.linspace(0, 2 * np.pi, grid + 1)
@@ -314,13 +314,13 @@ def _instanced_scene_text(n_side=6, grid=24):
            'WorldBegin', 'Material "diffuse" "rgb reflectance" [0.6 0.6 0.6]',
            'Shape "trianglemesh" "integer indices" [0 1 2 2 3 0] "point3 P" [-8 0 -8  8 0 -8  8 0 8  -8 0 8]',
            'AttributeBegin', 'AreaLightSource "diffuse" "rgb L" [1 1 1] "float scale" [14]', 'Translate 0 6 0',
-           'Shape "trianglemesh" "integer indices" [0 2 1 0 3 2] "point3 P" [-2 0 -2  2 0 -2  2 0 2  -2 0 2]', 'AttributeEnd',
+           'Shape "trianglemesh" "integer indices" [0 1 2 0 2 3] "point3 P" [-2 0 -2  2 0 -2  2 0 2  -2 0 2]', 'AttributeEnd',
            'ObjectBegin "blob"', 'Material "conductor" "spectrum eta" ["metal-Cu-eta"] "spectrum k" ["metal-Cu-k"] "float roughness" [0.15]', mesh,
            'Material "diffuse" "rgb reflectance" [0.3 0.5 0.7]', 'Translate 0 0.55 0', 'Scale 0.4 0.4 0.4', mesh, 'ObjectEnd']
     k = 0
     for i in range(n_side):
         for j in range(n_side):
-            x, z = (i - (n_side - 1) / 2) * 1.3, (j - (n_side - 1) / 2) * 1.3
+            x, z = (i - (n_side - 1) / 2) * spacing, (j - (n_side - 1) / 2) * spacing
             out += ['AttributeBegin', 'Translate %.4f 0.45 %.4f' % (x, z), 'Rotate %d 0 1 0' % (37 * k % 360), 'Rotate %d 1 0 0' % (11 * k % 40),
                     'Scale %.3f %.3f %.3f' % (0.8 + 0.05 * (k % 5), (1.0 + 0.1 * (k % 3)) * (-1 if k % 7 == 3 else 1), 0.9),
                     'ObjectInstance "blob"', 'AttributeEnd']
@@ -350,10 +350,38 @@ def test_two_level_instancing_matches_flattened_and_shares_geometry(b200pt, tmp_
         imgs.append(film.get_pixel_rgb())
         film.close()
         integ.close()
-    assert np.isfinite(imgs[0]).all()
+    assert np.isfinite(imgs[0]).all() and imgs[1].mean() > 0.02      # a lit image
     r, f = rel_mse(imgs[0], imgs[1]), frac_close(imgs[0], imgs[1])
     assert r <= 2e-4 and f >= 0.985, (r, f)
     assert abs(imgs[0].mean() - imgs[1].mean()) <= 2e-3 * imgs[1].mean()
+
+
+def test_instance_tree_with_many_overlapping_instances(b200pt, tmp_path):
+    """1600 instances in a 40 x 40 grid at a spacing well under their size (every ray touches many instance boxes): the tree over
+    the instance boxes, its suspend / resume around each object walk and the per-proxy box test, against the flattened scene;
+    the structural check covers the instance tree (its leaf records are the proxies: n_triangles + n_instances references)."""
+    text = _instanced_scene_text(n_side=40, grid=6, spacing=0.33)
+    p = os.path.join(str(tmp_path), "inst_many.pbrt")
+    open(p, "w").write(text)
+    two = b200pt.pbrt_scene.load(p, spp=16)
+    flat = b200pt.pbrt_scene.load(p, spp=16, flatten_instances=True)
+    d2 = two.to_desc()
+    assert d2.n_instances == 1600 and d2.n_triangles == 4 + 2 * 2 * 6 * 6
+    imgs = []
+    for sc in (two, flat):
+        integ = b200pt.WavefrontPathIntegrator(sc, device=0)
+        if sc is two:
+            v = integ.accel.validate()
+            assert v["bad_boxes"] == 0 and v["triangle_refs"] == d2.n_triangles + d2.n_instances
+        film = integ.create_film()
+        integ.render(film)
+        imgs.append(film.get_pixel_rgb())
+        film.close()
+        integ.close()
+    assert np.isfinite(imgs[0]).all() and imgs[1].mean() > 0.02      # a lit image
+    r, f = rel_mse(imgs[0], imgs[1]), frac_close(imgs[0], imgs[1])
+    assert r <= 1e-3 and f >= 0.97, (r, f)
+    assert abs(imgs[0].mean() - imgs[1].mean()) <= 3e-3 * imgs[1].mean()
 
 
 def test_many_lights_statistical_gate(b200pt, tmp_path):
