@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb200pt.so")
+LIB_PATH = os.environ.get("B200PT_LIB") or os.path.join(HERE, "libb200pt.so")   # B200PT_LIB: another build of the library (A/B runs)
 
 
 class B200ptError(RuntimeError):

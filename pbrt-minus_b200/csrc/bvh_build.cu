@@ -448,6 +448,11 @@ __device__ __forceinline__ float half_area(const float4 &lo, const float4 &hi) {
     return dx * dy + dy * dz + dz * dx;
 }
 
+// One thread per BVH8 node.  What the thread keeps per child while the treelet grows is three words (node id, area, child word):
+// the child boxes are NOT kept -- 8 x 6 floats of dynamically indexed local memory per thread were 100 MB across the resident
+// threads, as much as the L2 holds, and the biggest level moved 2.6 KB of DRAM reads per node for 0.7 KB of records and
+// triangles (ncu, round 2).  The boxes are read again from the BVH2 records (cache hits: this thread fetched them a moment
+// ago) when the node box, the slot order and the quantised bytes need them; the bytes are assembled in registers in slot order.
 __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
     const int n = a.t.n;
     const int2 work = a.q_in[item];
@@ -455,16 +460,12 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
 
     int c[8];
     float area[8];
-    float clo[8][3], chi[8][3];
-    uint32_t cA[8], cB[8];
+    uint32_t cA[8];
     int cnt;
     auto load_child = [&](int slot, int id) {
         const float4 lo = a.t.rec[2 * id], hi = a.t.rec[2 * id + 1];
         c[slot] = id;
-        clo[slot][0] = lo.x; clo[slot][1] = lo.y; clo[slot][2] = lo.z;
-        chi[slot][0] = hi.x; chi[slot][1] = hi.y; chi[slot][2] = hi.z;
         cA[slot] = __float_as_uint(lo.w);
-        cB[slot] = __float_as_uint(hi.w);
         area[slot] = (id >= n - 1) ? -1.f : half_area(lo, hi);
     };
     if (root2 >= n - 1) { // single-leaf tree (n == 1)
@@ -492,21 +493,24 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
         cnt++;
     }
 
-    // triangle counts, node box (the child boxes came with the records above)
-    int tcount[8], tfirst[8];
+    // node box and triangle ranges (second read of the records)
     float nlo[3] = {kInf, kInf, kInf}, nhi[3] = {-kInf, -kInf, -kInf};
+    int tfirst[8];
+    unsigned tcount4 = 0; // 4 bits per child: 1..3 triangles, 4 = "more than 3": an interior child of the BVH8 node
     for (int i = 0; i < cnt; i++) {
-        for (int k = 0; k < 3; k++) {
-            nlo[k] = fminf(nlo[k], clo[i][k]);
-            nhi[k] = fmaxf(nhi[k], chi[i][k]);
-        }
+        const float4 lo = a.t.rec[2 * c[i]], hi = a.t.rec[2 * c[i] + 1];
+        nlo[0] = fminf(nlo[0], lo.x); nlo[1] = fminf(nlo[1], lo.y); nlo[2] = fminf(nlo[2], lo.z);
+        nhi[0] = fmaxf(nhi[0], hi.x); nhi[1] = fmaxf(nhi[1], hi.y); nhi[2] = fmaxf(nhi[2], hi.z);
+        int tc;
         if (c[i] >= n - 1) {
             tfirst[i] = c[i] - (n - 1);
-            tcount[i] = 1;
+            tc = 1;
         } else {
-            tfirst[i] = int(cB[i] & 0x3fffffffu);
-            tcount[i] = int(cB[i] >> 30) + 1; // 4 stands for "more than 3": an interior child of the BVH8 node
+            const uint32_t B = __float_as_uint(hi.w);
+            tfirst[i] = int(B & 0x3fffffffu);
+            tc = int(B >> 30) + 1;
         }
+        tcount4 |= unsigned(tc) << (4 * i);
     }
 
     // octant-ordered slots: slot s prefers the child farthest along (+-x, +-y, +-z) by the bits
@@ -515,17 +519,14 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
     // the node centre (in its own octant's slot): children are taken in the order of that norm, largest first,
     // and each gets the best slot still free -- 64 score evaluations per node instead of the 512 of a greedy
     // search over all (child, slot) pairs, with the same outcome whenever the octants do not collide.
-    int slot_of[8];
+    unsigned child_in_slot4 = 0x88888888u; // 4 bits per slot: the child in it, 8 = empty
     {
         const float pcx = 0.5f * (nlo[0] + nhi[0]), pcy = 0.5f * (nlo[1] + nhi[1]), pcz = 0.5f * (nlo[2] + nhi[2]);
-        float ccx[8], ccy[8], ccz[8], norm[8];
+        float norm[8];
         for (int i = 0; i < cnt; i++) {
-            ccx[i] = 0.5f * (clo[i][0] + chi[i][0]) - pcx;
-            ccy[i] = 0.5f * (clo[i][1] + chi[i][1]) - pcy;
-            ccz[i] = 0.5f * (clo[i][2] + chi[i][2]) - pcz;
-            const float l1 = fabsf(ccx[i]) + fabsf(ccy[i]) + fabsf(ccz[i]);
+            const float4 lo = a.t.rec[2 * c[i]], hi = a.t.rec[2 * c[i] + 1];
+            const float l1 = fabsf(0.5f * (lo.x + hi.x) - pcx) + fabsf(0.5f * (lo.y + hi.y) - pcy) + fabsf(0.5f * (lo.z + hi.z) - pcz);
             norm[i] = (l1 == l1) ? l1 : -1.f; // non-finite centroids go last
-            slot_of[i] = -1;
         }
         unsigned used_slots = 0, done = 0;
         for (int round = 0; round < cnt; round++) {
@@ -540,7 +541,8 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
                 for (int i = cnt - 1; i >= 0; i--)
                     if (!(done & (1u << i))) bi = i;
             done |= 1u << bi;
-            const float ax = ccx[bi], ay = ccy[bi], az = ccz[bi];
+            const float4 lo = a.t.rec[2 * c[bi]], hi = a.t.rec[2 * c[bi] + 1];
+            const float ax = 0.5f * (lo.x + hi.x) - pcx, ay = 0.5f * (lo.y + hi.y) - pcy, az = 0.5f * (lo.z + hi.z) - pcz;
             float best = -kInf;
             int bs = -1;
 #pragma unroll
@@ -552,25 +554,24 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
                 }
             }
             if (bs < 0) bs = __ffs(~used_slots & 0xffu) - 1; // non-finite scores: first free slot
-            slot_of[bi] = bs;
+            child_in_slot4 = (child_in_slot4 & ~(0xfu << (4 * bs))) | (unsigned(bi) << (4 * bs));
             used_slots |= 1u << bs;
         }
     }
-    int child_in_slot[8];
-    for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
-    for (int i = 0; i < cnt; i++) child_in_slot[slot_of[i]] = i;
 
     // allocate child nodes, triangle slots and queue entries
     unsigned imask = 0;
     int n_inner = 0, n_tris = 0;
+#pragma unroll
     for (int s = 0; s < 8; s++) {
-        const int i = child_in_slot[s];
-        if (i < 0) continue;
-        if (tcount[i] > 3) {
+        const unsigned i = (child_in_slot4 >> (4 * s)) & 0xfu;
+        if (i > 7u) continue;
+        const int tc = int((tcount4 >> (4 * i)) & 0xfu);
+        if (tc > 3) {
             imask |= 1u << s;
             n_inner++;
         } else {
-            n_tris += tcount[i];
+            n_tris += tc;
         }
     }
     unsigned child_base = 0, tri_base = 0, q_base = 0;
@@ -603,61 +604,61 @@ __device__ __forceinline__ void collapse_item(const CollapseArgs &a, int item) {
         inv_scale[k] = pow2_double(-ek);
     }
 
-    unsigned char meta[8], qlo[3][8], qhi[3][8];
+    // the node's byte planes, in slot order, straight into the words that are stored (third read of the records)
+    uint32_t w_meta[2] = {0u, 0u}, w_lo[3][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}}, w_hi[3][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}};
     int tri_off = 0, inner_rank = 0;
+#pragma unroll
     for (int s = 0; s < 8; s++) {
-        const int i = child_in_slot[s];
-        if (i < 0) { // empty slot: inverted box never hit
-            meta[s] = 0;
-            for (int k = 0; k < 3; k++) {
-                qlo[k][s] = 255;
-                qhi[k][s] = 0;
-            }
+        const int h = s >> 2, sh = 8 * (s & 3);
+        const unsigned i = (child_in_slot4 >> (4 * s)) & 0xfu;
+        if (i > 7u) { // empty slot: inverted box never hit (meta 0, mins 255, maxes 0)
+            for (int k = 0; k < 3; k++) w_lo[k][h] |= 255u << sh;
             continue;
         }
+        const float4 lo = a.t.rec[2 * c[i]], hi = a.t.rec[2 * c[i] + 1];
+        const float clo[3] = {lo.x, lo.y, lo.z}, chi[3] = {hi.x, hi.y, hi.z};
         for (int k = 0; k < 3; k++) {
-            const double l = ((double)clo[i][k] - (double)nlo[k]) * inv_scale[k];
-            const double h = ((double)chi[i][k] - (double)nlo[k]) * inv_scale[k];
-            int ql = (int)floor(l), qh = (int)ceil(h);
+            const double l = ((double)clo[k] - (double)nlo[k]) * inv_scale[k];
+            const double hh = ((double)chi[k] - (double)nlo[k]) * inv_scale[k];
+            int ql = (int)floor(l), qh = (int)ceil(hh);
             ql = max(0, min(255, ql));
             qh = max(0, min(255, qh));
             // exactness guard (all terms are exact in double): p + ql*2^e <= lo, p + qh*2^e >= hi
-            while (ql > 0 && (double)nlo[k] + ql * scale[k] > (double)clo[i][k]) ql--;
-            while (qh < 255 && (double)nlo[k] + qh * scale[k] < (double)chi[i][k]) qh++;
-            qlo[k][s] = (unsigned char)ql;
-            qhi[k][s] = (unsigned char)qh;
+            while (ql > 0 && (double)nlo[k] + ql * scale[k] > (double)clo[k]) ql--;
+            while (qh < 255 && (double)nlo[k] + qh * scale[k] < (double)chi[k]) qh++;
+            w_lo[k][h] |= unsigned(ql) << sh;
+            w_hi[k][h] |= unsigned(qh) << sh;
         }
+        const int tc = int((tcount4 >> (4 * i)) & 0xfu);
         if (imask & (1u << s)) {
-            meta[s] = (unsigned char)((1u << 5) | (24u + s));
+            w_meta[h] |= ((1u << 5) | (24u + s)) << sh;
             a.q_out[q_base + inner_rank] = make_int2(c[i], (int)(child_base + inner_rank));
             inner_rank++;
         } else {
-            const unsigned unary = (1u << tcount[i]) - 1u; // 1, 3, 7
-            meta[s] = (unsigned char)((unary << 5) | (unsigned)tri_off);
-            for (int k = 0; k < tcount[i]; k++) { // the leaf records exist already, in sorted order: a contiguous run moves over
+            const unsigned unary = (1u << tc) - 1u; // 1, 3, 7
+            w_meta[h] |= ((unary << 5) | (unsigned)tri_off) << sh;
+            for (int k = 0; k < tc; k++) { // the leaf records exist already, in sorted order: a contiguous run moves over
                 const float4 *src = a.tri_sorted + 3 * (size_t)(tfirst[i] + k);
                 float4 *dst = a.tris + 3 * (size_t)(tri_base + tri_off + k);
                 dst[0] = src[0];
                 dst[1] = src[1];
                 dst[2] = src[2];
             }
-            tri_off += tcount[i];
+            tri_off += tc;
         }
     }
 
-    auto pack4 = [](const unsigned char *b) -> float {
-        return __uint_as_float((unsigned)b[0] | ((unsigned)b[1] << 8) | ((unsigned)b[2] << 16) | ((unsigned)b[3] << 24));
-    };
+    auto f = [](uint32_t v) { return __uint_as_float(v); };
     const unsigned ebits = (unsigned)(e[0] + 127) | ((unsigned)(e[1] + 127) << 8) | ((unsigned)(e[2] + 127) << 16) | (imask << 24);
     float4 *dst = a.nodes + 5 * (size_t)work.y;
-    dst[0] = make_float4(nlo[0], nlo[1], nlo[2], __uint_as_float(ebits));
-    dst[1] = make_float4(__uint_as_float(child_base), __uint_as_float(tri_base), pack4(meta), pack4(meta + 4));
-    dst[2] = make_float4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
-    dst[3] = make_float4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
-    dst[4] = make_float4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
+    dst[0] = make_float4(nlo[0], nlo[1], nlo[2], f(ebits));
+    dst[1] = make_float4(f(child_base), f(tri_base), f(w_meta[0]), f(w_meta[1]));
+    dst[2] = make_float4(f(w_lo[0][0]), f(w_lo[0][1]), f(w_lo[1][0]), f(w_lo[1][1]));
+    dst[3] = make_float4(f(w_lo[2][0]), f(w_lo[2][1]), f(w_hi[0][0]), f(w_hi[0][1]));
+    dst[4] = make_float4(f(w_hi[1][0]), f(w_hi[1][1]), f(w_hi[2][0]), f(w_hi[2][1]));
 }
 
-__global__ void __launch_bounds__(128) k_collapse_level(CollapseArgs a) {
+__global__ void __launch_bounds__(128, 8) k_collapse_level(CollapseArgs a) {
     const int count = (int)a.counters[4 + a.parity];
     for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < count; item += gridDim.x * blockDim.x) collapse_item(a, item);
 }
