@@ -829,7 +829,7 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
     }
     Arena tmp;
     {
-        const size_t sz = Arena::pad(12 * 4) * 2 + Arena::pad(n * 8) + Arena::pad(256 * sort_tiles(n) * 4) +
+        const size_t sz = Arena::pad(sort_onesweep_bytes(n, n_passes)) + Arena::pad(12 * 4) * 2 + Arena::pad(n * 8) + Arena::pad(256 * sort_tiles(n) * 4) +
                           Arena::pad(sort_scan_tmp_words(n) * 4) + Arena::pad(4 * n * sizeof(float4)) + 3 * Arena::pad(n * 4) + Arena::pad(3 * n * sizeof(float4)) +
                           Arena::pad(2 * n * 4) + Arena::pad(n * 4) + 2 * Arena::pad(n * sizeof(int2)) + Arena::pad(8 * 4);
         CU_TRY(cudaMalloc(&tmp.base, sz));
@@ -847,6 +847,12 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
     sb.keys[(n_passes & 1) ^ 1] = d_keys_tmp;
     tmp.take(&sb.tile_hist, 256 * sort_tiles(n));
     tmp.take(&sb.scan_tmp, sort_scan_tmp_words(n));
+    {
+        static const int onesweep = getenv("B200PT_SORT_ONESWEEP") ? atoi(getenv("B200PT_SORT_ONESWEEP")) : 1;
+        unsigned long long *os = nullptr;
+        tmp.take(&os, (sort_onesweep_bytes(n, n_passes) + 7) / 8);
+        sb.onesweep = onesweep ? os : nullptr;
+    }
     float4 *d_tri_sorted;
     tmp.take(&d_tri_sorted, 3 * n);
     Bvh2 t;
@@ -881,7 +887,7 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
     else k_morton<false><<<grid_n, tb, 0, st>>>(range_P, range_idx, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
     CU_TRY(cudaEventRecord(ev[1], st));
     // 2. LSD radix sort (key-only)
-    const int res = radix_sort_u64(sb, n, sort_lo, sort_hi, st, &bs.sort_passes);
+    const int res = radix_sort_u64(sb, n, sort_lo, sort_hi, st, &bs.sort_passes, s->sm_count);
     if (sb.keys[res] != d_sorted_keys) {
         set_error("b200pt_bvh_build: sort ended in the wrong buffer");
         return B200PT_ERR_STATE;
