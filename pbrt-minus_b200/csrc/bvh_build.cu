@@ -58,12 +58,35 @@ __device__ __forceinline__ float3 centroid_of(const float3 &lo, const float3 &hi
                        __fmul_rn(0.5f, __fadd_rn(lo.z, hi.z)));
 }
 
+struct GatherArgs {
+    const float *P;
+    const int32_t *idx;
+    const int32_t *tri_material, *tri_light;
+    const uint8_t *tri_flip;
+    int32_t prim_offset; // global id of the range's first triangle
+};
+
+// the 48-byte leaf record {v0 | prim, v1 | material word, v2 | light} of triangle t of the range
+//   v1.w = material id | degenerate << 28 | has-normals << 29 | has-uv << 30 | flip << 31 (b200pt.h: tri_flip bits 1, 2, 0)
+__device__ __forceinline__ void write_leaf_record(const GatherArgs &g, const TriVerts &tv, int64_t t, float4 *__restrict__ rec) {
+    const uint32_t flip = g.tri_flip ? uint32_t(g.tri_flip[t]) : 0u;
+    const uint32_t mat = (g.tri_material ? (uint32_t)g.tri_material[t] : 0u) | ((flip & 1u) << 31) | ((flip & 6u) << 28) |
+                         (triangle_is_degenerate(tv.a.x, tv.a.y, tv.a.z, tv.b.x, tv.b.y, tv.b.z, tv.c.x, tv.c.y, tv.c.z) ? kTriDegenerate : 0u);
+    const int light = g.tri_light ? g.tri_light[t] : -1;
+    rec[0] = make_float4(tv.a.x, tv.a.y, tv.a.z, __int_as_float((int)t + g.prim_offset));
+    rec[1] = make_float4(tv.b.x, tv.b.y, tv.b.z, __uint_as_float(mat));
+    rec[2] = make_float4(tv.c.x, tv.c.y, tv.c.z, __int_as_float(light));
+}
+
 // red[0..5] = centroid box (min xyz, max xyz), red[6..11] = scene box; all as orderable uints
-__global__ void __launch_bounds__(256) k_centroid_bounds(const float *__restrict__ P, const int32_t *__restrict__ idx, int64_t n,
-                                                         uint32_t *__restrict__ red) {
+// The pass also writes every triangle's leaf record in PRIMITIVE order (coalesced): the Morton pass reads those instead of
+// chasing the index triples again, and the one random gather of the build (k_gather_sorted) then moves one contiguous
+// 48-byte record per triangle instead of six scattered words.
+__global__ void __launch_bounds__(256) k_centroid_bounds(GatherArgs g, int64_t n, uint32_t *__restrict__ red, float4 *__restrict__ rec_unsorted) {
     float v[12] = {kInf, kInf, kInf, -kInf, -kInf, -kInf, kInf, kInf, kInf, -kInf, -kInf, -kInf};
     for (int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; t < n; t += int64_t(gridDim.x) * blockDim.x) {
-        const TriVerts tv = load_tri(P, idx, t);
+        const TriVerts tv = load_tri(g.P, g.idx, t);
+        write_leaf_record(g, tv, t, rec_unsorted + 3 * t);
         float3 lo, hi;
         tri_bounds(tv, lo, hi);
         const float3 c = centroid_of(lo, hi);
@@ -142,12 +165,16 @@ __device__ __forceinline__ uint64_t spread21(uint64_t x) {
 // otherwise (N > 16 Mi): key = morton(3 * axis_bits) << prim_bits | prim, axis_bits = (64 - prim_bits) / 3 <= 21 --
 // still one 8-byte key-only sort, over 3 * axis_bits bits instead of 63 bits + a 4-byte payload.
 template <bool KEY30>
-__global__ void __launch_bounds__(256) k_morton(const float *__restrict__ P, const int32_t *__restrict__ idx, int64_t n,
+__global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ rec_unsorted, int64_t n,
                                                 const float *__restrict__ boxes, uint64_t *__restrict__ keys, int axis_bits,
                                                 int prim_bits) {
     const int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (t >= n) return;
-    const TriVerts tv = load_tri(P, idx, t);
+    const float4 r0 = rec_unsorted[3 * t], r1 = rec_unsorted[3 * t + 1], r2 = rec_unsorted[3 * t + 2];
+    TriVerts tv;
+    tv.a = make_float3(r0.x, r0.y, r0.z);
+    tv.b = make_float3(r1.x, r1.y, r1.z);
+    tv.c = make_float3(r2.x, r2.y, r2.z);
     float3 lo, hi;
     tri_bounds(tv, lo, hi);
     const float3 c = centroid_of(lo, hi);
@@ -178,31 +205,22 @@ __global__ void __launch_bounds__(256) k_morton(const float *__restrict__ P, con
     }
 }
 
-// The ONE random gather of the build: sorted position k -> primitive -> index triple -> vertices and per-triangle ids, written
-// as the 48-byte leaf record {v0 | prim, v1 | material word, v2 | light} in SORTED order.  The refit reads its leaf boxes from
+// The ONE random gather of the build: sorted position k -> primitive -> its 48-byte leaf record (written in primitive order by
+// k_centroid_bounds), moved to SORTED order.  The refit reads its leaf boxes from
 // these records and the collapse copies them into BVH8 leaf order, both as contiguous runs.
 //   v1.w = material id | degenerate << 28 | has-normals << 29 | has-uv << 30 | flip << 31 (b200pt.h: tri_flip bits 1, 2, 0)
-struct GatherArgs {
-    const float *P;
-    const int32_t *idx;
-    const int32_t *tri_material, *tri_light;
-    const uint8_t *tri_flip;
-    int32_t prim_offset; // global id of the range's first triangle
-};
-__global__ void __launch_bounds__(256) k_gather_sorted(const uint64_t *__restrict__ keys, int64_t n, uint32_t mask, GatherArgs g,
-                                                       uint32_t *__restrict__ prims, float4 *__restrict__ rec) {
+__global__ void __launch_bounds__(256) k_gather_sorted(const uint64_t *__restrict__ keys, int64_t n, uint32_t mask,
+                                                       const float4 *__restrict__ rec_unsorted, uint32_t *__restrict__ prims,
+                                                       float4 *__restrict__ rec) {
     const int64_t k = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (k >= n) return;
     const uint32_t prim = uint32_t(keys[k]) & mask;
     prims[k] = prim;
-    const TriVerts tv = load_tri(g.P, g.idx, prim);
-    const uint32_t flip = g.tri_flip ? uint32_t(g.tri_flip[prim]) : 0u;
-    const uint32_t mat = (g.tri_material ? (uint32_t)g.tri_material[prim] : 0u) | ((flip & 1u) << 31) | ((flip & 6u) << 28) |
-                         (triangle_is_degenerate(tv.a.x, tv.a.y, tv.a.z, tv.b.x, tv.b.y, tv.b.z, tv.c.x, tv.c.y, tv.c.z) ? kTriDegenerate : 0u);
-    const int light = g.tri_light ? g.tri_light[prim] : -1;
-    rec[3 * k] = make_float4(tv.a.x, tv.a.y, tv.a.z, __int_as_float((int)prim + g.prim_offset));
-    rec[3 * k + 1] = make_float4(tv.b.x, tv.b.y, tv.b.z, __uint_as_float(mat));
-    rec[3 * k + 2] = make_float4(tv.c.x, tv.c.y, tv.c.z, __int_as_float(light));
+    const float4 *src = rec_unsorted + 3 * size_t(prim);
+    const float4 a = __ldg(src), b = __ldg(src + 1), c = __ldg(src + 2);
+    rec[3 * k] = a;
+    rec[3 * k + 1] = b;
+    rec[3 * k + 2] = c;
 }
 
 // ------------------------------------------------------------------------ BVH2 (build only)
@@ -830,7 +848,7 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
     Arena tmp;
     {
         const size_t sz = Arena::pad(sort_onesweep_bytes(n, n_passes)) + Arena::pad(12 * 4) * 2 + Arena::pad(n * 8) + Arena::pad(256 * sort_tiles(n) * 4) +
-                          Arena::pad(sort_scan_tmp_words(n) * 4) + Arena::pad(4 * n * sizeof(float4)) + 3 * Arena::pad(n * 4) + Arena::pad(3 * n * sizeof(float4)) +
+                          Arena::pad(sort_scan_tmp_words(n) * 4) + Arena::pad(4 * n * sizeof(float4)) + 3 * Arena::pad(n * 4) + 2 * Arena::pad(3 * n * sizeof(float4)) +
                           Arena::pad(2 * n * 4) + Arena::pad(n * 4) + 2 * Arena::pad(n * sizeof(int2)) + Arena::pad(8 * 4);
         CU_TRY(cudaMalloc(&tmp.base, sz));
         tmp.size = sz;
@@ -853,8 +871,9 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
         tmp.take(&os, (sort_onesweep_bytes(n, n_passes) + 7) / 8);
         sb.onesweep = onesweep ? os : nullptr;
     }
-    float4 *d_tri_sorted;
+    float4 *d_tri_sorted, *d_tri_unsorted;
     tmp.take(&d_tri_sorted, 3 * n);
+    tmp.take(&d_tri_unsorted, 3 * n);
     Bvh2 t;
     t.n = int32_t(n);
     tmp.take(&t.rec, 4 * n);
@@ -881,10 +900,17 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
     CU_TRY(cudaEventRecord(ev[0], st));
     // 1. centroid box + Morton keys
     k_init_reduction<<<1, 32, 0, st>>>(d_red);
-    k_centroid_bounds<<<std::min<int64_t>(grid_n, s->sm_count * 16), tb, 0, st>>>(range_P, range_idx, n, d_red);
+    GatherArgs ga;
+    ga.P = range_P;
+    ga.idx = range_idx;
+    ga.tri_material = (s->d_tri_material && !proxies) ? s->d_tri_material + first : nullptr;
+    ga.tri_light = (s->d_tri_light && !proxies) ? s->d_tri_light + first : nullptr;
+    ga.tri_flip = (s->d_tri_flip && !proxies) ? s->d_tri_flip + first : nullptr;
+    ga.prim_offset = (int32_t)first;
+    k_centroid_bounds<<<std::min<int64_t>(grid_n, s->sm_count * 16), tb, 0, st>>>(ga, n, d_red, d_tri_unsorted);
     k_cubify<<<1, 1, 0, st>>>(d_red, d_boxes);
-    if (key30) k_morton<true><<<grid_n, tb, 0, st>>>(range_P, range_idx, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
-    else k_morton<false><<<grid_n, tb, 0, st>>>(range_P, range_idx, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
+    if (key30) k_morton<true><<<grid_n, tb, 0, st>>>(d_tri_unsorted, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
+    else k_morton<false><<<grid_n, tb, 0, st>>>(d_tri_unsorted, n, d_boxes, sb.keys[0], axis_bits, prim_bits);
     CU_TRY(cudaEventRecord(ev[1], st));
     // 2. LSD radix sort (key-only)
     const int res = radix_sort_u64(sb, n, sort_lo, sort_hi, st, &bs.sort_passes, s->sm_count);
@@ -892,17 +918,8 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
         set_error("b200pt_bvh_build: sort ended in the wrong buffer");
         return B200PT_ERR_STATE;
     }
-    {
-        GatherArgs ga;
-        ga.P = range_P;
-        ga.idx = range_idx;
-        ga.tri_material = (s->d_tri_material && !proxies) ? s->d_tri_material + first : nullptr;
-        ga.tri_light = (s->d_tri_light && !proxies) ? s->d_tri_light + first : nullptr;
-        ga.tri_flip = (s->d_tri_flip && !proxies) ? s->d_tri_flip + first : nullptr;
-        ga.prim_offset = (int32_t)first;
-        k_gather_sorted<<<grid_n, tb, 0, st>>>(d_sorted_keys, n, key30 ? 0xffffffffu : uint32_t((uint64_t(1) << prim_bits) - 1), ga, d_sorted_prim,
-                                               d_tri_sorted);
-    }
+    k_gather_sorted<<<grid_n, tb, 0, st>>>(d_sorted_keys, n, key30 ? 0xffffffffu : uint32_t((uint64_t(1) << prim_bits) - 1), d_tri_unsorted,
+                                           d_sorted_prim, d_tri_sorted);
     CU_TRY(cudaEventRecord(ev[2], st));
     // 3. hierarchy emission
     CU_TRY(cudaMemsetAsync(t.arrive, 0, n * sizeof(uint32_t), st));
