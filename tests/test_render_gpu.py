@@ -148,6 +148,17 @@ def test_emissive_spheres_match_reference(b200pt, tmp_path):
     check_against_golden(b200pt, tmp_path, "spherelight_96x64_1024spp")
 
 
+def test_occluders_inside_the_visibility_margins_match_reference(b200pt, tmp_path):
+    """The reference decides visibility with three traversals (IntegratorBase::unoccluded: an any-hit ray of length 0.6 from
+    either end; compute_transmittance: a normalised ray that stops 1e-4 of the distance short of the light,
+    base/integrator_base.cu:12-71); here ONE any-hit ray covers the segment and skips the sampled light's own primitive.
+    tests/scenes/occluders.pbrt puts geometry where the two could part: a sheet 1e-4 under the light, a fin touching the light, a
+    box hovering 1e-4 above the floor, a wall standing exactly on it, a second floor layer 2e-4 above the first.  Measured:
+    relMSE 4.7e-7 at 64 spp, 1.4e-7 at 1024 spp, >= 99.97 % of the pixels within 1 % (bounds: 10x, tolerances.json)."""
+    check_against_golden(b200pt, tmp_path, "occluders_96x64_64spp")
+    check_against_golden(b200pt, tmp_path, "occluders_96x64_1024spp")
+
+
 def test_cornell_480x270_converged_4096spp(b200pt, tmp_path):
     """config C3's image between the 48x48 golden and full HD: 480x270 at 4096 spp against the reference's film, relMSE +
     the per-pixel 3 sigma gate (sigma_p from 16 disjoint sample ranges of ours, which also exercises the sample partition)"""

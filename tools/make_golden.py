@@ -74,6 +74,9 @@ CASES = [
     # planar / spherical / cylindrical texture mappings, float textures on conductor / dielectric roughness
     ("textures2_96x64_64spp", "textures2.pbrt", None, 64, None, None),
     ("textures2_96x64_1024spp", "textures2.pbrt", None, 1024, None, None),
+    # occluders inside the margins of the reference's three-ray visibility test (base/integrator_base.cu:12-71)
+    ("occluders_96x64_64spp", "occluders.pbrt", None, 64, None, None),
+    ("occluders_96x64_1024spp", "occluders.pbrt", None, 1024, None, None),
 ]
 
 
