@@ -241,11 +241,11 @@ struct Bvh2 {
 __device__ __forceinline__ int bvh2_left(uint32_t A, int n) { return int(A & 0x3fffffffu) + ((A & 0x40000000u) ? n - 1 : 0); }
 __device__ __forceinline__ int bvh2_right(uint32_t A, int n) { return int(A & 0x3fffffffu) + 1 + ((A & 0x80000000u) ? n - 1 : 0); }
 
+// length of the common prefix of keys i and j.  The keys carry the primitive id in their low bits, so no two are equal and the
+// usual index tie-break is not needed (the kernel is issue-bound: every instruction of this function counts ~13 times per node).
 __device__ __forceinline__ int delta_fn(const uint64_t *__restrict__ keys, int n, int i, uint64_t ki, int j) {
-    if (j < 0 || j >= n) return -1;
-    const uint64_t kj = keys[j];
-    if (ki == kj) return 64 + __clz(i ^ j);
-    return __clzll((long long)(ki ^ kj));
+    if ((unsigned)j >= (unsigned)n) return -1;
+    return __clzll((long long)(ki ^ __ldg(keys + j)));
 }
 
 // Binary radix tree over sorted keys, one thread per interior node (every split is the highest
