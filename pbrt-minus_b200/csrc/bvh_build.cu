@@ -84,8 +84,7 @@ __device__ __forceinline__ void write_leaf_record(const GatherArgs &g, const Tri
 // 48-byte record per triangle instead of six scattered words.
 __global__ void __launch_bounds__(256) k_centroid_bounds(GatherArgs g, int64_t n, uint32_t *__restrict__ red, float4 *__restrict__ rec_unsorted) {
     float v[12] = {kInf, kInf, kInf, -kInf, -kInf, -kInf, kInf, kInf, kInf, -kInf, -kInf, -kInf};
-    for (int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; t < n; t += int64_t(gridDim.x) * blockDim.x) {
-        const TriVerts tv = load_tri(g.P, g.idx, t);
+    auto take = [&](const TriVerts &tv, int64_t t) {
         write_leaf_record(g, tv, t, rec_unsorted + 3 * t);
         float3 lo, hi;
         tri_bounds(tv, lo, hi);
@@ -94,7 +93,16 @@ __global__ void __launch_bounds__(256) k_centroid_bounds(GatherArgs g, int64_t n
         v[3] = fmaxf(v[3], c.x); v[4] = fmaxf(v[4], c.y); v[5] = fmaxf(v[5], c.z);
         v[6] = fminf(v[6], lo.x); v[7] = fminf(v[7], lo.y); v[8] = fminf(v[8], lo.z);
         v[9] = fmaxf(v[9], hi.x); v[10] = fmaxf(v[10], hi.y); v[11] = fmaxf(v[11], hi.z);
+    };
+    // two triangles per trip: both index -> vertex chains are in flight before either is used
+    const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+    int64_t t = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    for (; t + stride < n; t += 2 * stride) {
+        const TriVerts ta = load_tri(g.P, g.idx, t), tb = load_tri(g.P, g.idx, t + stride);
+        take(ta, t);
+        take(tb, t + stride);
     }
+    if (t < n) take(load_tri(g.P, g.idx, t), t);
 #pragma unroll
     for (int k = 0; k < 12; k++) {
         const bool is_min = (k % 6) < 3;
