@@ -2092,7 +2092,9 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     CU_TRY(cudaSetDevice(s->device));
     const long long n_pixels = (long long)r->width * r->height;
     const long long total = n_pixels * (opts->sample_end - opts->sample_begin);
-    int pool_size = opts->pool_size > 0 ? opts->pool_size : (1 << 21);
+    // default pool: 16 Mi slots (about 5 GB of the 180): passes over a bigger pool have shorter tails and fewer launches --
+    // C3's shape 622 -> 683 Msamples/s against the 2 Mi of round 1, nothing more beyond 16 Mi (tools/render_probe.py --pool)
+    int pool_size = opts->pool_size > 0 ? opts->pool_size : (1 << 24);
     pool_size = (int)std::min<long long>(pool_size, std::max<long long>(total, 1024));
     pool_size = (pool_size + 31) & ~31;
     int rc = ensure_pool(s, pool_size);
