@@ -43,10 +43,18 @@
 #include <pbrt/cameras/perspective.h>
 #include <pbrt/integrators/wavefront_path.h>
 #include <pbrt/lights/diffuse_area_light.h>
+#include <pbrt/lights/distant_light.h>
+#include <pbrt/lights/spot_light.h>
+#include <pbrt/lights/uniform_infinite_light.h>
+#include <pbrt/materials/coated_conductor_material.h>
+#include <pbrt/materials/coated_diffuse_material.h>
 #include <pbrt/materials/conductor_material.h>
 #include <pbrt/materials/dielectric_material.h>
 #include <pbrt/materials/diffuse_material.h>
 #include <pbrt/materials/diffuse_transmission_material.h>
+#include <pbrt/materials/mix_material.h>
+#include <pbrt/medium/homogeneous_medium.h>
+#include <pbrt/medium/medium_interface.h>
 #include <pbrt/primitives/geometric_primitive.h>
 #include <pbrt/primitives/simple_primitive.h>
 #include <pbrt/shapes/disk.h>
@@ -152,6 +160,41 @@ struct B200ptBridge {
         }
     }
 
+    // ---- media (medium/homogeneous_medium.{h,cu}): sigma_a / sigma_s are DenselySampledSpectrum(spec, scale) already -- handed over
+    // as dense tables with scale 1 (the device reads the two integer-wavelength entries and lerps, exactly as from spec * scale)
+    std::vector<b200pt_medium> media;
+    std::map<const Medium *, int> medium_ids;
+    int dense_spectrum(const DenselySampledSpectrum *d) {
+        b200pt_spectrum o = {};
+        o.type = B200PT_SPEC_DENSE;
+        o.n = 471;
+        std::vector<float> v(471);
+        for (int l = 360; l <= 830; l++) v[l - 360] = (float)(*d)((Real)l);
+        spectrum_store.push_back(v);
+        spectra.push_back(o);
+        return (int)spectra.size() - 1;
+    }
+    int medium(const Medium *m) {
+        if (!m) return -1;
+        auto it = medium_ids.find(m);
+        if (it != medium_ids.end()) return it->second;
+        b200pt_medium o = {};
+        o.sigma_a = dense_spectrum(m->sigma_a);
+        o.sigma_s = dense_spectrum(m->sigma_s);
+        o.scale = 1.f;
+        o.g = (float)m->phase.g;
+        media.push_back(o);
+        medium_ids[m] = (int)media.size() - 1;
+        return (int)media.size() - 1;
+    }
+    // the per-triangle medium word of b200pt_scene_desc.tri_medium
+    uint32_t medium_code(bool geometric, const MediumInterface *mi) {
+        if (!geometric) return 0u; // SimplePrimitive: the spawned ray keeps the incoming ray's medium
+        if (mi && mi->interior != mi->exterior) return uint32_t(medium(mi->interior) + 1) | (uint32_t(medium(mi->exterior) + 1) << 16);
+        return 0xffffffffu;        // GeometricPrimitive without a transition: no medium
+    }
+    int interface_material = -1;
+
     int constant_texture(const SpectrumTexture *t) {
         if (!t) return -1;
         if (t->type != SpectrumTexture::Type::constant) refuse("a non-constant spectrum texture");
@@ -167,7 +210,17 @@ struct B200ptBridge {
     std::vector<b200pt_material> materials;
     std::map<const Material *, int> material_ids;
     int material(const Material *m) {
-        if (!m) refuse("a primitive without a material (medium interface)");
+        if (!m) { // Material "interface": no material at all, the surface only separates media (base/material.cu:34-36)
+            if (interface_material < 0) {
+                b200pt_material o = {};
+                o.type = B200PT_MAT_INTERFACE;
+                o.reflectance = o.eta = o.k = o.transmittance = o.albedo = o.c_eta = o.c_k = -1;
+                o.remap_roughness = 1;
+                materials.push_back(o);
+                interface_material = (int)materials.size() - 1;
+            }
+            return interface_material;
+        }
         auto it = material_ids.find(m);
         if (it != material_ids.end()) return it->second;
         b200pt_material o = {};
@@ -208,7 +261,56 @@ struct B200ptBridge {
             o.scale = (float)p->scale;
             break;
         }
-        default: refuse("a coated / mix material");
+        case Material::Type::coated_diffuse: { // materials/coated_diffuse_material.cu:9-51
+            const auto *p = static_cast<const CoatedDiffuseMaterial *>(m->ptr);
+            o.type = B200PT_MAT_COATED_DIFFUSE;
+            o.reflectance = constant_texture(p->reflectance);
+            o.albedo = constant_texture(p->albedo);
+            o.eta = spectrum(p->eta);
+            o.u_roughness = constant_float(p->u_roughness);
+            o.v_roughness = constant_float(p->v_roughness);
+            o.thickness = constant_float(p->thickness);
+            o.g = constant_float(p->g);
+            o.remap_roughness = p->remapRoughness ? 1 : 0;
+            o.max_depth = p->maxDepth;
+            o.n_samples = p->nSamples;
+            break;
+        }
+        case Material::Type::coated_conductor: { // materials/coated_conductor_material.cu:26-90
+            const auto *p = static_cast<const CoatedConductorMaterial *>(m->ptr);
+            o.type = B200PT_MAT_COATED_CONDUCTOR;
+            o.eta = spectrum(p->interfaceEta);
+            o.u_roughness = constant_float(p->interfaceURoughness);
+            o.v_roughness = constant_float(p->interfaceVRoughness);
+            o.thickness = constant_float(p->thickness);
+            o.g = constant_float(p->g);
+            o.albedo = constant_texture(p->albedo);
+            o.c_u_roughness = constant_float(p->conductorURoughness);
+            o.c_v_roughness = constant_float(p->conductorVRoughness);
+            if (p->reflectance) o.reflectance = constant_texture(p->reflectance);
+            else {
+                o.c_eta = constant_texture(p->conductorEta);
+                o.c_k = constant_texture(p->k);
+            }
+            o.remap_roughness = p->remapRoughness ? 1 : 0;
+            o.max_depth = p->maxDepth;
+            o.n_samples = p->nSamples;
+            break;
+        }
+        case Material::Type::mix: { // materials/mix_material.cu: resolved per hit by a hash of the hit point
+            const auto *p = static_cast<const MixMaterial *>(m->ptr);
+            o.type = B200PT_MAT_MIX;
+            o.scale = (float)p->amount;
+            // the slot is taken before the two inputs are converted, so that material ids stay in creation order
+            materials.push_back(o);
+            const int self = (int)materials.size() - 1;
+            material_ids[m] = self;
+            const int a = material(p->materials[0]), bb = material(p->materials[1]);
+            materials[self].mix_a = a;
+            materials[self].mix_b = bb;
+            return self;
+        }
+        default: refuse("a material type the bridge does not know");
         }
         materials.push_back(o);
         material_ids[m] = (int)materials.size() - 1;
@@ -219,11 +321,12 @@ struct B200ptBridge {
     std::vector<float> P, N, UV;
     std::vector<int32_t> indices, tri_material, tri_light;
     std::vector<uint8_t> tri_flip;
+    std::vector<uint32_t> tri_medium;
     std::vector<b200pt_sphere> spheres;
     std::map<const Shape *, int> triangle_of_shape, sphere_of_shape;
     bool any_n = false, any_uv = false;
 
-    void add_shape(const Shape *shape, const Material *mat) {
+    void add_shape(const Shape *shape, const Material *mat, uint32_t mcode) {
         const int mid = material(mat);
         if (shape->type == Shape::Type::triangle) {
             const auto *tri = static_cast<const Triangle *>(shape->ptr);
@@ -242,11 +345,13 @@ struct B200ptBridge {
             any_n |= mesh->n != nullptr;
             any_uv |= mesh->uv != nullptr;
             tri_material.push_back(mid);
+            tri_medium.push_back(mcode);
             tri_light.push_back(-1);
             tri_flip.push_back((uint8_t)(((mesh->reverse_orientation ^ mesh->transform_swaps_handedness) ? 1 : 0) | (mesh->n ? 2 : 0) |
                                          (mesh->uv ? 4 : 0)));
             return;
         }
+        if (mcode != 0u && mcode != 0xffffffffu) refuse("a sphere or disk on a medium transition");
         b200pt_sphere s = {};
         s.material = mid;
         s.light = -1;
@@ -287,6 +392,7 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
         const Shape *shape = nullptr;
         const Material *mat = nullptr;
         const Light *area = nullptr;
+        uint32_t mcode = 0u;
         if (prim->type == Primitive::Type::simple) {
             const auto *sp = static_cast<const SimplePrimitive *>(prim->ptr);
             shape = sp->shape;
@@ -296,11 +402,11 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
             shape = gp->shape_ptr;
             mat = gp->material;
             area = gp->area_light;
-            if (gp->medium_interface) refuse("a MediumInterface");
+            mcode = b.medium_code(true, gp->medium_interface);
         } else {
             refuse("an ObjectInstance");
         }
-        b.add_shape(shape, mat);
+        b.add_shape(shape, mat, mcode);
         if (area) {
             const int li = light_ids.at(area);
             if (area->type != Light::Type::diffuse_area_light) refuse("an area light that is not a DiffuseAreaLight");
@@ -323,12 +429,46 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
             lights[li] = L;
         }
     }
-    for (size_t i = 0; i < sb.gpu_lights.size(); i++)
-        if (sb.gpu_lights[i]->type != Light::Type::diffuse_area_light) refuse("a LightSource (distant / infinite / spot)");
+    // LightSource lights (base/light.cu:22-75): the constructors have folded from / to / scale / power / illuminance into
+    // render_from_light and `scale` already
+    for (size_t i = 0; i < sb.gpu_lights.size(); i++) {
+        const Light *lt = sb.gpu_lights[i];
+        if (lt->type == Light::Type::diffuse_area_light) continue;
+        b200pt_light L = {};
+        L.triangle = -1;
+        L.image = -1;
+        if (lt->type == Light::Type::distant_light) { // lights/distant_light.cu:10-41: the light shines along -render_from_light(0,0,1)
+            const auto *d = static_cast<const DistantLight *>(lt->ptr);
+            L.type = B200PT_LIGHT_DISTANT;
+            L.spectrum = b.spectrum(d->Lemit);
+            L.scale = (float)d->scale;
+            for (int r = 0; r < 3; r++) L.v[r] = (float)d->render_from_light.m.val[r][2];
+        } else if (lt->type == Light::Type::uniform_infinite_light) { // lights/uniform_infinite_light.cu:7-32
+            const auto *u = static_cast<const UniformInfiniteLight *>(lt->ptr);
+            L.type = B200PT_LIGHT_UNIFORM_INFINITE;
+            L.spectrum = b.spectrum(u->Lemit);
+            L.scale = (float)u->scale;
+        } else if (lt->type == Light::Type::spot_light) { // lights/spot_light.cu:8-41
+            const auto *sp = static_cast<const SpotLight *>(lt->ptr);
+            L.type = B200PT_LIGHT_SPOT;
+            L.spectrum = b.spectrum(sp->i_emit);
+            L.scale = (float)sp->scale;
+            for (int r = 0; r < 3; r++) {
+                L.v[r] = (float)sp->render_from_light.m.val[r][3];
+                for (int c = 0; c < 3; c++) L.light_from_render[3 * r + c] = (float)sp->render_from_light.inv_m.val[r][c];
+            }
+            L.cos_falloff_start = (float)sp->cosFalloffStart;
+            L.cos_falloff_end = (float)sp->cosFalloffEnd;
+        } else {
+            refuse("an image infinite light");
+        }
+        lights[i] = L;
+    }
 
     // camera (cameras/perspective.cu:7-63), pixel filter tabulated as FilterSampler's constructor does (filters/filter_sampler.cu:4-20)
     b200pt_camera cam = {};
     cam.medium = -1;
+    cuda::std::visit([&](auto &x) { cam.medium = b.medium(x.camera_base.medium); }, *sb.integrator_base->camera);
     cuda::std::visit(
         [&](auto &x) {
             matrix16(x.camera_from_raster, false, cam.camera_from_raster);
@@ -377,8 +517,22 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
     d.spheres = b.spheres.data();
     d.n_spectra = (int32_t)b.spectra.size();
     d.spectra = b.spectra.data();
+    d.n_media = (int32_t)b.media.size();
+    d.media = b.media.data();
+    d.tri_medium = b.media.empty() ? nullptr : b.tri_medium.data();
     d.n_materials = (int32_t)b.materials.size();
     d.materials = b.materials.data();
+    if (getenv("B200PT_BRIDGE_DUMP")) { // what the bridge read out of the reference's objects, for comparisons with the Python front-end
+        for (size_t i = 0; i < b.materials.size(); i++) {
+            const b200pt_material &m = b.materials[i];
+            fprintf(stderr, "material %zu: type %d refl %d eta %d k %d ur %g vr %g remap %d trans %d scale %g thick %g g %g albedo %d depth %d ns %d cur %g cvr %g ceta %d ck %d mix %d %d\n",
+                    i, m.type, m.reflectance, m.eta, m.k, m.u_roughness, m.v_roughness, m.remap_roughness, m.transmittance, m.scale, m.thickness,
+                    m.g, m.albedo, m.max_depth, m.n_samples, m.c_u_roughness, m.c_v_roughness, m.c_eta, m.c_k, m.mix_a, m.mix_b);
+        }
+        for (size_t i = 0; i < b.spectra.size(); i++)
+            fprintf(stderr, "spectrum %zu: type %d c %g %g %g %g n %d\n", i, b.spectra[i].type, b.spectra[i].c[0], b.spectra[i].c[1], b.spectra[i].c[2],
+                    b.spectra[i].c[3], b.spectra[i].n);
+    }
     d.n_lights = (int32_t)lights.size();
     d.lights = lights.data();
     d.camera = &cam;
