@@ -11,11 +11,13 @@
 //     b200pt_scene_create -> b200pt_bvh_build           (replaces HLBVH::HLBVH,                    scene_builder.cu:912)
 //     b200pt_film_create  -> b200pt_render              (replaces WavefrontPathIntegrator::render,  :1041)
 //     b200pt_film_read_srgb8 / b200pt_film_read          (replaces Film::write_to_png's pixel loop,  base/film.cu:57-99)
-// What it carries over: triangle meshes (with normals / uvs), spheres and disks, diffuse / conductor / dielectric /
-// diffusetransmission materials with constant textures, every reference spectrum class, diffuse area lights on triangles and
-// spheres, the perspective camera, any pixel filter (tabulated through Filter::evaluate), the RGB film.  Anything else
-// (instances, media, image textures, the other light types) is refused with a message naming it: the Python front-end
-// (pbrt-minus_b200/pbrt_scene.py) covers those.
+// What it carries over: triangle meshes (with normals / uvs), spheres and disks, every material type (diffuse, conductor,
+// dielectric, diffusetransmission, coateddiffuse, coatedconductor, mix, interface) with constant textures, every reference
+// spectrum class, diffuse area lights on triangles and spheres, LightSource distant / uniform infinite / spot, homogeneous
+// media with MediumInterface and the camera medium, object instances (triangle objects), the perspective camera, any pixel
+// filter (tabulated through Filter::evaluate), the RGB film.  Anything else (non-constant textures, the image infinite light,
+// quadrics inside instanced objects) is refused with a message naming it: the Python front-end (pbrt-minus_b200/pbrt_scene.py)
+// covers those.
 //
 // Built by oracle/ref_build/build_ref.py into oracle/_ref/pbrt-minus-b200 (it links the reference's objects, so it lives with
 // them); exercised by tests/test_bridge_gpu.py.
@@ -57,6 +59,8 @@
 #include <pbrt/medium/medium_interface.h>
 #include <pbrt/primitives/geometric_primitive.h>
 #include <pbrt/primitives/simple_primitive.h>
+#include <pbrt/primitives/transformed_primitive.h>
+#include <pbrt/accelerator/hlbvh.h>
 #include <pbrt/shapes/disk.h>
 #include <pbrt/shapes/sphere.h>
 #include <pbrt/shapes/triangle.h>
@@ -387,6 +391,9 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
     for (size_t i = 0; i < sb.gpu_lights.size(); i++) light_ids[sb.gpu_lights[i]] = (int)i;
     std::vector<b200pt_light> lights(sb.gpu_lights.size());
 
+    std::vector<b200pt_instance> instances;
+    std::vector<const HLBVH *> object_bvhs;
+    std::map<const HLBVH *, int> object_ids;
     // primitives, in the order the parser created them (= the reference's primitive indices)
     for (const Primitive *prim : sb.gpu_primitives) {
         const Shape *shape = nullptr;
@@ -404,7 +411,29 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
             area = gp->area_light;
             mcode = b.medium_code(true, gp->medium_interface);
         } else {
-            refuse("an ObjectInstance");
+            // ObjectInstance (scene_builder.cu:845-876): the object's HLBVH itself (identity transform) or a TransformedPrimitive
+            // around it.  Its triangles go in AFTER all top-level ones (below); here only the instance is noted.
+            b200pt_instance in = {};
+            const Primitive *target = prim;
+            for (int k = 0; k < 4; k++) in.render_from_instance[5 * k] = in.instance_from_render[5 * k] = 1.f;
+            if (prim->type == Primitive::Type::transformed) {
+                const auto *tp = static_cast<const TransformedPrimitive *>(prim->ptr);
+                matrix16(tp->render_from_primitive, false, in.render_from_instance);
+                matrix16(tp->render_from_primitive, true, in.instance_from_render);
+                target = tp->primitive;
+            }
+            if (target->type != Primitive::Type::bvh) refuse("an instance of something that is not an object's BVH");
+            const auto *hl = static_cast<const HLBVH *>(target->ptr);
+            auto it = object_ids.find(hl);
+            if (it == object_ids.end()) {
+                object_ids[hl] = (int)object_bvhs.size();
+                in.object = (int)object_bvhs.size();
+                object_bvhs.push_back(hl);
+            } else {
+                in.object = it->second;
+            }
+            instances.push_back(in);
+            continue;
         }
         b.add_shape(shape, mat, mcode);
         if (area) {
@@ -429,6 +458,31 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
             lights[li] = L;
         }
     }
+    // the instanced objects' triangles, each object once, after the top-level triangles (b200pt_object)
+    std::vector<b200pt_object> objects;
+    for (const HLBVH *hl : object_bvhs) {
+        b200pt_object ob = {};
+        ob.first_triangle = (int64_t)b.tri_material.size();
+        for (int k = 0; k < hl->num_primitives; k++) {
+            const Primitive *q = hl->primitives[k];
+            const Shape *shape = nullptr;
+            const Material *mat = nullptr;
+            if (q->type == Primitive::Type::simple) {
+                const auto *sp = static_cast<const SimplePrimitive *>(q->ptr);
+                shape = sp->shape;
+                mat = sp->material;
+            } else if (q->type == Primitive::Type::geometric) { // not reachable: emissive / medium-transition shapes are refused inside objects
+                refuse("an emissive or medium-transition shape inside an instanced object");
+            } else {
+                refuse("a nested object instance");
+            }
+            if (shape->type != Shape::Type::triangle) refuse("a sphere or disk inside an instanced object (the Python front-end flattens those)");
+            b.add_shape(shape, mat, 0u);
+        }
+        ob.n_triangles = (int64_t)b.tri_material.size() - ob.first_triangle;
+        objects.push_back(ob);
+    }
+
     // LightSource lights (base/light.cu:22-75): the constructors have folded from / to / scale / power / illuminance into
     // render_from_light and `scale` already
     for (size_t i = 0; i < sb.gpu_lights.size(); i++) {
@@ -517,6 +571,10 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
     d.spheres = b.spheres.data();
     d.n_spectra = (int32_t)b.spectra.size();
     d.spectra = b.spectra.data();
+    d.n_objects = (int32_t)objects.size();
+    d.objects = objects.data();
+    d.n_instances = (int32_t)instances.size();
+    d.instances = instances.data();
     d.n_media = (int32_t)b.media.size();
     d.media = b.media.data();
     d.tri_medium = b.media.empty() ? nullptr : b.tri_medium.data();

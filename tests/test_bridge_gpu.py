@@ -111,6 +111,20 @@ def test_media_through_the_bridge(b200pt, tmp_path):
     bridge_equals_golden_and_ctypes(b200pt, tmp_path, "media2_96x64_64spp", ctypes_tol=2e-5)
 
 
+def test_object_instances_through_the_bridge(b200pt, tmp_path):
+    """ObjectBegin / ObjectInstance: the bridge hands the object's triangles over ONCE (read from the object's own HLBVH primitive
+    list) plus one TransformedPrimitive transform per instance; 36 rotated / scaled / mirrored instances of a two-mesh object
+    against the Python front-end's two-level description of the same file"""
+    text = T._instanced_scene_text()
+    r, out = run_bridge(text, 64, tmp_path)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    film = np.fromfile(out + ".f32", dtype=np.float32).reshape(64, 96, 3)
+    ours, _ = T.render(b200pt, text, 64, tmp_path)
+    assert ours.mean() > 0.02 and np.isfinite(film).all()
+    assert T.rel_mse(film, ours) <= 1e-5, T.rel_mse(film, ours)
+    assert abs(film.mean() - ours.mean()) <= 1e-3 * ours.mean()
+
+
 def test_coated_and_mix_materials_through_the_bridge(b200pt, tmp_path):
     """coateddiffuse / coatedconductor (LayeredBxDF) and Material "mix" hash the BITS of directions / hit points, and the bridge's
     vertices are the reference's own transformed points while the Python front-end transforms them itself (an ulp apart here and
@@ -128,6 +142,6 @@ def test_coated_and_mix_materials_through_the_bridge(b200pt, tmp_path):
 
 
 def test_bridge_refuses_what_it_does_not_carry(tmp_path):
-    r, out = run_bridge(T.scene_text("instances.pbrt"), 4, tmp_path)     # ObjectInstance
+    r, out = run_bridge(T.scene_text("instances.pbrt"), 4, tmp_path)     # a sphere inside an instanced object
     assert r.returncode == 2 and "not carried over by the C++ bridge" in r.stderr
     assert not os.path.exists(out)
