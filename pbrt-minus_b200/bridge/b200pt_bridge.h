@@ -15,8 +15,9 @@
 // dielectric, diffusetransmission, coateddiffuse, coatedconductor, mix, interface) with constant textures, every reference
 // spectrum class, diffuse area lights on triangles and spheres, LightSource distant / uniform infinite / spot, homogeneous
 // media with MediumInterface and the camera medium, object instances (triangle objects), the perspective camera, any pixel
-// filter (tabulated through Filter::evaluate), the RGB film.  Anything else (non-constant textures, the image infinite light,
-// quadrics inside instanced objects) is refused with a message naming it: the Python front-end (pbrt-minus_b200/pbrt_scene.py)
+// filter (tabulated through Filter::evaluate), the RGB film, image / scale / mix / directionmix / float textures with all four
+// mappings, the image infinite light.  Anything else (quadrics inside instanced objects, spheres on a medium transition, a
+// texture on a parameter the kernels take constants for) is refused with a message naming it: the Python front-end (pbrt-minus_b200/pbrt_scene.py)
 // covers those.
 //
 // Built by oracle/ref_build/build_ref.py into oracle/_ref/pbrt-minus-b200 (it links the reference's objects, so it lives with
@@ -46,6 +47,7 @@
 #include <pbrt/integrators/wavefront_path.h>
 #include <pbrt/lights/diffuse_area_light.h>
 #include <pbrt/lights/distant_light.h>
+#include <pbrt/lights/image_infinite_light.h>
 #include <pbrt/lights/spot_light.h>
 #include <pbrt/lights/uniform_infinite_light.h>
 #include <pbrt/materials/coated_conductor_material.h>
@@ -73,9 +75,32 @@
 #include <pbrt/spectra/rgb_unbounded_spectrum.h>
 #include <pbrt/spectrum_util/global_spectra.h>
 #include <pbrt/spectrum_util/rgb_color_space.h>
+#include <pbrt/spectrum_util/rgb_to_spectrum_data.h>
 #include <pbrt/textures/float_constant_texture.h>
+#include <pbrt/textures/float_image_texture.h>
+#include <pbrt/textures/float_scaled_texture.h>
+#include <pbrt/textures/gpu_image.h>
+#include <pbrt/textures/mipmap.h>
+#include <pbrt/textures/spectrum_direction_mix_texture.h>
+#include <pbrt/textures/spectrum_image_texture.h>
+#include <pbrt/textures/spectrum_mix_texture.h>
+#include <pbrt/textures/spectrum_scaled_texture.h>
+#include <pbrt/textures/texture_mapping_2d.h>
 #include <pbrt/textures/spectrum_constant_texture.h>
 #include <ext/lodepng/lodepng.h>
+
+// the reference's own Simpson tables of the RGB-to-spectrum fit (spectrum_util/rgb_to_spectrum_data.cu:34-40, 163-212): the
+// struct lives in that .cu file, the function has external linkage
+namespace RGBtoSpectrumData {
+struct RGBtoSpectrumBuffer {
+    double lambda_tbl[CIE_FINE_SAMPLES];
+    double rgb_tbl[3][CIE_FINE_SAMPLES];
+    double rgb_to_xyz[3][3];
+    double xyz_to_rgb[3][3];
+    double xyz_whitepoint[3];
+};
+void init_tables(RGBtoSpectrumBuffer *data, Gamut gamut);
+} // namespace RGBtoSpectrumData
 
 struct B200ptBridge {
     [[noreturn]] static void refuse(const char *what) {
@@ -199,10 +224,175 @@ struct B200ptBridge {
     }
     int interface_material = -1;
 
+    // ---- textures (base/spectrum_texture.cu, base/float_texture.cu): one b200pt_texture per node, children before parents
+    std::vector<b200pt_texture> textures;
+    std::map<const void *, int> texture_ids;
+    std::vector<b200pt_image> images;
+    std::vector<std::vector<float>> image_store;
+    std::map<const GPUImage *, int> image_ids;
+    int image(const GPUImage *im) {
+        auto it = image_ids.find(im);
+        if (it != image_ids.end()) return it->second;
+        b200pt_image o = {};
+        o.width = im->resolution.x;
+        o.height = im->resolution.y;
+        std::vector<float> px((size_t)o.width * o.height * 3);
+        for (size_t k = 0; k < (size_t)o.width * o.height; k++) {
+            px[3 * k] = (float)im->pixels[k].r;
+            px[3 * k + 1] = (float)im->pixels[k].g;
+            px[3 * k + 2] = (float)im->pixels[k].b;
+        }
+        image_store.push_back(std::move(px));
+        images.push_back(o);
+        image_ids[im] = (int)images.size() - 1;
+        return (int)images.size() - 1;
+    }
+    static b200pt_texture blank_texture(int type) {
+        b200pt_texture t = {};
+        t.type = type;
+        t.a = t.b = t.c = -1;
+        t.map[0] = t.map[1] = 1.f;
+        t.texture_from_render[0] = t.texture_from_render[5] = t.texture_from_render[10] = 1.f;
+        t.v1[0] = 1.f;
+        t.v2[1] = 1.f;
+        return t;
+    }
+    int push_texture(const void *key, const b200pt_texture &t) {
+        textures.push_back(t);
+        if (key) texture_ids[key] = (int)textures.size() - 1;
+        return (int)textures.size() - 1;
+    }
+    // image node: ImageTextureBase (mapping, MIPMap -> GPUImage, scale, invert)
+    void image_node(const ImageTextureBase *b, b200pt_texture &t) {
+        if (b->mipmap->wrap_mode != WrapMode::Repeat) refuse("a texture wrap mode other than repeat");
+        t.a = image(b->mipmap->image);
+        t.f[0] = (float)b->scale;
+        t.f[1] = b->invert ? 1.f : 0.f;
+        const TextureMapping2D *tm = b->texture_mapping;
+        auto rows = [&](const Transform &x) {
+            for (int r = 0; r < 3; r++)
+                for (int c = 0; c < 4; c++) t.texture_from_render[4 * r + c] = (float)x.m.val[r][c];
+        };
+        switch (tm->type) {
+        case TextureMapping2D::Type::uv: {
+            const auto *m = static_cast<const UVMapping *>(tm->ptr);
+            t.mapping = B200PT_MAP_UV;
+            t.map[0] = (float)m->su; t.map[1] = (float)m->sv; t.map[2] = (float)m->du; t.map[3] = (float)m->dv;
+            break;
+        }
+        case TextureMapping2D::Type::planar: {
+            const auto *m = static_cast<const PlanarMapping *>(tm->ptr);
+            t.mapping = B200PT_MAP_PLANAR;
+            rows(m->textureFromRender);
+            t.v1[0] = (float)m->vs.x; t.v1[1] = (float)m->vs.y; t.v1[2] = (float)m->vs.z;
+            t.v2[0] = (float)m->vt.x; t.v2[1] = (float)m->vt.y; t.v2[2] = (float)m->vt.z;
+            t.map[2] = (float)m->ds; t.map[3] = (float)m->dt;
+            break;
+        }
+        case TextureMapping2D::Type::spherical:
+            t.mapping = B200PT_MAP_SPHERICAL;
+            rows(static_cast<const SphericalMapping *>(tm->ptr)->textureFromRender);
+            break;
+        default:
+            t.mapping = B200PT_MAP_CYLINDRICAL;
+            rows(static_cast<const CylindricalMapping *>(tm->ptr)->textureFromRender);
+        }
+    }
+    int float_texture(const FloatTexture *t) {
+        auto it = texture_ids.find(t);
+        if (it != texture_ids.end()) return it->second;
+        switch (t->type) {
+        case FloatTexture::Type::constant: {
+            b200pt_texture o = blank_texture(B200PT_TEX_FLOAT_CONSTANT);
+            o.f[0] = (float)static_cast<const FloatConstantTexture *>(t->ptr)->value;
+            return push_texture(t, o);
+        }
+        case FloatTexture::Type::image: {
+            b200pt_texture o = blank_texture(B200PT_TEX_FLOAT_IMAGE);
+            image_node((const ImageTextureBase *)static_cast<const FloatImageTexture *>(t->ptr), o); // (a C cast: the base is private)
+            return push_texture(t, o);
+        }
+        default: { // scale: the product of two float textures (textures/float_scaled_texture.cu)
+            const auto *p = static_cast<const FloatScaledTexture *>(t->ptr);
+            b200pt_texture o = blank_texture(B200PT_TEX_FLOAT_SCALE);
+            o.a = float_texture(p->scale);
+            o.b = float_texture(p->texture);
+            return push_texture(t, o);
+        }
+        }
+    }
+    int spectrum_texture(const SpectrumTexture *t) {
+        auto it = texture_ids.find(t);
+        if (it != texture_ids.end()) return it->second;
+        switch (t->type) {
+        case SpectrumTexture::Type::constant: {
+            b200pt_texture o = blank_texture(B200PT_TEX_CONSTANT);
+            o.a = spectrum(static_cast<const SpectrumConstantTexture *>(t->ptr)->value);
+            return push_texture(t, o);
+        }
+        case SpectrumTexture::Type::image: {
+            const auto *p = static_cast<const SpectrumImageTexture *>(t->ptr);
+            if (p->spectrum_type != SpectrumType::Albedo) refuse("an image texture that is not an albedo (illuminant / unbounded image textures)");
+            b200pt_texture o = blank_texture(B200PT_TEX_IMAGE);
+            image_node((const ImageTextureBase *)p, o);
+            return push_texture(t, o);
+        }
+        case SpectrumTexture::Type::scaled: {
+            const auto *p = static_cast<const SpectrumScaledTexture *>(t->ptr);
+            b200pt_texture o = blank_texture(B200PT_TEX_SCALE);
+            o.a = spectrum_texture(p->texture);
+            o.f[0] = (float)p->scale;
+            return push_texture(t, o);
+        }
+        case SpectrumTexture::Type::mix: {
+            const auto *p = static_cast<const SpectrumMixTexture *>(t->ptr);
+            b200pt_texture o = blank_texture(B200PT_TEX_MIX);
+            o.a = spectrum_texture(p->tex1);
+            o.b = spectrum_texture(p->tex2);
+            o.c = float_texture(p->amount);
+            return push_texture(t, o);
+        }
+        case SpectrumTexture::Type::direction_mix: {
+            const auto *p = static_cast<const SpectrumDirectionMixTexture *>(t->ptr);
+            b200pt_texture o = blank_texture(B200PT_TEX_DIRECTION_MIX);
+            o.a = spectrum_texture(p->tex1);
+            o.b = spectrum_texture(p->tex2);
+            o.f[0] = (float)p->dir.x; o.f[1] = (float)p->dir.y; o.f[2] = (float)p->dir.z;
+            return push_texture(t, o);
+        }
+        default:
+            refuse("a checkerboard texture (the reference itself renders NaN with it)");
+        }
+    }
     int constant_texture(const SpectrumTexture *t) {
         if (!t) return -1;
-        if (t->type != SpectrumTexture::Type::constant) refuse("a non-constant spectrum texture");
+        if (t->type != SpectrumTexture::Type::constant) refuse("a non-constant spectrum texture on a parameter that takes none here");
         return spectrum(static_cast<const SpectrumConstantTexture *>(t->ptr)->value);
+    }
+    // a "reflectance" / "transmittance" parameter: the spectrum id of a constant texture, or a placeholder spectrum plus the
+    // texture id + 1 (b200pt_material.*_tex1)
+    int textured(const SpectrumTexture *t, int32_t *tex1) {
+        *tex1 = 0;
+        if (!t) return -1;
+        if (t->type == SpectrumTexture::Type::constant) return spectrum(static_cast<const SpectrumConstantTexture *>(t->ptr)->value);
+        *tex1 = spectrum_texture(t) + 1;
+        if (placeholder_spectrum < 0) {
+            b200pt_spectrum o = {};
+            o.type = B200PT_SPEC_CONSTANT;
+            o.c[0] = 0.5f;
+            spectra.push_back(o);
+            placeholder_spectrum = (int)spectra.size() - 1;
+        }
+        return placeholder_spectrum;
+    }
+    int placeholder_spectrum = -1;
+    // a roughness parameter: the value of a constant float texture, or 0 plus the texture id + 1
+    float roughness(const FloatTexture *t, int32_t *tex1) {
+        *tex1 = 0;
+        if (!t) return 0.f;
+        if (t->type == FloatTexture::Type::constant) return (float)static_cast<const FloatConstantTexture *>(t->ptr)->value;
+        *tex1 = float_texture(t) + 1;
+        return 0.f;
     }
     float constant_float(const FloatTexture *t) {
         if (!t) return 0.f;
@@ -233,18 +423,18 @@ struct B200ptBridge {
         switch (m->type) {
         case Material::Type::diffuse:
             o.type = B200PT_MAT_DIFFUSE;
-            o.reflectance = constant_texture(static_cast<const DiffuseMaterial *>(m->ptr)->reflectance);
+            o.reflectance = textured(static_cast<const DiffuseMaterial *>(m->ptr)->reflectance, &o.reflectance_tex1);
             break;
         case Material::Type::conductor: {
             const auto *p = static_cast<const ConductorMaterial *>(m->ptr);
             o.type = B200PT_MAT_CONDUCTOR;
-            if (p->reflectance) o.reflectance = constant_texture(p->reflectance);
+            if (p->reflectance) o.reflectance = textured(p->reflectance, &o.reflectance_tex1);
             else {
                 o.eta = constant_texture(p->eta);
                 o.k = constant_texture(p->k);
             }
-            o.u_roughness = constant_float(p->uRoughness);
-            o.v_roughness = constant_float(p->vRoughness);
+            o.u_roughness = roughness(p->uRoughness, &o.u_roughness_tex1);
+            o.v_roughness = roughness(p->vRoughness, &o.v_roughness_tex1);
             o.remap_roughness = p->remapRoughness ? 1 : 0;
             break;
         }
@@ -252,23 +442,23 @@ struct B200ptBridge {
             const auto *p = static_cast<const DielectricMaterial *>(m->ptr);
             o.type = B200PT_MAT_DIELECTRIC;
             o.eta = spectrum(p->eta);
-            o.u_roughness = constant_float(p->uRoughness);
-            o.v_roughness = constant_float(p->vRoughness);
+            o.u_roughness = roughness(p->uRoughness, &o.u_roughness_tex1);
+            o.v_roughness = roughness(p->vRoughness, &o.v_roughness_tex1);
             o.remap_roughness = p->remapRoughness ? 1 : 0;
             break;
         }
         case Material::Type::diffuse_transmission: {
             const auto *p = static_cast<const DiffuseTransmissionMaterial *>(m->ptr);
             o.type = B200PT_MAT_DIFFUSE_TRANSMISSION;
-            o.reflectance = constant_texture(p->reflectance);
-            o.transmittance = constant_texture(p->transmittance);
+            o.reflectance = textured(p->reflectance, &o.reflectance_tex1);
+            o.transmittance = textured(p->transmittance, &o.transmittance_tex1);
             o.scale = (float)p->scale;
             break;
         }
         case Material::Type::coated_diffuse: { // materials/coated_diffuse_material.cu:9-51
             const auto *p = static_cast<const CoatedDiffuseMaterial *>(m->ptr);
             o.type = B200PT_MAT_COATED_DIFFUSE;
-            o.reflectance = constant_texture(p->reflectance);
+            o.reflectance = textured(p->reflectance, &o.reflectance_tex1);
             o.albedo = constant_texture(p->albedo);
             o.eta = spectrum(p->eta);
             o.u_roughness = constant_float(p->u_roughness);
@@ -291,7 +481,7 @@ struct B200ptBridge {
             o.albedo = constant_texture(p->albedo);
             o.c_u_roughness = constant_float(p->conductorURoughness);
             o.c_v_roughness = constant_float(p->conductorVRoughness);
-            if (p->reflectance) o.reflectance = constant_texture(p->reflectance);
+            if (p->reflectance) o.reflectance = textured(p->reflectance, &o.reflectance_tex1);
             else {
                 o.c_eta = constant_texture(p->conductorEta);
                 o.c_k = constant_texture(p->k);
@@ -513,8 +703,19 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
             }
             L.cos_falloff_start = (float)sp->cosFalloffStart;
             L.cos_falloff_end = (float)sp->cosFalloffEnd;
-        } else {
-            refuse("an image infinite light");
+        } else { // lights/image_infinite_light.cu: the image in the equal-area octahedral parameterisation
+            const auto *im = static_cast<const ImageInfiniteLight *>(lt->ptr);
+            for (size_t k = 0; k < i; k++)
+                if (lights[k].type == B200PT_LIGHT_IMAGE_INFINITE) refuse("a second image infinite light");
+            L.type = B200PT_LIGHT_IMAGE_INFINITE;
+            L.spectrum = -1;
+            L.scale = (float)im->scale;
+            L.image = b.image(im->image_ptr);
+            for (int r = 0; r < 3; r++)
+                for (int c = 0; c < 3; c++) {
+                    L.light_from_render[3 * r + c] = (float)im->render_from_light.inv_m.val[r][c];
+                    L.render_from_light[3 * r + c] = (float)im->render_from_light.m.val[r][c];
+                }
         }
         lights[i] = L;
     }
@@ -571,6 +772,25 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
     d.spheres = b.spheres.data();
     d.n_spectra = (int32_t)b.spectra.size();
     d.spectra = b.spectra.data();
+    std::vector<double> fit;
+    if (!b.images.empty()) {
+        for (size_t i = 0; i < b.images.size(); i++) b.images[i].rgb = b.image_store[i].data();
+        // [3 x 283 rgb_tbl | 3 white | 283 lambda01] from the reference's own init_tables
+        auto *buf = new RGBtoSpectrumData::RGBtoSpectrumBuffer();
+        RGBtoSpectrumData::init_tables(buf, RGBtoSpectrumData::Gamut::sRGB);
+        const int F = RGBtoSpectrumData::CIE_FINE_SAMPLES;
+        for (int k = 0; k < 3; k++)
+            for (int i = 0; i < F; i++) fit.push_back(buf->rgb_tbl[k][i]);
+        for (int k = 0; k < 3; k++) fit.push_back(buf->xyz_whitepoint[k]);
+        for (int i = 0; i < F; i++)
+            fit.push_back((buf->lambda_tbl[i] - RGBtoSpectrumData::CIE_LAMBDA_MIN) / (RGBtoSpectrumData::CIE_LAMBDA_MAX - RGBtoSpectrumData::CIE_LAMBDA_MIN));
+        delete buf;
+        d.rgb2spec_fit = fit.data();
+    }
+    d.n_textures = (int32_t)b.textures.size();
+    d.textures = b.textures.data();
+    d.n_images = (int32_t)b.images.size();
+    d.images = b.images.data();
     d.n_objects = (int32_t)objects.size();
     d.objects = objects.data();
     d.n_instances = (int32_t)instances.size();
