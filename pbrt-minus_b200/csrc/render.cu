@@ -1217,8 +1217,64 @@ constexpr int VOL_BLOCK = 128;
 // bounds) to the light sample: march the normalised shadow ray from hit to hit, attenuating by the medium of each segment;
 // any surface with a material blocks, material-less interfaces are crossed (normal := ray direction, so the far side is
 // the interface's exterior, or whatever a plain primitive hands on).
+// Does any instanced object block the ray within t_max?  Per-thread form of k_trace_wf's instance walk for the transmittance
+// walk below: the tree over the instance boxes is walked with a small local stack, each proxy whose own box the ray touches takes
+// the ray into the instance's space (Transform::apply_inverse(Ray, &t_max)) and walks the object's tree for ANY hit.  Instanced
+// surfaces always carry a material (the reference refuses medium transitions inside objects, scene_builder.cu:651-656), so any
+// hit ends a transmittance walk with zero.
+__device__ __forceinline__ bool instances_block(const WF &wf, V3 o, V3 d, float t_max, uint2 *sm_stack, unsigned *overflow) {
+    if (wf.inst_root < 0) return false;
+    const float idx = safe_rcp_dir(d.x), idy = safe_rcp_dir(d.y), idz = safe_rcp_dir(d.z);
+    const uint32_t octinv = (idx < 0.f ? 0u : 4u) | (idy < 0.f ? 0u : 2u) | (idz < 0.f ? 0u : 1u);
+    const uint32_t octinv4 = octinv * 0x01010101u;
+    constexpr int DEPTH = 24;
+    uint2 stack[DEPTH];
+    int sp = 0;
+    uint2 ng = make_uint2((uint32_t)wf.inst_root, 0x80000000u), tg = make_uint2(0u, 0u);
+    while (true) {
+        if (tg.y != 0u) {
+            const int ti = __ffs(tg.y) - 1;
+            tg.y &= tg.y - 1u;
+            const int ni = __float_as_int(__ldg(&wf.bvh.tris[3 * size_t(tg.x + ti)].w)) - int(wf.bvh.n_tris);
+            const InstRec &I = wf.instances[ni];
+            if (ray_touches_instance(I, o.x, o.y, o.z, idx, idy, idz, t_max)) {
+                V3 oi, di;
+                float dt;
+                instance_ray(I.ifr, o, d, &oi, &di, &dt);
+                RayHit h;
+                TraceCounters ctr;
+                traverse_bvh8<true, false, true>(wf.bvh, oi.x, oi.y, oi.z, di.x, di.y, di.z, t_max - dt, sm_stack, VOL_BLOCK, h, ctr, overflow,
+                                                 I.root_node);
+                if (h.prim >= 0) return true;
+            }
+            continue;
+        }
+        if (ng.y <= 0x00ffffffu) {
+            if (sp == 0) return false;
+            ng = stack[--sp];
+        }
+        const uint32_t hits = ng.y;
+        const int child_bit = 31 - __clz(hits);
+        ng.y &= ~(1u << child_bit);
+        if (ng.y > 0x00ffffffu) {
+            if (sp < DEPTH) stack[sp++] = ng;
+            else *overflow = 1u;
+        }
+        const uint32_t cslot = (uint32_t(child_bit) - 24u) ^ octinv;
+        const uint32_t rel = __popc(hits & 0xffu & ((1u << cslot) - 1u));
+        const float4 *np = wf.bvh.nodes + 5 * size_t(ng.x + rel);
+        const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+        const uint32_t hitmask = intersect_node8(n0, n1, n2, n3, n4, o.x, o.y, o.z, idx, idy, idz, octinv4, t_max, 0x47000000u);
+        ng.x = __float_as_uint(n1.x);
+        tg.x = __float_as_uint(n1.y);
+        ng.y = (hitmask & 0xff000000u) | (__float_as_uint(n0.w) >> 24);
+        tg.y = hitmask & 0x00ffffffu;
+    }
+}
+
 // p0: the scattering point (offset_ray_origin with n = 0 moves nothing, base/ray.h:30-49); pt: the light point offset towards
 // p0 (it fixes the direction of the walk); lp: the light point itself (the distances).
+template <bool INST>
 __device__ __forceinline__ S4 volume_transmittance(const WF &wf, V3 p0, int medium, V3 pt, V3 lp, S4 lambda, uint2 *sm_stack,
                                                    unsigned *overflow) {
     const float epsilon_distance = len(p0 - lp) * 1e-4f;
@@ -1240,6 +1296,8 @@ __device__ __forceinline__ S4 volume_transmittance(const WF &wf, V3 p0, int medi
                 break;
             }
         }
+        // an instanced object in front of whatever was found ends the walk too
+        if (INST && !sphere_closer && instances_block(wf, o, d, h.t, sm_stack, overflow)) sphere_closer = true;
         const bool hit = sphere_closer || h.prim >= 0;
         // a sphere always carries a material here, so a sphere in front of the triangle hit ends the walk with 0 whatever
         // its exact distance; otherwise next_t is the triangle hit
@@ -1399,6 +1457,7 @@ __global__ void __launch_bounds__(VOL_BLOCK) k_volume(WF wf) {
 }
 
 // the transmittance requests of k_volume<1>, one thread per scattering point of this pass
+template <bool INST>
 __global__ void __launch_bounds__(VOL_BLOCK) k_transmit(WF wf) {
     __shared__ uint2 s_stack[SM_STACK * VOL_BLOCK];
     if (wf.c->finished >= (unsigned long long)wf.total_paths) return;
@@ -1411,7 +1470,7 @@ __global__ void __launch_bounds__(VOL_BLOCK) k_transmit(WF wf) {
         const float4 r1 = wf.q.sh_d[i], r2 = wf.q.sh_contrib[i];
         const int slot = wf.q.vol[i];
         const S4 lambda = wf.pool.lambda[slot];
-        const S4 T = volume_transmittance(wf, v3(r0), medium, v3(r1), v3(r2), lambda, s_stack + threadIdx.x, &wf.c->stack_overflow);
+        const S4 T = volume_transmittance<INST>(wf, v3(r0), medium, v3(r1), v3(r2), lambda, s_stack + threadIdx.x, &wf.c->stack_overflow);
         const float pdf_light = r1.w;
         const bool delta = signbit(r2.w); // the phase pdf is positive: its sign carries "delta light, no MIS"
         const float ppdf = fabsf(r2.w);
@@ -2111,10 +2170,6 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
     wf.instances = s->d_instances;
     wf.n_instances = (int32_t)s->instances.size();
     wf.inst_root = s->inst_root_node;
-    if (wf.n_instances > 0 && r->n_media > 0) {
-        set_error("b200pt_render: object instances in scenes with media are not supported");
-        return B200PT_ERR_UNSUPPORTED;
-    }
     wf.N = s->d_N;
     wf.uv = s->d_uv;
     wf.idx = s->d_idx;
@@ -2189,7 +2244,8 @@ B200PT_API int b200pt_render(b200pt_scene *s, b200pt_film *film, const b200pt_re
             if (wf.has_media) {
                 k_volume<0><<<grid, VOL_BLOCK, 0, st>>>(wf);
                 k_volume<1><<<grid, VOL_BLOCK, 0, st>>>(wf);
-                k_transmit<<<grid, VOL_BLOCK, 0, st>>>(wf);
+                if (wf.n_instances > 0) k_transmit<true><<<grid, VOL_BLOCK, 0, st>>>(wf);
+                else k_transmit<false><<<grid, VOL_BLOCK, 0, st>>>(wf);
             }
             if (r->env.light >= 0) {
                 if (wf.has_media) k_logic<true, true><<<grid, WF_BLOCK, 0, st>>>(wf);

@@ -357,19 +357,6 @@ __device__ __forceinline__ int next_sphere(const SphereRec *sph, int n, int k, f
     return k;
 }
 
-// does the ray (o, 1/d, [0, t_max]) touch the instance's padded render-space box?  (a leaf child of the instance tree bounds up to
-// three proxies with ONE box: each candidate is tested against its own)
-__device__ __forceinline__ bool ray_touches_instance(const InstRec &I, float ox, float oy, float oz, float idx, float idy, float idz,
-                                                     float t_max) {
-    const float *lo = I.box_lo, *hi = I.box_hi;
-    const float x0 = (__ldg(lo) - ox) * idx, x1 = (__ldg(hi) - ox) * idx;
-    const float y0 = (__ldg(lo + 1) - oy) * idy, y1 = (__ldg(hi + 1) - oy) * idy;
-    const float z0 = (__ldg(lo + 2) - oz) * idz, z1 = (__ldg(hi + 2) - oz) * idz;
-    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.f));
-    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
-    return tn <= tf * 1.00001f + 1e-30f;
-}
-
 // INST: the scene has object instances (two-level traversal).  A ray first walks the top-level tree of the scene's own
 // triangles (and the quadrics); when that is exhausted it walks the INSTANCE TREE -- a BVH8 over the instances' padded
 // render-space boxes whose leaf records are proxies carrying the instance index -- with the same node steps.  A proxy the ray

@@ -99,17 +99,31 @@ __device__ __forceinline__ uint32_t intersect_node8(const float4 &n0, const floa
     return hitmask;
 }
 
+// does the ray (o, 1/d, [0, t_max]) touch the instance's padded render-space box?  (a leaf child of the instance tree bounds up to
+// three proxies with ONE box: each candidate is tested against its own)
+__device__ __forceinline__ bool ray_touches_instance(const InstRec &I, float ox, float oy, float oz, float idx, float idy, float idz,
+                                                     float t_max) {
+    const float *lo = I.box_lo, *hi = I.box_hi;
+    const float x0 = (__ldg(lo) - ox) * idx, x1 = (__ldg(hi) - ox) * idx;
+    const float y0 = (__ldg(lo + 1) - oy) * idy, y1 = (__ldg(hi + 1) - oy) * idy;
+    const float z0 = (__ldg(lo + 2) - oz) * idz, z1 = (__ldg(hi + 2) - oz) * idz;
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.f));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_max));
+    return tn <= tf * 1.00001f + 1e-30f;
+}
+
 // sm_stack: this thread's column of the CTA's shared stack, addressed as sm_stack[depth * stride].
 // hit.prim = the triangle's primitive id, or (SLOT) its leaf-order record index.
 template <bool ANY, bool COUNT, bool SLOT = false>
 __device__ __forceinline__ bool traverse_bvh8(const BVH8 &bvh, float ox, float oy, float oz, float dx, float dy, float dz,
                                               float t_max, uint2 *sm_stack, int stride, RayHit &hit, TraceCounters &ctr,
-                                              unsigned *overflow_flag) {
+                                              unsigned *overflow_flag, int root = -1) {
+    // root: -1 walks the scene's own tree (node 0, if there is one); otherwise the tree of an instanced object rooted at that node
     hit.prim = -1;
     hit.t = t_max;
     hit.b1 = 0.f;
     hit.b2 = 0.f;
-    if (bvh.n_nodes == 0) return false;
+    if (root < 0 && bvh.n_nodes == 0) return false;
 
     const float idx = safe_rcp_dir(dx), idy = safe_rcp_dir(dy), idz = safe_rcp_dir(dz);
     const bool negx = idx < 0.f, negy = idy < 0.f, negz = idz < 0.f; // sign of the clamped reciprocal (covers -0)
@@ -118,7 +132,7 @@ __device__ __forceinline__ bool traverse_bvh8(const BVH8 &bvh, float ox, float o
 
     uint2 lstack[LOCAL_STACK];
     int sp = 0;
-    uint2 ng = make_uint2(0u, 0x80000000u); // node group: x = child base index, y = hit bits | imask
+    uint2 ng = make_uint2(root < 0 ? 0u : (uint32_t)root, 0x80000000u); // node group: x = child base index, y = hit bits | imask
     uint2 tg = make_uint2(0u, 0u);          // triangle group: x = tri base, y = hit bits
 
     while (true) {

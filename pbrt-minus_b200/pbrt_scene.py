@@ -925,8 +925,6 @@ class Scene:
         keep += [sph, spec, mats, lights]
         objs = [o for o in getattr(self, "objects", []) if o.get("count", 0) > 0]
         if objs:
-            if self.media:
-                raise SceneError("object instances in scenes with media are outside the hot path")
             oa = (api.Object * len(objs))()
             for i, o in enumerate(objs):
                 oa[i].first_triangle, oa[i].n_triangles = o["first"], o["count"]
