@@ -16,8 +16,8 @@
 // spectrum class, diffuse area lights on triangles and spheres, LightSource distant / uniform infinite / spot, homogeneous
 // media with MediumInterface and the camera medium, object instances (triangle objects), the perspective camera, any pixel
 // filter (tabulated through Filter::evaluate), the RGB film, image / scale / mix / directionmix / float textures with all four
-// mappings, the image infinite light.  Anything else (quadrics inside instanced objects, spheres on a medium transition, a
-// texture on a parameter the kernels take constants for) is refused with a message naming it: the Python front-end (pbrt-minus_b200/pbrt_scene.py)
+// mappings, the image infinite light.  Anything else (spheres on a medium transition, a texture on a parameter the kernels take
+// constants for) is refused with a message naming it: the Python front-end (pbrt-minus_b200/pbrt_scene.py)
 // covers those.
 //
 // Built by oracle/ref_build/build_ref.py into oracle/_ref/pbrt-minus-b200 (it links the reference's objects, so it lives with
@@ -650,6 +650,7 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
     }
     // the instanced objects' triangles, each object once, after the top-level triangles (b200pt_object)
     std::vector<b200pt_object> objects;
+    std::map<int, std::vector<std::pair<const Shape *, const Material *>>> object_quadrics;
     for (const HLBVH *hl : object_bvhs) {
         b200pt_object ob = {};
         ob.first_triangle = (int64_t)b.tri_material.size();
@@ -666,11 +667,38 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
             } else {
                 refuse("a nested object instance");
             }
-            if (shape->type != Shape::Type::triangle) refuse("a sphere or disk inside an instanced object (the Python front-end flattens those)");
+            if (shape->type != Shape::Type::triangle) { // quadrics do not go into the object's tree: one copy per instance, below
+                object_quadrics[(int)objects.size()].push_back({shape, mat});
+                continue;
+            }
             b.add_shape(shape, mat, 0u);
         }
         ob.n_triangles = (int64_t)b.tri_material.size() - ob.first_triangle;
         objects.push_back(ob);
+    }
+    // spheres and disks of instanced objects ride in the flat quadric list under the composite transform
+    // (render_from_instance * render_from_object); the orientation flag stays that of the quadric's own transform, because
+    // Transform::operator()(SurfaceInteraction) carries the normal through the instance transform without a handedness flip
+    for (const b200pt_instance &in : instances) {
+        auto it = object_quadrics.find(in.object);
+        if (it == object_quadrics.end()) continue;
+        for (const auto &sm : it->second) {
+            b.add_shape(sm.first, sm.second, 0u);
+            b200pt_sphere &q = b.spheres.back();
+            float rfo[16], ofr[16];
+            for (int r = 0; r < 4; r++)
+                for (int c = 0; c < 4; c++) {
+                    double a = 0, bb = 0;
+                    for (int k = 0; k < 4; k++) {
+                        a += (double)in.render_from_instance[4 * r + k] * (double)q.render_from_object[4 * k + c];
+                        bb += (double)q.object_from_render[4 * r + k] * (double)in.instance_from_render[4 * k + c];
+                    }
+                    rfo[4 * r + c] = (float)a;
+                    ofr[4 * r + c] = (float)bb;
+                }
+            memcpy(q.render_from_object, rfo, sizeof(rfo));
+            memcpy(q.object_from_render, ofr, sizeof(ofr));
+        }
     }
 
     // LightSource lights (base/light.cu:22-75): the constructors have folded from / to / scale / power / illuminance into

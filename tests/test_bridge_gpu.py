@@ -141,6 +141,12 @@ def test_textures_through_the_bridge(b200pt, tmp_path):
     bridge_equals_golden_and_ctypes(b200pt, tmp_path, "envmap_96x64_64spp", ctypes_tol=1e-6, golden_tol=1e-6)
 
 
+def test_instanced_quadrics_through_the_bridge(b200pt, tmp_path):
+    """tests/scenes/instances.pbrt: an object holding a mesh AND a clipped sphere, placed four times (once mirrored) -- the mesh
+    goes into the object's tree, the sphere is copied per instance under the composite transform; against the reference's film"""
+    bridge_equals_golden_and_ctypes(b200pt, tmp_path, "instances_96x64_64spp", ctypes_tol=1e-5)
+
+
 def test_coated_and_mix_materials_through_the_bridge(b200pt, tmp_path):
     """coateddiffuse / coatedconductor (LayeredBxDF) and Material "mix" hash the BITS of directions / hit points, and the bridge's
     vertices are the reference's own transformed points while the Python front-end transforms them itself (an ulp apart here and
@@ -158,6 +164,8 @@ def test_coated_and_mix_materials_through_the_bridge(b200pt, tmp_path):
 
 
 def test_bridge_refuses_what_it_does_not_carry(tmp_path):
-    r, out = run_bridge(T.scene_text("instances.pbrt"), 4, tmp_path)     # a sphere inside an instanced object
+    text = T.scene_text("media2.pbrt").replace('MediumInterface "haze" "haze"\n  Material "conductor"', 'MediumInterface "mist" "haze"\n  Material "conductor"')
+    assert 'MediumInterface "mist" "haze"\n  Material "conductor"' in text
+    r, out = run_bridge(text, 4, tmp_path)     # a sphere on a medium transition
     assert r.returncode == 2 and "not carried over by the C++ bridge" in r.stderr
     assert not os.path.exists(out)
