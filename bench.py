@@ -4,7 +4,9 @@
 Headline line (`value`, Mrays/s): config C2, the largest single-GPU configuration -- traversal-only bench, synthetic
 10M-triangle random soup, 1920x1080 primary + incoherent diffuse-bounce + shadow rays.  One step = one pass of the hot
 path (closest-hit on the primary set, closest-hit on the bounce set, any-hit on the shadow set) over the materialised ray
-sets.  `parity` = hit ids of that step against the oracle's host BVH over the FULL ray sets.
+sets, issued as ONE b200pt_trace_device_batch call (consecutive sets on two traversal streams); the per-kernel durations of the
+roofline come from a second pass with one launch per set.  `parity` = hit ids of that step against the oracle's host BVH over
+the FULL ray sets.
 
 Second timed leg (`render`, Msamples/s): config C3's shape -- cornell-box-specular at 1920x1080, sample-partitioned across
 the N GPUs with ONE ncclReduce of the film inside the timed region (strong scaling), its own roofline and e2e.
@@ -331,9 +333,12 @@ def run_ours(args):
         rb.upload(rays)
         dev.append((name, any_hit, len(o), rb, hb))
 
+    dev_sets = [(rb, n, hb, any_hit) for _, any_hit, n, rb, hb in dev]
+
     def step_device():
-        for name, any_hit, n, rb, hb in dev:
-            scene.trace_device(rb, n, hb, any_hit=bool(any_hit), sync=False)
+        # one call for the three sets of a step: b200pt_trace_device_batch puts consecutive sets on the scene's two traversal
+        # streams, so the tail of one persistent kernel overlaps the start of the next (same hit records as one call per set)
+        scene.trace_device_batch(dev_sets, sync=False)
 
     def barrier():
         scene.sync()
@@ -355,6 +360,14 @@ def run_ours(args):
     sampler = ClockSampler(local)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 + 2 * len(dev) * args.steps)]
     ev[0].record(stream)
+    for _ in range(args.steps):
+        step_device()
+    ev[1].record(stream)
+    barrier()
+    scene.counters()     # raises if ANY of the asynchronous launches above reported a traversal-stack overflow (sticky flag)
+    ms_total = ev[0].elapsed_time(ev[1])
+    # the same K steps once more with one launch per set on ONE stream and events around every kernel: the per-kernel durations
+    # of the roofline (in the timed region above the sets of a step overlap, so a kernel has no duration of its own there)
     k = 2
     for _ in range(args.steps):
         for name, any_hit, n, rb, hb in dev:   # per-kernel events on the launching stream
@@ -362,11 +375,9 @@ def run_ours(args):
             scene.trace_device(rb, n, hb, any_hit=bool(any_hit), sync=False)
             ev[k + 1].record(stream)
             k += 2
-    ev[1].record(stream)
     barrier()
-    scene.counters()     # raises if ANY of the asynchronous launches above reported a traversal-stack overflow (sticky flag)
+    scene.counters()
     clocks = sampler.stop()
-    ms_total = ev[0].elapsed_time(ev[1])
     per_set_ms = {name: 0.0 for name, *_ in dev}
     k = 2
     for _ in range(args.steps):
@@ -443,6 +454,8 @@ def run_ours(args):
     roofline = {"bound": "issue", "kernel": "k_trace<closest> on the %s set" % dom, "achieved": round(achieved, 1),
                 "peak": peak, "peak_source": pk_src, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None,
                 "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": round(per_set_ms[dom], 4),
+                "kernel_ms_source": "CUDA events around every launch in a second pass of the same %d steps, one launch per set on one stream, "
+                                    "right after the timed region (whose steps overlap their three sets on two streams)" % args.steps,
                 "nodes_per_ray": round(c["nodes"] / max(1, c["rays"]), 2), "tris_per_ray": round(c["tris"] / max(1, c["rays"]), 2)}
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
@@ -462,6 +475,8 @@ def run_ours(args):
                 "call": "b200pt_trace_batch (pinned host buffers; outputs the caller passes as NULL are not copied back: the any-hit "
                         "set returns its occlusion flags only)", "ids_equal_device_resident": e2e_ids_equal},
         "gpu_launches": 3 * args.steps,
+        "step": "b200pt_trace_device_batch: the three ray sets of a step in one call, consecutive sets on two traversal streams",
+        "ms_per_step_one_stream": round(sum(per_set_ms.values()), 4),
         "clocks": clocks,
         "roofline": roofline,
         "notes": {"l2": "inputs larger than L2 (BVH8 nodes + triangles %.0f MB, rays %.0f MB)"

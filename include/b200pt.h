@@ -316,6 +316,16 @@ int b200pt_trace_batch(b200pt_scene *scene, const b200pt_ray_set *sets, int n_se
  * {prim (int bits), t, b1, b2} (16 B).  Asynchronous on the scene's stream unless sync != 0. */
 int b200pt_trace_device(b200pt_scene *scene, const void *rays_dev, int64_t n, int any_hit,
                         void *hits_dev, int sync);
+/* Several device-resident ray sets in one call (same record formats as b200pt_trace_device): the sets run on the scene's two
+ * traversal streams in turn, so the tail of one set's persistent kernel overlaps the start of the next; ordered on the scene's
+ * stream like one operation.  Asynchronous unless sync != 0. */
+typedef struct {
+    const void *rays_dev;
+    int64_t n;
+    int32_t any_hit, reserved;
+    void *hits_dev;
+} b200pt_device_ray_set;
+int b200pt_trace_device_batch(b200pt_scene *scene, const b200pt_device_ray_set *sets, int32_t n_sets, int sync);
 /* Per-launch traversal counters of the most recent trace with counting enabled:
  * out[0] = BVH8 nodes fetched, out[1] = triangles tested, out[2] = rays. */
 int b200pt_trace_set_counting(b200pt_scene *scene, int enable);

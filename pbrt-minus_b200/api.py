@@ -127,6 +127,10 @@ class RenderStats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class DeviceRaySet(C.Structure):
+    _fields_ = [("rays_dev", C.c_void_p), ("n", C.c_int64), ("any_hit", C.c_int32), ("reserved", C.c_int32), ("hits_dev", C.c_void_p)]
+
+
 class RaySet(C.Structure):
     """b200pt_ray_set (include/b200pt.h)"""
     _fields_ = [("o_xyz", C.POINTER(C.c_float)), ("d_xyz", C.POINTER(C.c_float)), ("tmax", C.POINTER(C.c_float)),
@@ -138,7 +142,7 @@ class RaySet(C.Structure):
 SYMBOLS = [
     "b200pt_abi_version", "b200pt_last_error", "b200pt_device_count",
     "b200pt_scene_create", "b200pt_scene_destroy", "b200pt_bvh_build", "b200pt_bvh_debug_sorted", "b200pt_bvh_validate",
-    "b200pt_trace", "b200pt_trace_batch", "b200pt_trace_device", "b200pt_trace_set_counting", "b200pt_trace_counters", "b200pt_trace_tune",
+    "b200pt_trace", "b200pt_trace_batch", "b200pt_trace_device", "b200pt_trace_device_batch", "b200pt_trace_set_counting", "b200pt_trace_counters", "b200pt_trace_tune",
     "b200pt_scene_stream", "b200pt_scene_sync",
     "b200pt_device_alloc", "b200pt_device_free", "b200pt_copy_to_device", "b200pt_copy_to_host",
     "b200pt_film_create", "b200pt_film_destroy", "b200pt_film_clear", "b200pt_render", "b200pt_film_reduce",
@@ -168,6 +172,7 @@ def load_library():
     lib.b200pt_bvh_validate.argtypes = [vp, C.POINTER(i64)]
     lib.b200pt_trace.argtypes = [vp, fp, fp, fp, i64, i32, ip, fp, fp]
     lib.b200pt_trace_batch.argtypes = [vp, C.POINTER(RaySet), i32]
+    lib.b200pt_trace_device_batch.argtypes = [vp, C.POINTER(DeviceRaySet), i32, i32]
     lib.b200pt_trace_device.argtypes = [vp, vp, i64, i32, vp, i32]
     lib.b200pt_trace_set_counting.argtypes = [vp, i32]
     lib.b200pt_trace_counters.argtypes = [vp, C.POINTER(i64)]

@@ -332,6 +332,49 @@ B200PT_API int b200pt_trace_device(b200pt_scene *s, const void *rays_dev, int64_
     return B200PT_OK;
 }
 
+// Several device-resident ray sets in one call: consecutive sets go to the scene's two traversal streams in turn, each with its own
+// work ticket, so the CTAs of set k+1 take the SM slots the last warps of set k have left (the tail of a persistent kernel is a few
+// per cent of a launch).  Ordered like one operation on the scene's stream: it starts after what the stream held and the stream
+// goes on after the last set.  Counting runs and single sets keep one stream.
+B200PT_API int b200pt_trace_device_batch(b200pt_scene *s, const b200pt_device_ray_set *sets, int n_sets, int sync) {
+    if (!s || n_sets < 0 || (n_sets > 0 && !sets)) {
+        set_error("b200pt_trace_device_batch: null argument");
+        return B200PT_ERR_INVALID;
+    }
+    int64_t total = 0;
+    for (int i = 0; i < n_sets; i++) {
+        if (sets[i].n < 0 || (sets[i].n > 0 && (!sets[i].rays_dev || !sets[i].hits_dev))) {
+            set_error("b200pt_trace_device_batch: bad ray set %d", i);
+            return B200PT_ERR_INVALID;
+        }
+        total += sets[i].n;
+    }
+    CU_TRY(cudaSetDevice(s->device));
+    const bool two = n_sets > 1 && !s->counting;
+    if (two) {
+        if (!s->stream2) CU_TRY(cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking));
+        while (s->pipe_events.size() < 2) {
+            cudaEvent_t e;
+            CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            s->pipe_events.push_back(e);
+        }
+        CU_TRY(cudaEventRecord(s->pipe_events[0], s->stream));
+        CU_TRY(cudaStreamWaitEvent(s->stream2, s->pipe_events[0], 0));
+    }
+    for (int i = 0; i < n_sets; i++) {
+        cudaStream_t cs = (two && (i & 1)) ? s->stream2 : s->stream;
+        const int rc = launch_trace(s, sets[i].rays_dev, sets[i].n, sets[i].any_hit, sets[i].hits_dev, i > 0, nullptr, two ? i : -1, cs);
+        if (rc) return rc;
+    }
+    if (two) {
+        CU_TRY(cudaEventRecord(s->pipe_events[1], s->stream2));
+        CU_TRY(cudaStreamWaitEvent(s->stream, s->pipe_events[1], 0));
+    }
+    s->last_counts[2] = total;
+    if (sync) return check_trace_status(s);
+    return B200PT_OK;
+}
+
 // Host-buffer traversal.  A three-stage pipeline over chunks of ALL the sets of the call: the copy-in of chunk k+1 (H2D
 // engine), the traversal of chunk k and the copy-out of chunk k-1 (D2H engine) run at the same time, so with pinned host
 // buffers a call costs about max(copy-in, traversal, copy-out) + one chunk of fill and drain, instead of their sum per set.

@@ -117,6 +117,13 @@ class HLBVH:
     def trace_device(self, rays_buf, n, hits_buf, any_hit=False, sync=False):
         _check(self.lib.b200pt_trace_device(self.handle, rays_buf.ptr, int(n), int(any_hit), hits_buf.ptr, int(sync)))
 
+    def trace_device_batch(self, sets, sync=False):
+        """sets: [(rays_buf, n, hits_buf, any_hit)]; b200pt_trace_device_batch (two traversal streams, one call)"""
+        arr = (api.DeviceRaySet * len(sets))()
+        for i, (rb, n, hb, any_hit) in enumerate(sets):
+            arr[i].rays_dev, arr[i].n, arr[i].any_hit, arr[i].hits_dev = rb.ptr, int(n), int(bool(any_hit)), hb.ptr
+        _check(self.lib.b200pt_trace_device_batch(self.handle, arr, len(sets), int(sync)))
+
     def set_counting(self, enable):
         _check(self.lib.b200pt_trace_set_counting(self.handle, int(enable)))
 

@@ -44,7 +44,7 @@ def test_struct_layouts_match_header(b200pt):
         #include <stdio.h>
         #include "b200pt.h"
         int main(void) {
-            printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(b200pt_texture), sizeof(b200pt_image),
+            printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(b200pt_device_ray_set), sizeof(b200pt_texture), sizeof(b200pt_image),
                    sizeof(b200pt_medium), sizeof(b200pt_object), sizeof(b200pt_instance), sizeof(b200pt_ray_set), sizeof(b200pt_spectrum), sizeof(b200pt_material),
                    sizeof(b200pt_light), sizeof(b200pt_sphere), sizeof(b200pt_camera), sizeof(b200pt_filter),
                    sizeof(b200pt_film_desc), sizeof(b200pt_scene_desc), sizeof(b200pt_build_stats),
@@ -58,6 +58,6 @@ def test_struct_layouts_match_header(b200pt):
         subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe], check=True)
         sizes = list(map(int, subprocess.run([exe], capture_output=True, text=True, check=True).stdout.split()))
     a = b200pt.api
-    mirrors = [a.Texture, a.Image, a.Medium, a.Object, a.Instance, a.RaySet, a.Spectrum, a.Material, a.Light, a.Sphere, a.Camera, a.Filter, a.FilmDesc, a.SceneDesc, a.BuildStats,
+    mirrors = [a.DeviceRaySet, a.Texture, a.Image, a.Medium, a.Object, a.Instance, a.RaySet, a.Spectrum, a.Material, a.Light, a.Sphere, a.Camera, a.Filter, a.FilmDesc, a.SceneDesc, a.BuildStats,
                a.RenderOpts, a.RenderStats]
     assert sizes == [C.sizeof(m) for m in mirrors]

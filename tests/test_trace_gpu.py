@@ -387,6 +387,35 @@ def test_c2_size_hit_ids_vs_reference_hlbvh_and_oracle_bvh(b200pt, oracle, tmp_p
     s.close()
 
 
+def test_device_batch_equals_one_call_per_set(b200pt):
+    """b200pt_trace_device_batch (consecutive sets on the scene's two traversal streams, separate work tickets) returns the hit
+    records of b200pt_trace_device called once per set, for closest- and any-hit sets of different sizes, twice in a row"""
+    P, idx = b200pt.workloads.triangle_soup(300_000, seed=9)
+    s = b200pt.HLBVH(P, idx)
+    wl = b200pt.workloads
+    o, d, tm = wl.primary_rays(320, 200)
+    prim, t, _ = s.intersect(o, d, tm)
+    bo, bd, bt = wl.bounce_rays(P, idx, o, d, prim, t, seed=3)
+    so, sd, st = wl.shadow_rays(P, idx, o, d, prim, t, seed=4)
+    sets = []
+    for (ro, rd, rt), any_hit in (((o, d, tm), 0), ((bo, bd, bt), 0), ((so, sd, st), 1), ((o[:777], d[:777], tm if np.ndim(tm) == 0 else tm[:777]), 0)):
+        rays = s.pack_rays(ro, rd, rt)
+        rb, hb, hb2 = s.alloc(rays.nbytes), s.alloc(len(ro) * 16), s.alloc(len(ro) * 16)
+        rb.upload(rays)
+        sets.append((rb, len(ro), hb, hb2, any_hit))
+    for rb, n, hb, hb2, any_hit in sets:
+        s.trace_device(rb, n, hb, any_hit=bool(any_hit), sync=True)
+    for _ in range(2):
+        s.trace_device_batch([(rb, n, hb2, any_hit) for rb, n, hb, hb2, any_hit in sets], sync=True)
+        for rb, n, hb, hb2, any_hit in sets:
+            a, b = hb.download(np.uint32, n * 4).reshape(n, 4), hb2.download(np.uint32, n * 4).reshape(n, 4)
+            if any_hit:
+                assert np.array_equal(a[:, 0] != 0xffffffff, b[:, 0] != 0xffffffff)
+            else:
+                assert np.array_equal(a, b)
+    s.close()
+
+
 @pytest.mark.parametrize("n_tris,seed", [(1, 0), (3, 1), (9, 2), (1000, 3), (200_000, 4), (3_000_000, 5)])
 def test_bvh8_is_conservative(b200pt, n_tris, seed):
     """The quantised tree itself, not only its answers: every child box, dequantised the way the traversal reads it, contains
