@@ -147,6 +147,15 @@ def test_instanced_quadrics_through_the_bridge(b200pt, tmp_path):
     bridge_equals_golden_and_ctypes(b200pt, tmp_path, "instances_96x64_64spp", ctypes_tol=1e-5)
 
 
+@pytest.mark.parametrize("name,ctypes_tol", [("loopsubdiv_96x64_64spp", 1e-6), ("disk_96x64_64spp", 1e-6), ("occluders_96x64_64spp", 1e-5),
+                                             ("normals_96x64_64spp", 1e-3)])
+def test_remaining_scenes_through_the_bridge(b200pt, tmp_path, name, ctypes_tol):
+    """the other golden scenes: Loop subdivision surfaces (the reference's own subdivision code produces the mesh the bridge reads),
+    disks, the near-contact occluders, per-vertex normals / uvs with ReverseOrientation and a mirrored instance (one coated sheet
+    in it hashes float bits: a looser bound against the Python path for that scene)"""
+    bridge_equals_golden_and_ctypes(b200pt, tmp_path, name, ctypes_tol=ctypes_tol)
+
+
 def test_coated_and_mix_materials_through_the_bridge(b200pt, tmp_path):
     """coateddiffuse / coatedconductor (LayeredBxDF) and Material "mix" hash the BITS of directions / hit points, and the bridge's
     vertices are the reference's own transformed points while the Python front-end transforms them itself (an ulp apart here and
