@@ -150,6 +150,8 @@ typedef struct {
     int32_t material; /* material id */
     int32_t light;    /* -1: not emissive; else the index of its B200PT_LIGHT_SPHERE_AREA light (spheres only, not disks) */
     int32_t kind;     /* 0 sphere (shapes/sphere.{h,cu}); 1 disk (shapes/disk.{h,cu}): z_min = height, z_max = inner radius */
+    uint32_t medium;  /* the quadric's medium word, as b200pt_scene_desc.tri_medium has one per triangle: 0 = SimplePrimitive,
+                       * 0xffffffff = GeometricPrimitive without a transition, else (interior + 1) | (exterior + 1) << 16 */
 } b200pt_sphere;
 
 /* ---- camera (cameras/perspective.cu:7-86) ------------------------------------------------ */

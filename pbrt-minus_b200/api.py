@@ -44,7 +44,7 @@ class Sphere(C.Structure):
     _fields_ = [("render_from_object", C.c_float * 16), ("object_from_render", C.c_float * 16),
                 ("radius", C.c_float), ("z_min", C.c_float), ("z_max", C.c_float), ("phi_max", C.c_float),
                 ("reverse_orientation", C.c_int32), ("transform_swaps_handedness", C.c_int32),
-                ("material", C.c_int32), ("light", C.c_int32), ("kind", C.c_int32)]
+                ("material", C.c_int32), ("light", C.c_int32), ("kind", C.c_int32), ("medium", C.c_uint32)]
 
 
 class Camera(C.Structure):

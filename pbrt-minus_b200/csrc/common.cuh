@@ -59,6 +59,7 @@ struct SphereRec {
     int material;
     int kind; // 0 sphere; 1 disk: z_min = height, z_max = inner radius
     int light; // -1, or the light id of this emissive sphere
+    uint32_t medium; // medium word (b200pt_sphere.medium)
     // render-space AABB of the quadric, padded: a ray that misses it cannot pass the interval-arithmetic test, so the
     // trace kernels skip that (long) test for most rays
     float box_lo[3], box_hi[3];

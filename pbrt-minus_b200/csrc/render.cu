@@ -241,6 +241,7 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             o.phi_max = sp.phi_max;
             o.flip = (sp.reverse_orientation != 0) ^ (sp.transform_swaps_handedness != 0);
             o.material = sp.material;
+            o.medium = sp.medium;
             o.kind = sp.kind;
             if (sp.kind == 1) { // Disk (shapes/disk.cu:7-20): height, inner radius as given
                 o.z_min = sp.z_min;
@@ -435,11 +436,17 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             set_error("b200pt_scene_create: camera medium %d", r->camera_medium);
             return B200PT_ERR_INVALID;
         }
-        for (int i = 0; i < desc->n_spheres; i++)
+        for (int i = 0; i < desc->n_spheres; i++) {
             if (desc->materials[desc->spheres[i].material].type == B200PT_MAT_INTERFACE) {
                 set_error("b200pt_scene_create: interface spheres are not supported");
                 return B200PT_ERR_UNSUPPORTED;
             }
+            const uint32_t c = desc->spheres[i].medium;
+            if (c != 0u && c != 0xffffffffu && !(med_ok(c & 0xffffu) && med_ok(c >> 16))) {
+                set_error("b200pt_scene_create: quadric %d has medium code 0x%x", i, c);
+                return B200PT_ERR_INVALID;
+            }
+        }
         if ((rc = dev_upload(r, &r->d_media, med.data(), med.size(), st))) return rc;
         if ((rc = dev_upload(r, &r->d_tri_medium, desc->tri_medium, (size_t)desc->n_triangles, st))) return rc;
     }
@@ -1199,13 +1206,13 @@ __device__ __forceinline__ S4 medium_sigma_t(const WF &wf, int medium, S4 lambda
 }
 __device__ __forceinline__ S4 exp_s4(S4 a) { return make_float4(expf(a.x), expf(a.y), expf(a.z), expf(a.w)); }
 
-// Interaction::get_medium(w) (base/interaction.h:60-66) for a hit on triangle `prim_id` (< 0: a sphere, always a
-// SimplePrimitive here): a medium transition picks exterior / interior by the side of the GEOMETRIC normal, a SimplePrimitive
+// Interaction::get_medium(w) (base/interaction.h:60-66) for a hit on triangle `prim_id` (or a quadric, see below): a medium transition picks exterior / interior by the side of the GEOMETRIC normal, a SimplePrimitive
 // hands on the medium of the ray that hit it, a GeometricPrimitive without transition has no medium at all
 // (primitives/geometric_primitive.cu:27, base/interaction.cu:59-63)
 __device__ __forceinline__ int surface_medium(const WF &wf, int prim_id, V3 n, V3 w, int ray_medium) {
-    if (prim_id < 0) return ray_medium;
-    const uint32_t code = wf.tri_medium[prim_id];
+    // prim_id <= -2: quadric number -2 - prim_id, which carries its own medium word
+    if (prim_id == -1) return ray_medium;
+    const uint32_t code = prim_id < 0 ? wf.spheres[-2 - prim_id].medium : wf.tri_medium[prim_id];
     if (code == 0u) return ray_medium;
     if (code == 0xffffffffu) return -1;
     return dot(n, w) > 0.f ? int(code >> 16) - 1 : int(code & 0xffffu) - 1;
@@ -1838,6 +1845,7 @@ __global__ void __launch_bounds__(WF_BLOCK, OCC ? OCC : ((MAT >= B200PT_MAT_COAT
             if (prim >= (int)wf.bvh.n_tris) {
                 const SphereRec &sp = wf.spheres[prim - (int)wf.bvh.n_tris];
                 sphere_interaction(sp, ro, rd, hit.y, -rd, si);
+                prim_id = -2 - (prim - (int)wf.bvh.n_tris);
             } else {
                 const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;
                 prim_id = __float_as_int(__ldg(&tp[0].w));

@@ -880,6 +880,7 @@ class Scene:
             sph[i].radius, sph[i].z_min, sph[i].z_max, sph[i].phi_max = s["radius"], s["zmin"], s["zmax"], s["phimax"]
             sph[i].reverse_orientation, sph[i].transform_swaps_handedness = int(s["ro"]), int(s["swaps"])
             sph[i].material, sph[i].light, sph[i].kind = s["material"], s.get("light", -1), s.get("kind", 0)
+            sph[i].medium = (s.get("medium", 0) & 0xFFFFFFFF) if self.media else 0
             if s.get("light", -1) >= 0 and self.media:
                 raise SceneError("emissive spheres in scenes with media are outside the hot path")
         d.n_spheres, d.spheres = len(self.spheres), sph
@@ -1103,13 +1104,11 @@ def load(path=None, text=None, spp=None, integrator=None, scene_dir=None, flatte
         else:
             if area_light is not None and rec["kind"] == "disk":
                 raise SceneError("emissive disks are outside the hot path")
-            if rec.get("mcode", 0) != 0 and not (area_light is not None and rec["mcode"] == 0xFFFFFFFF):
-                raise SceneError("spheres on a medium transition are outside the hot path")
             if sc.materials[rec["material"]]["type"] == 7:
                 raise SceneError("interface spheres are outside the hot path")
             sc.spheres.append({"rfo": rfo_x.m, "ofr": rfo_x.inv, "radius": rec["radius"], "zmin": rec["zmin"], "zmax": rec["zmax"],
                                "phimax": rec["phimax"], "ro": rec["ro"], "swaps": swaps_handedness(rec["rfo"].m), "material": rec["material"],
-                               "kind": 1 if rec["kind"] == "disk" else 0})
+                               "kind": 1 if rec["kind"] == "disk" else 0, "medium": int(rec.get("mcode", 0))})
             if area_light is not None:
                 sc.spheres[-1]["light"] = sc.add_sphere_light(len(sc.spheres) - 1, area_light, scene_dir)
 

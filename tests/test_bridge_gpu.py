@@ -147,11 +147,11 @@ def test_instanced_quadrics_through_the_bridge(b200pt, tmp_path):
     bridge_equals_golden_and_ctypes(b200pt, tmp_path, "instances_96x64_64spp", ctypes_tol=1e-5)
 
 
-@pytest.mark.parametrize("name,ctypes_tol", [("loopsubdiv_96x64_64spp", 1e-6), ("disk_96x64_64spp", 1e-6), ("occluders_96x64_64spp", 1e-5),
+@pytest.mark.parametrize("name,ctypes_tol", [("loopsubdiv_96x64_64spp", 1e-6), ("disk_96x64_64spp", 1e-6), ("occluders_96x64_64spp", 1e-5), ("mediaball_96x64_64spp", 5e-5),
                                              ("normals_96x64_64spp", 1e-3)])
 def test_remaining_scenes_through_the_bridge(b200pt, tmp_path, name, ctypes_tol):
     """the other golden scenes: Loop subdivision surfaces (the reference's own subdivision code produces the mesh the bridge reads),
-    disks, the near-contact occluders, per-vertex normals / uvs with ReverseOrientation and a mirrored instance (one coated sheet
+    disks, the near-contact occluders, spheres on medium transitions, per-vertex normals / uvs with ReverseOrientation and a mirrored instance (one coated sheet
     in it hashes float bits: a looser bound against the Python path for that scene)"""
     bridge_equals_golden_and_ctypes(b200pt, tmp_path, name, ctypes_tol=ctypes_tol)
 
@@ -173,8 +173,9 @@ def test_coated_and_mix_materials_through_the_bridge(b200pt, tmp_path):
 
 
 def test_bridge_refuses_what_it_does_not_carry(tmp_path):
-    text = T.scene_text("media2.pbrt").replace('MediumInterface "haze" "haze"\n  Material "conductor"', 'MediumInterface "mist" "haze"\n  Material "conductor"')
-    assert 'MediumInterface "mist" "haze"\n  Material "conductor"' in text
-    r, out = run_bridge(text, 4, tmp_path)     # a sphere on a medium transition
-    assert r.returncode == 2 and "not carried over by the C++ bridge" in r.stderr
+    # a conductor whose eta / k come from an image texture: the kernels take spectra there
+    text = T.scene_text("textures.pbrt").replace('WorldEnd', '') + \
+        '\nAttributeBegin\n  Material "conductor" "texture eta" ["colours"] "texture k" ["colours"]\n  Translate 0 3 0\n  Shape "sphere" "float radius" [0.2]\nAttributeEnd\n'
+    r, out = run_bridge(text, 4, tmp_path)
+    assert r.returncode == 2 and "not carried over by the C++ bridge" in r.stderr, r.stdout[-800:] + r.stderr[-800:]
     assert not os.path.exists(out)

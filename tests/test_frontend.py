@@ -155,8 +155,8 @@ def test_media_front_end(b200pt):
         ps.load(text=head + 'WorldBegin\nMediumInterface "nope" ""\n' + quad)
     with pytest.raises(ps.SceneError):
         ps.load(text=head + 'WorldBegin\nMakeNamedMedium "m" "string type" ["uniformgrid"]\n')
-    with pytest.raises(ps.SceneError):   # spheres on a transition are outside the hot path
-        ps.load(text=head + 'WorldBegin\nMakeNamedMedium "m" "string type" ["homogeneous"]\nMediumInterface "m" ""\nShape "sphere"\n')
+    ball = ps.load(text=head + 'WorldBegin\nMakeNamedMedium "m" "string type" ["homogeneous"]\nMediumInterface "m" ""\nShape "sphere"\n')
+    assert ball.spheres[0]["medium"] == 1 and ball.to_desc().spheres[0].medium == 1     # interior m (id 0 -> 1), exterior vacuum
 
 
 def test_loop_subdivision_mesh_producer(b200pt):

@@ -159,6 +159,14 @@ def test_occluders_inside_the_visibility_margins_match_reference(b200pt, tmp_pat
     check_against_golden(b200pt, tmp_path, "occluders_96x64_1024spp")
 
 
+def test_spheres_on_medium_transitions_match_reference(b200pt, tmp_path):
+    """GeometricPrimitive + MediumInterface over Shape "sphere": a glass ball filled with a coloured scattering medium, a
+    diffuse-transmission ball holding fog -- rays entering through the quadric pick up its interior medium by the side of the
+    geometric normal (Interaction::get_medium, base/interaction.h:60-66), NEE from inside is attenuated by it"""
+    check_against_golden(b200pt, tmp_path, "mediaball_96x64_64spp")
+    check_against_golden(b200pt, tmp_path, "mediaball_96x64_1024spp")
+
+
 def test_cornell_480x270_converged_4096spp(b200pt, tmp_path):
     """config C3's image between the 48x48 golden and full HD: 480x270 at 4096 spp against the reference's film, relMSE +
     the per-pixel 3 sigma gate (sigma_p from 16 disjoint sample ranges of ours, which also exercises the sample partition)"""

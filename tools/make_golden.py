@@ -77,6 +77,9 @@ CASES = [
     # occluders inside the margins of the reference's three-ray visibility test (base/integrator_base.cu:12-71)
     ("occluders_96x64_64spp", "occluders.pbrt", None, 64, None, None),
     ("occluders_96x64_1024spp", "occluders.pbrt", None, 1024, None, None),
+    # spheres on medium transitions (a glass ball of dye, a diffuse-transmission ball of fog)
+    ("mediaball_96x64_64spp", "mediaball.pbrt", None, 64, None, None),
+    ("mediaball_96x64_1024spp", "mediaball.pbrt", None, 1024, None, None),
 ]
 
 
