@@ -16,8 +16,7 @@
 // spectrum class, diffuse area lights on triangles and spheres, LightSource distant / uniform infinite / spot, homogeneous
 // media with MediumInterface and the camera medium, object instances (triangle objects), the perspective camera, any pixel
 // filter (tabulated through Filter::evaluate), the RGB film, image / scale / mix / directionmix / float textures with all four
-// mappings, the image infinite light.  Anything else (a texture on a parameter the kernels take constants for, interface
-// spheres) is refused with a message naming it: the Python front-end (pbrt-minus_b200/pbrt_scene.py)
+// mappings, the image infinite light.  Anything else (a texture on a parameter the kernels take constants for) is refused with a message naming it: the Python front-end (pbrt-minus_b200/pbrt_scene.py)
 // covers those.
 //
 // Built by oracle/ref_build/build_ref.py into oracle/_ref/pbrt-minus-b200 (it links the reference's objects, so it lives with

@@ -437,10 +437,6 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             return B200PT_ERR_INVALID;
         }
         for (int i = 0; i < desc->n_spheres; i++) {
-            if (desc->materials[desc->spheres[i].material].type == B200PT_MAT_INTERFACE) {
-                set_error("b200pt_scene_create: interface spheres are not supported");
-                return B200PT_ERR_UNSUPPORTED;
-            }
             const uint32_t c = desc->spheres[i].medium;
             if (c != 0u && c != 0xffffffffu && !(med_ok(c & 0xffffu) && med_ok(c >> 16))) {
                 set_error("b200pt_scene_create: quadric %d has medium code 0x%x", i, c);
@@ -1296,21 +1292,41 @@ __device__ __forceinline__ S4 volume_transmittance(const WF &wf, V3 p0, int medi
         TraceCounters ctr;
         traverse_bvh8<false, false, true>(wf.bvh, o.x, o.y, o.z, d.x, d.y, d.z, t_max, sm_stack, VOL_BLOCK, h, ctr, overflow);
         bool sphere_closer = false;
-        for (int k = 0; k < wf.n_spheres; k++) {
+        int sphere_k = -1;
+        float sphere_t = h.t;
+        for (int k = 0; k < wf.n_spheres; k++) { // the closest quadric in front of the triangle hit
             SphereHit sh;
-            if (sphere_intersect(wf.spheres[k], o, d, h.t, sh)) {
+            if (sphere_intersect(wf.spheres[k], o, d, sphere_t, sh)) {
                 sphere_closer = true;
-                break;
+                sphere_k = k;
+                sphere_t = sh.t;
             }
         }
-        // an instanced object in front of whatever was found ends the walk too
-        if (INST && !sphere_closer && instances_block(wf, o, d, h.t, sm_stack, overflow)) sphere_closer = true;
+        // a quadric with a material in front of the triangle hit ends the walk with 0 whatever its exact distance; a material-less
+        // quadric is crossed like an interface triangle
+        bool cross_sphere = sphere_k >= 0 && wf.materials[wf.spheres[sphere_k].material].type == B200PT_MAT_INTERFACE;
+        // an instanced object in front of whatever was found (and would be crossed or is the end of the segment) ends the walk too
+        if (INST && (!sphere_closer || cross_sphere) && instances_block(wf, o, d, sphere_closer ? sphere_t : h.t, sm_stack, overflow)) {
+            sphere_closer = true;
+            cross_sphere = false;
+        }
         const bool hit = sphere_closer || h.prim >= 0;
-        // a sphere always carries a material here, so a sphere in front of the triangle hit ends the walk with 0 whatever
-        // its exact distance; otherwise next_t is the triangle hit
-        const float next_t = hit ? h.t : distance_to_light;
+        const float next_t = hit ? (cross_sphere ? sphere_t : h.t) : distance_to_light;
         if (medium >= 0) T = T * exp_s4(medium_sigma_t(wf, medium, lambda) * (-next_t));
         if (!hit) return T;
+        if (cross_sphere) {
+            Isect si;
+            sphere_interaction(wf.spheres[sphere_k], o, d, sphere_t, -d, si);
+            o = offset_ray_origin(si.p, si.err, d, d);
+            medium = surface_medium(wf, -2 - sphere_k, d, d, medium);
+            if (sphere_t < epsilon_distance) {
+                if (previous_self_intersection) o = o + epsilon_distance * d;
+                previous_self_intersection = true;
+            } else {
+                previous_self_intersection = false;
+            }
+            continue;
+        }
         if (sphere_closer) return s4(0.f);
         const float4 *tp = wf.bvh.tris + 3 * (size_t)h.prim;
         const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
@@ -1560,6 +1576,21 @@ __global__ void __launch_bounds__(WF_BLOCK, 4) k_logic(WF wf) {
                     dirty_L = true;
                 }
                 terminate = true;
+            }
+            if (!terminate && !stay && MEDIA && prim >= (int)wf.bvh.n_tris) {
+                const int k = prim - (int)wf.bvh.n_tris;
+                const SphereRec &sp = wf.spheres[k];
+                if (wf.materials[sp.material].type == B200PT_MAT_INTERFACE) { // a material-less quadric: as for a triangle below
+                    const V3 ro = v3(wf.pool.ray_o[slot]), rd = v3(wf.pool.ray_d[slot]);
+                    Isect si;
+                    sphere_interaction(sp, ro, rd, hit.y, -rd, si);
+                    const V3 o = offset_ray_origin(si.p, si.err, si.n, rd);
+                    wf.pool.ray_o[slot] = make_float4(o.x, o.y, o.z, kInf);
+                    vol.x = depth + 0.3f;
+                    vol.y = __int_as_float(surface_medium(wf, -2 - k, si.n, rd, __float_as_int(vol.y)));
+                    wf.pool.vol[slot] = vol;
+                    stay = true;
+                }
             }
             if (!terminate && !stay && MEDIA && prim < (int)wf.bvh.n_tris) {
                 const float4 *tp = wf.bvh.tris + 3 * (size_t)prim;

@@ -1104,8 +1104,6 @@ def load(path=None, text=None, spp=None, integrator=None, scene_dir=None, flatte
         else:
             if area_light is not None and rec["kind"] == "disk":
                 raise SceneError("emissive disks are outside the hot path")
-            if sc.materials[rec["material"]]["type"] == 7:
-                raise SceneError("interface spheres are outside the hot path")
             sc.spheres.append({"rfo": rfo_x.m, "ofr": rfo_x.inv, "radius": rec["radius"], "zmin": rec["zmin"], "zmax": rec["zmax"],
                                "phimax": rec["phimax"], "ro": rec["ro"], "swaps": swaps_handedness(rec["rfo"].m), "material": rec["material"],
                                "kind": 1 if rec["kind"] == "disk" else 0, "medium": int(rec.get("mcode", 0))})

@@ -147,7 +147,7 @@ def test_instanced_quadrics_through_the_bridge(b200pt, tmp_path):
     bridge_equals_golden_and_ctypes(b200pt, tmp_path, "instances_96x64_64spp", ctypes_tol=1e-5)
 
 
-@pytest.mark.parametrize("name,ctypes_tol", [("loopsubdiv_96x64_64spp", 1e-6), ("disk_96x64_64spp", 1e-6), ("occluders_96x64_64spp", 1e-5), ("mediaball_96x64_64spp", 5e-5),
+@pytest.mark.parametrize("name,ctypes_tol", [("loopsubdiv_96x64_64spp", 1e-6), ("disk_96x64_64spp", 1e-6), ("occluders_96x64_64spp", 1e-5), ("mediaball_96x64_64spp", 5e-5), ("smokeball_96x64_64spp", 5e-5),
                                              ("normals_96x64_64spp", 1e-3)])
 def test_remaining_scenes_through_the_bridge(b200pt, tmp_path, name, ctypes_tol):
     """the other golden scenes: Loop subdivision surfaces (the reference's own subdivision code produces the mesh the bridge reads),

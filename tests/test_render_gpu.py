@@ -167,6 +167,14 @@ def test_spheres_on_medium_transitions_match_reference(b200pt, tmp_path):
     check_against_golden(b200pt, tmp_path, "mediaball_96x64_1024spp")
 
 
+def test_material_less_quadrics_match_reference(b200pt, tmp_path):
+    """Material "interface" over Shape "sphere" (a ball of smoke with a diffuse ball inside, a clipped ball of coloured medium):
+    camera and bounce rays pass the quadric unchanged and only change medium (k_logic: depth += 0.3), NEE from scattering points
+    inside walks out through it (k_transmit crosses material-less quadrics like interface triangles)"""
+    check_against_golden(b200pt, tmp_path, "smokeball_96x64_64spp")
+    check_against_golden(b200pt, tmp_path, "smokeball_96x64_1024spp")
+
+
 def test_cornell_480x270_converged_4096spp(b200pt, tmp_path):
     """config C3's image between the 48x48 golden and full HD: 480x270 at 4096 spp against the reference's film, relMSE +
     the per-pixel 3 sigma gate (sigma_p from 16 disjoint sample ranges of ours, which also exercises the sample partition)"""

@@ -3,7 +3,7 @@
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 export B200PT_REQUIRE_GPU=1
-python tools/make_golden.py mediaball_96x64_64spp mediaball_96x64_1024spp > gpurun_out/ah_make.log 2>&1; tail -3 gpurun_out/ah_make.log
+python tools/make_golden.py smokeball_96x64_64spp smokeball_96x64_1024spp > gpurun_out/ah_make.log 2>&1; tail -3 gpurun_out/ah_make.log
 python - <<'PY'
 import json, shutil, os
 g="gpurun_out/golden"; dst="tests/golden/films"
@@ -16,5 +16,5 @@ json.dump(m,open(os.path.join(dst,"manifest.json"),"w"),indent=1)
 json.dump(m,open("gpurun_out/manifest_merged.json","w"),indent=1)
 print(sorted(new))
 PY
-python tools/measure_golden.py > gpurun_out/ah_measure.log 2>&1; grep mediaball gpurun_out/ah_measure.log
-ls gpurun_out/golden | grep mediaball
+python tools/measure_golden.py > gpurun_out/ah_measure.log 2>&1; grep smokeball gpurun_out/ah_measure.log
+ls gpurun_out/golden | grep smokeball

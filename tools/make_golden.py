@@ -80,6 +80,9 @@ CASES = [
     # spheres on medium transitions (a glass ball of dye, a diffuse-transmission ball of fog)
     ("mediaball_96x64_64spp", "mediaball.pbrt", None, 64, None, None),
     ("mediaball_96x64_1024spp", "mediaball.pbrt", None, 1024, None, None),
+    # material-less quadrics: balls of smoke behind Material "interface" (a diffuse ball inside one of them)
+    ("smokeball_96x64_64spp", "smokeball.pbrt", None, 64, None, None),
+    ("smokeball_96x64_1024spp", "smokeball.pbrt", None, 1024, None, None),
 ]
 
 
