@@ -90,6 +90,11 @@ typedef struct {
     /* FLOAT textures (base/float_texture.cu) for "uroughness" / "vroughness" ("roughness" sets both) of conductor and dielectric
      * materials (materials/conductor_material.cu:35-44, dielectric_material.cu:20-31): texture id + 1, 0 = the constants above */
     int32_t u_roughness_tex1, v_roughness_tex1;
+    /* spectrum textures for the conductor's "eta" / "k" (coated conductor: "conductor.eta" / "conductor.k"): texture id + 1, 0 = the
+     * spectrum ids above.  The reference evaluates these as Unbounded spectra (materials/conductor_material.cu:52-75); its image
+     * textures abort for that type (textures/spectrum_image_texture.cu:23-33), so the graph holds constant / scale / mix /
+     * directionmix nodes (mix amounts may be float IMAGE textures: a spatially varying blend of two metals) */
+    int32_t eta_tex1, k_tex1;
 } b200pt_material;
 
 /* ---- textures (textures/, base/{spectrum,float}_texture.cu) ---------------------------------------------------------------

@@ -30,7 +30,7 @@ class Material(C.Structure):
                 ("thickness", C.c_float), ("g", C.c_float), ("albedo", C.c_int32), ("max_depth", C.c_int32),
                 ("n_samples", C.c_int32), ("c_u_roughness", C.c_float), ("c_v_roughness", C.c_float),
                 ("c_eta", C.c_int32), ("c_k", C.c_int32), ("mix_a", C.c_int32), ("mix_b", C.c_int32), ("reflectance_tex1", C.c_int32), ("transmittance_tex1", C.c_int32),
-                ("u_roughness_tex1", C.c_int32), ("v_roughness_tex1", C.c_int32)]
+                ("u_roughness_tex1", C.c_int32), ("v_roughness_tex1", C.c_int32), ("eta_tex1", C.c_int32), ("k_tex1", C.c_int32)]
 
 
 class Light(C.Structure):

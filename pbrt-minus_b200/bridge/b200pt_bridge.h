@@ -429,8 +429,8 @@ struct B200ptBridge {
             o.type = B200PT_MAT_CONDUCTOR;
             if (p->reflectance) o.reflectance = textured(p->reflectance, &o.reflectance_tex1);
             else {
-                o.eta = constant_texture(p->eta);
-                o.k = constant_texture(p->k);
+                o.eta = textured(p->eta, &o.eta_tex1);   // Unbounded-kind graphs: constants under scale / mix / directionmix
+                o.k = textured(p->k, &o.k_tex1);
             }
             o.u_roughness = roughness(p->uRoughness, &o.u_roughness_tex1);
             o.v_roughness = roughness(p->vRoughness, &o.v_roughness_tex1);
@@ -482,8 +482,8 @@ struct B200ptBridge {
             o.c_v_roughness = constant_float(p->conductorVRoughness);
             if (p->reflectance) o.reflectance = textured(p->reflectance, &o.reflectance_tex1);
             else {
-                o.c_eta = constant_texture(p->conductorEta);
-                o.c_k = constant_texture(p->k);
+                o.c_eta = textured(p->conductorEta, &o.eta_tex1);
+                o.c_k = textured(p->k, &o.k_tex1);
             }
             o.remap_roughness = p->remapRoughness ? 1 : 0;
             o.max_depth = p->maxDepth;

@@ -166,8 +166,47 @@ using namespace b200pt;
 // AliasTable ctor (distribution/alias_table.cu:9-68): repeatedly take the smallest bin, top it up
 // from the largest.  The reference re-sorts the whole vector per step (O(n^2 log n)); an ordered
 // set gives the same extraction order (up to ties) in O(n log n), which config C4 (100 k lights) needs.
-static void build_alias(const std::vector<float> &values, std::vector<AliasBin> &bins, std::vector<float> &pdfs) {
+//
+// Ties decide the layout too: bins of EQUAL weight (the two triangles of a quad light, after both were topped up to exactly 1)
+// leave the reference's std::sort in the order its vector held them, which an ordered set keyed on (p, index) does not
+// reproduce -- and a different bin order picks a different light for the same variate.  With `replay_sort` the table is
+// built the reference's way (re-sort the remaining bins with std::sort, take the front, top it up from the back), which
+// gives the same order bin for bin because it IS the same libstdc++ sort on the same sequence; the callers ask for it
+// while the O(n^2 log n) cost is negligible and keep the ordered set beyond (C4's 100 k lights: statistical parity).
+static void build_alias(const std::vector<float> &values, std::vector<AliasBin> &bins, std::vector<float> &pdfs, bool replay_sort = false) {
     const int n = (int)values.size();
+    if (replay_sort && n > 0) {
+        double total = 0.0;
+        for (float v : values) total += v;
+        if (total != 0.0) {
+            struct R {
+                float p;
+                int first, second;
+                bool operator<(const R &o) const { return p < o.p; }
+            };
+            std::vector<R> rest(n);
+            pdfs.assign(n, 0.f);
+            for (int i = 0; i < n; i++) {
+                rest[i] = R{float(values[i] * n / total), i, -1};
+                pdfs[i] = float(values[i] / total);
+            }
+            bins.clear();
+            bins.reserve(n);
+            size_t front = 0;   // bins before `front` are done (the reference erases them; sorting the tail is the same sort)
+            while (n - front > 1) {
+                std::sort(rest.begin() + front, rest.end());
+                R &lo = rest[front];
+                if (lo.p < 1.f - 0.001f) {
+                    lo.second = rest.back().first;
+                    rest.back().p -= 1.f - lo.p;
+                }
+                bins.push_back(AliasBin{lo.p, lo.first, lo.second});
+                front++;
+            }
+            bins.push_back(AliasBin{rest[front].p, rest[front].first, rest[front].second});
+            return;
+        }
+    }
     bins.assign(n, AliasBin{1.f, 0, -1});
     pdfs.assign(n, 0.f);
     double sum = 0.0;
@@ -349,9 +388,10 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
         const b200pt_material &m = desc->materials[i];
         mats[i] = MatRec{m.type, m.reflectance, m.eta, m.k, m.u_roughness, m.v_roughness, m.remap_roughness, m.transmittance, m.scale,
                          m.thickness, m.g, m.albedo, m.max_depth, m.n_samples, m.c_u_roughness, m.c_v_roughness, m.c_eta, m.c_k, m.mix_a, m.mix_b,
-                         m.reflectance_tex1, m.transmittance_tex1, m.u_roughness_tex1, m.v_roughness_tex1};
+                         m.reflectance_tex1, m.transmittance_tex1, m.u_roughness_tex1, m.v_roughness_tex1, m.eta_tex1, m.k_tex1};
         if (m.reflectance_tex1 < 0 || m.reflectance_tex1 > desc->n_textures || m.transmittance_tex1 < 0 || m.transmittance_tex1 > desc->n_textures ||
-            m.u_roughness_tex1 < 0 || m.u_roughness_tex1 > desc->n_textures || m.v_roughness_tex1 < 0 || m.v_roughness_tex1 > desc->n_textures) {
+            m.u_roughness_tex1 < 0 || m.u_roughness_tex1 > desc->n_textures || m.v_roughness_tex1 < 0 || m.v_roughness_tex1 > desc->n_textures ||
+            m.eta_tex1 < 0 || m.eta_tex1 > desc->n_textures || m.k_tex1 < 0 || m.k_tex1 > desc->n_textures) {
             set_error("b200pt_scene_create: material %d names a texture that does not exist", i);
             return B200PT_ERR_INVALID;
         }
@@ -370,8 +410,9 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
             ok = refl_ok() && spec_ok(m.eta) && spec_ok(m.albedo) && m.max_depth >= 0 && m.n_samples >= 1;
         else if (m.type == B200PT_MAT_COATED_CONDUCTOR)
             ok = spec_ok(m.eta) && spec_ok(m.albedo) && m.max_depth >= 0 && m.n_samples >= 1 &&
-                 ((spec_ok(m.c_eta) && spec_ok(m.c_k)) || (m.c_eta < 0 && refl_ok()));
-        else if (m.type == B200PT_MAT_CONDUCTOR) ok = (spec_ok(m.eta) && spec_ok(m.k)) || (m.eta < 0 && refl_ok());
+                 (((spec_ok(m.c_eta) || m.eta_tex1 > 0) && (spec_ok(m.c_k) || m.k_tex1 > 0)) || (m.c_eta < 0 && m.eta_tex1 == 0 && refl_ok()));
+        else if (m.type == B200PT_MAT_CONDUCTOR)
+            ok = ((spec_ok(m.eta) || m.eta_tex1 > 0) && (spec_ok(m.k) || m.k_tex1 > 0)) || (m.eta < 0 && m.eta_tex1 == 0 && refl_ok());
         else if (m.type == B200PT_MAT_DIELECTRIC) ok = spec_ok(m.eta);
         else if (m.type == B200PT_MAT_INTERFACE) ok = desc->n_media > 0; // only meaningful between media
         else ok = false;
@@ -589,17 +630,19 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
                     if (v < threshold) v = 0.f;
                 std::vector<float> col(W), ypdf((size_t)W * H), xpdf;
                 std::vector<AliasBin> ybins((size_t)W * H), xbins;
+                // small maps get the reference's own tie order (see build_alias): ~W * H^2 log H / 2 comparisons
+                const bool replay_env = (double)W * H * H * 4.0 <= 3e7;
                 for (int x = 0; x < W; x++) {
                     float sum = 0.f;
                     for (int y = 0; y < H; y++) sum += lum[(size_t)x * H + y];
                     col[x] = sum;
                     std::vector<float> vals(lum.begin() + (size_t)x * H, lum.begin() + (size_t)(x + 1) * H), pd;
                     std::vector<AliasBin> bn;
-                    build_alias(vals, bn, pd);
+                    build_alias(vals, bn, pd, replay_env);
                     std::copy(bn.begin(), bn.end(), ybins.begin() + (size_t)x * H);
                     std::copy(pd.begin(), pd.end(), ypdf.begin() + (size_t)x * H);
                 }
-                build_alias(col, xbins, xpdf);
+                build_alias(col, xbins, xpdf, W <= 2048);
                 AliasBin *d_xb = nullptr, *d_yb = nullptr;
                 float *d_xp = nullptr, *d_yp = nullptr;
                 if ((rc = dev_upload(r, &d_xb, xbins.data(), xbins.size(), st))) return rc;
@@ -724,7 +767,7 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
         CU_TRY(cudaStreamSynchronize(st));
         std::vector<AliasBin> bins;
         std::vector<float> pdfs;
-        build_alias(w, bins, pdfs);
+        build_alias(w, bins, pdfs, desc->n_lights <= 2048);
         for (int i = 0; i < desc->n_lights; i++) lights[i].pmf = pdfs[i];
         if (getenv("B200PT_DEBUG_LIGHTS"))
             for (int i = 0; i < desc->n_lights && i < 64; i++)
@@ -1738,9 +1781,9 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_CONDUCTOR>(const WF &wf, co
         ur = sqrtf(ur);
         vr = sqrtf(vr);
     }
-    if (m.eta >= 0) {
-        b.eta = spectrum_sample(wf.spectra, m.eta, lambda);
-        b.k = spectrum_sample(wf.spectra, m.k, lambda);
+    if (m.eta >= 0 || m.eta_tex1 > 0) {
+        b.eta = material_spectrum(wf, m.eta, m.eta_tex1, si, lambda, ext);
+        b.k = material_spectrum(wf, m.k, m.k_tex1, si, lambda, ext);
     } else {
         const S4 r = clamp_s4(material_spectrum(wf, m.reflectance, m.reflectance_tex1, si, lambda, ext), 0.f, 0.9999f);
         b.eta = s4(1.f);
@@ -1828,9 +1871,9 @@ __device__ __forceinline__ void make_bsdf<B200PT_MAT_COATED_CONDUCTOR>(const WF 
     // materials/coated_conductor_material.cu:92-141
     make_coat(wf, m, lambda, lpdf, lpdf_dirty, ext, b);
     S4 ce, ck;
-    if (m.c_eta >= 0) {
-        ce = spectrum_sample(wf.spectra, m.c_eta, lambda);
-        ck = spectrum_sample(wf.spectra, m.c_k, lambda);
+    if (m.c_eta >= 0 || m.eta_tex1 > 0) {
+        ce = material_spectrum(wf, m.c_eta, m.eta_tex1, si, lambda, ext);
+        ck = material_spectrum(wf, m.c_k, m.k_tex1, si, lambda, ext);
     } else {
         const S4 r = clamp_s4(material_spectrum(wf, m.reflectance, m.reflectance_tex1, si, lambda, ext), 0.f, 0.9999f);
         ce = s4(1.f);

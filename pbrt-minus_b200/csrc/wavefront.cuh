@@ -29,6 +29,7 @@ struct MatRec {
     int32_t mix_a, mix_b;         // mix material: the two material ids; `scale` holds the amount
     int32_t reflectance_tex1, transmittance_tex1; // spectrum texture id + 1 (0: the spectrum id is used)
     int32_t u_rough_tex1, v_rough_tex1;           // float texture id + 1 for the roughnesses (0: the constants)
+    int32_t eta_tex1, k_tex1;                     // spectrum texture id + 1 for the conductor's eta / k (0: the spectrum ids)
 };
 constexpr int WF_NMAT = B200PT_MAT_COUNT; // one shading queue per material type
 

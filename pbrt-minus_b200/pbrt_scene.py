@@ -379,6 +379,9 @@ class Scene:
         self.N, self.uv, self.any_N, self.any_uv = [], [], False, False
         self.media, self.tri_medium, self.camera_medium = [], [], -1
         self.textures, self.images, self.named_spec_tex, self.named_float_tex, self._image_ids = [], [], {}, {}, {}
+        # the reference instantiates every spectrum Texture once per SpectrumType (scene_builder.cu:679-708); here: the albedo graph
+        # (reflectance / transmittance) in named_spec_tex and the unbounded one (conductor eta / k) in named_spec_tex_unbounded
+        self.named_spec_tex_unbounded = {}
         self.n_verts = 0
         self.spheres, self.spectra, self.materials, self.lights = [], [], [], []
         self.camera = self.filter = self.film = None
@@ -425,7 +428,7 @@ class Scene:
             return None
         t, v = p[name]
         if t == "texture":          # resolved by material_texture(); the spectrum slot gets a placeholder
-            if name not in ("reflectance", "transmittance"):
+            if name not in ("reflectance", "transmittance", "eta", "k", "conductor.eta", "conductor.k"):
                 raise SceneError("a texture for '%s' is outside the hot path" % name)
             return self.spec_constant(0.5)
         if t == "rgb":
@@ -471,15 +474,22 @@ class Scene:
         self._image_ids[path] = len(self.images) - 1
         return self._image_ids[path]
 
-    def spectrum_texture_param(self, p, key, scene_dir, default=None):
+    def spec_tex_table(self, kind):
+        return self.named_spec_tex if kind == "albedo" else self.named_spec_tex_unbounded
+
+    def spectrum_texture_param(self, p, key, scene_dir, default=None, kind="albedo"):
         """ParameterDictionary::get_spectrum_texture (parameter_dictionary.cu:276-330): a named texture, or a constant one"""
         if key in p:
             t, v = p[key]
             if t == "texture":
-                if str(v[0]) not in self.named_spec_tex:
+                table = self.spec_tex_table(kind)
+                if str(v[0]) not in table:
                     raise SceneError("spectrum texture '%s' not defined" % v[0])
-                return self.named_spec_tex[str(v[0])]
-            return self._tex(0, a=self.spec_param(p, key, "albedo", scene_dir))
+                if table[str(v[0])] is None:
+                    raise SceneError("texture '%s' holds an image: the reference's image textures abort for %s spectra "
+                                     "(textures/spectrum_image_texture.cu:23-33)" % (v[0], kind))
+                return table[str(v[0])]
+            return self._tex(0, a=self.spec_param(p, key, kind, scene_dir))
         return None if default is None else self._tex(0, a=self.spec_constant(default))
 
     def float_texture_param(self, p, key, default):
@@ -529,23 +539,32 @@ class Scene:
             return
         if color_type != "spectrum":
             raise SceneError("Texture colour type '%s' (scene_builder.cu:706-707)" % color_type)
+        self.named_spec_tex[name] = self._spectrum_texture(tex_type, p, render_from_texture, scene_dir, "albedo")
+        try:    # the unbounded instantiation of the same directive (conductor eta / k); images and their users have none
+            self.named_spec_tex_unbounded[name] = self._spectrum_texture(tex_type, p, render_from_texture, scene_dir, "unbounded")
+        except SceneError:
+            self.named_spec_tex_unbounded[name] = None
+
+    def _spectrum_texture(self, tex_type, p, render_from_texture, scene_dir, kind):
         if tex_type == "constant":
-            v = self.spec_param(p, "value", "albedo", scene_dir)
+            v = self.spec_param(p, "value", kind, scene_dir)
             tid = self._tex(0, a=self.spec_constant(1.0) if v is None else v)
         elif tex_type == "imagemap":
+            if kind != "albedo":
+                raise SceneError("image textures abort in the reference for %s spectra (textures/spectrum_image_texture.cu:23-33)" % kind)
             tid = self._image_node(1, p, scene_dir, render_from_texture)
         elif tex_type == "scale":
-            t = self.spectrum_texture_param(p, "tex", scene_dir)
+            t = self.spectrum_texture_param(p, "tex", scene_dir, kind=kind)
             if t is None:
                 raise SceneError("scale texture without \"tex\"")
             tid = self._tex(2, a=t, f=(p_float(p, "scale", 1.0), 0, 0, 0))
         elif tex_type == "mix":
-            t1 = self.spectrum_texture_param(p, "tex1", scene_dir, 0.0)
-            t2 = self.spectrum_texture_param(p, "tex2", scene_dir, 1.0)
+            t1 = self.spectrum_texture_param(p, "tex1", scene_dir, 0.0, kind=kind)
+            t2 = self.spectrum_texture_param(p, "tex2", scene_dir, 1.0, kind=kind)
             tid = self._tex(3, a=t1, b=t2, c=self.float_texture_param(p, "amount", 0.5))
         elif tex_type == "directionmix":
-            t1 = self.spectrum_texture_param(p, "tex1", scene_dir, 0.0)
-            t2 = self.spectrum_texture_param(p, "tex2", scene_dir, 1.0)
+            t1 = self.spectrum_texture_param(p, "tex1", scene_dir, 0.0, kind=kind)
+            t2 = self.spectrum_texture_param(p, "tex2", scene_dir, 1.0, kind=kind)
             d = np.asarray(p["dir"][1][:3] if "dir" in p else (0, 1, 0), dtype=F32)
             d = xf_vectors(render_from_texture.m, d.reshape(1, 3))[0]
             d = (d / F32(np.sqrt(F32(F32(d[0] * d[0]) + F32(d[1] * d[1])) + F32(d[2] * d[2])))).astype(F32)
@@ -558,15 +577,12 @@ class Scene:
                              "every textured pixel is NaN and the render aborts; nothing to reproduce")
         else:
             raise SceneError("spectrum texture '%s' is not a reference texture (base/spectrum_texture.cu:9-58)" % tex_type)
-        self.named_spec_tex[name] = tid
+        return tid
 
-    def material_texture(self, p, key):
+    def material_texture(self, p, key, kind="albedo"):
         """texture id + 1 when the material parameter names a texture, else 0"""
         if key in p and p[key][0] == "texture":
-            name = str(p[key][1][0])
-            if name not in self.named_spec_tex:
-                raise SceneError("spectrum texture '%s' not defined" % name)
-            return self.named_spec_tex[name] + 1
+            return self.spectrum_texture_param(p, key, None, kind=kind) + 1
         return 0
 
     # ---- materials
@@ -577,6 +593,11 @@ class Scene:
             m = self.materials[-1]
             m["reflectance_tex1"] = self.material_texture(p, "reflectance") if m["type"] in (0, 1, 3, 4, 5) else 0
             m["transmittance_tex1"] = self.material_texture(p, "transmittance") if m["type"] == 3 else 0
+            if m["type"] == 1:        # conductor_material.cu:52-75: eta / k are Unbounded spectrum textures
+                m["eta_tex1"], m["k_tex1"] = self.material_texture(p, "eta", "unbounded"), self.material_texture(p, "k", "unbounded")
+            elif m["type"] == 5:      # coated_conductor_material.cu:26-90
+                m["eta_tex1"] = self.material_texture(p, "conductor.eta", "unbounded")
+                m["k_tex1"] = self.material_texture(p, "conductor.k", "unbounded")
             if m["type"] in (1, 2):   # conductor_material.cu:35-44, dielectric_material.cu:20-31: "uroughness" else "roughness"
                 for fld, key in (("ur_tex1", "uroughness"), ("vr_tex1", "vroughness")):
                     k = key if key in p else "roughness"
@@ -908,6 +929,7 @@ class Scene:
             mats[i].mix_a, mats[i].mix_b = m.get("mix_a", -1), m.get("mix_b", -1)
             mats[i].reflectance_tex1, mats[i].transmittance_tex1 = m.get("reflectance_tex1", 0), m.get("transmittance_tex1", 0)
             mats[i].u_roughness_tex1, mats[i].v_roughness_tex1 = m.get("ur_tex1", 0), m.get("vr_tex1", 0)
+            mats[i].eta_tex1, mats[i].k_tex1 = m.get("eta_tex1", 0), m.get("k_tex1", 0)
         d.n_materials, d.materials = len(self.materials), mats
         lights = (api.Light * max(1, len(self.lights)))()
         for i, l in enumerate(self.lights):

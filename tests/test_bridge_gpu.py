@@ -135,6 +135,8 @@ def test_textures_through_the_bridge(b200pt, tmp_path):
     own init_tables"""
     bridge_equals_golden_and_ctypes(b200pt, tmp_path, "textures_96x64_64spp", ctypes_tol=1e-6)
     bridge_equals_golden_and_ctypes(b200pt, tmp_path, "textures2_96x64_64spp", ctypes_tol=1e-6)
+    # spectrum textures on conductor eta / k: the Unbounded texture objects the reference's ConductorMaterial holds
+    bridge_equals_golden_and_ctypes(b200pt, tmp_path, "metals_96x64_64spp", ctypes_tol=1e-6)
     # LightSource "infinite" with an image (lights/image_infinite_light.cu): the environment map's pixels and transform
     # (1.3e-7 from the reference's film where the Python front-end's description gives 6e-12: the bridge hands over the reference's
     # numerically inverted light transform, the Python side the exact transpose of the rotation)

@@ -258,6 +258,28 @@ def test_texture_mappings_and_roughness_textures_match_reference(b200pt, tmp_pat
     check_against_golden(b200pt, tmp_path, "textures2_96x64_1024spp")
 
 
+def test_conductor_eta_k_textures_match_reference(b200pt, tmp_path):
+    """spectrum TEXTURES on the conductor's "eta" / "k" (materials/conductor_material.cu:11-12): the Unbounded instantiation of
+    each Texture directive (scene/scene_builder.cu:699-701) -- named-metal constants under "mix" (amount = a float image),
+    "scale", "directionmix" (under the directive's own transform) and an rgb constant (an RGBUnboundedSpectrum); one material
+    with only k textured.  The scene's two quad lights also pin the alias table's order among bins of EQUAL weight
+    (distribution/alias_table.cu:43-63): four triangle lights that tie pairwise, where the order std::sort leaves ties in
+    decides which light a variate selects (before that order was replayed: relMSE 1e-3 on the bare room, now 3e-8)."""
+    check_against_golden(b200pt, tmp_path, "metals_96x64_64spp")
+    check_against_golden(b200pt, tmp_path, "metals_96x64_1024spp")
+
+
+def test_coated_conductor_eta_k_textures_statistical_gate(b200pt, tmp_path):
+    """the same mix textures as "conductor.eta" / "conductor.k" of a coatedconductor (coated_conductor_material.cu:56-57);
+    LayeredBxDF walks are hash-seeded, so this is the statistical gate of test_coated_materials_statistical_gate"""
+    m, ref = golden("metals_coated_96x64_1024spp")
+    p = os.path.join(str(tmp_path), "metals_coated.pbrt")
+    open(p, "w").write(scene_text(m["scene"], None, None, [tuple(e) for e in m.get("edits", [])]))
+    import shutil
+    shutil.copytree(os.path.join(ROOT, "tests", "scenes", "textures"), os.path.join(str(tmp_path), "textures"), dirs_exist_ok=True)
+    statistical_gate(b200pt, p, m, ref)
+
+
 def test_device_srgb8_equals_the_reference_encoding(b200pt, tmp_path):
     """b200pt_film_read_srgb8: Film::write_to_png's pixel loop on the device (base/film.cu:57-99) with the reference's minimax
     sRGB curve (spectrum_util/color_encoding.h:6-45), against a float64 restatement of that curve on the host"""

@@ -83,6 +83,13 @@ CASES = [
     # material-less quadrics: balls of smoke behind Material "interface" (a diffuse ball inside one of them)
     ("smokeball_96x64_64spp", "smokeball.pbrt", None, 64, None, None),
     ("smokeball_96x64_1024spp", "smokeball.pbrt", None, 1024, None, None),
+    # spectrum textures (mix over a float image, scale, directionmix, constant) on conductor / coatedconductor eta and k
+    ("metals_96x64_64spp", "metals.pbrt", None, 64, None, None),
+    ("metals_96x64_1024spp", "metals.pbrt", None, 1024, None, None),
+    # the same textures under a coating (LayeredBxDF walks are hash-seeded: a statistical golden, like coated.pbrt)
+    ("metals_coated_96x64_1024spp", "metals.pbrt", None, 1024, None, None,
+     [('Material "conductor" "texture eta" ["inlay-eta"] "texture k" ["inlay-k"] "float roughness" [0.12]',
+       'Material "coatedconductor" "texture conductor.eta" ["inlay-eta"] "texture conductor.k" ["inlay-k"] "float interface.roughness" [0.02] "float conductor.roughness" [0.1] "float thickness" [0.02]')]),
 ]
 
 

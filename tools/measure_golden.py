@@ -13,7 +13,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
-STATISTICAL = ("coated_", "mix_", "c4tiny_")   # compared as two unbiased estimators (tests: statistical_gate)
+STATISTICAL = ("coated_", "mix_", "c4tiny_", "metals_coated_")   # compared as two unbiased estimators (tests: statistical_gate)
 
 
 def main():
