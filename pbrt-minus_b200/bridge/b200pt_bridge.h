@@ -44,6 +44,9 @@
 #include <pbrt/base/spectrum_texture.h>
 #include <pbrt/cameras/perspective.h>
 #include <pbrt/integrators/wavefront_path.h>
+#include <pbrt/distribution/alias_table.h>
+#include <pbrt/distribution/distribution_1d.h>
+#include <pbrt/light_samplers/power_light_sampler.h>
 #include <pbrt/lights/diffuse_area_light.h>
 #include <pbrt/lights/distant_light.h>
 #include <pbrt/lights/image_infinite_light.h>
@@ -837,6 +840,23 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
         for (size_t i = 0; i < b.spectra.size(); i++)
             fprintf(stderr, "spectrum %zu: type %d c %g %g %g %g n %d\n", i, b.spectra[i].type, b.spectra[i].c[0], b.spectra[i].c[1], b.spectra[i].c[2],
                     b.spectra[i].c[3], b.spectra[i].n);
+        for (int i = 0; i < 471; i++) {
+            uint32_t bits;
+            memcpy(&bits, &fd.illuminant[i], 4);
+            fprintf(stderr, "[refillum] %d %08x\n", i, bits);
+        }
+        for (size_t i = 0; i < lights.size(); i++) {
+            uint32_t bits;
+            memcpy(&bits, &lights[i].scale, 4);
+            fprintf(stderr, "[reflightrec] %zu tri %d spectrum %d scale %08x two_sided %d\n", i, lights[i].triangle, lights[i].spectrum, bits, lights[i].two_sided);
+        }
+        // the reference's own light sampler table, bin by bin, in the format of the library's B200PT_DEBUG_LIGHTS lines
+        if (const PowerLightSampler *ls = sb.integrator_base->light_sampler; ls && ls->light_num > 0) {
+            const AliasTable *at = ls->lights_power_distribution->alias_table;
+            for (int i = 0; i < at->size && i < 4096; i++)
+                fprintf(stderr, "[reflight] %d pdf %.9g bin p %.9g first %d second %d\n", i, (double)at->pdfs[i], (double)at->bins[i].p,
+                        at->bins[i].first_idx, at->bins[i].second_idx);
+        }
     }
     d.n_lights = (int32_t)lights.size();
     d.lights = lights.data();

@@ -163,6 +163,92 @@ __global__ void k_light_power(SpectrumTable tab, const LightRec *lights, const L
 
 using namespace b200pt;
 
+// ---- the light sampler's weights as the reference's HOST constructor rounds them (light_samplers/power_light_sampler.cu:15-21) --
+// The weights decide the ORDER of the alias-table bins, so two lights whose powers differ in the last bit -- or tie -- on the
+// host must do the same here: host compilers do not contract a * b + c (the device does), hence 1 + x * x in the sigmoid and
+// (1 - t) * a + t * b in the table lookups are restated in plain C++ (fma only where the reference writes FMA itself).
+static float host_sigmoid_poly(const float *c, float lambda) { // spectrum_util/rgb_sigmoid_polynomial.h:14-37
+    const float x = std::fma(lambda, std::fma(lambda, c[0], c[1]), c[2]);
+    if (std::isinf(x)) return x > 0.f ? 1.f : 0.f;
+    const float xx = x * x;
+    const float root = std::sqrt(1.f + xx);
+    return 0.5f + x / (2.f * root);
+}
+static float host_lerp(float t, float a, float b) { // util/math.h:74-76
+    const float l = (1.f - t) * a, h = t * b;
+    return l + h;
+}
+static float host_dense_lookup(const float *v, float lambda) { // spectra/densely_sampled_spectrum.h:46-55
+    const int fl = (int)std::floor(lambda), ce = (int)std::ceil(lambda);
+    if (fl < 360 || ce > 830) return 0.f;
+    return host_lerp(lambda - (float)fl, v[fl - 360], v[ce - 360]);
+}
+static float host_piecewise_lookup(const float *lam, const float *val, int n, float lambda) { // spectra/piecewise_linear_spectrum.cu:93-103
+    if (n == 0 || lambda < lam[0] || lambda > lam[n - 1]) return 0.f;
+    int size = n - 2, first = 1;
+    while (size > 0) { // find_interval (util/math.h:129-141)
+        const int half = size >> 1, middle = first + half;
+        const bool pred = lam[middle] <= lambda;
+        first = pred ? middle + 1 : first;
+        size = pred ? size - (half + 1) : half;
+    }
+    int o = first - 1;
+    o = o < 0 ? 0 : (o > n - 2 ? n - 2 : o);
+    const float t = (lambda - lam[o]) / (lam[o + 1] - lam[o]);
+    return host_lerp(t, val[o], val[o + 1]);
+}
+static float host_spectrum_at(const std::vector<SpecRec> &spec, const std::vector<float> &pool, const float *illuminant, int id, float lambda) {
+    const SpecRec &r = spec[id];
+    switch (r.type) {
+    case B200PT_SPEC_CONSTANT: return r.c[0];
+    case B200PT_SPEC_RGB_ALBEDO: return host_sigmoid_poly(r.c, lambda);
+    case B200PT_SPEC_RGB_UNBOUNDED: return r.c[3] * host_sigmoid_poly(r.c, lambda);
+    case B200PT_SPEC_RGB_ILLUMINANT: {
+        const float a = r.c[3] * host_sigmoid_poly(r.c, lambda);
+        return a * host_dense_lookup(illuminant, lambda);
+    }
+    case B200PT_SPEC_PIECEWISE: return host_piecewise_lookup(pool.data() + r.offset, pool.data() + r.offset + r.n, r.n, lambda);
+    case B200PT_SPEC_DENSE: return host_dense_lookup(pool.data() + r.offset, lambda);
+    }
+    return 0.f;
+}
+// phi(lambda).safe_div(pdf).average() of one light; false for the kinds that stay on the device (image infinite lights)
+static bool host_light_weight(const LightRec &L, const std::vector<LightExt> &ext, const std::vector<SpecRec> &spec, const std::vector<float> &pool,
+                              const float *illuminant, float scene_radius, const float *lambda, const float *pdf, float *out) {
+    float f;
+    bool scaled_le = true; // Le = sample(lambda) * scale first, then the geometric factor
+    switch (light_type(L)) {
+    case B200PT_LIGHT_IMAGE_INFINITE: return false;
+    case B200PT_LIGHT_DISTANT: f = scene_radius * scene_radius; break;
+    case B200PT_LIGHT_UNIFORM_INFINITE:
+        f = 4.f * kPi * kPi * (scene_radius * scene_radius) * L.scale;
+        scaled_le = false;
+        break;
+    case B200PT_LIGHT_SPOT: {
+        const LightExt &e = ext[L.ext];
+        f = 0.f; // applied in two steps below, as the device kernel does
+        float sum = 0.f;
+        for (int i = 0; i < 4; i++) {
+            float le = L.spectrum >= 0 ? host_spectrum_at(spec, pool, illuminant, L.spectrum, lambda[i]) * L.scale : 0.f;
+            le = le * 2.f * kPi * ((1.f - e.cos_start) + (e.cos_start - e.cos_end) / 2.f);
+            sum += pdf[i] == 0.f ? 0.f : le / pdf[i];
+        }
+        *out = sum / 4.f;
+        return true;
+    }
+    default: f = kPi * ((L.flags & 1) ? 2.f : 1.f) * L.area; // lights/diffuse_area_light.cu:130-134
+    }
+    float sum = 0.f;
+    for (int i = 0; i < 4; i++) {
+        float le = L.spectrum >= 0 ? host_spectrum_at(spec, pool, illuminant, L.spectrum, lambda[i]) : 0.f;
+        if (scaled_le) le = L.spectrum >= 0 ? le * L.scale : 0.f;
+        const float phi = le * f;
+        sum += pdf[i] == 0.f ? 0.f : phi / pdf[i];
+    }
+    *out = sum / 4.f;
+    return true;
+}
+
 // AliasTable ctor (distribution/alias_table.cu:9-68): repeatedly take the smallest bin, top it up
 // from the largest.  The reference re-sorts the whole vector per step (O(n^2 log n)); an ordered
 // set gives the same extraction order (up to ties) in O(n log n), which config C4 (100 k lights) needs.
@@ -765,12 +851,28 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
                                                                   make_float4(hp[0], hp[1], hp[2], hp[3]), d_w, r->env, r->tex);
         CU_TRY(cudaMemcpyAsync(w.data(), d_w, w.size() * 4, cudaMemcpyDeviceToHost, st));
         CU_TRY(cudaStreamSynchronize(st));
+        // every kind but the image infinite light (a sum over the map through the device's fit table) is re-evaluated with the
+        // host's rounding, which is what the reference's constructor sees; B200PT_LIGHT_WEIGHTS=device keeps the kernel's values
+        const char *lw = getenv("B200PT_LIGHT_WEIGHTS");
+        if (!(lw && !strcmp(lw, "device"))) {
+            int moved = 0;
+            for (int i = 0; i < desc->n_lights; i++) {
+                float hw;
+                if (host_light_weight(lights[i], ext, spec, pool, fd.illuminant, r->scene_radius, hl, hp, &hw)) {
+                    moved += hw != w[i];
+                    w[i] = hw;
+                }
+            }
+            if (getenv("B200PT_DEBUG_LIGHTS")) fprintf(stderr, "[lightdbg] %d of %d weights differ between host and device rounding\n", moved, desc->n_lights);
+        }
         std::vector<AliasBin> bins;
         std::vector<float> pdfs;
-        build_alias(w, bins, pdfs, desc->n_lights <= 2048);
+        // B200PT_ALIAS_REPLAY_MAX moves the limit (the reference itself spends minutes there at 100 k lights)
+        const char *rm = getenv("B200PT_ALIAS_REPLAY_MAX");
+        build_alias(w, bins, pdfs, desc->n_lights <= (rm ? atoi(rm) : 4096));
         for (int i = 0; i < desc->n_lights; i++) lights[i].pmf = pdfs[i];
         if (getenv("B200PT_DEBUG_LIGHTS"))
-            for (int i = 0; i < desc->n_lights && i < 64; i++)
+            for (int i = 0; i < desc->n_lights && i < 4096; i++)
                 fprintf(stderr, "[lightdbg] %d weight %.9g pdf %.9g bin p %.9g first %d second %d\n", i, (double)w[i], (double)pdfs[i],
                         (double)bins[i].p, bins[i].first, bins[i].second);
         CU_TRY(cudaMemcpyAsync(r->d_lights, lights.data(), lights.size() * sizeof(LightRec), cudaMemcpyHostToDevice, st));

@@ -863,12 +863,13 @@ class Scene:
         rec = self.spectra[spec_id]
         y = spectral.cie_xyz()[1]
         grid = np.arange(360, 831)
+        # fp32 running sums over 360..830 nm, as the reference's inner_product loops round them
         if rec["type"] == 3:
-            return F32(spectral.inner_product_dense(spectral.illuminant_d65()[2], y))
+            return spectral.inner_product32(spectral.illuminant_d65()[2], y)
         if rec["type"] == 4:
-            return F32(spectral.inner_product_dense(spectral.piecewise_eval(rec["lambda"], rec["value"], grid), y))
+            return spectral.inner_product32(spectral.piecewise_eval32(rec["lambda"], rec["value"], grid), y)
         if rec["type"] == 0:
-            return F32(rec["c"][0] * float(np.sum(y.astype(np.float64))))
+            return spectral.inner_product32(np.full(471, rec["c"][0], dtype=F32), y)
         raise SceneError("to_photometric: unsupported spectrum type")
 
     # ---- to the C-ABI

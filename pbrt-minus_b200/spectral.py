@@ -39,6 +39,31 @@ def piecewise_eval(lam, val, x):
     return np.where((x < lam[0]) | (x > lam[-1]), 0.0, y)
 
 
+def piecewise_eval32(lam, val, x):
+    """PiecewiseLinearSpectrum::operator() (spectra/piecewise_linear_spectrum.cu:93-103) in the reference's fp32 arithmetic, one
+    rounding per operation: t = (x - l0) / (l1 - l0), then lerp = (1 - t) * a + t * b (util/math.h:74-76).  The colour space's
+    illuminant and every light's photometric scale come out of this, so it has to round the way the reference's host does."""
+    lam, val = _f32(lam), _f32(val)
+    x = _f32(x)
+    n = len(lam)
+    o = np.clip(np.searchsorted(lam, x, side="right") - 1, 0, n - 2)     # find_interval: the last knot <= x, clamped to [0, n - 2]
+    l0, l1, a, b = lam[o], lam[o + 1], val[o], val[o + 1]
+    t = ((x - l0).astype(np.float32) / (l1 - l0).astype(np.float32)).astype(np.float32)
+    lo = ((np.float32(1) - t).astype(np.float32) * a).astype(np.float32)
+    hi = (t * b).astype(np.float32)
+    y = (lo + hi).astype(np.float32)
+    return np.where((x < lam[0]) | (x > lam[-1]), np.float32(0), y).astype(np.float32)
+
+
+def inner_product32(a, b):
+    """Spectrum::inner_product (e.g. spectra/densely_sampled_spectrum.h:17-24): an fp32 running sum of fp32 products over the
+    integer wavelengths 360..830"""
+    acc = np.float32(0)
+    for p, q in zip(_f32(a), _f32(b)):
+        acc = np.float32(acc + np.float32(p * q))
+    return acc
+
+
 def interleaved_to_knots(samples):
     """spectra/piecewise_linear_spectrum.cu:5-27: extend to [360, 830] with constant ends."""
     s = np.asarray(samples, dtype=np.float32)
@@ -66,13 +91,10 @@ def illuminant_d65():
     lam, val = interleaved_to_knots(tables()["illum_d65_interleaved"])
     grid = np.arange(LAMBDA_MIN, LAMBDA_MAX + 1)
     y = cie_xyz()[1]
-    acc = np.float32(0)
-    v = _f32(piecewise_eval(lam, val, grid))
-    for a, b in zip(v, y):   # fp32 running sum, as inner_product does
-        acc = np.float32(acc + np.float32(a * b))
-    scale = np.float32(CIE_Y_INTEGRAL / acc)
+    acc = inner_product32(piecewise_eval32(lam, val, grid), y)
+    scale = np.float32(np.float32(CIE_Y_INTEGRAL) / acc)
     val = _f32(val * scale)
-    dense = _f32(piecewise_eval(lam, val, grid))
+    dense = piecewise_eval32(lam, val, grid)
     return lam, val, dense
 
 
