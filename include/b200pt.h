@@ -341,7 +341,9 @@ int b200pt_trace_counters(b200pt_scene *scene, int64_t out[3]);
  * of k_trace refills (1/4/8/16), 1 = triangle tests per triangle phase (1..3), 2 = resident CTAs per SM cap
  * (0 = occupancy limit), 3 / 4 = the same two knobs for the wavefront integrator's trace kernels (0 = default),
  * 5 = resident CTAs per SM the plain shade kernels' register allocation is held to (0 = default, 3, 4),
- * 6 = k_trace with a one-deep triangle stash (0 / 1). */
+ * 6 = k_trace with a one-deep triangle stash (0 / 1), 7 = MB of BVH-build scratch a scene keeps between builds (default 16384;
+ * a rebuild reuses the previous build's scratch, node and leaf-record arrays while they fit; 0 = allocate and free per build,
+ * and a value below what is held releases it at once). */
 int b200pt_trace_tune(b200pt_scene *scene, int key, int value);
 void *b200pt_scene_stream(b200pt_scene *scene); /* cudaStream_t the scene launches on */
 int b200pt_scene_sync(b200pt_scene *scene);

@@ -210,7 +210,7 @@ B200PT_API void b200pt_scene_destroy(b200pt_scene *s) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     free_render(s);
     void *ptrs[] = {s->d_instances, s->d_scratch, s->d_P, s->d_N, s->d_uv, s->d_idx, s->d_tri_material, s->d_tri_light, s->d_tri_flip, s->d_spheres,
-                    s->d_nodes, s->d_tris, s->d_sorted_keys, s->d_sorted_prim, s->d_trace_counters};
+                    s->d_nodes, s->d_tris, s->d_sorted_keys, s->d_sorted_prim, s->d_trace_counters, s->build_scratch};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     for (void *p : s->user_allocs) cudaFree(p);
@@ -492,6 +492,16 @@ B200PT_API int b200pt_trace_tune(b200pt_scene *s, int key, int value) {
     case 4: s->tune_wf_tri_steps = value > 3 ? 3 : value; break;
     case 5: s->tune_shade_occ = value; break;
     case 6: s->tune_stash = value != 0; break;
+    case 7: // MB of build scratch a scene keeps between builds; lowering it below what is held releases the scratch now
+        s->tune_build_scratch_mb = value;
+        if (s->build_scratch && s->build_scratch_bytes > (size_t)value << 20) {
+            CU_TRY(cudaSetDevice(s->device));
+            CU_TRY(cudaStreamSynchronize(s->stream));
+            cudaFree(s->build_scratch);
+            s->build_scratch = nullptr;
+            s->build_scratch_bytes = 0;
+        }
+        break;
     default: set_error("b200pt_trace_tune: unknown key %d", key); return B200PT_ERR_INVALID;
     }
     return B200PT_OK;

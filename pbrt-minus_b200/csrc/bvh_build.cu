@@ -786,8 +786,9 @@ namespace {
 struct Arena {
     char *base = nullptr;
     size_t size = 0, used = 0;
+    bool borrowed = false; // the scene's kept scratch (b200pt_scene::build_scratch): not freed here
     ~Arena() {
-        if (base) cudaFree(base);
+        if (base && !borrowed) cudaFree(base);
     }
     static size_t pad(size_t b) { return (b + 255) & ~size_t(255); }
     template <typename T>
@@ -847,18 +848,44 @@ static int build_range(b200pt_scene *s, int64_t first, int64_t n, unsigned node_
             }
         }
     } sorted_free{&d_sorted_keys, &d_sorted_prim, keep_sorted};
-    CU_TRY(cudaMalloc(&d_sorted_keys, n * sizeof(uint64_t)));
-    CU_TRY(cudaMalloc(&d_sorted_prim, n * sizeof(uint32_t)));
-    if (keep_sorted) {
-        s->d_sorted_keys = d_sorted_keys;
-        s->d_sorted_prim = d_sorted_prim;
+    if (keep_sorted && s->d_sorted_keys && s->d_sorted_prim && s->sorted_cap >= n && s->sorted_cap <= 2 * n + 1024) {
+        d_sorted_keys = s->d_sorted_keys; // the previous build's arrays
+        d_sorted_prim = s->d_sorted_prim;
+    } else {
+        if (keep_sorted) {
+            if (s->d_sorted_keys) cudaFree(s->d_sorted_keys);
+            if (s->d_sorted_prim) cudaFree(s->d_sorted_prim);
+            s->d_sorted_keys = nullptr;
+            s->d_sorted_prim = nullptr;
+            s->sorted_cap = 0;
+        }
+        CU_TRY(cudaMalloc(&d_sorted_keys, n * sizeof(uint64_t)));
+        if (keep_sorted) s->d_sorted_keys = d_sorted_keys; // owned by the scene from here on, whatever happens next
+        CU_TRY(cudaMalloc(&d_sorted_prim, n * sizeof(uint32_t)));
+        if (keep_sorted) {
+            s->d_sorted_prim = d_sorted_prim;
+            s->sorted_cap = n;
+        }
     }
     Arena tmp;
     {
         const size_t sz = Arena::pad(sort_onesweep_bytes(n, n_passes)) + Arena::pad(12 * 4) * 2 + Arena::pad(n * 8) + Arena::pad(256 * sort_tiles(n) * 4) +
                           Arena::pad(sort_scan_tmp_words(n) * 4) + Arena::pad(4 * n * sizeof(float4)) + 3 * Arena::pad(n * 4) + 2 * Arena::pad(3 * n * sizeof(float4)) +
                           Arena::pad(2 * n * 4) + Arena::pad(n * 4) + 2 * Arena::pad(n * sizeof(int2)) + Arena::pad(8 * 4);
-        CU_TRY(cudaMalloc(&tmp.base, sz));
+        if (s->build_scratch && s->build_scratch_bytes >= sz) {
+            tmp.base = s->build_scratch;
+            tmp.borrowed = true;
+        } else if (sz <= (size_t)s->tune_build_scratch_mb << 20) {
+            if (s->build_scratch) cudaFree(s->build_scratch);
+            s->build_scratch = nullptr;
+            s->build_scratch_bytes = 0;
+            CU_TRY(cudaMalloc(&tmp.base, sz));
+            s->build_scratch = tmp.base;
+            s->build_scratch_bytes = sz;
+            tmp.borrowed = true;
+        } else {
+            CU_TRY(cudaMalloc(&tmp.base, sz));
+        }
         tmp.size = sz;
     }
     uint32_t *d_red;
@@ -1006,13 +1033,16 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
     const int64_t n = s->n_triangles;
     b200pt_build_stats bs = {};
     bs.n_triangles = n;
-    if (s->d_nodes) { cudaFree(s->d_nodes); s->d_nodes = nullptr; }
-    if (s->d_tris) { cudaFree(s->d_tris); s->d_tris = nullptr; }
-    if (s->d_sorted_keys) { cudaFree(s->d_sorted_keys); s->d_sorted_keys = nullptr; }
-    if (s->d_sorted_prim) { cudaFree(s->d_sorted_prim); s->d_sorted_prim = nullptr; }
+    // traversals of the previous tree may still be in flight on the scene's streams (the cudaFree calls this replaces waited too)
+    CU_TRY(cudaDeviceSynchronize());
     s->bvh = BVH8();
     s->built = false;
     if (n == 0) {
+        if (s->d_nodes) { cudaFree(s->d_nodes); s->d_nodes = nullptr; s->d_nodes_bytes = 0; }
+        if (s->d_tris) { cudaFree(s->d_tris); s->d_tris = nullptr; s->d_tris_bytes = 0; }
+        if (s->d_sorted_keys) { cudaFree(s->d_sorted_keys); s->d_sorted_keys = nullptr; }
+        if (s->d_sorted_prim) { cudaFree(s->d_sorted_prim); s->d_sorted_prim = nullptr; }
+        s->sorted_cap = 0;
         s->built = true;
         if (stats) *stats = bs;
         return B200PT_OK;
@@ -1029,8 +1059,22 @@ int build_bvh(b200pt_scene *s, b200pt_build_stats *stats) {
     for (const auto &o : s->objects) cap += size_t(o.n_triangles / 2 + 64);
     if (n_inst > 0) cap += size_t(n_inst / 2 + 64); // the tree over the instance boxes
     const unsigned node_capacity = unsigned(cap);
-    CU_TRY(cudaMalloc(&s->d_nodes, size_t(node_capacity) * 5 * sizeof(float4)));
-    CU_TRY(cudaMalloc(&s->d_tris, size_t(n + n_inst) * 3 * sizeof(float4))); // + one proxy leaf record per instance
+    const size_t nodes_bytes = size_t(node_capacity) * 5 * sizeof(float4);
+    const size_t tris_bytes = size_t(n + n_inst) * 3 * sizeof(float4); // + one proxy leaf record per instance
+    if (!s->d_nodes || s->d_nodes_bytes < nodes_bytes || s->d_nodes_bytes > 2 * nodes_bytes + (1 << 20)) {
+        if (s->d_nodes) cudaFree(s->d_nodes);
+        s->d_nodes = nullptr;
+        s->d_nodes_bytes = 0;
+        CU_TRY(cudaMalloc(&s->d_nodes, nodes_bytes));
+        s->d_nodes_bytes = nodes_bytes;
+    }
+    if (!s->d_tris || s->d_tris_bytes < tris_bytes || s->d_tris_bytes > 2 * tris_bytes + (1 << 20)) {
+        if (s->d_tris) cudaFree(s->d_tris);
+        s->d_tris = nullptr;
+        s->d_tris_bytes = 0;
+        CU_TRY(cudaMalloc(&s->d_tris, tris_bytes));
+        s->d_tris_bytes = tris_bytes;
+    }
     unsigned node_base = 0;
     RangeOut ro;
     if (n_top > 0) {

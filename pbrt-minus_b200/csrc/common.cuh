@@ -120,6 +120,14 @@ struct b200pt_scene {
     // debug copies of the sorted build order (kept for parity tests of the build stages)
     uint64_t *d_sorted_keys = nullptr;
     uint32_t *d_sorted_prim = nullptr;
+    // a rebuild reuses the node / leaf-record / sorted-order arrays and the build scratch of the previous build while they are
+    // large enough: the six cudaFree + cudaMalloc pairs of a 10 M-triangle build cost more host time than the build's kernels run.
+    // The scratch is kept up to tune_build_scratch_mb (b200pt_trace_tune key 7; 0 = allocate and free per build).
+    size_t d_nodes_bytes = 0, d_tris_bytes = 0;
+    int64_t sorted_cap = 0;
+    char *build_scratch = nullptr;
+    size_t build_scratch_bytes = 0;
+    int tune_build_scratch_mb = 16384;
     int key_bits = 0;
     float scene_bounds[6] = {0, 0, 0, 0, 0, 0};
 

@@ -127,7 +127,7 @@ class HLBVH:
     def set_counting(self, enable):
         _check(self.lib.b200pt_trace_set_counting(self.handle, int(enable)))
 
-    TUNE_KEYS = {"refill": 0, "tri_steps": 1, "ctas_per_sm": 2, "wf_refill": 3, "wf_tri_steps": 4, "shade_occ": 5, "stash": 6}
+    TUNE_KEYS = {"refill": 0, "tri_steps": 1, "ctas_per_sm": 2, "wf_refill": 3, "wf_tri_steps": 4, "shade_occ": 5, "stash": 6, "build_scratch_mb": 7}
 
     def tune(self, **kw):
         """scheduling knobs of the traversal kernels (b200pt_trace_tune): they change speed, never results"""

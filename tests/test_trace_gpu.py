@@ -435,6 +435,35 @@ def test_bvh8_is_conservative(b200pt, n_tris, seed):
     s.close()
 
 
+def test_rebuild_reuses_its_buffers_and_gives_the_same_tree(b200pt):
+    """b200pt_bvh_build called again on the same scene reuses the node / leaf-record / sorted-order arrays and the build scratch
+    of the previous build (csrc/bvh_build.cu: build_bvh); the tree, the sorted order and the hits must not depend on whether the
+    buffers were fresh, reused, or (b200pt_trace_tune key 7 = 0) allocated and freed per build."""
+    P, idx = b200pt.workloads.triangle_soup(200_000, seed=5)
+    s = b200pt.HLBVH(P, idx)
+    o, d = random_rays(100_000, 6)
+    first = s.build_stats
+    prim0, t0, b0 = s.intersect(o, d)
+    order0 = s.sorted_order()
+    walls = []
+    for mode in ("reused", "reused", "no kept scratch", "kept again"):
+        if mode == "no kept scratch":
+            s.tune(build_scratch_mb=0)
+        elif mode == "kept again":
+            s.tune(build_scratch_mb=16384)
+        st = s.build()
+        walls.append(st["ms_wall"])
+        assert st["n_bvh8_nodes"] == first["n_bvh8_nodes"] and st["n_triangles"] == first["n_triangles"]
+        v = s.validate()
+        assert v["bad_boxes"] == 0 and v["triangle_refs"] == len(idx)
+        prim, t, b = s.intersect(o, d)
+        assert np.array_equal(prim, prim0) and np.array_equal(t.view(np.uint32), t0.view(np.uint32)), mode
+        order = s.sorted_order()
+        assert np.array_equal(order[0], order0[0]) and np.array_equal(order[1], order0[1]), mode
+    print("build wall ms: first %.3f, then %s" % (first["ms_wall"], ["%.3f" % w for w in walls]))
+    s.close()
+
+
 def test_packed_key_build_above_16M_triangles(b200pt, oracle):
     """N > 16 Mi: key = morton(3 * b) << ceil(log2 N) | prim, b = floor((64 - ceil(log2 N)) / 3), one 8-byte key-only sort
     (csrc/bvh_build.cu).  17 M triangles: the sorted order is a permutation, keys strictly increase, the low bits are the
