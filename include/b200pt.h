@@ -285,6 +285,10 @@ int b200pt_device_count(void);
 
 /* Scene + accelerator: replaces HLBVH::HLBVH (accelerator/hlbvh.cu:172-404) */
 int b200pt_scene_create(const b200pt_scene_desc *desc, int device, b200pt_scene **out);
+/* Debugging aid: writes every field of a scene description to `dir` (which must exist) as raw arrays, one file per field, so that
+ * the descriptions of two front-ends -- the Python one and the reference's own through the bridge -- can be compared bit by bit
+ * (tools/desc_diff.py).  Makes no CUDA call; b200pt_scene_create calls it when B200PT_DESC_DUMP names a directory. */
+int b200pt_debug_dump_desc(const b200pt_scene_desc *desc, const char *dir);
 void b200pt_scene_destroy(b200pt_scene *scene);
 int b200pt_bvh_build(b200pt_scene *scene, b200pt_build_stats *stats_out);
 /* Morton codes of the build (reference-compatible 30-bit codes, accelerator/hlbvh.cu:128-142):

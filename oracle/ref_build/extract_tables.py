@@ -40,11 +40,14 @@ def main():
     metal = arrays(os.path.join(d, "spectrum_constants_metal.h"))
     glass = arrays(os.path.join(d, "spectrum_constants_glass.h"))
     fit = arrays(os.path.join(d, "rgb_to_spectrum_data.h"))
+    enc = arrays(os.path.join(d, "color_encoding.h"))   # the 256-entry sRGB-to-linear table 8-bit images are decoded through
     out = {
         "cie_x": cie["CIE_X_VALUE_CPU"], "cie_y": cie["CIE_Y_VALUE_CPU"], "cie_z": cie["CIE_Z_VALUE_CPU"],
         "cie_lambda": cie["CIE_LAMBDA_CPU"], "illum_d65_interleaved": cie["CIE_Illum_D6500"],
         "fit_cie_x": fit["cie_x"], "fit_cie_y": fit["cie_y"], "fit_cie_z": fit["cie_z"], "fit_cie_d65": fit["cie_d65"] / 10566.864005283874576,
     }
+    assert len(enc["SRGBToLinearLUT"]) == 256
+    out["srgb_to_linear_lut"] = enc["SRGBToLinearLUT"]
     for k, v in list(metal.items()) + list(glass.items()):
         out["named_" + k] = v
     for k, v in out.items():

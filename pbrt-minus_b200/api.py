@@ -141,7 +141,7 @@ class RaySet(C.Structure):
 # every symbol include/b200pt.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "b200pt_abi_version", "b200pt_last_error", "b200pt_device_count",
-    "b200pt_scene_create", "b200pt_scene_destroy", "b200pt_bvh_build", "b200pt_bvh_debug_sorted", "b200pt_bvh_validate",
+    "b200pt_scene_create", "b200pt_debug_dump_desc", "b200pt_scene_destroy", "b200pt_bvh_build", "b200pt_bvh_debug_sorted", "b200pt_bvh_validate",
     "b200pt_trace", "b200pt_trace_batch", "b200pt_trace_device", "b200pt_trace_device_batch", "b200pt_trace_set_counting", "b200pt_trace_counters", "b200pt_trace_tune",
     "b200pt_scene_stream", "b200pt_scene_sync",
     "b200pt_device_alloc", "b200pt_device_free", "b200pt_copy_to_device", "b200pt_copy_to_host",
@@ -165,6 +165,7 @@ def load_library():
     fp, ip = C.POINTER(C.c_float), C.POINTER(C.c_int32)
     lib.b200pt_last_error.restype = C.c_char_p
     lib.b200pt_scene_create.argtypes = [C.POINTER(SceneDesc), i32, C.POINTER(vp)]
+    lib.b200pt_debug_dump_desc.argtypes = [C.POINTER(SceneDesc), C.c_char_p]
     lib.b200pt_scene_destroy.argtypes = [vp]
     lib.b200pt_scene_destroy.restype = None
     lib.b200pt_bvh_build.argtypes = [vp, C.POINTER(BuildStats)]

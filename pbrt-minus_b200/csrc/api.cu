@@ -111,12 +111,95 @@ B200PT_API int b200pt_device_count(void) {
 
 int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc); // render.cu
 
+// Writes a scene description to `dir` as raw arrays, one file per field (tools/desc_diff.py reads them): the way two front-ends
+// -- the Python one and the reference's own through the bridge -- are compared field by field, bit by bit.  No CUDA call.
+B200PT_API int b200pt_debug_dump_desc(const b200pt_scene_desc *d, const char *dir) {
+    if (!d || !dir) return B200PT_ERR_INVALID;
+    bool ok = true;
+    auto put = [&](const char *name, const void *p, size_t bytes) {
+        const std::string path = std::string(dir) + "/" + name;
+        FILE *f = fopen(path.c_str(), "wb");
+        if (!f) {
+            ok = false;
+            return;
+        }
+        if (p && bytes) ok = fwrite(p, 1, bytes, f) == bytes && ok;
+        fclose(f);
+    };
+    const size_t nv = (size_t)d->n_vertices, nt = (size_t)d->n_triangles;
+    put("P.f32", d->P, nv * 12);
+    put("N.f32", d->N, d->N ? nv * 12 : 0);
+    put("uv.f32", d->uv, d->uv ? nv * 8 : 0);
+    put("indices.i32", d->indices, nt * 12);
+    put("tri_material.i32", d->tri_material, d->tri_material ? nt * 4 : 0);
+    put("tri_light.i32", d->tri_light, d->tri_light ? nt * 4 : 0);
+    put("tri_flip.u8", d->tri_flip, d->tri_flip ? nt : 0);
+    put("tri_medium.u32", d->tri_medium, d->tri_medium ? nt * 4 : 0);
+    put("spheres.bin", d->spheres, (size_t)d->n_spheres * sizeof(b200pt_sphere));
+    put("materials.bin", d->materials, (size_t)d->n_materials * sizeof(b200pt_material));
+    put("lights.bin", d->lights, (size_t)d->n_lights * sizeof(b200pt_light));
+    put("textures.bin", d->textures, (size_t)d->n_textures * sizeof(b200pt_texture));
+    put("media.bin", d->media, (size_t)d->n_media * sizeof(b200pt_medium));
+    put("objects.bin", d->objects, (size_t)d->n_objects * sizeof(b200pt_object));
+    put("instances.bin", d->instances, (size_t)d->n_instances * sizeof(b200pt_instance));
+    if (d->camera) put("camera.bin", d->camera, sizeof(b200pt_camera));
+    { // spectra: {type, c[4], n} records and one pool of lambda[n] then value[n] per spectrum that has them
+        std::vector<int32_t> rec;
+        std::vector<float> pool;
+        for (int i = 0; i < d->n_spectra; i++) {
+            const b200pt_spectrum &sp = d->spectra[i];
+            int32_t w[6];
+            w[0] = sp.type;
+            memcpy(&w[1], sp.c, 16);
+            w[5] = sp.n;
+            rec.insert(rec.end(), w, w + 6);
+            if (sp.type == B200PT_SPEC_PIECEWISE && sp.lambda && sp.value) {
+                pool.insert(pool.end(), sp.lambda, sp.lambda + sp.n);
+                pool.insert(pool.end(), sp.value, sp.value + sp.n);
+            } else if (sp.type == B200PT_SPEC_DENSE && sp.value) {
+                pool.insert(pool.end(), sp.value, sp.value + sp.n);
+            }
+        }
+        put("spectra.i32", rec.data(), rec.size() * 4);
+        put("spectra_pool.f32", pool.data(), pool.size() * 4);
+    }
+    if (d->filter) {
+        const float hdr[4] = {d->filter->radius_x, d->filter->radius_y, (float)d->filter->nx, (float)d->filter->ny};
+        put("filter_hdr.f32", hdr, sizeof(hdr));
+        put("filter_f.f32", d->filter->f, (size_t)d->filter->nx * d->filter->ny * 4);
+    }
+    if (d->film) {
+        std::vector<float> v = {(float)d->film->width, (float)d->film->height, d->film->imaging_ratio};
+        v.insert(v.end(), d->film->output_rgb_from_sensor_rgb, d->film->output_rgb_from_sensor_rgb + 9);
+        for (const float *t : {d->film->cie_x, d->film->cie_y, d->film->cie_z, d->film->illuminant})
+            if (t) v.insert(v.end(), t, t + 471);
+        put("film.f32", v.data(), v.size() * 4);
+    }
+    {
+        std::vector<int32_t> dims;
+        std::vector<float> px;
+        for (int i = 0; i < d->n_images; i++) {
+            dims.push_back(d->images[i].width);
+            dims.push_back(d->images[i].height);
+            if (d->images[i].rgb) px.insert(px.end(), d->images[i].rgb, d->images[i].rgb + (size_t)d->images[i].width * d->images[i].height * 3);
+        }
+        put("images_dims.i32", dims.data(), dims.size() * 4);
+        put("images_rgb.f32", px.data(), px.size() * 4);
+    }
+    if (!ok) {
+        set_error("b200pt_debug_dump_desc: cannot write to '%s'", dir);
+        return B200PT_ERR_INVALID;
+    }
+    return B200PT_OK;
+}
+
 B200PT_API int b200pt_scene_create(const b200pt_scene_desc *desc, int device, b200pt_scene **out) {
     if (!desc || !out) {
         set_error("b200pt_scene_create: null argument");
         return B200PT_ERR_INVALID;
     }
     *out = nullptr;
+    if (const char *dump = getenv("B200PT_DESC_DUMP")) b200pt_debug_dump_desc(desc, dump);
     if (desc->n_triangles < 0 || desc->n_vertices < 0 || (desc->n_triangles > 0 && (!desc->P || !desc->indices))) {
         set_error("b200pt_scene_create: inconsistent geometry description");
         return B200PT_ERR_INVALID;

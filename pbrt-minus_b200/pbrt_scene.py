@@ -121,10 +121,43 @@ def _mm(a, b):
     return r
 
 
+def inverse32(m):
+    """SquareMatrix<4>::inverse (euclidean_space/squared_matrix.cu:83-151): the Laplace expansion over 2x2 sub-determinants, in
+    fp32.  Its difference_of_products / inner_product are error-compensated (util/math.h:167-181), i.e. the exact value rounded
+    once to fp32 -- evaluated here in fp64 (products of fp32 numbers are exact there) and rounded; then s = 1 / det and one
+    fp32 product per entry.  Camera and LookAt matrices come out of this, so it has to round as the reference's does."""
+    m = np.asarray(m, dtype=F32).reshape(4, 4)
+    d = m.astype(np.float64)
+
+    def dop(a, b, c, e):
+        return np.float64(F32(a * b - c * e))
+
+    def ip(*t):
+        return np.float64(F32(sum(t[i] * t[i + 1] for i in range(0, len(t), 2))))
+
+    s0, s1, s2 = dop(d[0, 0], d[1, 1], d[1, 0], d[0, 1]), dop(d[0, 0], d[1, 2], d[1, 0], d[0, 2]), dop(d[0, 0], d[1, 3], d[1, 0], d[0, 3])
+    s3, s4, s5 = dop(d[0, 1], d[1, 2], d[1, 1], d[0, 2]), dop(d[0, 1], d[1, 3], d[1, 1], d[0, 3]), dop(d[0, 2], d[1, 3], d[1, 2], d[0, 3])
+    c0, c1, c2 = dop(d[2, 0], d[3, 1], d[3, 0], d[2, 1]), dop(d[2, 0], d[3, 2], d[3, 0], d[2, 2]), dop(d[2, 0], d[3, 3], d[3, 0], d[2, 3])
+    c3, c4, c5 = dop(d[2, 1], d[3, 2], d[3, 1], d[2, 2]), dop(d[2, 1], d[3, 3], d[3, 1], d[2, 3]), dop(d[2, 2], d[3, 3], d[3, 2], d[2, 3])
+    det = ip(s0, c5, -s1, c4, s2, c3, s3, c2, s5, c0, -s4, c1)
+    if det == 0:
+        return np.full((4, 4), np.nan, dtype=F32)
+    s = F32(1.0 / det)
+    rows = [[ip(d[1, 1], c5, d[1, 3], c3, -d[1, 2], c4), ip(-d[0, 1], c5, d[0, 2], c4, -d[0, 3], c3),
+             ip(d[3, 1], s5, d[3, 3], s3, -d[3, 2], s4), ip(-d[2, 1], s5, d[2, 2], s4, -d[2, 3], s3)],
+            [ip(-d[1, 0], c5, d[1, 2], c2, -d[1, 3], c1), ip(d[0, 0], c5, d[0, 3], c1, -d[0, 2], c2),
+             ip(-d[3, 0], s5, d[3, 2], s2, -d[3, 3], s1), ip(d[2, 0], s5, d[2, 3], s1, -d[2, 2], s2)],
+            [ip(d[1, 0], c4, d[1, 3], c0, -d[1, 1], c2), ip(-d[0, 0], c4, d[0, 1], c2, -d[0, 3], c0),
+             ip(d[3, 0], s4, d[3, 3], s0, -d[3, 1], s2), ip(-d[2, 0], s4, d[2, 1], s2, -d[2, 3], s0)],
+            [ip(-d[1, 0], c3, d[1, 1], c1, -d[1, 2], c0), ip(d[0, 0], c3, d[0, 2], c0, -d[0, 1], c1),
+             ip(-d[3, 0], s3, d[3, 1], s1, -d[3, 2], s0), ip(d[2, 0], s3, d[2, 2], s0, -d[2, 1], s1)]]
+    return (s * np.array(rows, dtype=F32)).astype(F32)
+
+
 class Xf:
     def __init__(self, m, inv_m=None):
         self.m = np.asarray(m, dtype=F32).reshape(4, 4).copy()
-        self.inv = (np.linalg.inv(self.m.astype(np.float64)).astype(F32) if inv_m is None else np.asarray(inv_m, dtype=F32).reshape(4, 4).copy())
+        self.inv = inverse32(self.m) if inv_m is None else np.asarray(inv_m, dtype=F32).reshape(4, 4).copy()
 
     def __mul__(self, o):
         return Xf(_mm(self.m, o.m), _mm(o.inv, self.inv))
@@ -191,7 +224,7 @@ def lookat(pos, look, up):
     new_up = np.cross(d.astype(np.float64), right.astype(np.float64)).astype(F32)
     wfc = np.eye(4, dtype=F32)
     wfc[:3, 0], wfc[:3, 1], wfc[:3, 2], wfc[:3, 3] = right, new_up, d, pos
-    return Xf(np.linalg.inv(wfc.astype(np.float64)).astype(F32), wfc)
+    return Xf(inverse32(wfc), wfc)
 
 
 def perspective(fov, n, f):
@@ -409,14 +442,14 @@ class Scene:
                 raise SceneError("rgb albedo components must be <= 1 (base/spectrum.cu:67-69)")
             c = spectral.rgb_to_sigmoid(rgb)
             return self.add_spectrum(("a",) + rgb, {"type": 1, "c": [c[0], c[1], c[2], 1.0]})
+        # RGBUnboundedSpectrum / RGBIlluminantSpectrum ctors (spectra/rgb_unbounded_spectrum.cu:5-14, rgb_illuminant_spectrum.cu:6-10):
+        # the components are fp32 (Real), scale = 2 * max and rgb / scale are fp32 operations
+        r32 = np.asarray(rgb, dtype=F32)
+        sc = F32(F32(2) * r32.max())
+        c = spectral.rgb_to_sigmoid((r32 / sc).astype(F32) if sc > 0 else (0, 0, 0))
         if kind == "unbounded":
-            m = max(rgb)
-            sc = 2.0 * m
-            c = spectral.rgb_to_sigmoid([v / sc for v in rgb] if sc > 0 else (0, 0, 0))
-            return self.add_spectrum(("u",) + rgb, {"type": 2, "c": [c[0], c[1], c[2], sc]})
-        sc = 2.0 * max(rgb)
-        c = spectral.rgb_to_sigmoid([v / sc for v in rgb] if sc > 0 else (0, 0, 0))
-        return self.add_spectrum(("i",) + rgb, {"type": 3, "c": [c[0], c[1], c[2], sc]})
+            return self.add_spectrum(("u",) + rgb, {"type": 2, "c": [c[0], c[1], c[2], float(sc)]})
+        return self.add_spectrum(("i",) + rgb, {"type": 3, "c": [c[0], c[1], c[2], float(sc)]})
 
     def spec_piecewise(self, key, lam, val):
         lam, val = np.ascontiguousarray(lam, dtype=F32), np.ascontiguousarray(val, dtype=F32)
@@ -468,8 +501,7 @@ class Scene:
         if im.mode in ("I;16", "I;16B", "I"):
             raise SceneError("16-bit PNG textures are not supported")
         px = np.asarray(im.convert("RGBA"), dtype=np.uint8)[:, :, :3]
-        c = np.arange(256, dtype=np.float64) / 255.0
-        lut = np.where(c <= 0.04045, c / 12.92, ((c + 0.055) / 1.055) ** 2.4).astype(F32)
+        lut = spectral.tables()["srgb_to_linear_lut"].astype(F32)   # SRGBColorEncoding::to_linear (spectrum_util/color_encoding.h:29-31,46)
         self.images.append(np.ascontiguousarray(lut[px], dtype=F32))
         self._image_ids[path] = len(self.images) - 1
         return self._image_ids[path]
@@ -705,8 +737,15 @@ class Scene:
             raise SceneError("illuminating volume not implemented (homogeneous_medium.cu:25-30)")
         sa = self.spec_param(p, "sigma_a", "unbounded", scene_dir)
         ss = self.spec_param(p, "sigma_s", "unbounded", scene_dir)
-        self.media.append({"sigma_a": self.spec_constant(1.0) if sa is None else sa, "sigma_s": self.spec_constant(1.0) if ss is None else ss,
-                           "scale": p_float(p, "scale", 1.0), "g": p_float(p, "g", 0.0)})
+        sa, ss = self.spec_constant(1.0) if sa is None else sa, self.spec_constant(1.0) if ss is None else ss
+        # Medium::Medium (medium/homogeneous_medium.cu:7-13) keeps DenselySampledSpectrum(sigma, scale): the spectrum times "scale"
+        # tabulated at the integer wavelengths on the host, interpolated linearly in between at render time -- not the analytic curve
+        scale = F32(p_float(p, "scale", 1.0))
+        dense = []
+        for sid in (sa, ss):
+            v = spectral.dense_scaled32(self.spectra[sid], scale)
+            dense.append(self.add_spectrum(("dense", v.tobytes()), {"type": 5, "c": [0, 0, 0, 0], "value": v}))
+        self.media.append({"sigma_a": dense[0], "sigma_s": dense[1], "scale": 1.0, "g": p_float(p, "g", 0.0)})
         return len(self.media) - 1
 
     # ---- lights that are not emissive shapes (SceneBuilder::parse_light_source, scene_builder.cu:493-504)
@@ -1080,9 +1119,10 @@ def load(path=None, text=None, spp=None, integrator=None, scene_dir=None, flatte
         raster_from_ndc = scale(W, -H, 1.0)
         raster_from_screen = raster_from_ndc * ndc_from_screen
         screen_from_camera = perspective(p_float(cp, "fov", 90.0), 1e-2, 1000.0)
-        # Transform::inverse() of a product swaps (m, inv_m); raster_from_screen.inverse() is numeric in the
-        # reference too (SquareMatrix::inverse); cameras/perspective.cu:34-40
-        cfr = (screen_from_camera.inverse() * Xf(raster_from_screen.m).inverse()).m
+        # Transform::inverse() swaps (m, inv_m) (euclidean_space/transform.h:244-246): raster_from_screen's inverse is the product
+        # of the analytic inverses of its scale / translate factors, the perspective matrix's the numeric SquareMatrix::inverse
+        # (cameras/perspective.cu:34-40)
+        cfr = (screen_from_camera.inverse() * raster_from_screen.inverse()).m
         sc.camera = {"cfr": cfr, "rfc": rfc, "lens_radius": p_float(cp, "lensradius", 0.0),
                      "focal_distance": p_float(cp, "focaldistance", 1e6)}
         if g.medium_interface is not None:      # build_camera (scene_builder.cu:166-171)

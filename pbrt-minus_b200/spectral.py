@@ -55,6 +55,52 @@ def piecewise_eval32(lam, val, x):
     return np.where((x < lam[0]) | (x > lam[-1]), np.float32(0), y).astype(np.float32)
 
 
+def _fma32(a, b, c):
+    return (np.asarray(a, np.float64) * np.asarray(b, np.float64) + np.asarray(c, np.float64)).astype(np.float32)
+
+
+def sigmoid_poly32(c, lam):
+    """RGBSigmoidPolynomial::operator() (spectrum_util/rgb_sigmoid_polynomial.h:14-37) as the reference's HOST rounds it:
+    Horner with fma, then .5 + x / (2 sqrt(1 + x^2)) one fp32 operation at a time"""
+    lam = _f32(lam)
+    c0, c1, c2 = (np.float32(v) for v in c[:3])
+    x = _fma32(lam, _fma32(lam, c0, c1), c2)
+    with np.errstate(invalid="ignore", over="ignore"):
+        xx = (x * x).astype(np.float32)
+        root = np.sqrt((np.float32(1) + xx).astype(np.float32)).astype(np.float32)
+        y = (np.float32(0.5) + (x / (np.float32(2) * root).astype(np.float32)).astype(np.float32)).astype(np.float32)
+    return np.where(np.isinf(x), np.where(x > 0, np.float32(1), np.float32(0)), y).astype(np.float32)
+
+
+def spectrum_eval32(rec, lam):
+    """Spectrum::operator()(lambda) of a front-end spectrum record in the reference's host fp32 arithmetic (types as in
+    include/b200pt.h: constant, rgb albedo / unbounded / illuminant, piecewise linear, dense)"""
+    lam = _f32(lam)
+    t, c = rec["type"], rec["c"]
+    if t == 0:
+        return np.full(lam.shape, np.float32(c[0]), dtype=np.float32)
+    if t == 1:
+        return sigmoid_poly32(c, lam)
+    if t == 2:
+        return (np.float32(c[3]) * sigmoid_poly32(c, lam)).astype(np.float32)
+    if t == 3:
+        a = (np.float32(c[3]) * sigmoid_poly32(c, lam)).astype(np.float32)
+        grid = np.arange(LAMBDA_MIN, LAMBDA_MAX + 1).astype(np.float32)
+        return (a * piecewise_eval32(grid, illuminant_d65()[2], lam)).astype(np.float32)
+    if t == 4:
+        return piecewise_eval32(rec["lambda"], rec["value"], lam)
+    if t == 5:
+        grid = np.arange(LAMBDA_MIN, LAMBDA_MAX + 1).astype(np.float32)
+        return piecewise_eval32(grid, rec["value"], lam)
+    raise ValueError("spectrum type %r" % t)
+
+
+def dense_scaled32(rec, scale):
+    """DenselySampledSpectrum(spectrum, scale) (spectra/densely_sampled_spectrum.h:10-14): spectrum(lambda) * scale at 360..830"""
+    grid = np.arange(LAMBDA_MIN, LAMBDA_MAX + 1).astype(np.float32)
+    return (spectrum_eval32(rec, grid) * np.float32(scale)).astype(np.float32)
+
+
 def inner_product32(a, b):
     """Spectrum::inner_product (e.g. spectra/densely_sampled_spectrum.h:17-24): an fp32 running sum of fp32 products over the
     integer wavelengths 360..830"""
@@ -240,15 +286,20 @@ def rgb_to_sigmoid(rgb):
     m = (0 if r > b else 2) if r > g else (1 if g > b else 2)
     c = [r, g, b]
     z = c[m]
-    x = c[(m + 1) % 3] * (RES - 1) / z
-    y = c[(m + 2) % 3] * (RES - 1) / z
+    # the reference's mixed arithmetic: rgb * (RES - 1) is an fp32 product, x / y / z and the offsets are doubles, and every lerp
+    # is pbrt::lerp(Real, Real, Real) -- its double arguments (offsets, table entries) are rounded to fp32 at the call and the
+    # interpolation itself runs in fp32 on the host (no contraction)
+    x = float(np.float32(np.float32(c[(m + 1) % 3]) * np.float32(RES - 1))) / z
+    y = float(np.float32(np.float32(c[(m + 2) % 3]) * np.float32(RES - 1))) / z
     xi, yi = min(int(x), RES - 2), min(int(y), RES - 2)
     zi = int(np.clip(np.searchsorted(_Z_NODES, z, side="left") - 1, 0, RES - 2))
     dx, dy = x - xi, y - yi
     dz = (z - _Z_NODES[zi]) / (_Z_NODES[zi + 1] - _Z_NODES[zi])
 
     def lerp(t, a, b_):
-        return (1 - t) * a + t * b_
+        t, a, b_ = np.float32(t), np.asarray(a, np.float32), np.asarray(b_, np.float32)
+        lo = ((np.float32(1) - t).astype(np.float32) * a).astype(np.float32)
+        return (lo + (t * b_).astype(np.float32)).astype(np.float32)
 
     def co(ddx, ddy, ddz):
         return _column(m, yi + ddy, xi + ddx)[zi + ddz]

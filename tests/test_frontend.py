@@ -140,7 +140,14 @@ def test_media_front_end(b200pt):
     ps = b200pt.pbrt_scene
     sc = ps.load(os.path.join(ROOT, "tests", "scenes", "media.pbrt"))
     assert len(sc.media) == 2 and sc.camera_medium == -1
-    assert sc.media[0]["g"] == pytest.approx(0.3) and sc.media[1]["scale"] == 2.0
+    # sigma spectra are handed over as the reference keeps them (medium/homogeneous_medium.cu:7-13): DenselySampledSpectrum(sigma,
+    # scale), i.e. the spectrum times "scale" tabulated at 360..830 nm in fp32, so the record's own scale is 1
+    assert sc.media[0]["g"] == pytest.approx(0.3) and sc.media[1]["scale"] == 1.0
+    dye_a, dye_s = sc.spectra[sc.media[1]["sigma_a"]], sc.spectra[sc.media[1]["sigma_s"]]
+    assert dye_a["type"] == 5 and len(dye_a["value"]) == 471 and dye_a["value"].dtype == np.float32
+    # rgb (0.8 0.2 0.1) * 2: strong in the red, weak in the blue; (0.3 0.6 0.9) * 2 the other way round
+    assert dye_a["value"][650 - 360] > 4 * dye_a["value"][450 - 360] > 0 and 1.2 < dye_a["value"][650 - 360] < 2.6
+    assert dye_s["value"][450 - 360] > 2 * dye_s["value"][650 - 360] > 0
     codes = np.concatenate(sc.tri_medium)
     per_shape = [int(codes[i]) for i in (0, 2, 4, 6, 18, 30)]
     # light (GeometricPrimitive, no transition), floor, wall, fog box (interior fog, exterior vacuum), block (fog|fog is no

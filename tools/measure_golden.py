@@ -18,6 +18,8 @@ STATISTICAL = ("coated_", "mix_", "metals_coated_")   # compared as two unbiased
 
 def main():
     import test_render_gpu as T
+    import test_bridge_gpu as B
+    import numpy as np
     pkg = importlib.import_module("pbrt-minus_b200")
     out = {}
     with tempfile.TemporaryDirectory() as td:
@@ -42,6 +44,17 @@ def main():
             r, f = T.rel_mse(ours, ref), T.frac_close(ours, ref)
             out[name] = {"relMSE_measured": r, "frac_close_measured": f, "relMSE_tol": max(10.0 * r, 1e-9),
                          "frac_close_tol": round(max(0.0, f - 0.01), 4), "ms": round(st["ms_total"], 2)}
+            # the same scene through the reference's own front-end + the bridge (tests/test_bridge_gpu.py): its own measured
+            # distance to the golden and to the Python path's film (the two descriptions differ in a few last bits)
+            if m["scene"] != "@c4tiny" and m["spp"] <= 64 and os.path.exists(B.EXE):
+                import pathlib
+                tmp = pathlib.Path(tempfile.mkdtemp())
+                rb, outp = B.run_bridge(text, m["spp"], tmp)
+                if rb.returncode == 0:
+                    film = np.fromfile(outp + ".f32", dtype=np.float32).reshape(m["height"], m["width"], 3)
+                    br, bc = T.rel_mse(film, ref), T.rel_mse(film, ours)
+                    out[name].update({"bridge_relMSE_measured": br, "bridge_relMSE_tol": max(10.0 * br, 1e-9),
+                                      "bridge_vs_python_measured": bc, "bridge_vs_python_tol": max(10.0 * bc, 1e-9)})
             print(name, json.dumps(out[name]), flush=True)
     dst = os.path.join(ROOT, "tests", "golden", "films", "tolerances.json") if "--write" in sys.argv else os.path.join(ROOT, "gpurun_out", "tolerances.json")
     json.dump(out, open(dst, "w"), indent=1)
