@@ -234,8 +234,9 @@ def loop_subdivide(levels, indices, P):
         if not m.boundary[v]:
             for j in range(valence):
                 ang = F32(F32(F32(F32(2) * pi) * F32(j)) / F32(valence))
-                S = S + F32(np.cos(ang)) * ring[j]
-                T = T + F32(np.sin(ang)) * ring[j]
+                # cosf / sinf of the host's libm: the exact value rounded once (numpy's fp32 routines may be an ulp off)
+                S = S + F32(math.cos(float(ang))) * ring[j]
+                T = T + F32(math.sin(float(ang))) * ring[j]
         else:
             S = ring[-1] - ring[0]
             if valence == 2:
@@ -246,12 +247,15 @@ def loop_subdivide(levels, indices, P):
                 T = F32(-1) * ring[0] + F32(2) * ring[1] + F32(2) * ring[2] + F32(-1) * ring[3] + F32(-2) * m.p[v]
             else:
                 theta = F32(pi / F32(valence - 1))
-                T = F32(np.sin(theta)) * (ring[0] + ring[-1])
+                T = F32(math.sin(float(theta))) * (ring[0] + ring[-1])
                 for k in range(1, valence - 1):
-                    wt = F32(F32(F32(2) * F32(np.cos(theta)) - F32(2)) * F32(np.sin(F32(F32(k) * theta))))
+                    wt = F32(F32(F32(2) * F32(math.cos(float(theta))) - F32(2)) * F32(math.sin(float(F32(F32(k) * theta)))))
                     T = T + wt * ring[k]
                 T = -T
         S = S.astype(F32)
         T = T.astype(F32)
-        normals[v] = np.array([S[1] * T[2] - S[2] * T[1], S[2] * T[0] - S[0] * T[2], S[0] * T[1] - S[1] * T[0]], dtype=F32)
+        # Vector3::cross is built on difference_of_products (euclidean_space/vector3.h:151-155): error-compensated, i.e. the
+        # exact value rounded once -- fp64 holds the products of fp32 numbers exactly
+        S64, T64 = S.astype(np.float64), T.astype(np.float64)
+        normals[v] = np.array([S64[1] * T64[2] - S64[2] * T64[1], S64[2] * T64[0] - S64[0] * T64[2], S64[0] * T64[1] - S64[1] * T64[0]]).astype(F32)
     return limit, np.asarray(m.fv, dtype=np.int32).reshape(-1, 3), normals

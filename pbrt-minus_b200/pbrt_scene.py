@@ -395,9 +395,15 @@ def filter_table(kind, p):
     else:  # gaussian
         sigma = F32(p_float(p, "sigma", 0.5))
 
-        def g(x, r):
-            gs = lambda v: np.exp(-v * v / (2 * sigma * sigma)) / np.sqrt(2 * np.pi * sigma * sigma)
-            return np.maximum(0, gs(x) - gs(r))
+        def g(x, r):   # gaussian() and GaussianFilter::evaluate (filters/gaussian.cu:8-11,33-37), one fp32 operation at a time
+            two_ss = F32(F32(F32(2) * sigma) * sigma)
+            norm = F32(F32(1) / F32(np.sqrt(F32(F32(F32(F32(2) * F32(np.pi)) * sigma) * sigma))))
+
+            def gs(v):
+                v = np.asarray(v, dtype=F32)
+                arg = (-(v * v).astype(F32) / two_ss).astype(F32)
+                return (norm * np.exp(arg.astype(np.float64)).astype(F32)).astype(F32)   # expf: the exact value rounded once
+            return np.maximum(F32(0), (gs(x) - gs(r)).astype(F32)).astype(F32)
 
         f = np.outer(g(ys, ry), g(xs, rx))
     return float(rx), float(ry), nx, ny, np.ascontiguousarray(f, dtype=F32)

@@ -23,8 +23,27 @@ pkg = importlib.import_module("pbrt-minus_b200")
 api = pkg.api
 
 
+FILES = ("P.f32", "N.f32", "uv.f32", "indices.i32", "tri_material.i32", "tri_light.i32", "tri_flip.u8", "tri_medium.u32", "camera.bin", "filter_hdr.f32",
+         "filter_f.f32", "film.f32", "images_dims.i32", "images_rgb.f32", "spectra.i32", "spectra_pool.f32", "spheres.bin", "materials.bin", "lights.bin",
+         "textures.bin", "media.bin", "objects.bin", "instances.bin")
+
+
+def pack(d, out_path):
+    """a dump directory as one compressed .npz (the committed fixtures under tests/golden/desc/)"""
+    z = {f.replace(".", "__"): np.fromfile(os.path.join(d, f), dtype=np.uint8) for f in FILES if os.path.exists(os.path.join(d, f))}
+    sp = os.path.join(d, "scene.pbrt")
+    if os.path.exists(sp):
+        z["scene__pbrt"] = np.frombuffer(open(sp, "rb").read(), dtype=np.uint8)
+    np.savez_compressed(out_path, **z)
+
+
 def load(d):
+    packed = dict(np.load(d)) if os.path.isfile(d) else None
+
     def arr(name, dt):
+        if packed is not None:
+            raw = packed.get(name.replace(".", "__"), np.zeros(0, np.uint8))
+            return np.frombuffer(raw.tobytes(), dtype=dt).copy()
         p = os.path.join(d, name)
         return np.fromfile(p, dtype=dt) if os.path.exists(p) else np.zeros(0, dt)
     out = {"P": arr("P.f32", np.float32).reshape(-1, 3), "N": arr("N.f32", np.float32).reshape(-1, 3), "uv": arr("uv.f32", np.float32).reshape(-1, 2),
@@ -46,6 +65,13 @@ def load(d):
         specs.append((int(t), tuple(int(x) for x in used), out["pool"][off:off + k].view(np.uint32).tobytes()))
         off += k
     out["spec_content"] = specs
+    import hashlib
+    imgs, off = [], 0
+    for w, h in out["images_dims"].reshape(-1, 2):
+        px = out["images_rgb"][off:off + int(w) * int(h) * 3]
+        imgs.append((int(w), int(h), hashlib.sha1(px.tobytes()).hexdigest()))
+        off += int(w) * int(h) * 3
+    out["image_content"] = imgs
     return out
 
 
@@ -67,12 +93,23 @@ TEX_FIELDS = {"Material": ("reflectance_tex1", "transmittance_tex1", "u_roughnes
 
 def texture_content(d, i, depth=0):
     t = d["textures"][i]
-    rec = {f: bits(getattr(t, f)) for f in fields(type(t)) if f not in ("a", "b", "c")}
     ty = t.type
+    used = {0: (), 1: ("f", "map", "mapping", "texture_from_render", "v1", "v2"), 17: ("f", "map", "mapping", "texture_from_render", "v1", "v2"),
+            2: ("f",), 3: ("f",) if t.c < 0 else (), 4: ("f",), 16: ("f",), 18: ()}.get(ty, ())
+    rec = {"type": ty}
+    for f in used:
+        v = bits(getattr(t, f))
+        if f == "f":
+            v = v[:{1: 2, 17: 2, 2: 1, 3: 1, 4: 3, 16: 1}[ty]]
+        if f in ("texture_from_render", "v1", "v2") and t.mapping == 0:
+            continue                                      # uv mapping reads none of them
+        if f in ("v1", "v2") and t.mapping != 1:
+            continue
+        rec[f] = v
     if ty == 0:
         rec["a"] = d["spec_content"][t.a]
     elif ty in (1, 17):
-        rec["a"] = ("image", t.a)
+        rec["a"] = ("image", d["image_content"][t.a])      # by content: one front-end shares an image between textures, the other loads it per texture
     elif ty in (2,):
         rec["a"] = texture_content(d, t.a, depth + 1)
     elif ty in (3, 4, 18):
@@ -182,14 +219,19 @@ def diff(A, B):
                 if ma[i] != mb[j]:
                     d = {k: (ma[i][k], mb[j][k]) for k in ma[i] if ma[i][k] != mb[j][k]}
                     report.append("material of triangle %d differs (ids %d / %d): %s" % (t, i, j, str(d)[:600]))
-    for k in ("camera", "filter_hdr", "filter_f", "film", "images_dims", "images_rgb"):
+    for k in ("camera", "filter_hdr", "filter_f", "film"):
         cmp_arrays(k, A[k], B[k], report)
+    if set(A["image_content"]) != set(B["image_content"]):
+        report.append("images differ: %s vs %s" % (sorted(set(A["image_content"]) - set(B["image_content"])), sorted(set(B["image_content"]) - set(A["image_content"]))))
     for name in ("lights", "spheres", "media", "instances", "objects"):
         if len(A[name]) != len(B[name]):
             report.append("%s: %d vs %d" % (name, len(A[name]), len(B[name])))
             continue
         for i, (ra, rb) in enumerate(zip(A[name], B[name])):
             ca, cb = record_content(A, ra), record_content(B, rb)
+            if name == "spheres" and not (len(A["media"]) or len(B["media"])):
+                ca.pop("medium", None)
+                cb.pop("medium", None)
             if name == "spheres":   # material ids by content
                 ca["material"] = record_content(A, A["materials"][ra.material]) if ra.material >= 0 else None
                 cb["material"] = record_content(B, B["materials"][rb.material]) if rb.material >= 0 else None
@@ -207,7 +249,11 @@ def main():
     ap.add_argument("--python-scene")
     ap.add_argument("--spp", type=int, default=64)
     ap.add_argument("--ref")
+    ap.add_argument("--pack", nargs=2, metavar=("DIR", "NPZ"), help="write a dump directory as one compressed fixture")
     args = ap.parse_args()
+    if args.pack:
+        pack(*args.pack)
+        return 0
     if args.python_scene:
         sc = pkg.pbrt_scene.load(args.python_scene, spp=args.spp, scene_dir=os.path.join(ROOT, "tests", "scenes"))
         tmp = tempfile.mkdtemp()

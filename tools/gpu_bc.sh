@@ -38,3 +38,4 @@ for name in names:
     print("%-32s bridge vs golden %.3e | python vs golden %.3e | bridge vs python %.3e" % (name, T.rel_mse(film, ref), T.rel_mse(ours, ref), T.rel_mse(film, ours)), flush=True)
 PY
 du -sh gpurun_out/desc
+# back in the container: for n in $(ls gpurun_out/desc); do python tools/desc_diff.py --pack gpurun_out/desc/$n tests/golden/desc/$n.npz; done
