@@ -1851,6 +1851,15 @@ __global__ void __launch_bounds__(WF_BLOCK) k_emit(WF wf) {
             const float dir_pdf = wf.pool.misc[slot].y * dir_pdf_scale;
             L = L + beta * Le * power_heuristic(dir_pdf, pdf_light);
         }
+#ifdef B200PT_DEBUG_PIXELS
+        {
+            const int4 ids = wf.pool.ids[slot];
+            if (B200PT_DEBUG_PIXELS(ids.x)) {
+                const S4 was = wf.pool.L[slot];
+                printf("[emit] pixel %d sample %d raw %d add %.9g %.9g %.9g %.9g\n", ids.x, ids.y, raw ? 1 : 0, L.x - was.x, L.y - was.y, L.z - was.z, L.w - was.w);
+            }
+        }
+#endif
         wf.pool.L[slot] = L;
     }
 }
@@ -2119,6 +2128,14 @@ __global__ void __launch_bounds__(WF_BLOCK, OCC ? OCC : ((MAT >= B200PT_MAT_COAT
                                 // delta lights: no MIS (megakernel_path.cu:236-239)
                                 const float w = delta ? 1.f : power_heuristic(pdf_light, pdf_bsdf);
                                 const S4 Ld = f * (Le / pdf_light) * w;
+#ifdef B200PT_DEBUG_PIXELS // debug build only (tools/build_debug_lib.py): the NEE record of chosen pixels, one line per sample
+                                if (B200PT_DEBUG_PIXELS(ids.x))
+                                    printf("[nee] pixel %d sample %d depth %d mat %d contrib %.9g %.9g %.9g %.9g p %.9g %.9g %.9g err %.9g %.9g %.9g n %.9g %.9g %.9g lp %.9g %.9g %.9g "
+                                           "lerr %.9g %.9g %.9g ln %.9g %.9g %.9g skip %d\n",
+                                           ids.x, ids.y, (ids.w >> 16) & 0xff, MAT, (beta * Ld).x, (beta * Ld).y, (beta * Ld).z, (beta * Ld).w, si.p.x, si.p.y, si.p.z,
+                                           si.err.x, si.err.y, si.err.z, si.n.x, si.n.y, si.n.z, ls.p.x, ls.p.y, ls.p.z, ls.err.x, ls.err.y, ls.err.z, ls.n.x, ls.n.y,
+                                           ls.n.z, Lr.prim);
+#endif
                                 shadow = true;
                                 sh_o = make_float4(pf.x, pf.y, pf.z, 1.f);
                                 sh_d = make_float4(sd.x, sd.y, sd.z, __int_as_float(Lr.prim)); // .w: primitive to skip
