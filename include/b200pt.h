@@ -197,6 +197,11 @@ typedef struct {
  *      (scene_builder.cu:651-656). */
 typedef struct {
     int64_t first_triangle, n_triangles;
+    /* the object's bounding box in its own space as the reference's per-object HLBVH has it (the union of its primitives' bounds,
+     * quadrics of the definition included): lo xyz, hi xyz.  lo[0] > hi[0] = derive it from the triangles.  An instance enters
+     * the scene bounds as the box of this box under its transform (TransformedPrimitive::bounds), and the scene radius scales
+     * the power of infinite and distant lights, i.e. the light sampler's probabilities. */
+    float bounds[6];
 } b200pt_object;
 typedef struct {
     int32_t object;

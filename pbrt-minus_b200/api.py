@@ -78,7 +78,7 @@ class Image(C.Structure):
 
 
 class Object(C.Structure):
-    _fields_ = [("first_triangle", C.c_int64), ("n_triangles", C.c_int64)]
+    _fields_ = [("first_triangle", C.c_int64), ("n_triangles", C.c_int64), ("bounds", C.c_float * 6)]
 
 
 class Instance(C.Structure):

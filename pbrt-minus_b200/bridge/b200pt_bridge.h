@@ -676,6 +676,9 @@ inline void B200ptBridge::render(const SceneBuilder &sb) {
             b.add_shape(shape, mat, 0u);
         }
         ob.n_triangles = (int64_t)b.tri_material.size() - ob.first_triangle;
+        const Bounds3f hb = hl->bounds(); // what TransformedPrimitive::bounds() transforms (primitives/transformed_primitive.cu:10-12)
+        ob.bounds[0] = (float)hb.p_min.x; ob.bounds[1] = (float)hb.p_min.y; ob.bounds[2] = (float)hb.p_min.z;
+        ob.bounds[3] = (float)hb.p_max.x; ob.bounds[4] = (float)hb.p_max.y; ob.bounds[5] = (float)hb.p_max.z;
         objects.push_back(ob);
     }
     // spheres and disks of instanced objects ride in the flat quadric list under the composite transform

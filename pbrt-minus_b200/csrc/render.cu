@@ -795,13 +795,50 @@ int b200pt_upload_render_data(b200pt_scene *s, const b200pt_scene_desc *desc) {
     }
     if (any_other) {
         // Bounds3::bounding_sphere of HLBVH::bounds() (scene_builder.cu:914-925, euclidean_space/bounds3.h:142-152):
-        // union of the triangle vertices and of the spheres' transformed boxes (transform.h:326-351)
+        // union of the top-level triangles' vertices, of the spheres' transformed boxes (transform.h:326-351) and, per instance, of
+        // the OBJECT's bounding box taken through the instance transform the same way (TransformedPrimitive::bounds: the box of
+        // the box, not the transformed vertices) -- the radius scales the power of infinite and distant lights, i.e. the light
+        // sampler's pmf: without the instances the sky was picked with a slightly different probability in instanced scenes
         float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-        for (int64_t t = 0; t < desc->n_triangles * 3; t++) {
+        const int64_t n_top = desc->n_objects > 0 ? desc->objects[0].first_triangle : desc->n_triangles;
+        for (int64_t t = 0; t < n_top * 3; t++) {
             const float *p = desc->P + 3 * (size_t)desc->indices[t];
             for (int k = 0; k < 3; k++) {
                 lo[k] = std::min(lo[k], p[k]);
                 hi[k] = std::max(hi[k], p[k]);
+            }
+        }
+        std::vector<float> obox((size_t)desc->n_objects * 6);
+        for (int i = 0; i < desc->n_objects; i++) {
+            float *b = &obox[6 * (size_t)i];
+            b[0] = b[1] = b[2] = INFINITY;
+            b[3] = b[4] = b[5] = -INFINITY;
+            const b200pt_object &ob = desc->objects[i];
+            if (ob.bounds[0] <= ob.bounds[3]) { // given by the front-end (includes the definition's quadrics)
+                for (int k = 0; k < 6; k++) b[k] = ob.bounds[k];
+                continue;
+            }
+            for (int64_t t = 3 * ob.first_triangle; t < 3 * (ob.first_triangle + ob.n_triangles); t++) {
+                const float *p = desc->P + 3 * (size_t)desc->indices[t];
+                for (int k = 0; k < 3; k++) {
+                    b[k] = std::min(b[k], p[k]);
+                    b[3 + k] = std::max(b[3 + k], p[k]);
+                }
+            }
+        }
+        for (int j = 0; j < desc->n_instances; j++) {
+            const b200pt_instance &in = desc->instances[j];
+            if (in.object < 0 || in.object >= desc->n_objects || desc->objects[in.object].n_triangles <= 0) continue;
+            const float *b = &obox[6 * (size_t)in.object];
+            for (int a = 0; a < 3; a++) {
+                float mn = in.render_from_instance[4 * a + 3], mx = mn;
+                for (int k = 0; k < 3; k++) {
+                    const float x = in.render_from_instance[4 * a + k] * b[k], y = in.render_from_instance[4 * a + k] * b[3 + k];
+                    mn += std::min(x, y);
+                    mx += std::max(x, y);
+                }
+                lo[a] = std::min(lo[a], mn);
+                hi[a] = std::max(hi[a], mx);
             }
         }
         for (int i = 0; i < desc->n_spheres; i++) {

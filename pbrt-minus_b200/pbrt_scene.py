@@ -860,7 +860,7 @@ class Scene:
         self.tri_light.append(tl)
 
     # ---- object instancing (two-level: one BVH8 per object, a transformed ray per instance)
-    def add_instance(self, name, mesh_recs, rfi, scene_dir):
+    def add_instance(self, name, mesh_recs, rfi, scene_dir, quadric_recs=()):
         """ObjectInstance of an object's MESHES (scene_builder.cu:845-876, primitives/transformed_primitive.cu): the object's
         triangles are stored once, in the object's own space, at the end of the triangle array (finalize_objects); each
         instance is a transform.  `mesh_recs` are the shape records of the object definition."""
@@ -868,7 +868,7 @@ class Scene:
             self.objects, self.object_index, self.instances = [], {}, []
         if name not in self.object_index:
             self.object_index[name] = len(self.objects)
-            self.objects.append({"name": name, "meshes": mesh_recs})
+            self.objects.append({"name": name, "meshes": mesh_recs, "quadrics": list(quadric_recs)})
         self.instances.append({"object": self.object_index[name], "rfi": rfi})
 
     def finalize_objects(self, scene_dir):
@@ -885,6 +885,31 @@ class Scene:
                 flip = rec["ro"] ^ swaps_handedness(rec["rfo"].m)
                 self.add_mesh(Pr, rec["idx"], rec["material"], flip, None, scene_dir, N=Nr, uv=rec.get("uv"), medium_code=0)
             ob["first"], ob["count"] = first, sum(len(i) for i in self.idx) - first
+            # the object's own bounds, as its HLBVH in the reference has them: triangle vertices and the quadrics' boxes through
+            # Transform::operator()(Bounds3f) (euclidean_space/transform.h:326-351), fp32
+            lo, hi = np.full(3, np.inf, dtype=F32), np.full(3, -np.inf, dtype=F32)
+            tris = np.concatenate(self.idx)[first:first + ob["count"]] if ob["count"] else np.zeros((0, 3), np.int32)
+            if len(tris):
+                Pall = np.concatenate(self.P)
+                v = Pall[np.unique(tris)]
+                lo, hi = np.minimum(lo, v.min(axis=0)), np.maximum(hi, v.max(axis=0))
+            for q in ob.get("quadrics", ()):
+                r = F32(q["radius"])
+                if q["kind"] == "disk":
+                    bmin, bmax = np.array([-r, -r, q["zmin"]], F32), np.array([r, r, q["zmin"]], F32)
+                else:
+                    zmin = min(max(min(F32(q["zmin"]), F32(q["zmax"])), -r), r)
+                    zmax = min(max(max(F32(q["zmin"]), F32(q["zmax"])), -r), r)
+                    bmin, bmax = np.array([-r, -r, zmin], F32), np.array([r, r, zmax], F32)
+                m = q["rfo"].m
+                qlo, qhi = m[:3, 3].astype(F32).copy(), m[:3, 3].astype(F32).copy()
+                for i in range(3):
+                    for k in range(3):
+                        a, b = F32(m[i, k] * bmin[k]), F32(m[i, k] * bmax[k])
+                        qlo[i] = F32(qlo[i] + min(a, b))
+                        qhi[i] = F32(qhi[i] + max(a, b))
+                lo, hi = np.minimum(lo, qlo), np.maximum(hi, qhi)
+            ob["bounds"] = [float(x) for x in lo] + [float(x) for x in hi]
 
     def area_light_params(self, light_params, scene_dir):
         """DiffuseAreaLight ctor (lights/diffuse_area_light.cu:9-31): Lemit (default: the colour space's illuminant), scale
@@ -997,6 +1022,7 @@ class Scene:
             oa = (api.Object * len(objs))()
             for i, o in enumerate(objs):
                 oa[i].first_triangle, oa[i].n_triangles = o["first"], o["count"]
+                oa[i].bounds[:] = o.get("bounds", [1.0, 0, 0, 0.0, 0, 0])
             remap = {id(o): i for i, o in enumerate(objs)}
             live = [n for n in self.instances if id(self.objects[n["object"]]) in remap]
             ia = (api.Instance * max(1, len(live)))()
@@ -1298,7 +1324,8 @@ def load(path=None, text=None, spp=None, integrator=None, scene_dir=None, flatte
             rfi = (render_from_world * g.ctm) * render_from_world.inverse()
             meshes = [rec for rec in instances[args[0]] if rec["kind"] == "mesh"]
             if meshes and not flatten_instances:
-                sc.add_instance(args[0], meshes, rfi, scene_dir)     # two-level: the object's tree is shared by its instances
+                sc.add_instance(args[0], meshes, rfi, scene_dir,      # two-level: the object's tree is shared by its instances
+                                quadric_recs=[rec for rec in instances[args[0]] if rec["kind"] != "mesh"])
             for rec in instances[args[0]]:
                 if rec["kind"] != "mesh" or flatten_instances:       # quadrics ride in the flat list under the composite transform
                     place_shape(rec, None if rfi.is_identity() else rfi, None)

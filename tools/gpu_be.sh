@@ -8,7 +8,7 @@ import sys, os, numpy as np, tempfile, importlib
 sys.path.insert(0, "tests")
 b200pt = importlib.import_module("pbrt-minus_b200")
 import test_render_gpu as T
-for name in ("normals_96x64_64spp", "loopsubdiv_96x64_64spp", "instances_96x64_64spp", "disk_96x64_64spp", "materials_96x64_64spp", "occluders_96x64_64spp"):
+for name in ("normals_96x64_1024spp", "loopsubdiv_96x64_1024spp", "materials_96x64_1024spp", "disk_96x64_1024spp"):
     m, ref = T.golden(name)
     text = T.scene_text(m["scene"], None, None, [tuple(e) for e in m.get("edits", [])])
     ours, _ = T.render(b200pt, text, m["spp"], tempfile.mkdtemp())
