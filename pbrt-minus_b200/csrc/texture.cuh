@@ -118,9 +118,11 @@ __device__ __forceinline__ void rgb_to_sigmoid(const TexTables &T, V3 rgb, float
         auto co = [&](int ddx, int ddy, int ddz) {
             return T.coeff[3 * ((((size_t)m * 64 + (zi + ddz)) * 64 + (yi + ddy)) * 64 + (xi + ddx)) + i];
         };
-        auto lerp = [](double t, double a, double b) { return (1 - t) * a + t * b; };
-        c_out[i] = (float)lerp(dz, lerp(dy, lerp(dx, co(0, 0, 0), co(1, 0, 0)), lerp(dx, co(0, 1, 0), co(1, 1, 0))),
-                               lerp(dy, lerp(dx, co(0, 0, 1), co(1, 0, 1)), lerp(dx, co(0, 1, 1), co(1, 1, 1))));
+        // pbrt::lerp(Real, Real, Real) (util/math.h:74-76): the double offsets and table entries are rounded to fp32 at the call and
+        // the interpolation runs in fp32 (spectrum_util/rgb_to_spectrum_data.cu:411-424)
+        auto lerp = [](float t, float a, float b) { return (1 - t) * a + t * b; };
+        c_out[i] = lerp((float)dz, lerp((float)dy, lerp((float)dx, (float)co(0, 0, 0), (float)co(1, 0, 0)), lerp((float)dx, (float)co(0, 1, 0), (float)co(1, 1, 0))),
+                        lerp((float)dy, lerp((float)dx, (float)co(0, 0, 1), (float)co(1, 0, 1)), lerp((float)dx, (float)co(0, 1, 1), (float)co(1, 1, 1))));
     }
 }
 
