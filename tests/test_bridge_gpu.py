@@ -141,8 +141,9 @@ def test_textures_through_the_bridge(b200pt, tmp_path):
     # spectrum textures on conductor eta / k: the Unbounded texture objects the reference's ConductorMaterial holds
     bridge_equals_golden_and_ctypes(b200pt, tmp_path, "metals_96x64_64spp", ctypes_tol=1e-6)
     # LightSource "infinite" with an image (lights/image_infinite_light.cu): the environment map's pixels and transform
-    # (1.3e-7 from the reference's film where the Python front-end's description gives 6e-12: the bridge hands over the reference's
-    # numerically inverted light transform, the Python side the exact transpose of the rotation)
+    # (1.3e-7 from the reference's film -- one pixel, one sample -- through EITHER front-end now that their descriptions are the
+    # same to the bit; the light's two matrices are exact transposes of each other in both, and evaluating the map's power with
+    # host rounding does not move it: a kernel-level last-bit difference, not a description one)
     bridge_equals_golden_and_ctypes(b200pt, tmp_path, "envmap_96x64_64spp", ctypes_tol=1e-6, golden_tol=1e-6)
 
 
